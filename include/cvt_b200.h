@@ -1,0 +1,168 @@
+/*
+ * cvt_b200.h — C-ABI of libcvt_b200.so, the B200 (sm_100a) implementation of the CvT
+ * forward/backward hot path of POCHUN-CHEN/Transformer-STM.
+ *
+ * The reference has no FFI of its own: its boundary for this path is the Keras-2 Python surface its
+ * scripts call.  Each entry point below cites the reference call it stands in for (paths relative
+ * to the reference repo).  The Python mirror of that surface (transformer-stm_b200/keras_api.py)
+ * binds these symbols with ctypes; INTEGRATION.md shows the binding a reference maintainer would add.
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative cvt_status; cvt_last_error() gives the message
+ *     of the calling thread's last failure.  Nothing throws, nothing falls back to the CPU.
+ *   - one cvt_model per GPU; a model is not thread-safe; all device work runs on the model's stream.
+ *   - `*_dev` pointers are device pointers, every other pointer is host memory owned by the caller.
+ *   - tensors are fp32, NHWC / [B, T, D] row-major exactly as in the reference.
+ */
+#ifndef CVT_B200_H
+#define CVT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define CVT_API __attribute__((visibility("default")))
+#else
+#define CVT_API
+#endif
+
+#define CVT_MAX_STAGES 4
+#define CVT_ABI_VERSION 1
+
+typedef enum {
+  CVT_OK = 0,
+  CVT_ERR_INVALID = -1,      /* bad argument / unsupported configuration */
+  CVT_ERR_CUDA = -2,         /* a CUDA runtime call or kernel launch failed */
+  CVT_ERR_NO_DEVICE = -3,    /* no CUDA device / wrong architecture: there is no CPU fallback */
+  CVT_ERR_STATE = -4,        /* call order (e.g. backward without a training forward) */
+  CVT_ERR_NCCL = -5
+} cvt_status;
+
+/* qkv_method of a stage — Projection.__init__, models/CvT(Par).py:92-100 */
+enum { CVT_PROJ_DW_BN = 0, CVT_PROJ_AVG = 1, CVT_PROJ_LINEAR = 2 };
+/* head of create_cvt_model, models/CvT(Par).py:326-337 */
+enum { CVT_HEAD_CLS_LN = 0, CVT_HEAD_LN_MEAN = 1 };
+/* arithmetic of the dense contractions */
+enum { CVT_PREC_FP32 = 0,   /* fp32 FFMA everywhere (exact-parity mode) */
+       CVT_PREC_TF32 = 1,   /* tcgen05 kind::tf32, fp32 accumulate in TMEM (what TF does on sm_80+) */
+       CVT_PREC_BF16 = 2 }; /* tcgen05 kind::f16 (bf16 operands), fp32 accumulate */
+/* dropout source */
+enum { CVT_DROPOUT_OFF = 0, CVT_DROPOUT_PHILOX = 1, CVT_DROPOUT_MASKS = 2 };
+
+/* One entry of the reference's `spec['stages']` list, models/CvT(Par).py:66-72 */
+typedef struct {
+  int32_t embed_dim;      /* multiple of 64 (key_dim = 64 in every reference spec) */
+  int32_t patch_size;     /* ConvEmbed kernel (7 / 3 / 3) */
+  int32_t stride;         /* ConvEmbed stride (4 / 2 / 2) */
+  int32_t num_heads;      /* embed_dim / 64 */
+  int32_t qkv_method;     /* CVT_PROJ_* */
+  int32_t with_cls_token; /* 0/1; only honoured on the last stage (as in the reference) */
+} cvt_stage_config;
+
+/* Mirrors the module-level constants + `spec` that create_cvt_model reads, models/CvT(Par).py:25-72,292 */
+typedef struct {
+  int32_t image_h, image_w, in_chans;     /* 128,128,1  (models/CvT(Par).py:40-42) */
+  int32_t n_stages;
+  cvt_stage_config stage[CVT_MAX_STAGES];
+  int32_t proc_dim;                       /* 5; 0 = CvT(Img) variant (models/CvT(Img).py:291) */
+  int32_t proc_hidden;                    /* 256 (Proc_Dense_1/2, models/CvT(Par).py:343-344) */
+  int32_t num_classes;                    /* 1 (models/CvT(Par).py:44) */
+  int32_t mlp_ratio;                      /* 4 (Mlp_dim_factor, :232) */
+  float   drop_rate;                      /* 0.1 (:116,232) */
+  float   ln_eps;                         /* 1e-6 (:248,328) */
+  float   bn_eps;                         /* 1e-3 (Keras BatchNormalization default) */
+  float   bn_momentum;                    /* 0.99 */
+  int32_t precision;                      /* CVT_PREC_* */
+  int32_t max_batch;                      /* largest per-call batch; bigger host batches are chunked */
+  int32_t device;                         /* CUDA ordinal */
+} cvt_config;
+
+typedef struct cvt_model cvt_model;
+
+/* ---- lifetime ------------------------------------------------------------------------------- */
+CVT_API int  cvt_abi_version(void);
+/* fills `cfg` with the reference configuration (spec at models/CvT(Par).py:66-72, dw_bn, cls on stage 3) */
+CVT_API void cvt_default_config(cvt_config* cfg);
+/* create_cvt_model(image_height, image_width, num_channels, proc_dim, num_classes) — models/CvT(Par).py:292 */
+CVT_API int  cvt_create(const cvt_config* cfg, cvt_model** out);
+CVT_API void cvt_destroy(cvt_model* m);
+CVT_API const char* cvt_last_error(void);
+
+/* ---- weights: model.get_weights / set_weights / save_weights / load_weights (models/CvT(Par).py:489,
+ *      models/CvT_test(Par).py:513).  Canonical names in DESIGN.md; shapes are Keras' own. ------------ */
+CVT_API int  cvt_param_count(const cvt_model* m);
+CVT_API int  cvt_param_info(const cvt_model* m, int index, const char** name, int32_t* rank, int64_t shape[4],
+                    int32_t* trainable, int64_t* numel);
+CVT_API int  cvt_param_index(const cvt_model* m, const char* name);          /* <0 if unknown */
+CVT_API int  cvt_set_param(cvt_model* m, int index, const float* host_src);
+CVT_API int  cvt_get_param(cvt_model* m, int index, float* host_dst);
+CVT_API int  cvt_get_grad(cvt_model* m, int index, float* host_dst);          /* after cvt_loss_backward; trainable only */
+/* glorot_uniform / zeros / ones exactly as the Keras layers of the reference initialise */
+CVT_API int  cvt_init_params(cvt_model* m, uint64_t seed);
+
+/* ---- model.predict / model(x, training=...) — models/CvT_test(Par).py:522, Keras train_step forward -- */
+/* img_dev [B,H,W,C], proc_dev [B,proc_dim] or NULL (Img variant), out_dev [B,num_classes]; B <= max_batch */
+CVT_API int  cvt_forward(cvt_model* m, const float* img_dev, const float* proc_dev, int batch, int training, float* out_dev);
+/* host-buffer predict: H2D, forward(training=0) in chunks of max_batch, D2H.  n may exceed max_batch. */
+CVT_API int  cvt_predict_host(cvt_model* m, const float* img, const float* proc, int64_t n, float* out);
+
+/* ---- model.compile(Adam(1e-3), 'mean_squared_error', ['mae']) + train_step — models/CvT(Par).py:464-476 */
+/* MSE / MAE of the last training forward against y_dev [B,nc]; fills every gradient (no optimizer step). */
+CVT_API int  cvt_loss_backward(cvt_model* m, const float* y_dev, float* loss_host, float* mae_host);
+/* Keras Adam step on all trainable weights with the gradients currently held (eps 1e-7, bias-corrected). */
+CVT_API int  cvt_adam_step(cvt_model* m, float lr);
+/* one full train step on device buffers: forward(training) + loss + backward + [all-reduce] + Adam +
+ * BN moving-stat update.  loss/mae are written to device scalars readable with cvt_read_metrics. */
+CVT_API int  cvt_train_step(cvt_model* m, const float* img_dev, const float* proc_dev, const float* y_dev, int batch, float lr);
+/* same from host buffers (pinned staging inside): the call `model.fit` makes per batch */
+CVT_API int  cvt_train_step_host(cvt_model* m, const float* img, const float* proc, const float* y, int batch, float lr,
+                         float* loss, float* mae);
+/* evaluation (validation pass of fit): forward(training=0) + MSE/MAE sums over n host samples */
+CVT_API int  cvt_evaluate_host(cvt_model* m, const float* img, const float* proc, const float* y, int64_t n,
+                       float* loss, float* mae);
+CVT_API int  cvt_read_metrics(cvt_model* m, float* loss, float* mae);         /* synchronises the model stream */
+CVT_API int  cvt_optimizer_reset(cvt_model* m);                                /* zero m, v, t (a fresh compile) */
+CVT_API int64_t cvt_optimizer_step_count(const cvt_model* m);
+
+/* ---- dropout (layers.Dropout at models/CvT(Par).py:189,255,257) ------------------------------- */
+/* PHILOX: keep-masks come from Philox4x32-10(seed, step, site) — reproducible by the oracle.
+ * MASKS : the caller supplies uint8 keep-masks per site with cvt_set_dropout_mask (parity tests). */
+CVT_API int  cvt_set_dropout(cvt_model* m, int mode, uint64_t seed);
+/* site = stage*4 + {0: attention proj, 1: mlp hidden, 2: mlp out}; count = B*Tc*width */
+CVT_API int  cvt_set_dropout_mask(cvt_model* m, int site, const uint8_t* host_mask, int64_t count);
+
+/* ---- Grad-CAM taps: Model(inputs, [get_layer(name).output, output]) + tape.gradient
+ *      (tools/grad_cam_CvT.py:430-457) and the per-layer parity tests --------------------------------- */
+/* copies a named activation of the last forward to host; returns its element count (<0 on error).
+ * names: "s{i}.embed|x0|xn|conv_qkv|qkv0|qkv1|qkv2|attn_o|a1|x1|y|hpre|hact|x2|out", "head.feat", "pred" */
+CVT_API int64_t cvt_get_tap(cvt_model* m, const char* name, float* host_dst, int64_t capacity);
+/* d(sum_b dout[b,:]·pred[b,:]) / d tap for the block output "s{i}.x2"; forward must have run.  */
+CVT_API int  cvt_backward_to_tap(cvt_model* m, const float* dout_host, const char* name, float* host_dst, int64_t capacity);
+
+/* ---- data-parallel training: one process per GPU, gradients summed over NCCL/NVLink ------- */
+/* unique_id: 128 bytes from cvt_comm_unique_id on rank 0, broadcast by the host (torch.distributed).  */
+CVT_API int  cvt_comm_unique_id(uint8_t id_out[128]);
+CVT_API int  cvt_comm_init(cvt_model* m, const uint8_t unique_id[128], int rank, int world);
+CVT_API int  cvt_comm_destroy(cvt_model* m);
+/* flat trainable arenas so the host may run its own collective instead (torch.distributed plumbing) */
+CVT_API int  cvt_grad_arena(cvt_model* m, float** grads_dev, int64_t* count);
+CVT_API int  cvt_param_arena(cvt_model* m, float** params_dev, int64_t* count);
+
+/* ---- streams / graphs / bookkeeping ----------------------------------------------------------------------- */
+CVT_API int  cvt_synchronize(cvt_model* m);
+CVT_API void* cvt_stream(cvt_model* m);                     /* cudaStream_t the model launches on */
+CVT_API int  cvt_set_graphs(cvt_model* m, int enable);      /* capture train/predict steps into CUDA graphs */
+CVT_API int64_t cvt_kernel_launches(const cvt_model* m);    /* kernels this model has launched so far (own kernels only) */
+CVT_API int64_t cvt_workspace_bytes(const cvt_model* m);
+/* name of the kernel group timed last + its device time; used by bench.py's roofline leg */
+CVT_API int  cvt_profile_step(cvt_model* m, const float* img_dev, const float* proc_dev, const float* y_dev, int batch,
+                      int training, int max_entries, const char** names, float* ms, int* n_entries);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CVT_B200_H */

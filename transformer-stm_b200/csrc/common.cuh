@@ -1,0 +1,81 @@
+// Shared helpers for libcvt_b200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+
+namespace cvt {
+
+// ---- error plumbing: every launcher returns a cudaError_t; the API layer turns it into cvt_status ----
+void set_error(const std::string& msg);
+extern thread_local long long g_launch_count;      // kernels launched by this thread (own kernels only)
+
+#define CVT_CUDA(expr)                                                                      \
+  do {                                                                                      \
+    cudaError_t _e = (expr);                                                                \
+    if (_e != cudaSuccess) {                                                                \
+      ::cvt::set_error(std::string(#expr) + ": " + cudaGetErrorString(_e) + " @" + __FILE__ + ":" + std::to_string(__LINE__)); \
+      return _e;                                                                            \
+    }                                                                                       \
+  } while (0)
+
+#define CVT_LAUNCH_CHECK()                                                                  \
+  do {                                                                                      \
+    ::cvt::g_launch_count++;                                                                \
+    cudaError_t _e = cudaGetLastError();                                                    \
+    if (_e != cudaSuccess) {                                                                \
+      ::cvt::set_error(std::string("kernel launch: ") + cudaGetErrorString(_e) + " @" + __FILE__ + ":" + std::to_string(__LINE__)); \
+      return _e;                                                                            \
+    }                                                                                       \
+  } while (0)
+
+constexpr int kNumSMs = 148;
+
+__host__ __device__ inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+__host__ __device__ inline long long cdivl(long long a, long long b) { return (a + b - 1) / b; }
+
+// token-row remap used to splice the cls row in and out of [B, Tc, D] tensors:
+// r -> (r / period) * stride + r % period + off      (period == 0: identity)
+struct RowMap {
+  int period, stride, off;
+  __host__ __device__ inline long long operator()(long long r) const {
+    return period ? (r / period) * (long long)stride + (r % period) + off : r;
+  }
+};
+inline RowMap rowmap_none() { return RowMap{0, 0, 0}; }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// exact-erf GELU (tf.nn.gelu default, approximate=False) and its derivative
+__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f)); }
+__device__ __forceinline__ float gelu_erf_grad(float x) {
+  const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752440f));
+  const float pdf = 0.39894228040143267794f * __expf(-0.5f * x * x);
+  return cdf + x * pdf;
+}
+
+// ---- Philox4x32-10, bit-identical to oracle/cvt_oracle.py:philox4x32 ----
+__host__ __device__ inline void philox4x32_10(uint32_t c[4], uint32_t k0, uint32_t k1) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const unsigned long long p0 = (unsigned long long)c[0] * 0xD2511F53ull;
+    const unsigned long long p1 = (unsigned long long)c[2] * 0xCD9E8D57ull;
+    const uint32_t hi0 = (uint32_t)(p0 >> 32), lo0 = (uint32_t)p0;
+    const uint32_t hi1 = (uint32_t)(p1 >> 32), lo1 = (uint32_t)p1;
+    const uint32_t n0 = hi1 ^ c[1] ^ k0, n1 = lo1, n2 = hi0 ^ c[3] ^ k1, n3 = lo0;
+    c[0] = n0; c[1] = n1; c[2] = n2; c[3] = n3;
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+}
+
+}  // namespace cvt

@@ -1,0 +1,1019 @@
+// C-ABI of libcvt_b200 (include/cvt_b200.h): model construction, weights, forward / backward / Adam orchestration.
+// The network built here is the one create_cvt_model builds in the reference (models/CvT(Par).py:292-354,
+// models/CvT(Img).py:291-341); layer semantics are the Keras-2 ones restated in SURVEY.md section 9.
+#include <dlfcn.h>
+#include <math.h>
+#include <string.h>
+
+#include <algorithm>
+#include <random>
+
+#include "model.cuh"
+
+namespace cvt {
+
+static thread_local std::string g_err;
+thread_local long long g_launch_count = 0;
+void set_error(const std::string& msg) { g_err = msg; }
+
+#define API_CUDA(expr)                                   \
+  do {                                                   \
+    cudaError_t _e = (expr);                             \
+    if (_e != cudaSuccess) {                             \
+      if (g_err.empty() || g_err.find(cudaGetErrorString(_e)) == std::string::npos) \
+        set_error(std::string(#expr) + ": " + cudaGetErrorString(_e)); \
+      return CVT_ERR_CUDA;                               \
+    }                                                    \
+  } while (0)
+
+// ---- profiling marks (cvt_profile_step) -----------------------------------------------------------------
+struct ProfMark { const char* name; cudaEvent_t ev; };
+static thread_local std::vector<ProfMark>* g_prof = nullptr;
+static inline void prof_mark(cudaStream_t s, const char* name) {
+  if (!g_prof) return;
+  cudaEvent_t e; cudaEventCreate(&e); cudaEventRecord(e, s);
+  g_prof->push_back({name, e});
+}
+static const char* kStageNames[CVT_MAX_STAGES][12] = {
+  {"s1.conv_embed", "s1.ln_proj_bn", "s1.qkv_gemm", "s1.attention", "s1.out_gemm", "s1.mlp", "s1.bwd_mlp", "s1.bwd_out", "s1.bwd_attention", "s1.bwd_qkv", "s1.bwd_proj_ln", "s1.bwd_conv"},
+  {"s2.conv_embed", "s2.ln_proj_bn", "s2.qkv_gemm", "s2.attention", "s2.out_gemm", "s2.mlp", "s2.bwd_mlp", "s2.bwd_out", "s2.bwd_attention", "s2.bwd_qkv", "s2.bwd_proj_ln", "s2.bwd_conv"},
+  {"s3.conv_embed", "s3.ln_proj_bn", "s3.qkv_gemm", "s3.attention", "s3.out_gemm", "s3.mlp", "s3.bwd_mlp", "s3.bwd_out", "s3.bwd_attention", "s3.bwd_qkv", "s3.bwd_proj_ln", "s3.bwd_conv"},
+  {"s4.conv_embed", "s4.ln_proj_bn", "s4.qkv_gemm", "s4.attention", "s4.out_gemm", "s4.mlp", "s4.bwd_mlp", "s4.bwd_out", "s4.bwd_attention", "s4.bwd_qkv", "s4.bwd_proj_ln", "s4.bwd_conv"}};
+
+// ---- contraction dispatch ----------------------------------------------------------------------------------
+cudaError_t run_gemm(const Model* m, const GemmP& p, cudaStream_t s) {
+  if (m->cfg.precision != CVT_PREC_FP32 && gemm_tc_supports(p)) return launch_gemm_tc(p, s);
+  return launch_gemm_simt(p, s);
+}
+
+static int auto_splitk(int M, int N, int K, int batch) {
+  const int tiles = cdiv(M, 64) * cdiv(N, 64) * batch;
+  int sk = cdiv(kNumSMs * 4, tiles);
+  const int maxsk = std::max(1, K / 128);
+  return std::max(1, std::min(sk, maxsk));
+}
+
+static GemmP dense_fwd(const float* A, long long lda, int M, int K, const float* W, int N, const float* bias, float* C, long long ldc) {
+  GemmP p; p.M = M; p.N = N; p.K = K; p.A = A; p.lda = lda; p.B = W; p.ldb = N; p.b_mode = B_KN; p.C = C; p.ldc = ldc;
+  if (bias) { p.bias = bias; p.epi |= EPI_BIAS; }
+  return p;
+}
+// dX[M,Kin] = dY[M,Nout] * W[Kin,Nout]^T
+static GemmP dense_dgrad(const float* dY, long long lddy, int M, int Nout, const float* W, int Kin, float* dX, long long lddx) {
+  GemmP p; p.M = M; p.N = Kin; p.K = Nout; p.A = dY; p.lda = lddy; p.B = W; p.ldb = Nout; p.b_mode = B_NK; p.C = dX; p.ldc = lddx;
+  return p;
+}
+// dW[Kin,Nout] += X[tokens,Kin]^T * dY[tokens,Nout]
+static GemmP dense_wgrad(const float* X, long long ldx, int Kin, const float* dY, long long lddy, int Nout, int tokens, float* dW) {
+  GemmP p; p.M = Kin; p.N = Nout; p.K = tokens; p.A = X; p.lda = ldx; p.a_mode = A_TRANS; p.B = dY; p.ldb = lddy; p.b_mode = B_KN;
+  p.C = dW; p.ldc = Nout; p.epi = EPI_ATOMIC; p.splitk = auto_splitk(Kin, Nout, tokens, 1);
+  return p;
+}
+
+// ---- parameters ------------------------------------------------------------------------------------------------
+static int64_t add_param(Model* m, const std::string& name, std::initializer_list<int64_t> shape, bool trainable) {
+  ParamInfo pi; pi.name = name; pi.rank = (int)shape.size(); pi.trainable = trainable;
+  int64_t n = 1; int i = 0;
+  for (int64_t d : shape) { pi.shape[i++] = d; n *= d; }
+  pi.numel = n;
+  int64_t& cursor = trainable ? m->n_train : m->n_state;
+  pi.offset = cursor;
+  cursor += (n + 3) / 4 * 4;
+  m->params.push_back(pi);
+  return pi.offset;
+}
+
+static void build_params(Model* m) {
+  const cvt_config& c = m->cfg;
+  int cin = c.in_chans;
+  for (int i = 0; i < m->n_stages; ++i) {
+    const StageGeo& g = m->geo[i];
+    StageW& w = m->w[i];
+    const int64_t D = g.D, N = g.heads, hd = D / N;
+    const std::string ps = "stage" + std::to_string(i + 1);
+    const std::string t = ps + "_transformer";
+    w.conv_w = add_param(m, ps + "_ConvEmbed/kernel", {g.k, g.k, cin, D}, true);
+    w.conv_b = add_param(m, ps + "_ConvEmbed/bias", {D}, true);
+    w.cls = g.has_cls ? add_param(m, t + "/cls_token", {1, 1, 1, D}, true) : -1;
+    w.ln_g = add_param(m, t + "/norm1/gamma", {D}, true);
+    w.ln_b = add_param(m, t + "/norm1/beta", {D}, true);
+    w.dw = w.bn_g = w.bn_b = w.bn_mm = w.bn_mv = -1;
+    const char* qkv[3] = {"q", "k", "v"};
+    if (g.method == CVT_PROJ_DW_BN) {
+      for (int z = 0; z < 3; ++z) { int64_t o = add_param(m, t + "/attn/" + qkv[z] + "_proj/depthwise_kernel", {3, 3, D, 1}, true); if (z == 0) w.dw = o; }
+      for (int z = 0; z < 3; ++z) { int64_t o = add_param(m, t + "/attn/" + qkv[z] + "_proj/bn/gamma", {D}, true); if (z == 0) w.bn_g = o; }
+      for (int z = 0; z < 3; ++z) { int64_t o = add_param(m, t + "/attn/" + qkv[z] + "_proj/bn/beta", {D}, true); if (z == 0) w.bn_b = o; }
+      for (int z = 0; z < 3; ++z) { int64_t o = add_param(m, t + "/attn/" + qkv[z] + "_proj/bn/moving_mean", {D}, false); if (z == 0) w.bn_mm = o; }
+      for (int z = 0; z < 3; ++z) { int64_t o = add_param(m, t + "/attn/" + qkv[z] + "_proj/bn/moving_variance", {D}, false); if (z == 0) w.bn_mv = o; }
+    }
+    for (int z = 0; z < 3; ++z) { int64_t o = add_param(m, t + "/attn/proj_" + qkv[z] + "/kernel", {D, D}, true); if (z == 0) w.pw = o; }
+    for (int z = 0; z < 3; ++z) { int64_t o = add_param(m, t + "/attn/proj_" + qkv[z] + "/bias", {D}, true); if (z == 0) w.pb = o; }
+    const char* mh[3] = {"query", "key", "value"};
+    for (int z = 0; z < 3; ++z) { int64_t o = add_param(m, t + "/attn/mha/" + mh[z] + "/kernel", {D, N, hd}, true); if (z == 0) w.mw = o; }
+    for (int z = 0; z < 3; ++z) { int64_t o = add_param(m, t + "/attn/mha/" + mh[z] + "/bias", {N, hd}, true); if (z == 0) w.mb = o; }
+    w.ow = add_param(m, t + "/attn/mha/attention_output/kernel", {N, hd, D}, true);
+    w.ob = add_param(m, t + "/attn/mha/attention_output/bias", {D}, true);
+    w.prw = add_param(m, t + "/attn/proj/kernel", {D, D}, true);
+    w.prb = add_param(m, t + "/attn/proj/bias", {D}, true);
+    w.f1w = add_param(m, t + "/mlp/fc1/kernel", {D, c.mlp_ratio * D}, true);
+    w.f1b = add_param(m, t + "/mlp/fc1/bias", {c.mlp_ratio * D}, true);
+    w.f2w = add_param(m, t + "/mlp/fc2/kernel", {c.mlp_ratio * D, D}, true);
+    w.f2b = add_param(m, t + "/mlp/fc2/bias", {D}, true);
+    cin = (int)D;
+  }
+  const int64_t D = m->d_last;
+  m->hn_g = add_param(m, "head_norm/gamma", {D}, true);
+  m->hn_b = add_param(m, "head_norm/beta", {D}, true);
+  if (c.proc_dim > 0) {
+    m->pd1w = add_param(m, "Proc_Dense_1/kernel", {c.proc_dim, c.proc_hidden}, true);
+    m->pd1b = add_param(m, "Proc_Dense_1/bias", {c.proc_hidden}, true);
+    m->pd2w = add_param(m, "Proc_Dense_2/kernel", {c.proc_hidden, c.proc_hidden}, true);
+    m->pd2b = add_param(m, "Proc_Dense_2/bias", {c.proc_hidden}, true);
+  }
+  m->fw = add_param(m, "Final_Dense/kernel", {m->feat_dim, c.num_classes}, true);
+  m->fb = add_param(m, "Final_Dense/bias", {c.num_classes}, true);
+}
+
+// ---- workspace ---------------------------------------------------------------------------------------------------
+struct Bump {
+  char* base = nullptr; int64_t off = 0;
+  template <typename T> T* take(int64_t count) {
+    off = (off + 255) / 256 * 256;
+    T* p = base ? reinterpret_cast<T*>(base + off) : nullptr;
+    off += count * (int64_t)sizeof(T);
+    return p;
+  }
+};
+
+static void carve(Model* m, Bump& b) {
+  const cvt_config& c = m->cfg;
+  const int64_t MB = c.max_batch;
+  int64_t maxRD = 0, maxRH = 0, maxS = 0, maxIn = 0;
+  const bool need_scores = true;   // the fp32 attention path (also the fallback of the tensor-core path) keeps P
+  for (int i = 0; i < m->n_stages; ++i) {
+    const StageGeo& g = m->geo[i];
+    StageBuf& s = m->buf[i];
+    const int64_t R = MB * g.Tc, RD = R * g.D, RH = RD * c.mlp_ratio;
+    const int64_t S = MB * g.heads * (int64_t)g.Tc * g.Tc;
+    maxRD = std::max(maxRD, RD); maxRH = std::max(maxRH, RH); maxS = std::max(maxS, S);
+    maxIn = std::max(maxIn, MB * (int64_t)g.hin * g.win * g.cin);
+    s.x0 = b.take<float>(RD); s.xn = b.take<float>(RD); s.conv = b.take<float>(3 * RD);
+    s.qkv1 = b.take<float>(3 * RD); s.qkv2 = b.take<float>(3 * RD);
+    s.attn_o = b.take<float>(RD); s.a1 = b.take<float>(RD); s.x1 = b.take<float>(RD); s.y = b.take<float>(RD);
+    s.hpre = b.take<float>(RH); s.hact = b.take<float>(RH); s.x2 = b.take<float>(RD);
+    s.lna_mean = b.take<float>(R); s.lna_rstd = b.take<float>(R); s.lnb_mean = b.take<float>(R); s.lnb_rstd = b.take<float>(R);
+    s.bn_stats = b.take<float>(6 * g.D); s.bn_scale = b.take<float>(3 * g.D); s.bn_shift = b.take<float>(3 * g.D);
+    s.bn_mean = b.take<float>(3 * g.D); s.bn_rstd = b.take<float>(3 * g.D);
+    s.scores = need_scores ? b.take<float>(S) : nullptr;
+    s.lse = b.take<float>(MB * g.heads * (int64_t)g.Tc);
+    s.mask_proj = b.take<uint8_t>(RD); s.mask1 = b.take<uint8_t>(RH); s.mask2 = b.take<uint8_t>(RD);
+  }
+  const StageGeo& gl = m->geo[m->n_stages - 1];
+  m->feat = b.take<float>(MB * m->feat_dim);
+  m->hln = b.take<float>(MB * (int64_t)gl.Tc * gl.D);
+  m->h_mean = b.take<float>(MB * (int64_t)gl.Tc); m->h_rstd = b.take<float>(MB * (int64_t)gl.Tc);
+  m->p1 = b.take<float>(MB * std::max(1, c.proc_hidden));
+  m->pred = b.take<float>(MB * c.num_classes);
+  m->dpred = b.take<float>(MB * c.num_classes);
+  m->dfeat = b.take<float>(MB * m->feat_dim);
+  m->dp1 = b.take<float>(MB * std::max(1, c.proc_hidden));
+  m->dhln = b.take<float>(MB * (int64_t)gl.Tc * gl.D);
+  m->metrics = b.take<float>(4);
+  m->gX[0] = b.take<float>(maxRD); m->gX[1] = b.take<float>(maxRD);
+  m->gH = b.take<float>(maxRH); m->gC = b.take<float>(maxRD); m->gD = b.take<float>(maxRD); m->gE = b.take<float>(maxRD);
+  m->gM = b.take<float>(maxRD); m->gQ = b.take<float>(3 * maxRD); m->gQ2 = b.take<float>(3 * maxRD);
+  m->gS = need_scores ? b.take<float>(maxS) : nullptr;
+  m->in_img = b.take<float>(maxIn > 0 ? MB * (int64_t)c.image_h * c.image_w * c.in_chans : 0);
+  m->in_proc = b.take<float>(MB * std::max(1, c.proc_dim));
+  m->in_y = b.take<float>(MB * c.num_classes);
+  m->out_pred = b.take<float>(MB * c.num_classes);
+  m->lr_dev = b.take<float>(4);
+}
+
+static int same_pad(int n, int k, int s, int* before) {
+  const int out = (n + s - 1) / s;
+  const int total = std::max((out - 1) * s + k - n, 0);
+  *before = total / 2;
+  return out;
+}
+
+}  // namespace cvt
+
+using namespace cvt;
+
+struct cvt_model { Model m; };
+
+extern "C" {
+
+int cvt_abi_version(void) { return CVT_ABI_VERSION; }
+const char* cvt_last_error(void) { return g_err.c_str(); }
+
+void cvt_default_config(cvt_config* c) {
+  memset(c, 0, sizeof(*c));
+  c->image_h = 128; c->image_w = 128; c->in_chans = 1; c->n_stages = 3;
+  const int dims[3] = {64, 128, 256}, patch[3] = {7, 3, 3}, stride[3] = {4, 2, 2}, heads[3] = {1, 2, 4};
+  for (int i = 0; i < 3; ++i) {
+    c->stage[i].embed_dim = dims[i]; c->stage[i].patch_size = patch[i]; c->stage[i].stride = stride[i];
+    c->stage[i].num_heads = heads[i]; c->stage[i].qkv_method = CVT_PROJ_DW_BN; c->stage[i].with_cls_token = (i == 2);
+  }
+  c->proc_dim = 5; c->proc_hidden = 256; c->num_classes = 1; c->mlp_ratio = 4;
+  c->drop_rate = 0.1f; c->ln_eps = 1e-6f; c->bn_eps = 1e-3f; c->bn_momentum = 0.99f;
+  c->precision = CVT_PREC_FP32; c->max_batch = 64; c->device = 0;
+}
+
+int cvt_create(const cvt_config* cfg, cvt_model** out) {
+  if (!cfg || !out) { set_error("cvt_create: null argument"); return CVT_ERR_INVALID; }
+  *out = nullptr;
+  const cvt_config& c = *cfg;
+  if (c.n_stages < 1 || c.n_stages > CVT_MAX_STAGES || c.image_h < 1 || c.image_w < 1 || c.in_chans < 1 || c.num_classes < 1 ||
+      c.max_batch < 1 || c.mlp_ratio < 1 || c.proc_dim < 0 || (c.proc_dim > 0 && c.proc_hidden < 1)) {
+    set_error("cvt_create: invalid configuration"); return CVT_ERR_INVALID;
+  }
+  if (c.drop_rate < 0.f || c.drop_rate >= 1.f) { set_error("cvt_create: drop_rate must be in [0,1)"); return CVT_ERR_INVALID; }
+  for (int i = 0; i < c.n_stages; ++i) {
+    const cvt_stage_config& s = c.stage[i];
+    if (s.embed_dim < 64 || s.embed_dim % 64 != 0 || s.embed_dim > 512 || s.num_heads * 64 != s.embed_dim) {
+      set_error("cvt_create: embed_dim must be a multiple of 64 (<= 512) with num_heads = embed_dim / 64 (key_dim 64)"); return CVT_ERR_INVALID;
+    }
+    if (s.patch_size < 1 || s.stride < 1 || s.qkv_method < 0 || s.qkv_method > 2) { set_error("cvt_create: bad stage spec"); return CVT_ERR_INVALID; }
+    if (s.with_cls_token && i != c.n_stages - 1) { set_error("cvt_create: cls token is supported on the last stage only"); return CVT_ERR_INVALID; }
+  }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= c.device) {
+    (void)cudaGetLastError();
+    set_error("cvt_create: no CUDA device " + std::to_string(c.device) + " (libcvt_b200 has no CPU fallback)");
+    return CVT_ERR_NO_DEVICE;
+  }
+  cudaDeviceProp prop;
+  API_CUDA(cudaGetDeviceProperties(&prop, c.device));
+  if (prop.major != 10) {
+    set_error(std::string("cvt_create: device is sm_") + std::to_string(prop.major) + std::to_string(prop.minor) + ", this library is built for sm_100a only");
+    return CVT_ERR_NO_DEVICE;
+  }
+  API_CUDA(cudaSetDevice(c.device));
+
+  cvt_model* h = new cvt_model();
+  Model* m = &h->m;
+  m->cfg = c; m->n_stages = c.n_stages;
+  int hh = c.image_h, ww = c.image_w, cin = c.in_chans;
+  for (int i = 0; i < c.n_stages; ++i) {
+    StageGeo& g = m->geo[i];
+    const cvt_stage_config& s = c.stage[i];
+    g.hin = hh; g.win = ww; g.cin = cin; g.k = s.patch_size; g.s = s.stride;
+    g.H = same_pad(hh, g.k, g.s, &g.pt); g.W = same_pad(ww, g.k, g.s, &g.pl);
+    g.D = s.embed_dim; g.T = g.H * g.W; g.has_cls = s.with_cls_token ? 1 : 0; g.Tc = g.T + g.has_cls;
+    g.heads = s.num_heads; g.method = s.qkv_method;
+    hh = g.H; ww = g.W; cin = g.D;
+  }
+  m->d_last = m->geo[c.n_stages - 1].D;
+  m->head_kind = m->geo[c.n_stages - 1].has_cls ? CVT_HEAD_CLS_LN : CVT_HEAD_LN_MEAN;
+  m->feat_dim = m->d_last + (c.proc_dim > 0 ? c.proc_hidden : 0);
+  build_params(m);
+
+  Bump measure; carve(m, measure);
+  const int64_t arena_bytes = (4 * m->n_train + std::max<int64_t>(m->n_state, 4)) * (int64_t)sizeof(float);
+  m->workspace_bytes = measure.off + 256 + arena_bytes + 1024;
+  cudaError_t e = cudaMalloc(&m->workspace, (size_t)m->workspace_bytes);
+  if (e != cudaSuccess) { set_error(std::string("cvt_create: cudaMalloc of ") + std::to_string(m->workspace_bytes) + " bytes: " + cudaGetErrorString(e)); delete h; return CVT_ERR_CUDA; }
+  Bump b; b.base = reinterpret_cast<char*>(m->workspace);
+  m->P = b.take<float>(m->n_train); m->G = b.take<float>(m->n_train); m->Mo = b.take<float>(m->n_train); m->Vo = b.take<float>(m->n_train);
+  m->St = b.take<float>(std::max<int64_t>(m->n_state, 4));
+  carve(m, b);
+  API_CUDA(cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking));
+  API_CUDA(cudaMemsetAsync(m->workspace, 0, (size_t)m->workspace_bytes, m->stream));
+  API_CUDA(cudaMallocHost(&m->pin_metrics, 4 * sizeof(float)));
+  API_CUDA(cudaStreamSynchronize(m->stream));
+  *out = h;
+  return CVT_OK;
+}
+
+void cvt_destroy(cvt_model* h) {
+  if (!h) return;
+  Model* m = &h->m;
+  cvt_comm_destroy(h);
+  if (m->train_graph) cudaGraphExecDestroy(m->train_graph);
+  if (m->fwd_graph) cudaGraphExecDestroy(m->fwd_graph);
+  if (m->stream) { cudaStreamSynchronize(m->stream); cudaStreamDestroy(m->stream); }
+  if (m->workspace) cudaFree(m->workspace);
+  if (m->pin_metrics) cudaFreeHost(m->pin_metrics);
+  delete h;
+}
+
+int cvt_param_count(const cvt_model* h) { return h ? (int)h->m.params.size() : CVT_ERR_INVALID; }
+
+int cvt_param_info(const cvt_model* h, int index, const char** name, int32_t* rank, int64_t shape[4], int32_t* trainable, int64_t* numel) {
+  if (!h || index < 0 || index >= (int)h->m.params.size()) { set_error("cvt_param_info: bad index"); return CVT_ERR_INVALID; }
+  const ParamInfo& p = h->m.params[index];
+  if (name) *name = p.name.c_str();
+  if (rank) *rank = p.rank;
+  if (shape) for (int i = 0; i < 4; ++i) shape[i] = p.shape[i];
+  if (trainable) *trainable = p.trainable ? 1 : 0;
+  if (numel) *numel = p.numel;
+  return CVT_OK;
+}
+
+int cvt_param_index(const cvt_model* h, const char* name) {
+  if (!h || !name) return CVT_ERR_INVALID;
+  for (size_t i = 0; i < h->m.params.size(); ++i) if (h->m.params[i].name == name) return (int)i;
+  return CVT_ERR_INVALID;
+}
+
+static float* param_ptr(Model* m, const ParamInfo& p, float* train_arena) { return (p.trainable ? train_arena : m->St) + p.offset; }
+
+int cvt_set_param(cvt_model* h, int index, const float* src) {
+  if (!h || !src || index < 0 || index >= (int)h->m.params.size()) { set_error("cvt_set_param: bad argument"); return CVT_ERR_INVALID; }
+  Model* m = &h->m; const ParamInfo& p = m->params[index];
+  API_CUDA(cudaMemcpyAsync(param_ptr(m, p, m->P), src, p.numel * sizeof(float), cudaMemcpyHostToDevice, m->stream));
+  API_CUDA(cudaStreamSynchronize(m->stream));
+  return CVT_OK;
+}
+int cvt_get_param(cvt_model* h, int index, float* dst) {
+  if (!h || !dst || index < 0 || index >= (int)h->m.params.size()) { set_error("cvt_get_param: bad argument"); return CVT_ERR_INVALID; }
+  Model* m = &h->m; const ParamInfo& p = m->params[index];
+  API_CUDA(cudaMemcpyAsync(dst, param_ptr(m, p, m->P), p.numel * sizeof(float), cudaMemcpyDeviceToHost, m->stream));
+  API_CUDA(cudaStreamSynchronize(m->stream));
+  return CVT_OK;
+}
+int cvt_get_grad(cvt_model* h, int index, float* dst) {
+  if (!h || !dst || index < 0 || index >= (int)h->m.params.size()) { set_error("cvt_get_grad: bad argument"); return CVT_ERR_INVALID; }
+  Model* m = &h->m; const ParamInfo& p = m->params[index];
+  if (!p.trainable) { set_error("cvt_get_grad: parameter is not trainable"); return CVT_ERR_INVALID; }
+  API_CUDA(cudaMemcpyAsync(dst, m->G + p.offset, p.numel * sizeof(float), cudaMemcpyDeviceToHost, m->stream));
+  API_CUDA(cudaStreamSynchronize(m->stream));
+  return CVT_OK;
+}
+
+int cvt_init_params(cvt_model* h, uint64_t seed) {
+  if (!h) return CVT_ERR_INVALID;
+  Model* m = &h->m;
+  std::mt19937_64 rng(seed);
+  std::vector<float> host;
+  for (size_t i = 0; i < m->params.size(); ++i) {
+    const ParamInfo& p = m->params[i];
+    host.assign(p.numel, 0.f);
+    const std::string leaf = p.name.substr(p.name.rfind('/') + 1);
+    if (leaf == "kernel" || leaf == "depthwise_kernel") {
+      // keras glorot_uniform: receptive = prod(shape[:-2]); fan_in = shape[-2]*rec; fan_out = shape[-1]*rec
+      double fi, fo;
+      if (p.rank == 2) { fi = (double)p.shape[0]; fo = (double)p.shape[1]; }
+      else { double rec = 1; for (int d = 0; d < p.rank - 2; ++d) rec *= (double)p.shape[d]; fi = p.shape[p.rank - 2] * rec; fo = p.shape[p.rank - 1] * rec; }
+      const double lim = sqrt(6.0 / (fi + fo));
+      std::uniform_real_distribution<double> U(-lim, lim);
+      for (auto& v : host) v = (float)U(rng);
+    } else if (leaf == "gamma" || leaf == "moving_variance") {
+      for (auto& v : host) v = 1.f;
+    }
+    int r = cvt_set_param(h, (int)i, host.data());
+    if (r != CVT_OK) return r;
+  }
+  return CVT_OK;
+}
+
+// =====================================================================================================================
+// forward
+// =====================================================================================================================
+static cudaError_t stage_forward(Model* m, int si, const float* xin, long long xin_bstride, int xin_boff, int B, int training) {
+  const StageGeo& g = m->geo[si]; const StageW& w = m->w[si]; StageBuf& a = m->buf[si];
+  const cvt_config& c = m->cfg;
+  cudaStream_t s = m->stream;
+  const int D = g.D, R = B * g.Tc, H4 = c.mlp_ratio * D;
+  const long long RD = (long long)R * D;
+  const bool drop = training && m->dropout_mode != CVT_DROPOUT_OFF && c.drop_rate > 0.f;
+  const float keep_scale = 1.f / (1.f - c.drop_rate);
+  float* P = m->P;
+
+  prof_mark(s, kStageNames[si][0]);
+  {  // ConvEmbed: Conv2D(D, patch, stride, 'same') + bias — models/CvT(Par).py:203-212 (its LayerNorm is dead code)
+    GemmP p; p.M = B * g.T; p.N = D; p.K = g.k * g.k * g.cin;
+    p.A = xin; p.a_mode = A_CONV; p.cv = ConvGeom{g.hin, g.win, g.cin, g.H, g.W, g.k, g.s, g.pt, g.pl, xin_bstride, xin_boff};
+    p.B = P + w.conv_w; p.ldb = D; p.b_mode = B_KN; p.C = a.x0; p.ldc = D;
+    if (g.has_cls) p.c_map = RowMap{g.T, g.Tc, 1};
+    p.bias = P + w.conv_b; p.epi = EPI_BIAS;
+    CVT_CUDA(run_gemm(m, p, s));
+    if (g.has_cls) CVT_CUDA(launch_fill_rows(a.x0, RowMap{1, g.Tc, 0}, D, P + w.cls, B, D, s));   // :264-268
+  }
+  prof_mark(s, kStageNames[si][1]);
+  // x = norm1(inputs)  :272
+  CVT_CUDA(launch_ln_fwd(a.x0, rowmap_none(), D, P + w.ln_g, P + w.ln_b, c.ln_eps, a.xn, D, a.lna_mean, a.lna_rstd, R, D, s));
+  {  // q/k/v Projection  :157-170
+    const bool bn = g.method == CVT_PROJ_DW_BN;
+    DwProjP dp; dp.xn = a.xn; dp.out = a.conv; dp.out_bs = RD; dp.w = bn ? P + w.dw : nullptr;
+    const int mz = g.method == CVT_PROJ_DW_BN ? 0 : (g.method == CVT_PROJ_AVG ? 1 : 2);
+    dp.method[0] = (g.method == CVT_PROJ_AVG) ? 2 : mz;      // q is 'linear' when the stage method is 'avg'  (:127)
+    dp.method[1] = mz; dp.method[2] = mz;
+    dp.B = B; dp.H = g.H; dp.W = g.W; dp.D = D; dp.Tc = g.Tc; dp.has_cls = g.has_cls;
+    dp.stats = (bn && training) ? a.bn_stats : nullptr;
+    if (dp.stats) CVT_CUDA(cudaMemsetAsync(a.bn_stats, 0, 6 * D * sizeof(float), s));
+    CVT_CUDA(launch_dwproj_fwd(dp, s));
+    if (bn) {
+      BnFinalizeP f; f.stats = a.bn_stats; f.count = (long long)B * g.T; f.gamma = P + w.bn_g; f.beta = P + w.bn_b;
+      f.moving_mean = m->St + w.bn_mm; f.moving_var = m->St + w.bn_mv; f.training = training; f.update_moving = training;
+      f.eps = c.bn_eps; f.momentum = c.bn_momentum; f.scale = a.bn_scale; f.shift = a.bn_shift; f.save_mean = a.bn_mean; f.save_rstd = a.bn_rstd; f.D = D;
+      CVT_CUDA(launch_bn_finalize(f, s));
+    }
+  }
+  prof_mark(s, kStageNames[si][2]);
+  {  // proj_q/k/v = Dense(dim)  :180-182  (BatchNorm applied while the A operand is loaded)
+    GemmP p = dense_fwd(a.conv, D, R, D, P + w.pw, D, P + w.pb, a.qkv1, D);
+    p.batch = 3; p.a_bs0 = RD; p.b_bs0 = (long long)D * D; p.c_bs0 = RD; p.bias_bs = D;
+    if (g.method == CVT_PROJ_DW_BN) { p.a_scale = a.bn_scale; p.a_shift = a.bn_shift; p.a_aff_bs = D; p.a_skip_period = g.has_cls ? g.Tc : 0; }
+    CVT_CUDA(run_gemm(m, p, s));
+    // keras MultiHeadAttention query/key/value EinsumDense; query scaled by 1/sqrt(key_dim) after its bias
+    GemmP q = dense_fwd(a.qkv1, D, R, D, P + w.mw, D, P + w.mb, a.qkv2, D);
+    q.batch = 3; q.a_bs0 = RD; q.b_bs0 = (long long)D * D; q.c_bs0 = RD; q.bias_bs = D;
+    q.epi |= EPI_ALPHA0; q.alpha0 = 0.125f;
+    CVT_CUDA(run_gemm(m, q, s));
+  }
+  prof_mark(s, kStageNames[si][3]);
+  CVT_CUDA(attention_forward(m, si, B, s));                                 // self.attention(q, v, k)  :185
+  prof_mark(s, kStageNames[si][4]);
+  {
+    GemmP p = dense_fwd(a.attn_o, D, R, D, P + w.ow, D, P + w.ob, a.a1, D);      // MHA attention_output
+    CVT_CUDA(run_gemm(m, p, s));
+    GemmP q = dense_fwd(a.a1, D, R, D, P + w.prw, D, P + w.prb, a.x1, D);        // self.proj :188, dropout :189, residual :274
+    q.epi |= EPI_RESID; q.resid = a.x0; q.ldr = D;
+    if (drop) { q.epi |= EPI_MASK; q.mask = a.mask_proj; q.mask_scale = keep_scale; }
+    CVT_CUDA(run_gemm(m, q, s));
+  }
+  prof_mark(s, kStageNames[si][5]);
+  // y = norm1(x)  :278  (same gamma/beta)
+  CVT_CUDA(launch_ln_fwd(a.x1, rowmap_none(), D, P + w.ln_g, P + w.ln_b, c.ln_eps, a.y, D, a.lnb_mean, a.lnb_rstd, R, D, s));
+  {  // Mlp :253-258
+    GemmP p = dense_fwd(a.y, D, R, D, P + w.f1w, H4, P + w.f1b, a.hact, H4);
+    p.epi |= EPI_GELU; p.aux = a.hpre;
+    if (drop) { p.epi |= EPI_MASK; p.mask = a.mask1; p.mask_scale = keep_scale; }
+    CVT_CUDA(run_gemm(m, p, s));
+    GemmP q = dense_fwd(a.hact, H4, R, H4, P + w.f2w, D, P + w.f2b, a.x2, D);
+    q.epi |= EPI_RESID; q.resid = a.x1; q.ldr = D;                                // output = x + Mlp_output :281
+    if (drop) { q.epi |= EPI_MASK; q.mask = a.mask2; q.mask_scale = keep_scale; }
+    CVT_CUDA(run_gemm(m, q, s));
+  }
+  return cudaSuccess;
+}
+
+static cudaError_t head_forward(Model* m, const float* proc, int B) {
+  const cvt_config& c = m->cfg; cudaStream_t s = m->stream;
+  const StageGeo& g = m->geo[m->n_stages - 1]; StageBuf& a = m->buf[m->n_stages - 1];
+  const int D = g.D, F = m->feat_dim; float* P = m->P;
+  prof_mark(s, "head");
+  if (m->head_kind == CVT_HEAD_CLS_LN) {          // LayerNormalization(1e-6)(cls_tokens); squeeze  :328-329
+    CVT_CUDA(launch_ln_fwd(a.x2, RowMap{1, g.Tc, 0}, D, P + m->hn_g, P + m->hn_b, c.ln_eps, m->feat, F, m->h_mean, m->h_rstd, B, D, s));
+  } else {                                        // reshape -> LN -> reduce_mean over tokens  :334-337
+    CVT_CUDA(launch_ln_fwd(a.x2, rowmap_none(), D, P + m->hn_g, P + m->hn_b, c.ln_eps, m->hln, D, m->h_mean, m->h_rstd, B * g.Tc, D, s));
+    CVT_CUDA(launch_token_mean(m->hln, B, g.Tc, D, m->feat, F, s));
+  }
+  if (c.proc_dim > 0) {                           // Proc_Dense_1/2 (relu) :343-344, concatenate :347
+    GemmP p = dense_fwd(proc, c.proc_dim, B, c.proc_dim, P + m->pd1w, c.proc_hidden, P + m->pd1b, m->p1, c.proc_hidden);
+    p.epi |= EPI_RELU;
+    CVT_CUDA(launch_gemm_simt(p, s));
+    GemmP q = dense_fwd(m->p1, c.proc_hidden, B, c.proc_hidden, P + m->pd2w, c.proc_hidden, P + m->pd2b, m->feat + D, F);
+    q.epi |= EPI_RELU;
+    CVT_CUDA(launch_gemm_simt(q, s));
+  }
+  GemmP f = dense_fwd(m->feat, F, B, F, P + m->fw, c.num_classes, P + m->fb, m->pred, c.num_classes);   // Final_Dense :350
+  CVT_CUDA(launch_gemm_simt(f, s));
+  return cudaSuccess;
+}
+
+static cudaError_t forward_impl(Model* m, const float* img, const float* proc, int B, int training) {
+  cudaStream_t s = m->stream;
+  const cvt_config& c = m->cfg;
+  const bool drop = training && m->dropout_mode == CVT_DROPOUT_PHILOX && c.drop_rate > 0.f;
+  if (drop) {
+    for (int i = 0; i < m->n_stages; ++i) {
+      const StageGeo& g = m->geo[i]; StageBuf& a = m->buf[i];
+      const long long RD = (long long)B * g.Tc * g.D;
+      CVT_CUDA(launch_philox_mask(a.mask_proj, RD, c.drop_rate, m->dropout_seed, m->dropout_step, i * 4 + 0, s));
+      CVT_CUDA(launch_philox_mask(a.mask1, RD * c.mlp_ratio, c.drop_rate, m->dropout_seed, m->dropout_step, i * 4 + 1, s));
+      CVT_CUDA(launch_philox_mask(a.mask2, RD, c.drop_rate, m->dropout_seed, m->dropout_step, i * 4 + 2, s));
+    }
+  }
+  const float* x = img; long long bstride = (long long)c.image_h * c.image_w * c.in_chans; int boff = 0;
+  for (int i = 0; i < m->n_stages; ++i) {
+    CVT_CUDA(stage_forward(m, i, x, bstride, boff, B, training));
+    const StageGeo& g = m->geo[i];
+    x = m->buf[i].x2; bstride = (long long)g.Tc * g.D; boff = g.has_cls * g.D;
+  }
+  CVT_CUDA(head_forward(m, proc, B));
+  prof_mark(s, "end_forward");
+  m->last_batch = B; m->last_training = training; m->have_forward = 1;
+  if (training && m->dropout_mode == CVT_DROPOUT_PHILOX) m->dropout_step++;
+  return cudaSuccess;
+}
+
+// =====================================================================================================================
+// backward
+// =====================================================================================================================
+static cudaError_t head_backward(Model* m, const float* proc, int B, float* dX2) {
+  const cvt_config& c = m->cfg; cudaStream_t s = m->stream;
+  const StageGeo& g = m->geo[m->n_stages - 1]; StageBuf& a = m->buf[m->n_stages - 1];
+  const int D = g.D, F = m->feat_dim, nc = c.num_classes, PH = c.proc_hidden; float* P = m->P; float* G = m->G;
+  prof_mark(s, "bwd_head");
+  // Final_Dense
+  CVT_CUDA(launch_colsum(m->dpred, nc, rowmap_none(), B, nc, 1, 0, G + m->fb, 0, s));
+  CVT_CUDA(launch_gemm_simt(dense_wgrad(m->feat, F, F, m->dpred, nc, nc, B, G + m->fw), s));
+  {  // d feat (image half)
+    GemmP p = dense_dgrad(m->dpred, nc, B, nc, P + m->fw, D, m->dfeat, F);
+    CVT_CUDA(launch_gemm_simt(p, s));
+  }
+  if (c.proc_dim > 0) {
+    GemmP p = dense_dgrad(m->dpred, nc, B, nc, P + m->fw + (long long)D * nc, PH, m->dfeat + D, F);     // through relu of Proc_Dense_2
+    p.epi |= EPI_RELU_BWD; p.aux = m->feat + D;
+    CVT_CUDA(launch_gemm_simt(p, s));
+    CVT_CUDA(launch_colsum(m->dfeat + D, F, rowmap_none(), B, PH, 1, 0, G + m->pd2b, 0, s));
+    CVT_CUDA(launch_gemm_simt(dense_wgrad(m->p1, PH, PH, m->dfeat + D, F, PH, B, G + m->pd2w), s));
+    GemmP q = dense_dgrad(m->dfeat + D, F, B, PH, P + m->pd2w, PH, m->dp1, PH);
+    q.epi |= EPI_RELU_BWD; q.aux = m->p1;
+    CVT_CUDA(launch_gemm_simt(q, s));
+    CVT_CUDA(launch_colsum(m->dp1, PH, rowmap_none(), B, PH, 1, 0, G + m->pd1b, 0, s));
+    CVT_CUDA(launch_gemm_simt(dense_wgrad(proc, c.proc_dim, c.proc_dim, m->dp1, PH, PH, B, G + m->pd1w), s));
+  }
+  // image branch -> gradient w.r.t. the last block's output
+  CVT_CUDA(cudaMemsetAsync(dX2, 0, (size_t)B * g.Tc * D * sizeof(float), s));
+  if (m->head_kind == CVT_HEAD_CLS_LN) {
+    CVT_CUDA(launch_ln_bwd(m->dfeat, F, a.x2, RowMap{1, g.Tc, 0}, D, m->h_mean, m->h_rstd, P + m->hn_g, nullptr, dX2,
+                           RowMap{1, g.Tc, 0}, D, G + m->hn_g, G + m->hn_b, B, D, s));
+  } else {
+    CVT_CUDA(launch_token_mean_bwd(m->dfeat, F, B, g.Tc, D, m->dhln, s));
+    CVT_CUDA(launch_ln_bwd(m->dhln, D, a.x2, rowmap_none(), D, m->h_mean, m->h_rstd, P + m->hn_g, nullptr, dX2, rowmap_none(), D,
+                           G + m->hn_g, G + m->hn_b, B * g.Tc, D, s));
+  }
+  return cudaSuccess;
+}
+
+// dX2: gradient w.r.t. this block's output [B,Tc,D]; dXprev: gradient buffer of the previous block's output (nullptr for stage 0)
+static cudaError_t stage_backward(Model* m, int si, const float* xin, long long xin_bstride, int xin_boff, int B, int training,
+                                  const float* dX2, float* dXprev, bool param_grads_only_to_input) {
+  (void)param_grads_only_to_input;
+  const StageGeo& g = m->geo[si]; const StageW& w = m->w[si]; StageBuf& a = m->buf[si];
+  const cvt_config& c = m->cfg; cudaStream_t s = m->stream;
+  const int D = g.D, R = B * g.Tc, H4 = c.mlp_ratio * D;
+  const long long RD = (long long)R * D;
+  const bool drop = training && m->dropout_mode != CVT_DROPOUT_OFF && c.drop_rate > 0.f;
+  const float keep_scale = 1.f / (1.f - c.drop_rate);
+  float* P = m->P; float* G = m->G;
+
+  prof_mark(s, kStageNames[si][6]);
+  // ---- Mlp ----
+  const float* dM = dX2;
+  if (drop) { CVT_CUDA(launch_mask_scale(m->gM, dX2, a.mask2, keep_scale, RD, s)); dM = m->gM; }
+  CVT_CUDA(launch_colsum(dM, D, rowmap_none(), R, D, 1, 0, G + w.f2b, 0, s));
+  CVT_CUDA(run_gemm(m, dense_wgrad(a.hact, H4, H4, dM, D, D, R, G + w.f2w), s));
+  {
+    GemmP p = dense_dgrad(dM, D, R, D, P + w.f2w, H4, m->gH, H4);      // d hpre = (dM W2^T) * gelu'(hpre) * mask1/keep
+    p.epi |= EPI_GELU_BWD; p.aux = a.hpre;
+    if (drop) { p.epi |= EPI_MASK; p.mask = a.mask1; p.mask_scale = keep_scale; }
+    CVT_CUDA(run_gemm(m, p, s));
+  }
+  CVT_CUDA(launch_colsum(m->gH, H4, rowmap_none(), R, H4, 1, 0, G + w.f1b, 0, s));
+  CVT_CUDA(run_gemm(m, dense_wgrad(a.y, D, D, m->gH, H4, H4, R, G + w.f1w), s));
+  CVT_CUDA(run_gemm(m, dense_dgrad(m->gH, H4, R, H4, P + w.f1w, D, m->gC, D), s));          // dY
+  // second use of norm1 (:278): dX1 = dX2 + LN'(dY)
+  CVT_CUDA(launch_ln_bwd(m->gC, D, a.x1, rowmap_none(), D, a.lnb_mean, a.lnb_rstd, P + w.ln_g, dX2, m->gD, rowmap_none(), D,
+                         G + w.ln_g, G + w.ln_b, R, D, s));
+  prof_mark(s, kStageNames[si][7]);
+  // ---- attention output projections ----
+  const float* dA2 = m->gD;
+  if (drop) { CVT_CUDA(launch_mask_scale(m->gM, m->gD, a.mask_proj, keep_scale, RD, s)); dA2 = m->gM; }
+  CVT_CUDA(launch_colsum(dA2, D, rowmap_none(), R, D, 1, 0, G + w.prb, 0, s));
+  CVT_CUDA(run_gemm(m, dense_wgrad(a.a1, D, D, dA2, D, D, R, G + w.prw), s));
+  CVT_CUDA(run_gemm(m, dense_dgrad(dA2, D, R, D, P + w.prw, D, m->gC, D), s));              // dA1
+  CVT_CUDA(launch_colsum(m->gC, D, rowmap_none(), R, D, 1, 0, G + w.ob, 0, s));
+  CVT_CUDA(run_gemm(m, dense_wgrad(a.attn_o, D, D, m->gC, D, D, R, G + w.ow), s));
+  CVT_CUDA(run_gemm(m, dense_dgrad(m->gC, D, R, D, P + w.ow, D, m->gE, D), s));             // dO
+  prof_mark(s, kStageNames[si][8]);
+  CVT_CUDA(attention_backward(m, si, B, m->gE, m->gQ, s));                                  // gQ = [dQ(pre-scale), dK, dV]
+  prof_mark(s, kStageNames[si][9]);
+  // ---- MHA q/k/v EinsumDense ----
+  CVT_CUDA(launch_colsum(m->gQ, D, rowmap_none(), R, D, 3, RD, G + w.mb, D, s));
+  {
+    GemmP p = dense_wgrad(a.qkv1, D, D, m->gQ, D, D, R, G + w.mw);
+    p.batch = 3; p.a_bs0 = RD; p.b_bs0 = RD; p.c_bs0 = (long long)D * D; p.splitk = auto_splitk(D, D, R, 3);
+    CVT_CUDA(run_gemm(m, p, s));
+    GemmP q = dense_dgrad(m->gQ, D, R, D, P + w.mw, D, m->gQ2, D);
+    q.batch = 3; q.a_bs0 = RD; q.b_bs0 = (long long)D * D; q.c_bs0 = RD;
+    CVT_CUDA(run_gemm(m, q, s));
+  }
+  // ---- proj_q/k/v Dense (input = BN(conv) recomputed on load) ----
+  CVT_CUDA(launch_colsum(m->gQ2, D, rowmap_none(), R, D, 3, RD, G + w.pb, D, s));
+  {
+    GemmP p = dense_wgrad(a.conv, D, D, m->gQ2, D, D, R, G + w.pw);
+    p.batch = 3; p.a_bs0 = RD; p.b_bs0 = RD; p.c_bs0 = (long long)D * D; p.splitk = auto_splitk(D, D, R, 3);
+    if (g.method == CVT_PROJ_DW_BN) { p.a_scale = a.bn_scale; p.a_shift = a.bn_shift; p.a_aff_bs = D; p.a_skip_period = g.has_cls ? g.Tc : 0; }
+    CVT_CUDA(run_gemm(m, p, s));
+    GemmP q = dense_dgrad(m->gQ2, D, R, D, P + w.pw, D, m->gQ, D);
+    q.batch = 3; q.a_bs0 = RD; q.b_bs0 = (long long)D * D; q.c_bs0 = RD;
+    CVT_CUDA(run_gemm(m, q, s));                                                            // gQ = d(q0,k0,v0)
+  }
+  prof_mark(s, kStageNames[si][10]);
+  // ---- Projection backward (BatchNorm + depthwise conv / avg pool / identity) ----
+  {
+    const bool bn = g.method == CVT_PROJ_DW_BN;
+    if (bn) {
+      if (training)
+        CVT_CUDA(launch_bn_bwd_reduce(m->gQ, a.conv, RD, a.bn_mean, a.bn_rstd, G + w.bn_g, G + w.bn_b, B, g.T, g.Tc, g.has_cls, D, s));
+      CVT_CUDA(launch_bn_bwd_apply(m->gQ, a.conv, RD, a.bn_mean, a.bn_rstd, P + w.bn_g, a.bn_scale, G + w.bn_g, G + w.bn_b, training,
+                                   B, g.T, g.Tc, g.has_cls, D, s));
+    }
+    DwProjBwdP dp; dp.dconv = m->gQ; dp.bs = RD; dp.xn = a.xn; dp.w = bn ? P + w.dw : nullptr;
+    const int mz = bn ? 0 : (g.method == CVT_PROJ_AVG ? 1 : 2);
+    dp.method[0] = (g.method == CVT_PROJ_AVG) ? 2 : mz; dp.method[1] = mz; dp.method[2] = mz;
+    dp.B = B; dp.H = g.H; dp.W = g.W; dp.D = D; dp.Tc = g.Tc; dp.has_cls = g.has_cls; dp.dxn = m->gE; dp.ddw = bn ? G + w.dw : nullptr;
+    CVT_CUDA(launch_dwproj_bwd(dp, s));
+  }
+  // first use of norm1 (:272): dX0 = dX1 + LN'(dXn)   (in place on gD)
+  CVT_CUDA(launch_ln_bwd(m->gE, D, a.x0, rowmap_none(), D, a.lna_mean, a.lna_rstd, P + w.ln_g, m->gD, m->gD, rowmap_none(), D,
+                         G + w.ln_g, G + w.ln_b, R, D, s));
+  prof_mark(s, kStageNames[si][11]);
+  // ---- cls token + ConvEmbed ----
+  if (g.has_cls) CVT_CUDA(launch_colsum(m->gD, D, RowMap{1, g.Tc, 0}, B, D, 1, 0, G + w.cls, 0, s));
+  const RowMap emap = g.has_cls ? RowMap{g.T, g.Tc, 1} : rowmap_none();
+  CVT_CUDA(launch_colsum(m->gD, D, emap, B * g.T, D, 1, 0, G + w.conv_b, 0, s));
+  const ConvGeom cv{g.hin, g.win, g.cin, g.H, g.W, g.k, g.s, g.pt, g.pl, xin_bstride, xin_boff};
+  {
+    GemmP p; p.M = g.k * g.k * g.cin; p.N = D; p.K = B * g.T; p.A = xin; p.a_mode = A_CONVT; p.cv = cv;
+    p.B = m->gD; p.ldb = D; p.b_mode = B_KN; p.b_map = emap; p.C = G + w.conv_w; p.ldc = D; p.epi = EPI_ATOMIC;
+    p.splitk = auto_splitk(p.M, p.N, p.K, 1);
+    CVT_CUDA(run_gemm(m, p, s));
+  }
+  if (dXprev) {
+    const StageGeo& gp = m->geo[si - 1];
+    CVT_CUDA(cudaMemsetAsync(dXprev, 0, (size_t)B * gp.Tc * gp.D * sizeof(float), s));
+    GemmP p; p.M = B * g.T; p.N = g.k * g.k * g.cin; p.K = D; p.A = m->gD; p.lda = D; p.a_map = emap;
+    p.B = P + w.conv_w; p.ldb = D; p.b_mode = B_NK; p.C = dXprev; p.cv = cv; p.epi = EPI_SCATTER;
+    CVT_CUDA(run_gemm(m, p, s));
+  }
+  return cudaSuccess;
+}
+
+struct FwdInputs { const float* img; const float* proc; };
+static thread_local FwdInputs g_last_inputs{nullptr, nullptr};
+
+// runs the backward pass from m->dpred down to stage `stop_stage` (0 = all the way); returns the buffer holding the
+// gradient w.r.t. the output of block `stop_stage` when stop_stage > 0 ... (grad-cam tap)
+static cudaError_t backward_impl(Model* m, const float* img, const float* proc, int B, int training, int stop_after_stage, float** tap_grad) {
+  cudaStream_t s = m->stream;
+  CVT_CUDA(cudaMemsetAsync(m->G, 0, (size_t)m->n_train * sizeof(float), s));
+  int cur = (m->n_stages - 1) & 1;
+  CVT_CUDA(head_backward(m, proc, B, m->gX[cur]));
+  for (int i = m->n_stages - 1; i >= 0; --i) {
+    if (tap_grad && i == stop_after_stage) { *tap_grad = m->gX[cur]; return cudaSuccess; }
+    const float* xin; long long bstride; int boff;
+    if (i == 0) { xin = img; bstride = (long long)m->cfg.image_h * m->cfg.image_w * m->cfg.in_chans; boff = 0; }
+    else { const StageGeo& gp = m->geo[i - 1]; xin = m->buf[i - 1].x2; bstride = (long long)gp.Tc * gp.D; boff = gp.has_cls * gp.D; }
+    float* dprev = i > 0 ? m->gX[cur ^ 1] : nullptr;
+    CVT_CUDA(stage_backward(m, i, xin, bstride, boff, B, training, m->gX[cur], dprev, false));
+    cur ^= 1;
+  }
+  prof_mark(s, "end_backward");
+  return cudaSuccess;
+}
+
+static int check_batch(Model* m, int batch, const char* who) {
+  if (batch < 1 || batch > m->cfg.max_batch) { set_error(std::string(who) + ": batch " + std::to_string(batch) + " outside [1, max_batch=" + std::to_string(m->cfg.max_batch) + "]"); return CVT_ERR_INVALID; }
+  return CVT_OK;
+}
+
+int cvt_forward(cvt_model* h, const float* img_dev, const float* proc_dev, int batch, int training, float* out_dev) {
+  if (!h || !img_dev) { set_error("cvt_forward: null argument"); return CVT_ERR_INVALID; }
+  Model* m = &h->m;
+  if (m->cfg.proc_dim > 0 && !proc_dev) { set_error("cvt_forward: this model needs process parameters"); return CVT_ERR_INVALID; }
+  int r = check_batch(m, batch, "cvt_forward"); if (r) return r;
+  API_CUDA(cudaSetDevice(m->cfg.device));
+  const long long l0 = g_launch_count;
+  API_CUDA(forward_impl(m, img_dev, proc_dev, batch, training));
+  g_last_inputs = {img_dev, proc_dev};
+  if (out_dev) API_CUDA(cudaMemcpyAsync(out_dev, m->pred, (size_t)batch * m->cfg.num_classes * sizeof(float), cudaMemcpyDeviceToDevice, m->stream));
+  m->launches += g_launch_count - l0;
+  return CVT_OK;
+}
+
+int cvt_loss_backward(cvt_model* h, const float* y_dev, float* loss_host, float* mae_host) {
+  if (!h || !y_dev) { set_error("cvt_loss_backward: null argument"); return CVT_ERR_INVALID; }
+  Model* m = &h->m;
+  if (!m->have_forward || !g_last_inputs.img) { set_error("cvt_loss_backward: call cvt_forward first"); return CVT_ERR_STATE; }
+  const int B = m->last_batch;
+  const long long l0 = g_launch_count;
+  const float gs = 1.f;
+  API_CUDA(launch_mse_loss(m->pred, y_dev, B * m->cfg.num_classes, m->metrics, m->dpred, gs, 0, m->stream));
+  API_CUDA(backward_impl(m, g_last_inputs.img, g_last_inputs.proc, B, m->last_training, -1, nullptr));
+  m->launches += g_launch_count - l0;
+  if (loss_host || mae_host) {
+    float l, a; int r = cvt_read_metrics(h, &l, &a); if (r) return r;
+    if (loss_host) *loss_host = l;
+    if (mae_host) *mae_host = a;
+  }
+  return CVT_OK;
+}
+
+int cvt_read_metrics(cvt_model* h, float* loss, float* mae) {
+  if (!h) return CVT_ERR_INVALID;
+  Model* m = &h->m;
+  API_CUDA(cudaMemcpyAsync(m->pin_metrics, m->metrics, 2 * sizeof(float), cudaMemcpyDeviceToHost, m->stream));
+  API_CUDA(cudaStreamSynchronize(m->stream));
+  if (loss) *loss = m->pin_metrics[0];
+  if (mae) *mae = m->pin_metrics[1];
+  return CVT_OK;
+}
+
+// ---- NCCL (dlopen'ed so that the library loads on machines without it) -------------------------------------------
+typedef int (*nccl_get_uid_t)(void*);
+struct NcclUid { char internal[128]; };   // ncclUniqueId is passed by value (128 bytes)
+typedef int (*nccl_init_rank_fn)(void**, int, NcclUid, int);
+typedef int (*nccl_allreduce_fn)(const void*, void*, size_t, int, int, void*, cudaStream_t);
+typedef int (*nccl_destroy_fn)(void*);
+typedef const char* (*nccl_errstr_fn)(int);
+static struct { void* lib; nccl_get_uid_t get_uid; nccl_init_rank_fn init_rank; nccl_allreduce_fn allreduce; nccl_destroy_fn destroy; nccl_errstr_fn errstr; } g_nccl = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+
+static int nccl_load() {
+  if (g_nccl.lib) return CVT_OK;
+  const char* names[] = {"libnccl.so.2", "libnccl.so"};
+  for (const char* n : names) { g_nccl.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL); if (g_nccl.lib) break; }
+  if (!g_nccl.lib) { set_error("NCCL: libnccl.so.2 not found"); return CVT_ERR_NCCL; }
+  g_nccl.get_uid = (nccl_get_uid_t)dlsym(g_nccl.lib, "ncclGetUniqueId");
+  g_nccl.init_rank = (nccl_init_rank_fn)dlsym(g_nccl.lib, "ncclCommInitRank");
+  g_nccl.allreduce = (nccl_allreduce_fn)dlsym(g_nccl.lib, "ncclAllReduce");
+  g_nccl.destroy = (nccl_destroy_fn)dlsym(g_nccl.lib, "ncclCommDestroy");
+  g_nccl.errstr = (nccl_errstr_fn)dlsym(g_nccl.lib, "ncclGetErrorString");
+  if (!g_nccl.get_uid || !g_nccl.init_rank || !g_nccl.allreduce || !g_nccl.destroy) { set_error("NCCL: missing symbols"); return CVT_ERR_NCCL; }
+  return CVT_OK;
+}
+#define API_NCCL(expr) do { int _r = (expr); if (_r != 0) { set_error(std::string(#expr) + ": " + (g_nccl.errstr ? g_nccl.errstr(_r) : "nccl error")); return CVT_ERR_NCCL; } } while (0)
+
+int cvt_comm_unique_id(uint8_t id_out[128]) {
+  int r = nccl_load(); if (r) return r;
+  API_NCCL(g_nccl.get_uid(id_out));
+  return CVT_OK;
+}
+int cvt_comm_init(cvt_model* h, const uint8_t unique_id[128], int rank, int world) {
+  if (!h || !unique_id || world < 1 || rank < 0 || rank >= world) { set_error("cvt_comm_init: bad argument"); return CVT_ERR_INVALID; }
+  int r = nccl_load(); if (r) return r;
+  Model* m = &h->m;
+  API_CUDA(cudaSetDevice(m->cfg.device));
+  NcclUid uid; memcpy(uid.internal, unique_id, 128);
+  API_NCCL(g_nccl.init_rank(&m->nccl_comm, world, uid, rank));
+  m->rank = rank; m->world = world;
+  return CVT_OK;
+}
+int cvt_comm_destroy(cvt_model* h) {
+  if (!h) return CVT_ERR_INVALID;
+  Model* m = &h->m;
+  if (m->nccl_comm && g_nccl.destroy) { g_nccl.destroy(m->nccl_comm); m->nccl_comm = nullptr; }
+  m->world = 1; m->rank = 0;
+  return CVT_OK;
+}
+int cvt_grad_arena(cvt_model* h, float** g, int64_t* count) {
+  if (!h) return CVT_ERR_INVALID;
+  if (g) *g = h->m.G; if (count) *count = h->m.n_train;
+  return CVT_OK;
+}
+int cvt_param_arena(cvt_model* h, float** p, int64_t* count) {
+  if (!h) return CVT_ERR_INVALID;
+  if (p) *p = h->m.P; if (count) *count = h->m.n_train;
+  return CVT_OK;
+}
+
+static cudaError_t adam_impl(Model* m, float lr, float grad_scale) {
+  m->adam_t += 1;
+  const double b1 = 0.9, b2 = 0.999;
+  const double t = (double)m->adam_t;
+  const float alpha = (float)((double)lr * sqrt(1.0 - pow(b2, t)) / (1.0 - pow(b1, t)));
+  return launch_adam(m->P, m->G, m->Mo, m->Vo, m->n_train, alpha, 0.9f, 0.999f, 1e-7f, grad_scale, m->stream);
+}
+
+int cvt_adam_step(cvt_model* h, float lr) {
+  if (!h) return CVT_ERR_INVALID;
+  Model* m = &h->m;
+  const long long l0 = g_launch_count;
+  API_CUDA(adam_impl(m, lr, 1.f));
+  m->launches += g_launch_count - l0;
+  return CVT_OK;
+}
+int cvt_optimizer_reset(cvt_model* h) {
+  if (!h) return CVT_ERR_INVALID;
+  Model* m = &h->m;
+  API_CUDA(cudaMemsetAsync(m->Mo, 0, (size_t)m->n_train * sizeof(float), m->stream));
+  API_CUDA(cudaMemsetAsync(m->Vo, 0, (size_t)m->n_train * sizeof(float), m->stream));
+  m->adam_t = 0;
+  return CVT_OK;
+}
+int64_t cvt_optimizer_step_count(const cvt_model* h) { return h ? h->m.adam_t : -1; }
+
+static int train_step_dev(Model* m, const float* img, const float* proc, const float* y, int B, float lr) {
+  API_CUDA(forward_impl(m, img, proc, B, 1));
+  API_CUDA(launch_mse_loss(m->pred, y, B * m->cfg.num_classes, m->metrics, m->dpred, 1.f, 0, m->stream));
+  API_CUDA(backward_impl(m, img, proc, B, 1, -1, nullptr));
+  float gs = 1.f;
+  if (m->nccl_comm && m->world > 1) {
+    // data parallel: sum of per-rank mean-loss gradients / world == gradient of the global-batch mean loss
+    API_NCCL(g_nccl.allreduce(m->G, m->G, (size_t)m->n_train, /*ncclFloat32*/ 7, /*ncclSum*/ 0, m->nccl_comm, m->stream));
+    gs = 1.f / (float)m->world;
+  }
+  API_CUDA(adam_impl(m, lr, gs));
+  return CVT_OK;
+}
+
+int cvt_train_step(cvt_model* h, const float* img_dev, const float* proc_dev, const float* y_dev, int batch, float lr) {
+  if (!h || !img_dev || !y_dev) { set_error("cvt_train_step: null argument"); return CVT_ERR_INVALID; }
+  Model* m = &h->m;
+  if (m->cfg.proc_dim > 0 && !proc_dev) { set_error("cvt_train_step: this model needs process parameters"); return CVT_ERR_INVALID; }
+  int r = check_batch(m, batch, "cvt_train_step"); if (r) return r;
+  API_CUDA(cudaSetDevice(m->cfg.device));
+  const long long l0 = g_launch_count;
+  r = train_step_dev(m, img_dev, proc_dev, y_dev, batch, lr);
+  g_last_inputs = {img_dev, proc_dev};
+  m->launches += g_launch_count - l0;
+  return r;
+}
+
+int cvt_train_step_host(cvt_model* h, const float* img, const float* proc, const float* y, int batch, float lr, float* loss, float* mae) {
+  if (!h || !img || !y) { set_error("cvt_train_step_host: null argument"); return CVT_ERR_INVALID; }
+  Model* m = &h->m; const cvt_config& c = m->cfg;
+  if (c.proc_dim > 0 && !proc) { set_error("cvt_train_step_host: this model needs process parameters"); return CVT_ERR_INVALID; }
+  int r = check_batch(m, batch, "cvt_train_step_host"); if (r) return r;
+  API_CUDA(cudaSetDevice(c.device));
+  const size_t per = (size_t)c.image_h * c.image_w * c.in_chans;
+  API_CUDA(cudaMemcpyAsync(m->in_img, img, batch * per * sizeof(float), cudaMemcpyHostToDevice, m->stream));
+  if (c.proc_dim > 0) API_CUDA(cudaMemcpyAsync(m->in_proc, proc, (size_t)batch * c.proc_dim * sizeof(float), cudaMemcpyHostToDevice, m->stream));
+  API_CUDA(cudaMemcpyAsync(m->in_y, y, (size_t)batch * c.num_classes * sizeof(float), cudaMemcpyHostToDevice, m->stream));
+  r = cvt_train_step(h, m->in_img, c.proc_dim > 0 ? m->in_proc : nullptr, m->in_y, batch, lr);
+  if (r) return r;
+  if (loss || mae) return cvt_read_metrics(h, loss, mae);
+  return CVT_OK;
+}
+
+int cvt_predict_host(cvt_model* h, const float* img, const float* proc, int64_t n, float* out) {
+  if (!h || !img || !out || n < 0) { set_error("cvt_predict_host: bad argument"); return CVT_ERR_INVALID; }
+  Model* m = &h->m; const cvt_config& c = m->cfg;
+  if (c.proc_dim > 0 && !proc) { set_error("cvt_predict_host: this model needs process parameters"); return CVT_ERR_INVALID; }
+  API_CUDA(cudaSetDevice(c.device));
+  const size_t per = (size_t)c.image_h * c.image_w * c.in_chans;
+  const long long l0 = g_launch_count;
+  for (int64_t o = 0; o < n; o += c.max_batch) {
+    const int B = (int)std::min<int64_t>(c.max_batch, n - o);
+    API_CUDA(cudaMemcpyAsync(m->in_img, img + o * per, B * per * sizeof(float), cudaMemcpyHostToDevice, m->stream));
+    if (c.proc_dim > 0) API_CUDA(cudaMemcpyAsync(m->in_proc, proc + o * c.proc_dim, (size_t)B * c.proc_dim * sizeof(float), cudaMemcpyHostToDevice, m->stream));
+    API_CUDA(forward_impl(m, m->in_img, c.proc_dim > 0 ? m->in_proc : nullptr, B, 0));
+    API_CUDA(cudaMemcpyAsync(out + o * c.num_classes, m->pred, (size_t)B * c.num_classes * sizeof(float), cudaMemcpyDeviceToHost, m->stream));
+  }
+  API_CUDA(cudaStreamSynchronize(m->stream));
+  g_last_inputs = {m->in_img, c.proc_dim > 0 ? m->in_proc : nullptr};
+  m->launches += g_launch_count - l0;
+  return CVT_OK;
+}
+
+int cvt_evaluate_host(cvt_model* h, const float* img, const float* proc, const float* y, int64_t n, float* loss, float* mae) {
+  if (!h || !img || !y || n < 1) { set_error("cvt_evaluate_host: bad argument"); return CVT_ERR_INVALID; }
+  Model* m = &h->m; const cvt_config& c = m->cfg;
+  if (c.proc_dim > 0 && !proc) { set_error("cvt_evaluate_host: this model needs process parameters"); return CVT_ERR_INVALID; }
+  API_CUDA(cudaSetDevice(c.device));
+  const size_t per = (size_t)c.image_h * c.image_w * c.in_chans;
+  const long long l0 = g_launch_count;
+  API_CUDA(cudaMemsetAsync(m->metrics + 2, 0, 2 * sizeof(float), m->stream));
+  for (int64_t o = 0; o < n; o += c.max_batch) {
+    const int B = (int)std::min<int64_t>(c.max_batch, n - o);
+    API_CUDA(cudaMemcpyAsync(m->in_img, img + o * per, B * per * sizeof(float), cudaMemcpyHostToDevice, m->stream));
+    if (c.proc_dim > 0) API_CUDA(cudaMemcpyAsync(m->in_proc, proc + o * c.proc_dim, (size_t)B * c.proc_dim * sizeof(float), cudaMemcpyHostToDevice, m->stream));
+    API_CUDA(cudaMemcpyAsync(m->in_y, y + o * c.num_classes, (size_t)B * c.num_classes * sizeof(float), cudaMemcpyHostToDevice, m->stream));
+    API_CUDA(forward_impl(m, m->in_img, c.proc_dim > 0 ? m->in_proc : nullptr, B, 0));
+    API_CUDA(launch_mse_loss(m->pred, m->in_y, B * c.num_classes, m->metrics + 2, nullptr, 1.f, 1, m->stream));
+  }
+  API_CUDA(cudaMemcpyAsync(m->pin_metrics + 2, m->metrics + 2, 2 * sizeof(float), cudaMemcpyDeviceToHost, m->stream));
+  API_CUDA(cudaStreamSynchronize(m->stream));
+  const double cnt = (double)n * c.num_classes;
+  if (loss) *loss = (float)(m->pin_metrics[2] / cnt);
+  if (mae) *mae = (float)(m->pin_metrics[3] / cnt);
+  m->launches += g_launch_count - l0;
+  return CVT_OK;
+}
+
+int cvt_set_dropout(cvt_model* h, int mode, uint64_t seed) {
+  if (!h || mode < 0 || mode > 2) { set_error("cvt_set_dropout: bad mode"); return CVT_ERR_INVALID; }
+  h->m.dropout_mode = mode; h->m.dropout_seed = seed; h->m.dropout_step = 0;
+  return CVT_OK;
+}
+int cvt_set_dropout_mask(cvt_model* h, int site, const uint8_t* host_mask, int64_t count) {
+  if (!h || !host_mask || site < 0 || site / 4 >= h->m.n_stages || site % 4 > 2) { set_error("cvt_set_dropout_mask: bad site"); return CVT_ERR_INVALID; }
+  Model* m = &h->m; const StageGeo& g = m->geo[site / 4]; StageBuf& a = m->buf[site / 4];
+  const int64_t width = (site % 4 == 1) ? (int64_t)m->cfg.mlp_ratio * g.D : g.D;
+  const int64_t cap = (int64_t)m->cfg.max_batch * g.Tc * width;
+  if (count < 0 || count > cap) { set_error("cvt_set_dropout_mask: count exceeds max_batch*Tc*width"); return CVT_ERR_INVALID; }
+  uint8_t* dst = site % 4 == 0 ? a.mask_proj : (site % 4 == 1 ? a.mask1 : a.mask2);
+  API_CUDA(cudaMemcpyAsync(dst, host_mask, (size_t)count, cudaMemcpyHostToDevice, m->stream));
+  API_CUDA(cudaStreamSynchronize(m->stream));
+  return CVT_OK;
+}
+
+// ---- taps -------------------------------------------------------------------------------------------------------------
+static int parse_stage(const char* name, int* stage, const char** field) {
+  if (name[0] != 's' || name[1] < '1' || name[1] > '9' || name[2] != '.') return -1;
+  *stage = name[1] - '1'; *field = name + 3;
+  return 0;
+}
+
+int64_t cvt_get_tap(cvt_model* h, const char* name, float* dst, int64_t capacity) {
+  if (!h || !name) { set_error("cvt_get_tap: null argument"); return CVT_ERR_INVALID; }
+  Model* m = &h->m;
+  if (!m->have_forward) { set_error("cvt_get_tap: no forward pass has run"); return CVT_ERR_STATE; }
+  const int B = m->last_batch; cudaStream_t s = m->stream;
+  const float* src = nullptr; int64_t n = 0;
+  int si; const char* f;
+  if (!strcmp(name, "pred")) { src = m->pred; n = (int64_t)B * m->cfg.num_classes; }
+  else if (!strcmp(name, "head.feat")) { src = m->feat; n = (int64_t)B * m->feat_dim; }
+  else if (!strcmp(name, "head.proc1")) { src = m->p1; n = (int64_t)B * m->cfg.proc_hidden; }
+  else if (parse_stage(name, &si, &f) == 0 && si < m->n_stages) {
+    const StageGeo& g = m->geo[si]; StageBuf& a = m->buf[si];
+    const int64_t RD = (int64_t)B * g.Tc * g.D, TD = (int64_t)B * g.T * g.D;
+    const RowMap strip = g.has_cls ? RowMap{g.T, g.Tc, 1} : rowmap_none();
+    if (!strcmp(f, "x0")) { src = a.x0; n = RD; }
+    else if (!strcmp(f, "xn")) { src = a.xn; n = RD; }
+    else if (!strcmp(f, "qkv1")) { src = a.qkv1; n = 3 * RD; }
+    else if (!strcmp(f, "qkv2")) { src = a.qkv2; n = 3 * RD; }
+    else if (!strcmp(f, "attn_o")) { src = a.attn_o; n = RD; }
+    else if (!strcmp(f, "a1")) { src = a.a1; n = RD; }
+    else if (!strcmp(f, "x1")) { src = a.x1; n = RD; }
+    else if (!strcmp(f, "y")) { src = a.y; n = RD; }
+    else if (!strcmp(f, "hpre")) { src = a.hpre; n = RD * m->cfg.mlp_ratio; }
+    else if (!strcmp(f, "hact")) { src = a.hact; n = RD * m->cfg.mlp_ratio; }
+    else if (!strcmp(f, "x2")) { src = a.x2; n = RD; }
+    else if (!strcmp(f, "embed") || !strcmp(f, "out")) {
+      const float* from = !strcmp(f, "embed") ? a.x0 : a.x2;
+      API_CUDA(launch_copy_rows(m->gQ2, rowmap_none(), g.D, from, strip, g.D, B * g.T, g.D, s));
+      src = m->gQ2; n = TD;
+    } else if (!strcmp(f, "conv_qkv")) {
+      for (int z = 0; z < 3; ++z)
+        API_CUDA(launch_copy_rows(m->gQ2 + z * TD, rowmap_none(), g.D, a.conv + z * RD, strip, g.D, B * g.T, g.D, s));
+      src = m->gQ2; n = 3 * TD;
+    }
+  }
+  if (!src) { set_error(std::string("cvt_get_tap: unknown tap '") + name + "'"); return CVT_ERR_INVALID; }
+  if (dst) {
+    if (capacity < n) { set_error("cvt_get_tap: destination too small"); return CVT_ERR_INVALID; }
+    API_CUDA(cudaMemcpyAsync(dst, src, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, s));
+    API_CUDA(cudaStreamSynchronize(s));
+  }
+  return n;
+}
+
+int cvt_backward_to_tap(cvt_model* h, const float* dout_host, const char* name, float* dst, int64_t capacity) {
+  if (!h || !dout_host || !name || !dst) { set_error("cvt_backward_to_tap: null argument"); return CVT_ERR_INVALID; }
+  Model* m = &h->m;
+  if (!m->have_forward || !g_last_inputs.img) { set_error("cvt_backward_to_tap: call cvt_forward first"); return CVT_ERR_STATE; }
+  int si; const char* f;
+  if (parse_stage(name, &si, &f) != 0 || si >= m->n_stages || strcmp(f, "x2") != 0) { set_error("cvt_backward_to_tap: tap must be s{i}.x2"); return CVT_ERR_INVALID; }
+  const int B = m->last_batch; const StageGeo& g = m->geo[si];
+  const int64_t n = (int64_t)B * g.Tc * g.D;
+  if (capacity < n) { set_error("cvt_backward_to_tap: destination too small"); return CVT_ERR_INVALID; }
+  API_CUDA(cudaMemcpyAsync(m->dpred, dout_host, (size_t)B * m->cfg.num_classes * sizeof(float), cudaMemcpyHostToDevice, m->stream));
+  float* gptr = nullptr;
+  API_CUDA(backward_impl(m, g_last_inputs.img, g_last_inputs.proc, B, m->last_training, si, &gptr));
+  API_CUDA(cudaMemcpyAsync(dst, gptr, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, m->stream));
+  API_CUDA(cudaStreamSynchronize(m->stream));
+  return CVT_OK;
+}
+
+int cvt_synchronize(cvt_model* h) {
+  if (!h) return CVT_ERR_INVALID;
+  API_CUDA(cudaStreamSynchronize(h->m.stream));
+  return CVT_OK;
+}
+void* cvt_stream(cvt_model* h) { return h ? (void*)h->m.stream : nullptr; }
+int cvt_set_graphs(cvt_model* h, int enable) { if (!h) return CVT_ERR_INVALID; h->m.use_graphs = enable; return CVT_OK; }
+int64_t cvt_kernel_launches(const cvt_model* h) { return h ? h->m.launches : -1; }
+int64_t cvt_workspace_bytes(const cvt_model* h) { return h ? h->m.workspace_bytes : -1; }
+
+int cvt_profile_step(cvt_model* h, const float* img_dev, const float* proc_dev, const float* y_dev, int batch, int training,
+                     int max_entries, const char** names, float* ms, int* n_entries) {
+  if (!h || !img_dev || !names || !ms || !n_entries) { set_error("cvt_profile_step: null argument"); return CVT_ERR_INVALID; }
+  Model* m = &h->m;
+  int r = check_batch(m, batch, "cvt_profile_step"); if (r) return r;
+  if (training && !y_dev) { set_error("cvt_profile_step: training needs targets"); return CVT_ERR_INVALID; }
+  std::vector<ProfMark> marks;
+  g_prof = &marks;
+  int rc = CVT_OK;
+  do {
+    if (forward_impl(m, img_dev, proc_dev, batch, training) != cudaSuccess) { rc = CVT_ERR_CUDA; break; }
+    if (training) {
+      if (launch_mse_loss(m->pred, y_dev, batch * m->cfg.num_classes, m->metrics, m->dpred, 1.f, 0, m->stream) != cudaSuccess) { rc = CVT_ERR_CUDA; break; }
+      if (backward_impl(m, img_dev, proc_dev, batch, 1, -1, nullptr) != cudaSuccess) { rc = CVT_ERR_CUDA; break; }
+      prof_mark(m->stream, "adam");
+      if (adam_impl(m, 0.f, 1.f) != cudaSuccess) { rc = CVT_ERR_CUDA; break; }
+      m->adam_t -= 1;   // lr = 0: weights untouched; keep the step counter where it was
+      prof_mark(m->stream, "end");
+    }
+  } while (0);
+  g_prof = nullptr;
+  cudaStreamSynchronize(m->stream);
+  int n = 0;
+  for (size_t i = 0; i + 1 < marks.size() && n < max_entries; ++i) {
+    float t = 0.f; cudaEventElapsedTime(&t, marks[i].ev, marks[i + 1].ev);
+    if (!strncmp(marks[i].name, "end", 3)) continue;
+    names[n] = marks[i].name; ms[n] = t; ++n;
+  }
+  for (auto& mk : marks) cudaEventDestroy(mk.ev);
+  *n_entries = n;
+  g_last_inputs = {img_dev, proc_dev};
+  return rc;
+}
+
+}  // extern "C"

@@ -1,0 +1,58 @@
+// Generic dense-contraction descriptor shared by the fp32 FFMA kernel (gemm_simt.cu) and the
+// tcgen05/TMEM kernel (gemm_tc.cu).  One description covers every dense op of the CvT block:
+//   forward  Dense / EinsumDense / Conv2D-as-implicit-GEMM   (models/CvT(Par).py:180-188,203-208,253-258)
+//   backward dgrad (B read k-contiguous), wgrad (A read transposed, split-K + atomics), conv scatter.
+#pragma once
+#include "common.cuh"
+
+namespace cvt {
+
+enum AMode : int { A_PLAIN = 0,   // A(m,k) = A[tok(m)*lda + k]
+                   A_TRANS = 1,   // A(m,k) = A[tok(k)*lda + m]            (wgrad: X^T)
+                   A_CONV  = 2,   // A(m,k) = im2col(x)[m=(b,i,j), k=(kh,kw,ci)]   (Conv2D SAME forward)
+                   A_CONVT = 3 }; // A(m,k) = im2col(x)[k=(b,i,j), m=(kh,kw,ci)]   (Conv2D wgrad)
+enum BMode : int { B_KN = 0,      // B(k,n) = B[row(k)*ldb + n]
+                   B_NK = 1 };    // B(k,n) = B[n*ldb + k]
+enum Epi : uint32_t {
+  EPI_BIAS = 1u, EPI_GELU = 2u, EPI_RESID = 4u, EPI_MASK = 8u, EPI_ATOMIC = 16u, EPI_SCATTER = 32u,
+  EPI_GELU_BWD = 64u, EPI_RELU = 128u, EPI_RELU_BWD = 256u, EPI_ALPHA0 = 512u
+};
+
+// Conv2D(padding='same') geometry.  The input map of image b starts at x + b*bstride + boff (floats), which lets a
+// [B,Tc,D] block output with a leading cls row be read as the next stage's [B,H,W,C] input without a copy.
+struct ConvGeom { int hin, win, cin, ho, wo, k, s, pt, pl; long long bstride; int boff; };
+
+struct GemmP {
+  int M = 0, N = 0, K = 0;
+  int batch = 1, splitk = 1, bdiv = 1;          // z -> (z / bdiv, z % bdiv) selects the operand slices
+  // A
+  const float* A = nullptr; long long lda = 0, a_bs0 = 0, a_bs1 = 0;
+  int a_mode = A_PLAIN; RowMap a_map{0, 0, 0};
+  const float* a_scale = nullptr; const float* a_shift = nullptr; long long a_aff_bs = 0;   // per-feature affine (BN on load)
+  int a_skip_period = 0;                       // tokens with tok % period == 0 (cls rows) skip the affine
+  ConvGeom cv{0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+  // B
+  const float* B = nullptr; long long ldb = 0, b_bs0 = 0, b_bs1 = 0;
+  int b_mode = B_KN; RowMap b_map{0, 0, 0};
+  // C
+  float* C = nullptr; long long ldc = 0, c_bs0 = 0, c_bs1 = 0; RowMap c_map{0, 0, 0};
+  // epilogue:  v = (acc + bias[n]) * alpha ; gelu/relu ; *gelu'(aux) ; *mask*mask_scale ; + resid ; store|atomic|scatter
+  const float* bias = nullptr; long long bias_bs = 0;
+  float alpha = 1.f, alpha0 = 1.f;
+  uint32_t epi = 0;
+  const float* resid = nullptr; long long ldr = 0;
+  const uint8_t* mask = nullptr; float mask_scale = 1.f;
+  float* aux = nullptr;                        // same indexing as C: GELU pre-activation (write) / saved activation (read)
+};
+
+// fp32 FFMA path (always available, exact fp32 arithmetic)
+cudaError_t launch_gemm_simt(const GemmP& p, cudaStream_t s);
+// tcgen05 kind::tf32 path; returns cudaErrorNotSupported for shapes it does not take
+cudaError_t launch_gemm_tc(const GemmP& p, cudaStream_t s);
+bool gemm_tc_supports(const GemmP& p);
+
+// column sums (bias gradients): out[z][n] += sum_r X[z][map(r)*ld + n]
+cudaError_t launch_colsum(const float* X, long long ld, RowMap map, int rows, int N, int batch, long long x_bs,
+                          float* out, long long out_bs, cudaStream_t s);
+
+}  // namespace cvt

@@ -1,0 +1,74 @@
+// Launchers for the memory-bound layers of the CvT block (everything that is not a contraction).
+#pragma once
+#include "common.cuh"
+
+namespace cvt {
+
+// LayerNormalization(epsilon) over the last axis, biased variance — models/CvT(Par).py:248,272,278,328.
+// y[row*ldy + c] = (x[in_map(row)*ldx + c] - mu) * rstd * gamma[c] + beta[c]; mean/rstd saved per row.
+cudaError_t launch_ln_fwd(const float* x, RowMap in_map, long long ldx, const float* gamma, const float* beta, float eps,
+                          float* y, long long ldy, float* mean, float* rstd, int rows, int D, cudaStream_t s);
+// dx[out_map(row)*ldo + c] = (dres ? dres[out_map(row)*ldo + c] : 0) + LNbwd(dy)[c];  dgamma/dbeta += (atomics)
+cudaError_t launch_ln_bwd(const float* dy, long long lddy, const float* x, RowMap in_map, long long ldx,
+                          const float* mean, const float* rstd, const float* gamma,
+                          const float* dres, float* dx, RowMap out_map, long long ldo,
+                          float* dgamma, float* dbeta, int rows, int D, cudaStream_t s);
+
+// Projection.call for q, k, v in one pass over the normalised map — models/CvT(Par).py:102-112,157-170.
+//   method[z]: 0 depthwise 3x3 (SAME, no bias), 1 3x3 average pool (SAME, valid-count divisor), 2 identity
+//   xn [B,Tc,D] (cls row first when has_cls); out [3][B,Tc,D]; cls rows are copied through.
+//   stats (nullable) [6][D]: per-channel sum (q,k,v) then sum of squares (q,k,v) over the B*H*W non-cls tokens.
+struct DwProjP {
+  const float* xn; float* out; long long out_bs; const float* w; int method[3];
+  int B, H, W, D, Tc, has_cls; float* stats;
+};
+cudaError_t launch_dwproj_fwd(const DwProjP& p, cudaStream_t s);
+
+// BatchNormalization bookkeeping for the three branches: batch (training) or moving (inference) statistics ->
+// per-channel scale/shift applied when the q/k/v GEMM loads its A operand; moving-stat update (momentum, Bessel).
+struct BnFinalizeP {
+  const float* stats; long long count; const float* gamma; const float* beta; float* moving_mean; float* moving_var;
+  int training; int update_moving; float eps, momentum; float* scale; float* shift; float* save_mean; float* save_rstd; int D;
+};
+cudaError_t launch_bn_finalize(const BnFinalizeP& p, cudaStream_t s);
+
+// BN backward, pass 1: dgamma[z][c] += sum dy*xhat, dbeta[z][c] += sum dy over the non-cls tokens.
+cudaError_t launch_bn_bwd_reduce(const float* dy, const float* conv, long long bs, const float* save_mean, const float* save_rstd,
+                                 float* dgamma, float* dbeta, int B, int T, int Tc, int has_cls, int D, cudaStream_t s);
+// BN backward, pass 2 (in place on dy): dconv = gamma*rstd*(dy - dbeta/N - xhat*dgamma/N)  (training)
+//                                       dconv = dy*scale                                   (inference statistics)
+cudaError_t launch_bn_bwd_apply(float* dy, const float* conv, long long bs, const float* save_mean, const float* save_rstd,
+                                const float* gamma, const float* scale, const float* dgamma, const float* dbeta, int training,
+                                int B, int T, int Tc, int has_cls, int D, cudaStream_t s);
+// transposed Projection: dxn = sum_z proj_z^T(dconv_z) (+ cls rows summed), ddw[z][9][D] += (atomics)
+struct DwProjBwdP {
+  const float* dconv; long long bs; const float* xn; const float* w; int method[3];
+  int B, H, W, D, Tc, has_cls; float* dxn; float* ddw;
+};
+cudaError_t launch_dwproj_bwd(const DwProjBwdP& p, cudaStream_t s);
+
+// softmax over the last axis, in place (fp32 attention path) and its backward dS = P*(dP - sum(dP*P)), in place on dP
+cudaError_t launch_softmax_rows(float* S, long long rows, int cols, cudaStream_t s);
+cudaError_t launch_softmax_bwd_rows(float* dP, const float* P, long long rows, int cols, cudaStream_t s);
+
+// dropout keep-masks from Philox4x32-10 (same stream as oracle.dropout_mask)
+cudaError_t launch_philox_mask(uint8_t* mask, long long n, float rate, uint64_t seed, uint32_t step, uint32_t site, cudaStream_t s);
+// dst = src * mask * scale
+cudaError_t launch_mask_scale(float* dst, const float* src, const uint8_t* mask, float scale, long long n, cudaStream_t s);
+// dst[map(r)*ld + c] = src[c] for r < rows (cls token broadcast)
+cudaError_t launch_fill_rows(float* dst, RowMap map, long long ld, const float* src, int rows, int D, cudaStream_t s);
+// out[b*ldo + c] = mean_t x[(b*T+t)*D + c]  and its transpose dx[(b*T+t)*D + c] = dy[b*ldy + c] / T
+cudaError_t launch_token_mean(const float* x, int B, int T, int D, float* out, long long ldo, cudaStream_t s);
+cudaError_t launch_token_mean_bwd(const float* dy, long long lddy, int B, int T, int D, float* dx, cudaStream_t s);
+// copy rows: dst[dmap(r)*ldd + c] = src[smap(r)*lds + c]
+cudaError_t launch_copy_rows(float* dst, RowMap dmap, long long ldd, const float* src, RowMap smap, long long lds, int rows, int D, cudaStream_t s);
+
+// MSE + MAE + dL/dpred  (model.compile(loss='mean_squared_error', metrics=['mae']), models/CvT(Par).py:464-466)
+// metrics[0] = mean((p-y)^2), metrics[1] = mean(|p-y|); dpred = 2 (p-y) / (B*nc) * grad_scale (nullable)
+cudaError_t launch_mse_loss(const float* pred, const float* y, int n, float* metrics, float* dpred, float grad_scale, int accumulate, cudaStream_t s);
+
+// Keras Adam on a flat arena: m,v update; theta -= alpha * m / (sqrt(v) + eps); alpha = lr*sqrt(1-b2^t)/(1-b1^t)
+cudaError_t launch_adam(float* params, const float* grads, float* m, float* v, long long n, float alpha, float b1, float b2,
+                        float eps, float grad_scale, cudaStream_t s);
+
+}  // namespace cvt

@@ -1,0 +1,97 @@
+// Internal model state of libcvt_b200: parameter arenas, per-stage activation buffers, scratch.
+#pragma once
+#include <string>
+#include <vector>
+
+#include "../../include/cvt_b200.h"
+#include "common.cuh"
+#include "gemm.cuh"
+#include "layers.cuh"
+
+namespace cvt {
+
+struct ParamInfo {
+  std::string name;
+  int rank = 0;
+  int64_t shape[4] = {1, 1, 1, 1};
+  bool trainable = true;
+  int64_t numel = 0;
+  int64_t offset = 0;          // floats; into the trainable arena or the state arena
+};
+
+// offsets (floats) of one stage's weights inside the trainable arena P (and G / Adam m / v)
+struct StageW {
+  int64_t conv_w, conv_b, cls, ln_g, ln_b;
+  int64_t dw, bn_g, bn_b;                 // [3][9][D], [3][D], [3][D]       (dw_bn only)
+  int64_t pw, pb, mw, mb;                 // proj_{q,k,v} [3][D][D],[3][D]; mha {query,key,value} [3][D][D],[3][D]
+  int64_t ow, ob, prw, prb, f1w, f1b, f2w, f2b;
+  int64_t bn_mm, bn_mv;                   // state arena: moving mean / variance [3][D]
+};
+
+struct StageGeo {
+  int hin, win, cin, H, W, D, T, Tc, heads, has_cls, k, s, pt, pl, method;
+};
+
+// activations kept from the forward pass (training keeps everything the backward reads)
+struct StageBuf {
+  float *x0, *xn, *conv, *qkv1, *qkv2, *attn_o, *a1, *x1, *y, *hpre, *hact, *x2;
+  float *lna_mean, *lna_rstd, *lnb_mean, *lnb_rstd;
+  float *bn_stats, *bn_scale, *bn_shift, *bn_mean, *bn_rstd;
+  float *scores;                         // fp32 attention path: P [B*heads, Tc, Tc]
+  float *lse;                            // tensor-core attention path: log-sum-exp [B*heads, Tc]
+  uint8_t *mask_proj, *mask1, *mask2;
+};
+
+struct Model {
+  cvt_config cfg;
+  int n_stages = 0;
+  StageGeo geo[CVT_MAX_STAGES];
+  StageW w[CVT_MAX_STAGES];
+  StageBuf buf[CVT_MAX_STAGES];
+  int64_t hn_g = 0, hn_b = 0, pd1w = 0, pd1b = 0, pd2w = 0, pd2b = 0, fw = 0, fb = 0;   // head weights
+  int head_kind = CVT_HEAD_CLS_LN, feat_dim = 0, d_last = 0;
+
+  std::vector<ParamInfo> params;
+  int64_t n_train = 0, n_state = 0;       // arena lengths (floats, multiples of 4)
+  float *P = nullptr, *G = nullptr, *Mo = nullptr, *Vo = nullptr, *St = nullptr;
+
+  // head buffers
+  float *feat = nullptr, *hln = nullptr, *h_mean = nullptr, *h_rstd = nullptr, *p1 = nullptr, *pred = nullptr;
+  float *dpred = nullptr, *dfeat = nullptr, *dp1 = nullptr, *dhln = nullptr;
+  float *metrics = nullptr;               // device [2]: loss, mae
+  // gradient scratch shared by the stages
+  float *gX[2] = {nullptr, nullptr};      // gradient w.r.t. a block output [B,Tc,D] (ping-pong across stages)
+  float *gH = nullptr, *gC = nullptr, *gD = nullptr, *gE = nullptr, *gM = nullptr, *gQ = nullptr, *gQ2 = nullptr, *gS = nullptr;
+  // staging for host-buffer entry points
+  float *in_img = nullptr, *in_proc = nullptr, *in_y = nullptr, *out_pred = nullptr;
+  float *pin_metrics = nullptr;           // pinned host [2]
+
+  void* workspace = nullptr;
+  int64_t workspace_bytes = 0;
+
+  cudaStream_t stream = nullptr;
+  int last_batch = 0, last_training = 0, have_forward = 0;
+  int dropout_mode = CVT_DROPOUT_OFF;
+  uint64_t dropout_seed = 0;
+  uint32_t dropout_step = 0;
+  int64_t adam_t = 0;
+  long long launches = 0;
+
+  // data parallel
+  void* nccl_comm = nullptr;
+  int rank = 0, world = 1;
+
+  // CUDA graphs
+  int use_graphs = 0;
+  cudaGraphExec_t train_graph = nullptr; int train_graph_batch = 0; float* lr_dev = nullptr;
+  cudaGraphExec_t fwd_graph = nullptr; int fwd_graph_batch = 0;
+};
+
+// attention dispatch (attention.cu)
+cudaError_t attention_forward(Model* m, int si, int B, cudaStream_t s);
+cudaError_t attention_backward(Model* m, int si, int B, const float* dO, float* dQKV, cudaStream_t s);
+
+// contraction dispatch by precision (fp32 FFMA vs tcgen05)
+cudaError_t run_gemm(const Model* m, const GemmP& p, cudaStream_t s);
+
+}  // namespace cvt
