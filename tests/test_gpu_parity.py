@@ -1,0 +1,161 @@
+"""Parity of the CUDA path (through the C-ABI) against the CPU oracle on the same seeded inputs.
+Tolerance: max|a-b| / max|b| per tensor; 1e-4 for activations and 1e-3 for gradients in fp32 mode (north_star: rtol 1e-3)."""
+import numpy as np
+import pytest
+import torch
+
+import transformer_stm_b200 as T
+from oracle import cvt_oracle as O
+from tests.parity_utils import compare_grads, compare_taps, fmt, make_pair, rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+def _dev(a):
+    return torch.tensor(np.ascontiguousarray(a, dtype=np.float32), device="cuda")
+
+
+def _run_forward_backward(spec, eng, params, img, proc, y, training, masks=None):
+    d_img, d_y = _dev(img), _dev(y)
+    d_proc = _dev(proc) if spec.proc_dim > 0 else None
+    torch.cuda.synchronize()
+    eng.forward_dev(d_img, d_proc, img.shape[0], training)
+    loss, mae = eng.loss_backward_dev(d_y)
+    keep = (d_img, d_proc, d_y)
+    return loss, mae, keep
+
+
+def test_param_table_matches_oracle():
+    spec, eng, params, *_ = make_pair(hw=(32, 32), batch=1)
+    infos = {p["name"]: p for p in eng.param_infos()}
+    want = {n: (s, t) for n, s, t in O.param_specs(spec)}
+    assert set(infos) == set(want)
+    for n, (s, t) in want.items():
+        assert tuple(infos[n]["shape"]) == tuple(s) and infos[n]["trainable"] == t, n
+    back = eng.get_params()
+    for k, v in params.items():
+        assert np.array_equal(back[k], v.astype(np.float32)), k
+    eng.close()
+
+
+@pytest.mark.parametrize("method,cls,proc_dim,nc,hw", [
+    ("dw_bn", True, 5, 1, (32, 32)),
+    ("dw_bn", False, 0, 1, (32, 32)),
+    ("avg", True, 5, 3, (32, 32)),
+    ("linear", False, 5, 1, (32, 32)),
+    ("dw_bn", True, 5, 1, (36, 44)),          # ragged maps: 9x11 / 5x6 / 3x3, odd SAME pads
+])
+def test_inference_forward_taps(method, cls, proc_dim, nc, hw):
+    spec, eng, params, img, proc, y = make_pair(method, cls, proc_dim, nc, hw, batch=3)
+    pred = eng.predict(img, proc)
+    ref, taps = O.forward(spec, params, img, proc, training=False)
+    bad, report = compare_taps(eng, taps, tol=2e-4)
+    assert not bad, "forward mismatches:\n" + fmt(report)
+    assert rel_err(pred, ref) < 2e-4
+    eng.close()
+
+
+@pytest.mark.parametrize("method,cls,proc_dim,nc,hw,batch", [
+    ("dw_bn", True, 5, 1, (32, 32), 4),
+    ("dw_bn", False, 0, 2, (32, 32), 3),
+    ("avg", False, 5, 1, (32, 32), 3),
+    ("linear", True, 5, 1, (32, 32), 3),
+    ("dw_bn", True, 5, 1, (36, 44), 2),
+])
+def test_training_forward_and_gradients(method, cls, proc_dim, nc, hw, batch):
+    spec, eng, params, img, proc, y = make_pair(method, cls, proc_dim, nc, hw, batch=batch)
+    masks = O.make_dropout_masks(spec, batch, seed=99, step=0)
+    eng.set_dropout("masks")
+    eng.set_dropout_masks(masks)
+    loss, mae, keep = _run_forward_backward(spec, eng, params, img, proc, y, True)
+    r = O.loss_and_grads(spec, params, img, proc, y, masks)
+    bad, report = compare_taps(eng, r["taps"], tol=2e-4)
+    assert not bad, "training forward mismatches:\n" + fmt(report)
+    assert abs(loss - r["loss"]) <= 1e-4 * abs(r["loss"]) and abs(mae - r["mae"]) <= 1e-4 * abs(r["mae"])
+    bad, report = compare_grads(eng, r["grads"], tol=1e-3)
+    assert not bad, "gradient mismatches:\n" + fmt(report)
+    # BN moving statistics updated by the training forward
+    got = eng.get_params()
+    for k, v in r["new_moving"].items():
+        assert rel_err(got[k], v) < 1e-4, k
+    eng.close()
+
+
+def test_philox_dropout_matches_oracle_stream():
+    spec, eng, params, img, proc, y = make_pair(hw=(32, 32), batch=3)
+    eng.set_dropout("philox", seed=2024)
+    for step in range(2):
+        loss, mae, keep = _run_forward_backward(spec, eng, params, img, proc, y, True)
+        masks = O.make_dropout_masks(spec, 3, seed=2024, step=step)
+        # the forward above changed the BN moving stats but not the trainable weights -> same oracle weights
+        r = O.loss_and_grads(spec, params, img, proc, y, masks)
+        assert rel_err(eng.tap("s1.hact"), r["taps"]["s1.hact"]) < 2e-4
+        assert rel_err(eng.tap("pred"), r["taps"]["pred"]) < 2e-4
+    eng.close()
+
+
+def test_reference_config_128_train_step_matches_oracle():
+    """configs[1] geometry (128x128, dims 64/128/256, cls, dw_bn, proc) at a batch the oracle finishes in seconds."""
+    spec, eng, params, img, proc, y = make_pair(hw=(128, 128), batch=4)
+    eng.set_dropout("off")
+    loss, mae = eng.train_step(img, proc, y, 1e-3)
+    p64 = {k: v.copy() for k, v in params.items()}
+    st = O.new_opt_state(p64)
+    r = O.train_step(spec, p64, st, img, proc, y, 1e-3, None)
+    assert abs(loss - r["loss"]) <= 1e-4 * abs(r["loss"])
+    bad, report = compare_grads(eng, r["grads"], tol=1e-3)
+    assert not bad, "gradient mismatches:\n" + fmt(report)
+    got = eng.get_params()
+    # Adam's first step moves every weight by ~lr*sign(g): compare the update direction where |g| is not tiny
+    for k in r["grads"]:
+        upd_ref = p64[k] - params[k]
+        upd = got[k].astype(np.float64) - params[k].astype(np.float32).astype(np.float64)
+        sel = np.abs(r["grads"][k]) > 1e-3 * np.abs(r["grads"][k]).max()
+        if sel.any():
+            assert np.allclose(upd[sel], upd_ref[sel], atol=2e-5), k
+    eng.close()
+
+
+def test_three_train_steps_track_oracle():
+    spec, eng, params, img, proc, y = make_pair(hw=(32, 32), batch=4)
+    eng.set_dropout("off")
+    p64 = {k: v.copy() for k, v in params.items()}
+    st = O.new_opt_state(p64)
+    for step in range(3):
+        loss, _ = eng.train_step(img, proc, y, 1e-3)
+        r = O.train_step(spec, p64, st, img, proc, y, 1e-3, None)
+        assert abs(loss - r["loss"]) <= 2e-3 * abs(r["loss"]), (step, loss, r["loss"])
+    eng.close()
+
+
+def test_predict_chunks_and_ragged_batch():
+    spec, eng, params, img, proc, y = make_pair(hw=(32, 32), batch=7, max_batch=3)
+    pred = eng.predict(img, proc)                  # 7 samples through max_batch 3 -> chunks 3,3,1
+    ref, _ = O.forward(spec, params, img, proc)
+    assert rel_err(pred, ref) < 2e-4
+    l, a = eng.evaluate(img, proc, y)
+    assert abs(l - float(((ref - y) ** 2).mean())) <= 1e-4 * l
+    eng.close()
+
+
+def test_errors_are_loud():
+    with pytest.raises(T.CvtError):
+        T.CvtEngine(T.CvtConfig.reference(dims=(64, 100, 256)))      # embed_dim not a multiple of 64
+    with pytest.raises(ValueError):
+        T.CvtConfig.reference(projection_method="conv").to_c()        # Unknown method (models/CvT(Par).py:100)
+    eng = T.CvtEngine(T.CvtConfig.reference(image_h=32, image_w=32, max_batch=2))
+    with pytest.raises(T.CvtError):
+        eng.predict(np.zeros((1, 32, 32, 1), np.float32), None)       # Par model without process parameters
+    with pytest.raises(T.CvtError):
+        eng.tap("s9.nope")
+    eng.close()
+
+
+def test_gradcam_tap_gradient():
+    """tools/grad_cam_CvT.py:446-457: d pred[:,0] / d block output, here for a no-cls model (head = LN + token mean)."""
+    spec, eng, params, img, proc, y = make_pair("dw_bn", False, 5, 1, (32, 32), batch=2)
+    pred = eng.predict(img, proc)
+    g = eng.backward_to_tap(np.ones((2, 1), np.float32), "s3.x2", 2 * 4 * 256)
+    heat, feat, gref = O.gradcam(spec, params, img, proc, "s3.out")
+    assert rel_err(g, gref) < 1e-3
+    eng.close()

@@ -1,0 +1,102 @@
+"""ctypes binding of libcvt_b200.so (include/cvt_b200.h).  No CPU fallback: if the library is missing this raises."""
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "csrc", "libcvt_b200.so")
+MAX_STAGES = 4
+
+PROJ = {"dw_bn": 0, "avg": 1, "linear": 2}
+PREC = {"fp32": 0, "tf32": 1, "bf16": 2}
+DROPOUT_OFF, DROPOUT_PHILOX, DROPOUT_MASKS = 0, 1, 2
+
+
+class StageConfig(C.Structure):
+    _fields_ = [("embed_dim", C.c_int32), ("patch_size", C.c_int32), ("stride", C.c_int32),
+                ("num_heads", C.c_int32), ("qkv_method", C.c_int32), ("with_cls_token", C.c_int32)]
+
+
+class Config(C.Structure):
+    _fields_ = [("image_h", C.c_int32), ("image_w", C.c_int32), ("in_chans", C.c_int32), ("n_stages", C.c_int32),
+                ("stage", StageConfig * MAX_STAGES),
+                ("proc_dim", C.c_int32), ("proc_hidden", C.c_int32), ("num_classes", C.c_int32), ("mlp_ratio", C.c_int32),
+                ("drop_rate", C.c_float), ("ln_eps", C.c_float), ("bn_eps", C.c_float), ("bn_momentum", C.c_float),
+                ("precision", C.c_int32), ("max_batch", C.c_int32), ("device", C.c_int32)]
+
+
+class CvtError(RuntimeError):
+    pass
+
+
+_PROTOS = {
+    "cvt_abi_version": (C.c_int, []),
+    "cvt_default_config": (None, [C.POINTER(Config)]),
+    "cvt_create": (C.c_int, [C.POINTER(Config), C.POINTER(C.c_void_p)]),
+    "cvt_destroy": (None, [C.c_void_p]),
+    "cvt_last_error": (C.c_char_p, []),
+    "cvt_param_count": (C.c_int, [C.c_void_p]),
+    "cvt_param_info": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_int32), C.POINTER(C.c_int64),
+                                 C.POINTER(C.c_int32), C.POINTER(C.c_int64)]),
+    "cvt_param_index": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "cvt_set_param": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
+    "cvt_get_param": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
+    "cvt_get_grad": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
+    "cvt_init_params": (C.c_int, [C.c_void_p, C.c_uint64]),
+    "cvt_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "cvt_predict_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
+    "cvt_loss_backward": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
+    "cvt_adam_step": (C.c_int, [C.c_void_p, C.c_float]),
+    "cvt_train_step": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float]),
+    "cvt_train_step_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float,
+                                      C.POINTER(C.c_float), C.POINTER(C.c_float)]),
+    "cvt_evaluate_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                    C.POINTER(C.c_float), C.POINTER(C.c_float)]),
+    "cvt_read_metrics": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
+    "cvt_optimizer_reset": (C.c_int, [C.c_void_p]),
+    "cvt_optimizer_step_count": (C.c_int64, [C.c_void_p]),
+    "cvt_set_dropout": (C.c_int, [C.c_void_p, C.c_int, C.c_uint64]),
+    "cvt_set_dropout_mask": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int64]),
+    "cvt_get_tap": (C.c_int64, [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int64]),
+    "cvt_backward_to_tap": (C.c_int, [C.c_void_p, C.c_void_p, C.c_char_p, C.c_void_p, C.c_int64]),
+    "cvt_comm_unique_id": (C.c_int, [C.c_void_p]),
+    "cvt_comm_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
+    "cvt_comm_destroy": (C.c_int, [C.c_void_p]),
+    "cvt_grad_arena": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]),
+    "cvt_param_arena": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]),
+    "cvt_synchronize": (C.c_int, [C.c_void_p]),
+    "cvt_stream": (C.c_void_p, [C.c_void_p]),
+    "cvt_set_graphs": (C.c_int, [C.c_void_p, C.c_int]),
+    "cvt_kernel_launches": (C.c_int64, [C.c_void_p]),
+    "cvt_workspace_bytes": (C.c_int64, [C.c_void_p]),
+    "cvt_profile_step": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
+                                   C.POINTER(C.c_char_p), C.POINTER(C.c_float), C.POINTER(C.c_int)]),
+}
+
+_lib = None
+
+
+def exported_names():
+    return sorted(_PROTOS)
+
+
+def load():
+    """Loads the shared library (building nothing: run __graft_entry__.build() first)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise CvtError("libcvt_b200.so is not built (%s); run `python __graft_entry__.py` — there is no CPU fallback" % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in _PROTOS.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc, what=""):
+    if rc is not None and rc < 0:
+        msg = load().cvt_last_error()
+        raise CvtError("%s failed (%d): %s" % (what or "cvt call", rc, msg.decode() if msg else "?"))
+    return rc
