@@ -415,12 +415,12 @@ def forward_torch(spec: CvtSpec, P: Dict[str, torch.Tensor], img: torch.Tensor, 
         feat = layer_norm(cls_out, hg, hb, spec.ln_eps).squeeze(1)
     else:
         feat = layer_norm(x.reshape(bsz, -1, x.shape[-1]), hg, hb, spec.ln_eps).mean(dim=1)
-    taps["head.feat"] = feat
     if spec.proc_dim > 0:
         p1 = torch.relu(proc @ P["Proc_Dense_1/kernel"] + P["Proc_Dense_1/bias"])
         p2 = torch.relu(p1 @ P["Proc_Dense_2/kernel"] + P["Proc_Dense_2/bias"])
         taps["head.proc1"], taps["head.proc2"] = p1, p2
         feat = torch.cat([feat, p2], dim=1)
+    taps["head.feat"] = feat
     pred = feat @ P["Final_Dense/kernel"] + P["Final_Dense/bias"]
     taps["pred"] = pred
     return pred, taps, bn_stats

@@ -21,11 +21,11 @@ def make_pair(method="dw_bn", cls=True, proc_dim=5, nc=1, hw=(32, 32), dims=(64,
     return spec, eng, params, img, proc, y
 
 
-def rel_err(a, b):
+def rel_err(a, b, floor=1e-30):
     a = np.asarray(a, dtype=np.float64).reshape(-1)
     b = np.asarray(b, dtype=np.float64).reshape(-1)
     assert a.shape == b.shape, (a.shape, b.shape)
-    den = max(float(np.abs(b).max()), 1e-30)
+    den = max(float(np.abs(b).max()), floor)
     return float(np.abs(a - b).max()) / den
 
 
@@ -49,10 +49,13 @@ def compare_taps(eng, taps, n_stages=3, tol=1e-4, names=TAPS):
 
 
 def compare_grads(eng, grads, tol=1e-3):
+    """Per tensor max|a-b| / max(max|b|, floor).  The floor (1e-4 of the largest gradient in the model) keeps
+    analytically-zero gradients (key biases: softmax is shift-invariant) from dividing noise by noise."""
     got = eng.get_grads()
     bad, report = [], []
+    floor = 1e-4 * max(float(np.abs(g).max()) for g in grads.values())
     for k, g in grads.items():
-        e = rel_err(got[k], g)
+        e = rel_err(got[k], g, floor)
         report.append((k, e))
         if not (e <= tol):
             bad.append((k, e))

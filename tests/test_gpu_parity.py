@@ -107,10 +107,12 @@ def test_reference_config_128_train_step_matches_oracle():
     assert not bad, "gradient mismatches:\n" + fmt(report)
     got = eng.get_params()
     # Adam's first step moves every weight by ~lr*sign(g): compare the update direction where |g| is not tiny
+    # (analytically-zero gradients, e.g. key biases, are fp noise that Adam's 1e-7 epsilon amplifies: excluded)
+    gfloor = 1e-4 * max(float(np.abs(g).max()) for g in r["grads"].values())
     for k in r["grads"]:
         upd_ref = p64[k] - params[k]
         upd = got[k].astype(np.float64) - params[k].astype(np.float32).astype(np.float64)
-        sel = np.abs(r["grads"][k]) > 1e-3 * np.abs(r["grads"][k]).max()
+        sel = np.abs(r["grads"][k]) > max(1e-3 * np.abs(r["grads"][k]).max(), gfloor)
         if sel.any():
             assert np.allclose(upd[sel], upd_ref[sel], atol=2e-5), k
     eng.close()

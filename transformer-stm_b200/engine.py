@@ -168,7 +168,7 @@ class CvtEngine:
     def predict(self, img, proc=None) -> np.ndarray:
         a = self._img(img)
         n = a.shape[0]
-        p = _f32(proc, (n, self.cfg.proc_dim)) if self.cfg.proc_dim > 0 else None
+        p = _f32(proc, (n, self.cfg.proc_dim)) if (self.cfg.proc_dim > 0 and proc is not None) else None
         out = np.empty((n, self.cfg.num_classes), dtype=np.float32)
         L.check(self.lib.cvt_predict_host(self.h, a.ctypes.data_as(C.c_void_p), p.ctypes.data_as(C.c_void_p) if p is not None else None,
                                           n, out.ctypes.data_as(C.c_void_p)), "cvt_predict_host")
@@ -177,7 +177,7 @@ class CvtEngine:
     def train_step(self, img, proc, y, lr: float):
         a = self._img(img)
         n = a.shape[0]
-        p = _f32(proc, (n, self.cfg.proc_dim)) if self.cfg.proc_dim > 0 else None
+        p = _f32(proc, (n, self.cfg.proc_dim)) if (self.cfg.proc_dim > 0 and proc is not None) else None
         t = _f32(y, (n, self.cfg.num_classes))
         loss, mae = C.c_float(), C.c_float()
         L.check(self.lib.cvt_train_step_host(self.h, a.ctypes.data_as(C.c_void_p), p.ctypes.data_as(C.c_void_p) if p is not None else None,
@@ -187,7 +187,7 @@ class CvtEngine:
     def evaluate(self, img, proc, y):
         a = self._img(img)
         n = a.shape[0]
-        p = _f32(proc, (n, self.cfg.proc_dim)) if self.cfg.proc_dim > 0 else None
+        p = _f32(proc, (n, self.cfg.proc_dim)) if (self.cfg.proc_dim > 0 and proc is not None) else None
         t = _f32(y, (n, self.cfg.num_classes))
         loss, mae = C.c_float(), C.c_float()
         L.check(self.lib.cvt_evaluate_host(self.h, a.ctypes.data_as(C.c_void_p), p.ctypes.data_as(C.c_void_p) if p is not None else None,
