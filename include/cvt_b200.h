@@ -162,6 +162,10 @@ CVT_API int64_t cvt_workspace_bytes(const cvt_model* m);
 CVT_API int  cvt_profile_step(cvt_model* m, const float* img_dev, const float* proc_dev, const float* y_dev, int batch,
                       int training, int max_entries, const char** names, float* ms, int* n_entries);
 
+/* diagnostics: C[M,N] = A x B through the fp32 FFMA kernel (use_tc = 0) or the tcgen05 kernel (use_tc = 1) on device 0.
+ * a_mode 0: A is [M,K] row-major, 1: A is [K,M] (read transposed);  b_mode 0: B is [K,N], 1: B is [N,K]. */
+CVT_API int  cvt_debug_gemm(int a_mode, int b_mode, int M, int N, int K, int splitk, int use_tc, const float* A, const float* B, float* C);
+
 #ifdef __cplusplus
 }
 #endif

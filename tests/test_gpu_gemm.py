@@ -1,0 +1,54 @@
+"""The tcgen05 (TF32) contraction kernel against the fp32 FFMA kernel and numpy, for every operand major-ness."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from transformer_stm_b200 import _lib
+
+pytestmark = pytest.mark.gpu
+
+
+def run(a_mode, b_mode, M, N, K, splitk, use_tc, A, B):
+    lib = _lib.load()
+    out = np.zeros((M, N), np.float32)
+    _lib.check(lib.cvt_debug_gemm(a_mode, b_mode, M, N, K, splitk, use_tc, A.ctypes.data_as(C.c_void_p), B.ctypes.data_as(C.c_void_p),
+                                  out.ctypes.data_as(C.c_void_p)), "cvt_debug_gemm")
+    return out
+
+
+def tf32(x):
+    """round-to-nearest (ties away) to 10 mantissa bits, what cvt.rna.tf32.f32 does"""
+    u = x.astype(np.float32).view(np.uint32).astype(np.uint64)
+    u = (u + 0x1000) & 0xFFFFE000
+    return u.astype(np.uint32).view(np.float32)
+
+
+CASES = [(128, 64, 32), (128, 64, 64), (256, 128, 96), (300, 256, 64), (128, 64, 49), (1000, 192, 256), (64, 1024, 128), (4160, 256, 256)]
+
+
+@pytest.mark.parametrize("a_mode,b_mode", [(0, 1), (0, 0), (1, 1), (1, 0)])
+@pytest.mark.parametrize("M,N,K", CASES)
+def test_tc_gemm_matches_ffma(a_mode, b_mode, M, N, K):
+    rng = np.random.default_rng(M * 7 + N * 3 + K + a_mode * 2 + b_mode)
+    A = rng.standard_normal((M, K)).astype(np.float32)
+    B = rng.standard_normal((K, N)).astype(np.float32)
+    Ah = np.ascontiguousarray(A if a_mode == 0 else A.T)
+    Bh = np.ascontiguousarray(B if b_mode == 0 else B.T)
+    ref = tf32(A).astype(np.float64) @ tf32(B).astype(np.float64)
+    simt = run(a_mode, b_mode, M, N, K, 1, 0, Ah, Bh)
+    assert np.abs(simt - A.astype(np.float64) @ B.astype(np.float64)).max() < 1e-3 * np.sqrt(K)
+    got = run(a_mode, b_mode, M, N, K, 1, 1, Ah, Bh)
+    err = np.abs(got - ref).max()
+    assert err < 2e-4 * np.sqrt(K), (a_mode, b_mode, M, N, K, err, np.abs(got).max())
+
+
+@pytest.mark.parametrize("a_mode,b_mode", [(1, 0), (0, 1)])
+def test_tc_gemm_splitk_atomic(a_mode, b_mode):
+    M, N, K = 192, 128, 4096
+    rng = np.random.default_rng(5)
+    A = rng.standard_normal((M, K)).astype(np.float32); B = rng.standard_normal((K, N)).astype(np.float32)
+    Ah = np.ascontiguousarray(A if a_mode == 0 else A.T); Bh = np.ascontiguousarray(B if b_mode == 0 else B.T)
+    ref = tf32(A).astype(np.float64) @ tf32(B).astype(np.float64)
+    got = run(a_mode, b_mode, M, N, K, 8, 1, Ah, Bh)
+    assert np.abs(got - ref).max() < 2e-4 * np.sqrt(K)
