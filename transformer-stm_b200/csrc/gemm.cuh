@@ -42,6 +42,7 @@ struct GemmP {
   uint32_t epi = 0;
   const float* resid = nullptr; long long ldr = 0;
   const uint8_t* mask = nullptr; float mask_scale = 1.f;
+  int dbg = 0;                                 // diagnostics only (cvt_debug_gemm): bit 0 swaps LBO/SBO of MN-major descriptors
   float* aux = nullptr;                        // same indexing as C: GELU pre-activation (write) / saved activation (read)
 };
 

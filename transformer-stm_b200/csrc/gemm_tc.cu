@@ -136,8 +136,8 @@ __global__ void __launch_bounds__(128) gemm_tc_kernel(const __grid_constant__ Ge
       const uint32_t a0 = smem_u32(sA + s * A_TILE_BYTES), b0 = smem_u32(sB + s * C::B_TILE_BYTES);
 #pragma unroll
       for (int j = 0; j < TBK / 8; ++j) {
-        const uint64_t ad = A_ROWFIXED ? make_smem_desc(a0 + j * 32, 16, 1024) : make_smem_desc(a0 + j * (TBM / 32) * 1024, 1024, (TBM / 32) * 1024);
-        const uint64_t bd = B_KMAJOR ? make_smem_desc(b0 + j * 32, 16, 1024) : make_smem_desc(b0 + j * (BN / 32) * 1024, 1024, (BN / 32) * 1024);
+        const uint64_t ad = A_ROWFIXED ? make_smem_desc(a0 + j * 32, 16, 1024) : make_smem_desc(a0 + j * (TBM / 32) * 1024, (p.dbg & 1) ? (TBM / 32) * 512 : 512, (p.dbg & 1) ? 512 : (TBM / 32) * 512, kLayoutSw128Base32);
+        const uint64_t bd = B_KMAJOR ? make_smem_desc(b0 + j * 32, 16, 1024) : make_smem_desc(b0 + j * (BN / 32) * 1024, (p.dbg & 1) ? (BN / 32) * 512 : 512, (p.dbg & 1) ? 512 : (BN / 32) * 512, kLayoutSw128Base32);
         mma_tf32_ss(tmem_base, ad, bd, idesc, (kt > 0 || j > 0) ? 1u : 0u);
       }
       mma_commit(&bars[s]);
@@ -267,6 +267,7 @@ extern "C" CVT_API int cvt_debug_gemm(int a_mode, int b_mode, int M, int N, int 
   p.A = dA; p.a_mode = a_mode; p.lda = a_mode == A_PLAIN ? K : M;
   p.B = dB; p.b_mode = b_mode; p.ldb = b_mode == B_KN ? N : K;
   p.C = dC; p.ldc = N; if (splitk > 1) p.epi = EPI_ATOMIC;
+  p.dbg = use_tc >> 1;
   if (use_tc && !gemm_tc_supports(p)) { cudaFree(dA); cudaFree(dB); cudaFree(dC); set_error("cvt_debug_gemm: shape not supported by the tcgen05 kernel"); return CVT_ERR_INVALID; }
   e = use_tc ? launch_gemm_tc(p, 0) : launch_gemm_simt(p, 0);
   if (e != cudaSuccess) return fail(e);

@@ -97,14 +97,16 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float v[32]) {
 
 // ---- descriptors -----------------------------------------------------------------------------------------------------------
 // Shared-memory matrix descriptor (64 bit): [0,14) start>>4, [16,30) LBO>>4, [32,46) SBO>>4, [46,48) version=1, [61,64) layout.
-constexpr uint64_t kLayoutSw128 = 2;
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+constexpr uint64_t kLayoutSw128 = 2;        // Swizzle<3,4,3>: 16-byte chunk ^= 128-byte line index (mod 8); K-major operands
+constexpr uint64_t kLayoutSw128Base32 = 1;  // Swizzle<2,5,2>: 32-byte chunk ^= 128-byte line index (mod 4); the only swizzle a
+                                            // 32-bit (tf32) MN-major operand may use
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint64_t layout = kLayoutSw128) {
   uint64_t d = 0;
   d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
   d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
   d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
   d |= (uint64_t)1 << 46;
-  d |= kLayoutSw128 << 61;
+  d |= layout << 61;
   return d;
 }
 // Instruction descriptor (32 bit) for kind::tf32 / kind::f16 with fp32 accumulate:
@@ -119,9 +121,11 @@ __host__ __device__ constexpr uint32_t make_idesc(uint32_t fmt, uint32_t M, uint
 __device__ __forceinline__ uint32_t sw128_kmajor_off(int row, int chunk /*0..7, 16-byte units along K*/) {
   return (uint32_t)((row >> 3) * 1024 + (row & 7) * 128 + ((chunk ^ (row & 7)) << 4));
 }
-// MN-major tile [32 k][mn]: atom = 8 k-lines x 32 mn-floats; atoms ordered [k/8][mn/32]
+// MN-major fp32 tile [k][mn] (SWIZZLE_128B_BASE32B): atom = 4 k-lines x 32 mn-floats (512 bytes); atoms ordered [k/4][mn/32];
+// inside an atom line k&3 holds four 32-byte chunks, chunk index ^= (k & 3).   LBO = 512 (next MN atom), SBO = mn_atoms*512
+// (next group of 4 k); one K=8 MMA spans two k-groups.
 __device__ __forceinline__ uint32_t sw128_mnmajor_off(int k, int mn4 /*float4 index along MN*/, int mn_atoms) {
-  return (uint32_t)(((k >> 3) * mn_atoms + (mn4 >> 3)) * 1024 + (k & 7) * 128 + (((mn4 & 7) ^ (k & 7)) << 4));
+  return (uint32_t)(((k >> 2) * mn_atoms + (mn4 >> 3)) * 512 + (k & 3) * 128 + (((((mn4 >> 1) & 3) ^ (k & 3))) << 5) + ((mn4 & 1) << 4));
 }
 
 __device__ __forceinline__ float to_tf32(float x) {
