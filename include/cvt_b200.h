@@ -166,6 +166,11 @@ CVT_API int  cvt_profile_step(cvt_model* m, const float* img_dev, const float* p
  * a_mode 0: A is [M,K] row-major, 1: A is [K,M] (read transposed);  b_mode 0: B is [K,N], 1: B is [N,K]. */
 CVT_API int  cvt_debug_gemm(int a_mode, int b_mode, int M, int N, int K, int splitk, int use_tc, const float* A, const float* B, float* C);
 
+/* diagnostics: the tcgen05 flash-attention kernels on host arrays.  Q (already scaled by 1/sqrt(64)), K, V, dO, O, dQ, dK, dV are
+ * [B, Tc, heads*64]; LSE is [B*heads, Tc].  dO == NULL runs the forward only.  dQ is w.r.t. the un-scaled query (x 0.125). */
+CVT_API int  cvt_debug_attention(int B, int Tc, int heads, const float* Q, const float* K, const float* V, const float* dO,
+                         float* O, float* LSE, float* dQ, float* dK, float* dV);
+
 #ifdef __cplusplus
 }
 #endif

@@ -69,6 +69,7 @@ _PROTOS = {
     "cvt_kernel_launches": (C.c_int64, [C.c_void_p]),
     "cvt_workspace_bytes": (C.c_int64, [C.c_void_p]),
     "cvt_debug_gemm": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "cvt_debug_attention": (C.c_int, [C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 9),
     "cvt_profile_step": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                    C.POINTER(C.c_char_p), C.POINTER(C.c_float), C.POINTER(C.c_int)]),
 }

@@ -149,7 +149,8 @@ static void carve(Model* m, Bump& b) {
   const cvt_config& c = m->cfg;
   const int64_t MB = c.max_batch;
   int64_t maxRD = 0, maxRH = 0, maxS = 0, maxIn = 0;
-  const bool need_scores = true;   // the fp32 attention path (also the fallback of the tensor-core path) keeps P
+  const bool need_scores = c.precision == CVT_PREC_FP32;   // only the fp32 attention path materialises P
+  int64_t maxL = 0;
   for (int i = 0; i < m->n_stages; ++i) {
     const StageGeo& g = m->geo[i];
     StageBuf& s = m->buf[i];
@@ -157,6 +158,7 @@ static void carve(Model* m, Bump& b) {
     const int64_t S = MB * g.heads * (int64_t)g.Tc * g.Tc;
     maxRD = std::max(maxRD, RD); maxRH = std::max(maxRH, RH); maxS = std::max(maxS, S);
     maxIn = std::max(maxIn, MB * (int64_t)g.hin * g.win * g.cin);
+    maxL = std::max(maxL, MB * g.heads * (int64_t)g.Tc);
     s.x0 = b.take<float>(RD); s.xn = b.take<float>(RD); s.conv = b.take<float>(3 * RD);
     s.qkv1 = b.take<float>(3 * RD); s.qkv2 = b.take<float>(3 * RD);
     s.attn_o = b.take<float>(RD); s.a1 = b.take<float>(RD); s.x1 = b.take<float>(RD); s.y = b.take<float>(RD);
@@ -183,6 +185,7 @@ static void carve(Model* m, Bump& b) {
   m->gH = b.take<float>(maxRH); m->gC = b.take<float>(maxRD); m->gD = b.take<float>(maxRD); m->gE = b.take<float>(maxRD);
   m->gM = b.take<float>(maxRD); m->gQ = b.take<float>(3 * maxRD); m->gQ2 = b.take<float>(3 * maxRD);
   m->gS = need_scores ? b.take<float>(maxS) : nullptr;
+  m->attn_dd = b.take<float>(maxL);
   m->in_img = b.take<float>(maxIn > 0 ? MB * (int64_t)c.image_h * c.image_w * c.in_chans : 0);
   m->in_proc = b.take<float>(MB * std::max(1, c.proc_dim));
   m->in_y = b.take<float>(MB * c.num_classes);

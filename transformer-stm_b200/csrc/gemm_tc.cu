@@ -277,9 +277,3 @@ extern "C" CVT_API int cvt_debug_gemm(int a_mode, int b_mode, int M, int N, int 
   return CVT_OK;
 }
 
-namespace cvt {
-bool attention_tc_enabled(const Model*, int) { return false; }
-cudaError_t attention_forward_tc(Model*, int, int, cudaStream_t) { set_error("attention_tc: not built"); return cudaErrorNotSupported; }
-cudaError_t attention_backward_tc(Model*, int, int, const float*, float*, cudaStream_t) { set_error("attention_tc: not built"); return cudaErrorNotSupported; }
-
-}  // namespace cvt

@@ -61,6 +61,7 @@ struct Model {
   float *metrics = nullptr;               // device [2]: loss, mae
   // gradient scratch shared by the stages
   float *gX[2] = {nullptr, nullptr};      // gradient w.r.t. a block output [B,Tc,D] (ping-pong across stages)
+  float* attn_dd = nullptr;               // tensor-core attention backward: rowsum(dO * O) [B*heads, Tc]
   float *gH = nullptr, *gC = nullptr, *gD = nullptr, *gE = nullptr, *gM = nullptr, *gQ = nullptr, *gQ2 = nullptr, *gS = nullptr;
   // staging for host-buffer entry points
   float *in_img = nullptr, *in_proc = nullptr, *in_y = nullptr, *out_pred = nullptr;
