@@ -39,8 +39,11 @@ __host__ __device__ inline long long cdivl(long long a, long long b) { return (a
 // r -> (r / period) * stride + r % period + off      (period == 0: identity)
 struct RowMap {
   int period, stride, off;
+  // 32-bit index arithmetic: token counts are far below 2^31 and a 64-bit division costs ~100 instructions on the device
   __host__ __device__ inline long long operator()(long long r) const {
-    return period ? (r / period) * (long long)stride + (r % period) + off : r;
+    if (!period) return r;
+    const int ri = (int)r, q = ri / period;
+    return (long long)q * stride + (ri - q * period) + off;
   }
 };
 inline RowMap rowmap_none() { return RowMap{0, 0, 0}; }

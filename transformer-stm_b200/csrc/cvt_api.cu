@@ -46,7 +46,14 @@ cudaError_t run_gemm(const Model* m, const GemmP& p, cudaStream_t s) {
   return launch_gemm_simt(p, s);
 }
 
+static thread_local bool g_tc = false;     // the model being run uses the tcgen05 contraction kernel (128-row tiles, 2 CTAs per SM)
 static int auto_splitk(int M, int N, int K, int batch) {
+  if (g_tc) {
+    const int tiles = cdiv(M, 128) * cdiv(N, 64) * batch;
+    const int sk = cdiv(kNumSMs * 2, tiles);
+    const int maxsk = std::max(1, K / 256);              // at least 8 k-tiles of 32 per CTA
+    return std::max(1, std::min(sk, maxsk));
+  }
   const int tiles = cdiv(M, 64) * cdiv(N, 64) * batch;
   int sk = cdiv(kNumSMs * 4, tiles);
   const int maxsk = std::max(1, K / 128);
@@ -656,6 +663,7 @@ static thread_local FwdInputs g_last_inputs{nullptr, nullptr};
 // gradient w.r.t. the output of block `stop_stage` when stop_stage > 0 ... (grad-cam tap)
 static cudaError_t backward_impl(Model* m, const float* img, const float* proc, int B, int training, int stop_after_stage, float** tap_grad) {
   cudaStream_t s = m->stream;
+  g_tc = m->cfg.precision != CVT_PREC_FP32;
   CVT_CUDA(cudaMemsetAsync(m->G, 0, (size_t)m->n_train * sizeof(float), s));
   int cur = (m->n_stages - 1) & 1;
   CVT_CUDA(head_backward(m, proc, B, m->gX[cur]));

@@ -18,23 +18,26 @@ using namespace fetch;
 using namespace tc;
 
 namespace {
-constexpr int TBM = 128, TBK = 32, A_TILE_BYTES = TBM * TBK * 4, NT = 256, STAGES = 3;
+constexpr int TBM = 128, TBK = 32, A_TILE_BYTES = TBM * TBK * 4, NT = 256;
 
 template <int BN> struct Cfg {
+  static constexpr int NS = BN == 64 ? 4 : 3;                       // pipeline slots: 96 KB either way -> 2 CTAs per SM
   static constexpr int B_TILE_BYTES = BN * TBK * 4;
-  static constexpr int SMEM = 1024 + STAGES * (A_TILE_BYTES + B_TILE_BYTES) + 16 * 8 + 16;
+  static constexpr int SMEM = 1024 + NS * (A_TILE_BYTES + B_TILE_BYTES) + 17 * 8 + 16;
 };
 
-// ---- epilogue of one accumulator row segment: 32 consecutive output columns held by one thread ------------------------------
-__device__ __forceinline__ void epilogue_row32(const GemmP& p, float v[32], float* Cp, float* aux, const float* bias, float alpha,
-                                               int m, int n0) {
-  if (p.epi & EPI_SCATTER) {
+// ---- epilogue of 4 consecutive output columns of one row (coalesced domain: a quarter-warp covers 128 contiguous bytes) ----------
+// E = the compile-time epilogue kind (GELU | RESID | GELU_BWD | SCATTER | ATOMIC); bias / alpha / dropout mask stay run-time
+template <uint32_t E>
+__device__ __forceinline__ void epilogue_f4(const GemmP& p, float4 acc, float* Cp, float* aux, const float* bias, float alpha, int m, int n0) {
+  float v[4] = {acc.x, acc.y, acc.z, acc.w};
+  if (E & EPI_SCATTER) {
     // C is the conv input gradient [B,hin,win,cin]; m = output pixel, n = (tap, c)
     const ConvGeom& g = p.cv;
     const int hw = g.ho * g.wo; const int b = m / hw; const int rr = m - b * hw; const int oi = rr / g.wo; const int oj = rr - oi * g.wo;
     float* img = Cp + (long long)b * g.bstride + g.boff;
 #pragma unroll
-    for (int j = 0; j < 32; ++j) {
+    for (int j = 0; j < 4; ++j) {
       const int n = n0 + j;
       const int tap = n / g.cin, c = n - tap * g.cin; const int kh = tap / g.k, kw = tap - kh * g.k;
       const int yy = g.s * oi + kh - g.pt, xx = g.s * oj + kw - g.pl;
@@ -45,66 +48,95 @@ __device__ __forceinline__ void epilogue_row32(const GemmP& p, float v[32], floa
   const long long crow = p.c_map(m);
   const long long idx0 = crow * p.ldc + n0;
   if (bias) {
-#pragma unroll
-    for (int j = 0; j < 32; j += 4) {
-      const float4 b4 = *reinterpret_cast<const float4*>(bias + n0 + j);
-      v[j] += b4.x; v[j + 1] += b4.y; v[j + 2] += b4.z; v[j + 3] += b4.w;
-    }
+    const float4 b4 = *reinterpret_cast<const float4*>(bias + n0);
+    v[0] += b4.x; v[1] += b4.y; v[2] += b4.z; v[3] += b4.w;
   }
-  if (alpha != 1.f) {
 #pragma unroll
-    for (int j = 0; j < 32; ++j) v[j] *= alpha;
+  for (int j = 0; j < 4; ++j) v[j] *= alpha;
+  if (E & EPI_GELU) {
+    if (aux) *reinterpret_cast<float4*>(aux + idx0) = make_float4(v[0], v[1], v[2], v[3]);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v[j] = gelu_erf(v[j]);
   }
-  if (p.epi & EPI_GELU) {
-    if (aux) {
-#pragma unroll
-      for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(aux + idx0 + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-    }
-#pragma unroll
-    for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
-  }
-  if (p.epi & EPI_RELU) {
-#pragma unroll
-    for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
-  }
-  if (p.epi & (EPI_GELU_BWD | EPI_RELU_BWD)) {
-#pragma unroll
-    for (int j = 0; j < 32; j += 4) {
-      const float4 a4 = *reinterpret_cast<const float4*>(aux + idx0 + j);
-      const float a[4] = {a4.x, a4.y, a4.z, a4.w};
-#pragma unroll
-      for (int t = 0; t < 4; ++t) v[j + t] = (p.epi & EPI_GELU_BWD) ? v[j + t] * gelu_erf_grad(a[t]) : (a[t] > 0.f ? v[j + t] : 0.f);
-    }
+  if (E & EPI_GELU_BWD) {
+    const float4 a4 = *reinterpret_cast<const float4*>(aux + idx0);
+    v[0] *= gelu_erf_grad(a4.x); v[1] *= gelu_erf_grad(a4.y); v[2] *= gelu_erf_grad(a4.z); v[3] *= gelu_erf_grad(a4.w);
   }
   if (p.epi & EPI_MASK) {
+    const uint32_t mk = *reinterpret_cast<const uint32_t*>(p.mask + idx0);
 #pragma unroll
-    for (int j = 0; j < 32; j += 16) {
-      const uint4 mk = *reinterpret_cast<const uint4*>(p.mask + idx0 + j);
-      const uint32_t w[4] = {mk.x, mk.y, mk.z, mk.w};
-#pragma unroll
-      for (int t = 0; t < 16; ++t) v[j + t] = ((w[t >> 2] >> ((t & 3) * 8)) & 0xFFu) ? v[j + t] * p.mask_scale : 0.f;
-    }
+    for (int j = 0; j < 4; ++j) v[j] = ((mk >> (8 * j)) & 0xFFu) ? v[j] * p.mask_scale : 0.f;
   }
-  if (p.epi & EPI_RESID) {
-    const float* rp = p.resid + crow * p.ldr + n0;
-#pragma unroll
-    for (int j = 0; j < 32; j += 4) {
-      const float4 r4 = *reinterpret_cast<const float4*>(rp + j);
-      v[j] += r4.x; v[j + 1] += r4.y; v[j + 2] += r4.z; v[j + 3] += r4.w;
-    }
+  if (E & EPI_RESID) {
+    const float4 r4 = *reinterpret_cast<const float4*>(p.resid + crow * p.ldr + n0);
+    v[0] += r4.x; v[1] += r4.y; v[2] += r4.z; v[3] += r4.w;
   }
-  if (p.epi & EPI_ATOMIC) {
+  if (E & EPI_ATOMIC) {
 #pragma unroll
-    for (int j = 0; j < 32; ++j) atomicAdd(Cp + idx0 + j, v[j]);
+    for (int j = 0; j < 4; ++j) atomicAdd(Cp + idx0 + j, v[j]);
   } else {
-#pragma unroll
-    for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(Cp + idx0 + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+    *reinterpret_cast<float4*>(Cp + idx0) = make_float4(v[0], v[1], v[2], v[3]);
   }
 }
 
-template <int AM, int BMODE, int BN>
+// ---- operand sources: where the 4 floats of one 16-byte shared-memory chunk come from ------------------------------------------
+// n = number of valid floats (0..4) at p; n == -1: the four floats are not contiguous in memory (im2col with cin % 4 != 0)
+struct Src { const float* p; int n; };
+
+template <int AM>
+__device__ __forceinline__ Src srcA_row(const GemmP& p, const float* A, int k, int kend, bool mvalid, long long tok, int cb, int ci_, int cj) {
+  if (!mvalid || k >= kend) return Src{A, 0};
+  if (AM == A_PLAIN) return Src{A + tok * p.lda + k, min(4, kend - k)};
+  const ConvGeom& g = p.cv;
+  if ((g.cin & 3) != 0) return Src{A, -1};
+  const int tap = k / g.cin, c = k - tap * g.cin;
+  const int kh = tap / g.k, kw = tap - kh * g.k;
+  const int yy = g.s * ci_ + kh - g.pt, xx = g.s * cj + kw - g.pl;
+  if (yy < 0 || yy >= g.hin || xx < 0 || xx >= g.win) return Src{A, 0};
+  return Src{A + (long long)cb * g.bstride + g.boff + ((long long)yy * g.win + xx) * g.cin + c, 4};
+}
+template <int AM>
+__device__ __forceinline__ Src srcA_col(const GemmP& p, const float* A, int k, int kend, int m0) {
+  if (k >= kend || m0 >= p.M) return Src{A, 0};
+  if (AM == A_TRANS) return Src{A + p.a_map(k) * p.lda + m0, min(4, p.M - m0)};
+  const ConvGeom& g = p.cv;
+  if ((g.cin & 3) != 0) return Src{A, -1};
+  const int hw = g.ho * g.wo;
+  const int b = k / hw, r = k - b * hw;
+  const int oi = r / g.wo, oj = r - oi * g.wo;
+  const int tap = m0 / g.cin, c = m0 - tap * g.cin;
+  const int kh = tap / g.k, kw = tap - kh * g.k;
+  const int yy = g.s * oi + kh - g.pt, xx = g.s * oj + kw - g.pl;
+  if (yy < 0 || yy >= g.hin || xx < 0 || xx >= g.win) return Src{A, 0};
+  return Src{A + (long long)b * g.bstride + g.boff + ((long long)yy * g.win + xx) * g.cin + c, 4};
+}
+__device__ __forceinline__ Src srcB_kn(const GemmP& p, const float* B, int k, int kend, int n0) {
+  if (k >= kend || n0 >= p.N) return Src{B, 0};
+  return Src{B + p.b_map(k) * p.ldb + n0, min(4, p.N - n0)};
+}
+__device__ __forceinline__ Src srcB_nk(const GemmP& p, const float* B, int n, int k, int kend) {
+  if (n >= p.N || k >= kend) return Src{B, 0};
+  return Src{B + (long long)n * p.ldb + k, min(4, kend - k)};
+}
+
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// 16-byte chunk: asynchronous copy when the source is a full aligned float4, else assembled through registers
+__device__ __forceinline__ void copy_chunk(uint8_t* dst, const Src& s) {
+  if (s.n == 4 && aligned16(s.p)) { cp_async16(smem_u32(dst), s.p); return; }
+  float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (s.n > 0) { v.x = s.p[0]; if (s.n > 1) v.y = s.p[1]; if (s.n > 2) v.z = s.p[2]; if (s.n > 3) v.w = s.p[3]; }
+  *reinterpret_cast<float4*>(dst) = v;
+}
+
+template <int AM, int BMODE, int BN, uint32_t E>
 __global__ void __launch_bounds__(NT, 2) gemm_tc_kernel(const __grid_constant__ GemmP p) {
   using C = Cfg<BN>;
+  constexpr int NS = C::NS;
   constexpr bool A_ROWFIXED = (AM == A_PLAIN || AM == A_CONV);     // K-contiguous A  -> K-major
   constexpr bool B_KMAJOR = (BMODE == B_NK);
   constexpr int NA_FRAGS = TBM * 8 / NT;       // 4
@@ -113,8 +145,8 @@ __global__ void __launch_bounds__(NT, 2) gemm_tc_kernel(const __grid_constant__ 
   const uint32_t raw = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
   uint8_t* sA = smem;
-  uint8_t* sB = sA + STAGES * A_TILE_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sB + STAGES * C::B_TILE_BYTES);      // [STAGES] stage-free, [STAGES] accumulator-ready
+  uint8_t* sB = sA + NS * A_TILE_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sB + NS * C::B_TILE_BYTES);      // [NS] stage-free, [1] accumulator-ready
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -135,18 +167,14 @@ __global__ void __launch_bounds__(NT, 2) gemm_tc_kernel(const __grid_constant__ 
 
   if (warp == 0) tmem_alloc(tmem_slot, BN);
   if (tid == 32) {
-    for (int i = 0; i <= STAGES; ++i) mbar_init(&bars[i], 1);
+    for (int i = 0; i <= NS; ++i) mbar_init(&bars[i], 1);
     mbar_fence_init();
   }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
 
   // ---- per-thread operand coordinates ----
   // A, K-major:  chunk = tid & 7 (16 B along K), rows (tid >> 3) + 32 i
   // A, MN-major: m4 = tid & 31 (float4 along M),  k rows (tid >> 5) + 8 i
-  long long a_tok[NA_FRAGS]; int a_cb[NA_FRAGS], a_cij[NA_FRAGS]; uint32_t a_valid = 0;
+  long long a_tok[NA_FRAGS]; int a_cb[NA_FRAGS], a_cij[NA_FRAGS]; uint32_t a_valid = 0, a_skip = 0;
   if (A_ROWFIXED) {
 #pragma unroll
     for (int i = 0; i < NA_FRAGS; ++i) {
@@ -154,58 +182,131 @@ __global__ void __launch_bounds__(NT, 2) gemm_tc_kernel(const __grid_constant__ 
       a_tok[i] = 0; a_cb[i] = 0; a_cij[i] = 0;
       if (m < p.M) {
         a_valid |= 1u << i;
-        if (AM == A_PLAIN) a_tok[i] = p.a_map(m);
-        else {
+        if (AM == A_PLAIN) {
+          a_tok[i] = p.a_map(m);
+          if (p.a_skip_period && ((int)a_tok[i] % p.a_skip_period) == 0) a_skip |= 1u << i;
+        } else {
           const int hw = p.cv.ho * p.cv.wo; const int b = m / hw; const int r = m - b * hw; const int oi = r / p.cv.wo;
           a_cb[i] = b; a_cij[i] = (oi << 16) | (r - oi * p.cv.wo);
         }
       }
     }
   }
-  Frag ra[NA_FRAGS], rb[NB_FRAGS];
-  auto load_tile = [&](int k0) {
+  auto a_off = [&](int i) -> uint32_t {
+    return A_ROWFIXED ? sw128_kmajor_off((tid >> 3) + 32 * i, tid & 7) : sw128_mnmajor_off((tid >> 5) + 8 * i, tid & 31, TBM / 32);
+  };
+  auto b_off = [&](int i) -> uint32_t {
+    const int idx = tid + NT * i;
+    return B_KMAJOR ? sw128_kmajor_off(idx >> 3, idx & 7) : sw128_mnmajor_off(idx / (BN / 4), idx % (BN / 4), BN / 32);
+  };
+  // im2col element gather for Conv2D inputs whose channel count is not a multiple of 4 (stage 1: cin = 1)
+  auto gather_conv = [&](int m, int k, bool k_is_pixel) -> float {
+    // forward (A_CONV): m = output pixel, k = (tap, c);  wgrad (A_CONVT): k = output pixel, m = (tap, c)
+    const ConvGeom& g = p.cv;
+    const int pix = k_is_pixel ? k : m, tc = k_is_pixel ? m : k;
+    const int hw = g.ho * g.wo; const int b = pix / hw, r = pix - b * hw; const int oi = r / g.wo, oj = r - oi * g.wo;
+    const int tap = tc / g.cin, c = tc - tap * g.cin; const int kh = tap / g.k, kw = tap - kh * g.k;
+    const int yy = g.s * oi + kh - g.pt, xx = g.s * oj + kw - g.pl;
+    if (yy < 0 || yy >= g.hin || xx < 0 || xx >= g.win) return 0.f;
+    return A[(long long)b * g.bstride + g.boff + ((long long)yy * g.win + xx) * g.cin + c];
+  };
+  auto issue_tile = [&](int slot, int k0) {
+    uint8_t* a = sA + slot * A_TILE_BYTES; uint8_t* b = sB + slot * C::B_TILE_BYTES;
 #pragma unroll
     for (int i = 0; i < NA_FRAGS; ++i) {
-      if (A_ROWFIXED)
-        ra[i] = fetchA_row<AM>(p, A, sc, sh, m_blk + (tid >> 3) + 32 * i, k0 + ((tid & 7) << 2), kend, (a_valid >> i) & 1, a_tok[i],
-                               a_cb[i], a_cij[i] >> 16, a_cij[i] & 0xFFFF);
-      else
-        ra[i] = fetchA_col<AM>(p, A, sc, sh, k0 + (tid >> 5) + 8 * i, kend, m_blk + ((tid & 31) << 2));
+      Src s;
+      if (A_ROWFIXED) {
+        const int m = m_blk + (tid >> 3) + 32 * i, k = k0 + ((tid & 7) << 2);
+        s = srcA_row<AM>(p, A, k, kend, (a_valid >> i) & 1, a_tok[i], a_cb[i], a_cij[i] >> 16, a_cij[i] & 0xFFFF);
+        if (AM == A_CONV && s.n < 0) {
+          float4 v;
+          v.x = (k < kend) ? gather_conv(m, k, false) : 0.f; v.y = (k + 1 < kend) ? gather_conv(m, k + 1, false) : 0.f;
+          v.z = (k + 2 < kend) ? gather_conv(m, k + 2, false) : 0.f; v.w = (k + 3 < kend) ? gather_conv(m, k + 3, false) : 0.f;
+          *reinterpret_cast<float4*>(a + a_off(i)) = v;
+          continue;
+        }
+      } else {
+        const int k = k0 + (tid >> 5) + 8 * i, m0 = m_blk + ((tid & 31) << 2);
+        s = srcA_col<AM>(p, A, k, kend, m0);
+        if (AM == A_CONVT && s.n < 0) {
+          float4 v;
+          v.x = (m0 < p.M) ? gather_conv(m0, k, true) : 0.f; v.y = (m0 + 1 < p.M) ? gather_conv(m0 + 1, k, true) : 0.f;
+          v.z = (m0 + 2 < p.M) ? gather_conv(m0 + 2, k, true) : 0.f; v.w = (m0 + 3 < p.M) ? gather_conv(m0 + 3, k, true) : 0.f;
+          *reinterpret_cast<float4*>(a + a_off(i)) = v;
+          continue;
+        }
+      }
+      copy_chunk(a + a_off(i), s);
     }
 #pragma unroll
     for (int i = 0; i < NB_FRAGS; ++i) {
       const int idx = tid + NT * i;
-      if (B_KMAJOR) rb[i] = fetchB_nk(p, B, n_blk + (idx >> 3), k0 + ((idx & 7) << 2), kend);
-      else rb[i] = fetchB_kn(p, B, k0 + idx / (BN / 4), kend, n_blk + ((idx % (BN / 4)) << 2));
+      const Src s = B_KMAJOR ? srcB_nk(p, B, n_blk + (idx >> 3), k0 + ((idx & 7) << 2), kend)
+                             : srcB_kn(p, B, k0 + idx / (BN / 4), kend, n_blk + ((idx % (BN / 4)) << 2));
+      copy_chunk(b + b_off(i), s);
     }
   };
-  auto st4 = [](uint8_t* base, uint32_t off, const Frag& f) {
-    *reinterpret_cast<float4*>(base + off) = make_float4(to_tf32(f.v[0]), to_tf32(f.v[1]), to_tf32(f.v[2]), to_tf32(f.v[3]));
-  };
-  auto store_tile = [&](int s) {
-    uint8_t* a = sA + s * A_TILE_BYTES; uint8_t* b = sB + s * C::B_TILE_BYTES;
+  // second pass over the chunks this thread copied: optional per-feature affine on A (BatchNorm applied on load), then round to TF32
+  auto convert_tile = [&](int slot, int k0) {
+    uint8_t* a = sA + slot * A_TILE_BYTES; uint8_t* b = sB + slot * C::B_TILE_BYTES;
 #pragma unroll
     for (int i = 0; i < NA_FRAGS; ++i) {
-      if (A_ROWFIXED) st4(a, sw128_kmajor_off((tid >> 3) + 32 * i, tid & 7), ra[i]);
-      else st4(a, sw128_mnmajor_off((tid >> 5) + 8 * i, tid & 31, TBM / 32), ra[i]);
+      float4* q = reinterpret_cast<float4*>(a + a_off(i));
+      float4 v = *q;
+      if ((AM == A_PLAIN || AM == A_TRANS) && sc != nullptr) {
+        if (A_ROWFIXED) {
+          const int k = k0 + ((tid & 7) << 2);
+          if (((a_valid >> i) & 1) && !((a_skip >> i) & 1) && k < kend) {
+            // K is a multiple of 4 whenever the affine is used (feature counts are multiples of 64)
+            const float4 s4 = *reinterpret_cast<const float4*>(sc + k), h4 = *reinterpret_cast<const float4*>(sh + k);
+            v.x = fmaf(v.x, s4.x, h4.x); v.y = fmaf(v.y, s4.y, h4.y); v.z = fmaf(v.z, s4.z, h4.z); v.w = fmaf(v.w, s4.w, h4.w);
+          }
+        } else {
+          const int k = k0 + (tid >> 5) + 8 * i, m0 = m_blk + ((tid & 31) << 2);
+          if (k < kend && m0 < p.M) {
+            const int tok = (int)p.a_map(k);
+            if (!(p.a_skip_period && (tok % p.a_skip_period) == 0)) {
+              const float4 s4 = *reinterpret_cast<const float4*>(sc + m0), h4 = *reinterpret_cast<const float4*>(sh + m0);
+              v.x = fmaf(v.x, s4.x, h4.x); v.y = fmaf(v.y, s4.y, h4.y); v.z = fmaf(v.z, s4.z, h4.z); v.w = fmaf(v.w, s4.w, h4.w);
+            }
+          }
+        }
+      }
+      *q = make_float4(to_tf32(v.x), to_tf32(v.y), to_tf32(v.z), to_tf32(v.w));
     }
 #pragma unroll
     for (int i = 0; i < NB_FRAGS; ++i) {
-      const int idx = tid + NT * i;
-      if (B_KMAJOR) st4(b, sw128_kmajor_off(idx >> 3, idx & 7), rb[i]);
-      else st4(b, sw128_mnmajor_off(idx / (BN / 4), idx % (BN / 4), BN / 32), rb[i]);
+      float4* q = reinterpret_cast<float4*>(b + b_off(i));
+      const float4 v = *q;
+      *q = make_float4(to_tf32(v.x), to_tf32(v.y), to_tf32(v.z), to_tf32(v.w));
     }
   };
 
+  // ---- pipeline: NS-1 k-tiles of cp.async in flight ahead of the tensor core ----
+#pragma unroll 1
+  for (int t = 0; t < NS - 1; ++t) {
+    if (t < nk) issue_tile(t, kbeg + t * TBK);
+    cp_async_commit();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
   constexpr uint32_t idesc = make_idesc(kFmtTF32, TBM, BN, A_ROWFIXED ? 0u : 1u, B_KMAJOR ? 0u : 1u);
-  load_tile(kbeg);
   for (int kt = 0; kt < nk; ++kt) {
-    const int s = kt % STAGES, use = kt / STAGES;
-    if (use > 0) mbar_wait(&bars[s], (use - 1) & 1);               // the MMAs that read this slot have completed
-    store_tile(s);
+    const int s = kt % NS;
+    {  // refill the slot tile kt-1 used with tile kt+NS-1 once its MMAs have completed
+      const int nt = kt + NS - 1;
+      if (nt < nk) {
+        if (kt > 0) mbar_wait(&bars[(kt - 1) % NS], ((kt - 1) / NS) & 1);
+        issue_tile(nt % NS, kbeg + nt * TBK);
+      }
+      cp_async_commit();
+    }
+    cp_async_wait<NS - 1>();                                          // this thread's copies of tile kt have landed
+    convert_tile(s, kbeg + kt * TBK);
     fence_proxy_async_smem();
     __syncthreads();
-    if (kt + 1 < nk) load_tile(kbeg + (kt + 1) * TBK);              // global loads in flight while the tensor core works
     if (tid == 0) {
       tc_fence_after();
       const uint32_t a0 = smem_u32(sA + s * A_TILE_BYTES), b0 = smem_u32(sB + s * C::B_TILE_BYTES);
@@ -218,49 +319,63 @@ __global__ void __launch_bounds__(NT, 2) gemm_tc_kernel(const __grid_constant__ 
         mma_tf32_ss(tmem_base, ad, bd, idesc, (kt > 0 || j > 0) ? 1u : 0u);
       }
       mma_commit(&bars[s]);
-      if (kt == nk - 1) mma_commit(&bars[STAGES]);
+      if (kt == nk - 1) mma_commit(&bars[NS]);
     }
   }
-  mbar_wait(&bars[STAGES], 0);
+  mbar_wait(&bars[NS], 0);
   tc_fence_after();
 
-  // ---- epilogue: warp w reads TMEM lane quadrant w & 3, column half w >> 2; one accumulator row per thread ----
+  // ---- epilogue: warp w reads TMEM lane quadrant w & 3, column half w >> 2 (one accumulator row per thread), transposes each
+  //      32x32 block through its own staging tile (the pipeline slots are free now) and finishes in the coalesced domain ----
   float* Cp = p.C + zb * p.c_bs0 + zh * p.c_bs1;
   float* aux = p.aux ? p.aux + zb * p.c_bs0 + zh * p.c_bs1 : nullptr;
   const float* bias = (p.epi & EPI_BIAS) ? p.bias + z * p.bias_bs : nullptr;
   const float alpha = ((p.epi & EPI_ALPHA0) && z == 0) ? p.alpha0 : p.alpha;
   const int quad = warp & 3, half = warp >> 2;
   const uint32_t trow = tmem_base + ((uint32_t)(quad * 32) << 16);
-  const int m = m_blk + quad * 32 + lane;
+  float* stg = reinterpret_cast<float*>(smem) + warp * (32 * 36);    // 32 rows x 36 floats (16-byte aligned rows, conflict-free both ways)
+  const int er = lane >> 3, ec = (lane & 7) << 2;
 #pragma unroll 1
   for (int c0 = half * (BN / 2); c0 < (half + 1) * (BN / 2); c0 += 32) {
     float v[32];
-    tmem_ld32(trow + c0, v);                                         // warp-collective: issued by every lane, rows beyond M included
-    if (m < p.M) epilogue_row32(p, v, Cp, aux, bias, alpha, m, n_blk + c0);
+    tmem_ld32(trow + c0, v);
+#pragma unroll
+    for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(stg + lane * 36 + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+    __syncwarp();
+#pragma unroll 2
+    for (int i = 0; i < 8; ++i) {
+      const int rr = er + 4 * i;
+      const int m = m_blk + quad * 32 + rr;
+      const float4 acc = *reinterpret_cast<const float4*>(stg + rr * 36 + ec);
+      if (m < p.M) epilogue_f4<E>(p, acc, Cp, aux, bias, alpha, m, n_blk + c0 + ec);
+    }
+    __syncwarp();
   }
   tc_fence_before();
   __syncthreads();
   if (warp == 0) tmem_dealloc(tmem_base, BN);
 }
 
-template <int AM, int BMODE, int BN>
+template <int AM, int BMODE, int BN, uint32_t E>
 cudaError_t launch_cfg(const GemmP& p, cudaStream_t s) {
   static bool configured = false;
   if (!configured) {
-    CVT_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<AM, BMODE, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM));
+    CVT_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<AM, BMODE, BN, E>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM));
     configured = true;
   }
   dim3 grid(cdiv(p.N, BN), cdiv(p.M, TBM), p.batch * p.splitk);
-  gemm_tc_kernel<AM, BMODE, BN><<<grid, NT, Cfg<BN>::SMEM, s>>>(p);
+  gemm_tc_kernel<AM, BMODE, BN, E><<<grid, NT, Cfg<BN>::SMEM, s>>>(p);
   CVT_LAUNCH_CHECK();
   return cudaSuccess;
 }
 
-template <int AM, int BMODE>
+template <int AM, int BMODE, uint32_t E>
 cudaError_t launch_bn(const GemmP& p, int bn, cudaStream_t s) {
-  if (bn == 128) return launch_cfg<AM, BMODE, 128>(p, s);
-  return launch_cfg<AM, BMODE, 64>(p, s);
+  if (bn == 128) return launch_cfg<AM, BMODE, 128, E>(p, s);
+  return launch_cfg<AM, BMODE, 64, E>(p, s);
 }
+
+constexpr uint32_t kEpiKinds = EPI_GELU | EPI_RESID | EPI_GELU_BWD | EPI_SCATTER | EPI_ATOMIC;
 
 int pick_bn(const GemmP& p) {
   if (p.N % 128 != 0) return 64;
@@ -271,25 +386,40 @@ int pick_bn(const GemmP& p) {
 
 bool gemm_tc_supports(const GemmP& p) {
   if (p.N % 64 != 0 || p.M < 1 || p.K < 1) return false;
+  if (p.epi & (EPI_RELU | EPI_RELU_BWD)) return false;              // the tiny head layers stay on the FFMA kernel
   if (p.splitk > 1 && !(p.epi & (EPI_ATOMIC | EPI_SCATTER))) return false;
   return true;
 }
 
 cudaError_t launch_gemm_tc(const GemmP& p, cudaStream_t s) {
-  if (!gemm_tc_supports(p)) { set_error("gemm_tc: unsupported shape"); return cudaErrorNotSupported; }
+  if (!gemm_tc_supports(p)) { set_error("gemm_tc: unsupported shape / epilogue"); return cudaErrorNotSupported; }
   const int bn = pick_bn(p);
-  switch (p.a_mode * 2 + p.b_mode) {
-    case A_PLAIN * 2 + B_KN: return launch_bn<A_PLAIN, B_KN>(p, bn, s);
-    case A_PLAIN * 2 + B_NK: return launch_bn<A_PLAIN, B_NK>(p, bn, s);
-    case A_TRANS * 2 + B_KN: return launch_bn<A_TRANS, B_KN>(p, bn, s);
-    case A_TRANS * 2 + B_NK: return launch_bn<A_TRANS, B_NK>(p, bn, s);
-    case A_CONV * 2 + B_KN: return launch_bn<A_CONV, B_KN>(p, bn, s);
-    case A_CONV * 2 + B_NK: return launch_bn<A_CONV, B_NK>(p, bn, s);
-    case A_CONVT * 2 + B_KN: return launch_bn<A_CONVT, B_KN>(p, bn, s);
-    case A_CONVT * 2 + B_NK: return launch_bn<A_CONVT, B_NK>(p, bn, s);
+  const uint32_t kind = p.epi & kEpiKinds;
+  const int modes = p.a_mode * 2 + p.b_mode;
+  // the instantiations the CvT block uses (cvt_api.cu); anything else is refused loudly rather than silently slow
+  if (modes == A_PLAIN * 2 + B_KN) {            // Dense / EinsumDense forward
+    if (kind == 0) return launch_bn<A_PLAIN, B_KN, 0>(p, bn, s);
+    if (kind == EPI_RESID) return launch_bn<A_PLAIN, B_KN, EPI_RESID>(p, bn, s);
+    if (kind == EPI_GELU) return launch_bn<A_PLAIN, B_KN, EPI_GELU>(p, bn, s);
+    if (kind == EPI_ATOMIC) return launch_bn<A_PLAIN, B_KN, EPI_ATOMIC>(p, bn, s);
+  } else if (modes == A_PLAIN * 2 + B_NK) {     // dgrad
+    if (kind == 0) return launch_bn<A_PLAIN, B_NK, 0>(p, bn, s);
+    if (kind == EPI_GELU_BWD) return launch_bn<A_PLAIN, B_NK, EPI_GELU_BWD>(p, bn, s);
+    if (kind == EPI_SCATTER) return launch_bn<A_PLAIN, B_NK, EPI_SCATTER>(p, bn, s);
+    if (kind == EPI_ATOMIC) return launch_bn<A_PLAIN, B_NK, EPI_ATOMIC>(p, bn, s);
+  } else if (modes == A_TRANS * 2 + B_KN) {     // wgrad
+    if (kind == EPI_ATOMIC) return launch_bn<A_TRANS, B_KN, EPI_ATOMIC>(p, bn, s);
+    if (kind == 0) return launch_bn<A_TRANS, B_KN, 0>(p, bn, s);
+  } else if (modes == A_TRANS * 2 + B_NK) {
+    if (kind == 0) return launch_bn<A_TRANS, B_NK, 0>(p, bn, s);
+    if (kind == EPI_ATOMIC) return launch_bn<A_TRANS, B_NK, EPI_ATOMIC>(p, bn, s);
+  } else if (modes == A_CONV * 2 + B_KN) {      // Conv2D forward (implicit GEMM)
+    if (kind == 0) return launch_bn<A_CONV, B_KN, 0>(p, bn, s);
+  } else if (modes == A_CONVT * 2 + B_KN) {     // Conv2D wgrad
+    if (kind == EPI_ATOMIC) return launch_bn<A_CONVT, B_KN, EPI_ATOMIC>(p, bn, s);
   }
-  set_error("gemm_tc: bad operand modes");
-  return cudaErrorInvalidValue;
+  set_error("gemm_tc: no instantiation for a_mode " + std::to_string(p.a_mode) + " b_mode " + std::to_string(p.b_mode) + " epilogue " + std::to_string(p.epi));
+  return cudaErrorNotSupported;
 }
 
 }  // namespace cvt
