@@ -142,6 +142,7 @@ static void build_params(Model* m) {
 }
 
 // ---- workspace ---------------------------------------------------------------------------------------------------
+constexpr int kStatParts = 2 * kNumSMs;      // per-CTA partial slices of the BN statistics (dwproj.cu)
 struct Bump {
   char* base = nullptr; int64_t off = 0;
   template <typename T> T* take(int64_t count) {
@@ -171,8 +172,8 @@ static void carve(Model* m, Bump& b) {
     s.attn_o = b.take<float>(RD); s.a1 = b.take<float>(RD); s.x1 = b.take<float>(RD); s.y = b.take<float>(RD);
     s.hpre = b.take<float>(RH); s.hact = b.take<float>(RH); s.x2 = b.take<float>(RD);
     s.lna_mean = b.take<float>(R); s.lna_rstd = b.take<float>(R); s.lnb_mean = b.take<float>(R); s.lnb_rstd = b.take<float>(R);
-    s.bn_stats = b.take<float>(6 * g.D); s.bn_scale = b.take<float>(3 * g.D); s.bn_shift = b.take<float>(3 * g.D);
-    s.bn_mean = b.take<float>(3 * g.D); s.bn_rstd = b.take<float>(3 * g.D);
+    s.bn_stats = b.take<float>((int64_t)kStatParts * 6 * g.D); s.bn_scale = b.take<float>(3 * g.D); s.bn_shift = b.take<float>(3 * g.D);
+    s.bn_mean = b.take<float>(3 * g.D); s.bn_rstd = b.take<float>(3 * g.D); s.bn_coef = b.take<float>(9 * g.D);
     s.scores = need_scores ? b.take<float>(S) : nullptr;
     s.lse = b.take<float>(MB * g.heads * (int64_t)g.Tc);
     s.mask_proj = b.take<uint8_t>(RD); s.mask1 = b.take<uint8_t>(RH); s.mask2 = b.take<uint8_t>(RD);
@@ -193,6 +194,7 @@ static void carve(Model* m, Bump& b) {
   m->gM = b.take<float>(maxRD); m->gQ = b.take<float>(3 * maxRD); m->gQ2 = b.take<float>(3 * maxRD);
   m->gS = need_scores ? b.take<float>(maxS) : nullptr;
   m->attn_dd = b.take<float>(maxL);
+  { int64_t maxD = 0; for (int i = 0; i < m->n_stages; ++i) maxD = std::max<int64_t>(maxD, m->geo[i].D); m->dw_part = b.take<float>((int64_t)kNumSMs * 27 * maxD); }
   m->in_img = b.take<float>(maxIn > 0 ? MB * (int64_t)c.image_h * c.image_w * c.in_chans : 0);
   m->in_proc = b.take<float>(MB * std::max(1, c.proc_dim));
   m->in_y = b.take<float>(MB * c.num_classes);
@@ -413,10 +415,14 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
     dp.method[1] = mz; dp.method[2] = mz;
     dp.B = B; dp.H = g.H; dp.W = g.W; dp.D = D; dp.Tc = g.Tc; dp.has_cls = g.has_cls;
     dp.stats = (bn && training) ? a.bn_stats : nullptr;
-    if (dp.stats) CVT_CUDA(cudaMemsetAsync(a.bn_stats, 0, 6 * D * sizeof(float), s));
-    CVT_CUDA(launch_dwproj_fwd(dp, s));
+    const bool fast = g.D <= 256 && (g.D & 3) == 0;
+    if (fast) { dp.nparts = kStatParts; CVT_CUDA(launch_dwproj_fwd2(dp, s)); }
+    else {
+      if (dp.stats) CVT_CUDA(cudaMemsetAsync(a.bn_stats, 0, 6 * D * sizeof(float), s));
+      CVT_CUDA(launch_dwproj_fwd(dp, s));
+    }
     if (bn) {
-      BnFinalizeP f; f.stats = a.bn_stats; f.count = (long long)B * g.T; f.gamma = P + w.bn_g; f.beta = P + w.bn_b;
+      BnFinalizeP f; f.stats = a.bn_stats; f.nparts = fast ? kStatParts : 1; f.count = (long long)B * g.T; f.gamma = P + w.bn_g; f.beta = P + w.bn_b;
       f.moving_mean = m->St + w.bn_mm; f.moving_var = m->St + w.bn_mv; f.training = training; f.update_moving = training;
       f.eps = c.bn_eps; f.momentum = c.bn_momentum; f.scale = a.bn_scale; f.shift = a.bn_shift; f.save_mean = a.bn_mean; f.save_rstd = a.bn_rstd; f.D = D;
       CVT_CUDA(launch_bn_finalize(f, s));
@@ -619,17 +625,27 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
   // ---- Projection backward (BatchNorm + depthwise conv / avg pool / identity) ----
   {
     const bool bn = g.method == CVT_PROJ_DW_BN;
+    const bool fast = g.D <= 256 && (g.D & 3) == 0;
     if (bn) {
       if (training)
         CVT_CUDA(launch_bn_bwd_reduce(m->gQ, a.conv, RD, a.bn_mean, a.bn_rstd, G + w.bn_g, G + w.bn_b, B, g.T, g.Tc, g.has_cls, D, s));
-      CVT_CUDA(launch_bn_bwd_apply(m->gQ, a.conv, RD, a.bn_mean, a.bn_rstd, P + w.bn_g, a.bn_scale, G + w.bn_g, G + w.bn_b, training,
-                                   B, g.T, g.Tc, g.has_cls, D, s));
+      if (fast)
+        CVT_CUDA(launch_bn_bwd_coef(P + w.bn_g, a.bn_mean, a.bn_rstd, a.bn_scale, G + w.bn_g, G + w.bn_b, (long long)B * g.T, training, D, a.bn_coef, s));
+      else
+        CVT_CUDA(launch_bn_bwd_apply(m->gQ, a.conv, RD, a.bn_mean, a.bn_rstd, P + w.bn_g, a.bn_scale, G + w.bn_g, G + w.bn_b, training,
+                                     B, g.T, g.Tc, g.has_cls, D, s));
     }
     DwProjBwdP dp; dp.dconv = m->gQ; dp.bs = RD; dp.xn = a.xn; dp.w = bn ? P + w.dw : nullptr;
     const int mz = bn ? 0 : (g.method == CVT_PROJ_AVG ? 1 : 2);
     dp.method[0] = (g.method == CVT_PROJ_AVG) ? 2 : mz; dp.method[1] = mz; dp.method[2] = mz;
     dp.B = B; dp.H = g.H; dp.W = g.W; dp.D = D; dp.Tc = g.Tc; dp.has_cls = g.has_cls; dp.dxn = m->gE; dp.ddw = bn ? G + w.dw : nullptr;
-    CVT_CUDA(launch_dwproj_bwd(dp, s));
+    if (fast) {
+      if (bn) { dp.conv = a.conv; dp.coef = a.bn_coef; }
+      dp.ddw_part = m->dw_part;
+      CVT_CUDA(launch_dwproj_bwd2(dp, s));
+    } else {
+      CVT_CUDA(launch_dwproj_bwd(dp, s));
+    }
   }
   // first use of norm1 (:272): dX0 = dX1 + LN'(dXn)   (in place on gD)
   CVT_CUDA(launch_ln_bwd(m->gE, D, a.x0, rowmap_none(), D, a.lna_mean, a.lna_rstd, P + w.ln_g, m->gD, m->gD, rowmap_none(), D,

@@ -176,14 +176,27 @@ __global__ void dwproj_fwd_kernel(const __grid_constant__ DwProjP p) {
   }
 }
 
-__global__ void bn_finalize_kernel(const __grid_constant__ BnFinalizeP p) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;      // (z, c)
-  if (i >= 3 * p.D) return;
+// block = (32 channels, 8 partial lanes): the per-CTA partial slices of the statistics are summed 8-way in parallel
+__global__ void __launch_bounds__(256) bn_finalize_kernel(const __grid_constant__ BnFinalizeP p) {
+  __shared__ double red[2][8][33];
+  const int i = blockIdx.x * 32 + threadIdx.x;      // (z, c)
+  const bool ok = i < 3 * p.D;
+  double s1 = 0.0, s2 = 0.0;
+  if (ok && p.training) {
+    for (int k = threadIdx.y; k < p.nparts; k += 8) {
+      s1 += (double)p.stats[(long long)k * 6 * p.D + i]; s2 += (double)p.stats[(long long)k * 6 * p.D + 3 * p.D + i];
+    }
+  }
+  red[0][threadIdx.y][threadIdx.x] = s1; red[1][threadIdx.y][threadIdx.x] = s2;
+  __syncthreads();
+  if (threadIdx.y != 0 || !ok) return;
   float mu, var;
   if (p.training) {
+    s1 = 0.0; s2 = 0.0;
+    for (int k = 0; k < 8; ++k) { s1 += red[0][k][threadIdx.x]; s2 += red[1][k][threadIdx.x]; }
     const double n = (double)p.count;
-    const double m = (double)p.stats[i] / n;
-    double v = (double)p.stats[3 * p.D + i] / n - m * m;
+    const double m = s1 / n;
+    double v = s2 / n - m * m;
     if (v < 0.0) v = 0.0;
     mu = (float)m; var = (float)v;
     if (p.update_moving) {
@@ -494,6 +507,10 @@ cudaError_t launch_ln_fwd(const float* x, RowMap in_map, long long ldx, const fl
                           float* y, long long ldy, float* mean, float* rstd, int rows, int D, cudaStream_t s) {
   if (rows <= 0) return cudaSuccess;
   if (D % 32 != 0 || D > 32 * LN_MAXV) { set_error("layer norm: D must be a multiple of 32 and <= 512"); return cudaErrorInvalidValue; }
+  {
+    const cudaError_t e = launch_ln_fwd_v4(x, in_map, ldx, gamma, beta, eps, y, ldy, mean, rstd, rows, D, s);
+    if (e != cudaErrorNotSupported) return e;
+  }
   ln_fwd_kernel<<<ew_blocks(rows, 8), 256, 0, s>>>(x, in_map, ldx, gamma, beta, eps, y, ldy, mean, rstd, rows, D);
   CVT_LAUNCH_CHECK();
   return cudaSuccess;
@@ -504,6 +521,10 @@ cudaError_t launch_ln_bwd(const float* dy, long long lddy, const float* x, RowMa
                           float* dgamma, float* dbeta, int rows, int D, cudaStream_t s) {
   if (rows <= 0) return cudaSuccess;
   if (D % 32 != 0 || D > 32 * LN_MAXV) { set_error("layer norm: D must be a multiple of 32 and <= 512"); return cudaErrorInvalidValue; }
+  {
+    const cudaError_t e = launch_ln_bwd_v4(dy, lddy, x, in_map, ldx, mean, rstd, gamma, dres, dx, out_map, ldo, dgamma, dbeta, rows, D, s);
+    if (e != cudaErrorNotSupported) return e;
+  }
   int blocks = cdiv(rows, 8);
   if (blocks > kNumSMs * 2) blocks = kNumSMs * 2;
   ln_bwd_kernel<<<blocks, 256, 2 * D * sizeof(float), s>>>(dy, lddy, x, in_map, ldx, mean, rstd, gamma, dres, dx, out_map, ldo,
@@ -523,7 +544,7 @@ cudaError_t launch_dwproj_fwd(const DwProjP& p, cudaStream_t s) {
 }
 
 cudaError_t launch_bn_finalize(const BnFinalizeP& p, cudaStream_t s) {
-  bn_finalize_kernel<<<cdiv(3 * p.D, 128), 128, 0, s>>>(p);
+  bn_finalize_kernel<<<cdiv(3 * p.D, 32), dim3(32, 8), 0, s>>>(p);
   CVT_LAUNCH_CHECK();
   return cudaSuccess;
 }

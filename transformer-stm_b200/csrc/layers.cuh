@@ -14,6 +14,13 @@ cudaError_t launch_ln_bwd(const float* dy, long long lddy, const float* x, RowMa
                           const float* dres, float* dx, RowMap out_map, long long ldo,
                           float* dgamma, float* dbeta, int rows, int D, cudaStream_t s);
 
+// vectorised instantiations (ln.cu); cudaErrorNotSupported -> caller uses the generic kernel
+cudaError_t launch_ln_fwd_v4(const float* x, RowMap in_map, long long ldx, const float* gamma, const float* beta, float eps,
+                             float* y, long long ldy, float* mean, float* rstd, int rows, int D, cudaStream_t s);
+cudaError_t launch_ln_bwd_v4(const float* dy, long long lddy, const float* x, RowMap in_map, long long ldx, const float* mean,
+                             const float* rstd, const float* gamma, const float* dres, float* dx, RowMap out_map, long long ldo,
+                             float* dgamma, float* dbeta, int rows, int D, cudaStream_t s);
+
 // Projection.call for q, k, v in one pass over the normalised map — models/CvT(Par).py:102-112,157-170.
 //   method[z]: 0 depthwise 3x3 (SAME, no bias), 1 3x3 average pool (SAME, valid-count divisor), 2 identity
 //   xn [B,Tc,D] (cls row first when has_cls); out [3][B,Tc,D]; cls rows are copied through.
@@ -21,13 +28,14 @@ cudaError_t launch_ln_bwd(const float* dy, long long lddy, const float* x, RowMa
 struct DwProjP {
   const float* xn; float* out; long long out_bs; const float* w; int method[3];
   int B, H, W, D, Tc, has_cls; float* stats;
+  int nparts = 1;      // dwproj.cu: stats is [nparts][6][D] per-CTA partials (bn_finalize sums them); generic kernel: 1 (atomics)
 };
 cudaError_t launch_dwproj_fwd(const DwProjP& p, cudaStream_t s);
 
 // BatchNormalization bookkeeping for the three branches: batch (training) or moving (inference) statistics ->
 // per-channel scale/shift applied when the q/k/v GEMM loads its A operand; moving-stat update (momentum, Bessel).
 struct BnFinalizeP {
-  const float* stats; long long count; const float* gamma; const float* beta; float* moving_mean; float* moving_var;
+  const float* stats; int nparts = 1; long long count; const float* gamma; const float* beta; float* moving_mean; float* moving_var;
   int training; int update_moving; float eps, momentum; float* scale; float* shift; float* save_mean; float* save_rstd; int D;
 };
 cudaError_t launch_bn_finalize(const BnFinalizeP& p, cudaStream_t s);
@@ -44,8 +52,16 @@ cudaError_t launch_bn_bwd_apply(float* dy, const float* conv, long long bs, cons
 struct DwProjBwdP {
   const float* dconv; long long bs; const float* xn; const float* w; int method[3];
   int B, H, W, D, Tc, has_cls; float* dxn; float* ddw;
+  float* ddw_part = nullptr;                                  // dwproj.cu: scratch [148][27][D] for the per-CTA weight-gradient partials
+  const float* conv = nullptr; const float* coef = nullptr;   // register-window kernel only: BN backward applied on load (dwproj.cu)
 };
 cudaError_t launch_dwproj_bwd(const DwProjBwdP& p, cudaStream_t s);
+// register sliding-window versions (dwproj.cu); cudaErrorNotSupported -> caller uses the generic kernels above
+cudaError_t launch_dwproj_fwd2(const DwProjP& p, cudaStream_t s);
+cudaError_t launch_dwproj_bwd2(const DwProjBwdP& p, cudaStream_t s);
+// coef [3][3][D] = (A, E, F) with dconv = A dn + E conv + F  (BatchNorm backward as an affine map, training or moving statistics)
+cudaError_t launch_bn_bwd_coef(const float* gamma, const float* mean, const float* rstd, const float* scale, const float* dgamma,
+                               const float* dbeta, long long count, int training, int D, float* coef, cudaStream_t s);
 
 // softmax over the last axis, in place (fp32 attention path) and its backward dS = P*(dP - sum(dP*P)), in place on dP
 cudaError_t launch_softmax_rows(float* S, long long rows, int cols, cudaStream_t s);

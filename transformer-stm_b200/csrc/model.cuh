@@ -36,7 +36,7 @@ struct StageGeo {
 struct StageBuf {
   float *x0, *xn, *conv, *qkv1, *qkv2, *attn_o, *a1, *x1, *y, *hpre, *hact, *x2;
   float *lna_mean, *lna_rstd, *lnb_mean, *lnb_rstd;
-  float *bn_stats, *bn_scale, *bn_shift, *bn_mean, *bn_rstd;
+  float *bn_stats, *bn_scale, *bn_shift, *bn_mean, *bn_rstd, *bn_coef;
   float *scores;                         // fp32 attention path: P [B*heads, Tc, Tc]
   float *lse;                            // tensor-core attention path: log-sum-exp [B*heads, Tc]
   uint8_t *mask_proj, *mask1, *mask2;
@@ -61,6 +61,7 @@ struct Model {
   float *metrics = nullptr;               // device [2]: loss, mae
   // gradient scratch shared by the stages
   float *gX[2] = {nullptr, nullptr};      // gradient w.r.t. a block output [B,Tc,D] (ping-pong across stages)
+  float* dw_part = nullptr;               // per-CTA partials of the depthwise-weight gradient (dwproj.cu)
   float* attn_dd = nullptr;               // tensor-core attention backward: rowsum(dO * O) [B*heads, Tc]
   float *gH = nullptr, *gC = nullptr, *gD = nullptr, *gE = nullptr, *gM = nullptr, *gQ = nullptr, *gQ2 = nullptr, *gS = nullptr;
   // staging for host-buffer entry points
