@@ -52,3 +52,21 @@ def test_tc_gemm_splitk_atomic(a_mode, b_mode):
     ref = tf32(A).astype(np.float64) @ tf32(B).astype(np.float64)
     got = run(a_mode, b_mode, M, N, K, 8, 1, Ah, Bh)
     assert np.abs(got - ref).max() < 2e-4 * np.sqrt(K)
+
+
+def tf32_trunc(x):
+    """what the tensor core does to raw fp32 bits under kind::tf32: the low 13 mantissa bits are ignored"""
+    return (x.astype(np.float32).view(np.uint32) & np.uint32(0xFFFFE000)).view(np.float32)
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 64, 32), (128, 64, 64), (256, 128, 96), (300, 256, 64), (1000, 192, 256), (64, 1024, 128),
+                                   (4160, 256, 256), (65536, 64, 64), (20000, 256, 64), (16384, 128, 512), (4160, 256, 1024)])
+def test_tma_gemm_matches_truncated_tf32(M, N, K):
+    """persistent TMA-fed kernel (gemm_tma.cu): operands reach the tensor core unrounded, i.e. truncated to TF32"""
+    rng = np.random.default_rng(M + N * 3 + K)
+    A = rng.standard_normal((M, K)).astype(np.float32)
+    B = rng.standard_normal((K, N)).astype(np.float32)
+    ref = tf32_trunc(A).astype(np.float64) @ tf32_trunc(B).astype(np.float64)
+    got = run(0, 1, M, N, K, 1, 4, A, np.ascontiguousarray(B.T))
+    err = np.abs(got - ref).max()
+    assert err < 2e-4 * np.sqrt(K), (M, N, K, err, np.abs(got).max())

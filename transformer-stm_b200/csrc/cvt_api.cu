@@ -4,6 +4,7 @@
 #include <dlfcn.h>
 #include <math.h>
 #include <string.h>
+#include <stdlib.h>
 
 #include <algorithm>
 #include <random>
@@ -42,7 +43,18 @@ static const char* kStageNames[CVT_MAX_STAGES][12] = {
 
 // ---- contraction dispatch ----------------------------------------------------------------------------------
 cudaError_t run_gemm(const Model* m, const GemmP& p, cudaStream_t s) {
-  if (m->cfg.precision != CVT_PREC_FP32 && gemm_tc_supports(p)) return launch_gemm_tc(p, s);
+  if (m->cfg.precision != CVT_PREC_FP32) {
+    static const bool no_tma = getenv("CVT_NO_TMA") != nullptr;
+    if (!no_tma) {
+      if (p.b_mode == B_KN && p.a_mode == A_PLAIN && m->pt_valid && p.B >= m->P && p.B < m->P + m->n_train && p.ldb == p.N) {
+        // a dense kernel [K,N] of the parameter arena: read its K-major copy (same offset in Pt)
+        GemmP q = p; q.B = m->Pt + (p.B - m->P); q.b_mode = B_NK; q.ldb = p.K;
+        if (gemm_tma_supports(q)) return launch_gemm_tma(q, s);
+      }
+      if (gemm_tma_supports(p)) return launch_gemm_tma(p, s);
+    }
+    if (gemm_tc_supports(p)) return launch_gemm_tc(p, s);
+  }
   return launch_gemm_simt(p, s);
 }
 
@@ -200,6 +212,8 @@ static void carve(Model* m, Bump& b) {
   m->in_y = b.take<float>(MB * c.num_classes);
   m->out_pred = b.take<float>(MB * c.num_classes);
   m->lr_dev = b.take<float>(4);
+  m->Pt = b.take<float>(m->n_train);
+  m->tr_descs_dev = b.take<TrDesc>(64);
 }
 
 static int same_pad(int n, int k, int s, int* before) {
@@ -293,6 +307,17 @@ int cvt_create(const cvt_config* cfg, cvt_model** out) {
   carve(m, b);
   API_CUDA(cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking));
   API_CUDA(cudaMemsetAsync(m->workspace, 0, (size_t)m->workspace_bytes, m->stream));
+  {  // dense kernels the forward GEMMs read K-major (transposed copies in Pt)
+    m->tr_descs.clear(); int tiles = 0;
+    auto add = [&](int64_t off, int K, int N) { m->tr_descs.push_back(TrDesc{off, K, N, tiles}); tiles += cdiv(K, 32) * cdiv(N, 32); };
+    for (int i = 0; i < m->n_stages; ++i) {
+      const StageW& w = m->w[i]; const int D = m->geo[i].D, H4 = c.mlp_ratio * D;
+      for (int z = 0; z < 3; ++z) { add(w.pw + (int64_t)z * D * D, D, D); add(w.mw + (int64_t)z * D * D, D, D); }
+      add(w.ow, D, D); add(w.prw, D, D); add(w.f1w, D, H4); add(w.f2w, H4, D);
+    }
+    m->tr_tiles = tiles;
+    API_CUDA(cudaMemcpyAsync(m->tr_descs_dev, m->tr_descs.data(), m->tr_descs.size() * sizeof(TrDesc), cudaMemcpyHostToDevice, m->stream));
+  }
   API_CUDA(cudaMallocHost(&m->pin_metrics, 4 * sizeof(float)));
   API_CUDA(cudaStreamSynchronize(m->stream));
   *out = h;
@@ -503,6 +528,10 @@ static cudaError_t forward_impl(Model* m, const float* img, const float* proc, i
       CVT_CUDA(launch_philox_mask(a.mask1, RD * c.mlp_ratio, c.drop_rate, m->dropout_seed, m->dropout_step, i * 4 + 1, s));
       CVT_CUDA(launch_philox_mask(a.mask2, RD, c.drop_rate, m->dropout_seed, m->dropout_step, i * 4 + 2, s));
     }
+  }
+  if (c.precision != CVT_PREC_FP32) {
+    CVT_CUDA(launch_transpose_weights(m->P, m->Pt, m->tr_descs_dev, (int)m->tr_descs.size(), m->tr_tiles, s));
+    m->pt_valid = true;
   }
   const float* x = img; long long bstride = (long long)c.image_h * c.image_w * c.in_chans; int boff = 0;
   for (int i = 0; i < m->n_stages; ++i) {

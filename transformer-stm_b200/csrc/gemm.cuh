@@ -52,6 +52,13 @@ cudaError_t launch_gemm_simt(const GemmP& p, cudaStream_t s);
 cudaError_t launch_gemm_tc(const GemmP& p, cudaStream_t s);
 bool gemm_tc_supports(const GemmP& p);
 
+// persistent TMA-fed tcgen05 kernel (gemm_tma.cu): A_PLAIN x B_NK (both K-major), no split-K
+cudaError_t launch_gemm_tma(const GemmP& p, cudaStream_t s);
+bool gemm_tma_supports(const GemmP& p);
+// dst[off + n*K + k] = src[off + k*N + n] for every registered dense kernel (forward GEMMs read their weights K-major)
+struct TrDesc { long long off; int K, N, tile0; };
+cudaError_t launch_transpose_weights(const float* src, float* dst, const TrDesc* descs_dev, int ndesc, int total_tiles, cudaStream_t s);
+
 // column sums (bias gradients): out[z][n] += sum_r X[z][map(r)*ld + n]
 cudaError_t launch_colsum(const float* X, long long ld, RowMap map, int rows, int N, int batch, long long x_bs,
                           float* out, long long out_bs, cudaStream_t s);

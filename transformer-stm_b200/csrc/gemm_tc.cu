@@ -388,7 +388,16 @@ extern "C" CVT_API int cvt_debug_gemm(int a_mode, int b_mode, int M, int N, int 
   p.A = dA; p.a_mode = a_mode; p.lda = a_mode == A_PLAIN ? K : M;
   p.B = dB; p.b_mode = b_mode; p.ldb = b_mode == B_KN ? N : K;
   p.C = dC; p.ldc = N; if (splitk > 1) p.epi = EPI_ATOMIC;
-  p.dbg = use_tc >> 1;
+  p.dbg = (use_tc >> 1) & 1;
+  if (use_tc == 4) {
+    if (!gemm_tma_supports(p)) { cudaFree(dA); cudaFree(dB); cudaFree(dC); set_error("cvt_debug_gemm: shape not supported by the TMA kernel"); return CVT_ERR_INVALID; }
+    e = launch_gemm_tma(p, 0);
+    if (e != cudaSuccess) return fail(e);
+    if ((e = cudaDeviceSynchronize()) != cudaSuccess) return fail(e);
+    if ((e = cudaMemcpy(C, dC, nc * 4, cudaMemcpyDeviceToHost)) != cudaSuccess) return fail(e);
+    cudaFree(dA); cudaFree(dB); cudaFree(dC);
+    return CVT_OK;
+  }
   if (use_tc && !gemm_tc_supports(p)) { cudaFree(dA); cudaFree(dB); cudaFree(dC); set_error("cvt_debug_gemm: shape not supported by the tcgen05 kernel"); return CVT_ERR_INVALID; }
   e = use_tc ? launch_gemm_tc(p, 0) : launch_gemm_simt(p, 0);
   if (e != cudaSuccess) return fail(e);

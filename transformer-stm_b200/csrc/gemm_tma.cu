@@ -1,0 +1,259 @@
+// Persistent, warp-specialised tcgen05 contraction kernel fed by TMA (CVT_PREC_TF32) for the Dense / EinsumDense forward and
+// dgrad products of the CvT block (models/CvT(Par).py:180-188,253-258):  C[M,N] = epilogue(A[M,K] . B[N,K]^T), both operands
+// contiguous along K ("K-major"), fp32 in HBM, read by the tensor core as TF32 with fp32 accumulation in TMEM.
+//
+//   grid       one CTA per SM, each walks tiles (z, m-tile, n-tile) with stride gridDim.x
+//   warp 0     TMA producer: 128x32 A box + BNx32 B box per k-step into a 128B-swizzled ring (mbarrier complete_tx)
+//   warp 1     MMA issuer: 4 x tcgen05.mma 128xBNx8 kind::tf32 per k-step; tcgen05.commit frees the ring slot; the accumulator
+//              is double-buffered in TMEM (2 x BN columns) so the epilogue of tile i overlaps the MMAs of tile i+1
+//   warps 2-17 epilogue: tcgen05.ld -> per-warp smem transpose -> coalesced bias/GELU/mask/residual stores (gemm_epi.cuh)
+// These GEMMs are HBM/L2-bound at the reference sizes (K, N <= 1024): the design goal is bytes in flight, not MMA rate.
+#include <cuda.h>
+
+#include <map>
+#include <tuple>
+
+#include "gemm_epi.cuh"
+#include "model.cuh"
+#include "tc_common.cuh"
+
+namespace cvt {
+using namespace tc;
+
+namespace {
+constexpr int BM = 128, BK = 32, NEPI = 16, NTHREADS = 64 + 32 * NEPI;   // 16 epilogue warps: 4 TMEM lane quadrants x 4 column groups
+constexpr int A_STAGE = BM * BK * 4;                 // 16 KB
+constexpr int STG_BYTES = NEPI * 32 * 20 * 4;        // epilogue transpose tiles (32 rows x 16 columns, padded), one per epilogue warp
+
+template <int BN> struct TCfg {
+  static constexpr int B_STAGE = BN * BK * 4;
+  static constexpr int NS = BN == 64 ? 6 : (BN == 128 ? 5 : 3);
+  static constexpr int SMEM = 1024 + NS * (A_STAGE + B_STAGE) + STG_BYTES + (2 * NS + 4) * 8 + 16;
+};
+
+template <int BN, uint32_t E>
+__global__ void __launch_bounds__(NTHREADS, 1) gemm_tma_kernel(const __grid_constant__ GemmP p, const __grid_constant__ CUtensorMap tmA,
+                                                                const __grid_constant__ CUtensorMap tmB, int m_tiles, int n_tiles,
+                                                                int num_tiles) {
+  using C = TCfg<BN>;
+  constexpr int NS = C::NS;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
+  uint8_t* sA = smem;
+  uint8_t* sB = sA + NS * A_STAGE;
+  float* stg_all = reinterpret_cast<float*>(sB + NS * C::B_STAGE);
+  uint64_t* full = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(stg_all) + STG_BYTES);
+  uint64_t* empty = full + NS;
+  uint64_t* acc_full = empty + NS;       // [2]
+  uint64_t* acc_empty = acc_full + 2;    // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nk = cdiv(p.K, BK);
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB);
+    for (int i = 0; i < NS; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], NEPI); }
+    mbar_fence_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 2 * BN);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int z = tile / (m_tiles * n_tiles), r = tile - z * (m_tiles * n_tiles);
+        const int mt = r / n_tiles, nt = r - mt * n_tiles;
+        for (int kt = 0; kt < nk; ++kt) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          mbar_arrive_expect_tx(&full[stage], A_STAGE + C::B_STAGE);
+          tma_load_3d(sA + stage * A_STAGE, &tmA, &full[stage], kt * BK, mt * BM, z);
+          tma_load_3d(sB + stage * C::B_STAGE, &tmB, &full[stage], kt * BK, nt * BN, z);
+          if (++stage == NS) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(kFmtTF32, BM, BN, 0u, 0u);
+      int stage = 0; uint32_t phase = 0; int it = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+        const int buf = it & 1;
+        mbar_wait(&acc_empty[buf], ((it >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t d = tmem_base + buf * BN;
+        for (int kt = 0; kt < nk; ++kt) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t a0 = smem_u32(sA + stage * A_STAGE), b0 = smem_u32(sB + stage * C::B_STAGE);
+#pragma unroll
+          for (int j = 0; j < BK / 8; ++j)
+            mma_tf32_ss(d, make_smem_desc(a0 + j * 32, 16, 1024), make_smem_desc(b0 + j * 32, 16, 1024), idesc, (kt > 0 || j > 0) ? 1u : 0u);
+          mma_commit(&empty[stage]);
+          if (++stage == NS) { stage = 0; phase ^= 1; }
+        }
+        mma_commit(&acc_full[buf]);
+      }
+    }
+  } else {
+    // ===== epilogue warps: TMEM lane quadrant = warp % 4, 16-column chunks cg, cg + 4, ... =====
+    const int quad = warp & 3, cg = (warp - 2) >> 2;
+    float* stg = stg_all + (warp - 2) * (32 * 20);
+    const int er = lane >> 2, ec = (lane & 3) << 2;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      const int z = tile / (m_tiles * n_tiles), r = tile - z * (m_tiles * n_tiles);
+      const int mt = r / n_tiles, nt = r - mt * n_tiles;
+      const int buf = it & 1;
+      float* Cp = p.C + z * p.c_bs0;
+      float* aux = p.aux ? p.aux + z * p.c_bs0 : nullptr;
+      const float* bias = (p.epi & EPI_BIAS) ? p.bias + z * p.bias_bs : nullptr;
+      const float alpha = ((p.epi & EPI_ALPHA0) && z == 0) ? p.alpha0 : p.alpha;
+      mbar_wait(&acc_full[buf], (it >> 1) & 1);
+      tc_fence_after();
+      const uint32_t trow = tmem_base + buf * BN + ((uint32_t)(quad * 32) << 16);
+#pragma unroll 1
+      for (int c0 = cg * 16; c0 < BN; c0 += 64) {
+        float v[16];
+        tmem_ld16(trow + c0, v);
+#pragma unroll
+        for (int j = 0; j < 16; j += 4) *reinterpret_cast<float4*>(stg + lane * 20 + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int rr = er + 8 * i;
+          const int m = mt * BM + quad * 32 + rr;
+          const float4 acc = *reinterpret_cast<const float4*>(stg + rr * 20 + ec);
+          if (m < p.M) epilogue_f4<E>(p, acc, Cp, aux, bias, alpha, m, nt * BN + c0 + ec);
+        }
+        __syncwarp();
+      }
+      tc_fence_before();
+      if (lane == 0) mbar_arrive(&acc_empty[buf]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 2 * BN);
+}
+
+__global__ void __launch_bounds__(256) transpose_weights_kernel(const float* __restrict__ src, float* __restrict__ dst,
+                                                                const TrDesc* __restrict__ descs, int ndesc) {
+  __shared__ float t[32][33];
+  int d = 0;
+  while (d + 1 < ndesc && (int)blockIdx.x >= descs[d + 1].tile0) ++d;
+  const TrDesc e = descs[d];
+  const int tile = blockIdx.x - e.tile0, tn = cdiv(e.N, 32);
+  const int k0 = (tile / tn) * 32, n0 = (tile % tn) * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int i = ty; i < 32; i += 8) { const int k = k0 + i, n = n0 + tx; t[i][tx] = (k < e.K && n < e.N) ? src[e.off + (long long)k * e.N + n] : 0.f; }
+  __syncthreads();
+  for (int i = ty; i < 32; i += 8) { const int n = n0 + i, k = k0 + tx; if (n < e.N && k < e.K) dst[e.off + (long long)n * e.K + k] = t[tx][i]; }
+}
+
+// ---- tensor maps --------------------------------------------------------------------------------------------------------------
+typedef CUresult (*encode_fn_t)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+encode_fn_t encode_fn() {
+  static encode_fn_t fn = nullptr;
+  if (!fn) {
+    void* f = nullptr; cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<encode_fn_t>(f);
+  }
+  return fn;
+}
+}  // namespace
+
+// fp32 tensor [d2][d1][d0] (d0 contiguous), strides in floats, box {32, box_rows, 1}, 128-byte swizzle, zero fill out of bounds
+bool make_tmap_3d(CUtensorMap* out, const float* base, long long d0, long long d1, long long d2, long long stride1, long long stride2,
+                  int box_rows, int swizzle_mode) {
+  typedef std::tuple<const float*, long long, long long, long long, long long, long long, int, int> Key;
+  static thread_local std::map<Key, CUtensorMap> cache;
+  const Key key{base, d0, d1, d2, stride1, stride2, box_rows, swizzle_mode};
+  auto it = cache.find(key);
+  if (it != cache.end()) { *out = it->second; return true; }
+  encode_fn_t fn = encode_fn();
+  if (!fn) { set_error("cuTensorMapEncodeTiled entry point not found"); return false; }
+  if (d2 < 1) d2 = 1;
+  if (d2 == 1) stride2 = d1 * stride1;
+  const cuuint64_t dims[3] = {(cuuint64_t)d0, (cuuint64_t)d1, (cuuint64_t)d2};
+  const cuuint64_t strides[2] = {(cuuint64_t)stride1 * 4, (cuuint64_t)stride2 * 4};
+  const cuuint32_t box[3] = {32, (cuuint32_t)box_rows, 1};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  const CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(base), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, (CUtensorMapSwizzle)swizzle_mode, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed with code " + std::to_string((int)r)); return false; }
+  cache[key] = *out;
+  return true;
+}
+
+namespace {
+template <int BN, uint32_t E>
+cudaError_t launch_tma_cfg(const GemmP& p, cudaStream_t s) {
+  static bool configured = false;
+  if (!configured) {
+    CVT_CUDA(cudaFuncSetAttribute(gemm_tma_kernel<BN, E>, cudaFuncAttributeMaxDynamicSharedMemorySize, TCfg<BN>::SMEM));
+    configured = true;
+  }
+  CUtensorMap tmA, tmB;
+  if (!make_tmap_3d(&tmA, p.A, p.K, p.M, p.batch, p.lda, p.a_bs0, BM, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
+  if (!make_tmap_3d(&tmB, p.B, p.K, p.N, p.batch, p.ldb, p.b_bs0, BN, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
+  const int m_tiles = cdiv(p.M, BM), n_tiles = p.N / BN, num_tiles = m_tiles * n_tiles * p.batch;
+  const int grid = num_tiles < kNumSMs ? num_tiles : kNumSMs;
+  gemm_tma_kernel<BN, E><<<grid, NTHREADS, TCfg<BN>::SMEM, s>>>(p, tmA, tmB, m_tiles, n_tiles, num_tiles);
+  CVT_LAUNCH_CHECK();
+  return cudaSuccess;
+}
+template <uint32_t E>
+cudaError_t launch_tma_bn(const GemmP& p, int bn, cudaStream_t s) {
+  if (bn == 256) return launch_tma_cfg<256, E>(p, s);
+  if (bn == 128) return launch_tma_cfg<128, E>(p, s);
+  return launch_tma_cfg<64, E>(p, s);
+}
+constexpr uint32_t kTmaEpiKinds = EPI_GELU | EPI_RESID | EPI_GELU_BWD;
+}  // namespace
+
+cudaError_t launch_transpose_weights(const float* src, float* dst, const TrDesc* descs_dev, int ndesc, int total_tiles, cudaStream_t s) {
+  if (ndesc < 1 || total_tiles < 1) return cudaSuccess;
+  transpose_weights_kernel<<<total_tiles, 256, 0, s>>>(src, dst, descs_dev, ndesc);
+  CVT_LAUNCH_CHECK();
+  return cudaSuccess;
+}
+
+bool gemm_tma_supports(const GemmP& p) {
+  if (p.a_mode != A_PLAIN || p.b_mode != B_NK || p.a_map.period || p.a_scale || p.splitk != 1 || p.bdiv != 1) return false;
+  if (p.N % 64 != 0 || p.K % 4 != 0 || p.M < 1 || (p.lda & 3) || (p.ldb & 3) || (p.a_bs0 & 3) || (p.b_bs0 & 3)) return false;
+  if ((reinterpret_cast<uintptr_t>(p.A) & 15) || (reinterpret_cast<uintptr_t>(p.B) & 15)) return false;
+  if (p.epi & (EPI_RELU | EPI_RELU_BWD | EPI_ATOMIC | EPI_SCATTER)) return false;
+  if (p.batch > 1 && (p.c_bs1 || p.a_bs1 || p.b_bs1)) return false;
+  return true;
+}
+
+cudaError_t launch_gemm_tma(const GemmP& p, cudaStream_t s) {
+  if (!gemm_tma_supports(p)) { set_error("gemm_tma: unsupported shape / epilogue"); return cudaErrorNotSupported; }
+  // widest N tile that still gives every SM a tile
+  const long long mt = cdiv(p.M, BM) * (long long)p.batch;
+  int bn = 64;
+  if (p.N % 256 == 0 && mt * (p.N / 256) >= kNumSMs) bn = 256;
+  else if (p.N % 128 == 0 && mt * (p.N / 128) >= kNumSMs) bn = 128;
+  const uint32_t kind = p.epi & kTmaEpiKinds;
+  if (kind == 0) return launch_tma_bn<0>(p, bn, s);
+  if (kind == EPI_RESID) return launch_tma_bn<EPI_RESID>(p, bn, s);
+  if (kind == EPI_GELU) return launch_tma_bn<EPI_GELU>(p, bn, s);
+  if (kind == EPI_GELU_BWD) return launch_tma_bn<EPI_GELU_BWD>(p, bn, s);
+  set_error("gemm_tma: no instantiation for epilogue " + std::to_string(p.epi));
+  return cudaErrorNotSupported;
+}
+
+}  // namespace cvt

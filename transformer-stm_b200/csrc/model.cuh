@@ -54,6 +54,8 @@ struct Model {
   std::vector<ParamInfo> params;
   int64_t n_train = 0, n_state = 0;       // arena lengths (floats, multiples of 4)
   float *P = nullptr, *G = nullptr, *Mo = nullptr, *Vo = nullptr, *St = nullptr;
+  // K-major (transposed) copies of the dense kernels the forward GEMMs read, same offsets as P; refreshed at the start of a forward pass
+  float* Pt = nullptr; std::vector<TrDesc> tr_descs; TrDesc* tr_descs_dev = nullptr; int tr_tiles = 0; bool pt_valid = false;
 
   // head buffers
   float *feat = nullptr, *hln = nullptr, *h_mean = nullptr, *h_rstd = nullptr, *p1 = nullptr, *pred = nullptr;
