@@ -70,3 +70,16 @@ def test_tma_gemm_matches_truncated_tf32(M, N, K):
     got = run(0, 1, M, N, K, 1, 4, A, np.ascontiguousarray(B.T))
     err = np.abs(got - ref).max()
     assert err < 2e-4 * np.sqrt(K), (M, N, K, err, np.abs(got).max())
+
+
+@pytest.mark.parametrize("Kin,N,tokens", [(64, 64, 256), (64, 64, 65536), (64, 256, 8192), (256, 64, 8192), (128, 128, 16384), (128, 512, 4096),
+                                          (512, 128, 4096), (256, 256, 4160), (256, 1024, 4160), (1024, 256, 4160), (192, 192, 1000)])
+def test_tma_wgrad_matches_truncated_tf32(Kin, N, tokens):
+    """TMA-fed split-K weight-gradient kernel (gemm_wgrad.cu): dW = X^T dY with both operands read MN-major"""
+    rng = np.random.default_rng(Kin + N * 3 + tokens)
+    X = rng.standard_normal((tokens, Kin)).astype(np.float32)
+    dY = rng.standard_normal((tokens, N)).astype(np.float32)
+    ref = tf32_trunc(X).astype(np.float64).T @ tf32_trunc(dY).astype(np.float64)
+    got = run(1, 0, Kin, N, tokens, 1, 8, X, dY)
+    err = np.abs(got - ref).max()
+    assert err < 2e-4 * np.sqrt(tokens), (Kin, N, tokens, err, np.abs(got).max())

@@ -89,6 +89,21 @@ static GemmP dense_wgrad(const float* X, long long ldx, int Kin, const float* dY
   return p;
 }
 
+// Dense backward w.r.t. its kernel and bias: dW[z] += X[z]^T dY[z], db[z] += colsum(dY[z]).  TF32 mode: one TMA-fed kernel does both.
+static cudaError_t wgrad_bias(const Model* m, const float* X, long long ldx, int Kin, const float* dY, long long lddy, int Nout, int tokens,
+                              float* dW, float* db, int batch, long long x_bs, long long dy_bs, cudaStream_t s) {
+  static const bool no_tma = getenv("CVT_NO_TMA") != nullptr;
+  if (m->cfg.precision != CVT_PREC_FP32 && !no_tma) {
+    WgradP w; w.X = X; w.ldx = ldx; w.x_bs = x_bs; w.Kin = Kin; w.dY = dY; w.lddy = lddy; w.dy_bs = dy_bs; w.N = Nout; w.tokens = tokens;
+    w.batch = batch; w.dW = dW; w.dw_bs = (long long)Kin * Nout; w.db = db; w.db_bs = Nout;
+    if (wgrad_tma_supports(w)) return launch_wgrad_tma(w, s);
+  }
+  if (db) CVT_CUDA(launch_colsum(dY, lddy, rowmap_none(), tokens, Nout, batch, dy_bs, db, Nout, s));
+  GemmP p = dense_wgrad(X, ldx, Kin, dY, lddy, Nout, tokens, dW);
+  if (batch > 1) { p.batch = batch; p.a_bs0 = x_bs; p.b_bs0 = dy_bs; p.c_bs0 = (long long)Kin * Nout; p.splitk = auto_splitk(Kin, Nout, tokens, batch); }
+  return run_gemm(m, p, s);
+}
+
 // ---- parameters ------------------------------------------------------------------------------------------------
 static int64_t add_param(Model* m, const std::string& name, std::initializer_list<int64_t> shape, bool trainable) {
   ParamInfo pi; pi.name = name; pi.rank = (int)shape.size(); pi.trainable = trainable;
@@ -602,16 +617,14 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
   // ---- Mlp ----
   const float* dM = dX2;
   if (drop) { CVT_CUDA(launch_mask_scale(m->gM, dX2, a.mask2, keep_scale, RD, s)); dM = m->gM; }
-  CVT_CUDA(launch_colsum(dM, D, rowmap_none(), R, D, 1, 0, G + w.f2b, 0, s));
-  CVT_CUDA(run_gemm(m, dense_wgrad(a.hact, H4, H4, dM, D, D, R, G + w.f2w), s));
+  CVT_CUDA(wgrad_bias(m, a.hact, H4, H4, dM, D, D, R, G + w.f2w, G + w.f2b, 1, 0, 0, s));
   {
     GemmP p = dense_dgrad(dM, D, R, D, P + w.f2w, H4, m->gH, H4);      // d hpre = (dM W2^T) * gelu'(hpre) * mask1/keep
     p.epi |= EPI_GELU_BWD; p.aux = a.hpre;
     if (drop) { p.epi |= EPI_MASK; p.mask = a.mask1; p.mask_scale = keep_scale; }
     CVT_CUDA(run_gemm(m, p, s));
   }
-  CVT_CUDA(launch_colsum(m->gH, H4, rowmap_none(), R, H4, 1, 0, G + w.f1b, 0, s));
-  CVT_CUDA(run_gemm(m, dense_wgrad(a.y, D, D, m->gH, H4, H4, R, G + w.f1w), s));
+  CVT_CUDA(wgrad_bias(m, a.y, D, D, m->gH, H4, H4, R, G + w.f1w, G + w.f1b, 1, 0, 0, s));
   CVT_CUDA(run_gemm(m, dense_dgrad(m->gH, H4, R, H4, P + w.f1w, D, m->gC, D), s));          // dY
   // second use of norm1 (:278): dX1 = dX2 + LN'(dY)
   CVT_CUDA(launch_ln_bwd(m->gC, D, a.x1, rowmap_none(), D, a.lnb_mean, a.lnb_rstd, P + w.ln_g, dX2, m->gD, rowmap_none(), D,
@@ -620,21 +633,16 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
   // ---- attention output projections ----
   const float* dA2 = m->gD;
   if (drop) { CVT_CUDA(launch_mask_scale(m->gM, m->gD, a.mask_proj, keep_scale, RD, s)); dA2 = m->gM; }
-  CVT_CUDA(launch_colsum(dA2, D, rowmap_none(), R, D, 1, 0, G + w.prb, 0, s));
-  CVT_CUDA(run_gemm(m, dense_wgrad(a.a1, D, D, dA2, D, D, R, G + w.prw), s));
+  CVT_CUDA(wgrad_bias(m, a.a1, D, D, dA2, D, D, R, G + w.prw, G + w.prb, 1, 0, 0, s));
   CVT_CUDA(run_gemm(m, dense_dgrad(dA2, D, R, D, P + w.prw, D, m->gC, D), s));              // dA1
-  CVT_CUDA(launch_colsum(m->gC, D, rowmap_none(), R, D, 1, 0, G + w.ob, 0, s));
-  CVT_CUDA(run_gemm(m, dense_wgrad(a.attn_o, D, D, m->gC, D, D, R, G + w.ow), s));
+  CVT_CUDA(wgrad_bias(m, a.attn_o, D, D, m->gC, D, D, R, G + w.ow, G + w.ob, 1, 0, 0, s));
   CVT_CUDA(run_gemm(m, dense_dgrad(m->gC, D, R, D, P + w.ow, D, m->gE, D), s));             // dO
   prof_mark(s, kStageNames[si][8]);
   CVT_CUDA(attention_backward(m, si, B, m->gE, m->gQ, s));                                  // gQ = [dQ(pre-scale), dK, dV]
   prof_mark(s, kStageNames[si][9]);
   // ---- MHA q/k/v EinsumDense ----
-  CVT_CUDA(launch_colsum(m->gQ, D, rowmap_none(), R, D, 3, RD, G + w.mb, D, s));
+  CVT_CUDA(wgrad_bias(m, a.qkv1, D, D, m->gQ, D, D, R, G + w.mw, G + w.mb, 3, RD, RD, s));
   {
-    GemmP p = dense_wgrad(a.qkv1, D, D, m->gQ, D, D, R, G + w.mw);
-    p.batch = 3; p.a_bs0 = RD; p.b_bs0 = RD; p.c_bs0 = (long long)D * D; p.splitk = auto_splitk(D, D, R, 3);
-    CVT_CUDA(run_gemm(m, p, s));
     GemmP q = dense_dgrad(m->gQ, D, R, D, P + w.mw, D, m->gQ2, D);
     q.batch = 3; q.a_bs0 = RD; q.b_bs0 = (long long)D * D; q.c_bs0 = RD;
     CVT_CUDA(run_gemm(m, q, s));

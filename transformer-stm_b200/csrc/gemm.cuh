@@ -55,6 +55,18 @@ bool gemm_tc_supports(const GemmP& p);
 // persistent TMA-fed tcgen05 kernel (gemm_tma.cu): A_PLAIN x B_NK (both K-major), no split-K
 cudaError_t launch_gemm_tma(const GemmP& p, cudaStream_t s);
 bool gemm_tma_supports(const GemmP& p);
+// TMA-fed split-K weight-gradient kernel (gemm_wgrad.cu):  dW[z][Kin,N] += X[z][tokens,Kin]^T . dY[z][tokens,N],
+// db[z][N] += column sums of dY (nullable).  Both operands are read MN-major straight from their row-major activations.
+struct WgradP {
+  const float* X = nullptr; long long ldx = 0, x_bs = 0; int Kin = 0;
+  const float* dY = nullptr; long long lddy = 0, dy_bs = 0; int N = 0;
+  int tokens = 0, batch = 1;
+  float* dW = nullptr; long long dw_bs = 0;
+  float* db = nullptr; long long db_bs = 0;
+  int dbg = 0;
+};
+cudaError_t launch_wgrad_tma(const WgradP& p, cudaStream_t s);
+bool wgrad_tma_supports(const WgradP& p);
 // dst[off + n*K + k] = src[off + k*N + n] for every registered dense kernel (forward GEMMs read their weights K-major)
 struct TrDesc { long long off; int K, N, tile0; };
 cudaError_t launch_transpose_weights(const float* src, float* dst, const TrDesc* descs_dev, int ndesc, int total_tiles, cudaStream_t s);

@@ -16,6 +16,7 @@
 #include "gemm_epi.cuh"
 #include "model.cuh"
 #include "tc_common.cuh"
+#include "tma_host.cuh"
 
 namespace cvt {
 using namespace tc;
