@@ -175,7 +175,9 @@ def test_tf32_tensor_core_mode_tracks_oracle(hw, batch, cls):
     eng.set_dropout_masks(masks)
     loss, mae, keep = _run_forward_backward(spec, eng, params, img, proc, y, True)
     r = O.loss_and_grads(spec, params, img, proc, y, masks)
-    bad, report = compare_taps(eng, r["taps"], tol=5e-3)
+    # TF32 mode folds proj_q/k/v + MHA dense (and attention_output + proj) into one GEMM each: qkv1 / a1 are never materialised
+    from tests.parity_utils import TAPS
+    bad, report = compare_taps(eng, r["taps"], tol=5e-3, names=[t for t in TAPS if t not in ("qkv1", "a1")])
     assert not bad, "tf32 forward mismatches:\n" + fmt(report)
     assert abs(loss - r["loss"]) <= 2e-3 * abs(r["loss"])
     bad, report = compare_grads(eng, r["grads"], tol=2e-2)

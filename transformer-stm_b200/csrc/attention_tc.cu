@@ -27,6 +27,7 @@ struct AttnP {
   float* dQ; float* dK; float* dV;
   int Tc, D, heads;
   float dq_scale;
+  int round_out;                                       // store O / dQ / dK / dV rounded to TF32 (they only feed tensor-core GEMMs)
 };
 
 // ---- tile movers: global fp32 rows -> tf32 -> swizzled shared memory -------------------------------------------------
@@ -196,7 +197,11 @@ __global__ void __launch_bounds__(128, 2) attn_fwd_kernel(const __grid_constant_
     float* dst = p.O + base + (long long)q * p.D;
 #pragma unroll
     for (int c = 0; c < 16; ++c)
-      *reinterpret_cast<float4*>(dst + 4 * c) = make_float4(o[4 * c] * inv, o[4 * c + 1] * inv, o[4 * c + 2] * inv, o[4 * c + 3] * inv);
+    {
+      float4 t = make_float4(o[4 * c] * inv, o[4 * c + 1] * inv, o[4 * c + 2] * inv, o[4 * c + 3] * inv);
+      if (p.round_out) t = make_float4(to_tf32(t.x), to_tf32(t.y), to_tf32(t.z), to_tf32(t.w));
+      *reinterpret_cast<float4*>(dst + 4 * c) = t;
+    }
     if (p.LSE) p.LSE[(long long)bh * p.Tc + q] = m_run + logf(l_run);
   }
   tc_fence_before();
@@ -328,7 +333,11 @@ __global__ void __launch_bounds__(256, 1) attn_bwd_dq_kernel(const __grid_consta
     float* dst = p.dQ + base + (long long)q * p.D + half * 32;
 #pragma unroll
     for (int c = 0; c < 8; ++c)
-      *reinterpret_cast<float4*>(dst + 4 * c) = make_float4(acc[4 * c] * p.dq_scale, acc[4 * c + 1] * p.dq_scale, acc[4 * c + 2] * p.dq_scale, acc[4 * c + 3] * p.dq_scale);
+    {
+      float4 t = make_float4(acc[4 * c] * p.dq_scale, acc[4 * c + 1] * p.dq_scale, acc[4 * c + 2] * p.dq_scale, acc[4 * c + 3] * p.dq_scale);
+      if (p.round_out) t = make_float4(to_tf32(t.x), to_tf32(t.y), to_tf32(t.z), to_tf32(t.w));
+      *reinterpret_cast<float4*>(dst + 4 * c) = t;
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -420,13 +429,21 @@ __global__ void __launch_bounds__(256, 1) attn_bwd_dkv_kernel(const __grid_const
   if (kv < p.Tc) {
     float* dst = p.dV + base + (long long)kv * p.D + half * 32;
 #pragma unroll
-    for (int c = 0; c < 8; ++c) *reinterpret_cast<float4*>(dst + 4 * c) = make_float4(acc[4 * c], acc[4 * c + 1], acc[4 * c + 2], acc[4 * c + 3]);
+    for (int c = 0; c < 8; ++c) {
+      float4 t = make_float4(acc[4 * c], acc[4 * c + 1], acc[4 * c + 2], acc[4 * c + 3]);
+      if (p.round_out) t = make_float4(to_tf32(t.x), to_tf32(t.y), to_tf32(t.z), to_tf32(t.w));
+      *reinterpret_cast<float4*>(dst + 4 * c) = t;
+    }
   }
   tmem_ld32(t_row + 192, acc);
   if (kv < p.Tc) {
     float* dst = p.dK + base + (long long)kv * p.D + half * 32;
 #pragma unroll
-    for (int c = 0; c < 8; ++c) *reinterpret_cast<float4*>(dst + 4 * c) = make_float4(acc[4 * c], acc[4 * c + 1], acc[4 * c + 2], acc[4 * c + 3]);
+    for (int c = 0; c < 8; ++c) {
+      float4 t = make_float4(acc[4 * c], acc[4 * c + 1], acc[4 * c + 2], acc[4 * c + 3]);
+      if (p.round_out) t = make_float4(to_tf32(t.x), to_tf32(t.y), to_tf32(t.z), to_tf32(t.w));
+      *reinterpret_cast<float4*>(dst + 4 * c) = t;
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -470,7 +487,7 @@ cudaError_t attention_forward_tc(Model* m, int si, int B, cudaStream_t s) {
   const long long RD = (long long)B * g.Tc * g.D;
   AttnP p{};
   p.Q = a.qkv2; p.K = a.qkv2 + RD; p.V = a.qkv2 + 2 * RD; p.O = a.attn_o; p.LSE = a.lse;
-  p.Tc = g.Tc; p.D = g.D; p.heads = g.heads; p.dq_scale = 0.125f;
+  p.Tc = g.Tc; p.D = g.D; p.heads = g.heads; p.dq_scale = 0.125f; p.round_out = m->folded;
   return run_fwd(p, B, s);
 }
 
@@ -480,7 +497,7 @@ cudaError_t attention_backward_tc(Model* m, int si, int B, const float* dO, floa
   AttnP p{};
   p.Q = a.qkv2; p.K = a.qkv2 + RD; p.V = a.qkv2 + 2 * RD; p.O = a.attn_o; p.LSE = a.lse;
   p.dO = dO; p.Dd = m->attn_dd; p.dQ = dQKV; p.dK = dQKV + RD; p.dV = dQKV + 2 * RD;
-  p.Tc = g.Tc; p.D = g.D; p.heads = g.heads; p.dq_scale = 0.125f;
+  p.Tc = g.Tc; p.D = g.D; p.heads = g.heads; p.dq_scale = 0.125f; p.round_out = m->folded;
   return run_bwd(p, m->attn_dd, B, s);
 }
 

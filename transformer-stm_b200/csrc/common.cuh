@@ -59,6 +59,14 @@ __device__ __forceinline__ float warp_max(float v) {
   return v;
 }
 
+// round-to-nearest TF32 (10-bit mantissa): producers whose output only feeds tensor-core GEMMs store pre-rounded values, so that the
+// tensor core's own truncation of the low 13 bits is exact and the rounding error stays unbiased (what cuBLAS' cvt.rna path gives TF)
+__device__ __forceinline__ float round_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+
 // exact-erf GELU (tf.nn.gelu default, approximate=False) and its derivative
 __device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f)); }
 __device__ __forceinline__ float gelu_erf_grad(float x) {

@@ -51,6 +51,12 @@ cudaError_t run_gemm(const Model* m, const GemmP& p, cudaStream_t s) {
         GemmP q = p; q.B = m->Pt + (p.B - m->P); q.b_mode = B_NK; q.ldb = p.K;
         if (gemm_tma_supports(q)) return launch_gemm_tma(q, s);
       }
+      if (p.b_mode == B_NK && p.a_mode == A_PLAIN && m->pt_valid && p.B >= m->P && p.B < m->P + m->n_train) {
+        // dgrad through a dense kernel of the parameter arena: read its TF32-rounded copy when one is kept
+        const long long off = p.B - m->P;
+        for (const TrDesc& d : m->tr_descs)
+          if (d.copy && d.off == off) { GemmP q = p; q.B = m->Pr + off; if (gemm_tma_supports(q)) return launch_gemm_tma(q, s); }
+      }
       if (gemm_tma_supports(p)) return launch_gemm_tma(p, s);
     }
     if (gemm_tc_supports(p)) return launch_gemm_tc(p, s);
@@ -228,6 +234,9 @@ static void carve(Model* m, Bump& b) {
   m->out_pred = b.take<float>(MB * c.num_classes);
   m->lr_dev = b.take<float>(4);
   m->Pt = b.take<float>(m->n_train);
+  m->Pr = b.take<float>(m->n_train);
+  m->Fd = b.take<float>(m->n_fold);
+  m->mg_fwd_dev = b.take<MgDesc>(64); m->mg_bwd_dev = b.take<MgDesc>(96);
   m->tr_descs_dev = b.take<TrDesc>(64);
 }
 
@@ -311,27 +320,76 @@ int cvt_create(const cvt_config* cfg, cvt_model** out) {
   m->feat_dim = m->d_last + (c.proc_dim > 0 ? c.proc_hidden : 0);
   build_params(m);
 
+  {  // folded-weight scratch layout (TF32 / BF16 modes only)
+    m->folded = c.precision != CVT_PREC_FP32 && getenv("CVT_NO_FOLD") == nullptr;
+    int64_t f = 0, zc = 0;
+    auto al = [](int64_t v) { return (v + 63) / 64 * 64; };
+    for (int i = 0; i < c.n_stages; ++i) {
+      const int64_t D = m->geo[i].D; StageFold& q = m->fold[i];
+      q.Wc = f; f += al(3 * D * D); q.bc = f; f += al(3 * D); q.Wft = f; f += al(3 * D * D); q.bf = f; f += al(3 * D);
+      q.Wo = f; f += al(D * D); q.Wot = f; f += al(D * D); q.bo = f; f += al(D);
+      q.Zq = m->n_train + zc; zc += al(3 * D * D); q.Zo = m->n_train + zc; zc += al(D * D);
+    }
+    m->n_fold = m->folded ? f : 0; m->n_z = m->folded ? zc : 0;
+  }
   Bump measure; carve(m, measure);
-  const int64_t arena_bytes = (4 * m->n_train + std::max<int64_t>(m->n_state, 4)) * (int64_t)sizeof(float);
-  m->workspace_bytes = measure.off + 256 + arena_bytes + 1024;
+  const int64_t arena_bytes = (4 * m->n_train + m->n_z + std::max<int64_t>(m->n_state, 4)) * (int64_t)sizeof(float);
+  m->workspace_bytes = measure.off + 256 + arena_bytes + 8192;
   cudaError_t e = cudaMalloc(&m->workspace, (size_t)m->workspace_bytes);
   if (e != cudaSuccess) { set_error(std::string("cvt_create: cudaMalloc of ") + std::to_string(m->workspace_bytes) + " bytes: " + cudaGetErrorString(e)); delete h; return CVT_ERR_CUDA; }
   Bump b; b.base = reinterpret_cast<char*>(m->workspace);
-  m->P = b.take<float>(m->n_train); m->G = b.take<float>(m->n_train); m->Mo = b.take<float>(m->n_train); m->Vo = b.take<float>(m->n_train);
+  m->P = b.take<float>(m->n_train); m->G = b.take<float>(m->n_train + m->n_z); m->Mo = b.take<float>(m->n_train); m->Vo = b.take<float>(m->n_train);
   m->St = b.take<float>(std::max<int64_t>(m->n_state, 4));
   carve(m, b);
   API_CUDA(cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking));
   API_CUDA(cudaMemsetAsync(m->workspace, 0, (size_t)m->workspace_bytes, m->stream));
   {  // dense kernels the forward GEMMs read K-major (transposed copies in Pt)
     m->tr_descs.clear(); int tiles = 0;
-    auto add = [&](int64_t off, int K, int N) { m->tr_descs.push_back(TrDesc{off, K, N, tiles}); tiles += cdiv(K, 32) * cdiv(N, 32); };
+    auto add = [&](int64_t off, int K, int N, int copy = 0) { m->tr_descs.push_back(TrDesc{off, K, N, tiles, copy}); tiles += cdiv(K, 32) * cdiv(N, 32); };
     for (int i = 0; i < m->n_stages; ++i) {
       const StageW& w = m->w[i]; const int D = m->geo[i].D, H4 = c.mlp_ratio * D;
-      for (int z = 0; z < 3; ++z) { add(w.pw + (int64_t)z * D * D, D, D); add(w.mw + (int64_t)z * D * D, D, D); }
-      add(w.ow, D, D); add(w.prw, D, D); add(w.f1w, D, H4); add(w.f2w, H4, D);
+      if (!m->folded) {
+        for (int z = 0; z < 3; ++z) { add(w.pw + (int64_t)z * D * D, D, D); add(w.mw + (int64_t)z * D * D, D, D); }
+        add(w.ow, D, D); add(w.prw, D, D);
+      }
+      add(w.f1w, D, H4, 1); add(w.f2w, H4, D, 1);
     }
     m->tr_tiles = tiles;
     API_CUDA(cudaMemcpyAsync(m->tr_descs_dev, m->tr_descs.data(), m->tr_descs.size() * sizeof(TrDesc), cudaMemcpyHostToDevice, m->stream));
+  }
+  if (m->folded) {  // multi-GEMM lists that fold the stacked linear maps (forward) and unfold their gradients (backward), see fold.cu
+    std::vector<MgDesc> fw, bw; int tf = 0, tb = 0;
+    auto push = [](std::vector<MgDesc>& v, int& tiles, const float* A, int ta, const float* B, int tbb, float* C, int M, int N, int K,
+                   int lda, int ldb, int ldc, int acc, const float* u, const float* vv, int u1) {
+      MgDesc d{A, B, C, M, N, K, lda, ldb, ldc, ta, tbb, 1.f, acc, u, vv, u1, tiles, (M > 1 && !acc) ? 1 : 0};   // folded kernels are MMA operands
+      tiles += mg_tiles(d); v.push_back(d);
+    };
+    float* P = m->P; float* G = m->G; float* F = m->Fd;
+    for (int i = 0; i < m->n_stages; ++i) {
+      const StageW& w = m->w[i]; const StageFold& q = m->fold[i]; const int D = m->geo[i].D; const int64_t DD = (int64_t)D * D;
+      for (int z = 0; z < 3; ++z) {
+        const float* pw = P + w.pw + z * DD; const float* mw = P + w.mw + z * DD;
+        push(fw, tf, pw, 0, mw, 0, F + q.Wc + z * DD, D, D, D, D, D, D, 0, nullptr, nullptr, 0);                                // Wc = Wp Wm
+        push(fw, tf, P + w.pb + z * D, 0, mw, 0, F + q.bc + z * D, 1, D, D, D, D, D, 0, nullptr, P + w.mb + z * D, 1);            // bc = bp Wm + bm
+        float* N = G + q.Zq + z * DD; float* sv = G + w.mb + z * D;                                                               // s = colsum dq = dbm
+        push(bw, tb, pw, 1, N, 0, G + w.mw + z * DD, D, D, D, D, D, D, 1, P + w.pb + z * D, sv, 0);                               // dWm = Wp^T N + bp (x) s
+        push(bw, tb, N, 0, mw, 1, G + w.pw + z * DD, D, D, D, D, D, D, 1, nullptr, nullptr, 0);                                   // dWp = N Wm^T
+        push(bw, tb, sv, 0, mw, 1, G + w.pb + z * D, 1, D, D, D, D, D, 1, nullptr, nullptr, 0);                                   // dbp = s Wm^T
+      }
+      const float* ow = P + w.ow; const float* prw = P + w.prw;
+      push(fw, tf, ow, 0, prw, 0, F + q.Wo, D, D, D, D, D, D, 0, nullptr, nullptr, 0);                                            // Wo = Wout Wproj
+      push(fw, tf, prw, 1, ow, 1, F + q.Wot, D, D, D, D, D, D, 0, nullptr, nullptr, 0);                                           // Wo^T (K-major copy)
+      push(fw, tf, P + w.ob, 0, prw, 0, F + q.bo, 1, D, D, D, D, D, 0, nullptr, P + w.prb, 1);                                    // bo = bout Wproj + bproj
+      float* Zo = G + q.Zo; float* so = G + w.prb;
+      push(bw, tb, ow, 1, Zo, 0, G + w.prw, D, D, D, D, D, D, 1, P + w.ob, so, 0);                                                // dWproj = Wout^T Zo + bout (x) so
+      push(bw, tb, Zo, 0, prw, 1, G + w.ow, D, D, D, D, D, D, 1, nullptr, nullptr, 0);                                            // dWout = Zo Wproj^T
+      push(bw, tb, so, 0, prw, 1, G + w.ob, 1, D, D, D, D, D, 1, nullptr, nullptr, 0);                                            // dbout = so Wproj^T
+    }
+    if (fw.size() > 64 || bw.size() > 96) { set_error("cvt_create: too many stages for the fold descriptor tables"); cvt_destroy(h); return CVT_ERR_INVALID; }
+    m->mg_fwd_n = (int)fw.size(); m->mg_fwd_tiles = tf; m->mg_bwd_n = (int)bw.size(); m->mg_bwd_tiles = tb;
+    API_CUDA(cudaMemcpyAsync(m->mg_fwd_dev, fw.data(), fw.size() * sizeof(MgDesc), cudaMemcpyHostToDevice, m->stream));
+    API_CUDA(cudaMemcpyAsync(m->mg_bwd_dev, bw.data(), bw.size() * sizeof(MgDesc), cudaMemcpyHostToDevice, m->stream));
+    API_CUDA(cudaStreamSynchronize(m->stream));      // fw / bw are locals
   }
   API_CUDA(cudaMallocHost(&m->pin_metrics, 4 * sizeof(float)));
   API_CUDA(cudaStreamSynchronize(m->stream));
@@ -455,6 +513,8 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
     dp.method[1] = mz; dp.method[2] = mz;
     dp.B = B; dp.H = g.H; dp.W = g.W; dp.D = D; dp.Tc = g.Tc; dp.has_cls = g.has_cls;
     dp.stats = (bn && training) ? a.bn_stats : nullptr;
+    dp.cls_zero = m->folded && bn;
+    dp.round_out = m->folded;
     const bool fast = g.D <= 256 && (g.D & 3) == 0;
     if (fast) { dp.nparts = kStatParts; CVT_CUDA(launch_dwproj_fwd2(dp, s)); }
     else {
@@ -469,6 +529,16 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
     }
   }
   prof_mark(s, kStageNames[si][2]);
+  if (m->folded) {
+    // proj_q/k/v Dense (:180-182) + MHA query/key/value EinsumDense + BatchNorm affine + 1/sqrt(key_dim), folded into one GEMM (fold.cu)
+    const StageFold& f = m->fold[si]; float* F = m->Fd;
+    const bool bn = g.method == CVT_PROJ_DW_BN;
+    CVT_CUDA(launch_bn_fold(F + f.Wc, F + f.bc, bn ? a.bn_scale : nullptr, bn ? a.bn_shift : nullptr, 0.125f, D, F + f.Wft, F + f.bf, s));
+    GemmP p; p.M = R; p.N = D; p.K = D; p.A = a.conv; p.lda = D; p.B = F + f.Wft; p.ldb = D; p.b_mode = B_NK; p.C = a.qkv2; p.ldc = D;
+    p.bias = F + f.bf; p.epi = EPI_BIAS; p.batch = 3; p.a_bs0 = RD; p.b_bs0 = (long long)D * D; p.c_bs0 = RD; p.bias_bs = D;
+    CVT_CUDA(run_gemm(m, p, s));
+    if (bn && g.has_cls) CVT_CUDA(launch_cls_fix(a.xn, RD, F + f.Wc, F + f.bc, 0.125f, B, g.Tc, D, a.qkv2, s));   // cls rows skip BatchNorm
+  } else
   {  // proj_q/k/v = Dense(dim)  :180-182  (BatchNorm applied while the A operand is loaded)
     GemmP p = dense_fwd(a.conv, D, R, D, P + w.pw, D, P + w.pb, a.qkv1, D);
     p.batch = 3; p.a_bs0 = RD; p.b_bs0 = (long long)D * D; p.c_bs0 = RD; p.bias_bs = D;
@@ -483,6 +553,14 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
   prof_mark(s, kStageNames[si][3]);
   CVT_CUDA(attention_forward(m, si, B, s));                                 // self.attention(q, v, k)  :185
   prof_mark(s, kStageNames[si][4]);
+  if (m->folded) {
+    // MHA attention_output EinsumDense + self.proj Dense (:188) as one GEMM, dropout (:189) and residual (:274) in its epilogue
+    const StageFold& f = m->fold[si]; float* F = m->Fd;
+    GemmP q; q.M = R; q.N = D; q.K = D; q.A = a.attn_o; q.lda = D; q.B = F + f.Wot; q.ldb = D; q.b_mode = B_NK; q.C = a.x1; q.ldc = D;
+    q.bias = F + f.bo; q.epi = EPI_BIAS | EPI_RESID; q.resid = a.x0; q.ldr = D;
+    if (drop) { q.epi |= EPI_MASK; q.mask = a.mask_proj; q.mask_scale = keep_scale; }
+    CVT_CUDA(run_gemm(m, q, s));
+  } else
   {
     GemmP p = dense_fwd(a.attn_o, D, R, D, P + w.ow, D, P + w.ob, a.a1, D);      // MHA attention_output
     CVT_CUDA(run_gemm(m, p, s));
@@ -493,10 +571,11 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
   }
   prof_mark(s, kStageNames[si][5]);
   // y = norm1(x)  :278  (same gamma/beta)
-  CVT_CUDA(launch_ln_fwd(a.x1, rowmap_none(), D, P + w.ln_g, P + w.ln_b, c.ln_eps, a.y, D, a.lnb_mean, a.lnb_rstd, R, D, s));
+  CVT_CUDA(launch_ln_fwd(a.x1, rowmap_none(), D, P + w.ln_g, P + w.ln_b, c.ln_eps, a.y, D, a.lnb_mean, a.lnb_rstd, R, D, s, m->folded));
   {  // Mlp :253-258
     GemmP p = dense_fwd(a.y, D, R, D, P + w.f1w, H4, P + w.f1b, a.hact, H4);
     p.epi |= EPI_GELU; p.aux = a.hpre;
+    if (m->folded) p.epi |= EPI_ROUND;
     if (drop) { p.epi |= EPI_MASK; p.mask = a.mask1; p.mask_scale = keep_scale; }
     CVT_CUDA(run_gemm(m, p, s));
     GemmP q = dense_fwd(a.hact, H4, R, H4, P + w.f2w, D, P + w.f2b, a.x2, D);
@@ -545,8 +624,9 @@ static cudaError_t forward_impl(Model* m, const float* img, const float* proc, i
     }
   }
   if (c.precision != CVT_PREC_FP32) {
-    CVT_CUDA(launch_transpose_weights(m->P, m->Pt, m->tr_descs_dev, (int)m->tr_descs.size(), m->tr_tiles, s));
+    CVT_CUDA(launch_transpose_weights(m->P, m->Pt, m->Pr, m->tr_descs_dev, (int)m->tr_descs.size(), m->tr_tiles, s));
     m->pt_valid = true;
+    if (m->folded) CVT_CUDA(launch_multigemm(m->mg_fwd_dev, m->mg_fwd_n, m->mg_fwd_tiles, s));
   }
   const float* x = img; long long bstride = (long long)c.image_h * c.image_w * c.in_chans; int boff = 0;
   for (int i = 0; i < m->n_stages; ++i) {
@@ -616,11 +696,12 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
   prof_mark(s, kStageNames[si][6]);
   // ---- Mlp ----
   const float* dM = dX2;
-  if (drop) { CVT_CUDA(launch_mask_scale(m->gM, dX2, a.mask2, keep_scale, RD, s)); dM = m->gM; }
+  if (drop) { CVT_CUDA(launch_mask_scale(m->gM, dX2, a.mask2, keep_scale, RD, s, m->folded)); dM = m->gM; }
   CVT_CUDA(wgrad_bias(m, a.hact, H4, H4, dM, D, D, R, G + w.f2w, G + w.f2b, 1, 0, 0, s));
   {
     GemmP p = dense_dgrad(dM, D, R, D, P + w.f2w, H4, m->gH, H4);      // d hpre = (dM W2^T) * gelu'(hpre) * mask1/keep
     p.epi |= EPI_GELU_BWD; p.aux = a.hpre;
+    if (m->folded) p.epi |= EPI_ROUND;
     if (drop) { p.epi |= EPI_MASK; p.mask = a.mask1; p.mask_scale = keep_scale; }
     CVT_CUDA(run_gemm(m, p, s));
   }
@@ -630,6 +711,35 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
   CVT_CUDA(launch_ln_bwd(m->gC, D, a.x1, rowmap_none(), D, a.lnb_mean, a.lnb_rstd, P + w.ln_g, dX2, m->gD, rowmap_none(), D,
                          G + w.ln_g, G + w.ln_b, R, D, s));
   prof_mark(s, kStageNames[si][7]);
+  if (m->folded) {
+    // ---- folded path (fold.cu): one wgrad + one dgrad per stacked pair; individual gradients are unfolded at the end of backward ----
+    const StageFold& f = m->fold[si]; float* F = m->Fd;
+    const float* dA2 = m->gD;
+    if (drop) { CVT_CUDA(launch_mask_scale(m->gM, m->gD, a.mask_proj, keep_scale, RD, s, 1)); dA2 = m->gM; }
+    CVT_CUDA(wgrad_bias(m, a.attn_o, D, D, dA2, D, D, R, G + f.Zo, G + w.prb, 1, 0, 0, s));        // Zo = o^T dA2, so = colsum dA2 = dbproj
+    CVT_CUDA(run_gemm(m, dense_dgrad(dA2, D, R, D, F + f.Wo, D, m->gE, D), s));                      // dO = dA2 Wo^T
+    prof_mark(s, kStageNames[si][8]);
+    CVT_CUDA(attention_backward(m, si, B, m->gE, m->gQ, s));                                        // gQ = [dQ(pre-scale), dK, dV]
+    prof_mark(s, kStageNames[si][9]);
+    CVT_CUDA(wgrad_bias(m, a.conv, D, D, m->gQ, D, D, R, G + f.Zq, G + w.mb, 3, RD, RD, s));         // Z_z = c_z^T dq_z, s_z = dbm_z
+    const bool bn = g.method == CVT_PROJ_DW_BN;
+    if (bn)
+      CVT_CUDA(launch_qkv_unfold(G + f.Zq, G + w.mb, a.xn, m->gQ, RD, B, g.T, g.Tc, g.has_cls, D, F + f.Wc, a.bn_scale, a.bn_shift, P + w.bn_g,
+                                 a.bn_mean, a.bn_rstd, training, G + w.bn_g, G + w.bn_b, a.bn_coef, s));
+    {
+      GemmP q = dense_dgrad(m->gQ, D, R, D, F + f.Wc, D, m->gQ2, D);                                 // dn = dq Wc^T, BatchNorm backward in the epilogue
+      q.batch = 3; q.a_bs0 = RD; q.b_bs0 = (long long)D * D; q.c_bs0 = RD;
+      if (bn) { q.epi |= EPI_BN_BWD; q.aux = a.conv; q.epi_coef = a.bn_coef; q.epi_coef_bs = 3 * D; q.epi_skip_period = g.has_cls ? g.Tc : 0; }
+      CVT_CUDA(run_gemm(m, q, s));
+    }
+    prof_mark(s, kStageNames[si][10]);
+    DwProjBwdP dp; dp.dconv = m->gQ2; dp.bs = RD; dp.xn = a.xn; dp.w = bn ? P + w.dw : nullptr;
+    const int mz = bn ? 0 : (g.method == CVT_PROJ_AVG ? 1 : 2);
+    dp.method[0] = (g.method == CVT_PROJ_AVG) ? 2 : mz; dp.method[1] = mz; dp.method[2] = mz;
+    dp.B = B; dp.H = g.H; dp.W = g.W; dp.D = D; dp.Tc = g.Tc; dp.has_cls = g.has_cls; dp.dxn = m->gE; dp.ddw = bn ? G + w.dw : nullptr;
+    if (g.D <= 256 && (g.D & 3) == 0) { dp.ddw_part = m->dw_part; CVT_CUDA(launch_dwproj_bwd2(dp, s)); }
+    else CVT_CUDA(launch_dwproj_bwd(dp, s));
+  } else {
   // ---- attention output projections ----
   const float* dA2 = m->gD;
   if (drop) { CVT_CUDA(launch_mask_scale(m->gM, m->gD, a.mask_proj, keep_scale, RD, s)); dA2 = m->gM; }
@@ -684,6 +794,7 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
       CVT_CUDA(launch_dwproj_bwd(dp, s));
     }
   }
+  }
   // first use of norm1 (:272): dX0 = dX1 + LN'(dXn)   (in place on gD)
   CVT_CUDA(launch_ln_bwd(m->gE, D, a.x0, rowmap_none(), D, a.lna_mean, a.lna_rstd, P + w.ln_g, m->gD, m->gD, rowmap_none(), D,
                          G + w.ln_g, G + w.ln_b, R, D, s));
@@ -717,7 +828,7 @@ static thread_local FwdInputs g_last_inputs{nullptr, nullptr};
 static cudaError_t backward_impl(Model* m, const float* img, const float* proc, int B, int training, int stop_after_stage, float** tap_grad) {
   cudaStream_t s = m->stream;
   g_tc = m->cfg.precision != CVT_PREC_FP32;
-  CVT_CUDA(cudaMemsetAsync(m->G, 0, (size_t)m->n_train * sizeof(float), s));
+  CVT_CUDA(cudaMemsetAsync(m->G, 0, (size_t)(m->n_train + m->n_z) * sizeof(float), s));
   int cur = (m->n_stages - 1) & 1;
   CVT_CUDA(head_backward(m, proc, B, m->gX[cur]));
   for (int i = m->n_stages - 1; i >= 0; --i) {
@@ -729,6 +840,7 @@ static cudaError_t backward_impl(Model* m, const float* img, const float* proc, 
     CVT_CUDA(stage_backward(m, i, xin, bstride, boff, B, training, m->gX[cur], dprev, false));
     cur ^= 1;
   }
+  if (m->folded && !tap_grad) CVT_CUDA(launch_multigemm(m->mg_bwd_dev, m->mg_bwd_n, m->mg_bwd_tiles, s));   // unfold dWp, dbp, dWm, dWout, dbout, dWproj
   prof_mark(s, "end_backward");
   return cudaSuccess;
 }
@@ -991,10 +1103,12 @@ int64_t cvt_get_tap(cvt_model* h, const char* name, float* dst, int64_t capacity
     const RowMap strip = g.has_cls ? RowMap{g.T, g.Tc, 1} : rowmap_none();
     if (!strcmp(f, "x0")) { src = a.x0; n = RD; }
     else if (!strcmp(f, "xn")) { src = a.xn; n = RD; }
-    else if (!strcmp(f, "qkv1")) { src = a.qkv1; n = 3 * RD; }
+    else if (!strcmp(f, "qkv1") || !strcmp(f, "a1")) {
+      if (m->folded) { set_error(std::string("cvt_get_tap: '") + name + "' does not exist in TF32 mode (the stacked linear maps are folded into one GEMM)"); return CVT_ERR_STATE; }
+      if (!strcmp(f, "qkv1")) { src = a.qkv1; n = 3 * RD; } else { src = a.a1; n = RD; }
+    }
     else if (!strcmp(f, "qkv2")) { src = a.qkv2; n = 3 * RD; }
     else if (!strcmp(f, "attn_o")) { src = a.attn_o; n = RD; }
-    else if (!strcmp(f, "a1")) { src = a.a1; n = RD; }
     else if (!strcmp(f, "x1")) { src = a.x1; n = RD; }
     else if (!strcmp(f, "y")) { src = a.y; n = RD; }
     else if (!strcmp(f, "hpre")) { src = a.hpre; n = RD * m->cfg.mlp_ratio; }

@@ -64,7 +64,7 @@ __global__ void __launch_bounds__(384) dwproj_fwd2_kernel(const __grid_constant_
 #pragma unroll
       for (int t = 0; t < 9; ++t) y = f2_fma(win[t / 3][t % 3], w[t], y);
       if (method == 1) { const float ic = inv_count(i, j, H, W); y.x *= ic; y.y *= ic; }
-      *reinterpret_cast<float2*>(out + ((long long)i * W + j) * D) = y;
+      *reinterpret_cast<float2*>(out + ((long long)i * W + j) * D) = p.round_out ? make_float2(round_tf32(y.x), round_tf32(y.y)) : y;
       ssum.x += y.x; ssum.y += y.y; ssq = f2_fma(y, y, ssq);
 #pragma unroll
       for (int q = 0; q < 3; ++q) { win[0][q] = win[1][q]; win[1][q] = win[2][q]; win[2][q] = nx[q]; }
@@ -74,7 +74,7 @@ __global__ void __launch_bounds__(384) dwproj_fwd2_kernel(const __grid_constant_
   if (p.has_cls && jl == 0) {
     for (int b = blockIdx.x; b < p.B; b += gridDim.x) {
       const long long row = (long long)b * p.Tc * D + c;
-      *reinterpret_cast<float2*>(p.out + z * p.out_bs + row) = *reinterpret_cast<const float2*>(p.xn + row);
+      *reinterpret_cast<float2*>(p.out + z * p.out_bs + row) = p.cls_zero ? f2_zero() : *reinterpret_cast<const float2*>(p.xn + row);
     }
   }
   if (p.stats) {    // per-CTA partials, plain stores: bn_finalize sums the gridDim.x slices (no same-line atomics storm)

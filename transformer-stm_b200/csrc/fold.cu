@@ -1,0 +1,133 @@
+// Glue of the folded q/k/v path (TF32 mode): the two stacked linear maps of ConvAttention (proj_q/k/v Dense, then Keras
+// MultiHeadAttention's query/key/value EinsumDense; models/CvT(Par).py:180-185) and the BatchNorm affine in front of
+// them (Projection, :94) are applied as ONE D x D GEMM per token:
+//     q_z = alpha_z ( BN(c_z) Wp_z Wm_z + bp_z Wm_z + bm_z ) = c_z Wf_z + bf_z,    Wf_z = alpha_z diag(sc_z) Wc_z,  Wc_z = Wp_z Wm_z
+// The cls row bypasses BatchNorm (models/CvT(Par).py:150,168-170), so it is recomputed with the unscaled Wc_z by cls_fix_kernel.
+// Backward recovers every individual gradient (Wp, bp, Wm, bm, BN gamma/beta) from Z_z = c_z^T dq_z and s_z = colsum(dq_z):
+// see qkv_unfold_kernel and the multi-GEMM list built in cvt_api.cu.
+#include "layers.cuh"
+
+namespace cvt {
+namespace {
+
+// Wft[z][j][i] = alpha_z sc_z[i] Wc[z][i][j];   bf[z][j] = alpha_z (sum_i sh_z[i] Wc[z][i][j] + bc[z][j])
+// grid (D/32 j-tiles, D/32 i-tiles, 3), block (32, 8)
+__global__ void __launch_bounds__(256) bn_fold_kernel(const float* __restrict__ Wc, const float* __restrict__ bc, const float* __restrict__ sc,
+                                                      const float* __restrict__ sh, float alpha0, int D, float* __restrict__ Wft,
+                                                      float* __restrict__ bf) {
+  __shared__ float t[32][33];
+  __shared__ float red[8][33];
+  const int z = blockIdx.z, j0 = blockIdx.x * 32, i0 = blockIdx.y * 32, tx = threadIdx.x, ty = threadIdx.y;
+  const float alpha = z == 0 ? alpha0 : 1.f;
+  const float* W = Wc + (long long)z * D * D;
+  for (int r = ty; r < 32; r += 8) {
+    const int i = i0 + r;
+    const float s = sc ? sc[z * D + i] : 1.f;
+    t[r][tx] = round_tf32(W[(long long)i * D + j0 + tx] * s * alpha);      // B operand of the folded q/k/v GEMM
+  }
+  __syncthreads();
+  for (int r = ty; r < 32; r += 8) Wft[(long long)z * D * D + (long long)(j0 + r) * D + i0 + tx] = t[tx][r];
+  if (blockIdx.y == 0) {
+    float a = 0.f;
+    if (sh) for (int i = ty; i < D; i += 8) a += sh[z * D + i] * W[(long long)i * D + j0 + tx];
+    red[ty][tx] = a;
+    __syncthreads();
+    if (ty == 0) {
+      float s = 0.f;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) s += red[k][tx];
+      bf[z * D + j0 + tx] = alpha * (s + bc[z * D + j0 + tx]);
+    }
+  }
+}
+
+// q[z][b, cls row, :] = alpha_z (xn[b, cls row, :] Wc[z] + bc[z]);  grid (B, 3), block D threads
+__global__ void cls_fix_kernel(const float* __restrict__ xn, long long bs, const float* __restrict__ Wc, const float* __restrict__ bc,
+                               float alpha0, int Tc, int D, float* __restrict__ q) {
+  extern __shared__ float srow[];
+  const int b = blockIdx.x, z = blockIdx.y, j = threadIdx.x;
+  const long long row = (long long)z * bs + (long long)b * Tc * D;
+  for (int i = threadIdx.x; i < D; i += blockDim.x) srow[i] = xn[(long long)b * Tc * D + i];
+  __syncthreads();
+  const float* W = Wc + (long long)z * D * D;
+  float a = bc[z * D + j];
+  for (int i = 0; i < D; ++i) a = fmaf(srow[i], W[(long long)i * D + j], a);
+  q[row + j] = (z == 0 ? alpha0 : 1.f) * a;
+}
+
+// After Z[z] = c_z^T dq_z over the spatial rows (the cls rows of the conv maps are kept at zero in this mode, so the tensor-core
+// product never contains them and nothing has to be subtracted) and s[z] = colsum(dq_z) over all rows:
+//   Z_sp = Z,  Z_cls = xn_cls^T dq_cls (fp32, here),  s_sp = s - s_cls
+//   dbeta[c]  = sum_j s_sp[j] Wc[c][j]                      (= sum over spatial rows of dn, dn = dq Wc^T)
+//   dgamma[c] = rstd[c] (sum_j Wc[c][j] Z_sp[c][j] - mu[c] dbeta[c])
+//   coef = (A, E, F): dconv = A dn + E conv + F   (training: batch statistics; else A = scale, E = F = 0)
+//   N[c][j] = sc[c] Z_sp[c][j] + sh[c] s_sp[j] + Z_cls[c][j]      (= BN(c)^T dq incl. the un-normalised cls row), in place on Z
+// grid (D/32, 3), block 256: thread (row r = tid / 8, lane l = tid % 8) walks columns l, l + 8, ...
+__global__ void __launch_bounds__(256) qkv_unfold_kernel(float* __restrict__ Z, const float* __restrict__ s_all, const float* __restrict__ xn,
+                                                         const float* __restrict__ dq, long long bs, int B, int Tc, int has_cls, int D,
+                                                         const float* __restrict__ Wc, const float* __restrict__ sc, const float* __restrict__ sh,
+                                                         const float* __restrict__ gamma, const float* __restrict__ mu, const float* __restrict__ rstd,
+                                                         float invN, int training, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                         float* __restrict__ coef) {
+  const int z = blockIdx.y, c = blockIdx.x * 32 + (threadIdx.x >> 3), l = threadIdx.x & 7;
+  float* Zz = Z + (long long)z * D * D;
+  const float* W = Wc + (long long)z * D * D;
+  const float scc = sc[z * D + c], shc = sh[z * D + c];
+  float dot = 0.f, db = 0.f;
+  for (int j = l; j < D; j += 8) {
+    float zc = 0.f, scl = 0.f;
+    if (has_cls) {
+      for (int b = 0; b < B; ++b) {
+        const long long row = (long long)b * Tc * D;
+        const float g = dq[(long long)z * bs + row + j];
+        zc = fmaf(xn[row + c], g, zc); scl += g;
+      }
+    }
+    const float zsp = Zz[(long long)c * D + j], ssp = s_all[z * D + j] - scl;
+    const float w = W[(long long)c * D + j];
+    dot = fmaf(w, zsp, dot); db = fmaf(ssp, w, db);
+    Zz[(long long)c * D + j] = scc * zsp + shc * ssp + zc;
+  }
+#pragma unroll
+  for (int o = 4; o > 0; o >>= 1) { dot += __shfl_xor_sync(0xffffffffu, dot, o); db += __shfl_xor_sync(0xffffffffu, db, o); }
+  if (l == 0) {
+    const int i = z * D + c;
+    const float r = rstd[i], m = mu[i], g = gamma[i];
+    const float dg = r * (dot - m * db);
+    dgamma[i] += dg; dbeta[i] += db;
+    float A, E, F;
+    if (training) { A = g * r; E = -g * r * r * dg * invN; F = -g * r * db * invN + g * r * r * m * dg * invN; }
+    else { A = scc; E = 0.f; F = 0.f; }
+    coef[(z * 3 + 0) * D + c] = A; coef[(z * 3 + 1) * D + c] = E; coef[(z * 3 + 2) * D + c] = F;
+  }
+}
+
+}  // namespace
+
+cudaError_t launch_bn_fold(const float* Wc, const float* bc, const float* sc, const float* sh, float alpha0, int D, float* Wft, float* bf,
+                           cudaStream_t s) {
+  if (D % 32 != 0) { set_error("bn_fold: D must be a multiple of 32"); return cudaErrorInvalidValue; }
+  bn_fold_kernel<<<dim3(D / 32, D / 32, 3), dim3(32, 8), 0, s>>>(Wc, bc, sc, sh, alpha0, D, Wft, bf);
+  CVT_LAUNCH_CHECK();
+  return cudaSuccess;
+}
+
+cudaError_t launch_cls_fix(const float* xn, long long bs, const float* Wc, const float* bc, float alpha0, int B, int Tc, int D, float* q,
+                           cudaStream_t s) {
+  if (D > 1024) { set_error("cls_fix: D > 1024"); return cudaErrorInvalidValue; }
+  cls_fix_kernel<<<dim3(B, 3), D, D * sizeof(float), s>>>(xn, bs, Wc, bc, alpha0, Tc, D, q);
+  CVT_LAUNCH_CHECK();
+  return cudaSuccess;
+}
+
+cudaError_t launch_qkv_unfold(float* Z, const float* s_all, const float* xn, const float* dq, long long bs, int B, int T, int Tc, int has_cls,
+                              int D, const float* Wc, const float* sc, const float* sh, const float* gamma, const float* mu, const float* rstd,
+                              int training, float* dgamma, float* dbeta, float* coef, cudaStream_t s) {
+  if (D % 32 != 0) { set_error("qkv_unfold: D must be a multiple of 32"); return cudaErrorInvalidValue; }
+  qkv_unfold_kernel<<<dim3(D / 32, 3), 256, 0, s>>>(Z, s_all, xn, dq, bs, B, Tc, has_cls, D, Wc, sc, sh, gamma, mu, rstd,
+                                                    1.f / (float)((long long)B * T), training, dgamma, dbeta, coef);
+  CVT_LAUNCH_CHECK();
+  return cudaSuccess;
+}
+
+}  // namespace cvt

@@ -15,7 +15,9 @@ enum BMode : int { B_KN = 0,      // B(k,n) = B[row(k)*ldb + n]
                    B_NK = 1 };    // B(k,n) = B[n*ldb + k]
 enum Epi : uint32_t {
   EPI_BIAS = 1u, EPI_GELU = 2u, EPI_RESID = 4u, EPI_MASK = 8u, EPI_ATOMIC = 16u, EPI_SCATTER = 32u,
-  EPI_GELU_BWD = 64u, EPI_RELU = 128u, EPI_RELU_BWD = 256u, EPI_ALPHA0 = 512u
+  EPI_GELU_BWD = 64u, EPI_RELU = 128u, EPI_RELU_BWD = 256u, EPI_ALPHA0 = 512u,
+  EPI_ROUND = 2048u,      // store C rounded to TF32 (C only feeds tensor-core GEMMs); aux keeps full precision
+  EPI_BN_BWD = 1024u      // v = A[n] v + E[n] aux[idx] + F[n]  (BatchNorm backward as an affine map of (dn, conv); coef = [A|E|F][N])
 };
 
 // Conv2D(padding='same') geometry.  The input map of image b starts at x + b*bstride + boff (floats), which lets a
@@ -42,6 +44,7 @@ struct GemmP {
   uint32_t epi = 0;
   const float* resid = nullptr; long long ldr = 0;
   const uint8_t* mask = nullptr; float mask_scale = 1.f;
+  const float* epi_coef = nullptr; long long epi_coef_bs = 0; int epi_skip_period = 0;   // EPI_BN_BWD (rows m % period == 0 are cls rows: identity)
   int dbg = 0;                                 // diagnostics only (cvt_debug_gemm): bit 0 swaps LBO/SBO of MN-major descriptors
   float* aux = nullptr;                        // same indexing as C: GELU pre-activation (write) / saved activation (read)
 };
@@ -67,9 +70,17 @@ struct WgradP {
 };
 cudaError_t launch_wgrad_tma(const WgradP& p, cudaStream_t s);
 bool wgrad_tma_supports(const WgradP& p);
+// many small fp32 products per launch (multigemm.cu): C = alpha op(A) op(B) [+ u (x) v] [+ 1 (x) v] [+ C]
+struct MgDesc {
+  const float* A; const float* B; float* C; int M, N, K; int lda, ldb, ldc; int ta, tb;   // ta: A(m,k) = A[k*lda + m]; tb: B(k,n) = B[n*ldb + k]
+  float alpha; int accumulate; const float* u; const float* v; int u1; int tile0;
+  int round;      // store round-to-nearest TF32 (the result is a tensor-core operand)
+};
+int mg_tiles(const MgDesc& d);
+cudaError_t launch_multigemm(const MgDesc* descs_dev, int ndesc, int total_tiles, cudaStream_t s);
 // dst[off + n*K + k] = src[off + k*N + n] for every registered dense kernel (forward GEMMs read their weights K-major)
-struct TrDesc { long long off; int K, N, tile0; };
-cudaError_t launch_transpose_weights(const float* src, float* dst, const TrDesc* descs_dev, int ndesc, int total_tiles, cudaStream_t s);
+struct TrDesc { long long off; int K, N, tile0; int copy; };   // copy: dst2[off + k*N + n] = round(src) (a TF32-rounded straight copy, dgrad operand)
+cudaError_t launch_transpose_weights(const float* src, float* dst, float* dst2, const TrDesc* descs_dev, int ndesc, int total_tiles, cudaStream_t s);
 
 // column sums (bias gradients): out[z][n] += sum_r X[z][map(r)*ld + n]
 cudaError_t launch_colsum(const float* X, long long ld, RowMap map, int rows, int N, int batch, long long x_bs,

@@ -7,7 +7,8 @@ namespace {
 // ---- epilogue of 4 consecutive output columns of one row (coalesced domain: a quarter-warp covers 128 contiguous bytes) ----------
 // E = the compile-time epilogue kind (GELU | RESID | GELU_BWD | SCATTER | ATOMIC); bias / alpha / dropout mask stay run-time
 template <uint32_t E>
-__device__ __forceinline__ void epilogue_f4(const GemmP& p, float4 acc, float* Cp, float* aux, const float* bias, float alpha, int m, int n0) {
+__device__ __forceinline__ void epilogue_f4(const GemmP& p, float4 acc, float* Cp, float* aux, const float* bias, float alpha, int m, int n0,
+                                            const float* coef = nullptr) {
   float v[4] = {acc.x, acc.y, acc.z, acc.w};
   if (E & EPI_SCATTER) {
     // C is the conv input gradient [B,hin,win,cin]; m = output pixel, n = (tap, c)
@@ -31,6 +32,12 @@ __device__ __forceinline__ void epilogue_f4(const GemmP& p, float4 acc, float* C
   }
 #pragma unroll
   for (int j = 0; j < 4; ++j) v[j] *= alpha;
+  if (coef != nullptr && !(p.epi_skip_period && (m % p.epi_skip_period) == 0)) {     // EPI_BN_BWD
+    const float4 a4 = *reinterpret_cast<const float4*>(coef + n0), e4 = *reinterpret_cast<const float4*>(coef + p.N + n0);
+    const float4 f4 = *reinterpret_cast<const float4*>(coef + 2 * p.N + n0), c4 = *reinterpret_cast<const float4*>(aux + idx0);
+    v[0] = fmaf(a4.x, v[0], fmaf(e4.x, c4.x, f4.x)); v[1] = fmaf(a4.y, v[1], fmaf(e4.y, c4.y, f4.y));
+    v[2] = fmaf(a4.z, v[2], fmaf(e4.z, c4.z, f4.z)); v[3] = fmaf(a4.w, v[3], fmaf(e4.w, c4.w, f4.w));
+  }
   if (E & EPI_GELU) {
     if (aux) *reinterpret_cast<float4*>(aux + idx0) = make_float4(v[0], v[1], v[2], v[3]);
 #pragma unroll
@@ -48,6 +55,10 @@ __device__ __forceinline__ void epilogue_f4(const GemmP& p, float4 acc, float* C
   if (E & EPI_RESID) {
     const float4 r4 = *reinterpret_cast<const float4*>(p.resid + crow * p.ldr + n0);
     v[0] += r4.x; v[1] += r4.y; v[2] += r4.z; v[3] += r4.w;
+  }
+  if (p.epi & EPI_ROUND) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v[j] = round_tf32(v[j]);
   }
   if (E & EPI_ATOMIC) {
 #pragma unroll

@@ -118,6 +118,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tma_kernel(const __grid_cons
       float* aux = p.aux ? p.aux + z * p.c_bs0 : nullptr;
       const float* bias = (p.epi & EPI_BIAS) ? p.bias + z * p.bias_bs : nullptr;
       const float alpha = ((p.epi & EPI_ALPHA0) && z == 0) ? p.alpha0 : p.alpha;
+      const float* coef = (p.epi & EPI_BN_BWD) ? p.epi_coef + z * p.epi_coef_bs : nullptr;
       mbar_wait(&acc_full[buf], (it >> 1) & 1);
       tc_fence_after();
       const uint32_t trow = tmem_base + buf * BN + ((uint32_t)(quad * 32) << 16);
@@ -133,7 +134,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tma_kernel(const __grid_cons
           const int rr = er + 8 * i;
           const int m = mt * BM + quad * 32 + rr;
           const float4 acc = *reinterpret_cast<const float4*>(stg + rr * 20 + ec);
-          if (m < p.M) epilogue_f4<E>(p, acc, Cp, aux, bias, alpha, m, nt * BN + c0 + ec);
+          if (m < p.M) epilogue_f4<E>(p, acc, Cp, aux, bias, alpha, m, nt * BN + c0 + ec, coef);
         }
         __syncwarp();
       }
@@ -146,7 +147,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tma_kernel(const __grid_cons
   if (warp == 1) tmem_dealloc(tmem_base, 2 * BN);
 }
 
-__global__ void __launch_bounds__(256) transpose_weights_kernel(const float* __restrict__ src, float* __restrict__ dst,
+__global__ void __launch_bounds__(256) transpose_weights_kernel(const float* __restrict__ src, float* __restrict__ dst, float* __restrict__ dst2,
                                                                 const TrDesc* __restrict__ descs, int ndesc) {
   __shared__ float t[32][33];
   int d = 0;
@@ -155,7 +156,12 @@ __global__ void __launch_bounds__(256) transpose_weights_kernel(const float* __r
   const int tile = blockIdx.x - e.tile0, tn = cdiv(e.N, 32);
   const int k0 = (tile / tn) * 32, n0 = (tile % tn) * 32;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  for (int i = ty; i < 32; i += 8) { const int k = k0 + i, n = n0 + tx; t[i][tx] = (k < e.K && n < e.N) ? src[e.off + (long long)k * e.N + n] : 0.f; }
+  for (int i = ty; i < 32; i += 8) {
+    const int k = k0 + i, n = n0 + tx;
+    const float v = (k < e.K && n < e.N) ? round_tf32(src[e.off + (long long)k * e.N + n]) : 0.f;       // both copies are tensor-core operands
+    t[i][tx] = v;
+    if (e.copy && k < e.K && n < e.N) dst2[e.off + (long long)k * e.N + n] = v;
+  }
   __syncthreads();
   for (int i = ty; i < 32; i += 8) { const int n = n0 + i, k = k0 + tx; if (n < e.N && k < e.K) dst[e.off + (long long)n * e.K + k] = t[tx][i]; }
 }
@@ -225,9 +231,9 @@ cudaError_t launch_tma_bn(const GemmP& p, int bn, cudaStream_t s) {
 constexpr uint32_t kTmaEpiKinds = EPI_GELU | EPI_RESID | EPI_GELU_BWD;
 }  // namespace
 
-cudaError_t launch_transpose_weights(const float* src, float* dst, const TrDesc* descs_dev, int ndesc, int total_tiles, cudaStream_t s) {
+cudaError_t launch_transpose_weights(const float* src, float* dst, float* dst2, const TrDesc* descs_dev, int ndesc, int total_tiles, cudaStream_t s) {
   if (ndesc < 1 || total_tiles < 1) return cudaSuccess;
-  transpose_weights_kernel<<<total_tiles, 256, 0, s>>>(src, dst, descs_dev, ndesc);
+  transpose_weights_kernel<<<total_tiles, 256, 0, s>>>(src, dst, dst2, descs_dev, ndesc);
   CVT_LAUNCH_CHECK();
   return cudaSuccess;
 }

@@ -159,7 +159,7 @@ __global__ void dwproj_fwd_kernel(const __grid_constant__ DwProjP p) {
   if (p.has_cls) {
     for (int b = blockIdx.x * PY + py; b < p.B; b += gridDim.x * PY) {
       const long long row = (long long)b * p.Tc * D + c4 * 4;
-      const float4 v = *reinterpret_cast<const float4*>(p.xn + row);
+      const float4 v = p.cls_zero ? f4_zero() : *reinterpret_cast<const float4*>(p.xn + row);
 #pragma unroll
       for (int z = 0; z < 3; ++z) *reinterpret_cast<float4*>(p.out + z * p.out_bs + row) = v;
     }
@@ -413,9 +413,11 @@ __global__ void __launch_bounds__(256) philox_mask_kernel(uint8_t* __restrict__ 
   }
 }
 __global__ void __launch_bounds__(256) mask_scale_kernel(float* __restrict__ dst, const float* __restrict__ src,
-                                                         const uint8_t* __restrict__ mask, float scale, long long n) {
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
-    dst[i] = mask[i] ? src[i] * scale : 0.f;
+                                                         const uint8_t* __restrict__ mask, float scale, long long n, int round) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float v = mask[i] ? src[i] * scale : 0.f;
+    dst[i] = round ? round_tf32(v) : v;
+  }
 }
 __global__ void __launch_bounds__(256) fill_rows_kernel(float* __restrict__ dst, RowMap map, long long ld, const float* __restrict__ src, int rows, int D) {
   const long long total = (long long)rows * D;
@@ -504,11 +506,11 @@ inline int proj_grid(long long npix, int py) {
 }  // namespace
 
 cudaError_t launch_ln_fwd(const float* x, RowMap in_map, long long ldx, const float* gamma, const float* beta, float eps,
-                          float* y, long long ldy, float* mean, float* rstd, int rows, int D, cudaStream_t s) {
+                          float* y, long long ldy, float* mean, float* rstd, int rows, int D, cudaStream_t s, int round_out) {
   if (rows <= 0) return cudaSuccess;
   if (D % 32 != 0 || D > 32 * LN_MAXV) { set_error("layer norm: D must be a multiple of 32 and <= 512"); return cudaErrorInvalidValue; }
   {
-    const cudaError_t e = launch_ln_fwd_v4(x, in_map, ldx, gamma, beta, eps, y, ldy, mean, rstd, rows, D, s);
+    const cudaError_t e = launch_ln_fwd_v4(x, in_map, ldx, gamma, beta, eps, y, ldy, mean, rstd, rows, D, s, round_out);
     if (e != cudaErrorNotSupported) return e;
   }
   ln_fwd_kernel<<<ew_blocks(rows, 8), 256, 0, s>>>(x, in_map, ldx, gamma, beta, eps, y, ldy, mean, rstd, rows, D);
@@ -598,9 +600,9 @@ cudaError_t launch_philox_mask(uint8_t* mask, long long n, float rate, uint64_t 
   CVT_LAUNCH_CHECK();
   return cudaSuccess;
 }
-cudaError_t launch_mask_scale(float* dst, const float* src, const uint8_t* mask, float scale, long long n, cudaStream_t s) {
+cudaError_t launch_mask_scale(float* dst, const float* src, const uint8_t* mask, float scale, long long n, cudaStream_t s, int round) {
   if (n <= 0) return cudaSuccess;
-  mask_scale_kernel<<<ew_blocks(n), 256, 0, s>>>(dst, src, mask, scale, n);
+  mask_scale_kernel<<<ew_blocks(n), 256, 0, s>>>(dst, src, mask, scale, n, round);
   CVT_LAUNCH_CHECK();
   return cudaSuccess;
 }

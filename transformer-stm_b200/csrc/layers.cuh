@@ -7,7 +7,7 @@ namespace cvt {
 // LayerNormalization(epsilon) over the last axis, biased variance — models/CvT(Par).py:248,272,278,328.
 // y[row*ldy + c] = (x[in_map(row)*ldx + c] - mu) * rstd * gamma[c] + beta[c]; mean/rstd saved per row.
 cudaError_t launch_ln_fwd(const float* x, RowMap in_map, long long ldx, const float* gamma, const float* beta, float eps,
-                          float* y, long long ldy, float* mean, float* rstd, int rows, int D, cudaStream_t s);
+                          float* y, long long ldy, float* mean, float* rstd, int rows, int D, cudaStream_t s, int round_out = 0);
 // dx[out_map(row)*ldo + c] = (dres ? dres[out_map(row)*ldo + c] : 0) + LNbwd(dy)[c];  dgamma/dbeta += (atomics)
 cudaError_t launch_ln_bwd(const float* dy, long long lddy, const float* x, RowMap in_map, long long ldx,
                           const float* mean, const float* rstd, const float* gamma,
@@ -16,7 +16,7 @@ cudaError_t launch_ln_bwd(const float* dy, long long lddy, const float* x, RowMa
 
 // vectorised instantiations (ln.cu); cudaErrorNotSupported -> caller uses the generic kernel
 cudaError_t launch_ln_fwd_v4(const float* x, RowMap in_map, long long ldx, const float* gamma, const float* beta, float eps,
-                             float* y, long long ldy, float* mean, float* rstd, int rows, int D, cudaStream_t s);
+                             float* y, long long ldy, float* mean, float* rstd, int rows, int D, cudaStream_t s, int round_out = 0);
 cudaError_t launch_ln_bwd_v4(const float* dy, long long lddy, const float* x, RowMap in_map, long long ldx, const float* mean,
                              const float* rstd, const float* gamma, const float* dres, float* dx, RowMap out_map, long long ldo,
                              float* dgamma, float* dbeta, int rows, int D, cudaStream_t s);
@@ -28,6 +28,8 @@ cudaError_t launch_ln_bwd_v4(const float* dy, long long lddy, const float* x, Ro
 struct DwProjP {
   const float* xn; float* out; long long out_bs; const float* w; int method[3];
   int B, H, W, D, Tc, has_cls; float* stats;
+  int round_out = 0;   // store the maps rounded to TF32 (they only feed tensor-core GEMMs; BN statistics use the unrounded values)
+  int cls_zero = 0;    // write zeros instead of the cls row (folded mode: the cls row never enters the tensor-core products)
   int nparts = 1;      // dwproj.cu: stats is [nparts][6][D] per-CTA partials (bn_finalize sums them); generic kernel: 1 (atomics)
 };
 cudaError_t launch_dwproj_fwd(const DwProjP& p, cudaStream_t s);
@@ -63,6 +65,15 @@ cudaError_t launch_dwproj_bwd2(const DwProjBwdP& p, cudaStream_t s);
 cudaError_t launch_bn_bwd_coef(const float* gamma, const float* mean, const float* rstd, const float* scale, const float* dgamma,
                                const float* dbeta, long long count, int training, int D, float* coef, cudaStream_t s);
 
+// folded q/k/v path (fold.cu)
+cudaError_t launch_bn_fold(const float* Wc, const float* bc, const float* sc, const float* sh, float alpha0, int D, float* Wft, float* bf,
+                           cudaStream_t s);
+cudaError_t launch_cls_fix(const float* xn, long long bs, const float* Wc, const float* bc, float alpha0, int B, int Tc, int D, float* q,
+                           cudaStream_t s);
+cudaError_t launch_qkv_unfold(float* Z, const float* s_all, const float* xn, const float* dq, long long bs, int B, int T, int Tc, int has_cls,
+                              int D, const float* Wc, const float* sc, const float* sh, const float* gamma, const float* mu, const float* rstd,
+                              int training, float* dgamma, float* dbeta, float* coef, cudaStream_t s);
+
 // softmax over the last axis, in place (fp32 attention path) and its backward dS = P*(dP - sum(dP*P)), in place on dP
 cudaError_t launch_softmax_rows(float* S, long long rows, int cols, cudaStream_t s);
 cudaError_t launch_softmax_bwd_rows(float* dP, const float* P, long long rows, int cols, cudaStream_t s);
@@ -70,7 +81,7 @@ cudaError_t launch_softmax_bwd_rows(float* dP, const float* P, long long rows, i
 // dropout keep-masks from Philox4x32-10 (same stream as oracle.dropout_mask)
 cudaError_t launch_philox_mask(uint8_t* mask, long long n, float rate, uint64_t seed, uint32_t step, uint32_t site, cudaStream_t s);
 // dst = src * mask * scale
-cudaError_t launch_mask_scale(float* dst, const float* src, const uint8_t* mask, float scale, long long n, cudaStream_t s);
+cudaError_t launch_mask_scale(float* dst, const float* src, const uint8_t* mask, float scale, long long n, cudaStream_t s, int round = 0);
 // dst[map(r)*ld + c] = src[c] for r < rows (cls token broadcast)
 cudaError_t launch_fill_rows(float* dst, RowMap map, long long ld, const float* src, int rows, int D, cudaStream_t s);
 // out[b*ldo + c] = mean_t x[(b*T+t)*D + c]  and its transpose dx[(b*T+t)*D + c] = dy[b*ldy + c] / T

@@ -17,7 +17,7 @@ template <int VPL, int LPR, int U>
 __global__ void __launch_bounds__(256) ln_fwd_v4_kernel(const float* __restrict__ x, RowMap in_map, long long ldx,
                                                         const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
                                                         float* __restrict__ y, long long ldy, float* __restrict__ mean,
-                                                        float* __restrict__ rstd, int rows) {
+                                                        float* __restrict__ rstd, int rows, int round_out) {
   constexpr int RPW = 32 / LPR, D = LPR * VPL * 4;
   const int lane = threadIdx.x & 31, sub = lane / LPR, li = lane % LPR;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
@@ -63,6 +63,7 @@ __global__ void __launch_bounds__(256) ln_fwd_v4_kernel(const float* __restrict_
           float4 o;
           o.x = (xv[u][v].x - mu) * r * g[v].x + b[v].x; o.y = (xv[u][v].y - mu) * r * g[v].y + b[v].y;
           o.z = (xv[u][v].z - mu) * r * g[v].z + b[v].z; o.w = (xv[u][v].w - mu) * r * g[v].w + b[v].w;
+          if (round_out) o = make_float4(round_tf32(o.x), round_tf32(o.y), round_tf32(o.z), round_tf32(o.w));
           *reinterpret_cast<float4*>(yr + (li + v * LPR) * 4) = o;
         }
         if (li == 0) { if (mean) mean[row] = mu; if (rstd) rstd[row] = r; }
@@ -160,10 +161,10 @@ inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) =
 
 // returns cudaErrorNotSupported when the shape is not one of the vectorised instantiations (the caller falls back)
 cudaError_t launch_ln_fwd_v4(const float* x, RowMap in_map, long long ldx, const float* gamma, const float* beta, float eps,
-                             float* y, long long ldy, float* mean, float* rstd, int rows, int D, cudaStream_t s) {
+                             float* y, long long ldy, float* mean, float* rstd, int rows, int D, cudaStream_t s, int round_out) {
   if ((ldx & 3) || (ldy & 3) || !al16(x) || !al16(y) || !al16(gamma) || !al16(beta)) return cudaErrorNotSupported;
   auto grid = [&](int rpw_u) { long long w = cdivl(rows, rpw_u); long long b = cdivl(w, 8); return (int)(b < 1 ? 1 : (b > kNumSMs * 8 ? kNumSMs * 8 : b)); };
-#define LN_FWD(VPL, LPR, U) ln_fwd_v4_kernel<VPL, LPR, U><<<grid((32 / LPR) * U), 256, 0, s>>>(x, in_map, ldx, gamma, beta, eps, y, ldy, mean, rstd, rows)
+#define LN_FWD(VPL, LPR, U) ln_fwd_v4_kernel<VPL, LPR, U><<<grid((32 / LPR) * U), 256, 0, s>>>(x, in_map, ldx, gamma, beta, eps, y, ldy, mean, rstd, rows, round_out)
   if (D == 64) LN_FWD(1, 16, 4);
   else if (D == 128) LN_FWD(1, 32, 4);
   else if (D == 192) LN_FWD(3, 16, 2);
