@@ -227,7 +227,7 @@ static void carve(Model* m, Bump& b) {
   m->gM = b.take<float>(maxRD); m->gQ = b.take<float>(3 * maxRD); m->gQ2 = b.take<float>(3 * maxRD);
   m->gS = need_scores ? b.take<float>(maxS) : nullptr;
   m->attn_dd = b.take<float>(maxL);
-  { int64_t maxD = 0; for (int i = 0; i < m->n_stages; ++i) maxD = std::max<int64_t>(maxD, m->geo[i].D); m->dw_part = b.take<float>((int64_t)kNumSMs * 27 * maxD); }
+  { int64_t maxD = 0; for (int i = 0; i < m->n_stages; ++i) maxD = std::max<int64_t>(maxD, m->geo[i].D); m->dw_part = b.take<float>((int64_t)kNumSMs * 27 * maxD); m->cls_scratch = b.take<float>(3 * maxD * maxD + 3 * maxD); }
   m->in_img = b.take<float>(maxIn > 0 ? MB * (int64_t)c.image_h * c.image_w * c.in_chans : 0);
   m->in_proc = b.take<float>(MB * std::max(1, c.proc_dim));
   m->in_y = b.take<float>(MB * c.num_classes);
@@ -725,7 +725,7 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
     const bool bn = g.method == CVT_PROJ_DW_BN;
     if (bn)
       CVT_CUDA(launch_qkv_unfold(G + f.Zq, G + w.mb, a.xn, m->gQ, RD, B, g.T, g.Tc, g.has_cls, D, F + f.Wc, a.bn_scale, a.bn_shift, P + w.bn_g,
-                                 a.bn_mean, a.bn_rstd, training, G + w.bn_g, G + w.bn_b, a.bn_coef, s));
+                                 a.bn_mean, a.bn_rstd, training, G + w.bn_g, G + w.bn_b, a.bn_coef, m->cls_scratch, s));
     {
       GemmP q = dense_dgrad(m->gQ, D, R, D, F + f.Wc, D, m->gQ2, D);                                 // dn = dq Wc^T, BatchNorm backward in the epilogue
       q.batch = 3; q.a_bs0 = RD; q.b_bs0 = (long long)D * D; q.c_bs0 = RD;

@@ -51,45 +51,68 @@ __global__ void cls_fix_kernel(const float* __restrict__ xn, long long bs, const
   __syncthreads();
   const float* W = Wc + (long long)z * D * D;
   float a = bc[z * D + j];
+#pragma unroll 16
   for (int i = 0; i < D; ++i) a = fmaf(srow[i], W[(long long)i * D + j], a);
   q[row + j] = (z == 0 ? alpha0 : 1.f) * a;
 }
 
+// Zcls[z][c][j] = sum_b xn[b, cls, c] dq[z][b, cls, j]  and  scls[z][j] = sum_b dq[z][b, cls, j]   (fp32; the cls row is the only row
+// of the block that reaches the q/k/v GEMM without going through conv + BatchNorm).  grid (D/32 j, D/32 c, 3), block (32, 8)
+__global__ void __launch_bounds__(256) cls_outer_kernel(const float* __restrict__ xn, const float* __restrict__ dq, long long bs, int B, int Tc,
+                                                        int D, float* __restrict__ Zcls, float* __restrict__ scls) {
+  __shared__ float sx[32][33], sg[32][33];
+  const int z = blockIdx.z, j0 = blockIdx.x * 32, c0 = blockIdx.y * 32, tx = threadIdx.x, ty = threadIdx.y;
+  float acc[4] = {0.f, 0.f, 0.f, 0.f}, ssum = 0.f;
+  for (int b0 = 0; b0 < B; b0 += 32) {
+    for (int r = ty; r < 32; r += 8) {
+      const int b = b0 + r;
+      const long long row = (long long)b * Tc * D;
+      sx[r][tx] = b < B ? xn[row + c0 + tx] : 0.f;
+      sg[r][tx] = b < B ? dq[(long long)z * bs + row + j0 + tx] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll 8
+    for (int r = 0; r < 32; ++r) {
+      const float g = sg[r][tx];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) acc[q] = fmaf(sx[r][ty + 8 * q], g, acc[q]);
+      ssum += g;
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int q = 0; q < 4; ++q) Zcls[(long long)z * D * D + (long long)(c0 + ty + 8 * q) * D + j0 + tx] = acc[q];
+  if (blockIdx.y == 0 && ty == 0) scls[z * D + j0 + tx] = ssum;
+}
+
 // After Z[z] = c_z^T dq_z over the spatial rows (the cls rows of the conv maps are kept at zero in this mode, so the tensor-core
 // product never contains them and nothing has to be subtracted) and s[z] = colsum(dq_z) over all rows:
-//   Z_sp = Z,  Z_cls = xn_cls^T dq_cls (fp32, here),  s_sp = s - s_cls
+//   Z_sp = Z,  Z_cls / s_cls from cls_outer_kernel (nullptr without a cls token),  s_sp = s - s_cls
 //   dbeta[c]  = sum_j s_sp[j] Wc[c][j]                      (= sum over spatial rows of dn, dn = dq Wc^T)
 //   dgamma[c] = rstd[c] (sum_j Wc[c][j] Z_sp[c][j] - mu[c] dbeta[c])
 //   coef = (A, E, F): dconv = A dn + E conv + F   (training: batch statistics; else A = scale, E = F = 0)
 //   N[c][j] = sc[c] Z_sp[c][j] + sh[c] s_sp[j] + Z_cls[c][j]      (= BN(c)^T dq incl. the un-normalised cls row), in place on Z
-// grid (D/32, 3), block 256: thread (row r = tid / 8, lane l = tid % 8) walks columns l, l + 8, ...
-__global__ void __launch_bounds__(256) qkv_unfold_kernel(float* __restrict__ Z, const float* __restrict__ s_all, const float* __restrict__ xn,
-                                                         const float* __restrict__ dq, long long bs, int B, int Tc, int has_cls, int D,
+// grid (D/8, 3), block 256: one warp per row c, lanes over the columns (coalesced)
+__global__ void __launch_bounds__(256) qkv_unfold_kernel(float* __restrict__ Z, const float* __restrict__ s_all, const float* __restrict__ Zcls,
+                                                         const float* __restrict__ scls, int D,
                                                          const float* __restrict__ Wc, const float* __restrict__ sc, const float* __restrict__ sh,
                                                          const float* __restrict__ gamma, const float* __restrict__ mu, const float* __restrict__ rstd,
                                                          float invN, int training, float* __restrict__ dgamma, float* __restrict__ dbeta,
                                                          float* __restrict__ coef) {
-  const int z = blockIdx.y, c = blockIdx.x * 32 + (threadIdx.x >> 3), l = threadIdx.x & 7;
-  float* Zz = Z + (long long)z * D * D;
-  const float* W = Wc + (long long)z * D * D;
+  const int z = blockIdx.y, c = blockIdx.x * 8 + (threadIdx.x >> 5), l = threadIdx.x & 31;
+  float* Zr = Z + (long long)z * D * D + (long long)c * D;
+  const float* Wr = Wc + (long long)z * D * D + (long long)c * D;
+  const float* Zc = Zcls ? Zcls + (long long)z * D * D + (long long)c * D : nullptr;
   const float scc = sc[z * D + c], shc = sh[z * D + c];
   float dot = 0.f, db = 0.f;
-  for (int j = l; j < D; j += 8) {
-    float zc = 0.f, scl = 0.f;
-    if (has_cls) {
-      for (int b = 0; b < B; ++b) {
-        const long long row = (long long)b * Tc * D;
-        const float g = dq[(long long)z * bs + row + j];
-        zc = fmaf(xn[row + c], g, zc); scl += g;
-      }
-    }
-    const float zsp = Zz[(long long)c * D + j], ssp = s_all[z * D + j] - scl;
-    const float w = W[(long long)c * D + j];
+  for (int j = l; j < D; j += 32) {
+    const float zc = Zc ? Zc[j] : 0.f;
+    const float zsp = Zr[j], ssp = s_all[z * D + j] - (scls ? scls[z * D + j] : 0.f);
+    const float w = Wr[j];
     dot = fmaf(w, zsp, dot); db = fmaf(ssp, w, db);
-    Zz[(long long)c * D + j] = scc * zsp + shc * ssp + zc;
+    Zr[j] = scc * zsp + shc * ssp + zc;
   }
-#pragma unroll
-  for (int o = 4; o > 0; o >>= 1) { dot += __shfl_xor_sync(0xffffffffu, dot, o); db += __shfl_xor_sync(0xffffffffu, db, o); }
+  dot = warp_sum(dot); db = warp_sum(db);
   if (l == 0) {
     const int i = z * D + c;
     const float r = rstd[i], m = mu[i], g = gamma[i];
@@ -122,10 +145,16 @@ cudaError_t launch_cls_fix(const float* xn, long long bs, const float* Wc, const
 
 cudaError_t launch_qkv_unfold(float* Z, const float* s_all, const float* xn, const float* dq, long long bs, int B, int T, int Tc, int has_cls,
                               int D, const float* Wc, const float* sc, const float* sh, const float* gamma, const float* mu, const float* rstd,
-                              int training, float* dgamma, float* dbeta, float* coef, cudaStream_t s) {
+                              int training, float* dgamma, float* dbeta, float* coef, float* scratch, cudaStream_t s) {
   if (D % 32 != 0) { set_error("qkv_unfold: D must be a multiple of 32"); return cudaErrorInvalidValue; }
-  qkv_unfold_kernel<<<dim3(D / 32, 3), 256, 0, s>>>(Z, s_all, xn, dq, bs, B, Tc, has_cls, D, Wc, sc, sh, gamma, mu, rstd,
-                                                    1.f / (float)((long long)B * T), training, dgamma, dbeta, coef);
+  float* Zcls = nullptr; float* scls = nullptr;
+  if (has_cls) {
+    Zcls = scratch; scls = scratch + (long long)3 * D * D;
+    cls_outer_kernel<<<dim3(D / 32, D / 32, 3), dim3(32, 8), 0, s>>>(xn, dq, bs, B, Tc, D, Zcls, scls);
+    CVT_LAUNCH_CHECK();
+  }
+  qkv_unfold_kernel<<<dim3(D / 8, 3), 256, 0, s>>>(Z, s_all, Zcls, scls, D, Wc, sc, sh, gamma, mu, rstd,
+                                                   1.f / (float)((long long)B * T), training, dgamma, dbeta, coef);
   CVT_LAUNCH_CHECK();
   return cudaSuccess;
 }

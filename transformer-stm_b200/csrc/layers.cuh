@@ -72,7 +72,7 @@ cudaError_t launch_cls_fix(const float* xn, long long bs, const float* Wc, const
                            cudaStream_t s);
 cudaError_t launch_qkv_unfold(float* Z, const float* s_all, const float* xn, const float* dq, long long bs, int B, int T, int Tc, int has_cls,
                               int D, const float* Wc, const float* sc, const float* sh, const float* gamma, const float* mu, const float* rstd,
-                              int training, float* dgamma, float* dbeta, float* coef, cudaStream_t s);
+                              int training, float* dgamma, float* dbeta, float* coef, float* scratch /* [3][D][D] + [3][D] */, cudaStream_t s);
 
 // softmax over the last axis, in place (fp32 attention path) and its backward dS = P*(dP - sum(dP*P)), in place on dP
 cudaError_t launch_softmax_rows(float* S, long long rows, int cols, cudaStream_t s);

@@ -69,6 +69,7 @@ struct Model {
   float *metrics = nullptr;               // device [2]: loss, mae
   // gradient scratch shared by the stages
   float *gX[2] = {nullptr, nullptr};      // gradient w.r.t. a block output [B,Tc,D] (ping-pong across stages)
+  float* cls_scratch = nullptr;           // Z_cls [3][D][D] + s_cls [3][D] of the folded q/k/v backward (fold.cu)
   float* dw_part = nullptr;               // per-CTA partials of the depthwise-weight gradient (dwproj.cu)
   float* attn_dd = nullptr;               // tensor-core attention backward: rowsum(dO * O) [B*heads, Tc]
   float *gH = nullptr, *gC = nullptr, *gD = nullptr, *gE = nullptr, *gM = nullptr, *gQ = nullptr, *gQ2 = nullptr, *gS = nullptr;

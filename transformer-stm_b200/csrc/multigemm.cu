@@ -9,8 +9,11 @@
 namespace cvt {
 namespace {
 
+// 64 x 64 tile, K chunks of 32, 256 threads (4 x 4 outputs each).  Operand chunks are fetched as float4s along whichever index is
+// contiguous in memory and prefetched into registers while the previous chunk is multiplied out of shared memory.
+// Shapes: K % 8 == 0; a dimension read along its contiguous axis must be a multiple of 4 (all sizes here are 1 or multiples of 64).
 __global__ void __launch_bounds__(256) multigemm_kernel(const MgDesc* __restrict__ descs, int ndesc) {
-  __shared__ float sA[16][65], sB[16][65];
+  __shared__ __align__(16) float sA[32][68], sB[32][68];
   int d = 0;
   while (d + 1 < ndesc && (int)blockIdx.x >= descs[d + 1].tile0) ++d;
   const MgDesc e = descs[d];
@@ -22,30 +25,63 @@ __global__ void __launch_bounds__(256) multigemm_kernel(const MgDesc* __restrict
   for (int i = 0; i < 4; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-  for (int k0 = 0; k0 < e.K; k0 += 16) {
-    // stage A(m, k) and B(k, n) for 64 x 16 and 16 x 64
-    for (int i = tid; i < 64 * 16; i += 256) {
-      int m, k;
-      if (e.ta) { m = i & 63; k = i >> 6; } else { k = i & 15; m = i >> 4; }       // contiguous index follows the memory layout
-      const int gm = m0 + m, gk = k0 + k;
-      float v = 0.f;
-      if (gm < e.M && gk < e.K) v = e.ta ? e.A[(long long)gk * e.lda + gm] : e.A[(long long)gm * e.lda + gk];
-      sA[k][m] = v;
+  // fetch coordinates: "row-contiguous-in-k" operands (A plain, B transposed): row = tid / 4, k segment = (tid % 4) * 8
+  //                    "k-major" operands (A transposed, B plain):            k = tid / 8,  mn segment = (tid % 8) * 8
+  float4 ra[2], rb[2];
+  auto fetch = [&](int k0) {
+    if (!e.ta) {
+      const int m = m0 + (tid >> 2), k = k0 + ((tid & 3) << 3);
+      const bool ok = m < e.M && k < e.K;
+      const float4* src = reinterpret_cast<const float4*>(e.A + (long long)(ok ? m : 0) * e.lda + (ok ? k : 0));
+      ra[0] = ok ? src[0] : make_float4(0.f, 0.f, 0.f, 0.f); ra[1] = ok ? src[1] : make_float4(0.f, 0.f, 0.f, 0.f);
+    } else {
+      const int k = k0 + (tid >> 3), m = m0 + ((tid & 7) << 3);
+      const bool ok = k < e.K && m < e.M;
+      const float4* src = reinterpret_cast<const float4*>(e.A + (long long)(ok ? k : 0) * e.lda + (ok ? m : 0));
+      ra[0] = ok ? src[0] : make_float4(0.f, 0.f, 0.f, 0.f); ra[1] = (ok && m + 4 < e.M) ? src[1] : make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    for (int i = tid; i < 64 * 16; i += 256) {
-      int n, k;
-      if (e.tb) { k = i & 15; n = i >> 4; } else { n = i & 63; k = i >> 6; }
-      const int gn = n0 + n, gk = k0 + k;
-      float v = 0.f;
-      if (gn < e.N && gk < e.K) v = e.tb ? e.B[(long long)gn * e.ldb + gk] : e.B[(long long)gk * e.ldb + gn];
-      sB[k][n] = v;
+    if (e.tb) {
+      const int n = n0 + (tid >> 2), k = k0 + ((tid & 3) << 3);
+      const bool ok = n < e.N && k < e.K;
+      const float4* src = reinterpret_cast<const float4*>(e.B + (long long)(ok ? n : 0) * e.ldb + (ok ? k : 0));
+      rb[0] = ok ? src[0] : make_float4(0.f, 0.f, 0.f, 0.f); rb[1] = ok ? src[1] : make_float4(0.f, 0.f, 0.f, 0.f);
+    } else {
+      const int k = k0 + (tid >> 3), n = n0 + ((tid & 7) << 3);
+      const bool ok = k < e.K && n < e.N;
+      const float4* src = reinterpret_cast<const float4*>(e.B + (long long)(ok ? k : 0) * e.ldb + (ok ? n : 0));
+      rb[0] = ok ? src[0] : make_float4(0.f, 0.f, 0.f, 0.f); rb[1] = (ok && n + 4 < e.N) ? src[1] : make_float4(0.f, 0.f, 0.f, 0.f);
     }
+  };
+  auto stash = [&]() {
+    if (!e.ta) {
+      const int m = tid >> 2, k = (tid & 3) << 3;
+      const float v[8] = {ra[0].x, ra[0].y, ra[0].z, ra[0].w, ra[1].x, ra[1].y, ra[1].z, ra[1].w};
+#pragma unroll
+      for (int i = 0; i < 8; ++i) sA[k + i][m] = v[i];
+    } else {
+      const int k = tid >> 3, m = (tid & 7) << 3;
+      *reinterpret_cast<float4*>(&sA[k][m]) = ra[0]; *reinterpret_cast<float4*>(&sA[k][m + 4]) = ra[1];
+    }
+    if (e.tb) {
+      const int n = tid >> 2, k = (tid & 3) << 3;
+      const float v[8] = {rb[0].x, rb[0].y, rb[0].z, rb[0].w, rb[1].x, rb[1].y, rb[1].z, rb[1].w};
+#pragma unroll
+      for (int i = 0; i < 8; ++i) sB[k + i][n] = v[i];
+    } else {
+      const int k = tid >> 3, n = (tid & 7) << 3;
+      *reinterpret_cast<float4*>(&sB[k][n]) = rb[0]; *reinterpret_cast<float4*>(&sB[k][n + 4]) = rb[1];
+    }
+  };
+  fetch(0);
+  for (int k0 = 0; k0 < e.K; k0 += 32) {
+    stash();
     __syncthreads();
+    if (k0 + 32 < e.K) fetch(k0 + 32);
 #pragma unroll
-    for (int k = 0; k < 16; ++k) {
-      float a[4], b[4];
-#pragma unroll
-      for (int i = 0; i < 4; ++i) { a[i] = sA[k][ty * 4 + i]; b[i] = sB[k][tx * 4 + i]; }
+    for (int k = 0; k < 32; ++k) {
+      const float4 a4 = *reinterpret_cast<const float4*>(&sA[k][ty * 4]);
+      const float4 b4 = *reinterpret_cast<const float4*>(&sB[k][tx * 4]);
+      const float a[4] = {a4.x, a4.y, a4.z, a4.w}, b[4] = {b4.x, b4.y, b4.z, b4.w};
 #pragma unroll
       for (int i = 0; i < 4; ++i)
 #pragma unroll
