@@ -200,6 +200,7 @@ static void carve(Model* m, Bump& b) {
     maxRD = std::max(maxRD, RD); maxRH = std::max(maxRH, RH); maxS = std::max(maxS, S);
     maxIn = std::max(maxIn, MB * (int64_t)g.hin * g.win * g.cin);
     maxL = std::max(maxL, MB * g.heads * (int64_t)g.Tc);
+    s.col = m->folded ? b.take<float>(MB * g.T * (int64_t)m->fold[i].Kp) : nullptr;
     s.x0 = b.take<float>(RD); s.xn = b.take<float>(RD); s.conv = b.take<float>(3 * RD);
     s.qkv1 = b.take<float>(3 * RD); s.qkv2 = b.take<float>(3 * RD);
     s.attn_o = b.take<float>(RD); s.a1 = b.take<float>(RD); s.x1 = b.take<float>(RD); s.y = b.take<float>(RD);
@@ -233,7 +234,7 @@ static void carve(Model* m, Bump& b) {
   m->in_y = b.take<float>(MB * c.num_classes);
   m->out_pred = b.take<float>(MB * c.num_classes);
   m->lr_dev = b.take<float>(4);
-  m->Pt = b.take<float>(m->n_train);
+  m->Pt = b.take<float>(m->n_train + m->n_pt_extra);
   m->Pr = b.take<float>(m->n_train);
   m->Fd = b.take<float>(m->n_fold);
   m->mg_fwd_dev = b.take<MgDesc>(64); m->mg_bwd_dev = b.take<MgDesc>(96);
@@ -322,15 +323,17 @@ int cvt_create(const cvt_config* cfg, cvt_model** out) {
 
   {  // folded-weight scratch layout (TF32 / BF16 modes only)
     m->folded = c.precision != CVT_PREC_FP32 && getenv("CVT_NO_FOLD") == nullptr;
-    int64_t f = 0, zc = 0;
+    int64_t f = 0, zc = 0, pt_extra = 0;
     auto al = [](int64_t v) { return (v + 63) / 64 * 64; };
     for (int i = 0; i < c.n_stages; ++i) {
       const int64_t D = m->geo[i].D; StageFold& q = m->fold[i];
       q.Wc = f; f += al(3 * D * D); q.bc = f; f += al(3 * D); q.Wft = f; f += al(3 * D * D); q.bf = f; f += al(3 * D);
       q.Wo = f; f += al(D * D); q.Wot = f; f += al(D * D); q.bo = f; f += al(D);
       q.Zq = m->n_train + zc; zc += al(3 * D * D); q.Zo = m->n_train + zc; zc += al(D * D);
+      q.Kc = m->geo[i].k * m->geo[i].k * m->geo[i].cin; q.Kp = (q.Kc + 3) / 4 * 4;
+      q.convt = m->n_train + pt_extra; pt_extra += al(D * q.Kp);
     }
-    m->n_fold = m->folded ? f : 0; m->n_z = m->folded ? zc : 0;
+    m->n_fold = m->folded ? f : 0; m->n_z = m->folded ? zc : 0; m->n_pt_extra = m->folded ? pt_extra : 0;
   }
   Bump measure; carve(m, measure);
   const int64_t arena_bytes = (4 * m->n_train + m->n_z + std::max<int64_t>(m->n_state, 4)) * (int64_t)sizeof(float);
@@ -345,7 +348,8 @@ int cvt_create(const cvt_config* cfg, cvt_model** out) {
   API_CUDA(cudaMemsetAsync(m->workspace, 0, (size_t)m->workspace_bytes, m->stream));
   {  // dense kernels the forward GEMMs read K-major (transposed copies in Pt)
     m->tr_descs.clear(); int tiles = 0;
-    auto add = [&](int64_t off, int K, int N, int copy = 0) { m->tr_descs.push_back(TrDesc{off, K, N, tiles, copy}); tiles += cdiv(K, 32) * cdiv(N, 32); };
+    auto add = [&](int64_t off, int K, int N, int copy = 0, int64_t toff = -1, int ldt = 0) {
+      m->tr_descs.push_back(TrDesc{off, K, N, tiles, copy, toff < 0 ? off : toff, ldt ? ldt : K}); tiles += cdiv(K, 32) * cdiv(N, 32); };
     for (int i = 0; i < m->n_stages; ++i) {
       const StageW& w = m->w[i]; const int D = m->geo[i].D, H4 = c.mlp_ratio * D;
       if (!m->folded) {
@@ -353,6 +357,7 @@ int cvt_create(const cvt_config* cfg, cvt_model** out) {
         add(w.ow, D, D); add(w.prw, D, D);
       }
       add(w.f1w, D, H4, 1); add(w.f2w, H4, D, 1);
+      if (m->folded) add(w.conv_w, m->fold[i].Kc, D, i > 0 ? 1 : 0, m->fold[i].convt, m->fold[i].Kp);      // ConvEmbed kernel [K][D] -> [D][Kp]
     }
     m->tr_tiles = tiles;
     API_CUDA(cudaMemcpyAsync(m->tr_descs_dev, m->tr_descs.data(), m->tr_descs.size() * sizeof(TrDesc), cudaMemcpyHostToDevice, m->stream));
@@ -493,6 +498,17 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
   float* P = m->P;
 
   prof_mark(s, kStageNames[si][0]);
+  if (m->folded) {
+    // ConvEmbed as explicit im2col (kept for the weight gradient) + TMA-fed GEMM against the K-major kernel copy — im2col.cu
+    const StageFold& f = m->fold[si];
+    const ConvGeom cv{g.hin, g.win, g.cin, g.H, g.W, g.k, g.s, g.pt, g.pl, xin_bstride, xin_boff};
+    CVT_CUDA(launch_im2col(xin, cv, B * g.T, f.Kc, f.Kp, a.col, s));
+    GemmP p; p.M = B * g.T; p.N = D; p.K = f.Kp; p.A = a.col; p.lda = f.Kp; p.B = m->Pt + f.convt; p.ldb = f.Kp; p.b_mode = B_NK;
+    p.C = a.x0; p.ldc = D; if (g.has_cls) p.c_map = RowMap{g.T, g.Tc, 1};
+    p.bias = P + w.conv_b; p.epi = EPI_BIAS;
+    CVT_CUDA(run_gemm(m, p, s));
+    if (g.has_cls) CVT_CUDA(launch_fill_rows(a.x0, RowMap{1, g.Tc, 0}, D, P + w.cls, B, D, s));   // :264-268
+  } else
   {  // ConvEmbed: Conv2D(D, patch, stride, 'same') + bias — models/CvT(Par).py:203-212 (its LayerNorm is dead code)
     GemmP p; p.M = B * g.T; p.N = D; p.K = g.k * g.k * g.cin;
     p.A = xin; p.a_mode = A_CONV; p.cv = ConvGeom{g.hin, g.win, g.cin, g.H, g.W, g.k, g.s, g.pt, g.pl, xin_bstride, xin_boff};
@@ -801,6 +817,24 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
   prof_mark(s, kStageNames[si][11]);
   // ---- cls token + ConvEmbed ----
   if (g.has_cls) CVT_CUDA(launch_colsum(m->gD, D, RowMap{1, g.Tc, 0}, B, D, 1, 0, G + w.cls, 0, s));
+  if (m->folded) {
+    const StageFold& f = m->fold[si];
+    const float* dY = m->gD;                       // gradient w.r.t. the embed output, spatial rows only
+    if (g.has_cls) { CVT_CUDA(launch_copy_rows(m->gC, rowmap_none(), D, m->gD, RowMap{g.T, g.Tc, 1}, D, B * g.T, D, s)); dY = m->gC; }
+    WgradP wg; wg.X = a.col; wg.ldx = f.Kp; wg.Kin = f.Kc; wg.dY = dY; wg.lddy = D; wg.N = D; wg.tokens = B * g.T;
+    wg.dW = G + w.conv_w; wg.dw_bs = 0; wg.db = G + w.conv_b; wg.db_bs = 0;
+    CVT_CUDA(launch_wgrad_tma(wg, s));             // dW = col^T dY, db = colsum dY
+    if (dXprev) {
+      const StageGeo& gp = m->geo[si - 1];
+      const ConvGeom cv{g.hin, g.win, g.cin, g.H, g.W, g.k, g.s, g.pt, g.pl, xin_bstride, xin_boff};
+      if (gp.has_cls) CVT_CUDA(cudaMemsetAsync(dXprev, 0, (size_t)B * gp.Tc * gp.D * sizeof(float), s));
+      GemmP q; q.M = B * g.T; q.N = f.Kc; q.K = D; q.A = dY; q.lda = D; q.B = m->Pr + w.conv_w; q.ldb = D; q.b_mode = B_NK;
+      q.C = a.col; q.ldc = f.Kp;                   // dcol = dY W^T overwrites the patch matrix (its last reader was the wgrad above)
+      CVT_CUDA(run_gemm(m, q, s));
+      CVT_CUDA(launch_col2im(a.col, cv, B, f.Kp, dXprev, s));
+    }
+    return cudaSuccess;
+  }
   const RowMap emap = g.has_cls ? RowMap{g.T, g.Tc, 1} : rowmap_none();
   CVT_CUDA(launch_colsum(m->gD, D, emap, B * g.T, D, 1, 0, G + w.conv_b, 0, s));
   const ConvGeom cv{g.hin, g.win, g.cin, g.H, g.W, g.k, g.s, g.pt, g.pl, xin_bstride, xin_boff};

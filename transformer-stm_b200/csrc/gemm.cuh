@@ -79,8 +79,12 @@ struct MgDesc {
 int mg_tiles(const MgDesc& d);
 cudaError_t launch_multigemm(const MgDesc* descs_dev, int ndesc, int total_tiles, cudaStream_t s);
 // dst[off + n*K + k] = src[off + k*N + n] for every registered dense kernel (forward GEMMs read their weights K-major)
-struct TrDesc { long long off; int K, N, tile0; int copy; };   // copy: dst2[off + k*N + n] = round(src) (a TF32-rounded straight copy, dgrad operand)
+struct TrDesc { long long off; int K, N, tile0; int copy; long long toff; int ldt; };   // transposed copy at dst[toff + n*ldt + k]   // copy: dst2[off + k*N + n] = round(src) (a TF32-rounded straight copy, dgrad operand)
 cudaError_t launch_transpose_weights(const float* src, float* dst, float* dst2, const TrDesc* descs_dev, int ndesc, int total_tiles, cudaStream_t s);
+
+// explicit im2col / col2im for ConvEmbed in TF32 mode (im2col.cu)
+cudaError_t launch_im2col(const float* x, const ConvGeom& g, int M, int K, int ldc, float* col, cudaStream_t s);
+cudaError_t launch_col2im(const float* dcol, const ConvGeom& g, int B, int ldc, float* dx, cudaStream_t s);
 
 // column sums (bias gradients): out[z][n] += sum_r X[z][map(r)*ld + n]
 cudaError_t launch_colsum(const float* X, long long ld, RowMap map, int rows, int N, int batch, long long x_bs,

@@ -163,7 +163,7 @@ __global__ void __launch_bounds__(256) transpose_weights_kernel(const float* __r
     if (e.copy && k < e.K && n < e.N) dst2[e.off + (long long)k * e.N + n] = v;
   }
   __syncthreads();
-  for (int i = ty; i < 32; i += 8) { const int n = n0 + i, k = k0 + tx; if (n < e.N && k < e.K) dst[e.off + (long long)n * e.K + k] = t[tx][i]; }
+  for (int i = ty; i < 32; i += 8) { const int n = n0 + i, k = k0 + tx; if (n < e.N && k < e.K) dst[e.toff + (long long)n * e.ldt + k] = t[tx][i]; }
 }
 
 // ---- tensor maps --------------------------------------------------------------------------------------------------------------

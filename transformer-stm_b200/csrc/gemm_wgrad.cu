@@ -188,7 +188,7 @@ cudaError_t launch_w(const WgradP& p, cudaStream_t s) {
 }  // namespace
 
 bool wgrad_tma_supports(const WgradP& p) {
-  if (p.Kin < 4 || p.N < 4 || (p.Kin & 3) || (p.N & 3) || p.tokens < 1 || p.batch < 1) return false;
+  if (p.Kin < 1 || p.N < 4 || (p.N & 3) || p.tokens < 1 || p.batch < 1) return false;      // Kin need not be a multiple of 4 (ldx must)
   if ((p.ldx & 3) || (p.lddy & 3) || (p.x_bs & 3) || (p.dy_bs & 3) || (p.dw_bs & 3)) return false;
   if ((reinterpret_cast<uintptr_t>(p.X) & 15) || (reinterpret_cast<uintptr_t>(p.dY) & 15) || (reinterpret_cast<uintptr_t>(p.dW) & 15)) return false;
   return true;

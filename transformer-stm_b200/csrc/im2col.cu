@@ -1,0 +1,99 @@
+// ConvEmbed (Conv2D(D, k, s, 'same'), models/CvT(Par).py:203-208) as an explicit-im2col GEMM in TF32 mode: the patch matrix
+//     col[(b,i,j)][(kh,kw,c)] = x[b, s i + kh - pt, s j + kw - pl, c]          (0 outside the image: TF 'SAME' padding)
+// is written once (pre-rounded to TF32, row stride ldc = K rounded up to 4 floats so TMA can box it), then the forward product,
+// the weight gradient (col^T dY) and the input gradient (dcol = dY W^T, gathered back by col2im) all run on the TMA-fed tcgen05
+// kernels.  Both kernels here are pure data movement: coalesced along the channel axis, one pass, no atomics.
+#include "gemm.cuh"
+
+namespace cvt {
+namespace {
+
+// cin % 4 == 0: one thread per (row m, tap, float4 channel group)
+__global__ void __launch_bounds__(256) im2col_v4_kernel(const float* __restrict__ x, ConvGeom g, int M, int ldc, float* __restrict__ col) {
+  const int c4n = g.cin >> 2, per_row = g.k * g.k * c4n;
+  const long long total = (long long)M * per_row;
+  const int hw = g.ho * g.wo;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+    const int m = (int)(idx / per_row), r = (int)(idx - (long long)m * per_row);
+    const int tap = r / c4n, c = (r - tap * c4n) << 2;
+    const int kh = tap / g.k, kw = tap - kh * g.k;
+    const int b = m / hw, pix = m - b * hw, oi = pix / g.wo, oj = pix - oi * g.wo;
+    const int yy = g.s * oi + kh - g.pt, xx = g.s * oj + kw - g.pl;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (yy >= 0 && yy < g.hin && xx >= 0 && xx < g.win) {
+      v = *reinterpret_cast<const float4*>(x + (long long)b * g.bstride + g.boff + ((long long)yy * g.win + xx) * g.cin + c);
+      v = make_float4(round_tf32(v.x), round_tf32(v.y), round_tf32(v.z), round_tf32(v.w));
+    }
+    *reinterpret_cast<float4*>(col + (long long)m * ldc + tap * g.cin + c) = v;
+  }
+}
+
+// any cin (stage 1: cin = 1): one thread per (row m, padded column kk)
+__global__ void __launch_bounds__(256) im2col_scalar_kernel(const float* __restrict__ x, ConvGeom g, int M, int K, int ldc, float* __restrict__ col) {
+  const long long total = (long long)M * ldc;
+  const int hw = g.ho * g.wo;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+    const int m = (int)(idx / ldc), kk = (int)(idx - (long long)m * ldc);
+    float v = 0.f;
+    if (kk < K) {
+      const int tap = kk / g.cin, c = kk - tap * g.cin;
+      const int kh = tap / g.k, kw = tap - kh * g.k;
+      const int b = m / hw, pix = m - b * hw, oi = pix / g.wo, oj = pix - oi * g.wo;
+      const int yy = g.s * oi + kh - g.pt, xx = g.s * oj + kw - g.pl;
+      if (yy >= 0 && yy < g.hin && xx >= 0 && xx < g.win)
+        v = round_tf32(x[(long long)b * g.bstride + g.boff + ((long long)yy * g.win + xx) * g.cin + c]);
+    }
+    col[idx] = v;
+  }
+}
+
+// transposed gather: dx[b, y, x, c] = sum over taps (kh, kw) with s | (y + pt - kh), s | (x + pl - kw) of dcol[(b,i,j)][(kh,kw,c)]
+// one thread per (b, y, x, float4 channel group); cin % 4 == 0
+__global__ void __launch_bounds__(256) col2im_v4_kernel(const float* __restrict__ dcol, ConvGeom g, int B, int ldc, float* __restrict__ dx) {
+  const int c4n = g.cin >> 2;
+  const long long total = (long long)B * g.hin * g.win * c4n;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(idx % c4n) << 2;
+    long long r = idx / c4n;
+    const int xx = (int)(r % g.win); r /= g.win;
+    const int yy = (int)(r % g.hin); const int b = (int)(r / g.hin);
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int kh = 0; kh < g.k; ++kh) {
+      const int ty = yy + g.pt - kh;
+      if (ty < 0 || ty % g.s) continue;
+      const int oi = ty / g.s;
+      if (oi >= g.ho) continue;
+      for (int kw = 0; kw < g.k; ++kw) {
+        const int tx = xx + g.pl - kw;
+        if (tx < 0 || tx % g.s) continue;
+        const int oj = tx / g.s;
+        if (oj >= g.wo) continue;
+        const float4 v = *reinterpret_cast<const float4*>(dcol + ((long long)(b * g.ho + oi) * g.wo + oj) * ldc + (kh * g.k + kw) * g.cin + c);
+        a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+      }
+    }
+    *reinterpret_cast<float4*>(dx + (long long)b * g.bstride + g.boff + ((long long)yy * g.win + xx) * g.cin + c) = a;
+  }
+}
+
+inline int ew_grid(long long n) { long long b = (n + 255) / 256; const long long cap = (long long)kNumSMs * 16; return (int)(b < 1 ? 1 : (b > cap ? cap : b)); }
+
+}  // namespace
+
+cudaError_t launch_im2col(const float* x, const ConvGeom& g, int M, int K, int ldc, float* col, cudaStream_t s) {
+  if ((g.cin & 3) == 0 && (g.boff & 3) == 0 && (g.bstride & 3) == 0 && ldc == K)
+    im2col_v4_kernel<<<ew_grid((long long)M * (K >> 2)), 256, 0, s>>>(x, g, M, ldc, col);
+  else
+    im2col_scalar_kernel<<<ew_grid((long long)M * ldc), 256, 0, s>>>(x, g, M, K, ldc, col);
+  CVT_LAUNCH_CHECK();
+  return cudaSuccess;
+}
+
+cudaError_t launch_col2im(const float* dcol, const ConvGeom& g, int B, int ldc, float* dx, cudaStream_t s) {
+  if ((g.cin & 3) || (g.boff & 3) || (g.bstride & 3)) { set_error("col2im: cin must be a multiple of 4"); return cudaErrorInvalidValue; }
+  col2im_v4_kernel<<<ew_grid((long long)B * g.hin * g.win * (g.cin >> 2)), 256, 0, s>>>(dcol, g, B, ldc, dx);
+  CVT_LAUNCH_CHECK();
+  return cudaSuccess;
+}
+
+}  // namespace cvt

@@ -29,7 +29,7 @@ struct StageW {
 };
 
 // folded-weight scratch (TF32 mode): offsets (floats) into the fold arena Fd; Zq / Zo are offsets into the gradient arena past n_train
-struct StageFold { int64_t Wc, bc, Wft, bf, Wo, Wot, bo, Zq, Zo; };
+struct StageFold { int64_t Wc, bc, Wft, bf, Wo, Wot, bo, Zq, Zo; int64_t convt; int Kc, Kp; };   // convt: K-major conv kernel [D][Kp] in Pt
 
 struct StageGeo {
   int hin, win, cin, H, W, D, T, Tc, heads, has_cls, k, s, pt, pl, method;
@@ -37,6 +37,7 @@ struct StageGeo {
 
 // activations kept from the forward pass (training keeps everything the backward reads)
 struct StageBuf {
+  float* col;                            // TF32 mode: im2col patch matrix of this stage's ConvEmbed [B*T, Kp] (kept for the weight gradient)
   float *x0, *xn, *conv, *qkv1, *qkv2, *attn_o, *a1, *x1, *y, *hpre, *hact, *x2;
   float *lna_mean, *lna_rstd, *lnb_mean, *lnb_rstd;
   float *bn_stats, *bn_scale, *bn_shift, *bn_mean, *bn_rstd, *bn_coef;
@@ -58,7 +59,7 @@ struct Model {
   int64_t n_train = 0, n_state = 0;       // arena lengths (floats, multiples of 4)
   float *P = nullptr, *G = nullptr, *Mo = nullptr, *Vo = nullptr, *St = nullptr;
   // K-major (transposed) copies of the dense kernels the forward GEMMs read, same offsets as P; refreshed at the start of a forward pass
-  float* Fd = nullptr; int64_t n_fold = 0, n_z = 0; StageFold fold[CVT_MAX_STAGES]; bool folded = false;
+  float* Fd = nullptr; int64_t n_fold = 0, n_z = 0, n_pt_extra = 0; StageFold fold[CVT_MAX_STAGES]; bool folded = false;
   MgDesc* mg_fwd_dev = nullptr; int mg_fwd_n = 0, mg_fwd_tiles = 0; MgDesc* mg_bwd_dev = nullptr; int mg_bwd_n = 0, mg_bwd_tiles = 0;
   float* Pr = nullptr;                    // TF32-rounded straight copies of the dense kernels the dgrad GEMMs read (same offsets as P)
   float* Pt = nullptr; std::vector<TrDesc> tr_descs; TrDesc* tr_descs_dev = nullptr; int tr_tiles = 0; bool pt_valid = false;
