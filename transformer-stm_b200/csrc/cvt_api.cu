@@ -228,7 +228,7 @@ static void carve(Model* m, Bump& b) {
   m->gM = b.take<float>(maxRD); m->gQ = b.take<float>(3 * maxRD); m->gQ2 = b.take<float>(3 * maxRD);
   m->gS = need_scores ? b.take<float>(maxS) : nullptr;
   m->attn_dd = b.take<float>(maxL);
-  { int64_t maxD = 0; for (int i = 0; i < m->n_stages; ++i) maxD = std::max<int64_t>(maxD, m->geo[i].D); m->dw_part = b.take<float>((int64_t)kNumSMs * 27 * maxD); m->cls_scratch = b.take<float>(3 * maxD * maxD + 3 * maxD); }
+  { int64_t maxD = 0; for (int i = 0; i < m->n_stages; ++i) maxD = std::max<int64_t>(maxD, m->geo[i].D); m->dw_part = b.take<float>((int64_t)2 * kNumSMs * 27 * maxD); m->cls_scratch = b.take<float>(3 * maxD * maxD + 3 * maxD); }
   m->in_img = b.take<float>(maxIn > 0 ? MB * (int64_t)c.image_h * c.image_w * c.in_chans : 0);
   m->in_proc = b.take<float>(MB * std::max(1, c.proc_dim));
   m->in_y = b.take<float>(MB * c.num_classes);
@@ -532,7 +532,12 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
     dp.cls_zero = m->folded && bn;
     dp.round_out = m->folded;
     const bool fast = g.D <= 256 && (g.D & 3) == 0;
-    if (fast) { dp.nparts = kStatParts; CVT_CUDA(launch_dwproj_fwd2(dp, s)); }
+    if (fast) {
+      dp.nparts = kStatParts;
+      cudaError_t e = (m->folded && bn) ? launch_dwplane_fwd(dp, s) : cudaErrorNotSupported;
+      if (e == cudaErrorNotSupported) e = launch_dwproj_fwd2(dp, s);
+      CVT_CUDA(e);
+    }
     else {
       if (dp.stats) CVT_CUDA(cudaMemsetAsync(a.bn_stats, 0, 6 * D * sizeof(float), s));
       CVT_CUDA(launch_dwproj_fwd(dp, s));
@@ -753,7 +758,12 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
     const int mz = bn ? 0 : (g.method == CVT_PROJ_AVG ? 1 : 2);
     dp.method[0] = (g.method == CVT_PROJ_AVG) ? 2 : mz; dp.method[1] = mz; dp.method[2] = mz;
     dp.B = B; dp.H = g.H; dp.W = g.W; dp.D = D; dp.Tc = g.Tc; dp.has_cls = g.has_cls; dp.dxn = m->gE; dp.ddw = bn ? G + w.dw : nullptr;
-    if (g.D <= 256 && (g.D & 3) == 0) { dp.ddw_part = m->dw_part; CVT_CUDA(launch_dwproj_bwd2(dp, s)); }
+    if (g.D <= 256 && (g.D & 3) == 0) {
+      dp.ddw_part = m->dw_part;
+      cudaError_t e = bn ? launch_dwplane_bwd(dp, s) : cudaErrorNotSupported;
+      if (e == cudaErrorNotSupported) e = launch_dwproj_bwd2(dp, s);
+      CVT_CUDA(e);
+    }
     else CVT_CUDA(launch_dwproj_bwd(dp, s));
   } else {
   // ---- attention output projections ----

@@ -283,6 +283,12 @@ cudaError_t launch_dwproj_bwd2(const DwProjBwdP& p, cudaStream_t s) {
   return cudaSuccess;
 }
 
+cudaError_t launch_reduce_partials(const float* part, int nparts, int n, float* dst, cudaStream_t s) {
+  reduce_partials_kernel<<<cdiv(n, 32), dim3(32, 8), 0, s>>>(part, nparts, n, dst);
+  CVT_LAUNCH_CHECK();
+  return cudaSuccess;
+}
+
 cudaError_t launch_bn_bwd_coef(const float* gamma, const float* mean, const float* rstd, const float* scale, const float* dgamma,
                                const float* dbeta, long long count, int training, int D, float* coef, cudaStream_t s) {
   bn_bwd_coef_kernel<<<cdiv(3 * D, 128), 128, 0, s>>>(gamma, mean, rstd, scale, dgamma, dbeta, 1.f / (float)count, training, D, coef);
