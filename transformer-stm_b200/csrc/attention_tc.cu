@@ -2,16 +2,24 @@
 // models/CvT(Par).py:185:  S = Q K^T (Q already carries 1/sqrt(key_dim)), P = softmax(S), O = P V; key_dim = 64 in every spec.
 // The [B, heads, Tc, Tc] score tensor never reaches HBM: forward keeps the row log-sum-exp, backward recomputes P from it.
 //
-//   forward   CTA = 128 query rows of one (image, head); thread t owns row t (TMEM lane t).  Per 64-key tile:
-//             K/V tile -> swizzled smem, S = Q K^T (8 UMMA 128x64x8) -> TMEM, tcgen05.ld, online softmax in registers,
-//             P -> smem (K-major), P V -> TMEM, accumulated with the running rescale in registers.  2 CTAs per SM.
+// All three kernels are warp-specialised pipelines: warp 0 = TMA producer (K-major tiles with the 128B swizzle, MN-major tiles
+// with the 32-byte-atom 128B swizzle, both straight from the [B, Tc, D] tensors, zero fill past Tc), warp 1 = tcgen05.mma issuer,
+// the remaining warps own one TMEM lane (= one row of the 128-row tile) each.  The probabilities never touch shared memory:
+// they are written back over the scores in TMEM (tcgen05.st) and consumed from there as the A operand of the next product.
+// The score tile is double-buffered so that the tensor core works on tile j+1 while the row threads exponentiate tile j.
+//
+//   forward   CTA = 128 query rows of one (image, head), 64-key tiles, 2 CTAs per SM.  O accumulates in TMEM; the running max
+//             is only refreshed when it grows by more than 2^8 (the exponentials stay in fp32 range, the final O / l is exact),
+//             so O is rescaled in TMEM a handful of times per row block instead of once per tile.
 //   backward  dQ kernel (CTA = 128 query rows, loops over key tiles) and dK/dV kernel (CTA = 128 key rows, loops over query
-//             tiles, works on S^T so that P^T / dS^T are produced row-per-thread as K-major A operands).  256 threads:
-//             warps w and w+4 share a TMEM lane quadrant and split the 64 tile columns.  No atomics.
-//   layouts   Q/K/V/O/dO are [B, Tc, D] with head h in columns [64h, 64h+64); operands that are contiguous along the
-//             contraction index are staged K-major (SWIZZLE_128B), the others MN-major (SWIZZLE_128B_BASE32B).
+//             tiles, works on S^T so that P^T / dS^T are produced row-per-thread).  8 row warps: warps w and w+4 share a TMEM
+//             lane quadrant and split the 64 tile columns.  No atomics.
+//   operands  Q/K/V/dO must already be rounded to TF32 by their producers (EPI_ROUND); TMA moves raw fp32 words.
+#include <cuda.h>
+
 #include "model.cuh"
 #include "tc_common.cuh"
+#include "tma_host.cuh"
 
 namespace cvt {
 using namespace tc;
@@ -19,6 +27,9 @@ using namespace tc;
 namespace {
 constexpr int HD = 64;
 constexpr float kLog2e = 1.4426950408889634f;
+constexpr int TILE16K = 16384;                          // one 64-row x 64-float operand tile (two 32-float boxes of 8 KB)
+constexpr int TILE32K = 32768;                          // one 128-row x 64-float operand tile (two boxes of 16 KB)
+constexpr uint32_t kFullMask = 0xffffffffu;
 
 struct AttnP {
   const float* Q; const float* K; const float* V;      // [B, Tc, D]
@@ -30,212 +41,188 @@ struct AttnP {
   int round_out;                                       // store O / dQ / dK / dV rounded to TF32 (they only feed tensor-core GEMMs)
 };
 
-// ---- tile movers: global fp32 rows -> tf32 -> swizzled shared memory -------------------------------------------------
-// K-major tile of `rows` x 64 floats: two 32-float atoms along the contraction axis, atom a at a*rows*128 bytes.
-template <int ROWS, int NT>
-__device__ __forceinline__ void load_kmajor(uint8_t* dst, const float* src, long long ld, int row0, int nrows_valid, int tid) {
-  // ROWS x 16 float4
-#pragma unroll
-  for (int i = 0; i < ROWS * 16 / NT; ++i) {
-    const int idx = tid + NT * i;
-    const int r = idx >> 4, c4 = idx & 15;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (row0 + r < nrows_valid) v = *reinterpret_cast<const float4*>(src + (long long)(row0 + r) * ld + c4 * 4);
-    v.x = to_tf32(v.x); v.y = to_tf32(v.y); v.z = to_tf32(v.z); v.w = to_tf32(v.w);
-    *reinterpret_cast<float4*>(dst + (c4 >> 3) * (ROWS * 128) + sw128_kmajor_off(r, c4 & 7)) = v;
-  }
-}
-// MN-major tile: contraction index = row (ROWS of them), MN = the 64 features (2 atoms of 32 floats)
-template <int ROWS, int NT>
-__device__ __forceinline__ void load_mnmajor(uint8_t* dst, const float* src, long long ld, int row0, int nrows_valid, int tid) {
-#pragma unroll
-  for (int i = 0; i < ROWS * 16 / NT; ++i) {
-    const int idx = tid + NT * i;
-    const int r = idx >> 4, c4 = idx & 15;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (row0 + r < nrows_valid) v = *reinterpret_cast<const float4*>(src + (long long)(row0 + r) * ld + c4 * 4);
-    v.x = to_tf32(v.x); v.y = to_tf32(v.y); v.z = to_tf32(v.z); v.w = to_tf32(v.w);
-    *reinterpret_cast<float4*>(dst + sw128_mnmajor_off(r, c4, 2)) = v;
-  }
-}
-// both layouts from one global read
-template <int ROWS, int NT>
-__device__ __forceinline__ void load_both(uint8_t* dst_k, uint8_t* dst_mn, const float* src, long long ld, int row0, int nrows_valid, int tid) {
-#pragma unroll
-  for (int i = 0; i < ROWS * 16 / NT; ++i) {
-    const int idx = tid + NT * i;
-    const int r = idx >> 4, c4 = idx & 15;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (row0 + r < nrows_valid) v = *reinterpret_cast<const float4*>(src + (long long)(row0 + r) * ld + c4 * 4);
-    v.x = to_tf32(v.x); v.y = to_tf32(v.y); v.z = to_tf32(v.z); v.w = to_tf32(v.w);
-    *reinterpret_cast<float4*>(dst_k + (c4 >> 3) * (ROWS * 128) + sw128_kmajor_off(r, c4 & 7)) = v;
-    *reinterpret_cast<float4*>(dst_mn + sw128_mnmajor_off(r, c4, 2)) = v;
-  }
-}
-
-// D[tmem] (+)= A * B with A K-major [128 x 64] (atoms of A_ROWS rows) and B K-major [64 rows x 64] (contraction = 64 floats)
+// D[tmem] = A * B with A K-major [128 x 64] (two boxes of A_ROWS rows) and B K-major [B_ROWS x 64]; contraction = 64 floats
 template <int A_ROWS, int B_ROWS>
-__device__ __forceinline__ void mma_kk(uint32_t tmem_d, uint32_t a0, uint32_t b0, uint32_t idesc, bool accumulate) {
+__device__ __forceinline__ void mma_kk(uint32_t tmem_d, uint32_t a0, uint32_t b0, uint32_t idesc) {
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     const uint64_t ad = make_smem_desc(a0 + (j >> 2) * (A_ROWS * 128) + (j & 3) * 32, 16, 1024);
     const uint64_t bd = make_smem_desc(b0 + (j >> 2) * (B_ROWS * 128) + (j & 3) * 32, 16, 1024);
-    mma_tf32_ss(tmem_d, ad, bd, idesc, (accumulate || j > 0) ? 1u : 0u);
+    mma_tf32_ss(tmem_d, ad, bd, idesc, j > 0 ? 1u : 0u);
   }
 }
-// A K-major [128 x 64] and B MN-major [64 contraction rows x 64 features]
-template <int A_ROWS>
-__device__ __forceinline__ void mma_kmn(uint32_t tmem_d, uint32_t a0, uint32_t b0, uint32_t idesc, bool accumulate) {
+// D[tmem] (+)= A[tmem, 128 lanes x 64 columns] * B with B MN-major: 64 contraction rows x 64 features as two TMA boxes
+// (32 features x 64 rows, 8 KB each, 32-byte-atom swizzle): LBO = next feature box, SBO = next group of 4 contraction rows
+__device__ __forceinline__ void mma_tmn(uint32_t tmem_d, uint32_t tmem_a, uint32_t b0, uint32_t idesc, bool accumulate) {
 #pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const uint64_t ad = make_smem_desc(a0 + (j >> 2) * (A_ROWS * 128) + (j & 3) * 32, 16, 1024);
-    const uint64_t bd = make_smem_desc(b0 + j * 2048, 512, 1024, kLayoutSw128Base32);
-    mma_tf32_ss(tmem_d, ad, bd, idesc, (accumulate || j > 0) ? 1u : 0u);
-  }
+  for (int j = 0; j < 8; ++j)
+    mma_tf32_ts(tmem_d, tmem_a + j * 8, make_smem_desc(b0 + j * 1024, 8192, 512, kLayoutSw128Base32), idesc, (accumulate || j > 0) ? 1u : 0u);
 }
 
 __device__ __forceinline__ uint8_t* align1024(uint8_t* p) {
   const uint32_t a = smem_u32(p);
   return p + (((a + 1023u) & ~1023u) - a);
 }
-
-// one row of 32 tf32 values -> K-major swizzled tile (row-per-thread writers), atom `atom` of a tile with ROWS rows
-template <int ROWS>
-__device__ __forceinline__ void store_row32(uint8_t* tile, int row, int atom, const float v[32]) {
-  uint8_t* base = tile + atom * (ROWS * 128);
-#pragma unroll
-  for (int c = 0; c < 8; ++c)
-    *reinterpret_cast<float4*>(base + sw128_kmajor_off(row, c)) =
-        make_float4(to_tf32(v[4 * c]), to_tf32(v[4 * c + 1]), to_tf32(v[4 * c + 2]), to_tf32(v[4 * c + 3]));
+// two 32-float boxes of `rows` rows: columns [col0, col0 + 64) of rows [row0, row0 + rows) of image z
+__device__ __forceinline__ void tma_tile(uint8_t* dst, const CUtensorMap* tm, uint64_t* bar, int col0, int row0, int z, int rows) {
+  tma_load_3d(dst, tm, bar, col0, row0, z);
+  tma_load_3d(dst + rows * 128, tm, bar, col0 + 32, row0, z);
+}
+__device__ __forceinline__ float4 out4(const uint32_t* v, float sc, int round) {
+  float4 t = make_float4(__uint_as_float(v[0]) * sc, __uint_as_float(v[1]) * sc, __uint_as_float(v[2]) * sc, __uint_as_float(v[3]) * sc);
+  if (round) t = make_float4(to_tf32(t.x), to_tf32(t.y), to_tf32(t.z), to_tf32(t.w));
+  return t;
 }
 
 // =====================================================================================================================
 // forward
 // =====================================================================================================================
-constexpr int FWD_SMEM = 1024 + 32768 + 16384 + 16384 + 32768 + 64;
+constexpr int FWD_THREADS = 192;
+constexpr int FWD_SMEM = 1024 + TILE32K + 4 * TILE16K + 128;
+enum { FB_Q = 0, FB_KF = 1, FB_KE = 3, FB_VF = 5, FB_VE = 7, FB_SF = 9, FB_PF = 11, FB_PV = 13, FB_COUNT = 14 };
 
-__global__ void __launch_bounds__(128, 2) attn_fwd_kernel(const __grid_constant__ AttnP p) {
+__global__ void __launch_bounds__(FWD_THREADS, 2) attn_fwd_kernel(const __grid_constant__ AttnP p, const __grid_constant__ CUtensorMap tmQ,
+                                                                   const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = align1024(smem_raw);
-  uint8_t* sQ = sm; uint8_t* sK = sQ + 32768; uint8_t* sV = sK + 16384; uint8_t* sP = sV + 16384;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 32768);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2);
+  uint8_t* sQ = sm; uint8_t* sK = sQ + TILE32K; uint8_t* sV = sK + 2 * TILE16K;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sV + 2 * TILE16K);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + FB_COUNT);
 
-  const int tid = threadIdx.x, warp = tid >> 5;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int bh = blockIdx.y, b = bh / p.heads, h = bh - b * p.heads;
   const int q0 = blockIdx.x * 128;
-  const long long base = (long long)b * p.Tc * p.D + h * HD;
-  const float* Q = p.Q + base; const float* K = p.K + base; const float* V = p.V + base;
+  const int ntiles = cdiv(p.Tc, 64);
 
-  if (warp == 0) tmem_alloc(tmem_slot, 128);
-  if (tid == 32) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_fence_init(); }
-  load_kmajor<128, 128>(sQ, Q, p.D, q0, p.Tc, tid);
+  if (tid == 0) {
+    tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV);
+    for (int i = 0; i < FB_COUNT; ++i) mbar_init(&bars[i], (i == FB_PF || i == FB_PF + 1) ? 128 : 1);
+    mbar_fence_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 256);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem = *tmem_slot;
-  const uint32_t t_s = tmem + ((uint32_t)(warp * 32) << 16), t_o = t_s + 64;
-  constexpr uint32_t idesc_s = make_idesc(kFmtTF32, 128, 64, 0, 0);
-  constexpr uint32_t idesc_o = make_idesc(kFmtTF32, 128, 64, 0, 1);
+  const uint32_t tmem = *tmem_slot;                      // columns: S0 [0,64), S1 [64,128), O [128,192)
 
-  float o[64];
-#pragma unroll
-  for (int i = 0; i < 64; ++i) o[i] = 0.f;
-  float m_run = -INFINITY, l_run = 0.f;
-  const int ntiles = cdiv(p.Tc, 64);
-  for (int j = 0; j < ntiles; ++j) {
-    const int kv0 = j * 64;
-    load_kmajor<64, 128>(sK, K, p.D, kv0, p.Tc, tid);
-    load_mnmajor<64, 128>(sV, V, p.D, kv0, p.Tc, tid);
-    fence_proxy_async_smem();
-    tc_fence_before();
-    __syncthreads();
-    if (tid == 0) {
-      tc_fence_after();
-      mma_kk<128, 64>(tmem, smem_u32(sQ), smem_u32(sK), idesc_s, false);
-      mma_commit(&bars[0]);
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      mbar_arrive_expect_tx(&bars[FB_Q], TILE32K);
+      tma_tile(sQ, &tmQ, &bars[FB_Q], h * HD, q0, b, 128);
+      for (int j = 0; j < ntiles; ++j) {
+        const int st = j & 1; const uint32_t ph = (j >> 1) & 1;
+        mbar_wait(&bars[FB_KE + st], ph ^ 1);
+        mbar_arrive_expect_tx(&bars[FB_KF + st], TILE16K);
+        tma_tile(sK + st * TILE16K, &tmK, &bars[FB_KF + st], h * HD, j * 64, b, 64);
+        mbar_wait(&bars[FB_VE + st], ph ^ 1);
+        mbar_arrive_expect_tx(&bars[FB_VF + st], TILE16K);
+        tma_tile(sV + st * TILE16K, &tmV, &bars[FB_VF + st], h * HD, j * 64, b, 64);
+      }
     }
-    mbar_wait(&bars[0], j & 1);
-    tc_fence_after();
-    float s[64];
-    tmem_ld32(t_s, s);
-    tmem_ld32(t_s + 32, s + 32);
-    float mx = m_run;
-    const int nvalid = p.Tc - kv0;                    // keys beyond Tc are masked out
-#pragma unroll
-    for (int c = 0; c < 64; ++c) { if (c >= nvalid) s[c] = -INFINITY; mx = fmaxf(mx, s[c]); }
-    const float alpha = exp2f((m_run - mx) * kLog2e);
-    const float mb = mx * kLog2e;
-    float sum = 0.f;
-#pragma unroll
-    for (int c = 0; c < 64; ++c) { s[c] = exp2f(fmaf(s[c], kLog2e, -mb)); sum += s[c]; }
-    l_run = l_run * alpha + sum;
-    m_run = mx;
-    store_row32<128>(sP, tid, 0, s);
-    store_row32<128>(sP, tid, 1, s + 32);
-    fence_proxy_async_smem();
-    tc_fence_before();
-    __syncthreads();
-    if (tid == 0) {
-      tc_fence_after();
-      mma_kmn<128>(tmem + 64, smem_u32(sP), smem_u32(sV), idesc_o, false);
-      mma_commit(&bars[1]);
+  } else if (warp == 1) {
+    // ===== MMA issuer: S_0, S_1, PV_0, S_2, PV_1, ... (tcgen05.mma executes in issue order) =====
+    if (lane == 0) {
+      constexpr uint32_t idesc_s = make_idesc(kFmtTF32, 128, 64, 0, 0);
+      constexpr uint32_t idesc_o = make_idesc(kFmtTF32, 128, 64, 0, 1);
+      mbar_wait(&bars[FB_Q], 0);
+      auto issue_s = [&](int j) {
+        const int st = j & 1;
+        mbar_wait(&bars[FB_KF + st], (j >> 1) & 1);
+        tc_fence_after();
+        mma_kk<128, 64>(tmem + st * 64, smem_u32(sQ), smem_u32(sK + st * TILE16K), idesc_s);
+        mma_commit(&bars[FB_KE + st]);
+        mma_commit(&bars[FB_SF + st]);
+      };
+      issue_s(0);
+      for (int j = 0; j < ntiles; ++j) {
+        if (j + 1 < ntiles) issue_s(j + 1);
+        const int st = j & 1; const uint32_t ph = (j >> 1) & 1;
+        mbar_wait(&bars[FB_PF + st], ph);
+        mbar_wait(&bars[FB_VF + st], ph);
+        tc_fence_after();
+        mma_tmn(tmem + 128, tmem + st * 64, smem_u32(sV + st * TILE16K), idesc_o, j > 0);
+        mma_commit(&bars[FB_VE + st]);
+        mma_commit(&bars[FB_PV]);
+      }
     }
-    mbar_wait(&bars[1], j & 1);
+  } else {
+    // ===== row threads: thread owns query row q0 + 32 * quad + lane = TMEM lane 32 * quad + lane =====
+    const int quad = warp & 3;
+    const uint32_t t_row = tmem + ((uint32_t)(quad * 32) << 16);
+    float m_used = -INFINITY, l_run = 0.f;
+    for (int j = 0; j < ntiles; ++j) {
+      const int st = j & 1;
+      mbar_wait(&bars[FB_SF + st], (j >> 1) & 1);
+      tc_fence_after();
+      uint32_t s[64];
+      tmem_ld32_nowait(t_row + st * 64, s);
+      tmem_ld32_nowait(t_row + st * 64 + 32, s + 32);
+      tmem_wait_ld();
+      const int nvalid = p.Tc - j * 64;                  // keys beyond Tc are masked out
+      float mx = -INFINITY;
+#pragma unroll
+      for (int c = 0; c < 64; ++c) { if (c >= nvalid) s[c] = __float_as_uint(-INFINITY); mx = fmaxf(mx, __uint_as_float(s[c])); }
+      const float m_new = fmaxf(m_used, mx);
+      const bool grow = (m_new - m_used) * kLog2e > 8.f;
+      if (__any_sync(kFullMask, grow)) {
+        const float alpha = exp2f((m_used - m_new) * kLog2e);
+        if (j > 0) {                                     // rescale this warp's 32 rows of O once PV_{j-1} has landed
+          mbar_wait(&bars[FB_PV], (j - 1) & 1);
+          tc_fence_after();
+#pragma unroll
+          for (int half = 0; half < 2; ++half) {
+            uint32_t o[32];
+            tmem_ld32_nowait(t_row + 128 + half * 32, o);
+            tmem_wait_ld();
+#pragma unroll
+            for (int c = 0; c < 32; ++c) o[c] = __float_as_uint(__uint_as_float(o[c]) * alpha);
+            tmem_st32(t_row + 128 + half * 32, o);
+          }
+        }
+        l_run *= alpha;
+        m_used = m_new;
+      }
+      const float mb = m_used * kLog2e;
+      float sum = 0.f;
+#pragma unroll
+      for (int c = 0; c < 64; ++c) {
+        const float e = exp2f(fmaf(__uint_as_float(s[c]), kLog2e, -mb));
+        sum += e;
+        s[c] = __float_as_uint(to_tf32(e));
+      }
+      l_run += sum;
+      tmem_st32(t_row + st * 64, s);
+      tmem_st32(t_row + st * 64 + 32, s + 32);
+      tmem_wait_st();
+      tc_fence_before();
+      mbar_arrive(&bars[FB_PF + st]);
+    }
+    mbar_wait(&bars[FB_PV], (ntiles - 1) & 1);
     tc_fence_after();
-    float pv[32];
-    tmem_ld32(t_o, pv);
-#pragma unroll
-    for (int c = 0; c < 32; ++c) o[c] = fmaf(o[c], alpha, pv[c]);
-    tmem_ld32(t_o + 32, pv);
-#pragma unroll
-    for (int c = 0; c < 32; ++c) o[32 + c] = fmaf(o[32 + c], alpha, pv[c]);
-  }
-  const int q = q0 + tid;
-  if (q < p.Tc) {
+    const int q = q0 + quad * 32 + lane;
     const float inv = 1.f / l_run;
-    float* dst = p.O + base + (long long)q * p.D;
+    float* dst = p.O + ((long long)b * p.Tc + q) * p.D + h * HD;
 #pragma unroll
-    for (int c = 0; c < 16; ++c)
-    {
-      float4 t = make_float4(o[4 * c] * inv, o[4 * c + 1] * inv, o[4 * c + 2] * inv, o[4 * c + 3] * inv);
-      if (p.round_out) t = make_float4(to_tf32(t.x), to_tf32(t.y), to_tf32(t.z), to_tf32(t.w));
-      *reinterpret_cast<float4*>(dst + 4 * c) = t;
+    for (int half = 0; half < 2; ++half) {
+      uint32_t o[32];
+      tmem_ld32_nowait(t_row + 128 + half * 32, o);
+      tmem_wait_ld();
+      if (q < p.Tc) {
+#pragma unroll
+        for (int c = 0; c < 8; ++c) *reinterpret_cast<float4*>(dst + half * 32 + 4 * c) = out4(o + 4 * c, inv, p.round_out);
+      }
     }
-    if (p.LSE) p.LSE[(long long)bh * p.Tc + q] = m_run + logf(l_run);
+    if (q < p.Tc && p.LSE) p.LSE[(long long)bh * p.Tc + q] = m_used + logf(l_run);
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem, 128);
+  if (warp == 1) tmem_dealloc(tmem, 256);
 }
 
 // =====================================================================================================================
 // backward
 // =====================================================================================================================
-template <int ROWS, int NT> struct TileRegs { float4 v[ROWS * 16 / NT]; };
-
-template <int ROWS, int NT>
-__device__ __forceinline__ void ldg_tile(TileRegs<ROWS, NT>& t, const float* src, long long ld, int row0, int nrows_valid, int tid) {
-#pragma unroll
-  for (int i = 0; i < ROWS * 16 / NT; ++i) {
-    const int idx = tid + NT * i;
-    const int r = idx >> 4, c4 = idx & 15;
-    t.v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (row0 + r < nrows_valid) t.v[i] = *reinterpret_cast<const float4*>(src + (long long)(row0 + r) * ld + c4 * 4);
-  }
-}
-template <int ROWS, int NT, bool KMAJ, bool MNMAJ>
-__device__ __forceinline__ void sts_tile(const TileRegs<ROWS, NT>& t, uint8_t* dst_k, uint8_t* dst_mn, int tid) {
-#pragma unroll
-  for (int i = 0; i < ROWS * 16 / NT; ++i) {
-    const int idx = tid + NT * i;
-    const int r = idx >> 4, c4 = idx & 15;
-    const float4 v = make_float4(to_tf32(t.v[i].x), to_tf32(t.v[i].y), to_tf32(t.v[i].z), to_tf32(t.v[i].w));
-    if (KMAJ) *reinterpret_cast<float4*>(dst_k + (c4 >> 3) * (ROWS * 128) + sw128_kmajor_off(r, c4 & 7)) = v;
-    if (MNMAJ) *reinterpret_cast<float4*>(dst_mn + sw128_mnmajor_off(r, c4, 2)) = v;
-  }
-}
-
 // Dd[bh, t] = sum_d dO[b,t,h,d] * O[b,t,h,d]   (half a warp per (token, head))
 __global__ void __launch_bounds__(256) attn_dd_kernel(const float* __restrict__ dO, const float* __restrict__ O, float* __restrict__ Dd,
                                                       int B, int Tc, int D, int heads) {
@@ -256,198 +243,262 @@ __global__ void __launch_bounds__(256) attn_dd_kernel(const float* __restrict__ 
   if (gid < total && l16 == 0) Dd[(b * heads + h) * Tc + t] = s;
 }
 
-// ---- dQ: CTA = 128 query rows, loop over 64-key tiles -----------------------------------------------------------------
-constexpr int BQ_SMEM = 1024 + 32768 + 32768 + 16384 + 16384 + 16384 + 32768 + 64;
+constexpr int BWD_THREADS = 320;                       // producer, issuer, 8 row warps
 
-__global__ void __launch_bounds__(256, 1) attn_bwd_dq_kernel(const __grid_constant__ AttnP p) {
+// ---- dQ: CTA = 128 query rows, loop over 64-key tiles -----------------------------------------------------------------
+constexpr int BQ_STAGE = 3 * TILE16K;                  // K (K-major), V (K-major), K (MN-major)
+constexpr int BQ_SMEM = 1024 + 2 * TILE32K + 2 * BQ_STAGE + 128;
+enum { QB_QDO = 0, QB_KVF = 1, QB_KVE = 3, QB_KMF = 5, QB_KME = 7, QB_SF = 9, QB_DSF = 11, QB_DONE = 13, QB_COUNT = 14 };
+
+__global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dq_kernel(const __grid_constant__ AttnP p, const __grid_constant__ CUtensorMap tmQ,
+                                                                      const __grid_constant__ CUtensorMap tmdO, const __grid_constant__ CUtensorMap tmK,
+                                                                      const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmKmn) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = align1024(smem_raw);
-  uint8_t* sQ = sm; uint8_t* sdO = sQ + 32768; uint8_t* sK = sdO + 32768; uint8_t* sKmn = sK + 16384;
-  uint8_t* sV = sKmn + 16384; uint8_t* sdS = sV + 16384;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sdS + 32768);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2);
+  uint8_t* sQ = sm; uint8_t* sdO = sQ + TILE32K; uint8_t* stage0 = sdO + TILE32K;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(stage0 + 2 * BQ_STAGE);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + QB_COUNT);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int quad = warp & 3, half = warp >> 2;
-  const int r = quad * 32 + lane;
   const int bh = blockIdx.y, b = bh / p.heads, h = bh - b * p.heads;
   const int q0 = blockIdx.x * 128;
-  const long long base = (long long)b * p.Tc * p.D + h * HD;
-  const float* Q = p.Q + base; const float* K = p.K + base; const float* V = p.V + base; const float* dO = p.dO + base;
-
-  if (warp == 0) tmem_alloc(tmem_slot, 256);
-  if (tid == 32) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_fence_init(); }
-  load_kmajor<128, 256>(sQ, Q, p.D, q0, p.Tc, tid);
-  load_kmajor<128, 256>(sdO, dO, p.D, q0, p.Tc, tid);
-  const int q = q0 + r;
-  const float lse2 = q < p.Tc ? p.LSE[(long long)bh * p.Tc + q] * kLog2e : 0.f;
-  const float dd = q < p.Tc ? p.Dd[(long long)bh * p.Tc + q] : 0.f;
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem = *tmem_slot;
-  const uint32_t t_row = tmem + ((uint32_t)(quad * 32) << 16) + half * 32;
-  constexpr uint32_t idesc_kk = make_idesc(kFmtTF32, 128, 64, 0, 0);
-  constexpr uint32_t idesc_kmn = make_idesc(kFmtTF32, 128, 64, 0, 1);
-
   const int ntiles = cdiv(p.Tc, 64);
-  for (int j = 0; j < ntiles; ++j) {
-    const int kv0 = j * 64;
-    TileRegs<64, 256> rk, rv;
-    ldg_tile<64, 256>(rk, K, p.D, kv0, p.Tc, tid);
-    ldg_tile<64, 256>(rv, V, p.D, kv0, p.Tc, tid);
-    if (j > 0) { mbar_wait(&bars[1], (j - 1) & 1); tc_fence_after(); }     // the dQ MMAs that read sKmn / sdS have completed
-    sts_tile<64, 256, true, true>(rk, sK, sKmn, tid);
-    sts_tile<64, 256, true, false>(rv, sV, nullptr, tid);
-    fence_proxy_async_smem();
-    tc_fence_before();
-    __syncthreads();
-    if (tid == 0) {
-      tc_fence_after();
-      mma_kk<128, 64>(tmem, smem_u32(sQ), smem_u32(sK), idesc_kk, false);           // S  = Q K^T
-      mma_kk<128, 64>(tmem + 64, smem_u32(sdO), smem_u32(sV), idesc_kk, false);     // dP = dO V^T
-      mma_commit(&bars[0]);
-    }
-    mbar_wait(&bars[0], j & 1);
-    tc_fence_after();
-    float s[32], dp[32];
-    tmem_ld32(t_row, s);
-    tmem_ld32(t_row + 64, dp);
-#pragma unroll
-    for (int c = 0; c < 32; ++c) s[c] = exp2f(fmaf(s[c], kLog2e, -lse2)) * (dp[c] - dd);     // dS = P * (dP - D)
-    store_row32<128>(sdS, r, half, s);
-    fence_proxy_async_smem();
-    tc_fence_before();
-    __syncthreads();
-    if (tid == 0) {
-      tc_fence_after();
-      mma_kmn<128>(tmem + 128, smem_u32(sdS), smem_u32(sKmn), idesc_kmn, j > 0);      // dQ += dS K
-      mma_commit(&bars[1]);
-    }
+
+  if (tid == 0) {
+    tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmdO); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); tma_prefetch_desc(&tmKmn);
+    for (int i = 0; i < QB_COUNT; ++i) mbar_init(&bars[i], (i == QB_DSF || i == QB_DSF + 1) ? 256 : 1);
+    mbar_fence_init();
   }
-  mbar_wait(&bars[1], (ntiles - 1) & 1);
+  if (warp == 1) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
   tc_fence_after();
-  float acc[32];
-  tmem_ld32(t_row + 128, acc);
-  if (q < p.Tc) {
-    float* dst = p.dQ + base + (long long)q * p.D + half * 32;
+  const uint32_t tmem = *tmem_slot;                      // columns: S0 0, S1 64, dP0 128, dP1 192, dQ 256
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_arrive_expect_tx(&bars[QB_QDO], 2 * TILE32K);
+      tma_tile(sQ, &tmQ, &bars[QB_QDO], h * HD, q0, b, 128);
+      tma_tile(sdO, &tmdO, &bars[QB_QDO], h * HD, q0, b, 128);
+      for (int j = 0; j < ntiles; ++j) {
+        const int st = j & 1; const uint32_t ph = (j >> 1) & 1;
+        uint8_t* sg = stage0 + st * BQ_STAGE;
+        mbar_wait(&bars[QB_KVE + st], ph ^ 1);
+        mbar_arrive_expect_tx(&bars[QB_KVF + st], 2 * TILE16K);
+        tma_tile(sg, &tmK, &bars[QB_KVF + st], h * HD, j * 64, b, 64);
+        tma_tile(sg + TILE16K, &tmV, &bars[QB_KVF + st], h * HD, j * 64, b, 64);
+        mbar_wait(&bars[QB_KME + st], ph ^ 1);
+        mbar_arrive_expect_tx(&bars[QB_KMF + st], TILE16K);
+        tma_tile(sg + 2 * TILE16K, &tmKmn, &bars[QB_KMF + st], h * HD, j * 64, b, 64);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc_kk = make_idesc(kFmtTF32, 128, 64, 0, 0);
+      constexpr uint32_t idesc_kmn = make_idesc(kFmtTF32, 128, 64, 0, 1);
+      mbar_wait(&bars[QB_QDO], 0);
+      auto issue_s = [&](int j) {
+        const int st = j & 1;
+        const uint32_t sg = smem_u32(stage0 + st * BQ_STAGE);
+        mbar_wait(&bars[QB_KVF + st], (j >> 1) & 1);
+        tc_fence_after();
+        mma_kk<128, 64>(tmem + st * 64, smem_u32(sQ), sg, idesc_kk);                     // S  = Q K^T
+        mma_kk<128, 64>(tmem + 128 + st * 64, smem_u32(sdO), sg + TILE16K, idesc_kk);    // dP = dO V^T
+        mma_commit(&bars[QB_KVE + st]);
+        mma_commit(&bars[QB_SF + st]);
+      };
+      issue_s(0);
+      for (int j = 0; j < ntiles; ++j) {
+        if (j + 1 < ntiles) issue_s(j + 1);
+        const int st = j & 1; const uint32_t ph = (j >> 1) & 1;
+        mbar_wait(&bars[QB_DSF + st], ph);
+        mbar_wait(&bars[QB_KMF + st], ph);
+        tc_fence_after();
+        mma_tmn(tmem + 256, tmem + 128 + st * 64, smem_u32(stage0 + st * BQ_STAGE + 2 * TILE16K), idesc_kmn, j > 0);   // dQ += dS K
+        mma_commit(&bars[QB_KME + st]);
+      }
+      mma_commit(&bars[QB_DONE]);
+    }
+  } else {
+    const int quad = warp & 3, half = (warp - 2) >> 2;
+    const int q = q0 + quad * 32 + lane;
+    const uint32_t t_row = tmem + ((uint32_t)(quad * 32) << 16) + half * 32;
+    const float lse2 = q < p.Tc ? p.LSE[(long long)bh * p.Tc + q] * kLog2e : 0.f;
+    const float dd = q < p.Tc ? p.Dd[(long long)bh * p.Tc + q] : 0.f;
+    for (int j = 0; j < ntiles; ++j) {
+      const int st = j & 1;
+      mbar_wait(&bars[QB_SF + st], (j >> 1) & 1);
+      tc_fence_after();
+      uint32_t s[32], dp[32];
+      tmem_ld32_nowait(t_row + st * 64, s);
+      tmem_ld32_nowait(t_row + 128 + st * 64, dp);
+      tmem_wait_ld();
 #pragma unroll
-    for (int c = 0; c < 8; ++c)
-    {
-      float4 t = make_float4(acc[4 * c] * p.dq_scale, acc[4 * c + 1] * p.dq_scale, acc[4 * c + 2] * p.dq_scale, acc[4 * c + 3] * p.dq_scale);
-      if (p.round_out) t = make_float4(to_tf32(t.x), to_tf32(t.y), to_tf32(t.z), to_tf32(t.w));
-      *reinterpret_cast<float4*>(dst + 4 * c) = t;
+      for (int c = 0; c < 32; ++c)                                                       // dS = P * (dP - D)
+        dp[c] = __float_as_uint(to_tf32(exp2f(fmaf(__uint_as_float(s[c]), kLog2e, -lse2)) * (__uint_as_float(dp[c]) - dd)));
+      tmem_st32(t_row + 128 + st * 64, dp);
+      tmem_wait_st();
+      tc_fence_before();
+      mbar_arrive(&bars[QB_DSF + st]);
+    }
+    mbar_wait(&bars[QB_DONE], 0);
+    tc_fence_after();
+    uint32_t acc[32];
+    tmem_ld32_nowait(t_row + 256, acc);
+    tmem_wait_ld();
+    if (q < p.Tc) {
+      float* dst = p.dQ + ((long long)b * p.Tc + q) * p.D + h * HD + half * 32;
+#pragma unroll
+      for (int c = 0; c < 8; ++c) *reinterpret_cast<float4*>(dst + 4 * c) = out4(acc + 4 * c, p.dq_scale, p.round_out);
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem, 256);
+  if (warp == 1) tmem_dealloc(tmem, 512);
 }
 
 // ---- dK, dV: CTA = 128 key rows, loop over 64-query tiles; works on S^T ------------------------------------------------
-constexpr int BK_SMEM = 1024 + 2 * 32768 + 4 * 16384 + 2 * 32768 + 512 + 64;
+constexpr int BK_STAGE = 4 * TILE16K;                  // Q (K-major), dO (K-major), Q (MN-major), dO (MN-major)
+constexpr int BK_SMEM = 1024 + 2 * TILE32K + 2 * BK_STAGE + 128;
+enum { KB_KV = 0, KB_QF = 1, KB_QE = 3, KB_MF = 5, KB_ME = 7, KB_SF = 9, KB_DSF = 11, KB_DONE = 13, KB_COUNT = 14 };
 
-__global__ void __launch_bounds__(256, 1) attn_bwd_dkv_kernel(const __grid_constant__ AttnP p) {
+__global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dkv_kernel(const __grid_constant__ AttnP p, const __grid_constant__ CUtensorMap tmK,
+                                                                       const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmQ,
+                                                                       const __grid_constant__ CUtensorMap tmdO, const __grid_constant__ CUtensorMap tmQmn,
+                                                                       const __grid_constant__ CUtensorMap tmdOmn) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = align1024(smem_raw);
-  uint8_t* sK = sm; uint8_t* sV = sK + 32768; uint8_t* sQ = sV + 32768; uint8_t* sQmn = sQ + 16384;
-  uint8_t* sdO = sQmn + 16384; uint8_t* sdOmn = sdO + 16384; uint8_t* sPt = sdOmn + 16384; uint8_t* sdSt = sPt + 32768;
-  float* s_lse = reinterpret_cast<float*>(sdSt + 32768); float* s_dd = s_lse + 64;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_dd + 64);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2);
+  uint8_t* sK = sm; uint8_t* sV = sK + TILE32K; uint8_t* stage0 = sV + TILE32K;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(stage0 + 2 * BK_STAGE);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + KB_COUNT);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int quad = warp & 3, half = warp >> 2;
-  const int r = quad * 32 + lane;
   const int bh = blockIdx.y, b = bh / p.heads, h = bh - b * p.heads;
   const int kv0 = blockIdx.x * 128;
-  const long long base = (long long)b * p.Tc * p.D + h * HD;
-  const float* Q = p.Q + base; const float* K = p.K + base; const float* V = p.V + base; const float* dO = p.dO + base;
-  const float* LSE = p.LSE + (long long)bh * p.Tc; const float* Dd = p.Dd + (long long)bh * p.Tc;
-
-  if (warp == 0) tmem_alloc(tmem_slot, 256);
-  if (tid == 32) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_fence_init(); }
-  load_kmajor<128, 256>(sK, K, p.D, kv0, p.Tc, tid);
-  load_kmajor<128, 256>(sV, V, p.D, kv0, p.Tc, tid);
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem = *tmem_slot;
-  const uint32_t t_row = tmem + ((uint32_t)(quad * 32) << 16) + half * 32;
-  constexpr uint32_t idesc_kk = make_idesc(kFmtTF32, 128, 64, 0, 0);
-  constexpr uint32_t idesc_kmn = make_idesc(kFmtTF32, 128, 64, 0, 1);
-
   const int ntiles = cdiv(p.Tc, 64);
-  for (int i = 0; i < ntiles; ++i) {
-    const int q0 = i * 64;
-    TileRegs<64, 256> rq, rdo;
-    ldg_tile<64, 256>(rq, Q, p.D, q0, p.Tc, tid);
-    ldg_tile<64, 256>(rdo, dO, p.D, q0, p.Tc, tid);
-    float aux = 0.f;
-    if (tid < 128) { const int qq = q0 + (tid & 63); if (qq < p.Tc) aux = tid < 64 ? LSE[qq] * kLog2e : Dd[qq]; }
-    if (i > 0) { mbar_wait(&bars[1], (i - 1) & 1); tc_fence_after(); }     // dV / dK MMAs of the previous tile have completed
-    sts_tile<64, 256, true, true>(rq, sQ, sQmn, tid);
-    sts_tile<64, 256, true, true>(rdo, sdO, sdOmn, tid);
-    if (tid < 128) s_lse[tid] = aux;                                       // s_lse[0..63], s_dd = s_lse + 64
-    fence_proxy_async_smem();
-    tc_fence_before();
-    __syncthreads();
-    if (tid == 0) {
-      tc_fence_after();
-      mma_kk<128, 64>(tmem, smem_u32(sK), smem_u32(sQ), idesc_kk, false);           // S^T  = K Q^T
-      mma_kk<128, 64>(tmem + 64, smem_u32(sV), smem_u32(sdO), idesc_kk, false);     // dP^T = V dO^T
-      mma_commit(&bars[0]);
-    }
-    mbar_wait(&bars[0], i & 1);
-    tc_fence_after();
-    float s[32], dp[32];
-    tmem_ld32(t_row, s);
-    tmem_ld32(t_row + 64, dp);
-#pragma unroll
-    for (int c = 0; c < 32; ++c) {
-      const float pr = exp2f(fmaf(s[c], kLog2e, -s_lse[half * 32 + c]));
-      dp[c] = pr * (dp[c] - s_dd[half * 32 + c]);
-      s[c] = pr;
-    }
-    store_row32<128>(sPt, r, half, s);
-    store_row32<128>(sdSt, r, half, dp);
-    fence_proxy_async_smem();
-    tc_fence_before();
-    __syncthreads();
-    if (tid == 0) {
-      tc_fence_after();
-      mma_kmn<128>(tmem + 128, smem_u32(sPt), smem_u32(sdOmn), idesc_kmn, i > 0);     // dV += P^T dO
-      mma_kmn<128>(tmem + 192, smem_u32(sdSt), smem_u32(sQmn), idesc_kmn, i > 0);     // dK += dS^T Q
-      mma_commit(&bars[1]);
-    }
+
+  if (tid == 0) {
+    tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmdO); tma_prefetch_desc(&tmQmn); tma_prefetch_desc(&tmdOmn);
+    for (int i = 0; i < KB_COUNT; ++i) mbar_init(&bars[i], (i == KB_DSF || i == KB_DSF + 1) ? 256 : 1);
+    mbar_fence_init();
   }
-  mbar_wait(&bars[1], (ntiles - 1) & 1);
+  if (warp == 1) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
   tc_fence_after();
-  float acc[32];
-  const int kv = kv0 + r;
-  tmem_ld32(t_row + 128, acc);
-  if (kv < p.Tc) {
-    float* dst = p.dV + base + (long long)kv * p.D + half * 32;
-#pragma unroll
-    for (int c = 0; c < 8; ++c) {
-      float4 t = make_float4(acc[4 * c], acc[4 * c + 1], acc[4 * c + 2], acc[4 * c + 3]);
-      if (p.round_out) t = make_float4(to_tf32(t.x), to_tf32(t.y), to_tf32(t.z), to_tf32(t.w));
-      *reinterpret_cast<float4*>(dst + 4 * c) = t;
+  const uint32_t tmem = *tmem_slot;                      // columns: S^T0 0, S^T1 64, dP^T0 128, dP^T1 192, dV 256, dK 320
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_arrive_expect_tx(&bars[KB_KV], 2 * TILE32K);
+      tma_tile(sK, &tmK, &bars[KB_KV], h * HD, kv0, b, 128);
+      tma_tile(sV, &tmV, &bars[KB_KV], h * HD, kv0, b, 128);
+      for (int i = 0; i < ntiles; ++i) {
+        const int st = i & 1; const uint32_t ph = (i >> 1) & 1;
+        uint8_t* sg = stage0 + st * BK_STAGE;
+        mbar_wait(&bars[KB_QE + st], ph ^ 1);
+        mbar_arrive_expect_tx(&bars[KB_QF + st], 2 * TILE16K);
+        tma_tile(sg, &tmQ, &bars[KB_QF + st], h * HD, i * 64, b, 64);
+        tma_tile(sg + TILE16K, &tmdO, &bars[KB_QF + st], h * HD, i * 64, b, 64);
+        mbar_wait(&bars[KB_ME + st], ph ^ 1);
+        mbar_arrive_expect_tx(&bars[KB_MF + st], 2 * TILE16K);
+        tma_tile(sg + 2 * TILE16K, &tmQmn, &bars[KB_MF + st], h * HD, i * 64, b, 64);
+        tma_tile(sg + 3 * TILE16K, &tmdOmn, &bars[KB_MF + st], h * HD, i * 64, b, 64);
+      }
     }
-  }
-  tmem_ld32(t_row + 192, acc);
-  if (kv < p.Tc) {
-    float* dst = p.dK + base + (long long)kv * p.D + half * 32;
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc_kk = make_idesc(kFmtTF32, 128, 64, 0, 0);
+      constexpr uint32_t idesc_kmn = make_idesc(kFmtTF32, 128, 64, 0, 1);
+      mbar_wait(&bars[KB_KV], 0);
+      auto issue_s = [&](int i) {
+        const int st = i & 1;
+        const uint32_t sg = smem_u32(stage0 + st * BK_STAGE);
+        mbar_wait(&bars[KB_QF + st], (i >> 1) & 1);
+        tc_fence_after();
+        mma_kk<128, 64>(tmem + st * 64, smem_u32(sK), sg, idesc_kk);                     // S^T  = K Q^T
+        mma_kk<128, 64>(tmem + 128 + st * 64, smem_u32(sV), sg + TILE16K, idesc_kk);     // dP^T = V dO^T
+        mma_commit(&bars[KB_QE + st]);
+        mma_commit(&bars[KB_SF + st]);
+      };
+      issue_s(0);
+      for (int i = 0; i < ntiles; ++i) {
+        if (i + 1 < ntiles) issue_s(i + 1);
+        const int st = i & 1; const uint32_t ph = (i >> 1) & 1;
+        const uint32_t sg = smem_u32(stage0 + st * BK_STAGE);
+        mbar_wait(&bars[KB_DSF + st], ph);
+        mbar_wait(&bars[KB_MF + st], ph);
+        tc_fence_after();
+        mma_tmn(tmem + 256, tmem + st * 64, sg + 3 * TILE16K, idesc_kmn, i > 0);         // dV += P^T dO
+        mma_tmn(tmem + 320, tmem + 128 + st * 64, sg + 2 * TILE16K, idesc_kmn, i > 0);   // dK += dS^T Q
+        mma_commit(&bars[KB_ME + st]);
+      }
+      mma_commit(&bars[KB_DONE]);
+    }
+  } else {
+    const int quad = warp & 3, half = (warp - 2) >> 2;
+    const int kv = kv0 + quad * 32 + lane;
+    const uint32_t t_row = tmem + ((uint32_t)(quad * 32) << 16) + half * 32;
+    const float* LSE = p.LSE + (long long)bh * p.Tc; const float* Dd = p.Dd + (long long)bh * p.Tc;
+    const bool vec_ok = (p.Tc & 3) == 0;
+    for (int i = 0; i < ntiles; ++i) {
+      const int st = i & 1;
+      const int qc = i * 64 + half * 32;                 // this thread's 32 tile columns are queries qc .. qc + 31 (warp-uniform addresses)
+      float lse2[32], dd[32];
+      if (vec_ok && qc + 32 <= p.Tc) {
 #pragma unroll
-    for (int c = 0; c < 8; ++c) {
-      float4 t = make_float4(acc[4 * c], acc[4 * c + 1], acc[4 * c + 2], acc[4 * c + 3]);
-      if (p.round_out) t = make_float4(to_tf32(t.x), to_tf32(t.y), to_tf32(t.z), to_tf32(t.w));
-      *reinterpret_cast<float4*>(dst + 4 * c) = t;
+        for (int c = 0; c < 8; ++c) {
+          const float4 a = __ldg(reinterpret_cast<const float4*>(LSE + qc) + c), d4 = __ldg(reinterpret_cast<const float4*>(Dd + qc) + c);
+          lse2[4 * c] = a.x * kLog2e; lse2[4 * c + 1] = a.y * kLog2e; lse2[4 * c + 2] = a.z * kLog2e; lse2[4 * c + 3] = a.w * kLog2e;
+          dd[4 * c] = d4.x; dd[4 * c + 1] = d4.y; dd[4 * c + 2] = d4.z; dd[4 * c + 3] = d4.w;
+        }
+      } else {
+#pragma unroll
+        for (int c = 0; c < 32; ++c) { const bool ok = qc + c < p.Tc; lse2[c] = ok ? __ldg(LSE + qc + c) * kLog2e : 0.f; dd[c] = ok ? __ldg(Dd + qc + c) : 0.f; }
+      }
+      mbar_wait(&bars[KB_SF + st], (i >> 1) & 1);
+      tc_fence_after();
+      uint32_t s[32], dp[32];
+      tmem_ld32_nowait(t_row + st * 64, s);
+      tmem_ld32_nowait(t_row + 128 + st * 64, dp);
+      tmem_wait_ld();
+#pragma unroll
+      for (int c = 0; c < 32; ++c) {
+        const float pr = exp2f(fmaf(__uint_as_float(s[c]), kLog2e, -lse2[c]));
+        dp[c] = __float_as_uint(to_tf32(pr * (__uint_as_float(dp[c]) - dd[c])));
+        s[c] = __float_as_uint(to_tf32(pr));
+      }
+      tmem_st32(t_row + st * 64, s);
+      tmem_st32(t_row + 128 + st * 64, dp);
+      tmem_wait_st();
+      tc_fence_before();
+      mbar_arrive(&bars[KB_DSF + st]);
+    }
+    mbar_wait(&bars[KB_DONE], 0);
+    tc_fence_after();
+    uint32_t acc[32];
+    tmem_ld32_nowait(t_row + 256, acc);
+    tmem_wait_ld();
+    if (kv < p.Tc) {
+      float* dst = p.dV + ((long long)b * p.Tc + kv) * p.D + h * HD + half * 32;
+#pragma unroll
+      for (int c = 0; c < 8; ++c) *reinterpret_cast<float4*>(dst + 4 * c) = out4(acc + 4 * c, 1.f, p.round_out);
+    }
+    tmem_ld32_nowait(t_row + 320, acc);
+    tmem_wait_ld();
+    if (kv < p.Tc) {
+      float* dst = p.dK + ((long long)b * p.Tc + kv) * p.D + h * HD + half * 32;
+#pragma unroll
+      for (int c = 0; c < 8; ++c) *reinterpret_cast<float4*>(dst + 4 * c) = out4(acc + 4 * c, 1.f, p.round_out);
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem, 256);
+  if (warp == 1) tmem_dealloc(tmem, 512);
+}
+
+__global__ void __launch_bounds__(256) round_tf32_inplace_kernel(float* x, long long n) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) x[i] = to_tf32(x[i]);
 }
 
 cudaError_t configure_once() {
@@ -460,10 +511,20 @@ cudaError_t configure_once() {
   return cudaSuccess;
 }
 
+// tensor maps over one [B, Tc, D] tensor: K-major boxes (32 floats x rows, 128B swizzle) or MN-major boxes (32-byte-atom swizzle)
+bool tmap_kmajor(CUtensorMap* tm, const float* x, const AttnP& p, int B, int rows) {
+  return make_tmap_3d(tm, x, p.D, p.Tc, B, p.D, (long long)p.Tc * p.D, rows, CU_TENSOR_MAP_SWIZZLE_128B);
+}
+bool tmap_mnmajor(CUtensorMap* tm, const float* x, const AttnP& p, int B) {
+  return make_tmap_3d(tm, x, p.D, p.Tc, B, p.D, (long long)p.Tc * p.D, 64, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B);
+}
+
 cudaError_t run_fwd(const AttnP& p, int B, cudaStream_t s) {
   CVT_CUDA(configure_once());
   if (p.D % 4 != 0 || p.D != p.heads * HD) { set_error("attention_tc: D must equal heads * 64"); return cudaErrorInvalidValue; }
-  attn_fwd_kernel<<<dim3(cdiv(p.Tc, 128), B * p.heads), 128, FWD_SMEM, s>>>(p);
+  CUtensorMap tmQ, tmK, tmV;
+  if (!tmap_kmajor(&tmQ, p.Q, p, B, 128) || !tmap_kmajor(&tmK, p.K, p, B, 64) || !tmap_mnmajor(&tmV, p.V, p, B)) return cudaErrorInvalidValue;
+  attn_fwd_kernel<<<dim3(cdiv(p.Tc, 128), B * p.heads), FWD_THREADS, FWD_SMEM, s>>>(p, tmQ, tmK, tmV);
   CVT_LAUNCH_CHECK();
   return cudaSuccess;
 }
@@ -472,9 +533,16 @@ cudaError_t run_bwd(const AttnP& p, float* Dd, int B, cudaStream_t s) {
   const long long groups = (long long)B * p.Tc * p.heads;
   attn_dd_kernel<<<(unsigned)cdivl(groups * 16, 256), 256, 0, s>>>(p.dO, p.O, Dd, B, p.Tc, p.D, p.heads);
   CVT_LAUNCH_CHECK();
-  attn_bwd_dkv_kernel<<<dim3(cdiv(p.Tc, 128), B * p.heads), 256, BK_SMEM, s>>>(p);
+  CUtensorMap q128, do128, k128, v128, q64, do64, k64, v64, qmn, domn, kmn;
+  if (!tmap_kmajor(&q128, p.Q, p, B, 128) || !tmap_kmajor(&do128, p.dO, p, B, 128) || !tmap_kmajor(&k128, p.K, p, B, 128) ||
+      !tmap_kmajor(&v128, p.V, p, B, 128) || !tmap_kmajor(&q64, p.Q, p, B, 64) || !tmap_kmajor(&do64, p.dO, p, B, 64) ||
+      !tmap_kmajor(&k64, p.K, p, B, 64) || !tmap_kmajor(&v64, p.V, p, B, 64) || !tmap_mnmajor(&qmn, p.Q, p, B) ||
+      !tmap_mnmajor(&domn, p.dO, p, B) || !tmap_mnmajor(&kmn, p.K, p, B))
+    return cudaErrorInvalidValue;
+  const dim3 grid(cdiv(p.Tc, 128), B * p.heads);
+  attn_bwd_dkv_kernel<<<grid, BWD_THREADS, BK_SMEM, s>>>(p, k128, v128, q64, do64, qmn, domn);
   CVT_LAUNCH_CHECK();
-  attn_bwd_dq_kernel<<<dim3(cdiv(p.Tc, 128), B * p.heads), 256, BQ_SMEM, s>>>(p);
+  attn_bwd_dq_kernel<<<grid, BWD_THREADS, BQ_SMEM, s>>>(p, q128, do128, k64, v64, kmn);
   CVT_LAUNCH_CHECK();
   return cudaSuccess;
 }
@@ -505,6 +573,7 @@ cudaError_t attention_backward_tc(Model* m, int si, int B, const float* dO, floa
 
 // diagnostics (tests/test_gpu_attention.py): the tcgen05 attention kernels on host arrays, device 0.
 // Q (pre-scaled), K, V, dO: [B, Tc, heads*64]; O/dQ/dK/dV same shape; LSE [B*heads, Tc].  dO == NULL: forward only.
+// Inputs are rounded to TF32 on the device first (in the model their producers do that in the GEMM epilogue).
 extern "C" CVT_API int cvt_debug_attention(int B, int Tc, int heads, const float* Q, const float* K, const float* V, const float* dO,
                                            float* O, float* LSE, float* dQ, float* dK, float* dV) {
   using namespace cvt;
@@ -519,12 +588,14 @@ extern "C" CVT_API int cvt_debug_attention(int B, int Tc, int heads, const float
   auto fail = [&](cudaError_t err) { if (err != cudaSuccess) set_error(std::string("cvt_debug_attention: ") + cudaGetErrorString(err)); cudaFree(buf); return (int)CVT_ERR_CUDA; };
   if ((e = cudaMemcpy(dQ_, Q, n * 4, cudaMemcpyHostToDevice)) != cudaSuccess || (e = cudaMemcpy(dK_, K, n * 4, cudaMemcpyHostToDevice)) != cudaSuccess ||
       (e = cudaMemcpy(dV_, V, n * 4, cudaMemcpyHostToDevice)) != cudaSuccess) return fail(e);
+  if (dO && (e = cudaMemcpy(dO_, dO, n * 4, cudaMemcpyHostToDevice)) != cudaSuccess) return fail(e);
+  round_tf32_inplace_kernel<<<592, 256>>>(buf, (long long)(dO ? 4 : 3) * n);
+  if ((e = cudaGetLastError()) != cudaSuccess) return fail(e);
   AttnP p{};
   p.Q = dQ_; p.K = dK_; p.V = dV_; p.O = dOut; p.LSE = dL; p.Tc = Tc; p.D = D; p.heads = heads; p.dq_scale = 0.125f;
   if ((e = run_fwd(p, B, 0)) != cudaSuccess) return fail(e);
   if (dO) {
     if (!dQ || !dK || !dV) { cudaFree(buf); set_error("cvt_debug_attention: backward needs dQ, dK, dV"); return CVT_ERR_INVALID; }
-    if ((e = cudaMemcpy(dO_, dO, n * 4, cudaMemcpyHostToDevice)) != cudaSuccess) return fail(e);
     p.dO = dO_; p.Dd = dD; p.dQ = gQ; p.dK = gK; p.dV = gV;
     if ((e = run_bwd(p, dD, B, 0)) != cudaSuccess) return fail(e);
   }

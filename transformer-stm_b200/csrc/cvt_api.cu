@@ -556,7 +556,8 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
     const bool bn = g.method == CVT_PROJ_DW_BN;
     CVT_CUDA(launch_bn_fold(F + f.Wc, F + f.bc, bn ? a.bn_scale : nullptr, bn ? a.bn_shift : nullptr, 0.125f, D, F + f.Wft, F + f.bf, s));
     GemmP p; p.M = R; p.N = D; p.K = D; p.A = a.conv; p.lda = D; p.B = F + f.Wft; p.ldb = D; p.b_mode = B_NK; p.C = a.qkv2; p.ldc = D;
-    p.bias = F + f.bf; p.epi = EPI_BIAS; p.batch = 3; p.a_bs0 = RD; p.b_bs0 = (long long)D * D; p.c_bs0 = RD; p.bias_bs = D;
+    p.bias = F + f.bf; p.epi = EPI_BIAS | EPI_ROUND; p.batch = 3;
+    p.batch = 3; p.a_bs0 = RD; p.b_bs0 = (long long)D * D; p.c_bs0 = RD; p.bias_bs = D;
     CVT_CUDA(run_gemm(m, p, s));
     if (bn && g.has_cls) CVT_CUDA(launch_cls_fix(a.xn, RD, F + f.Wc, F + f.bc, 0.125f, B, g.Tc, D, a.qkv2, s));   // cls rows skip BatchNorm
   } else
@@ -569,6 +570,7 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
     GemmP q = dense_fwd(a.qkv1, D, R, D, P + w.mw, D, P + w.mb, a.qkv2, D);
     q.batch = 3; q.a_bs0 = RD; q.b_bs0 = (long long)D * D; q.c_bs0 = RD; q.bias_bs = D;
     q.epi |= EPI_ALPHA0; q.alpha0 = 0.125f;
+    if (c.precision != CVT_PREC_FP32) q.epi |= EPI_ROUND;
     CVT_CUDA(run_gemm(m, q, s));
   }
   prof_mark(s, kStageNames[si][3]);
@@ -738,7 +740,7 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
     const float* dA2 = m->gD;
     if (drop) { CVT_CUDA(launch_mask_scale(m->gM, m->gD, a.mask_proj, keep_scale, RD, s, 1)); dA2 = m->gM; }
     CVT_CUDA(wgrad_bias(m, a.attn_o, D, D, dA2, D, D, R, G + f.Zo, G + w.prb, 1, 0, 0, s));        // Zo = o^T dA2, so = colsum dA2 = dbproj
-    CVT_CUDA(run_gemm(m, dense_dgrad(dA2, D, R, D, F + f.Wo, D, m->gE, D), s));                      // dO = dA2 Wo^T
+    { GemmP q = dense_dgrad(dA2, D, R, D, F + f.Wo, D, m->gE, D); q.epi |= EPI_ROUND; CVT_CUDA(run_gemm(m, q, s)); }   // dO = dA2 Wo^T (TMA operand of attention backward)
     prof_mark(s, kStageNames[si][8]);
     CVT_CUDA(attention_backward(m, si, B, m->gE, m->gQ, s));                                        // gQ = [dQ(pre-scale), dK, dV]
     prof_mark(s, kStageNames[si][9]);
@@ -772,7 +774,7 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
   CVT_CUDA(wgrad_bias(m, a.a1, D, D, dA2, D, D, R, G + w.prw, G + w.prb, 1, 0, 0, s));
   CVT_CUDA(run_gemm(m, dense_dgrad(dA2, D, R, D, P + w.prw, D, m->gC, D), s));              // dA1
   CVT_CUDA(wgrad_bias(m, a.attn_o, D, D, m->gC, D, D, R, G + w.ow, G + w.ob, 1, 0, 0, s));
-  CVT_CUDA(run_gemm(m, dense_dgrad(m->gC, D, R, D, P + w.ow, D, m->gE, D), s));             // dO
+  { GemmP q = dense_dgrad(m->gC, D, R, D, P + w.ow, D, m->gE, D); if (c.precision != CVT_PREC_FP32) q.epi |= EPI_ROUND; CVT_CUDA(run_gemm(m, q, s)); }   // dO
   prof_mark(s, kStageNames[si][8]);
   CVT_CUDA(attention_backward(m, si, B, m->gE, m->gQ, s));                                  // gQ = [dQ(pre-scale), dK, dV]
   prof_mark(s, kStageNames[si][9]);

@@ -53,7 +53,7 @@ __global__ void cls_fix_kernel(const float* __restrict__ xn, long long bs, const
   float a = bc[z * D + j];
 #pragma unroll 16
   for (int i = 0; i < D; ++i) a = fmaf(srow[i], W[(long long)i * D + j], a);
-  q[row + j] = (z == 0 ? alpha0 : 1.f) * a;
+  q[row + j] = round_tf32((z == 0 ? alpha0 : 1.f) * a);     // attention operand (TMA): rounded by its producer
 }
 
 // Zcls[z][c][j] = sum_b xn[b, cls, c] dq[z][b, cls, j]  and  scls[z][j] = sum_b dq[z][b, cls, j]   (fp32; the cls row is the only row
