@@ -41,22 +41,35 @@ struct AttnP {
   int round_out;                                       // store O / dQ / dK / dV rounded to TF32 (they only feed tensor-core GEMMs)
 };
 
+// Descriptors are built once per operand tile; each MMA only adds a compile-time constant to the 14-bit start-address field
+// (the single issuing thread's instruction stream is what bounds the MMA rate of these small tiles).
+__device__ __forceinline__ uint64_t desc_add(uint64_t d, uint32_t bytes) { return d + (uint64_t)(bytes >> 4); }
+__device__ __forceinline__ uint64_t desc_kmajor(uint32_t saddr) { return make_smem_desc(saddr, 16, 1024); }
+__device__ __forceinline__ uint64_t desc_mnmajor(uint32_t saddr) { return make_smem_desc(saddr, 8192, 512, kLayoutSw128Base32); }
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.b32 %0, 1, 0, p;\n\t"
+      "}"
+      : "=r"(pred));
+  return pred != 0;
+}
 // D[tmem] = A * B with A K-major [128 x 64] (two boxes of A_ROWS rows) and B K-major [B_ROWS x 64]; contraction = 64 floats
 template <int A_ROWS, int B_ROWS>
-__device__ __forceinline__ void mma_kk(uint32_t tmem_d, uint32_t a0, uint32_t b0, uint32_t idesc) {
+__device__ __forceinline__ void mma_kk(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc) {
 #pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const uint64_t ad = make_smem_desc(a0 + (j >> 2) * (A_ROWS * 128) + (j & 3) * 32, 16, 1024);
-    const uint64_t bd = make_smem_desc(b0 + (j >> 2) * (B_ROWS * 128) + (j & 3) * 32, 16, 1024);
-    mma_tf32_ss(tmem_d, ad, bd, idesc, j > 0 ? 1u : 0u);
-  }
+  for (int j = 0; j < 8; ++j)
+    mma_tf32_ss(tmem_d, desc_add(adesc, (j >> 2) * (A_ROWS * 128) + (j & 3) * 32), desc_add(bdesc, (j >> 2) * (B_ROWS * 128) + (j & 3) * 32), idesc,
+                j > 0 ? 1u : 0u);
 }
 // D[tmem] (+)= A[tmem, 128 lanes x 64 columns] * B with B MN-major: 64 contraction rows x 64 features as two TMA boxes
 // (32 features x 64 rows, 8 KB each, 32-byte-atom swizzle): LBO = next feature box, SBO = next group of 4 contraction rows
-__device__ __forceinline__ void mma_tmn(uint32_t tmem_d, uint32_t tmem_a, uint32_t b0, uint32_t idesc, bool accumulate) {
+__device__ __forceinline__ void mma_tmn(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, bool accumulate) {
 #pragma unroll
-  for (int j = 0; j < 8; ++j)
-    mma_tf32_ts(tmem_d, tmem_a + j * 8, make_smem_desc(b0 + j * 1024, 8192, 512, kLayoutSw128Base32), idesc, (accumulate || j > 0) ? 1u : 0u);
+  for (int j = 0; j < 8; ++j) mma_tf32_ts(tmem_d, tmem_a + j * 8, desc_add(bdesc, j * 1024), idesc, (accumulate || j > 0) ? 1u : 0u);
 }
 
 __device__ __forceinline__ uint8_t* align1024(uint8_t* p) {
@@ -121,30 +134,38 @@ __global__ void __launch_bounds__(FWD_THREADS, 2) attn_fwd_kernel(const __grid_c
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer: S_0, S_1, PV_0, S_2, PV_1, ... (tcgen05.mma executes in issue order) =====
-    if (lane == 0) {
-      constexpr uint32_t idesc_s = make_idesc(kFmtTF32, 128, 64, 0, 0);
-      constexpr uint32_t idesc_o = make_idesc(kFmtTF32, 128, 64, 0, 1);
-      mbar_wait(&bars[FB_Q], 0);
-      auto issue_s = [&](int j) {
-        const int st = j & 1;
-        mbar_wait(&bars[FB_KF + st], (j >> 1) & 1);
-        tc_fence_after();
-        mma_kk<128, 64>(tmem + st * 64, smem_u32(sQ), smem_u32(sK + st * TILE16K), idesc_s);
+    // ===== MMA issuer: S_0, S_1, PV_0, S_2, PV_1, ... (tcgen05.mma executes in issue order).  The whole warp walks the loop
+    // (uniform control flow keeps the descriptor arithmetic on the uniform datapath); one elected lane issues.
+    constexpr uint32_t idesc_s = make_idesc(kFmtTF32, 128, 64, 0, 0);
+    constexpr uint32_t idesc_o = make_idesc(kFmtTF32, 128, 64, 0, 1);
+    const uint64_t dQ = desc_kmajor(smem_u32(sQ));
+    const uint64_t dK[2] = {desc_kmajor(smem_u32(sK)), desc_kmajor(smem_u32(sK + TILE16K))};
+    const uint64_t dV[2] = {desc_mnmajor(smem_u32(sV)), desc_mnmajor(smem_u32(sV + TILE16K))};
+    mbar_wait(&bars[FB_Q], 0);
+    auto issue_s = [&](int j) {
+      const int st = j & 1;
+      mbar_wait(&bars[FB_KF + st], (j >> 1) & 1);
+      tc_fence_after();
+      if (elect_one()) {
+        mma_kk<128, 64>(tmem + st * 64, dQ, dK[st], idesc_s);
         mma_commit(&bars[FB_KE + st]);
         mma_commit(&bars[FB_SF + st]);
-      };
-      issue_s(0);
-      for (int j = 0; j < ntiles; ++j) {
-        if (j + 1 < ntiles) issue_s(j + 1);
-        const int st = j & 1; const uint32_t ph = (j >> 1) & 1;
-        mbar_wait(&bars[FB_PF + st], ph);
-        mbar_wait(&bars[FB_VF + st], ph);
-        tc_fence_after();
-        mma_tmn(tmem + 128, tmem + st * 64, smem_u32(sV + st * TILE16K), idesc_o, j > 0);
+      }
+      __syncwarp();
+    };
+    issue_s(0);
+    for (int j = 0; j < ntiles; ++j) {
+      if (j + 1 < ntiles) issue_s(j + 1);
+      const int st = j & 1; const uint32_t ph = (j >> 1) & 1;
+      mbar_wait(&bars[FB_PF + st], ph);
+      mbar_wait(&bars[FB_VF + st], ph);
+      tc_fence_after();
+      if (elect_one()) {
+        mma_tmn(tmem + 128, tmem + st * 64, dV[st], idesc_o, j > 0);
         mma_commit(&bars[FB_VE + st]);
         mma_commit(&bars[FB_PV]);
       }
+      __syncwarp();
     }
   } else {
     // ===== row threads: thread owns query row q0 + 32 * quad + lane = TMEM lane 32 * quad + lane =====
@@ -159,10 +180,14 @@ __global__ void __launch_bounds__(FWD_THREADS, 2) attn_fwd_kernel(const __grid_c
       tmem_ld32_nowait(t_row + st * 64, s);
       tmem_ld32_nowait(t_row + st * 64 + 32, s + 32);
       tmem_wait_ld();
-      const int nvalid = p.Tc - j * 64;                  // keys beyond Tc are masked out
+      const int nvalid = p.Tc - j * 64;                  // keys beyond Tc are masked out (last tile only)
+      if (nvalid < 64) {
+#pragma unroll
+        for (int c = 0; c < 64; ++c) if (c >= nvalid) s[c] = __float_as_uint(-INFINITY);
+      }
       float mx = -INFINITY;
 #pragma unroll
-      for (int c = 0; c < 64; ++c) { if (c >= nvalid) s[c] = __float_as_uint(-INFINITY); mx = fmaxf(mx, __uint_as_float(s[c])); }
+      for (int c = 0; c < 64; ++c) mx = fmaxf(mx, __uint_as_float(s[c]));
       const float m_new = fmaxf(m_used, mx);
       const bool grow = (m_new - m_used) * kLog2e > 8.f;
       if (__any_sync(kFullMask, grow)) {
@@ -187,9 +212,9 @@ __global__ void __launch_bounds__(FWD_THREADS, 2) attn_fwd_kernel(const __grid_c
       float sum = 0.f;
 #pragma unroll
       for (int c = 0; c < 64; ++c) {
-        const float e = exp2f(fmaf(__uint_as_float(s[c]), kLog2e, -mb));
+        const float e = fast_ex2(fmaf(__uint_as_float(s[c]), kLog2e, -mb));
         sum += e;
-        s[c] = __float_as_uint(to_tf32(e));
+        s[c] = tf32_rna_bits(e);
       }
       l_run += sum;
       tmem_st32(t_row + st * 64, s);
@@ -247,8 +272,10 @@ constexpr int BWD_THREADS = 320;                       // producer, issuer, 8 ro
 
 // ---- dQ: CTA = 128 query rows, loop over 64-key tiles -----------------------------------------------------------------
 constexpr int BQ_STAGE = 3 * TILE16K;                  // K (K-major), V (K-major), K (MN-major)
-constexpr int BQ_SMEM = 1024 + 2 * TILE32K + 2 * BQ_STAGE + 128;
-enum { QB_QDO = 0, QB_KVF = 1, QB_KVE = 3, QB_KMF = 5, QB_KME = 7, QB_SF = 9, QB_DSF = 11, QB_DONE = 13, QB_COUNT = 14 };
+constexpr int BQ_NS = 3;                              // shared-memory stages (the TMEM score buffers stay double)
+constexpr int BQ_SMEM = 1024 + 2 * TILE32K + BQ_NS * BQ_STAGE + 128;
+enum { QB_QDO = 0, QB_KVF = 1, QB_KVE = QB_KVF + BQ_NS, QB_KMF = QB_KVE + BQ_NS, QB_KME = QB_KMF + BQ_NS, QB_SF = QB_KME + BQ_NS, QB_DSF = QB_SF + 2,
+       QB_DONE = QB_DSF + 2, QB_COUNT = QB_DONE + 1 };
 
 __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dq_kernel(const __grid_constant__ AttnP p, const __grid_constant__ CUtensorMap tmQ,
                                                                       const __grid_constant__ CUtensorMap tmdO, const __grid_constant__ CUtensorMap tmK,
@@ -256,7 +283,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dq_kernel(const __gri
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = align1024(smem_raw);
   uint8_t* sQ = sm; uint8_t* sdO = sQ + TILE32K; uint8_t* stage0 = sdO + TILE32K;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(stage0 + 2 * BQ_STAGE);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(stage0 + BQ_NS * BQ_STAGE);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + QB_COUNT);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -281,7 +308,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dq_kernel(const __gri
       tma_tile(sQ, &tmQ, &bars[QB_QDO], h * HD, q0, b, 128);
       tma_tile(sdO, &tmdO, &bars[QB_QDO], h * HD, q0, b, 128);
       for (int j = 0; j < ntiles; ++j) {
-        const int st = j & 1; const uint32_t ph = (j >> 1) & 1;
+        const int st = j % BQ_NS; const uint32_t ph = (j / BQ_NS) & 1;
         uint8_t* sg = stage0 + st * BQ_STAGE;
         mbar_wait(&bars[QB_KVE + st], ph ^ 1);
         mbar_arrive_expect_tx(&bars[QB_KVF + st], 2 * TILE16K);
@@ -293,31 +320,45 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dq_kernel(const __gri
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc_kk = make_idesc(kFmtTF32, 128, 64, 0, 0);
-      constexpr uint32_t idesc_kmn = make_idesc(kFmtTF32, 128, 64, 0, 1);
-      mbar_wait(&bars[QB_QDO], 0);
-      auto issue_s = [&](int j) {
-        const int st = j & 1;
-        const uint32_t sg = smem_u32(stage0 + st * BQ_STAGE);
-        mbar_wait(&bars[QB_KVF + st], (j >> 1) & 1);
-        tc_fence_after();
-        mma_kk<128, 64>(tmem + st * 64, smem_u32(sQ), sg, idesc_kk);                     // S  = Q K^T
-        mma_kk<128, 64>(tmem + 128 + st * 64, smem_u32(sdO), sg + TILE16K, idesc_kk);    // dP = dO V^T
-        mma_commit(&bars[QB_KVE + st]);
-        mma_commit(&bars[QB_SF + st]);
-      };
-      issue_s(0);
-      for (int j = 0; j < ntiles; ++j) {
-        if (j + 1 < ntiles) issue_s(j + 1);
-        const int st = j & 1; const uint32_t ph = (j >> 1) & 1;
-        mbar_wait(&bars[QB_DSF + st], ph);
-        mbar_wait(&bars[QB_KMF + st], ph);
-        tc_fence_after();
-        mma_tmn(tmem + 256, tmem + 128 + st * 64, smem_u32(stage0 + st * BQ_STAGE + 2 * TILE16K), idesc_kmn, j > 0);   // dQ += dS K
-        mma_commit(&bars[QB_KME + st]);
+    constexpr uint32_t idesc_kk = make_idesc(kFmtTF32, 128, 64, 0, 0);
+    constexpr uint32_t idesc_kmn = make_idesc(kFmtTF32, 128, 64, 0, 1);
+    const uint64_t dQ = desc_kmajor(smem_u32(sQ)), ddO = desc_kmajor(smem_u32(sdO));
+    uint64_t dK[BQ_NS], dV[BQ_NS], dKmn[BQ_NS];
+#pragma unroll
+    for (int i = 0; i < BQ_NS; ++i) {
+      const uint32_t sg = smem_u32(stage0 + i * BQ_STAGE);
+      dK[i] = desc_kmajor(sg); dV[i] = desc_kmajor(sg + TILE16K); dKmn[i] = desc_mnmajor(sg + 2 * TILE16K);
+    }
+    mbar_wait(&bars[QB_QDO], 0);
+    int st_s = 0; uint32_t ph_s = 0;                    // shared-memory stage / phase of the next S, dP product
+    auto issue_s = [&](int j) {
+      const int tb = j & 1;
+      mbar_wait(&bars[QB_KVF + st_s], ph_s);
+      tc_fence_after();
+      if (elect_one()) {
+        mma_kk<128, 64>(tmem + tb * 64, dQ, dK[st_s], idesc_kk);              // S  = Q K^T
+        mma_kk<128, 64>(tmem + 128 + tb * 64, ddO, dV[st_s], idesc_kk);       // dP = dO V^T
+        mma_commit(&bars[QB_KVE + st_s]);
+        mma_commit(&bars[QB_SF + tb]);
       }
-      mma_commit(&bars[QB_DONE]);
+      __syncwarp();
+      if (++st_s == BQ_NS) { st_s = 0; ph_s ^= 1; }
+    };
+    issue_s(0);
+    int st = 0; uint32_t ph = 0;
+    for (int j = 0; j < ntiles; ++j) {
+      if (j + 1 < ntiles) issue_s(j + 1);
+      const int tb = j & 1;
+      mbar_wait(&bars[QB_DSF + tb], (j >> 1) & 1);
+      mbar_wait(&bars[QB_KMF + st], ph);
+      tc_fence_after();
+      if (elect_one()) {
+        mma_tmn(tmem + 256, tmem + 128 + tb * 64, dKmn[st], idesc_kmn, j > 0);   // dQ += dS K
+        mma_commit(&bars[QB_KME + st]);
+        if (j == ntiles - 1) mma_commit(&bars[QB_DONE]);
+      }
+      __syncwarp();
+      if (++st == BQ_NS) { st = 0; ph ^= 1; }
     }
   } else {
     const int quad = warp & 3, half = (warp - 2) >> 2;
@@ -335,7 +376,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dq_kernel(const __gri
       tmem_wait_ld();
 #pragma unroll
       for (int c = 0; c < 32; ++c)                                                       // dS = P * (dP - D)
-        dp[c] = __float_as_uint(to_tf32(exp2f(fmaf(__uint_as_float(s[c]), kLog2e, -lse2)) * (__uint_as_float(dp[c]) - dd)));
+        dp[c] = tf32_rna_bits(fast_ex2(fmaf(__uint_as_float(s[c]), kLog2e, -lse2)) * (__uint_as_float(dp[c]) - dd));
       tmem_st32(t_row + 128 + st * 64, dp);
       tmem_wait_st();
       tc_fence_before();
@@ -407,33 +448,42 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dkv_kernel(const __gr
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc_kk = make_idesc(kFmtTF32, 128, 64, 0, 0);
-      constexpr uint32_t idesc_kmn = make_idesc(kFmtTF32, 128, 64, 0, 1);
-      mbar_wait(&bars[KB_KV], 0);
-      auto issue_s = [&](int i) {
-        const int st = i & 1;
-        const uint32_t sg = smem_u32(stage0 + st * BK_STAGE);
-        mbar_wait(&bars[KB_QF + st], (i >> 1) & 1);
-        tc_fence_after();
-        mma_kk<128, 64>(tmem + st * 64, smem_u32(sK), sg, idesc_kk);                     // S^T  = K Q^T
-        mma_kk<128, 64>(tmem + 128 + st * 64, smem_u32(sV), sg + TILE16K, idesc_kk);     // dP^T = V dO^T
+    constexpr uint32_t idesc_kk = make_idesc(kFmtTF32, 128, 64, 0, 0);
+    constexpr uint32_t idesc_kmn = make_idesc(kFmtTF32, 128, 64, 0, 1);
+    const uint64_t dK = desc_kmajor(smem_u32(sK)), dV = desc_kmajor(smem_u32(sV));
+    uint64_t dQ[2], ddO[2], dQmn[2], ddOmn[2];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      const uint32_t sg = smem_u32(stage0 + i * BK_STAGE);
+      dQ[i] = desc_kmajor(sg); ddO[i] = desc_kmajor(sg + TILE16K); dQmn[i] = desc_mnmajor(sg + 2 * TILE16K); ddOmn[i] = desc_mnmajor(sg + 3 * TILE16K);
+    }
+    mbar_wait(&bars[KB_KV], 0);
+    auto issue_s = [&](int i) {
+      const int st = i & 1;
+      mbar_wait(&bars[KB_QF + st], (i >> 1) & 1);
+      tc_fence_after();
+      if (elect_one()) {
+        mma_kk<128, 64>(tmem + st * 64, dK, dQ[st], idesc_kk);                // S^T  = K Q^T
+        mma_kk<128, 64>(tmem + 128 + st * 64, dV, ddO[st], idesc_kk);         // dP^T = V dO^T
         mma_commit(&bars[KB_QE + st]);
         mma_commit(&bars[KB_SF + st]);
-      };
-      issue_s(0);
-      for (int i = 0; i < ntiles; ++i) {
-        if (i + 1 < ntiles) issue_s(i + 1);
-        const int st = i & 1; const uint32_t ph = (i >> 1) & 1;
-        const uint32_t sg = smem_u32(stage0 + st * BK_STAGE);
-        mbar_wait(&bars[KB_DSF + st], ph);
-        mbar_wait(&bars[KB_MF + st], ph);
-        tc_fence_after();
-        mma_tmn(tmem + 256, tmem + st * 64, sg + 3 * TILE16K, idesc_kmn, i > 0);         // dV += P^T dO
-        mma_tmn(tmem + 320, tmem + 128 + st * 64, sg + 2 * TILE16K, idesc_kmn, i > 0);   // dK += dS^T Q
-        mma_commit(&bars[KB_ME + st]);
       }
-      mma_commit(&bars[KB_DONE]);
+      __syncwarp();
+    };
+    issue_s(0);
+    for (int i = 0; i < ntiles; ++i) {
+      if (i + 1 < ntiles) issue_s(i + 1);
+      const int st = i & 1; const uint32_t ph = (i >> 1) & 1;
+      mbar_wait(&bars[KB_DSF + st], ph);
+      mbar_wait(&bars[KB_MF + st], ph);
+      tc_fence_after();
+      if (elect_one()) {
+        mma_tmn(tmem + 256, tmem + st * 64, ddOmn[st], idesc_kmn, i > 0);          // dV += P^T dO
+        mma_tmn(tmem + 320, tmem + 128 + st * 64, dQmn[st], idesc_kmn, i > 0);     // dK += dS^T Q
+        mma_commit(&bars[KB_ME + st]);
+        if (i == ntiles - 1) mma_commit(&bars[KB_DONE]);
+      }
+      __syncwarp();
     }
   } else {
     const int quad = warp & 3, half = (warp - 2) >> 2;
@@ -464,9 +514,9 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dkv_kernel(const __gr
       tmem_wait_ld();
 #pragma unroll
       for (int c = 0; c < 32; ++c) {
-        const float pr = exp2f(fmaf(__uint_as_float(s[c]), kLog2e, -lse2[c]));
-        dp[c] = __float_as_uint(to_tf32(pr * (__uint_as_float(dp[c]) - dd[c])));
-        s[c] = __float_as_uint(to_tf32(pr));
+        const float pr = fast_ex2(fmaf(__uint_as_float(s[c]), kLog2e, -lse2[c]));
+        dp[c] = tf32_rna_bits(pr * (__uint_as_float(dp[c]) - dd[c]));
+        s[c] = tf32_rna_bits(pr);
       }
       tmem_st32(t_row + st * 64, s);
       tmem_st32(t_row + 128 + st * 64, dp);

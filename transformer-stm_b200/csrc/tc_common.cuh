@@ -201,5 +201,15 @@ __device__ __forceinline__ float to_tf32(float x) {
   return __uint_as_float(r);
 }
 
+// TF32 round-to-nearest (ties away, like cvt.rna.tf32.f32) for a value that only feeds the tensor core: the MMA ignores the low
+// 13 mantissa bits, so adding half an ulp of the 10-bit mantissa to the bit pattern is the whole rounding (one integer add).
+__device__ __forceinline__ uint32_t tf32_rna_bits(float x) { return __float_as_uint(x) + 0x1000u; }
+// 2^x on the MUFU without the denormal-range fix-up of exp2f (inputs here are <= 8; results below 2^-126 flush to zero)
+__device__ __forceinline__ float fast_ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 }  // namespace tc
 }  // namespace cvt
