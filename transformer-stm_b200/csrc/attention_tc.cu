@@ -17,6 +17,9 @@
 //   operands  Q/K/V/dO must already be rounded to TF32 by their producers (EPI_ROUND); TMA moves raw fp32 words.
 #include <cuda.h>
 
+#include <cstdio>
+#include <cstdlib>
+
 #include "model.cuh"
 #include "tc_common.cuh"
 #include "tma_host.cuh"
@@ -39,7 +42,9 @@ struct AttnP {
   int Tc, D, heads;
   float dq_scale;
   int round_out;                                       // store O / dQ / dK / dV rounded to TF32 (they only feed tensor-core GEMMs)
+  long long* trace;                                    // diagnostics: clock64 timeline of CTA (0,0) of the dQ kernel (CVT_ATTN_TRACE)
 };
+#define ATTN_TRACE(slot) do { if (p.trace && blockIdx.x == 0 && blockIdx.y == 0 && lane == 0) p.trace[(slot)] = clock64(); } while (0)
 
 // Descriptors are built once per operand tile; each MMA only adds a compile-time constant to the 14-bit start-address field
 // (the single issuing thread's instruction stream is what bounds the MMA rate of these small tiles).
@@ -334,6 +339,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dq_kernel(const __gri
     auto issue_s = [&](int j) {
       const int tb = j & 1;
       mbar_wait(&bars[QB_KVF + st_s], ph_s);
+      ATTN_TRACE(j * 8 + 0);
       tc_fence_after();
       if (elect_one()) {
         mma_kk<128, 64>(tmem + tb * 64, dQ, dK[st_s], idesc_kk);              // S  = Q K^T
@@ -349,8 +355,11 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dq_kernel(const __gri
     for (int j = 0; j < ntiles; ++j) {
       if (j + 1 < ntiles) issue_s(j + 1);
       const int tb = j & 1;
+      ATTN_TRACE(j * 8 + 1);
       mbar_wait(&bars[QB_DSF + tb], (j >> 1) & 1);
+      ATTN_TRACE(j * 8 + 2);
       mbar_wait(&bars[QB_KMF + st], ph);
+      ATTN_TRACE(j * 8 + 3);
       tc_fence_after();
       if (elect_one()) {
         mma_tmn(tmem + 256, tmem + 128 + tb * 64, dKmn[st], idesc_kmn, j > 0);   // dQ += dS K
@@ -368,12 +377,15 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dq_kernel(const __gri
     const float dd = q < p.Tc ? p.Dd[(long long)bh * p.Tc + q] : 0.f;
     for (int j = 0; j < ntiles; ++j) {
       const int st = j & 1;
+      if (warp == 2) ATTN_TRACE(j * 8 + 4);
       mbar_wait(&bars[QB_SF + st], (j >> 1) & 1);
+      if (warp == 2) ATTN_TRACE(j * 8 + 5);
       tc_fence_after();
       uint32_t s[32], dp[32];
       tmem_ld32_nowait(t_row + st * 64, s);
       tmem_ld32_nowait(t_row + 128 + st * 64, dp);
       tmem_wait_ld();
+      if (warp == 2) ATTN_TRACE(j * 8 + 6);
 #pragma unroll
       for (int c = 0; c < 32; ++c)                                                       // dS = P * (dP - D)
         dp[c] = tf32_rna_bits(fast_ex2(fmaf(__uint_as_float(s[c]), kLog2e, -lse2)) * (__uint_as_float(dp[c]) - dd));
@@ -381,6 +393,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dq_kernel(const __gri
       tmem_wait_st();
       tc_fence_before();
       mbar_arrive(&bars[QB_DSF + st]);
+      if (warp == 2) ATTN_TRACE(j * 8 + 7);
     }
     mbar_wait(&bars[QB_DONE], 0);
     tc_fence_after();
@@ -400,7 +413,8 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dq_kernel(const __gri
 
 // ---- dK, dV: CTA = 128 key rows, loop over 64-query tiles; works on S^T ------------------------------------------------
 constexpr int BK_STAGE = 4 * TILE16K;                  // Q (K-major), dO (K-major), Q (MN-major), dO (MN-major)
-constexpr int BK_SMEM = 1024 + 2 * TILE32K + 2 * BK_STAGE + 128;
+constexpr int BK_ROWSTAT = 2048;                        // LSE / D of up to this many queries are staged in shared memory once per CTA
+constexpr int BK_SMEM = 1024 + 2 * TILE32K + 2 * BK_STAGE + 128 + 2 * BK_ROWSTAT * 4;
 enum { KB_KV = 0, KB_QF = 1, KB_QE = 3, KB_MF = 5, KB_ME = 7, KB_SF = 9, KB_DSF = 11, KB_DONE = 13, KB_COUNT = 14 };
 
 __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dkv_kernel(const __grid_constant__ AttnP p, const __grid_constant__ CUtensorMap tmK,
@@ -412,6 +426,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dkv_kernel(const __gr
   uint8_t* sK = sm; uint8_t* sV = sK + TILE32K; uint8_t* stage0 = sV + TILE32K;
   uint64_t* bars = reinterpret_cast<uint64_t*>(stage0 + 2 * BK_STAGE);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + KB_COUNT);
+  float* s_lse = reinterpret_cast<float*>(stage0 + 2 * BK_STAGE + 128); float* s_dd = s_lse + BK_ROWSTAT;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int bh = blockIdx.y, b = bh / p.heads, h = bh - b * p.heads;
@@ -490,16 +505,23 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dkv_kernel(const __gr
     const int kv = kv0 + quad * 32 + lane;
     const uint32_t t_row = tmem + ((uint32_t)(quad * 32) << 16) + half * 32;
     const float* LSE = p.LSE + (long long)bh * p.Tc; const float* Dd = p.Dd + (long long)bh * p.Tc;
-    const bool vec_ok = (p.Tc & 3) == 0;
+    const bool staged = ntiles * 64 <= BK_ROWSTAT;
+    if (staged) {                                        // LSE * log2(e) and D of every query of this (image, head), zero past Tc
+      for (int t = tid - 64; t < ntiles * 64; t += BWD_THREADS - 64) {
+        const bool ok = t < p.Tc;
+        s_lse[t] = ok ? __ldg(LSE + t) * kLog2e : 0.f; s_dd[t] = ok ? __ldg(Dd + t) : 0.f;
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");     // the 8 row warps only
+    }
     for (int i = 0; i < ntiles; ++i) {
       const int st = i & 1;
       const int qc = i * 64 + half * 32;                 // this thread's 32 tile columns are queries qc .. qc + 31 (warp-uniform addresses)
       float lse2[32], dd[32];
-      if (vec_ok && qc + 32 <= p.Tc) {
+      if (staged) {
 #pragma unroll
         for (int c = 0; c < 8; ++c) {
-          const float4 a = __ldg(reinterpret_cast<const float4*>(LSE + qc) + c), d4 = __ldg(reinterpret_cast<const float4*>(Dd + qc) + c);
-          lse2[4 * c] = a.x * kLog2e; lse2[4 * c + 1] = a.y * kLog2e; lse2[4 * c + 2] = a.z * kLog2e; lse2[4 * c + 3] = a.w * kLog2e;
+          const float4 a = *reinterpret_cast<const float4*>(s_lse + qc + 4 * c), d4 = *reinterpret_cast<const float4*>(s_dd + qc + 4 * c);
+          lse2[4 * c] = a.x; lse2[4 * c + 1] = a.y; lse2[4 * c + 2] = a.z; lse2[4 * c + 3] = a.w;
           dd[4 * c] = d4.x; dd[4 * c + 1] = d4.y; dd[4 * c + 2] = d4.z; dd[4 * c + 3] = d4.w;
         }
       } else {
@@ -647,7 +669,16 @@ extern "C" CVT_API int cvt_debug_attention(int B, int Tc, int heads, const float
   if (dO) {
     if (!dQ || !dK || !dV) { cudaFree(buf); set_error("cvt_debug_attention: backward needs dQ, dK, dV"); return CVT_ERR_INVALID; }
     p.dO = dO_; p.Dd = dD; p.dQ = gQ; p.dK = gK; p.dV = gV;
+    long long* trace = nullptr;
+    if (getenv("CVT_ATTN_TRACE")) { cudaMalloc(&trace, 8 * 256 * sizeof(long long)); cudaMemset(trace, 0, 8 * 256 * sizeof(long long)); p.trace = trace; }
     if ((e = run_bwd(p, dD, B, 0)) != cudaSuccess) return fail(e);
+    if (trace) {
+      static long long h[8 * 256];
+      cudaMemcpy(h, trace, sizeof(h), cudaMemcpyDeviceToHost); cudaFree(trace);
+      const int nt = (Tc + 63) / 64; const long long t0 = h[0];
+      printf("dq trace (cycles since first kv_full): tile | kv_full  ds_wait ds_full kmn_full | row: s_wait s_full ld_done arrive\n");
+      for (int j = 0; j < nt && j < 256; ++j) { printf("%3d |", j); for (int k = 0; k < 8; ++k) printf(" %7lld", h[j * 8 + k] ? h[j * 8 + k] - t0 : -1); printf("\n"); }
+    }
   }
   if ((e = cudaDeviceSynchronize()) != cudaSuccess) return fail(e);
   if ((e = cudaMemcpy(O, dOut, n * 4, cudaMemcpyDeviceToHost)) != cudaSuccess || (e = cudaMemcpy(LSE, dL, nl * 4, cudaMemcpyDeviceToHost)) != cudaSuccess) return fail(e);
