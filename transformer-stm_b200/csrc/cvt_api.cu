@@ -111,6 +111,11 @@ static cudaError_t wgrad_bias(const Model* m, const float* X, long long ldx, int
 }
 
 // ---- parameters ------------------------------------------------------------------------------------------------
+static void clear_graphs(Model* m) {
+  for (auto& g : m->graphs) if (g.exec) cudaGraphExecDestroy(g.exec);
+  m->graphs.clear();
+}
+
 static int64_t add_param(Model* m, const std::string& name, std::initializer_list<int64_t> shape, bool trainable) {
   ParamInfo pi; pi.name = name; pi.rank = (int)shape.size(); pi.trainable = trainable;
   int64_t n = 1; int i = 0;
@@ -323,6 +328,7 @@ int cvt_create(const cvt_config* cfg, cvt_model** out) {
 
   {  // folded-weight scratch layout (TF32 / BF16 modes only)
     m->folded = c.precision != CVT_PREC_FP32 && getenv("CVT_NO_FOLD") == nullptr;
+    if (getenv("CVT_NO_GRAPH")) m->use_graphs = 0;
     int64_t f = 0, zc = 0, pt_extra = 0;
     auto al = [](int64_t v) { return (v + 63) / 64 * 64; };
     for (int i = 0; i < c.n_stages; ++i) {
@@ -406,8 +412,7 @@ void cvt_destroy(cvt_model* h) {
   if (!h) return;
   Model* m = &h->m;
   cvt_comm_destroy(h);
-  if (m->train_graph) cudaGraphExecDestroy(m->train_graph);
-  if (m->fwd_graph) cudaGraphExecDestroy(m->fwd_graph);
+  clear_graphs(m);
   if (m->stream) { cudaStreamSynchronize(m->stream); cudaStreamDestroy(m->stream); }
   if (m->workspace) cudaFree(m->workspace);
   if (m->pin_metrics) cudaFreeHost(m->pin_metrics);
@@ -641,9 +646,9 @@ static cudaError_t forward_impl(Model* m, const float* img, const float* proc, i
     for (int i = 0; i < m->n_stages; ++i) {
       const StageGeo& g = m->geo[i]; StageBuf& a = m->buf[i];
       const long long RD = (long long)B * g.Tc * g.D;
-      CVT_CUDA(launch_philox_mask(a.mask_proj, RD, c.drop_rate, m->dropout_seed, m->dropout_step, i * 4 + 0, s));
-      CVT_CUDA(launch_philox_mask(a.mask1, RD * c.mlp_ratio, c.drop_rate, m->dropout_seed, m->dropout_step, i * 4 + 1, s));
-      CVT_CUDA(launch_philox_mask(a.mask2, RD, c.drop_rate, m->dropout_seed, m->dropout_step, i * 4 + 2, s));
+      CVT_CUDA(launch_philox_mask(a.mask_proj, RD, c.drop_rate, m->dropout_seed, m->dropout_step, i * 4 + 0, s, m->dyn));
+      CVT_CUDA(launch_philox_mask(a.mask1, RD * c.mlp_ratio, c.drop_rate, m->dropout_seed, m->dropout_step, i * 4 + 1, s, m->dyn));
+      CVT_CUDA(launch_philox_mask(a.mask2, RD, c.drop_rate, m->dropout_seed, m->dropout_step, i * 4 + 2, s, m->dyn));
     }
   }
   if (c.precision != CVT_PREC_FP32) {
@@ -896,6 +901,8 @@ static int check_batch(Model* m, int batch, const char* who) {
   return CVT_OK;
 }
 
+static int infer_forward(Model* m, const float* img, const float* proc, int B);
+
 int cvt_forward(cvt_model* h, const float* img_dev, const float* proc_dev, int batch, int training, float* out_dev) {
   if (!h || !img_dev) { set_error("cvt_forward: null argument"); return CVT_ERR_INVALID; }
   Model* m = &h->m;
@@ -903,7 +910,8 @@ int cvt_forward(cvt_model* h, const float* img_dev, const float* proc_dev, int b
   int r = check_batch(m, batch, "cvt_forward"); if (r) return r;
   API_CUDA(cudaSetDevice(m->cfg.device));
   const long long l0 = g_launch_count;
-  API_CUDA(forward_impl(m, img_dev, proc_dev, batch, training));
+  if (training) API_CUDA(forward_impl(m, img_dev, proc_dev, batch, training));
+  else { const int rf = infer_forward(m, img_dev, proc_dev, batch); if (rf) return rf; }
   g_last_inputs = {img_dev, proc_dev};
   if (out_dev) API_CUDA(cudaMemcpyAsync(out_dev, m->pred, (size_t)batch * m->cfg.num_classes * sizeof(float), cudaMemcpyDeviceToDevice, m->stream));
   m->launches += g_launch_count - l0;
@@ -975,6 +983,7 @@ int cvt_comm_init(cvt_model* h, const uint8_t unique_id[128], int rank, int worl
   NcclUid uid; memcpy(uid.internal, unique_id, 128);
   API_NCCL(g_nccl.init_rank(&m->nccl_comm, world, uid, rank));
   m->rank = rank; m->world = world;
+  clear_graphs(m);
   return CVT_OK;
 }
 int cvt_comm_destroy(cvt_model* h) {
@@ -982,6 +991,7 @@ int cvt_comm_destroy(cvt_model* h) {
   Model* m = &h->m;
   if (m->nccl_comm && g_nccl.destroy) { g_nccl.destroy(m->nccl_comm); m->nccl_comm = nullptr; }
   m->world = 1; m->rank = 0;
+  clear_graphs(m);
   return CVT_OK;
 }
 int cvt_grad_arena(cvt_model* h, float** g, int64_t* count) {
@@ -995,12 +1005,14 @@ int cvt_param_arena(cvt_model* h, float** p, int64_t* count) {
   return CVT_OK;
 }
 
-static cudaError_t adam_impl(Model* m, float lr, float grad_scale) {
-  m->adam_t += 1;
+static float adam_alpha(Model* m, float lr) {
   const double b1 = 0.9, b2 = 0.999;
   const double t = (double)m->adam_t;
-  const float alpha = (float)((double)lr * sqrt(1.0 - pow(b2, t)) / (1.0 - pow(b1, t)));
-  return launch_adam(m->P, m->G, m->Mo, m->Vo, m->n_train, alpha, 0.9f, 0.999f, 1e-7f, grad_scale, m->stream);
+  return (float)((double)lr * sqrt(1.0 - pow(b2, t)) / (1.0 - pow(b1, t)));
+}
+static cudaError_t adam_impl(Model* m, float lr, float grad_scale) {
+  m->adam_t += 1;
+  return launch_adam(m->P, m->G, m->Mo, m->Vo, m->n_train, adam_alpha(m, lr), 0.9f, 0.999f, 1e-7f, grad_scale, m->stream);
 }
 
 int cvt_adam_step(cvt_model* h, float lr) {
@@ -1021,17 +1033,98 @@ int cvt_optimizer_reset(cvt_model* h) {
 }
 int64_t cvt_optimizer_step_count(const cvt_model* h) { return h ? h->m.adam_t : -1; }
 
+// ---- CUDA graphs: one captured graph per (kind, input buffers, batch) ----------------------------------------------
+enum { GRAPH_TRAIN = 0, GRAPH_INFER = 1 };
+static Model::GraphEntry* graph_slot(Model* m, int kind, const float* img, const float* proc, const float* y, int B) {
+  for (auto& g : m->graphs) if (g.kind == kind && g.img == img && g.proc == proc && g.y == y && g.batch == B) return &g;
+  if (m->graphs.size() >= 16) { if (m->graphs.front().exec) cudaGraphExecDestroy(m->graphs.front().exec); m->graphs.erase(m->graphs.begin()); }
+  m->graphs.push_back(Model::GraphEntry{kind, img, proc, y, B, nullptr, 0});
+  return nullptr;                                        // first sighting: the caller runs eagerly (also warms every lazy initialiser)
+}
+
+// the stream work of one train step; per-step scalars come from m->lr_dev (set by the caller), so the sequence can be replayed
+static int train_step_body(Model* m, const float* img, const float* proc, const float* y, int B) {
+  m->dyn = m->lr_dev;
+  int rc = CVT_OK;
+  do {
+    if (forward_impl(m, img, proc, B, 1) != cudaSuccess) { rc = CVT_ERR_CUDA; break; }
+    if (launch_mse_loss(m->pred, y, B * m->cfg.num_classes, m->metrics, m->dpred, 1.f, 0, m->stream) != cudaSuccess) { rc = CVT_ERR_CUDA; break; }
+    if (backward_impl(m, img, proc, B, 1, -1, nullptr) != cudaSuccess) { rc = CVT_ERR_CUDA; break; }
+    if (m->nccl_comm && m->world > 1) {
+      // data parallel: sum of per-rank mean-loss gradients / world == gradient of the global-batch mean loss
+      const int r = g_nccl.allreduce(m->G, m->G, (size_t)m->n_train, /*ncclFloat32*/ 7, /*ncclSum*/ 0, m->nccl_comm, m->stream);
+      if (r != 0) { set_error(std::string("ncclAllReduce: ") + (g_nccl.errstr ? g_nccl.errstr(r) : "nccl error")); rc = CVT_ERR_NCCL; break; }
+    }
+    if (launch_adam(m->P, m->G, m->Mo, m->Vo, m->n_train, 0.f, 0.9f, 0.999f, 1e-7f, 1.f, m->stream, m->dyn) != cudaSuccess) { rc = CVT_ERR_CUDA; break; }
+  } while (0);
+  m->dyn = nullptr;
+  return rc;
+}
+
 static int train_step_dev(Model* m, const float* img, const float* proc, const float* y, int B, float lr) {
-  API_CUDA(forward_impl(m, img, proc, B, 1));
-  API_CUDA(launch_mse_loss(m->pred, y, B * m->cfg.num_classes, m->metrics, m->dpred, 1.f, 0, m->stream));
-  API_CUDA(backward_impl(m, img, proc, B, 1, -1, nullptr));
-  float gs = 1.f;
-  if (m->nccl_comm && m->world > 1) {
-    // data parallel: sum of per-rank mean-loss gradients / world == gradient of the global-batch mean loss
-    API_NCCL(g_nccl.allreduce(m->G, m->G, (size_t)m->n_train, /*ncclFloat32*/ 7, /*ncclSum*/ 0, m->nccl_comm, m->stream));
-    gs = 1.f / (float)m->world;
+  const bool philox = m->dropout_mode == CVT_DROPOUT_PHILOX && m->cfg.drop_rate > 0.f;
+  const uint32_t step = m->dropout_step;
+  m->adam_t += 1;
+  const float gs = (m->nccl_comm && m->world > 1) ? 1.f / (float)m->world : 1.f;
+  API_CUDA(launch_set_step_params(m->lr_dev, adam_alpha(m, lr), gs, step, m->stream));
+  Model::GraphEntry* g = (m->use_graphs && !g_prof) ? graph_slot(m, GRAPH_TRAIN, img, proc, y, B) : nullptr;
+  if (g && !g->exec) {
+    const long long l0 = g_launch_count;
+    cudaGraph_t graph = nullptr;
+    API_CUDA(cudaStreamBeginCapture(m->stream, cudaStreamCaptureModeThreadLocal));
+    const int rc = train_step_body(m, img, proc, y, B);
+    const cudaError_t e = cudaStreamEndCapture(m->stream, &graph);
+    m->dropout_step = step;                              // forward_impl advanced it while capturing; the replay below counts
+    if (rc != CVT_OK || e != cudaSuccess || !graph) {
+      if (graph) cudaGraphDestroy(graph);
+      if (rc == CVT_OK) set_error(std::string("train step capture: ") + cudaGetErrorString(e));
+      cudaGetLastError();
+      return rc != CVT_OK ? rc : CVT_ERR_CUDA;
+    }
+    const cudaError_t ei = cudaGraphInstantiate(&g->exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (ei != cudaSuccess) { g->exec = nullptr; set_error(std::string("cudaGraphInstantiate: ") + cudaGetErrorString(ei)); return CVT_ERR_CUDA; }
+    g->launches = g_launch_count - l0;
+    g_launch_count = l0;
   }
-  API_CUDA(adam_impl(m, lr, gs));
+  if (g && g->exec) {
+    API_CUDA(cudaGraphLaunch(g->exec, m->stream));
+    g_launch_count += g->launches;
+    if (philox) m->dropout_step = step + 1;
+    m->last_batch = B; m->last_training = 1; m->have_forward = 1;
+    return CVT_OK;
+  }
+  return train_step_body(m, img, proc, y, B);
+}
+
+// inference forward (training = 0) through the graph cache; falls back to eager issue on first sighting
+static int infer_forward(Model* m, const float* img, const float* proc, int B) {
+  Model::GraphEntry* g = (m->use_graphs && !g_prof) ? graph_slot(m, GRAPH_INFER, img, proc, nullptr, B) : nullptr;
+  if (g && !g->exec) {
+    const long long l0 = g_launch_count;
+    cudaGraph_t graph = nullptr;
+    API_CUDA(cudaStreamBeginCapture(m->stream, cudaStreamCaptureModeThreadLocal));
+    const cudaError_t ef = forward_impl(m, img, proc, B, 0);
+    const cudaError_t e = cudaStreamEndCapture(m->stream, &graph);
+    if (ef != cudaSuccess || e != cudaSuccess || !graph) {
+      if (graph) cudaGraphDestroy(graph);
+      if (ef == cudaSuccess) set_error(std::string("forward capture: ") + cudaGetErrorString(e));
+      cudaGetLastError();
+      return CVT_ERR_CUDA;
+    }
+    const cudaError_t ei = cudaGraphInstantiate(&g->exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (ei != cudaSuccess) { g->exec = nullptr; set_error(std::string("cudaGraphInstantiate: ") + cudaGetErrorString(ei)); return CVT_ERR_CUDA; }
+    g->launches = g_launch_count - l0;
+    g_launch_count = l0;
+  }
+  if (g && g->exec) {
+    API_CUDA(cudaGraphLaunch(g->exec, m->stream));
+    g_launch_count += g->launches;
+    m->last_batch = B; m->last_training = 0; m->have_forward = 1;
+    return CVT_OK;
+  }
+  API_CUDA(forward_impl(m, img, proc, B, 0));
   return CVT_OK;
 }
 
@@ -1075,7 +1168,7 @@ int cvt_predict_host(cvt_model* h, const float* img, const float* proc, int64_t 
     const int B = (int)std::min<int64_t>(c.max_batch, n - o);
     API_CUDA(cudaMemcpyAsync(m->in_img, img + o * per, B * per * sizeof(float), cudaMemcpyHostToDevice, m->stream));
     if (c.proc_dim > 0) API_CUDA(cudaMemcpyAsync(m->in_proc, proc + o * c.proc_dim, (size_t)B * c.proc_dim * sizeof(float), cudaMemcpyHostToDevice, m->stream));
-    API_CUDA(forward_impl(m, m->in_img, c.proc_dim > 0 ? m->in_proc : nullptr, B, 0));
+    { const int rf = infer_forward(m, m->in_img, c.proc_dim > 0 ? m->in_proc : nullptr, B); if (rf) return rf; }
     API_CUDA(cudaMemcpyAsync(out + o * c.num_classes, m->pred, (size_t)B * c.num_classes * sizeof(float), cudaMemcpyDeviceToHost, m->stream));
   }
   API_CUDA(cudaStreamSynchronize(m->stream));
@@ -1112,6 +1205,7 @@ int cvt_evaluate_host(cvt_model* h, const float* img, const float* proc, const f
 int cvt_set_dropout(cvt_model* h, int mode, uint64_t seed) {
   if (!h || mode < 0 || mode > 2) { set_error("cvt_set_dropout: bad mode"); return CVT_ERR_INVALID; }
   h->m.dropout_mode = mode; h->m.dropout_seed = seed; h->m.dropout_step = 0;
+  clear_graphs(&h->m);                                   // mode and seed are baked into captured launches
   return CVT_OK;
 }
 int cvt_set_dropout_mask(cvt_model* h, int site, const uint8_t* host_mask, int64_t count) {
@@ -1202,7 +1296,7 @@ int cvt_synchronize(cvt_model* h) {
   return CVT_OK;
 }
 void* cvt_stream(cvt_model* h) { return h ? (void*)h->m.stream : nullptr; }
-int cvt_set_graphs(cvt_model* h, int enable) { if (!h) return CVT_ERR_INVALID; h->m.use_graphs = enable; return CVT_OK; }
+int cvt_set_graphs(cvt_model* h, int enable) { if (!h) return CVT_ERR_INVALID; h->m.use_graphs = enable; if (!enable) clear_graphs(&h->m); return CVT_OK; }
 int64_t cvt_kernel_launches(const cvt_model* h) { return h ? h->m.launches : -1; }
 int64_t cvt_workspace_bytes(const cvt_model* h) { return h ? h->m.workspace_bytes : -1; }
 

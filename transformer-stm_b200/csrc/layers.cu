@@ -397,8 +397,13 @@ __global__ void __launch_bounds__(256) softmax_bwd_rows_kernel(float* __restrict
 // ------------------------------------------------------------------------------------------------
 // small elementwise kernels
 // ------------------------------------------------------------------------------------------------
+// dyn (optional): per-step values kept in device memory so that a captured CUDA graph can be replayed: {alpha, grad_scale, dropout step}
+__global__ void set_step_params_kernel(float* dyn, float alpha, float gs, uint32_t step) {
+  dyn[0] = alpha; dyn[1] = gs; reinterpret_cast<uint32_t*>(dyn)[2] = step;
+}
 __global__ void __launch_bounds__(256) philox_mask_kernel(uint8_t* __restrict__ mask, long long n, uint32_t thr, uint32_t k0, uint32_t k1,
-                                                          uint32_t step, uint32_t site) {
+                                                          uint32_t step, uint32_t site, const float* __restrict__ dyn) {
+  if (dyn) step = reinterpret_cast<const uint32_t*>(dyn)[2];
   const long long nq = (n + 3) >> 2;
   for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < nq; q += (long long)gridDim.x * blockDim.x) {
     uint32_t c[4] = {(uint32_t)q, site, step, 0u};
@@ -473,7 +478,9 @@ __global__ void __launch_bounds__(256) mse_loss_kernel(const float* __restrict__
 }
 
 __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
-                                                   float* __restrict__ v, long long n4, float alpha, float b1, float b2, float eps, float gs) {
+                                                   float* __restrict__ v, long long n4, float alpha, float b1, float b2, float eps, float gs,
+                                                   const float* __restrict__ dyn) {
+  if (dyn) { alpha = dyn[0]; gs = dyn[1]; }
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
     float4 pp = reinterpret_cast<float4*>(p)[i];
     float4 gg = reinterpret_cast<const float4*>(g)[i];
@@ -592,11 +599,11 @@ cudaError_t launch_softmax_bwd_rows(float* dP, const float* P, long long rows, i
   return cudaSuccess;
 }
 
-cudaError_t launch_philox_mask(uint8_t* mask, long long n, float rate, uint64_t seed, uint32_t step, uint32_t site, cudaStream_t s) {
+cudaError_t launch_philox_mask(uint8_t* mask, long long n, float rate, uint64_t seed, uint32_t step, uint32_t site, cudaStream_t s, const float* dyn) {
   if (n <= 0) return cudaSuccess;
   double t = (double)rate * 4294967296.0;
   const uint32_t thr = t >= 4294967295.0 ? 0xFFFFFFFFu : (uint32_t)t;
-  philox_mask_kernel<<<ew_blocks((n + 3) / 4), 256, 0, s>>>(mask, n, thr, (uint32_t)(seed & 0xFFFFFFFFu), (uint32_t)(seed >> 32), step, site);
+  philox_mask_kernel<<<ew_blocks((n + 3) / 4), 256, 0, s>>>(mask, n, thr, (uint32_t)(seed & 0xFFFFFFFFu), (uint32_t)(seed >> 32), step, site, dyn);
   CVT_LAUNCH_CHECK();
   return cudaSuccess;
 }
@@ -633,11 +640,16 @@ cudaError_t launch_mse_loss(const float* pred, const float* y, int n, float* met
   CVT_LAUNCH_CHECK();
   return cudaSuccess;
 }
+cudaError_t launch_set_step_params(float* dyn, float alpha, float gs, uint32_t step, cudaStream_t s) {
+  set_step_params_kernel<<<1, 1, 0, s>>>(dyn, alpha, gs, step);
+  CVT_LAUNCH_CHECK();
+  return cudaSuccess;
+}
 cudaError_t launch_adam(float* params, const float* grads, float* m, float* v, long long n, float alpha, float b1, float b2,
-                        float eps, float grad_scale, cudaStream_t s) {
+                        float eps, float grad_scale, cudaStream_t s, const float* dyn) {
   if (n <= 0) return cudaSuccess;
   if (n % 4 != 0) { set_error("adam: arena length must be a multiple of 4"); return cudaErrorInvalidValue; }
-  adam_kernel<<<ew_blocks(n / 4), 256, 0, s>>>(params, grads, m, v, n / 4, alpha, b1, b2, eps, grad_scale);
+  adam_kernel<<<ew_blocks(n / 4), 256, 0, s>>>(params, grads, m, v, n / 4, alpha, b1, b2, eps, grad_scale, dyn);
   CVT_LAUNCH_CHECK();
   return cudaSuccess;
 }

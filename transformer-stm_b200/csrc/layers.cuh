@@ -82,7 +82,9 @@ cudaError_t launch_softmax_rows(float* S, long long rows, int cols, cudaStream_t
 cudaError_t launch_softmax_bwd_rows(float* dP, const float* P, long long rows, int cols, cudaStream_t s);
 
 // dropout keep-masks from Philox4x32-10 (same stream as oracle.dropout_mask)
-cudaError_t launch_philox_mask(uint8_t* mask, long long n, float rate, uint64_t seed, uint32_t step, uint32_t site, cudaStream_t s);
+cudaError_t launch_philox_mask(uint8_t* mask, long long n, float rate, uint64_t seed, uint32_t step, uint32_t site, cudaStream_t s,
+                               const float* dyn = nullptr);
+cudaError_t launch_set_step_params(float* dyn, float alpha, float gs, uint32_t step, cudaStream_t s);
 // dst = src * mask * scale
 cudaError_t launch_mask_scale(float* dst, const float* src, const uint8_t* mask, float scale, long long n, cudaStream_t s, int round = 0);
 // dst[map(r)*ld + c] = src[c] for r < rows (cls token broadcast)
@@ -99,6 +101,6 @@ cudaError_t launch_mse_loss(const float* pred, const float* y, int n, float* met
 
 // Keras Adam on a flat arena: m,v update; theta -= alpha * m / (sqrt(v) + eps); alpha = lr*sqrt(1-b2^t)/(1-b1^t)
 cudaError_t launch_adam(float* params, const float* grads, float* m, float* v, long long n, float alpha, float b1, float b2,
-                        float eps, float grad_scale, cudaStream_t s);
+                        float eps, float grad_scale, cudaStream_t s, const float* dyn = nullptr);
 
 }  // namespace cvt

@@ -94,9 +94,13 @@ struct Model {
   int rank = 0, world = 1;
 
   // CUDA graphs
-  int use_graphs = 0;
-  cudaGraphExec_t train_graph = nullptr; int train_graph_batch = 0; float* lr_dev = nullptr;
-  cudaGraphExec_t fwd_graph = nullptr; int fwd_graph_batch = 0;
+  // A step is first run eagerly for a given (kind, buffers, batch); the second time it is captured, afterwards replayed.
+  // Per-step scalars (Adam step size, gradient scale, dropout counter) live in lr_dev so that replays see fresh values.
+  struct GraphEntry { int kind; const float* img; const float* proc; const float* y; int batch; cudaGraphExec_t exec; long long launches; };
+  int use_graphs = 1;
+  std::vector<GraphEntry> graphs;
+  float* lr_dev = nullptr;
+  const float* dyn = nullptr;             // == lr_dev while a train step is being issued (eagerly or under capture)
 };
 
 // attention dispatch (attention.cu)
