@@ -228,6 +228,9 @@ static void carve(Model* m, Bump& b) {
   m->dp1 = b.take<float>(MB * std::max(1, c.proc_hidden));
   m->dhln = b.take<float>(MB * (int64_t)gl.Tc * gl.D);
   m->metrics = b.take<float>(4);
+  m->dz2 = b.take<float>(MB * std::max(1, c.proc_hidden));
+  m->head_partial = b.take<float>(2 * MB + 4);
+  m->head_ticket = reinterpret_cast<unsigned*>(b.take<float>(4));
   m->gX[0] = b.take<float>(maxRD); m->gX[1] = b.take<float>(maxRD);
   m->gH = b.take<float>(maxRH); m->gC = b.take<float>(maxRD); m->gD = b.take<float>(maxRD); m->gE = b.take<float>(maxRD);
   m->gM = b.take<float>(maxRD); m->gQ = b.take<float>(3 * maxRD); m->gQ2 = b.take<float>(3 * maxRD);
@@ -402,6 +405,7 @@ int cvt_create(const cvt_config* cfg, cvt_model** out) {
     API_CUDA(cudaMemcpyAsync(m->mg_bwd_dev, bw.data(), bw.size() * sizeof(MgDesc), cudaMemcpyHostToDevice, m->stream));
     API_CUDA(cudaStreamSynchronize(m->stream));      // fw / bw are locals
   }
+  API_CUDA(cudaMemsetAsync(m->head_ticket, 0, 16, m->stream));
   API_CUDA(cudaMallocHost(&m->pin_metrics, 4 * sizeof(float)));
   API_CUDA(cudaStreamSynchronize(m->stream));
   *out = h;
@@ -614,28 +618,38 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
   return cudaSuccess;
 }
 
+static HeadP head_params(Model* m, const float* proc, int B) {
+  const cvt_config& c = m->cfg;
+  const StageGeo& g = m->geo[m->n_stages - 1]; StageBuf& a = m->buf[m->n_stages - 1];
+  float* P = m->P; float* G = m->G;
+  HeadP p{};
+  p.B = B; p.D = g.D; p.F = m->feat_dim; p.PH = c.proc_dim > 0 ? c.proc_hidden : 0; p.proc_dim = c.proc_dim; p.nc = c.num_classes;
+  p.cls_ln = m->head_kind == CVT_HEAD_CLS_LN; p.eps = c.ln_eps;
+  p.x2 = a.x2; p.x2_bs = (long long)g.Tc * g.D;
+  p.hn_g = P + m->hn_g; p.hn_b = P + m->hn_b; p.h_mean = m->h_mean; p.h_rstd = m->h_rstd;
+  p.feat = m->feat; p.proc = proc; p.p1 = m->p1;
+  if (c.proc_dim > 0) { p.w1 = P + m->pd1w; p.b1 = P + m->pd1b; p.w2 = P + m->pd2w; p.b2 = P + m->pd2b; }
+  p.fw = P + m->fw; p.fb = P + m->fb; p.pred = m->pred;
+  p.dpred = m->dpred; p.metrics = m->metrics; p.partial = m->head_partial; p.ticket = m->head_ticket;
+  p.dfeat = m->dfeat; p.dz2 = m->dz2; p.dz1 = m->dp1;
+  if (c.proc_dim > 0) { p.g_w1 = G + m->pd1w; p.g_b1 = G + m->pd1b; p.g_w2 = G + m->pd2w; p.g_b2 = G + m->pd2b; }
+  p.g_fw = G + m->fw; p.g_fb = G + m->fb; p.g_hn_g = G + m->hn_g; p.g_hn_b = G + m->hn_b;
+  return p;
+}
+
+// head of create_cvt_model :325-350 as one launch (head.cu); with m->cur_y set it also produces the loss, the MAE and d pred
 static cudaError_t head_forward(Model* m, const float* proc, int B) {
   const cvt_config& c = m->cfg; cudaStream_t s = m->stream;
   const StageGeo& g = m->geo[m->n_stages - 1]; StageBuf& a = m->buf[m->n_stages - 1];
   const int D = g.D, F = m->feat_dim; float* P = m->P;
   prof_mark(s, "head");
-  if (m->head_kind == CVT_HEAD_CLS_LN) {          // LayerNormalization(1e-6)(cls_tokens); squeeze  :328-329
-    CVT_CUDA(launch_ln_fwd(a.x2, RowMap{1, g.Tc, 0}, D, P + m->hn_g, P + m->hn_b, c.ln_eps, m->feat, F, m->h_mean, m->h_rstd, B, D, s));
-  } else {                                        // reshape -> LN -> reduce_mean over tokens  :334-337
+  if (m->head_kind != CVT_HEAD_CLS_LN) {          // reshape -> LN -> reduce_mean over tokens  :334-337
     CVT_CUDA(launch_ln_fwd(a.x2, rowmap_none(), D, P + m->hn_g, P + m->hn_b, c.ln_eps, m->hln, D, m->h_mean, m->h_rstd, B * g.Tc, D, s));
     CVT_CUDA(launch_token_mean(m->hln, B, g.Tc, D, m->feat, F, s));
   }
-  if (c.proc_dim > 0) {                           // Proc_Dense_1/2 (relu) :343-344, concatenate :347
-    GemmP p = dense_fwd(proc, c.proc_dim, B, c.proc_dim, P + m->pd1w, c.proc_hidden, P + m->pd1b, m->p1, c.proc_hidden);
-    p.epi |= EPI_RELU;
-    CVT_CUDA(launch_gemm_simt(p, s));
-    GemmP q = dense_fwd(m->p1, c.proc_hidden, B, c.proc_hidden, P + m->pd2w, c.proc_hidden, P + m->pd2b, m->feat + D, F);
-    q.epi |= EPI_RELU;
-    CVT_CUDA(launch_gemm_simt(q, s));
-  }
-  GemmP f = dense_fwd(m->feat, F, B, F, P + m->fw, c.num_classes, P + m->fb, m->pred, c.num_classes);   // Final_Dense :350
-  CVT_CUDA(launch_gemm_simt(f, s));
-  return cudaSuccess;
+  HeadP p = head_params(m, proc, B);
+  p.y = m->cur_y;
+  return launch_head_fwd(p, s);
 }
 
 static cudaError_t forward_impl(Model* m, const float* img, const float* proc, int B, int training) {
@@ -675,33 +689,14 @@ static cudaError_t forward_impl(Model* m, const float* img, const float* proc, i
 static cudaError_t head_backward(Model* m, const float* proc, int B, float* dX2) {
   const cvt_config& c = m->cfg; cudaStream_t s = m->stream;
   const StageGeo& g = m->geo[m->n_stages - 1]; StageBuf& a = m->buf[m->n_stages - 1];
-  const int D = g.D, F = m->feat_dim, nc = c.num_classes, PH = c.proc_hidden; float* P = m->P; float* G = m->G;
+  const int D = g.D, F = m->feat_dim; float* P = m->P; float* G = m->G;
   prof_mark(s, "bwd_head");
-  // Final_Dense
-  CVT_CUDA(launch_colsum(m->dpred, nc, rowmap_none(), B, nc, 1, 0, G + m->fb, 0, s));
-  CVT_CUDA(launch_gemm_simt(dense_wgrad(m->feat, F, F, m->dpred, nc, nc, B, G + m->fw), s));
-  {  // d feat (image half)
-    GemmP p = dense_dgrad(m->dpred, nc, B, nc, P + m->fw, D, m->dfeat, F);
-    CVT_CUDA(launch_gemm_simt(p, s));
-  }
-  if (c.proc_dim > 0) {
-    GemmP p = dense_dgrad(m->dpred, nc, B, nc, P + m->fw + (long long)D * nc, PH, m->dfeat + D, F);     // through relu of Proc_Dense_2
-    p.epi |= EPI_RELU_BWD; p.aux = m->feat + D;
-    CVT_CUDA(launch_gemm_simt(p, s));
-    CVT_CUDA(launch_colsum(m->dfeat + D, F, rowmap_none(), B, PH, 1, 0, G + m->pd2b, 0, s));
-    CVT_CUDA(launch_gemm_simt(dense_wgrad(m->p1, PH, PH, m->dfeat + D, F, PH, B, G + m->pd2w), s));
-    GemmP q = dense_dgrad(m->dfeat + D, F, B, PH, P + m->pd2w, PH, m->dp1, PH);
-    q.epi |= EPI_RELU_BWD; q.aux = m->p1;
-    CVT_CUDA(launch_gemm_simt(q, s));
-    CVT_CUDA(launch_colsum(m->dp1, PH, rowmap_none(), B, PH, 1, 0, G + m->pd1b, 0, s));
-    CVT_CUDA(launch_gemm_simt(dense_wgrad(proc, c.proc_dim, c.proc_dim, m->dp1, PH, PH, B, G + m->pd1w), s));
-  }
-  // image branch -> gradient w.r.t. the last block's output
+  // gradient w.r.t. the last block's output: the cls row (cls head) or every row (LN-mean head); zero elsewhere
   CVT_CUDA(cudaMemsetAsync(dX2, 0, (size_t)B * g.Tc * D * sizeof(float), s));
-  if (m->head_kind == CVT_HEAD_CLS_LN) {
-    CVT_CUDA(launch_ln_bwd(m->dfeat, F, a.x2, RowMap{1, g.Tc, 0}, D, m->h_mean, m->h_rstd, P + m->hn_g, nullptr, dX2,
-                           RowMap{1, g.Tc, 0}, D, G + m->hn_g, G + m->hn_b, B, D, s));
-  } else {
+  HeadP p = head_params(m, proc, B);
+  p.dx2 = dX2;
+  CVT_CUDA(launch_head_bwd(p, s));                 // Final_Dense, Proc_Dense_1/2, cls LayerNormalization: input and parameter gradients
+  if (m->head_kind != CVT_HEAD_CLS_LN) {
     CVT_CUDA(launch_token_mean_bwd(m->dfeat, F, B, g.Tc, D, m->dhln, s));
     CVT_CUDA(launch_ln_bwd(m->dhln, D, a.x2, rowmap_none(), D, m->h_mean, m->h_rstd, P + m->hn_g, nullptr, dX2, rowmap_none(), D,
                            G + m->hn_g, G + m->hn_b, B * g.Tc, D, s));
@@ -1047,8 +1042,10 @@ static int train_step_body(Model* m, const float* img, const float* proc, const 
   m->dyn = m->lr_dev;
   int rc = CVT_OK;
   do {
-    if (forward_impl(m, img, proc, B, 1) != cudaSuccess) { rc = CVT_ERR_CUDA; break; }
-    if (launch_mse_loss(m->pred, y, B * m->cfg.num_classes, m->metrics, m->dpred, 1.f, 0, m->stream) != cudaSuccess) { rc = CVT_ERR_CUDA; break; }
+    m->cur_y = y;                                        // the head kernel also emits loss, MAE and d pred (mse_loss_kernel otherwise)
+    const cudaError_t ef = forward_impl(m, img, proc, B, 1);
+    m->cur_y = nullptr;
+    if (ef != cudaSuccess) { rc = CVT_ERR_CUDA; break; }
     if (backward_impl(m, img, proc, B, 1, -1, nullptr) != cudaSuccess) { rc = CVT_ERR_CUDA; break; }
     if (m->nccl_comm && m->world > 1) {
       // data parallel: sum of per-rank mean-loss gradients / world == gradient of the global-batch mean loss

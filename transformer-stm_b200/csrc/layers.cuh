@@ -103,4 +103,21 @@ cudaError_t launch_mse_loss(const float* pred, const float* y, int n, float* met
 cudaError_t launch_adam(float* params, const float* grads, float* m, float* v, long long n, float alpha, float b1, float b2,
                         float eps, float grad_scale, cudaStream_t s, const float* dyn = nullptr);
 
+// fused regression head + loss (head.cu): models/CvT(Par).py:325-350,464-466
+struct HeadP {
+  int B, D, F, PH, proc_dim, nc, cls_ln;
+  float eps;
+  const float* x2; long long x2_bs;          // last block's output [B, Tc, D]; the cls token is row 0 of every image (cls_ln head)
+  const float* hn_g; const float* hn_b; float* h_mean; float* h_rstd;
+  float* feat;                               // [B, F]: image feature (written here when cls_ln, else read) ++ process feature
+  const float* proc; const float* w1; const float* b1; const float* w2; const float* b2; float* p1;
+  const float* fw; const float* fb; float* pred;
+  const float* y; float* dpred; float* metrics; float* partial; unsigned* ticket;     // y == nullptr: no loss
+  // backward
+  float* dfeat; float* dz2; float* dz1; float* dx2;
+  float* g_w1; float* g_b1; float* g_w2; float* g_b2; float* g_fw; float* g_fb; float* g_hn_g; float* g_hn_b;
+};
+cudaError_t launch_head_fwd(const HeadP& p, cudaStream_t s);
+cudaError_t launch_head_bwd(const HeadP& p, cudaStream_t s);
+
 }  // namespace cvt

@@ -68,6 +68,8 @@ struct Model {
   float *feat = nullptr, *hln = nullptr, *h_mean = nullptr, *h_rstd = nullptr, *p1 = nullptr, *pred = nullptr;
   float *dpred = nullptr, *dfeat = nullptr, *dp1 = nullptr, *dhln = nullptr;
   float *metrics = nullptr;               // device [2]: loss, mae
+  float *dz2 = nullptr, *head_partial = nullptr; unsigned* head_ticket = nullptr;   // fused head (head.cu)
+  const float* cur_y = nullptr;           // targets of the train step being issued: the fused head also produces loss + d pred
   // gradient scratch shared by the stages
   float *gX[2] = {nullptr, nullptr};      // gradient w.r.t. a block output [B,Tc,D] (ping-pong across stages)
   float* cls_scratch = nullptr;           // Z_cls [3][D][D] + s_cls [3][D] of the folded q/k/v backward (fold.cu)
