@@ -61,6 +61,7 @@ cudaError_t run_gemm(const Model* m, const GemmP& p, cudaStream_t s) {
     }
     if (gemm_tc_supports(p)) return launch_gemm_tc(p, s);
   }
+  if (p.epi & EPI_PHILOX) { set_error("run_gemm: in-epilogue dropout needs a tensor-core shape"); return cudaErrorNotSupported; }
   return launch_gemm_simt(p, s);
 }
 
@@ -496,6 +497,24 @@ int cvt_init_params(cvt_model* h, uint64_t seed) {
 // =====================================================================================================================
 // forward
 // =====================================================================================================================
+// TF32 mode draws the dropout masks inside the GEMM epilogues that apply them (every such product has a tensor-core shape:
+// N = D or 4D with D a multiple of 64); the fp32 FFMA path keeps the separate philox_mask_kernel launches.
+static bool inline_philox(const Model* m) {
+  static const bool no_tma = getenv("CVT_NO_TMA") != nullptr;
+  if (no_tma || m->cfg.precision == CVT_PREC_FP32 || m->dropout_mode != CVT_DROPOUT_PHILOX) return false;
+  for (int i = 0; i < m->n_stages; ++i) if (m->geo[i].D % 64 != 0) return false;
+  return true;
+}
+static void epi_dropout(const Model* m, GemmP& q, uint8_t* mask, int site, float keep_scale) {
+  q.epi |= EPI_MASK; q.mask = mask; q.mask_scale = keep_scale;
+  if (inline_philox(m)) {
+    const double t = (double)m->cfg.drop_rate * 4294967296.0;
+    q.epi |= EPI_PHILOX; q.mask_gen = mask; q.ph_thr = t >= 4294967295.0 ? 0xFFFFFFFFu : (uint32_t)t;
+    q.ph_k0 = (uint32_t)(m->dropout_seed & 0xFFFFFFFFu); q.ph_k1 = (uint32_t)(m->dropout_seed >> 32);
+    q.ph_site = (uint32_t)site; q.ph_step = m->dropout_step; q.ph_dyn = m->dyn;
+  }
+}
+
 static cudaError_t stage_forward(Model* m, int si, const float* xin, long long xin_bstride, int xin_boff, int B, int training) {
   const StageGeo& g = m->geo[si]; const StageW& w = m->w[si]; StageBuf& a = m->buf[si];
   const cvt_config& c = m->cfg;
@@ -590,7 +609,7 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
     const StageFold& f = m->fold[si]; float* F = m->Fd;
     GemmP q; q.M = R; q.N = D; q.K = D; q.A = a.attn_o; q.lda = D; q.B = F + f.Wot; q.ldb = D; q.b_mode = B_NK; q.C = a.x1; q.ldc = D;
     q.bias = F + f.bo; q.epi = EPI_BIAS | EPI_RESID; q.resid = a.x0; q.ldr = D;
-    if (drop) { q.epi |= EPI_MASK; q.mask = a.mask_proj; q.mask_scale = keep_scale; }
+    if (drop) epi_dropout(m, q, a.mask_proj, si * 4 + 0, keep_scale);
     CVT_CUDA(run_gemm(m, q, s));
   } else
   {
@@ -598,7 +617,7 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
     CVT_CUDA(run_gemm(m, p, s));
     GemmP q = dense_fwd(a.a1, D, R, D, P + w.prw, D, P + w.prb, a.x1, D);        // self.proj :188, dropout :189, residual :274
     q.epi |= EPI_RESID; q.resid = a.x0; q.ldr = D;
-    if (drop) { q.epi |= EPI_MASK; q.mask = a.mask_proj; q.mask_scale = keep_scale; }
+    if (drop) epi_dropout(m, q, a.mask_proj, si * 4 + 0, keep_scale);
     CVT_CUDA(run_gemm(m, q, s));
   }
   prof_mark(s, kStageNames[si][5]);
@@ -608,11 +627,11 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
     GemmP p = dense_fwd(a.y, D, R, D, P + w.f1w, H4, P + w.f1b, a.hact, H4);
     p.epi |= EPI_GELU; p.aux = a.hpre;
     if (m->folded) p.epi |= EPI_ROUND;
-    if (drop) { p.epi |= EPI_MASK; p.mask = a.mask1; p.mask_scale = keep_scale; }
+    if (drop) epi_dropout(m, p, a.mask1, si * 4 + 1, keep_scale);
     CVT_CUDA(run_gemm(m, p, s));
     GemmP q = dense_fwd(a.hact, H4, R, H4, P + w.f2w, D, P + w.f2b, a.x2, D);
     q.epi |= EPI_RESID; q.resid = a.x1; q.ldr = D;                                // output = x + Mlp_output :281
-    if (drop) { q.epi |= EPI_MASK; q.mask = a.mask2; q.mask_scale = keep_scale; }
+    if (drop) epi_dropout(m, q, a.mask2, si * 4 + 2, keep_scale);
     CVT_CUDA(run_gemm(m, q, s));
   }
   return cudaSuccess;
@@ -656,7 +675,7 @@ static cudaError_t forward_impl(Model* m, const float* img, const float* proc, i
   cudaStream_t s = m->stream;
   const cvt_config& c = m->cfg;
   const bool drop = training && m->dropout_mode == CVT_DROPOUT_PHILOX && c.drop_rate > 0.f;
-  if (drop) {
+  if (drop && !inline_philox(m)) {
     for (int i = 0; i < m->n_stages; ++i) {
       const StageGeo& g = m->geo[i]; StageBuf& a = m->buf[i];
       const long long RD = (long long)B * g.Tc * g.D;

@@ -50,9 +50,15 @@ __global__ void cls_fix_kernel(const float* __restrict__ xn, long long bs, const
   for (int i = threadIdx.x; i < D; i += blockDim.x) srow[i] = xn[(long long)b * Tc * D + i];
   __syncthreads();
   const float* W = Wc + (long long)z * D * D;
-  float a = bc[z * D + j];
-#pragma unroll 16
-  for (int i = 0; i < D; ++i) a = fmaf(srow[i], W[(long long)i * D + j], a);
+  float a = bc[z * D + j], a1 = 0.f, a2 = 0.f, a3 = 0.f;
+  int i = 0;
+#pragma unroll 4
+  for (; i + 3 < D; i += 4) {                          // independent chains: the weight loads of many rows are in flight together
+    a = fmaf(srow[i], W[(long long)i * D + j], a); a1 = fmaf(srow[i + 1], W[(long long)(i + 1) * D + j], a1);
+    a2 = fmaf(srow[i + 2], W[(long long)(i + 2) * D + j], a2); a3 = fmaf(srow[i + 3], W[(long long)(i + 3) * D + j], a3);
+  }
+  for (; i < D; ++i) a = fmaf(srow[i], W[(long long)i * D + j], a);
+  a = (a + a1) + (a2 + a3);
   q[row + j] = round_tf32((z == 0 ? alpha0 : 1.f) * a);     // attention operand (TMA): rounded by its producer
 }
 

@@ -17,6 +17,7 @@ enum Epi : uint32_t {
   EPI_BIAS = 1u, EPI_GELU = 2u, EPI_RESID = 4u, EPI_MASK = 8u, EPI_ATOMIC = 16u, EPI_SCATTER = 32u,
   EPI_GELU_BWD = 64u, EPI_RELU = 128u, EPI_RELU_BWD = 256u, EPI_ALPHA0 = 512u,
   EPI_ROUND = 2048u,      // store C rounded to TF32 (C only feeds tensor-core GEMMs); aux keeps full precision
+  EPI_PHILOX = 4096u,     // with EPI_MASK: the keep-mask is drawn here (Philox4x32-10, same counters as philox_mask_kernel) and stored to mask_gen
   EPI_BN_BWD = 1024u      // v = A[n] v + E[n] aux[idx] + F[n]  (BatchNorm backward as an affine map of (dn, conv); coef = [A|E|F][N])
 };
 
@@ -44,6 +45,7 @@ struct GemmP {
   uint32_t epi = 0;
   const float* resid = nullptr; long long ldr = 0;
   const uint8_t* mask = nullptr; float mask_scale = 1.f;
+  uint8_t* mask_gen = nullptr; uint32_t ph_k0 = 0, ph_k1 = 0, ph_site = 0, ph_step = 0, ph_thr = 0; const float* ph_dyn = nullptr;   // EPI_PHILOX
   const float* epi_coef = nullptr; long long epi_coef_bs = 0; int epi_skip_period = 0;   // EPI_BN_BWD (rows m % period == 0 are cls rows: identity)
   int dbg = 0;                                 // diagnostics only (cvt_debug_gemm): bit 0 swaps LBO/SBO of MN-major descriptors
   float* aux = nullptr;                        // same indexing as C: GELU pre-activation (write) / saved activation (read)

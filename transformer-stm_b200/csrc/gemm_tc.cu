@@ -333,6 +333,7 @@ int pick_bn(const GemmP& p) {
 }  // namespace
 
 bool gemm_tc_supports(const GemmP& p) {
+  if (p.epi & EPI_PHILOX) return false;          // in-epilogue dropout masks are instantiated for the TMA kernel only
   if (p.N % 64 != 0 || p.M < 1 || p.K < 1) return false;
   if (p.epi & (EPI_RELU | EPI_RELU_BWD)) return false;              // the tiny head layers stay on the FFMA kernel
   if (p.splitk > 1 && !(p.epi & (EPI_ATOMIC | EPI_SCATTER))) return false;

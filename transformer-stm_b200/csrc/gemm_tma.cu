@@ -119,11 +119,22 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tma_kernel(const __grid_cons
       const float* bias = (p.epi & EPI_BIAS) ? p.bias + z * p.bias_bs : nullptr;
       const float alpha = ((p.epi & EPI_ALPHA0) && z == 0) ? p.alpha0 : p.alpha;
       const float* coef = (p.epi & EPI_BN_BWD) ? p.epi_coef + z * p.epi_coef_bs : nullptr;
-      mbar_wait(&acc_full[buf], (it >> 1) & 1);
-      tc_fence_after();
       const uint32_t trow = tmem_base + buf * BN + ((uint32_t)(quad * 32) << 16);
+      bool waited = false;
 #pragma unroll 1
       for (int c0 = cg * 16; c0 < BN; c0 += 64) {
+        // global operands of this chunk's 4 row groups first: they do not depend on the accumulator
+        const int n0 = nt * BN + c0 + ec;
+        EpiOps ops[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int m = mt * BM + quad * 32 + er + 8 * i;
+          if (m < p.M) ops[i] = epilogue_load<E>(p, aux, m, n0, coef != nullptr);
+        }
+        const float4 b4 = bias ? __ldg(reinterpret_cast<const float4*>(bias + n0)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        float4 cf[3];
+        if (coef) { cf[0] = __ldg(reinterpret_cast<const float4*>(coef + n0)); cf[1] = __ldg(reinterpret_cast<const float4*>(coef + p.N + n0)); cf[2] = __ldg(reinterpret_cast<const float4*>(coef + 2 * p.N + n0)); }
+        if (!waited) { mbar_wait(&acc_full[buf], (it >> 1) & 1); tc_fence_after(); waited = true; }
         float v[16];
         tmem_ld16(trow + c0, v);
 #pragma unroll
@@ -134,10 +145,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tma_kernel(const __grid_cons
           const int rr = er + 8 * i;
           const int m = mt * BM + quad * 32 + rr;
           const float4 acc = *reinterpret_cast<const float4*>(stg + rr * 20 + ec);
-          if (m < p.M) epilogue_f4<E>(p, acc, Cp, aux, bias, alpha, m, nt * BN + c0 + ec, coef);
+          if (m < p.M) epilogue_apply<E>(p, acc, Cp, aux, b4, alpha, m, n0, coef ? cf : nullptr, ops[i]);
         }
         __syncwarp();
       }
+      if (!waited) { mbar_wait(&acc_full[buf], (it >> 1) & 1); tc_fence_after(); }
       tc_fence_before();
       if (lane == 0) mbar_arrive(&acc_empty[buf]);
     }
@@ -228,7 +240,7 @@ cudaError_t launch_tma_bn(const GemmP& p, int bn, cudaStream_t s) {
   if (bn == 128) return launch_tma_cfg<128, E>(p, s);
   return launch_tma_cfg<64, E>(p, s);
 }
-constexpr uint32_t kTmaEpiKinds = EPI_GELU | EPI_RESID | EPI_GELU_BWD;
+constexpr uint32_t kTmaEpiKinds = EPI_GELU | EPI_RESID | EPI_GELU_BWD | EPI_PHILOX;
 }  // namespace
 
 cudaError_t launch_transpose_weights(const float* src, float* dst, float* dst2, const TrDesc* descs_dev, int ndesc, int total_tiles, cudaStream_t s) {
@@ -259,6 +271,8 @@ cudaError_t launch_gemm_tma(const GemmP& p, cudaStream_t s) {
   if (kind == EPI_RESID) return launch_tma_bn<EPI_RESID>(p, bn, s);
   if (kind == EPI_GELU) return launch_tma_bn<EPI_GELU>(p, bn, s);
   if (kind == EPI_GELU_BWD) return launch_tma_bn<EPI_GELU_BWD>(p, bn, s);
+  if (kind == (EPI_RESID | EPI_PHILOX)) return launch_tma_bn<EPI_RESID | EPI_PHILOX>(p, bn, s);     // dropout mask drawn in the epilogue
+  if (kind == (EPI_GELU | EPI_PHILOX)) return launch_tma_bn<EPI_GELU | EPI_PHILOX>(p, bn, s);
   set_error("gemm_tma: no instantiation for epilogue " + std::to_string(p.epi));
   return cudaErrorNotSupported;
 }

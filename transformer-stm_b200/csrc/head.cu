@@ -23,7 +23,7 @@ __device__ __forceinline__ float block_sum(float v, float* red) {   // red: 8 fl
 // ---- forward: grid = B, block = 256.  Shared: feat[F] + p1[PH] ------------------------------------------------------------
 __global__ void __launch_bounds__(HT) head_fwd_kernel(const HeadP p) {
   extern __shared__ float sh[];
-  float* s_feat = sh; float* s_p1 = sh + p.F;
+  float* s_feat = sh; float* s_p1 = sh + p.F; float* s_part = s_p1 + p.PH;     // s_part: [8][PH] partial sums of Proc_Dense_2
   __shared__ float red[8];
   __shared__ int s_last;
   const int b = blockIdx.x, tid = threadIdx.x;
@@ -52,16 +52,37 @@ __global__ void __launch_bounds__(HT) head_fwd_kernel(const HeadP p) {
       s_p1[i] = a; p.p1[(long long)b * PH + i] = a;
     }
     __syncthreads();
-    for (int j = tid; j < PH; j += HT) {
-      float a0 = p.b2[j], a1 = 0.f, a2 = 0.f, a3 = 0.f;
-      int i = 0;
-      for (; i + 3 < PH; i += 4) {
-        a0 = fmaf(s_p1[i], p.w2[(long long)i * PH + j], a0); a1 = fmaf(s_p1[i + 1], p.w2[(long long)(i + 1) * PH + j], a1);
-        a2 = fmaf(s_p1[i + 2], p.w2[(long long)(i + 2) * PH + j], a2); a3 = fmaf(s_p1[i + 3], p.w2[(long long)(i + 3) * PH + j], a3);
+    if ((PH & 3) == 0 && PH <= 4 * HT) {
+      // thread = (group of 4 consecutive outputs, slice of the contraction): many independent 16-byte weight loads in flight
+      const int groups = PH >> 2, slices = HT / groups > 0 ? min(HT / groups, 8) : 1;
+      const int grp = tid % groups, sl = tid / groups;
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (sl < slices) {
+        const int per = (PH + slices - 1) / slices, i0 = sl * per, i1 = min(PH, i0 + per);
+        const float4* w = reinterpret_cast<const float4*>(p.w2) + grp;
+#pragma unroll 8
+        for (int i = i0; i < i1; ++i) {
+          const float4 wv = __ldg(w + (long long)i * groups);
+          const float a = s_p1[i];
+          acc.x = fmaf(a, wv.x, acc.x); acc.y = fmaf(a, wv.y, acc.y); acc.z = fmaf(a, wv.z, acc.z); acc.w = fmaf(a, wv.w, acc.w);
+        }
       }
-      for (; i < PH; ++i) a0 = fmaf(s_p1[i], p.w2[(long long)i * PH + j], a0);
-      const float o = fmaxf((a0 + a1) + (a2 + a3), 0.f);
-      s_feat[D + j] = o; feat[D + j] = o;                 // concatenate([img, proc])  :347
+      float4* part = reinterpret_cast<float4*>(s_part);
+      if (sl < slices) part[sl * groups + grp] = acc;
+      __syncthreads();
+      for (int j = tid; j < PH; j += HT) {
+        float a = p.b2[j];
+        for (int q = 0; q < slices; ++q) a += s_part[q * PH + j];
+        const float o = fmaxf(a, 0.f);
+        s_feat[D + j] = o; feat[D + j] = o;               // concatenate([img, proc])  :347
+      }
+    } else {
+      for (int j = tid; j < PH; j += HT) {
+        float a = p.b2[j];
+        for (int i = 0; i < PH; ++i) a = fmaf(s_p1[i], p.w2[(long long)i * PH + j], a);
+        const float o = fmaxf(a, 0.f);
+        s_feat[D + j] = o; feat[D + j] = o;
+      }
     }
   }
   __syncthreads();
@@ -120,6 +141,7 @@ __global__ void __launch_bounds__(HT) head_bwd_image_kernel(const HeadP p) {
       s_dz2[j] = g; p.dz2[(long long)b * PH + j] = g;
     }
     __syncthreads();
+#pragma unroll 4
     for (int i = warp; i < PH; i += HT / 32) {           // d p1 = dz2 . W2^T, through relu of Proc_Dense_1 (one warp per row of W2)
       const float* w = p.w2 + (long long)i * PH;
       float a = 0.f;
@@ -152,6 +174,7 @@ __global__ void __launch_bounds__(HT) head_bwd_param_kernel(const HeadP p, int t
   if (job < tiles2) {
     const int i0 = (job / tn) * 32, j = (job % tn) * 32 + tx;
     float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 8
     for (int b = 0; b < B; ++b) {
       const float g = j < PH ? p.dz2[(long long)b * PH + j] : 0.f;
 #pragma unroll
@@ -169,6 +192,7 @@ __global__ void __launch_bounds__(HT) head_bwd_param_kernel(const HeadP p, int t
       float w[8];
 #pragma unroll
       for (int k = 0; k < 8; ++k) w[k] = 0.f;
+#pragma unroll 4
       for (int b = 0; b < B; ++b) {
         s2 += p.dz2[(long long)b * PH + i];
         const float g = p.dz1[(long long)b * PH + i];
@@ -188,6 +212,7 @@ __global__ void __launch_bounds__(HT) head_bwd_param_kernel(const HeadP p, int t
     for (int e = tid; e < p.F * nc; e += HT) {
       const int f = e / nc, c = e - f * nc;
       float a = 0.f;
+#pragma unroll 8
       for (int b = 0; b < B; ++b) a = fmaf(p.feat[(long long)b * p.F + f], p.dpred[(long long)b * nc + c], a);
       p.g_fw[e] = a;
     }
@@ -199,6 +224,7 @@ __global__ void __launch_bounds__(HT) head_bwd_param_kernel(const HeadP p, int t
   } else if (job == 2 && p.cls_ln) {
     for (int i = tid; i < D; i += HT) {
       float dg = 0.f, db = 0.f;
+#pragma unroll 8
       for (int b = 0; b < B; ++b) {
         const float g = p.dfeat[(long long)b * p.F + i];
         dg = fmaf(g, (p.x2[(long long)b * p.x2_bs + i] - p.h_mean[b]) * p.h_rstd[b], dg);
@@ -211,7 +237,7 @@ __global__ void __launch_bounds__(HT) head_bwd_param_kernel(const HeadP p, int t
 }  // namespace
 
 cudaError_t launch_head_fwd(const HeadP& p, cudaStream_t s) {
-  const size_t smem = (size_t)(p.F + p.PH) * sizeof(float);
+  const size_t smem = (size_t)(p.F + 9 * p.PH) * sizeof(float);
   if (smem > 48 * 1024) { set_error("head: feature + hidden width too large for the fused head kernel"); return cudaErrorInvalidValue; }
   head_fwd_kernel<<<p.B, HT, smem, s>>>(p);
   CVT_LAUNCH_CHECK();

@@ -176,14 +176,15 @@ __global__ void dwproj_fwd_kernel(const __grid_constant__ DwProjP p) {
   }
 }
 
-// block = (32 channels, 8 partial lanes): the per-CTA partial slices of the statistics are summed 8-way in parallel
-__global__ void __launch_bounds__(256) bn_finalize_kernel(const __grid_constant__ BnFinalizeP p) {
-  __shared__ double red[2][8][33];
+// block = (32 channels, 32 partial lanes): the per-CTA partial slices of the statistics are summed 32-way in parallel
+__global__ void __launch_bounds__(1024) bn_finalize_kernel(const __grid_constant__ BnFinalizeP p) {
+  __shared__ double red[2][32][33];
   const int i = blockIdx.x * 32 + threadIdx.x;      // (z, c)
   const bool ok = i < 3 * p.D;
   double s1 = 0.0, s2 = 0.0;
   if (ok && p.training) {
-    for (int k = threadIdx.y; k < p.nparts; k += 8) {
+#pragma unroll 4
+    for (int k = threadIdx.y; k < p.nparts; k += 32) {
       s1 += (double)p.stats[(long long)k * 6 * p.D + i]; s2 += (double)p.stats[(long long)k * 6 * p.D + 3 * p.D + i];
     }
   }
@@ -193,7 +194,7 @@ __global__ void __launch_bounds__(256) bn_finalize_kernel(const __grid_constant_
   float mu, var;
   if (p.training) {
     s1 = 0.0; s2 = 0.0;
-    for (int k = 0; k < 8; ++k) { s1 += red[0][k][threadIdx.x]; s2 += red[1][k][threadIdx.x]; }
+    for (int k = 0; k < 32; ++k) { s1 += red[0][k][threadIdx.x]; s2 += red[1][k][threadIdx.x]; }
     const double n = (double)p.count;
     const double m = s1 / n;
     double v = s2 / n - m * m;
@@ -553,7 +554,7 @@ cudaError_t launch_dwproj_fwd(const DwProjP& p, cudaStream_t s) {
 }
 
 cudaError_t launch_bn_finalize(const BnFinalizeP& p, cudaStream_t s) {
-  bn_finalize_kernel<<<cdiv(3 * p.D, 32), dim3(32, 8), 0, s>>>(p);
+  bn_finalize_kernel<<<cdiv(3 * p.D, 32), dim3(32, 32), 0, s>>>(p);
   CVT_LAUNCH_CHECK();
   return cudaSuccess;
 }
