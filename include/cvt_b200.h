@@ -121,6 +121,11 @@ CVT_API int  cvt_train_step(cvt_model* m, const float* img_dev, const float* pro
 /* same from host buffers (pinned staging inside): the call `model.fit` makes per batch */
 CVT_API int  cvt_train_step_host(cvt_model* m, const float* img, const float* proc, const float* y, int batch, float lr,
                          float* loss, float* mae);
+/* the batch loop of one fit epoch (models/CvT(Par).py:475-476) from host arrays in the caller's (shuffled) order: batches of
+ * `batch` samples, last partial batch kept; loss_out / mae_out [ceil(n / batch)].  Host->device copies of batch i+1 overlap the
+ * step on batch i (pinned host memory makes them asynchronous). */
+CVT_API int  cvt_train_epoch_host(cvt_model* m, const float* img, const float* proc, const float* y, int64_t n, int batch, float lr,
+                          float* loss_out, float* mae_out);
 /* evaluation (validation pass of fit): forward(training=0) + MSE/MAE sums over n host samples */
 CVT_API int  cvt_evaluate_host(cvt_model* m, const float* img, const float* proc, const float* y, int64_t n,
                        float* loss, float* mae);

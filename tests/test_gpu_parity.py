@@ -183,3 +183,28 @@ def test_tf32_tensor_core_mode_tracks_oracle(hw, batch, cls):
     bad, report = compare_grads(eng, r["grads"], tol=2e-2)
     assert not bad, "tf32 gradient mismatches:\n" + fmt(report)
     eng.close()
+
+
+@pytest.mark.parametrize("precision", ["fp32", "tf32"])
+def test_epoch_loop_equals_step_by_step(precision):
+    """cvt_train_epoch_host (double-buffered copies, CUDA-graph replays, last partial batch kept as model.fit does,
+    models/CvT(Par).py:475) walks the same trajectory as one cvt_train_step_host call per batch, and the pipelined predict
+    equals a single-chunk predict.  Tolerance: the weight-gradient kernels add with floating-point atomics."""
+    n, bs = 22, 4                                           # 5 full batches + a partial one of 2
+    spec, e1, params, img, proc, y = make_pair(batch=n, precision=precision, hw=(32, 32), drop_rate=0.1, max_batch=bs)
+    e2 = T.CvtEngine(e1.cfg)
+    e2.set_params(params)
+    for e in (e1, e2):
+        e.set_dropout("philox", 99)
+    l1, m1 = [], []
+    for o in range(0, n, bs):
+        l, a = e1.train_step(img[o:o + bs], proc[o:o + bs], y[o:o + bs], 1e-3)
+        l1.append(l); m1.append(a)
+    l2, m2 = e2.train_epoch(img, proc, y, bs, 1e-3)
+    tol = 1e-5 if precision == "fp32" else 2e-3
+    assert len(l2) == len(l1) == 6
+    assert rel_err(l2, l1) <= tol and rel_err(m2, m1) <= tol, (l1, list(l2))
+    # (weights with an analytically zero gradient, e.g. the key biases, random-walk under Adam on atomics noise: compare outputs)
+    assert rel_err(e2.predict(img, proc), e1.predict(img, proc)) <= (1e-3 if precision == "fp32" else 2e-2)
+    assert rel_err(e2.predict(img, proc), np.concatenate([e2.predict(img[o:o + bs], proc[o:o + bs]) for o in range(0, n, bs)])) <= 1e-6
+    e1.close(); e2.close()

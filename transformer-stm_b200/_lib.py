@@ -47,6 +47,7 @@ _PROTOS = {
     "cvt_loss_backward": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
     "cvt_adam_step": (C.c_int, [C.c_void_p, C.c_float]),
     "cvt_train_step": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float]),
+    "cvt_train_epoch_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_void_p, C.c_void_p]),
     "cvt_train_step_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float,
                                       C.POINTER(C.c_float), C.POINTER(C.c_float)]),
     "cvt_evaluate_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,

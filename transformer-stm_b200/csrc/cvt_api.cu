@@ -242,6 +242,9 @@ static void carve(Model* m, Bump& b) {
   m->in_proc = b.take<float>(MB * std::max(1, c.proc_dim));
   m->in_y = b.take<float>(MB * c.num_classes);
   m->out_pred = b.take<float>(MB * c.num_classes);
+  m->in_img2 = b.take<float>(maxIn > 0 ? MB * (int64_t)c.image_h * c.image_w * c.in_chans : 0);
+  m->in_proc2 = b.take<float>(MB * std::max(1, c.proc_dim));
+  m->in_y2 = b.take<float>(MB * c.num_classes);
   m->lr_dev = b.take<float>(4);
   m->Pt = b.take<float>(m->n_train + m->n_pt_extra);
   m->Pr = b.take<float>(m->n_train);
@@ -408,6 +411,8 @@ int cvt_create(const cvt_config* cfg, cvt_model** out) {
   }
   API_CUDA(cudaMemsetAsync(m->head_ticket, 0, 16, m->stream));
   API_CUDA(cudaMallocHost(&m->pin_metrics, 4 * sizeof(float)));
+  API_CUDA(cudaStreamCreateWithFlags(&m->copy_stream, cudaStreamNonBlocking));
+  for (int i = 0; i < 2; ++i) { API_CUDA(cudaEventCreateWithFlags(&m->ev_copy[i], cudaEventDisableTiming)); API_CUDA(cudaEventCreateWithFlags(&m->ev_done[i], cudaEventDisableTiming)); }
   API_CUDA(cudaStreamSynchronize(m->stream));
   *out = h;
   return CVT_OK;
@@ -421,6 +426,9 @@ void cvt_destroy(cvt_model* h) {
   if (m->stream) { cudaStreamSynchronize(m->stream); cudaStreamDestroy(m->stream); }
   if (m->workspace) cudaFree(m->workspace);
   if (m->pin_metrics) cudaFreeHost(m->pin_metrics);
+  if (m->pin_series) cudaFreeHost(m->pin_series);
+  if (m->copy_stream) { cudaStreamSynchronize(m->copy_stream); cudaStreamDestroy(m->copy_stream); }
+  for (int i = 0; i < 2; ++i) { if (m->ev_copy[i]) cudaEventDestroy(m->ev_copy[i]); if (m->ev_done[i]) cudaEventDestroy(m->ev_done[i]); }
   delete h;
 }
 
@@ -1173,6 +1181,63 @@ int cvt_train_step_host(cvt_model* h, const float* img, const float* proc, const
   return CVT_OK;
 }
 
+// ---- double-buffered host -> device staging ----------------------------------------------------------------------------
+struct Staging { float* img; float* proc; float* y; };
+static Staging staging_of(Model* m, int slot) {
+  return slot ? Staging{m->in_img2, m->in_proc2, m->in_y2} : Staging{m->in_img, m->in_proc, m->in_y};
+}
+// enqueue the copies of chunk `i` on the copy stream (after the step that last read this slot) and make the model stream wait for them
+static int stage_chunk(Model* m, int64_t i, const float* img, const float* proc, const float* y, int B) {
+  const cvt_config& c = m->cfg;
+  const int slot = (int)(i & 1); const Staging st = staging_of(m, slot);
+  const size_t per = (size_t)c.image_h * c.image_w * c.in_chans;
+  if (i >= 2) API_CUDA(cudaStreamWaitEvent(m->copy_stream, m->ev_done[slot], 0));
+  API_CUDA(cudaMemcpyAsync(st.img, img, B * per * sizeof(float), cudaMemcpyHostToDevice, m->copy_stream));
+  if (c.proc_dim > 0) API_CUDA(cudaMemcpyAsync(st.proc, proc, (size_t)B * c.proc_dim * sizeof(float), cudaMemcpyHostToDevice, m->copy_stream));
+  if (y) API_CUDA(cudaMemcpyAsync(st.y, y, (size_t)B * c.num_classes * sizeof(float), cudaMemcpyHostToDevice, m->copy_stream));
+  API_CUDA(cudaEventRecord(m->ev_copy[slot], m->copy_stream));
+  API_CUDA(cudaStreamWaitEvent(m->stream, m->ev_copy[slot], 0));
+  return CVT_OK;
+}
+
+static int ensure_pin_series(Model* m, int64_t floats) {
+  if (m->pin_series_cap >= floats) return CVT_OK;
+  API_CUDA(cudaStreamSynchronize(m->stream));
+  if (m->pin_series) cudaFreeHost(m->pin_series);
+  m->pin_series = nullptr; m->pin_series_cap = 0;
+  API_CUDA(cudaMallocHost(&m->pin_series, (size_t)(floats + 64) * sizeof(float)));
+  m->pin_series_cap = floats + 64;
+  return CVT_OK;
+}
+
+// The batch loop of one `model.fit` epoch (models/CvT(Par).py:475): n samples in the caller's (already shuffled) order, batches of
+// `batch` with the last partial batch kept, per-batch loss / MAE returned.  Batch i+1 is copied while batch i trains.
+int cvt_train_epoch_host(cvt_model* h, const float* img, const float* proc, const float* y, int64_t n, int batch, float lr,
+                         float* loss_out, float* mae_out) {
+  if (!h || !img || !y || n < 1) { set_error("cvt_train_epoch_host: bad argument"); return CVT_ERR_INVALID; }
+  Model* m = &h->m; const cvt_config& c = m->cfg;
+  if (c.proc_dim > 0 && !proc) { set_error("cvt_train_epoch_host: this model needs process parameters"); return CVT_ERR_INVALID; }
+  int r = check_batch(m, batch, "cvt_train_epoch_host"); if (r) return r;
+  API_CUDA(cudaSetDevice(c.device));
+  const int64_t nb = (n + batch - 1) / batch;
+  r = ensure_pin_series(m, 2 * nb); if (r) return r;
+  const size_t per = (size_t)c.image_h * c.image_w * c.in_chans;
+  const long long l0 = g_launch_count;
+  for (int64_t i = 0; i < nb; ++i) {
+    const int64_t o = i * batch; const int B = (int)std::min<int64_t>(batch, n - o);
+    r = stage_chunk(m, i, img + o * per, proc ? proc + o * c.proc_dim : nullptr, y + o * c.num_classes, B); if (r) return r;
+    const Staging st = staging_of(m, (int)(i & 1));
+    r = train_step_dev(m, st.img, c.proc_dim > 0 ? st.proc : nullptr, st.y, B, lr); if (r) return r;
+    API_CUDA(cudaMemcpyAsync(m->pin_series + 2 * i, m->metrics, 2 * sizeof(float), cudaMemcpyDeviceToHost, m->stream));
+    API_CUDA(cudaEventRecord(m->ev_done[i & 1], m->stream));
+    g_last_inputs = {st.img, c.proc_dim > 0 ? st.proc : nullptr};
+  }
+  API_CUDA(cudaStreamSynchronize(m->stream));
+  for (int64_t i = 0; i < nb; ++i) { if (loss_out) loss_out[i] = m->pin_series[2 * i]; if (mae_out) mae_out[i] = m->pin_series[2 * i + 1]; }
+  m->launches += g_launch_count - l0;
+  return CVT_OK;
+}
+
 int cvt_predict_host(cvt_model* h, const float* img, const float* proc, int64_t n, float* out) {
   if (!h || !img || !out || n < 0) { set_error("cvt_predict_host: bad argument"); return CVT_ERR_INVALID; }
   Model* m = &h->m; const cvt_config& c = m->cfg;
@@ -1180,15 +1245,20 @@ int cvt_predict_host(cvt_model* h, const float* img, const float* proc, int64_t 
   API_CUDA(cudaSetDevice(c.device));
   const size_t per = (size_t)c.image_h * c.image_w * c.in_chans;
   const long long l0 = g_launch_count;
-  for (int64_t o = 0; o < n; o += c.max_batch) {
+  { const int rp = ensure_pin_series(m, n * c.num_classes); if (rp) return rp; }       // device -> pinned -> out: the loop never blocks
+  Staging last = staging_of(m, 0);
+  int64_t i = 0;
+  for (int64_t o = 0; o < n; o += c.max_batch, ++i) {        // chunk i+1 is copied while chunk i runs
     const int B = (int)std::min<int64_t>(c.max_batch, n - o);
-    API_CUDA(cudaMemcpyAsync(m->in_img, img + o * per, B * per * sizeof(float), cudaMemcpyHostToDevice, m->stream));
-    if (c.proc_dim > 0) API_CUDA(cudaMemcpyAsync(m->in_proc, proc + o * c.proc_dim, (size_t)B * c.proc_dim * sizeof(float), cudaMemcpyHostToDevice, m->stream));
-    { const int rf = infer_forward(m, m->in_img, c.proc_dim > 0 ? m->in_proc : nullptr, B); if (rf) return rf; }
-    API_CUDA(cudaMemcpyAsync(out + o * c.num_classes, m->pred, (size_t)B * c.num_classes * sizeof(float), cudaMemcpyDeviceToHost, m->stream));
+    { const int rs = stage_chunk(m, i, img + o * per, proc ? proc + o * c.proc_dim : nullptr, nullptr, B); if (rs) return rs; }
+    last = staging_of(m, (int)(i & 1));
+    { const int rf = infer_forward(m, last.img, c.proc_dim > 0 ? last.proc : nullptr, B); if (rf) return rf; }
+    API_CUDA(cudaMemcpyAsync(m->pin_series + o * c.num_classes, m->pred, (size_t)B * c.num_classes * sizeof(float), cudaMemcpyDeviceToHost, m->stream));
+    API_CUDA(cudaEventRecord(m->ev_done[i & 1], m->stream));
   }
   API_CUDA(cudaStreamSynchronize(m->stream));
-  g_last_inputs = {m->in_img, c.proc_dim > 0 ? m->in_proc : nullptr};
+  memcpy(out, m->pin_series, (size_t)n * c.num_classes * sizeof(float));
+  g_last_inputs = {last.img, c.proc_dim > 0 ? last.proc : nullptr};
   m->launches += g_launch_count - l0;
   return CVT_OK;
 }

@@ -79,6 +79,10 @@ struct Model {
   // staging for host-buffer entry points
   float *in_img = nullptr, *in_proc = nullptr, *in_y = nullptr, *out_pred = nullptr;
   float *pin_metrics = nullptr;           // pinned host [2]
+  // double-buffered host -> device staging of the epoch / predict loops: copies of batch i+1 overlap the step on batch i
+  float *in_img2 = nullptr, *in_proc2 = nullptr, *in_y2 = nullptr;
+  cudaStream_t copy_stream = nullptr; cudaEvent_t ev_copy[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
+  float* pin_series = nullptr; int64_t pin_series_cap = 0;     // pinned host: per-batch {loss, mae} of an epoch
 
   void* workspace = nullptr;
   int64_t workspace_bytes = 0;

@@ -184,6 +184,20 @@ class CvtEngine:
                                              t.ctypes.data_as(C.c_void_p), n, lr, C.byref(loss), C.byref(mae)), "cvt_train_step_host")
         return loss.value, mae.value
 
+    def train_epoch(self, img, proc, y, batch: int, lr: float):
+        """One pass over (img, proc, y) in the given order, batches of `batch` (last partial batch kept, models/CvT(Par).py:475);
+        returns per-batch (loss, mae) arrays.  Copies of batch i+1 overlap the step on batch i."""
+        a = self._img(img)
+        n = a.shape[0]
+        p = _f32(proc, (n, self.cfg.proc_dim)) if (self.cfg.proc_dim > 0 and proc is not None) else None
+        t = _f32(y, (n, self.cfg.num_classes))
+        nb = (n + batch - 1) // batch
+        loss = np.empty(nb, np.float32); mae = np.empty(nb, np.float32)
+        L.check(self.lib.cvt_train_epoch_host(self.h, a.ctypes.data_as(C.c_void_p), p.ctypes.data_as(C.c_void_p) if p is not None else None,
+                                              t.ctypes.data_as(C.c_void_p), n, int(batch), lr, loss.ctypes.data_as(C.c_void_p),
+                                              mae.ctypes.data_as(C.c_void_p)), "cvt_train_epoch_host")
+        return loss, mae
+
     def evaluate(self, img, proc, y):
         a = self._img(img)
         n = a.shape[0]

@@ -313,13 +313,14 @@ class Model:
                 cb.on_epoch_begin(epoch)
             t0 = time.time()
             order = rng.permutation(n) if shuffle else np.arange(n)
-            lsum = asum = 0.0
-            for o in range(0, n, bs):
-                idx = order[o:o + bs]                      # Keras keeps the last partial batch
-                bi = img[idx]
-                bp = proc[idx] if has_proc else None
-                loss, mae = eng.train_step(bi, bp, yy[idx], float(self.optimizer.learning_rate))
-                lsum += loss * len(idx); asum += mae * len(idx)
+            # one native call per epoch: the batch loop (last partial batch kept, as Keras does) runs inside the library with
+            # host->device copies double-buffered against the train steps
+            ei = np.ascontiguousarray(img[order]) if shuffle else img
+            ep = (np.ascontiguousarray(proc[order]) if shuffle else proc) if has_proc else None
+            ey = np.ascontiguousarray(yy[order]) if shuffle else yy
+            losses, maes = eng.train_epoch(ei, ep, ey, bs, float(self.optimizer.learning_rate))
+            counts = np.minimum(bs, n - bs * np.arange(len(losses)))
+            lsum = float(np.dot(losses.astype(np.float64), counts)); asum = float(np.dot(maes.astype(np.float64), counts))
             logs = {"loss": lsum / n}
             if "mae" in self.metrics_names:
                 logs["mae"] = asum / n
