@@ -15,6 +15,8 @@ __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
 }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 struct Band { int CH, TR, nchunk, nband, ntiles; };
 
@@ -121,8 +123,8 @@ __global__ void __launch_bounds__(NT, 2) dwplane_bwd_kernel(const __grid_constan
   const int D = p.D, H = p.H, W = p.W, CH = bd.CH;
   const int psz = (TRC + 2) * W * CH;
   float* xpl = smem;                    // xn band
-  float* dpl = smem + psz;              // d(conv_z) band
-  float* dxs = smem + 2 * psz;          // dx band [TRC][W][CH]
+  float* dpl0 = smem + psz;             // d(conv_z) bands, double-buffered: branch z+1 streams in while branch z is consumed
+  float* dxs = smem + 3 * psz;          // dx band [TRC][W][CH]
   float* sdw = dxs + TRC * W * CH;      // [27][D] weight-gradient partial of this CTA
   float* sitem = sdw + 27 * D;          // [9][W][CH] per-item weight-gradient sums of this (tile, z)
   const int tid = threadIdx.x;
@@ -137,9 +139,13 @@ __global__ void __launch_bounds__(NT, 2) dwplane_bwd_kernel(const __grid_constan
     const int rend = min(TRC, H - r0);
     __syncthreads();
     load_band(xpl, p.xn + base, D, H, W, r0, TRC, CH);
+    load_band(dpl0, p.dconv + base, D, H, W, r0, TRC, CH);
+    cp_async_commit();
+    load_band(dpl0 + psz, p.dconv + p.bs + base, D, H, W, r0, TRC, CH);
+    cp_async_commit();
     for (int z = 0; z < 3; ++z) {
-      load_band(dpl, p.dconv + z * p.bs + base, D, H, W, r0, TRC, CH);
-      cp_async_wait_all();
+      const float* dpl = dpl0 + (z & 1) * psz;
+      if (z < 2) cp_async_wait<1>(); else cp_async_wait<0>();
       __syncthreads();
       for (int it = tid; it < 2 * half; it += NT) {
         const int role = it / half, rem = it - role * half, j = rem / q4n, c = (rem - j * q4n) << 2;
@@ -191,7 +197,8 @@ __global__ void __launch_bounds__(NT, 2) dwplane_bwd_kernel(const __grid_constan
           for (int k = 0; k < 9; ++k) *reinterpret_cast<float4*>(sitem + (k * W + j) * CH + c) = aw[k];
         }
       }
-      __syncthreads();                   // dpl is reloaded for the next z; sitem is complete
+      __syncthreads();                   // this d band may be overwritten; sitem is complete
+      if (z == 0) { load_band(dpl0, p.dconv + 2 * p.bs + base, D, H, W, r0, TRC, CH); cp_async_commit(); }
       if (p.ddw) {
         for (int o = tid; o < 9 * CH; o += NT) {
           const int k = o / CH, c = o - k * CH;
@@ -257,7 +264,7 @@ cudaError_t launch_dwplane_bwd(const DwProjBwdP& p, cudaStream_t s) {
   Band bd;
   if (p.method[0] != 0 || p.method[1] != 0 || p.method[2] != 0 || p.coef || !make_band(p.B, p.H, p.W, p.D, &bd)) return cudaErrorNotSupported;
   if (p.ddw && !p.ddw_part) return cudaErrorInvalidValue;
-  const size_t smem = ((size_t)2 * (bd.TR + 2) * p.W * bd.CH + (size_t)bd.TR * p.W * bd.CH + 27 * p.D + (size_t)9 * p.W * bd.CH) * sizeof(float);
+  const size_t smem = ((size_t)3 * (bd.TR + 2) * p.W * bd.CH + (size_t)bd.TR * p.W * bd.CH + 27 * p.D + (size_t)9 * p.W * bd.CH) * sizeof(float);
   if (smem > 200 * 1024) return cudaErrorNotSupported;
   static bool configured = false;
   if (!configured) { CVT_CUDA(cudaFuncSetAttribute(dwplane_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); configured = true; }
