@@ -158,6 +158,10 @@ def main_b200(a):
     import transformer_stm_b200 as T
 
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    # stdout carries exactly one JSON line: anything libraries print there (e.g. NCCL's version banner) goes to stderr instead
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device — this arm has no CPU fallback (use --impl reference for the CPU baseline)")
     torch.cuda.set_device(local)
@@ -210,6 +214,7 @@ def main_b200(a):
     for i in range(max(a.warmup, 3)):
         step(i)
     eng.synchronize()
+    print("[bench] rank %d: warm-up done" % rank, file=sys.stderr, flush=True)
     sampler = ClockSampler(local) if rank == 0 else None
     if sampler:
         sampler.start(); time.sleep(0.3)
@@ -234,6 +239,7 @@ def main_b200(a):
     value = world * B * a.steps / (total_ms / 1e3)
 
     # ---- end to end through the host-buffer C-ABI call (H2D of the batch + D2H of loss/predictions inside the timed region)
+    print("[bench] rank %d: device-timed region done" % rank, file=sys.stderr, flush=True)
     # One call of the public host-buffer API over `steps` batches, the way model.fit / model.predict walk a dataset
     # (models/CvT(Par).py:475, CvT_test(Par).py:522): every batch is copied from pinned host memory inside the timed region and
     # its loss / predictions are read back; the library double-buffers the copies against the steps.
@@ -253,6 +259,7 @@ def main_b200(a):
         e_pred = eng.predict(e_img.numpy(), e_proc.numpy())
     barrier()
     e2e_s = torch.tensor([time.time() - t0], device="cuda")
+    print("[bench] rank %d: end-to-end region done" % rank, file=sys.stderr, flush=True)
     if dist is not None:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     e2e = world * B * a.steps / float(e2e_s.item())
@@ -301,7 +308,8 @@ def main_b200(a):
     if world == 1 and not a.no_cpu_baseline:
         r = cpu_reference_run(3, 1, B, a.mode, budget_s=15.0)
         line["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]}
-    print(json.dumps(line))
+    sys.stdout.flush()
+    os.write(json_fd, (json.dumps(line) + "\n").encode())
     eng.close()
     if dist is not None:
         dist.destroy_process_group()

@@ -1064,22 +1064,28 @@ static Model::GraphEntry* graph_slot(Model* m, int kind, const float* img, const
   return nullptr;                                        // first sighting: the caller runs eagerly (also warms every lazy initialiser)
 }
 
-// the stream work of one train step; per-step scalars come from m->lr_dev (set by the caller), so the sequence can be replayed
-static int train_step_body(Model* m, const float* img, const float* proc, const float* y, int B) {
+// the stream work of one train step; per-step scalars come from m->lr_dev (set by the caller), so the sequence can be replayed.
+// parts: 1 = forward + loss + backward, 2 = gradient all-reduce + Adam.  With more than one rank only part 1 is captured into the
+// graph: the NCCL collective is issued on the stream directly after the replay.
+static int train_step_body(Model* m, const float* img, const float* proc, const float* y, int B, int parts) {
   m->dyn = m->lr_dev;
   int rc = CVT_OK;
   do {
-    m->cur_y = y;                                        // the head kernel also emits loss, MAE and d pred (mse_loss_kernel otherwise)
-    const cudaError_t ef = forward_impl(m, img, proc, B, 1);
-    m->cur_y = nullptr;
-    if (ef != cudaSuccess) { rc = CVT_ERR_CUDA; break; }
-    if (backward_impl(m, img, proc, B, 1, -1, nullptr) != cudaSuccess) { rc = CVT_ERR_CUDA; break; }
-    if (m->nccl_comm && m->world > 1) {
-      // data parallel: sum of per-rank mean-loss gradients / world == gradient of the global-batch mean loss
-      const int r = g_nccl.allreduce(m->G, m->G, (size_t)m->n_train, /*ncclFloat32*/ 7, /*ncclSum*/ 0, m->nccl_comm, m->stream);
-      if (r != 0) { set_error(std::string("ncclAllReduce: ") + (g_nccl.errstr ? g_nccl.errstr(r) : "nccl error")); rc = CVT_ERR_NCCL; break; }
+    if (parts & 1) {
+      m->cur_y = y;                                      // the head kernel also emits loss, MAE and d pred (mse_loss_kernel otherwise)
+      const cudaError_t ef = forward_impl(m, img, proc, B, 1);
+      m->cur_y = nullptr;
+      if (ef != cudaSuccess) { rc = CVT_ERR_CUDA; break; }
+      if (backward_impl(m, img, proc, B, 1, -1, nullptr) != cudaSuccess) { rc = CVT_ERR_CUDA; break; }
     }
-    if (launch_adam(m->P, m->G, m->Mo, m->Vo, m->n_train, 0.f, 0.9f, 0.999f, 1e-7f, 1.f, m->stream, m->dyn) != cudaSuccess) { rc = CVT_ERR_CUDA; break; }
+    if (parts & 2) {
+      if (m->nccl_comm && m->world > 1) {
+        // data parallel: sum of per-rank mean-loss gradients / world == gradient of the global-batch mean loss
+        const int r = g_nccl.allreduce(m->G, m->G, (size_t)m->n_train, /*ncclFloat32*/ 7, /*ncclSum*/ 0, m->nccl_comm, m->stream);
+        if (r != 0) { set_error(std::string("ncclAllReduce: ") + (g_nccl.errstr ? g_nccl.errstr(r) : "nccl error")); rc = CVT_ERR_NCCL; break; }
+      }
+      if (launch_adam(m->P, m->G, m->Mo, m->Vo, m->n_train, 0.f, 0.9f, 0.999f, 1e-7f, 1.f, m->stream, m->dyn) != cudaSuccess) { rc = CVT_ERR_CUDA; break; }
+    }
   } while (0);
   m->dyn = nullptr;
   return rc;
@@ -1091,12 +1097,13 @@ static int train_step_dev(Model* m, const float* img, const float* proc, const f
   m->adam_t += 1;
   const float gs = (m->nccl_comm && m->world > 1) ? 1.f / (float)m->world : 1.f;
   API_CUDA(launch_set_step_params(m->lr_dev, adam_alpha(m, lr), gs, step, m->stream));
+  const int graph_parts = (m->nccl_comm && m->world > 1) ? 1 : 3;
   Model::GraphEntry* g = (m->use_graphs && !g_prof) ? graph_slot(m, GRAPH_TRAIN, img, proc, y, B) : nullptr;
   if (g && !g->exec) {
     const long long l0 = g_launch_count;
     cudaGraph_t graph = nullptr;
     API_CUDA(cudaStreamBeginCapture(m->stream, cudaStreamCaptureModeThreadLocal));
-    const int rc = train_step_body(m, img, proc, y, B);
+    const int rc = train_step_body(m, img, proc, y, B, graph_parts);
     const cudaError_t e = cudaStreamEndCapture(m->stream, &graph);
     m->dropout_step = step;                              // forward_impl advanced it while capturing; the replay below counts
     if (rc != CVT_OK || e != cudaSuccess || !graph) {
@@ -1116,9 +1123,9 @@ static int train_step_dev(Model* m, const float* img, const float* proc, const f
     g_launch_count += g->launches;
     if (philox) m->dropout_step = step + 1;
     m->last_batch = B; m->last_training = 1; m->have_forward = 1;
-    return CVT_OK;
+    return graph_parts == 3 ? CVT_OK : train_step_body(m, img, proc, y, B, 2);
   }
-  return train_step_body(m, img, proc, y, B);
+  return train_step_body(m, img, proc, y, B, 3);
 }
 
 // inference forward (training = 0) through the graph cache; falls back to eager issue on first sighting
