@@ -208,3 +208,33 @@ def test_epoch_loop_equals_step_by_step(precision):
     assert rel_err(e2.predict(img, proc), e1.predict(img, proc)) <= (1e-3 if precision == "fp32" else 2e-2)
     assert rel_err(e2.predict(img, proc), np.concatenate([e2.predict(img[o:o + bs], proc[o:o + bs]) for o in range(0, n, bs)])) <= 1e-6
     e1.close(); e2.close()
+
+
+@pytest.mark.parametrize("precision", ["fp32", "tf32"])
+def test_widened_config_inference_and_train_step(precision):
+    """BASELINE.json configs[4]: 3 stages with embed dims 64/192/384 (heads 1/3/6) on a 340x345 input, i.e. 7395 / 1892 / 485(+cls)
+    tokens - the shapes where the attention kernels walk 116 key tiles, rows are ragged against every tile size and the
+    depthwise band kernels see widths that are not powers of two.  Against the fp32 oracle:
+      fp32 mode  predictions 2e-4, loss 1e-5, every gradient tensor 1e-3 (max|a-b| / max|b|);
+      tf32 mode  predictions 5e-3, loss 2e-3, all gradients together 2e-2 in the L2 norm and every tensor 5e-2 - except the
+                 BatchNorm gamma of the stage-3 value branch (0.25): with 484 tokens per image that sum cancels to ~1e-4 of its
+                 terms, the fp32 kernels reproduce it to 2e-4, TF32 operand rounding (2^-11) does not."""
+    dims, heads, hw = (64, 192, 384), (1, 3, 6), (340, 345)
+    spec, eng, params, img, proc, y = make_pair("dw_bn", True, 5, 1, hw, dims=dims, heads=heads, batch=2, precision=precision, drop_rate=0.0)
+    tf32 = precision == "tf32"
+    pred = eng.predict(img, proc)
+    ref, _ = O.forward(spec, params, img, proc, dtype=torch.float32)
+    assert rel_err(pred, ref) <= (5e-3 if tf32 else 2e-4), (pred, ref)
+    eng.set_dropout("off")
+    loss, mae = eng.train_step(img, proc, y, 1e-3)
+    r = O.loss_and_grads(spec, params, img, proc, y, None, dtype=torch.float32)
+    assert abs(loss - r["loss"]) <= (2e-3 if tf32 else 1e-5) * abs(r["loss"]), (loss, r["loss"])
+    bad, report = compare_grads(eng, r["grads"], tol=5e-2 if tf32 else 1e-3)
+    if tf32:
+        bad = [(k, e) for k, e in bad if not (k == "stage3_transformer/attn/v_proj/bn/gamma" and e <= 0.25)]
+        got = eng.get_grads()
+        num = sum(float(((got[k].astype(np.float64) - g) ** 2).sum()) for k, g in r["grads"].items())
+        den = sum(float((g.astype(np.float64) ** 2).sum()) for g in r["grads"].values())
+        assert (num / den) ** 0.5 <= 2e-2, (num / den) ** 0.5
+    assert not bad, "widened-config gradient mismatches:\n" + fmt(report)
+    eng.close()
