@@ -175,7 +175,7 @@ cudaError_t launch_w(const WgradP& p, cudaStream_t s) {
   const int m_tiles = cdiv(p.Kin, BM), n_tiles = cdiv(p.N, BN);
   const int tiles = m_tiles * n_tiles * p.batch;
   const int total_steps = cdiv(p.tokens, KT);
-  int splits = cdiv(2 * kNumSMs, tiles);                        // ~2 waves worth of CTAs ...
+  int splits = kNumSMs / tiles;                                 // one CTA per SM (a single wave: prologue and the atomic epilogue are paid once) ...
   const int max_splits = total_steps / 8 > 0 ? total_steps / 8 : 1;   // ... but at least 8 steps (256 tokens) each
   if (splits > max_splits) splits = max_splits;
   if (splits < 1) splits = 1;
