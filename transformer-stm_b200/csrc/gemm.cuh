@@ -47,6 +47,7 @@ struct GemmP {
   const uint8_t* mask = nullptr; float mask_scale = 1.f;
   uint8_t* mask_gen = nullptr; uint32_t ph_k0 = 0, ph_k1 = 0, ph_site = 0, ph_step = 0, ph_thr = 0; const float* ph_dyn = nullptr;   // EPI_PHILOX
   const float* epi_coef = nullptr; long long epi_coef_bs = 0; int epi_skip_period = 0;   // EPI_BN_BWD (rows m % period == 0 are cls rows: identity)
+  long long* trace = nullptr;                  // diagnostics only (CVT_GEMM_TRACE): clock64 timeline of CTA 0 of gemm_tma_kernel
   int dbg = 0;                                 // diagnostics only (cvt_debug_gemm): bit 0 swaps LBO/SBO of MN-major descriptors
   float* aux = nullptr;                        // same indexing as C: GELU pre-activation (write) / saved activation (read)
 };

@@ -10,6 +10,9 @@
 //   epilogue   accumulator TMEM -> registers (tcgen05.ld 32x32b) -> per-warp smem transpose -> coalesced
 //              bias/GELU/mask/residual/atomic/scatter epilogue (identical arithmetic to the FFMA kernel).
 #include "gemm_fetch.cuh"
+#include <cstdio>
+#include <cstdlib>
+
 #include "gemm_epi.cuh"
 #include "model.cuh"
 #include "tc_common.cuh"
@@ -404,6 +407,15 @@ extern "C" CVT_API int cvt_debug_gemm(int a_mode, int b_mode, int M, int N, int 
     if (!gemm_tma_supports(p)) { cudaFree(dA); cudaFree(dB); cudaFree(dC); set_error("cvt_debug_gemm: shape not supported by the TMA kernel"); return CVT_ERR_INVALID; }
     e = launch_gemm_tma(p, 0);
     if (e != cudaSuccess) return fail(e);
+    if (getenv("CVT_GEMM_TRACE")) {                      // second (warm) launch with the clock64 timeline of CTA 0
+      long long* tr = nullptr; static long long h[8 + 30 * 8];
+      cudaMalloc(&tr, sizeof(h)); cudaMemset(tr, 0, sizeof(h));
+      p.trace = tr; e = launch_gemm_tma(p, 0); p.trace = nullptr;
+      cudaDeviceSynchronize(); cudaMemcpy(h, tr, sizeof(h), cudaMemcpyDeviceToHost); cudaFree(tr);
+      printf("gemm_tma trace M=%d N=%d K=%d: start 0, setup done %lld, exit %lld (cycles)\n", M, N, K, h[1] - h[0], h[2] - h[0]);
+      printf("tile | producer: slot issued | mma: acc_free full commit | epilogue: wait_begin acc_full done\n");
+      for (int i = 0; i < 30 && h[8 + i * 8 + 1]; ++i) { printf("%3d |", i); for (int k = 0; k < 8; ++k) printf(" %7lld", h[8 + i * 8 + k] ? h[8 + i * 8 + k] - h[0] : -1); printf("\n"); }
+    }
     if ((e = cudaDeviceSynchronize()) != cudaSuccess) return fail(e);
     if ((e = cudaMemcpy(C, dC, nc * 4, cudaMemcpyDeviceToHost)) != cudaSuccess) return fail(e);
     cudaFree(dA); cudaFree(dB); cudaFree(dC);

@@ -52,6 +52,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tma_kernel(const __grid_cons
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nk = cdiv(p.K, BK);
+  // diagnostics (CVT_GEMM_TRACE, tools/gemm_trace.py): clock64 timeline of CTA 0; p.trace is null in the model
+#define GEMM_TRACE(slot) do { if (p.trace && blockIdx.x == 0 && lane == 0) p.trace[(slot)] = clock64(); } while (0)
+  if (threadIdx.x == 0) GEMM_TRACE(0);
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB);
@@ -64,21 +67,24 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tma_kernel(const __grid_cons
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (threadIdx.x == 0) GEMM_TRACE(1);
 
   if (warp == 0) {
     // ===== TMA producer =====
     if (lane == 0) {
-      int stage = 0; uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      int stage = 0; uint32_t phase = 0; int itp = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++itp) {
         const int z = tile / (m_tiles * n_tiles), r = tile - z * (m_tiles * n_tiles);
         const int mt = r / n_tiles, nt = r - mt * n_tiles;
         for (int kt = 0; kt < nk; ++kt) {
           mbar_wait(&empty[stage], phase ^ 1);
+          if (kt == 0 && itp < 30) GEMM_TRACE(8 + itp * 8 + 0);
           mbar_arrive_expect_tx(&full[stage], A_STAGE + C::B_STAGE);
           tma_load_3d(sA + stage * A_STAGE, &tmA, &full[stage], kt * BK, mt * BM, z);
           tma_load_3d(sB + stage * C::B_STAGE, &tmB, &full[stage], kt * BK, nt * BN, z);
           if (++stage == NS) { stage = 0; phase ^= 1; }
         }
+        if (itp < 30) GEMM_TRACE(8 + itp * 8 + 1);
       }
     }
   } else if (warp == 1) {
@@ -89,10 +95,12 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tma_kernel(const __grid_cons
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
         const int buf = it & 1;
         mbar_wait(&acc_empty[buf], ((it >> 1) & 1) ^ 1);
+        if (it < 30) GEMM_TRACE(8 + it * 8 + 2);
         tc_fence_after();
         const uint32_t d = tmem_base + buf * BN;
         for (int kt = 0; kt < nk; ++kt) {
           mbar_wait(&full[stage], phase);
+          if (kt == 0 && it < 30) GEMM_TRACE(8 + it * 8 + 3);
           tc_fence_after();
           const uint32_t a0 = smem_u32(sA + stage * A_STAGE), b0 = smem_u32(sB + stage * C::B_STAGE);
 #pragma unroll
@@ -102,6 +110,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tma_kernel(const __grid_cons
           if (++stage == NS) { stage = 0; phase ^= 1; }
         }
         mma_commit(&acc_full[buf]);
+        if (it < 30) GEMM_TRACE(8 + it * 8 + 4);
       }
     }
   } else {
@@ -118,11 +127,44 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tma_kernel(const __grid_cons
       float* aux = p.aux ? p.aux + z * p.c_bs0 : nullptr;
       const float* bias = (p.epi & EPI_BIAS) ? p.bias + z * p.bias_bs : nullptr;
       const float alpha = ((p.epi & EPI_ALPHA0) && z == 0) ? p.alpha0 : p.alpha;
-      const float* coef = (p.epi & EPI_BN_BWD) ? p.epi_coef + z * p.epi_coef_bs : nullptr;
+      const float* coef = (E & EPI_BN_BWD) ? p.epi_coef + z * p.epi_coef_bs : nullptr;      // compile-time kind in this kernel
       const uint32_t trow = tmem_base + buf * BN + ((uint32_t)(quad * 32) << 16);
       bool waited = false;
+      const bool wide = (p.ldc & 7) == 0 && (p.ldr & 7) == 0;       // 32-byte aligned rows: 8 columns per lane, 16 rows per instruction
 #pragma unroll 1
       for (int c0 = cg * 16; c0 < BN; c0 += 64) {
+        if (wide) {
+          const int er8 = lane >> 1, ec8 = (lane & 1) << 3;
+          const int n0 = nt * BN + c0 + ec8;
+          EpiOps ops[2][2];
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+            const int m = mt * BM + quad * 32 + er8 + 16 * i;
+            if (m < p.M) { ops[i][0] = epilogue_load<E>(p, aux, m, n0, coef != nullptr); ops[i][1] = epilogue_load<E>(p, aux, m, n0 + 4, coef != nullptr); }
+          }
+          float4 b4[2] = {make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
+          if (bias) { b4[0] = __ldg(reinterpret_cast<const float4*>(bias + n0)); b4[1] = __ldg(reinterpret_cast<const float4*>(bias + n0 + 4)); }
+          EpiCoef cf0{}, cf1{};
+          if (coef) {
+            cf0.a = __ldg(reinterpret_cast<const float4*>(coef + n0)); cf0.e = __ldg(reinterpret_cast<const float4*>(coef + p.N + n0)); cf0.f = __ldg(reinterpret_cast<const float4*>(coef + 2 * p.N + n0));
+            cf1.a = __ldg(reinterpret_cast<const float4*>(coef + n0 + 4)); cf1.e = __ldg(reinterpret_cast<const float4*>(coef + p.N + n0 + 4)); cf1.f = __ldg(reinterpret_cast<const float4*>(coef + 2 * p.N + n0 + 4));
+          }
+          if (!waited) { if (warp == 2 && it < 30) GEMM_TRACE(8 + it * 8 + 5); mbar_wait(&acc_full[buf], (it >> 1) & 1); tc_fence_after(); waited = true; if (warp == 2 && it < 30) GEMM_TRACE(8 + it * 8 + 6); }
+          float v[16];
+          tmem_ld16(trow + c0, v);
+#pragma unroll
+          for (int j = 0; j < 16; j += 4) *reinterpret_cast<float4*>(stg + lane * 20 + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+          __syncwarp();
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+            const int rr = er8 + 16 * i;
+            const int m = mt * BM + quad * 32 + rr;
+            const float4 a0 = *reinterpret_cast<const float4*>(stg + rr * 20 + ec8), a1 = *reinterpret_cast<const float4*>(stg + rr * 20 + ec8 + 4);
+            if (m < p.M) epilogue_apply8<E>(p, a0, a1, Cp, aux, b4[0], b4[1], alpha, m, n0, coef != nullptr, cf0, cf1, ops[i][0], ops[i][1]);
+          }
+          __syncwarp();
+          continue;
+        }
         // global operands of this chunk's 4 row groups first: they do not depend on the accumulator
         const int n0 = nt * BN + c0 + ec;
         EpiOps ops[4];
@@ -132,9 +174,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tma_kernel(const __grid_cons
           if (m < p.M) ops[i] = epilogue_load<E>(p, aux, m, n0, coef != nullptr);
         }
         const float4 b4 = bias ? __ldg(reinterpret_cast<const float4*>(bias + n0)) : make_float4(0.f, 0.f, 0.f, 0.f);
-        float4 cf[3];
-        if (coef) { cf[0] = __ldg(reinterpret_cast<const float4*>(coef + n0)); cf[1] = __ldg(reinterpret_cast<const float4*>(coef + p.N + n0)); cf[2] = __ldg(reinterpret_cast<const float4*>(coef + 2 * p.N + n0)); }
-        if (!waited) { mbar_wait(&acc_full[buf], (it >> 1) & 1); tc_fence_after(); waited = true; }
+        EpiCoef cf{};
+        if (coef) { cf.a = __ldg(reinterpret_cast<const float4*>(coef + n0)); cf.e = __ldg(reinterpret_cast<const float4*>(coef + p.N + n0)); cf.f = __ldg(reinterpret_cast<const float4*>(coef + 2 * p.N + n0)); }
+        if (!waited) { if (warp == 2 && it < 30) GEMM_TRACE(8 + it * 8 + 5); mbar_wait(&acc_full[buf], (it >> 1) & 1); tc_fence_after(); waited = true; if (warp == 2 && it < 30) GEMM_TRACE(8 + it * 8 + 6); }
         float v[16];
         tmem_ld16(trow + c0, v);
 #pragma unroll
@@ -145,18 +187,21 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tma_kernel(const __grid_cons
           const int rr = er + 8 * i;
           const int m = mt * BM + quad * 32 + rr;
           const float4 acc = *reinterpret_cast<const float4*>(stg + rr * 20 + ec);
-          if (m < p.M) epilogue_apply<E>(p, acc, Cp, aux, b4, alpha, m, n0, coef ? cf : nullptr, ops[i]);
+          if (m < p.M) epilogue_apply<E>(p, acc, Cp, aux, b4, alpha, m, n0, coef != nullptr, cf, ops[i]);
         }
         __syncwarp();
       }
       if (!waited) { mbar_wait(&acc_full[buf], (it >> 1) & 1); tc_fence_after(); }
+      if (warp == 2 && it < 30) GEMM_TRACE(8 + it * 8 + 7);
       tc_fence_before();
       if (lane == 0) mbar_arrive(&acc_empty[buf]);
     }
   }
   tc_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0) GEMM_TRACE(2);
   if (warp == 1) tmem_dealloc(tmem_base, 2 * BN);
+#undef GEMM_TRACE
 }
 
 __global__ void __launch_bounds__(256) transpose_weights_kernel(const float* __restrict__ src, float* __restrict__ dst, float* __restrict__ dst2,
@@ -240,7 +285,7 @@ cudaError_t launch_tma_bn(const GemmP& p, int bn, cudaStream_t s) {
   if (bn == 128) return launch_tma_cfg<128, E>(p, s);
   return launch_tma_cfg<64, E>(p, s);
 }
-constexpr uint32_t kTmaEpiKinds = EPI_GELU | EPI_RESID | EPI_GELU_BWD | EPI_PHILOX;
+constexpr uint32_t kTmaEpiKinds = EPI_GELU | EPI_RESID | EPI_GELU_BWD | EPI_PHILOX | EPI_BN_BWD;
 }  // namespace
 
 cudaError_t launch_transpose_weights(const float* src, float* dst, float* dst2, const TrDesc* descs_dev, int ndesc, int total_tiles, cudaStream_t s) {
@@ -271,6 +316,7 @@ cudaError_t launch_gemm_tma(const GemmP& p, cudaStream_t s) {
   if (kind == EPI_RESID) return launch_tma_bn<EPI_RESID>(p, bn, s);
   if (kind == EPI_GELU) return launch_tma_bn<EPI_GELU>(p, bn, s);
   if (kind == EPI_GELU_BWD) return launch_tma_bn<EPI_GELU_BWD>(p, bn, s);
+  if (kind == EPI_BN_BWD) return launch_tma_bn<EPI_BN_BWD>(p, bn, s);
   if (kind == (EPI_RESID | EPI_PHILOX)) return launch_tma_bn<EPI_RESID | EPI_PHILOX>(p, bn, s);     // dropout mask drawn in the epilogue
   if (kind == (EPI_GELU | EPI_PHILOX)) return launch_tma_bn<EPI_GELU | EPI_PHILOX>(p, bn, s);
   set_error("gemm_tma: no instantiation for epilogue " + std::to_string(p.epi));
