@@ -295,6 +295,10 @@ def main_b200(a):
             roof = {"bound": "tensor", "achieved": fl / t / 1e12, "peak": tf32_peak, "unit": "TFLOP/s", "frac": fl / t / 1e12 / tf32_peak, "traffic": None}
         else:
             roof = {"bound": "hbm", "achieved": by / t / 1e9, "peak": peaks["hbm"], "unit": "GB/s", "frac": by / t / 1e9 / peaks["hbm"], "traffic": None}
+        try:      # DRAM traffic of this kernel group from the committed ncu --set full capture (profiles/ncu_traffic.json), else null
+            roof["traffic"] = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get(top)
+        except Exception:
+            pass
         roof.update({"kernel_group": top, "group_ms": agg[top], "peak_source": peaks["src"], "algorithmic_flops": fl, "algorithmic_bytes": by})
     line = {"metric": METRIC if train else "cvt_par_infer_images_per_sec", "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps,
             "warmup": max(a.warmup, 3), "ms_per_step": total_ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
