@@ -48,12 +48,13 @@ def compare_taps(eng, taps, n_stages=3, tol=1e-4, names=TAPS):
     return bad, report
 
 
-def compare_grads(eng, grads, tol=1e-3):
+def compare_grads(eng, grads, tol=1e-3, floor_frac=1e-4):
     """Per tensor max|a-b| / max(max|b|, floor).  The floor (1e-4 of the largest gradient in the model) keeps
-    analytically-zero gradients (key biases: softmax is shift-invariant) from dividing noise by noise."""
+    analytically-zero gradients (key biases: softmax is shift-invariant) from dividing noise by noise; the TF32 tests raise
+    it to 1e-3, the size of one TF32 rounding, because there the noise on such a tensor is rounding noise of the whole dK sum."""
     got = eng.get_grads()
     bad, report = [], []
-    floor = 1e-4 * max(float(np.abs(g).max()) for g in grads.values())
+    floor = floor_frac * max(float(np.abs(g).max()) for g in grads.values())
     for k, g in grads.items():
         e = rel_err(got[k], g, floor)
         report.append((k, e))

@@ -1,0 +1,255 @@
+// Depthwise 3x3 q/k/v Projection (DepthwiseConv2D(3, 1, 'same', use_bias=False), models/CvT(Par).py:93,157-159), forward and
+// backward, as "column walkers": a thread owns one (column, channel) and walks down a segment of image rows.  A warp = 32
+// consecutive channels of one pixel, so every global access moves one full 128-byte line.  Rows stream through a shared-memory
+// ring filled by 4-byte cp.async (each thread copies its own pixel; the first / last warp also copy the halo column), several rows
+// ahead of the row being consumed, so ~2 KB per warp is in flight without holding prefetch registers; the left / right
+// neighbours of a pixel are read from the ring slots of the neighbouring warps.  HBM-bound by design: forward reads xn once and
+// writes the three maps; backward reads the three map gradients and xn once and writes dxn.  CTAs are persistent and keep their
+// channel group, so BatchNorm statistics / depthwise-weight gradients stay in registers across work items and leave the CTA once,
+// as per-CTA partial slices (summed by bn_finalize_kernel / reduce_partials_kernel).
+#include "layers.cuh"
+
+namespace cvt {
+namespace {
+constexpr int CT = 256, COLS = 8;                       // block = 32 channels x 8 columns
+constexpr int FP = 6, FR = FP + 2;                      // forward: rows in flight, ring rows
+constexpr int BP = 4, BR = BP + 2;                      // backward
+
+struct ColGeo { int CG, ncolg, nseg, RS, items_per_cg; };   // channel groups, column groups, row segments (of RS rows)
+
+// 4-byte asynchronous copy global -> shared; !ok writes a zero (src-size 0) and never dereferences src
+__device__ __forceinline__ void cp4(float* dst, const float* src, const float* safe, bool ok) {
+  const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst);
+  const int sz = ok ? 4 : 0;
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(d), "l"(ok ? src : safe), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// ---- forward -------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(CT, 2) dwcol_fwd_kernel(const __grid_constant__ DwProjP p, const ColGeo g) {
+  __shared__ float ring[FR][COLS + 2][32];
+  __shared__ float sred[COLS][6][32];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int D = p.D, H = p.H, W = p.W;
+  const int cg = blockIdx.x % g.CG, c = cg * 32 + tx;
+  float w[3][9];
+#pragma unroll
+  for (int z = 0; z < 3; ++z)
+#pragma unroll
+    for (int k = 0; k < 9; ++k) w[z][k] = p.w[(z * 9 + k) * D + c];
+  float ssum[3] = {0.f, 0.f, 0.f}, ssq[3] = {0.f, 0.f, 0.f};
+  for (int item = blockIdx.x / g.CG; item < g.items_per_cg; item += gridDim.x / g.CG) {
+    int t = item;
+    const int colg = t % g.ncolg; t /= g.ncolg;
+    const int seg = t % g.nseg; const int b = t / g.nseg;
+    const int j = colg * COLS + ty;
+    const bool jok = j < W;
+    const int r0 = seg * g.RS, rend = min(H, r0 + g.RS);
+    const long long base = ((long long)b * p.Tc + p.has_cls) * D + (long long)j * D + c;
+    const float* x = p.xn + base;
+    cp_wait<0>();                                        // (only zero rows past the segment end can still be pending)
+    __syncthreads();                                     // the previous item's last rows have been read
+    auto issue = [&](int row) {                          // rows r0-1 .. rend (halo rows included); anything else is a zero row
+      const bool rok = row >= 0 && row < H && row <= rend;
+      float* dst = &ring[(row - r0 + 1) % FR][ty + 1][tx];
+      const float* src = x + (long long)row * W * D;
+      cp4(dst, src, p.xn, rok && jok);
+      if (ty == 0) cp4(dst - 32, src - D, p.xn, rok && j > 0);
+      if (ty == COLS - 1) cp4(dst + 32, src + D, p.xn, rok && j + 1 < W);
+      cp_commit();
+    };
+#pragma unroll
+    for (int k = 0; k < FP; ++k) issue(r0 - 1 + k);
+    float a0[3] = {0.f, 0.f, 0.f}, a1[3] = {0.f, 0.f, 0.f}, a2[3] = {0.f, 0.f, 0.f};    // outputs g-1, g, g+1 of the three branches
+    for (int gi = r0 - 1; gi <= rend; ++gi) {
+      issue(gi + FP);
+      cp_wait<FP>();
+      __syncthreads();
+      const float* row = &ring[(gi - r0 + 1) % FR][ty][tx];
+      const float xl = row[0], xm = row[32], xr = row[64];
+#pragma unroll
+      for (int z = 0; z < 3; ++z) {
+        a0[z] = fmaf(xl, w[z][6], fmaf(xm, w[z][7], fmaf(xr, w[z][8], a0[z])));       // bottom tap row of output g-1
+        a1[z] = fmaf(xl, w[z][3], fmaf(xm, w[z][4], fmaf(xr, w[z][5], a1[z])));       // middle tap row of output g
+        a2[z] = fmaf(xl, w[z][0], fmaf(xm, w[z][1], fmaf(xr, w[z][2], a2[z])));       // top tap row of output g+1
+      }
+      const int io = gi - 1;
+      if (jok && io >= r0 && io < rend) {
+#pragma unroll
+        for (int z = 0; z < 3; ++z) {
+          const float y = a0[z];
+          p.out[z * p.out_bs + base + (long long)io * W * D] = p.round_out ? round_tf32(y) : y;
+          ssum[z] += y; ssq[z] = fmaf(y, y, ssq[z]);
+        }
+      }
+#pragma unroll
+      for (int z = 0; z < 3; ++z) { a0[z] = a1[z]; a1[z] = a2[z]; a2[z] = 0.f; }
+    }
+  }
+  cp_wait<0>();
+  // cls rows pass through untouched (models/CvT(Par).py:150,168-170), or are zeroed when the cls row is handled outside (fold.cu)
+  if (p.has_cls) {
+    for (int i = blockIdx.x * CT + threadIdx.x; i < p.B * 3 * (D >> 2); i += gridDim.x * CT) {
+      const int q = i % (D >> 2), z = (i / (D >> 2)) % 3, b = i / (3 * (D >> 2));
+      const long long row = (long long)b * p.Tc * D + q * 4;
+      *reinterpret_cast<float4*>(p.out + z * p.out_bs + row) = p.cls_zero ? make_float4(0.f, 0.f, 0.f, 0.f) : *reinterpret_cast<const float4*>(p.xn + row);
+    }
+  }
+  if (p.stats) {   // partial slice (blockIdx / CG): [sum q,k,v | sum of squares q,k,v][D]; this CTA fills its 32 channels
+#pragma unroll
+    for (int z = 0; z < 3; ++z) { sred[ty][z][tx] = ssum[z]; sred[ty][3 + z][tx] = ssq[z]; }
+    __syncthreads();
+    for (int o = threadIdx.x; o < 6 * 32; o += CT) {
+      const int k = o >> 5, l = o & 31;
+      float a = 0.f;
+#pragma unroll
+      for (int y = 0; y < COLS; ++y) a += sred[y][k][l];
+      p.stats[(long long)(blockIdx.x / g.CG) * 6 * D + k * D + cg * 32 + l] = a;
+    }
+  }
+}
+
+// ---- backward ------------------------------------------------------------------------------------------------------------------
+// dx[i,j] = sum_z sum_{kh,kw} d_z[i-kh+1, j-kw+1] w_z[kh,kw];   dw_z[kh,kw] += x[i+kh-1, j+kw-1] d_z[i,j]
+__global__ void __launch_bounds__(CT, 2) dwcol_bwd_kernel(const __grid_constant__ DwProjBwdP p, const ColGeo g) {
+  constexpr int RING = BR * (COLS + 2) * 4 * 32, RED = COLS * 27 * 32;
+  __shared__ float smem[RING > RED ? RING : RED];
+  float (*ring)[COLS + 2][4][32] = reinterpret_cast<float (*)[COLS + 2][4][32]>(smem);      // [row slot][column slot][x, d_q, d_k, d_v][channel]
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int D = p.D, H = p.H, W = p.W;
+  const int cg = blockIdx.x % g.CG, c = cg * 32 + tx;
+  float w[3][9], dw[3][9];
+#pragma unroll
+  for (int z = 0; z < 3; ++z)
+#pragma unroll
+    for (int k = 0; k < 9; ++k) { w[z][k] = p.w[(z * 9 + k) * D + c]; dw[z][k] = 0.f; }
+  for (int item = blockIdx.x / g.CG; item < g.items_per_cg; item += gridDim.x / g.CG) {
+    int t = item;
+    const int colg = t % g.ncolg; t /= g.ncolg;
+    const int seg = t % g.nseg; const int b = t / g.nseg;
+    const int j = colg * COLS + ty;
+    const bool jok = j < W;
+    const int r0 = seg * g.RS, rend = min(H, r0 + g.RS);
+    const long long base = ((long long)b * p.Tc + p.has_cls) * D + (long long)j * D + c;
+    const float* x = p.xn + base;
+    const float* d0 = p.dconv + base;
+    cp_wait<0>();                                        // (only zero rows past the segment end can still be pending)
+    __syncthreads();                                     // the previous item's last rows have been read
+    auto issue = [&](int row) {                          // rows r0-1 .. rend (halo rows included); anything else is a zero row
+      const bool rok = row >= 0 && row < H && row <= rend;
+      float* dst = &ring[(row - r0 + 1) % BR][ty + 1][0][tx];
+      const long long o = (long long)row * W * D;
+      const bool lok = rok && j > 0, rgt = rok && j + 1 < W;
+      cp4(dst, x + o, p.xn, rok && jok);
+      if (ty == 0) cp4(dst - 128, x + o - D, p.xn, lok);
+      if (ty == COLS - 1) cp4(dst + 128, x + o + D, p.xn, rgt);
+#pragma unroll
+      for (int z = 0; z < 3; ++z) {
+        const float* q = d0 + z * p.bs + o;
+        cp4(dst + 32 * (z + 1), q, p.xn, rok && jok);
+        if (ty == 0) cp4(dst + 32 * (z + 1) - 128, q - D, p.xn, lok);
+        if (ty == COLS - 1) cp4(dst + 32 * (z + 1) + 128, q + D, p.xn, rgt);
+      }
+      cp_commit();
+    };
+#pragma unroll
+    for (int k = 0; k < BP; ++k) issue(r0 - 1 + k);
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f;                  // dx of rows g-1, g, g+1
+    float dprev[3] = {0.f, 0.f, 0.f};                    // centre d of row g-1, counted only inside [r0, rend)
+    float pxl = 0.f, pxm = 0.f, pxr = 0.f, qxl = 0.f, qxm = 0.f, qxr = 0.f;   // x of rows g-1 (p) and g-2 (q)
+    for (int gi = r0 - 1; gi <= rend; ++gi) {
+      issue(gi + BP);
+      cp_wait<BP>();
+      __syncthreads();
+      const float* row = &ring[(gi - r0 + 1) % BR][ty][0][tx];
+      const float xl = row[0], xm = row[128], xr = row[256];
+      const bool cur_in = gi >= r0 && gi < rend;
+#pragma unroll
+      for (int z = 0; z < 3; ++z) {
+        const float dl = row[32 * (z + 1)], dm = row[32 * (z + 1) + 128], dr = row[32 * (z + 1) + 256];
+        // input gradient: d row g feeds dx rows g-1 (tap row 0), g (tap row 1), g+1 (tap row 2); d[., j-1] pairs with tap column 2
+        a0 = fmaf(dl, w[z][2], fmaf(dm, w[z][1], fmaf(dr, w[z][0], a0)));
+        a1 = fmaf(dl, w[z][5], fmaf(dm, w[z][4], fmaf(dr, w[z][3], a1)));
+        a2 = fmaf(dl, w[z][8], fmaf(dm, w[z][7], fmaf(dr, w[z][6], a2)));
+        // weight gradient, one row late: the centre d of row g-1 pairs with x rows g-2 (tap row 0), g-1 (tap row 1), g (tap row 2)
+        const float dp = dprev[z];
+        dw[z][0] = fmaf(qxl, dp, dw[z][0]); dw[z][1] = fmaf(qxm, dp, dw[z][1]); dw[z][2] = fmaf(qxr, dp, dw[z][2]);
+        dw[z][3] = fmaf(pxl, dp, dw[z][3]); dw[z][4] = fmaf(pxm, dp, dw[z][4]); dw[z][5] = fmaf(pxr, dp, dw[z][5]);
+        dw[z][6] = fmaf(xl, dp, dw[z][6]); dw[z][7] = fmaf(xm, dp, dw[z][7]); dw[z][8] = fmaf(xr, dp, dw[z][8]);
+        dprev[z] = cur_in ? dm : 0.f;
+      }
+      const int io = gi - 1;
+      if (jok && io >= r0 && io < rend) p.dxn[base + (long long)io * W * D] = a0;
+      a0 = a1; a1 = a2; a2 = 0.f;
+      qxl = pxl; qxm = pxm; qxr = pxr; pxl = xl; pxm = xm; pxr = xr;
+    }
+  }
+  cp_wait<0>();
+  if (p.has_cls) {   // the cls row bypassed conv and BN: its gradient is the plain sum of the three branches
+    for (int i = blockIdx.x * CT + threadIdx.x; i < p.B * (D >> 2); i += gridDim.x * CT) {
+      const int q = i % (D >> 2), b = i / (D >> 2);
+      const long long row = (long long)b * p.Tc * D + q * 4;
+      float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int z = 0; z < 3; ++z) { const float4 v = *reinterpret_cast<const float4*>(p.dconv + z * p.bs + row); s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w; }
+      *reinterpret_cast<float4*>(p.dxn + row) = s;
+    }
+  }
+  if (p.ddw) {       // partial slice (blockIdx / CG): [27][D]; this CTA fills its 32 channels
+    float (*sred)[27][32] = reinterpret_cast<float (*)[27][32]>(smem);
+    __syncthreads();                                     // the ring is dead
+#pragma unroll
+    for (int z = 0; z < 3; ++z)
+#pragma unroll
+      for (int k = 0; k < 9; ++k) sred[ty][z * 9 + k][tx] = dw[z][k];
+    __syncthreads();
+    for (int o = threadIdx.x; o < 27 * 32; o += CT) {
+      const int k = o >> 5, l = o & 31;
+      float a = 0.f;
+#pragma unroll
+      for (int y = 0; y < COLS; ++y) a += sred[y][k][l];
+      p.ddw_part[(long long)(blockIdx.x / g.CG) * 27 * D + k * D + cg * 32 + l] = a;
+    }
+  }
+}
+
+bool make_colgeo(int B, int H, int W, int D, int cap_blocks, ColGeo* g, int* grid) {
+  if (D % 32 != 0) return false;
+  g->CG = D / 32; g->ncolg = cdiv(W, COLS);
+  g->RS = H >= 32 ? 16 : 8;
+  g->nseg = cdiv(H, g->RS);
+  g->items_per_cg = B * g->nseg * g->ncolg;
+  int per_cg = cap_blocks / g->CG;
+  if (per_cg < 1) return false;
+  if (per_cg > g->items_per_cg) per_cg = g->items_per_cg;
+  *grid = per_cg * g->CG;
+  return true;
+}
+}  // namespace
+
+cudaError_t launch_reduce_partials(const float* part, int nparts, int n, float* dst, cudaStream_t s);
+
+// the three branches must all be depthwise convolutions (projection_method 'dw_bn'); otherwise cudaErrorNotSupported
+cudaError_t launch_dwcol_fwd(const DwProjP& p, cudaStream_t s) {
+  ColGeo g; int grid;
+  if (p.method[0] != 0 || p.method[1] != 0 || p.method[2] != 0 || !make_colgeo(p.B, p.H, p.W, p.D, p.nparts, &g, &grid)) return cudaErrorNotSupported;
+  const int slices = grid / g.CG;
+  if (p.stats && slices < p.nparts)
+    CVT_CUDA(cudaMemsetAsync(p.stats + (size_t)slices * 6 * p.D, 0, (size_t)(p.nparts - slices) * 6 * p.D * sizeof(float), s));
+  dwcol_fwd_kernel<<<grid, CT, 0, s>>>(p, g);
+  CVT_LAUNCH_CHECK();
+  return cudaSuccess;
+}
+
+cudaError_t launch_dwcol_bwd(const DwProjBwdP& p, cudaStream_t s) {
+  ColGeo g; int grid;
+  if (p.method[0] != 0 || p.method[1] != 0 || p.method[2] != 0 || p.coef || !make_colgeo(p.B, p.H, p.W, p.D, 2 * kNumSMs, &g, &grid)) return cudaErrorNotSupported;
+  if (p.ddw && !p.ddw_part) return cudaErrorInvalidValue;
+  dwcol_bwd_kernel<<<grid, CT, 0, s>>>(p, g);
+  CVT_LAUNCH_CHECK();
+  if (p.ddw) CVT_CUDA(launch_reduce_partials(p.ddw_part, grid / g.CG, 27 * p.D, p.ddw, s));
+  return cudaSuccess;
+}
+
+}  // namespace cvt

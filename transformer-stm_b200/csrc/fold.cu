@@ -41,25 +41,55 @@ __global__ void __launch_bounds__(256) bn_fold_kernel(const float* __restrict__ 
   }
 }
 
-// q[z][b, cls row, :] = alpha_z (xn[b, cls row, :] Wc[z] + bc[z]);  grid (B, 3), block D threads
-__global__ void cls_fix_kernel(const float* __restrict__ xn, long long bs, const float* __restrict__ Wc, const float* __restrict__ bc,
-                               float alpha0, int Tc, int D, float* __restrict__ q) {
-  extern __shared__ float srow[];
-  const int b = blockIdx.x, z = blockIdx.y, j = threadIdx.x;
-  const long long row = (long long)z * bs + (long long)b * Tc * D;
-  for (int i = threadIdx.x; i < D; i += blockDim.x) srow[i] = xn[(long long)b * Tc * D + i];
-  __syncthreads();
-  const float* W = Wc + (long long)z * D * D;
-  float a = bc[z * D + j], a1 = 0.f, a2 = 0.f, a3 = 0.f;
-  int i = 0;
-#pragma unroll 4
-  for (; i + 3 < D; i += 4) {                          // independent chains: the weight loads of many rows are in flight together
-    a = fmaf(srow[i], W[(long long)i * D + j], a); a1 = fmaf(srow[i + 1], W[(long long)(i + 1) * D + j], a1);
-    a2 = fmaf(srow[i + 2], W[(long long)(i + 2) * D + j], a2); a3 = fmaf(srow[i + 3], W[(long long)(i + 3) * D + j], a3);
+// q[z][b, cls row, :] = alpha_z (xn[b, cls row, :] Wc[z] + bc[z]): a [B, D] x [D, D] product per branch, far too small for the tensor
+// pipe and pure latency if done as one matvec per image.  grid (D/32 column tiles, B/16 image chunks, 3), block (32, 8): thread
+// (tx, ty) owns output column j0 + tx and the ty-th eighth of the contraction; it loads its weights in batches of 16 independent
+// loads, multiplies them into 16 images' cls rows held in shared memory, and the eight partial sums meet in shared memory.
+constexpr int CF_B = 16, CF_U = 16;
+__global__ void __launch_bounds__(256) cls_fix_kernel(const float* __restrict__ xn, long long bs, const float* __restrict__ Wc,
+                                                      const float* __restrict__ bc, float alpha0, int B, int Tc, int D, float* __restrict__ q) {
+  extern __shared__ float4 cf_smem[];
+  float* sx = reinterpret_cast<float*>(cf_smem);          // [CF_B][D] cls rows; reused as [8][CF_B][32] partial sums
+  const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * 32 + tx;
+  const int j = blockIdx.x * 32 + tx, b0 = blockIdx.y * CF_B, z = blockIdx.z;
+  const int nb = min(CF_B, B - b0);
+  for (int e = tid; e < CF_B * (D >> 2); e += 256) {
+    const int b = e / (D >> 2), c = e - b * (D >> 2);
+    reinterpret_cast<float4*>(sx)[e] = b < nb ? *reinterpret_cast<const float4*>(xn + (long long)(b0 + b) * Tc * D + c * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
   }
-  for (; i < D; ++i) a = fmaf(srow[i], W[(long long)i * D + j], a);
-  a = (a + a1) + (a2 + a3);
-  q[row + j] = round_tf32((z == 0 ? alpha0 : 1.f) * a);     // attention operand (TMA): rounded by its producer
+  const int per = D >> 3, i0 = ty * per;                  // D % 32 == 0: per is a multiple of 4
+  const float* W = Wc + (long long)z * D * D + (long long)i0 * D + j;
+  float acc[CF_B];
+#pragma unroll
+  for (int b = 0; b < CF_B; ++b) acc[b] = 0.f;
+  __syncthreads();
+  for (int u0 = 0; u0 < per; u0 += CF_U) {
+    float wv[CF_U];
+#pragma unroll
+    for (int u = 0; u < CF_U; ++u) wv[u] = u0 + u < per ? __ldg(W + (long long)(u0 + u) * D) : 0.f;
+#pragma unroll
+    for (int b = 0; b < CF_B; ++b) {
+      const float4* xr = reinterpret_cast<const float4*>(sx + b * D + i0 + u0);
+#pragma unroll
+      for (int u = 0; u < CF_U; u += 4) {
+        if (u0 + u < per) {
+          const float4 xv = xr[u >> 2];
+          acc[b] = fmaf(xv.x, wv[u], fmaf(xv.y, wv[u + 1], fmaf(xv.z, wv[u + 2], fmaf(xv.w, wv[u + 3], acc[b]))));
+        }
+      }
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int b = 0; b < CF_B; ++b) sx[(ty * CF_B + b) * 32 + tx] = acc[b];
+  __syncthreads();
+  const float alpha = z == 0 ? alpha0 : 1.f, bias = bc[z * D + j];
+  for (int b = ty; b < nb; b += 8) {
+    float a = bias;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a += sx[(k * CF_B + b) * 32 + tx];
+    q[(long long)z * bs + (long long)(b0 + b) * Tc * D + j] = round_tf32(alpha * a);     // attention operand (TMA): rounded by its producer
+  }
 }
 
 // Zcls[z][c][j] = sum_b xn[b, cls, c] dq[z][b, cls, j]  and  scls[z][j] = sum_b dq[z][b, cls, j]   (fp32; the cls row is the only row
@@ -143,8 +173,11 @@ cudaError_t launch_bn_fold(const float* Wc, const float* bc, const float* sc, co
 
 cudaError_t launch_cls_fix(const float* xn, long long bs, const float* Wc, const float* bc, float alpha0, int B, int Tc, int D, float* q,
                            cudaStream_t s) {
-  if (D > 1024) { set_error("cls_fix: D > 1024"); return cudaErrorInvalidValue; }
-  cls_fix_kernel<<<dim3(B, 3), D, D * sizeof(float), s>>>(xn, bs, Wc, bc, alpha0, Tc, D, q);
+  if (D % 32 != 0 || D > 1024) { set_error("cls_fix: D must be a multiple of 32, at most 1024"); return cudaErrorInvalidValue; }
+  static bool configured = false;
+  if (!configured) { CVT_CUDA(cudaFuncSetAttribute(cls_fix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CF_B * 1024 * 4)); configured = true; }
+  const size_t smem = (size_t)CF_B * (D > 256 ? D : 256) * sizeof(float);      // cls rows, later the [8][CF_B][32] partial sums
+  cls_fix_kernel<<<dim3(D / 32, (B + CF_B - 1) / CF_B, 3), dim3(32, 8), smem, s>>>(xn, bs, Wc, bc, alpha0, B, Tc, D, q);
   CVT_LAUNCH_CHECK();
   return cudaSuccess;
 }
