@@ -17,11 +17,10 @@ constexpr int BP = 4, BR = BP + 2;                      // backward
 
 struct ColGeo { int CG, ncolg, nseg, RS, items_per_cg; };   // channel groups, column groups, row segments (of RS rows)
 
-// 4-byte asynchronous copy global -> shared; !ok writes a zero (src-size 0) and never dereferences src
-__device__ __forceinline__ void cp4(float* dst, const float* src, const float* safe, bool ok) {
-  const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst);
-  const int sz = ok ? 4 : 0;
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(d), "l"(ok ? src : safe), "r"(sz) : "memory");
+// 4-byte asynchronous copy global -> shared address; sz = 0 writes a zero and reads nothing (the source address may then lie outside
+// the tensor: it is never dereferenced)
+__device__ __forceinline__ void cp4(uint32_t dst, const float* src, int sz) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(sz) : "memory");
 }
 __device__ __forceinline__ void cp_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N> __device__ __forceinline__ void cp_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
@@ -33,6 +32,7 @@ __global__ void __launch_bounds__(CT, 2) dwcol_fwd_kernel(const __grid_constant_
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int D = p.D, H = p.H, W = p.W;
   const int cg = blockIdx.x % g.CG, c = cg * 32 + tx;
+  const uint32_t ring_u32 = (uint32_t)__cvta_generic_to_shared(&ring[0][ty + 1][tx]);
   float w[3][9];
 #pragma unroll
   for (int z = 0; z < 3; ++z)
@@ -50,23 +50,29 @@ __global__ void __launch_bounds__(CT, 2) dwcol_fwd_kernel(const __grid_constant_
     const float* x = p.xn + base;
     cp_wait<0>();                                        // (only zero rows past the segment end can still be pending)
     __syncthreads();                                     // the previous item's last rows have been read
-    auto issue = [&](int row) {                          // rows r0-1 .. rend (halo rows included); anything else is a zero row
-      const bool rok = row >= 0 && row < H && row <= rend;
-      float* dst = &ring[(row - r0 + 1) % FR][ty + 1][tx];
-      const float* src = x + (long long)row * W * D;
-      cp4(dst, src, p.xn, rok && jok);
-      if (ty == 0) cp4(dst - 32, src - D, p.xn, rok && j > 0);
-      if (ty == COLS - 1) cp4(dst + 32, src + D, p.xn, rok && j + 1 < W);
+    // running state of the copy front (row ir into ring slot islot) and of the row being consumed: no multiplications in the loop
+    const int rs = W * D, rlo = max(r0 - 1, 0), rhi = min(rend, H - 1);
+    int ir = r0 - 1, islot = 0, cslot = 0;
+    const float* qx = x + (long long)ir * rs;
+    float* po = p.out + base + (long long)(r0 - 2) * rs;
+    auto issue = [&]() {                                 // rows r0-1 .. rend (halo rows included); anything else is a zero row
+      const bool rok = ir >= rlo && ir <= rhi;
+      const uint32_t dst = ring_u32 + islot * ((COLS + 2) * 128);
+      cp4(dst, qx, (rok && jok) ? 4 : 0);
+      if (ty == 0) cp4(dst - 128, qx - D, (rok && j > 0) ? 4 : 0);
+      if (ty == COLS - 1) cp4(dst + 128, qx + D, (rok && j + 1 < W) ? 4 : 0);
       cp_commit();
+      ++ir; qx += rs; islot = islot + 1 == FR ? 0 : islot + 1;
     };
 #pragma unroll
-    for (int k = 0; k < FP; ++k) issue(r0 - 1 + k);
+    for (int k = 0; k < FP; ++k) issue();
     float a0[3] = {0.f, 0.f, 0.f}, a1[3] = {0.f, 0.f, 0.f}, a2[3] = {0.f, 0.f, 0.f};    // outputs g-1, g, g+1 of the three branches
     for (int gi = r0 - 1; gi <= rend; ++gi) {
-      issue(gi + FP);
+      issue();
       cp_wait<FP>();
       __syncthreads();
-      const float* row = &ring[(gi - r0 + 1) % FR][ty][tx];
+      const float* row = &ring[cslot][ty][tx];
+      cslot = cslot + 1 == FR ? 0 : cslot + 1;
       const float xl = row[0], xm = row[32], xr = row[64];
 #pragma unroll
       for (int z = 0; z < 3; ++z) {
@@ -79,12 +85,13 @@ __global__ void __launch_bounds__(CT, 2) dwcol_fwd_kernel(const __grid_constant_
 #pragma unroll
         for (int z = 0; z < 3; ++z) {
           const float y = a0[z];
-          p.out[z * p.out_bs + base + (long long)io * W * D] = p.round_out ? round_tf32(y) : y;
+          po[z * p.out_bs] = p.round_out ? round_tf32(y) : y;
           ssum[z] += y; ssq[z] = fmaf(y, y, ssq[z]);
         }
       }
 #pragma unroll
       for (int z = 0; z < 3; ++z) { a0[z] = a1[z]; a1[z] = a2[z]; a2[z] = 0.f; }
+      po += rs;
     }
   }
   cp_wait<0>();
@@ -119,6 +126,7 @@ __global__ void __launch_bounds__(CT, 2) dwcol_bwd_kernel(const __grid_constant_
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int D = p.D, H = p.H, W = p.W;
   const int cg = blockIdx.x % g.CG, c = cg * 32 + tx;
+  const uint32_t ring_u32 = (uint32_t)__cvta_generic_to_shared(&ring[0][ty + 1][0][tx]);
   float w[3][9], dw[3][9];
 #pragma unroll
   for (int z = 0; z < 3; ++z)
@@ -136,33 +144,40 @@ __global__ void __launch_bounds__(CT, 2) dwcol_bwd_kernel(const __grid_constant_
     const float* d0 = p.dconv + base;
     cp_wait<0>();                                        // (only zero rows past the segment end can still be pending)
     __syncthreads();                                     // the previous item's last rows have been read
-    auto issue = [&](int row) {                          // rows r0-1 .. rend (halo rows included); anything else is a zero row
-      const bool rok = row >= 0 && row < H && row <= rend;
-      float* dst = &ring[(row - r0 + 1) % BR][ty + 1][0][tx];
-      const long long o = (long long)row * W * D;
-      const bool lok = rok && j > 0, rgt = rok && j + 1 < W;
-      cp4(dst, x + o, p.xn, rok && jok);
-      if (ty == 0) cp4(dst - 128, x + o - D, p.xn, lok);
-      if (ty == COLS - 1) cp4(dst + 128, x + o + D, p.xn, rgt);
-#pragma unroll
-      for (int z = 0; z < 3; ++z) {
-        const float* q = d0 + z * p.bs + o;
-        cp4(dst + 32 * (z + 1), q, p.xn, rok && jok);
-        if (ty == 0) cp4(dst + 32 * (z + 1) - 128, q - D, p.xn, lok);
-        if (ty == COLS - 1) cp4(dst + 32 * (z + 1) + 128, q + D, p.xn, rgt);
+    const int rs = W * D, rlo = max(r0 - 1, 0), rhi = min(rend, H - 1);
+    int ir = r0 - 1, islot = 0, cslot = 0;
+    const float* qx = x + (long long)ir * rs;
+    const float* q0 = d0 + (long long)ir * rs;
+    const float* q1 = q0 + p.bs;
+    const float* q2 = q1 + p.bs;
+    float* po = p.dxn + base + (long long)(r0 - 2) * rs;
+    auto issue = [&]() {                                 // rows r0-1 .. rend (halo rows included); anything else is a zero row
+      const bool rok = ir >= rlo && ir <= rhi;
+      const uint32_t dst = ring_u32 + islot * ((COLS + 2) * 512);
+      const int szc = (rok && jok) ? 4 : 0;
+      cp4(dst, qx, szc); cp4(dst + 128, q0, szc); cp4(dst + 256, q1, szc); cp4(dst + 384, q2, szc);
+      if (ty == 0) {
+        const int sz = (rok && j > 0) ? 4 : 0;
+        cp4(dst - 512, qx - D, sz); cp4(dst - 384, q0 - D, sz); cp4(dst - 256, q1 - D, sz); cp4(dst - 128, q2 - D, sz);
+      }
+      if (ty == COLS - 1) {
+        const int sz = (rok && j + 1 < W) ? 4 : 0;
+        cp4(dst + 512, qx + D, sz); cp4(dst + 640, q0 + D, sz); cp4(dst + 768, q1 + D, sz); cp4(dst + 896, q2 + D, sz);
       }
       cp_commit();
+      ++ir; qx += rs; q0 += rs; q1 += rs; q2 += rs; islot = islot + 1 == BR ? 0 : islot + 1;
     };
 #pragma unroll
-    for (int k = 0; k < BP; ++k) issue(r0 - 1 + k);
+    for (int k = 0; k < BP; ++k) issue();
     float a0 = 0.f, a1 = 0.f, a2 = 0.f;                  // dx of rows g-1, g, g+1
     float dprev[3] = {0.f, 0.f, 0.f};                    // centre d of row g-1, counted only inside [r0, rend)
     float pxl = 0.f, pxm = 0.f, pxr = 0.f, qxl = 0.f, qxm = 0.f, qxr = 0.f;   // x of rows g-1 (p) and g-2 (q)
     for (int gi = r0 - 1; gi <= rend; ++gi) {
-      issue(gi + BP);
+      issue();
       cp_wait<BP>();
       __syncthreads();
-      const float* row = &ring[(gi - r0 + 1) % BR][ty][0][tx];
+      const float* row = &ring[cslot][ty][0][tx];
+      cslot = cslot + 1 == BR ? 0 : cslot + 1;
       const float xl = row[0], xm = row[128], xr = row[256];
       const bool cur_in = gi >= r0 && gi < rend;
 #pragma unroll
@@ -180,7 +195,8 @@ __global__ void __launch_bounds__(CT, 2) dwcol_bwd_kernel(const __grid_constant_
         dprev[z] = cur_in ? dm : 0.f;
       }
       const int io = gi - 1;
-      if (jok && io >= r0 && io < rend) p.dxn[base + (long long)io * W * D] = a0;
+      if (jok && io >= r0 && io < rend) *po = a0;
+      po += rs;
       a0 = a1; a1 = a2; a2 = 0.f;
       qxl = pxl; qxm = pxm; qxr = pxr; pxl = xl; pxm = xm; pxr = xr;
     }
