@@ -568,10 +568,11 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
     dp.cls_zero = m->folded && bn;
     dp.round_out = m->folded;
     const bool fast = g.D <= 256 && (g.D & 3) == 0;
+    int stat_parts = fast ? kStatParts : 1;
     if (fast) {
       dp.nparts = kStatParts;
       static const bool use_col = getenv("CVT_NO_DWCOL") == nullptr;
-      cudaError_t e = (m->folded && bn && use_col) ? launch_dwcol_fwd(dp, s) : cudaErrorNotSupported;
+      cudaError_t e = (m->folded && bn && use_col) ? launch_dwcol_fwd(dp, s, &stat_parts) : cudaErrorNotSupported;
       if (e == cudaErrorNotSupported) e = (m->folded && bn) ? launch_dwplane_fwd(dp, s) : cudaErrorNotSupported;
       if (e == cudaErrorNotSupported) e = launch_dwproj_fwd2(dp, s);
       CVT_CUDA(e);
@@ -581,7 +582,7 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
       CVT_CUDA(launch_dwproj_fwd(dp, s));
     }
     if (bn) {
-      BnFinalizeP f; f.stats = a.bn_stats; f.nparts = fast ? kStatParts : 1; f.count = (long long)B * g.T; f.gamma = P + w.bn_g; f.beta = P + w.bn_b;
+      BnFinalizeP f; f.stats = a.bn_stats; f.nparts = stat_parts; f.count = (long long)B * g.T; f.gamma = P + w.bn_g; f.beta = P + w.bn_b;
       f.moving_mean = m->St + w.bn_mm; f.moving_var = m->St + w.bn_mv; f.training = training; f.update_moving = training;
       f.eps = c.bn_eps; f.momentum = c.bn_momentum; f.scale = a.bn_scale; f.shift = a.bn_shift; f.save_mean = a.bn_mean; f.save_rstd = a.bn_rstd; f.D = D;
       CVT_CUDA(launch_bn_finalize(f, s));

@@ -247,12 +247,10 @@ bool make_colgeo(int B, int H, int W, int D, int cap_blocks, ColGeo* g, int* gri
 cudaError_t launch_reduce_partials(const float* part, int nparts, int n, float* dst, cudaStream_t s);
 
 // the three branches must all be depthwise convolutions (projection_method 'dw_bn'); otherwise cudaErrorNotSupported
-cudaError_t launch_dwcol_fwd(const DwProjP& p, cudaStream_t s) {
+cudaError_t launch_dwcol_fwd(const DwProjP& p, cudaStream_t s, int* stat_slices) {
   ColGeo g; int grid;
   if (p.method[0] != 0 || p.method[1] != 0 || p.method[2] != 0 || !make_colgeo(p.B, p.H, p.W, p.D, p.nparts, &g, &grid)) return cudaErrorNotSupported;
-  const int slices = grid / g.CG;
-  if (p.stats && slices < p.nparts)
-    CVT_CUDA(cudaMemsetAsync(p.stats + (size_t)slices * 6 * p.D, 0, (size_t)(p.nparts - slices) * 6 * p.D * sizeof(float), s));
+  *stat_slices = grid / g.CG;                            // slices of p.stats written by this launch (<= p.nparts): bn_finalize sums exactly these
   dwcol_fwd_kernel<<<grid, CT, 0, s>>>(p, g);
   CVT_LAUNCH_CHECK();
   return cudaSuccess;

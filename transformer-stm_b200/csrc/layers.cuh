@@ -65,7 +65,7 @@ cudaError_t launch_dwproj_bwd2(const DwProjBwdP& p, cudaStream_t s);
 cudaError_t launch_dwplane_fwd(const DwProjP& p, cudaStream_t s);
 cudaError_t launch_dwplane_bwd(const DwProjBwdP& p, cudaStream_t s);
 // register column walkers, one channel per lane (dwcol.cu): D % 32 == 0; cudaErrorNotSupported -> caller uses the kernels above
-cudaError_t launch_dwcol_fwd(const DwProjP& p, cudaStream_t s);
+cudaError_t launch_dwcol_fwd(const DwProjP& p, cudaStream_t s, int* stat_slices);
 cudaError_t launch_dwcol_bwd(const DwProjBwdP& p, cudaStream_t s);
 // coef [3][3][D] = (A, E, F) with dconv = A dn + E conv + F  (BatchNorm backward as an affine map, training or moving statistics)
 cudaError_t launch_bn_bwd_coef(const float* gamma, const float* mean, const float* rstd, const float* scale, const float* dgamma,
