@@ -1,6 +1,6 @@
 // Depthwise 3x3 q/k/v Projection (DepthwiseConv2D(3, 1, 'same', use_bias=False), models/CvT(Par).py:93,157-159), forward and
 // backward, as "column walkers": a thread owns one (column, channel) and walks down a segment of image rows.  A warp = 32
-// consecutive channels of one pixel, so every global access moves one full 128-byte line.  Rows stream through a shared-memory
+// consecutive channels of two adjacent pixels (the filter taps in registers serve both), so every global access moves full 128-byte lines.  Rows stream through a shared-memory
 // ring filled by 4-byte cp.async (each thread copies its own pixel; the first / last warp also copy the halo column), several rows
 // ahead of the row being consumed, so ~2 KB per warp is in flight without holding prefetch registers; the left / right
 // neighbours of a pixel are read from the ring slots of the neighbouring warps.  HBM-bound by design: forward reads xn once and
@@ -11,11 +11,12 @@
 
 namespace cvt {
 namespace {
-constexpr int CT = 256, COLS = 8;                       // block = 32 channels x 8 columns
+constexpr int CT = 256, NW = 8, COLS = 2 * NW;          // block = 32 channels x 16 columns, two adjacent columns per thread
 constexpr int FP = 6, FR = FP + 2;                      // forward: rows in flight, ring rows
-constexpr int BP = 4, BR = BP + 2;                      // backward
+constexpr int BP = 3, BR = BP + 2;                      // backward (ring = 5 x 18 x 512 B = 45 KB)
 
-struct ColGeo { int CG, ncolg, nseg, RS, items_per_cg; };   // channel groups, column groups, row segments (of RS rows)
+struct ColGeo { int CG, ncolg, nseg, RS, items_per_cg, pack; };   // channel groups, column groups, row segments (of RS rows); pack = 2: images
+                                                                   // at most 8 columns wide go two to a CTA (warps 0-3 / 4-7)
 
 // 4-byte asynchronous copy global -> shared address; sz = 0 writes a zero and reads nothing (the source address may then lie outside
 // the tensor: it is never dereferenced)
@@ -27,12 +28,12 @@ template <int N> __device__ __forceinline__ void cp_wait() { asm volatile("cp.as
 
 // ---- forward -------------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(CT, 2) dwcol_fwd_kernel(const __grid_constant__ DwProjP p, const ColGeo g) {
-  __shared__ float ring[FR][COLS + 2][32];
-  __shared__ float sred[COLS][6][32];
+  __shared__ float ring[FR][COLS + 2][32];               // column slot s <-> image column colg * COLS - 1 + s
+  __shared__ float sred[NW][6][32];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int D = p.D, H = p.H, W = p.W;
   const int cg = blockIdx.x % g.CG, c = cg * 32 + tx;
-  const uint32_t ring_u32 = (uint32_t)__cvta_generic_to_shared(&ring[0][ty + 1][tx]);
+  const uint32_t ring_u32 = (uint32_t)__cvta_generic_to_shared(&ring[0][2 * ty + 1][tx]);
   float w[3][9];
 #pragma unroll
   for (int z = 0; z < 3; ++z)
@@ -42,9 +43,10 @@ __global__ void __launch_bounds__(CT, 2) dwcol_fwd_kernel(const __grid_constant_
   for (int item = blockIdx.x / g.CG; item < g.items_per_cg; item += gridDim.x / g.CG) {
     int t = item;
     const int colg = t % g.ncolg; t /= g.ncolg;
-    const int seg = t % g.nseg; const int b = t / g.nseg;
-    const int j = colg * COLS + ty;
-    const bool jok = j < W;
+    const int seg = t % g.nseg; const int b = (t / g.nseg) * g.pack + (g.pack == 2 ? ty >> 2 : 0);
+    const int j = colg * COLS + 2 * (g.pack == 2 ? ty & 3 : ty);            // this thread's columns: j, j + 1
+    const bool jok0 = b < p.B && j < W, jok1 = b < p.B && j + 1 < W;
+    const bool lz = g.pack == 2 && (ty & 3) == 0, rz = g.pack == 2 && (ty & 3) == 3;   // packed: the neighbour slot belongs to the other image
     const int r0 = seg * g.RS, rend = min(H, r0 + g.RS);
     const long long base = ((long long)b * p.Tc + p.has_cls) * D + (long long)j * D + c;
     const float* x = p.xn + base;
@@ -58,39 +60,53 @@ __global__ void __launch_bounds__(CT, 2) dwcol_fwd_kernel(const __grid_constant_
     auto issue = [&]() {                                 // rows r0-1 .. rend (halo rows included); anything else is a zero row
       const bool rok = ir >= rlo && ir <= rhi;
       const uint32_t dst = ring_u32 + islot * ((COLS + 2) * 128);
-      cp4(dst, qx, (rok && jok) ? 4 : 0);
+      cp4(dst, qx, (rok && jok0) ? 4 : 0);
+      cp4(dst + 128, qx + D, (rok && jok1) ? 4 : 0);
       if (ty == 0) cp4(dst - 128, qx - D, (rok && j > 0) ? 4 : 0);
-      if (ty == COLS - 1) cp4(dst + 128, qx + D, (rok && j + 1 < W) ? 4 : 0);
+      if (ty == NW - 1) cp4(dst + 256, qx + 2 * D, (rok && j + 2 < W) ? 4 : 0);
       cp_commit();
       ++ir; qx += rs; islot = islot + 1 == FR ? 0 : islot + 1;
     };
 #pragma unroll
     for (int k = 0; k < FP; ++k) issue();
-    float a0[3] = {0.f, 0.f, 0.f}, a1[3] = {0.f, 0.f, 0.f}, a2[3] = {0.f, 0.f, 0.f};    // outputs g-1, g, g+1 of the three branches
+    float a0[2][3], a1[2][3], a2[2][3];                  // outputs g-1, g, g+1 of the three branches, for both columns
+#pragma unroll
+    for (int q = 0; q < 2; ++q)
+#pragma unroll
+      for (int z = 0; z < 3; ++z) { a0[q][z] = 0.f; a1[q][z] = 0.f; a2[q][z] = 0.f; }
     for (int gi = r0 - 1; gi <= rend; ++gi) {
       issue();
       cp_wait<FP>();
       __syncthreads();
-      const float* row = &ring[cslot][ty][tx];
+      const float* row = &ring[cslot][2 * ty][tx];
       cslot = cslot + 1 == FR ? 0 : cslot + 1;
-      const float xl = row[0], xm = row[32], xr = row[64];
+      const float xv[4] = {lz ? 0.f : row[0], row[32], row[64], rz ? 0.f : row[96]};      // columns j-1, j, j+1, j+2
 #pragma unroll
-      for (int z = 0; z < 3; ++z) {
-        a0[z] = fmaf(xl, w[z][6], fmaf(xm, w[z][7], fmaf(xr, w[z][8], a0[z])));       // bottom tap row of output g-1
-        a1[z] = fmaf(xl, w[z][3], fmaf(xm, w[z][4], fmaf(xr, w[z][5], a1[z])));       // middle tap row of output g
-        a2[z] = fmaf(xl, w[z][0], fmaf(xm, w[z][1], fmaf(xr, w[z][2], a2[z])));       // top tap row of output g+1
-      }
-      const int io = gi - 1;
-      if (jok && io >= r0 && io < rend) {
+      for (int q = 0; q < 2; ++q)
 #pragma unroll
         for (int z = 0; z < 3; ++z) {
-          const float y = a0[z];
-          po[z * p.out_bs] = p.round_out ? round_tf32(y) : y;
-          ssum[z] += y; ssq[z] = fmaf(y, y, ssq[z]);
+          a0[q][z] = fmaf(xv[q], w[z][6], fmaf(xv[q + 1], w[z][7], fmaf(xv[q + 2], w[z][8], a0[q][z])));       // bottom tap row of output g-1
+          a1[q][z] = fmaf(xv[q], w[z][3], fmaf(xv[q + 1], w[z][4], fmaf(xv[q + 2], w[z][5], a1[q][z])));       // middle tap row of output g
+          a2[q][z] = fmaf(xv[q], w[z][0], fmaf(xv[q + 1], w[z][1], fmaf(xv[q + 2], w[z][2], a2[q][z])));       // top tap row of output g+1
+        }
+      const int io = gi - 1;
+      if (io >= r0 && io < rend) {
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+          if (q == 0 ? jok0 : jok1) {
+#pragma unroll
+            for (int z = 0; z < 3; ++z) {
+              const float y = a0[q][z];
+              po[z * p.out_bs + q * D] = p.round_out ? round_tf32(y) : y;
+              ssum[z] += y; ssq[z] = fmaf(y, y, ssq[z]);
+            }
+          }
         }
       }
 #pragma unroll
-      for (int z = 0; z < 3; ++z) { a0[z] = a1[z]; a1[z] = a2[z]; a2[z] = 0.f; }
+      for (int q = 0; q < 2; ++q)
+#pragma unroll
+        for (int z = 0; z < 3; ++z) { a0[q][z] = a1[q][z]; a1[q][z] = a2[q][z]; a2[q][z] = 0.f; }
       po += rs;
     }
   }
@@ -111,7 +127,7 @@ __global__ void __launch_bounds__(CT, 2) dwcol_fwd_kernel(const __grid_constant_
       const int k = o >> 5, l = o & 31;
       float a = 0.f;
 #pragma unroll
-      for (int y = 0; y < COLS; ++y) a += sred[y][k][l];
+      for (int y = 0; y < NW; ++y) a += sred[y][k][l];
       p.stats[(long long)(blockIdx.x / g.CG) * 6 * D + k * D + cg * 32 + l] = a;
     }
   }
@@ -120,13 +136,13 @@ __global__ void __launch_bounds__(CT, 2) dwcol_fwd_kernel(const __grid_constant_
 // ---- backward ------------------------------------------------------------------------------------------------------------------
 // dx[i,j] = sum_z sum_{kh,kw} d_z[i-kh+1, j-kw+1] w_z[kh,kw];   dw_z[kh,kw] += x[i+kh-1, j+kw-1] d_z[i,j]
 __global__ void __launch_bounds__(CT, 2) dwcol_bwd_kernel(const __grid_constant__ DwProjBwdP p, const ColGeo g) {
-  constexpr int RING = BR * (COLS + 2) * 4 * 32, RED = COLS * 27 * 32;
+  constexpr int RING = BR * (COLS + 2) * 4 * 32, RED = NW * 27 * 32;
   __shared__ float smem[RING > RED ? RING : RED];
   float (*ring)[COLS + 2][4][32] = reinterpret_cast<float (*)[COLS + 2][4][32]>(smem);      // [row slot][column slot][x, d_q, d_k, d_v][channel]
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int D = p.D, H = p.H, W = p.W;
   const int cg = blockIdx.x % g.CG, c = cg * 32 + tx;
-  const uint32_t ring_u32 = (uint32_t)__cvta_generic_to_shared(&ring[0][ty + 1][0][tx]);
+  const uint32_t ring_u32 = (uint32_t)__cvta_generic_to_shared(&ring[0][2 * ty + 1][0][tx]);
   float w[3][9], dw[3][9];
 #pragma unroll
   for (int z = 0; z < 3; ++z)
@@ -135,9 +151,10 @@ __global__ void __launch_bounds__(CT, 2) dwcol_bwd_kernel(const __grid_constant_
   for (int item = blockIdx.x / g.CG; item < g.items_per_cg; item += gridDim.x / g.CG) {
     int t = item;
     const int colg = t % g.ncolg; t /= g.ncolg;
-    const int seg = t % g.nseg; const int b = t / g.nseg;
-    const int j = colg * COLS + ty;
-    const bool jok = j < W;
+    const int seg = t % g.nseg; const int b = (t / g.nseg) * g.pack + (g.pack == 2 ? ty >> 2 : 0);
+    const int j = colg * COLS + 2 * (g.pack == 2 ? ty & 3 : ty);            // this thread's columns: j, j + 1
+    const bool jok0 = b < p.B && j < W, jok1 = b < p.B && j + 1 < W;
+    const bool lz = g.pack == 2 && (ty & 3) == 0, rz = g.pack == 2 && (ty & 3) == 3;   // packed: the neighbour slot belongs to the other image
     const int r0 = seg * g.RS, rend = min(H, r0 + g.RS);
     const long long base = ((long long)b * p.Tc + p.has_cls) * D + (long long)j * D + c;
     const float* x = p.xn + base;
@@ -154,51 +171,64 @@ __global__ void __launch_bounds__(CT, 2) dwcol_bwd_kernel(const __grid_constant_
     auto issue = [&]() {                                 // rows r0-1 .. rend (halo rows included); anything else is a zero row
       const bool rok = ir >= rlo && ir <= rhi;
       const uint32_t dst = ring_u32 + islot * ((COLS + 2) * 512);
-      const int szc = (rok && jok) ? 4 : 0;
-      cp4(dst, qx, szc); cp4(dst + 128, q0, szc); cp4(dst + 256, q1, szc); cp4(dst + 384, q2, szc);
+      const int s0 = (rok && jok0) ? 4 : 0, s1 = (rok && jok1) ? 4 : 0;
+      cp4(dst, qx, s0); cp4(dst + 128, q0, s0); cp4(dst + 256, q1, s0); cp4(dst + 384, q2, s0);
+      cp4(dst + 512, qx + D, s1); cp4(dst + 640, q0 + D, s1); cp4(dst + 768, q1 + D, s1); cp4(dst + 896, q2 + D, s1);
       if (ty == 0) {
         const int sz = (rok && j > 0) ? 4 : 0;
         cp4(dst - 512, qx - D, sz); cp4(dst - 384, q0 - D, sz); cp4(dst - 256, q1 - D, sz); cp4(dst - 128, q2 - D, sz);
       }
-      if (ty == COLS - 1) {
-        const int sz = (rok && j + 1 < W) ? 4 : 0;
-        cp4(dst + 512, qx + D, sz); cp4(dst + 640, q0 + D, sz); cp4(dst + 768, q1 + D, sz); cp4(dst + 896, q2 + D, sz);
+      if (ty == NW - 1) {
+        const int sz = (rok && j + 2 < W) ? 4 : 0;
+        cp4(dst + 1024, qx + 2 * D, sz); cp4(dst + 1152, q0 + 2 * D, sz); cp4(dst + 1280, q1 + 2 * D, sz); cp4(dst + 1408, q2 + 2 * D, sz);
       }
       cp_commit();
       ++ir; qx += rs; q0 += rs; q1 += rs; q2 += rs; islot = islot + 1 == BR ? 0 : islot + 1;
     };
 #pragma unroll
     for (int k = 0; k < BP; ++k) issue();
-    float a0 = 0.f, a1 = 0.f, a2 = 0.f;                  // dx of rows g-1, g, g+1
-    float dprev[3] = {0.f, 0.f, 0.f};                    // centre d of row g-1, counted only inside [r0, rend)
-    float pxl = 0.f, pxm = 0.f, pxr = 0.f, qxl = 0.f, qxm = 0.f, qxr = 0.f;   // x of rows g-1 (p) and g-2 (q)
+    float a0[2] = {0.f, 0.f}, a1[2] = {0.f, 0.f}, a2[2] = {0.f, 0.f};      // dx of rows g-1, g, g+1 for both columns
+    float dprev[2][3];                                   // centre d of row g-1, counted only inside [r0, rend)
+#pragma unroll
+    for (int q = 0; q < 2; ++q)
+#pragma unroll
+      for (int z = 0; z < 3; ++z) dprev[q][z] = 0.f;
+    float px[4] = {0.f, 0.f, 0.f, 0.f}, qx2[4] = {0.f, 0.f, 0.f, 0.f};     // x of rows g-1 (px) and g-2 (qx2), columns j-1 .. j+2
     for (int gi = r0 - 1; gi <= rend; ++gi) {
       issue();
       cp_wait<BP>();
       __syncthreads();
-      const float* row = &ring[cslot][ty][0][tx];
+      const float* row = &ring[cslot][2 * ty][0][tx];
       cslot = cslot + 1 == BR ? 0 : cslot + 1;
-      const float xl = row[0], xm = row[128], xr = row[256];
+      const float xv[4] = {lz ? 0.f : row[0], row[128], row[256], rz ? 0.f : row[384]};           // columns j-1, j, j+1, j+2
       const bool cur_in = gi >= r0 && gi < rend;
 #pragma unroll
       for (int z = 0; z < 3; ++z) {
-        const float dl = row[32 * (z + 1)], dm = row[32 * (z + 1) + 128], dr = row[32 * (z + 1) + 256];
-        // input gradient: d row g feeds dx rows g-1 (tap row 0), g (tap row 1), g+1 (tap row 2); d[., j-1] pairs with tap column 2
-        a0 = fmaf(dl, w[z][2], fmaf(dm, w[z][1], fmaf(dr, w[z][0], a0)));
-        a1 = fmaf(dl, w[z][5], fmaf(dm, w[z][4], fmaf(dr, w[z][3], a1)));
-        a2 = fmaf(dl, w[z][8], fmaf(dm, w[z][7], fmaf(dr, w[z][6], a2)));
-        // weight gradient, one row late: the centre d of row g-1 pairs with x rows g-2 (tap row 0), g-1 (tap row 1), g (tap row 2)
-        const float dp = dprev[z];
-        dw[z][0] = fmaf(qxl, dp, dw[z][0]); dw[z][1] = fmaf(qxm, dp, dw[z][1]); dw[z][2] = fmaf(qxr, dp, dw[z][2]);
-        dw[z][3] = fmaf(pxl, dp, dw[z][3]); dw[z][4] = fmaf(pxm, dp, dw[z][4]); dw[z][5] = fmaf(pxr, dp, dw[z][5]);
-        dw[z][6] = fmaf(xl, dp, dw[z][6]); dw[z][7] = fmaf(xm, dp, dw[z][7]); dw[z][8] = fmaf(xr, dp, dw[z][8]);
-        dprev[z] = cur_in ? dm : 0.f;
+        const float dv[4] = {lz ? 0.f : row[32 * (z + 1)], row[32 * (z + 1) + 128], row[32 * (z + 1) + 256], rz ? 0.f : row[32 * (z + 1) + 384]};
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+          // input gradient: d row g feeds dx rows g-1 (tap row 0), g (tap row 1), g+1 (tap row 2); d[., j-1] pairs with tap column 2
+          a0[q] = fmaf(dv[q], w[z][2], fmaf(dv[q + 1], w[z][1], fmaf(dv[q + 2], w[z][0], a0[q])));
+          a1[q] = fmaf(dv[q], w[z][5], fmaf(dv[q + 1], w[z][4], fmaf(dv[q + 2], w[z][3], a1[q])));
+          a2[q] = fmaf(dv[q], w[z][8], fmaf(dv[q + 1], w[z][7], fmaf(dv[q + 2], w[z][6], a2[q])));
+          // weight gradient, one row late: the centre d of row g-1 pairs with x rows g-2 (tap row 0), g-1 (tap row 1), g (tap row 2)
+          const float dp = dprev[q][z];
+          dw[z][0] = fmaf(qx2[q], dp, dw[z][0]); dw[z][1] = fmaf(qx2[q + 1], dp, dw[z][1]); dw[z][2] = fmaf(qx2[q + 2], dp, dw[z][2]);
+          dw[z][3] = fmaf(px[q], dp, dw[z][3]); dw[z][4] = fmaf(px[q + 1], dp, dw[z][4]); dw[z][5] = fmaf(px[q + 2], dp, dw[z][5]);
+          dw[z][6] = fmaf(xv[q], dp, dw[z][6]); dw[z][7] = fmaf(xv[q + 1], dp, dw[z][7]); dw[z][8] = fmaf(xv[q + 2], dp, dw[z][8]);
+          dprev[q][z] = cur_in ? dv[q + 1] : 0.f;
+        }
       }
       const int io = gi - 1;
-      if (jok && io >= r0 && io < rend) *po = a0;
+      if (io >= r0 && io < rend) {
+        if (jok0) po[0] = a0[0];
+        if (jok1) po[D] = a0[1];
+      }
       po += rs;
-      a0 = a1; a1 = a2; a2 = 0.f;
-      qxl = pxl; qxm = pxm; qxr = pxr; pxl = xl; pxm = xm; pxr = xr;
+#pragma unroll
+      for (int q = 0; q < 2; ++q) { a0[q] = a1[q]; a1[q] = a2[q]; a2[q] = 0.f; }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) { qx2[q] = px[q]; px[q] = xv[q]; }
     }
   }
   cp_wait<0>();
@@ -224,7 +254,7 @@ __global__ void __launch_bounds__(CT, 2) dwcol_bwd_kernel(const __grid_constant_
       const int k = o >> 5, l = o & 31;
       float a = 0.f;
 #pragma unroll
-      for (int y = 0; y < COLS; ++y) a += sred[y][k][l];
+      for (int y = 0; y < NW; ++y) a += sred[y][k][l];
       p.ddw_part[(long long)(blockIdx.x / g.CG) * 27 * D + k * D + cg * 32 + l] = a;
     }
   }
@@ -235,7 +265,8 @@ bool make_colgeo(int B, int H, int W, int D, int cap_blocks, ColGeo* g, int* gri
   g->CG = D / 32; g->ncolg = cdiv(W, COLS);
   g->RS = H >= 32 ? 16 : 8;
   g->nseg = cdiv(H, g->RS);
-  g->items_per_cg = B * g->nseg * g->ncolg;
+  g->pack = W <= COLS / 2 ? 2 : 1;
+  g->items_per_cg = cdiv(B, g->pack) * g->nseg * g->ncolg;
   int per_cg = cap_blocks / g->CG;
   if (per_cg < 1) return false;
   if (per_cg > g->items_per_cg) per_cg = g->items_per_cg;
