@@ -2,6 +2,7 @@
 Tolerance: max|a-b| / max|b| per tensor; 1e-4 for activations and 1e-3 for gradients in fp32 mode (north_star: rtol 1e-3)."""
 import numpy as np
 import pytest
+import scipy.special
 import torch
 
 import transformer_stm_b200 as T
@@ -177,8 +178,15 @@ def test_tf32_tensor_core_mode_tracks_oracle(hw, batch, cls):
     r = O.loss_and_grads(spec, params, img, proc, y, masks)
     # TF32 mode folds proj_q/k/v + MHA dense (and attention_output + proj) into one GEMM each: qkv1 / a1 are never materialised
     from tests.parity_utils import TAPS
-    bad, report = compare_taps(eng, r["taps"], tol=5e-3, names=[t for t in TAPS if t not in ("qkv1", "a1")])
+    # ... and after a training forward `hpre` holds d hact / d hpre (GELU derivative times the dropout keep factor): checked separately
+    bad, report = compare_taps(eng, r["taps"], tol=5e-3, names=[t for t in TAPS if t not in ("qkv1", "a1", "hpre")])
     assert not bad, "tf32 forward mismatches:\n" + fmt(report)
+    for i in range(1, 4):      # saved derivative = gelu'(hpre) * mask1 / keep, rebuilt from the oracle's pre-activation and mask
+        pre = np.asarray(r["taps"]["s%d.hpre" % i], dtype=np.float64)
+        cdf = 0.5 * (1.0 + scipy.special.erf(pre / np.sqrt(2.0)))
+        keep = (np.asarray(masks["s%d.mlp1" % i]) != 0).astype(np.float64).reshape(pre.shape)
+        want = (cdf + pre * np.exp(-0.5 * pre * pre) / np.sqrt(2.0 * np.pi)) * keep / (1.0 - spec.drop_rate)
+        assert rel_err(eng.tap("s%d.hpre" % i), want) <= 5e-3, "stage %d saved GELU derivative" % i
     assert abs(loss - r["loss"]) <= 2e-3 * abs(r["loss"])
     bad, report = compare_grads(eng, r["grads"], tol=2e-2, floor_frac=1e-3)
     assert not bad, "tf32 gradient mismatches:\n" + fmt(report)

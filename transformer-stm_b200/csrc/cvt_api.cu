@@ -59,10 +59,18 @@ cudaError_t run_gemm(const Model* m, const GemmP& p, cudaStream_t s) {
       }
       if (gemm_tma_supports(p)) return launch_gemm_tma(p, s);
     }
+    if (p.epi & EPI_GELU_DSAVE) { set_error("run_gemm: the saved-GELU-derivative epilogue exists only in the TMA kernel"); return cudaErrorNotSupported; }
     if (gemm_tc_supports(p)) return launch_gemm_tc(p, s);
   }
+  if (p.epi & EPI_GELU_DSAVE) { set_error("run_gemm: the saved-GELU-derivative epilogue exists only in the TMA kernel"); return cudaErrorNotSupported; }
   if (p.epi & EPI_PHILOX) { set_error("run_gemm: in-epilogue dropout needs a tensor-core shape"); return cudaErrorNotSupported; }
   return launch_gemm_simt(p, s);
+}
+
+// TF32 folded mode on the TMA kernel: the Mlp forward epilogue stores the GELU derivative instead of the pre-activation (gemm.cuh)
+static bool gelu_dsave(const Model* m, int D) {
+  static const bool off = getenv("CVT_NO_TMA") != nullptr || getenv("CVT_NO_DSAVE") != nullptr;
+  return !off && m->folded && m->cfg.precision != CVT_PREC_FP32 && D % 16 == 0;
 }
 
 static thread_local bool g_tc = false;     // the model being run uses the tcgen05 contraction kernel (128-row tiles, 2 CTAs per SM)
@@ -638,6 +646,7 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
     GemmP p = dense_fwd(a.y, D, R, D, P + w.f1w, H4, P + w.f1b, a.hact, H4);
     p.epi |= EPI_GELU; p.aux = a.hpre;
     if (m->folded) p.epi |= EPI_ROUND;
+    if (training && gelu_dsave(m, D)) p.epi |= EPI_GELU_DSAVE;      // hpre then holds d hact / d hpre (dropout included) for the backward epilogue
     if (drop) epi_dropout(m, p, a.mask1, si * 4 + 1, keep_scale);
     CVT_CUDA(run_gemm(m, p, s));
     GemmP q = dense_fwd(a.hact, H4, R, H4, P + w.f2w, D, P + w.f2b, a.x2, D);
@@ -755,7 +764,8 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
     GemmP p = dense_dgrad(dM, D, R, D, P + w.f2w, H4, m->gH, H4);      // d hpre = (dM W2^T) * gelu'(hpre) * mask1/keep
     p.epi |= EPI_GELU_BWD; p.aux = a.hpre;
     if (m->folded) p.epi |= EPI_ROUND;
-    if (drop) { p.epi |= EPI_MASK; p.mask = a.mask1; p.mask_scale = keep_scale; }
+    if (training && gelu_dsave(m, D)) p.epi |= EPI_GELU_DSAVE;      // the forward epilogue left gelu'(hpre) * mask1 / keep in hpre
+    else if (drop) { p.epi |= EPI_MASK; p.mask = a.mask1; p.mask_scale = keep_scale; }
     CVT_CUDA(run_gemm(m, p, s));
   }
   CVT_CUDA(wgrad_bias(m, a.y, D, D, m->gH, H4, H4, R, G + w.f1w, G + w.f1b, 1, 0, 0, s));

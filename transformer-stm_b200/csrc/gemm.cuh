@@ -18,6 +18,8 @@ enum Epi : uint32_t {
   EPI_GELU_BWD = 64u, EPI_RELU = 128u, EPI_RELU_BWD = 256u, EPI_ALPHA0 = 512u,
   EPI_ROUND = 2048u,      // store C rounded to TF32 (C only feeds tensor-core GEMMs); aux keeps full precision
   EPI_PHILOX = 4096u,     // with EPI_MASK: the keep-mask is drawn here (Philox4x32-10, same counters as philox_mask_kernel) and stored to mask_gen
+  EPI_GELU_DSAVE = 8192u, // tcgen05/TMA kernel only.  With EPI_GELU: aux receives d out / d pre = gelu'(pre) (times the dropout keep factor when
+                          // EPI_MASK) instead of pre; with EPI_GELU_BWD: aux holds that derivative, v *= aux (no erf, no mask load)
   EPI_BN_BWD = 1024u      // v = A[n] v + E[n] aux[idx] + F[n]  (BatchNorm backward as an affine map of (dn, conv); coef = [A|E|F][N])
 };
 

@@ -102,10 +102,17 @@ __device__ __forceinline__ void epilogue_math(const GemmP& p, float4 acc, float4
   }
   if (E & EPI_GELU) {
 #pragma unroll
-    for (int j = 0; j < 4; ++j) { pre[j] = v[j]; v[j] = gelu_erf(v[j]); }
+    for (int j = 0; j < 4; ++j) {
+      if (E & EPI_GELU_DSAVE) {                          // one erf serves the activation and its derivative
+        const float x = v[j], cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752440f));
+        pre[j] = fmaf(x, 0.39894228040143267794f * __expf(-0.5f * x * x), cdf);
+        v[j] = x * cdf;
+      } else { pre[j] = v[j]; v[j] = gelu_erf(v[j]); }
+    }
   }
   if (E & EPI_GELU_BWD) {
-    v[0] *= gelu_erf_grad(o.a4.x); v[1] *= gelu_erf_grad(o.a4.y); v[2] *= gelu_erf_grad(o.a4.z); v[3] *= gelu_erf_grad(o.a4.w);
+    if (E & EPI_GELU_DSAVE) { v[0] *= o.a4.x; v[1] *= o.a4.y; v[2] *= o.a4.z; v[3] *= o.a4.w; }
+    else { v[0] *= gelu_erf_grad(o.a4.x); v[1] *= gelu_erf_grad(o.a4.y); v[2] *= gelu_erf_grad(o.a4.z); v[3] *= gelu_erf_grad(o.a4.w); }
   }
   mk = o.mk;
   if (p.epi & EPI_MASK) {
@@ -115,7 +122,11 @@ __device__ __forceinline__ void epilogue_math(const GemmP& p, float4 acc, float4
       mk = (c[0] >= p.ph_thr ? 1u : 0u) | (c[1] >= p.ph_thr ? 0x100u : 0u) | (c[2] >= p.ph_thr ? 0x10000u : 0u) | (c[3] >= p.ph_thr ? 0x1000000u : 0u);
     }
 #pragma unroll
-    for (int j = 0; j < 4; ++j) v[j] = ((mk >> (8 * j)) & 0xFFu) ? v[j] * p.mask_scale : 0.f;
+    for (int j = 0; j < 4; ++j) {
+      const bool keep = ((mk >> (8 * j)) & 0xFFu) != 0u;
+      v[j] = keep ? v[j] * p.mask_scale : 0.f;
+      if ((E & EPI_GELU) && (E & EPI_GELU_DSAVE)) pre[j] = keep ? pre[j] * p.mask_scale : 0.f;
+    }
   }
   if (E & EPI_RESID) { v[0] += o.r4.x; v[1] += o.r4.y; v[2] += o.r4.z; v[3] += o.r4.w; }
   if (p.epi & EPI_ROUND) {

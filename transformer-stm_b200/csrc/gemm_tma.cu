@@ -285,7 +285,7 @@ cudaError_t launch_tma_bn(const GemmP& p, int bn, cudaStream_t s) {
   if (bn == 128) return launch_tma_cfg<128, E>(p, s);
   return launch_tma_cfg<64, E>(p, s);
 }
-constexpr uint32_t kTmaEpiKinds = EPI_GELU | EPI_RESID | EPI_GELU_BWD | EPI_PHILOX | EPI_BN_BWD;
+constexpr uint32_t kTmaEpiKinds = EPI_GELU | EPI_RESID | EPI_GELU_BWD | EPI_PHILOX | EPI_BN_BWD | EPI_GELU_DSAVE;
 }  // namespace
 
 cudaError_t launch_transpose_weights(const float* src, float* dst, float* dst2, const TrDesc* descs_dev, int ndesc, int total_tiles, cudaStream_t s) {
@@ -319,6 +319,9 @@ cudaError_t launch_gemm_tma(const GemmP& p, cudaStream_t s) {
   if (kind == EPI_BN_BWD) return launch_tma_bn<EPI_BN_BWD>(p, bn, s);
   if (kind == (EPI_RESID | EPI_PHILOX)) return launch_tma_bn<EPI_RESID | EPI_PHILOX>(p, bn, s);     // dropout mask drawn in the epilogue
   if (kind == (EPI_GELU | EPI_PHILOX)) return launch_tma_bn<EPI_GELU | EPI_PHILOX>(p, bn, s);
+  if (kind == (EPI_GELU | EPI_GELU_DSAVE)) return launch_tma_bn<EPI_GELU | EPI_GELU_DSAVE>(p, bn, s);
+  if (kind == (EPI_GELU | EPI_PHILOX | EPI_GELU_DSAVE)) return launch_tma_bn<EPI_GELU | EPI_PHILOX | EPI_GELU_DSAVE>(p, bn, s);
+  if (kind == (EPI_GELU_BWD | EPI_GELU_DSAVE)) return launch_tma_bn<EPI_GELU_BWD | EPI_GELU_DSAVE>(p, bn, s);
   set_error("gemm_tma: no instantiation for epilogue " + std::to_string(p.epi));
   return cudaErrorNotSupported;
 }
