@@ -104,9 +104,8 @@ __device__ __forceinline__ void epilogue_math(const GemmP& p, float4 acc, float4
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       if (E & EPI_GELU_DSAVE) {                          // one erf serves the activation and its derivative
-        const float x = v[j], cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752440f));
-        pre[j] = fmaf(x, 0.39894228040143267794f * __expf(-0.5f * x * x), cdf);
-        v[j] = x * cdf;
+        const float x = v[j];
+        gelu_and_grad(x, v[j], pre[j]);
       } else { pre[j] = v[j]; v[j] = gelu_erf(v[j]); }
     }
   }
