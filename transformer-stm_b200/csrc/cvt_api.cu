@@ -593,7 +593,7 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
       BnFinalizeP f; f.stats = a.bn_stats; f.nparts = stat_parts; f.count = (long long)B * g.T; f.gamma = P + w.bn_g; f.beta = P + w.bn_b;
       f.moving_mean = m->St + w.bn_mm; f.moving_var = m->St + w.bn_mv; f.training = training; f.update_moving = training;
       f.eps = c.bn_eps; f.momentum = c.bn_momentum; f.scale = a.bn_scale; f.shift = a.bn_shift; f.save_mean = a.bn_mean; f.save_rstd = a.bn_rstd; f.D = D;
-      CVT_CUDA(launch_bn_finalize(f, s));
+      if (training || !m->skip_prep) CVT_CUDA(launch_bn_finalize(f, s));      // inference statistics are the moving ones: weight-only
     }
   }
   prof_mark(s, kStageNames[si][2]);
@@ -601,7 +601,8 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
     // proj_q/k/v Dense (:180-182) + MHA query/key/value EinsumDense + BatchNorm affine + 1/sqrt(key_dim), folded into one GEMM (fold.cu)
     const StageFold& f = m->fold[si]; float* F = m->Fd;
     const bool bn = g.method == CVT_PROJ_DW_BN;
-    CVT_CUDA(launch_bn_fold(F + f.Wc, F + f.bc, bn ? a.bn_scale : nullptr, bn ? a.bn_shift : nullptr, 0.125f, D, F + f.Wft, F + f.bf, s));
+    if (training || !m->skip_prep)
+      CVT_CUDA(launch_bn_fold(F + f.Wc, F + f.bc, bn ? a.bn_scale : nullptr, bn ? a.bn_shift : nullptr, 0.125f, D, F + f.Wft, F + f.bf, s));
     GemmP p; p.M = R; p.N = D; p.K = D; p.A = a.conv; p.lda = D; p.B = F + f.Wft; p.ldb = D; p.b_mode = B_NK; p.C = a.qkv2; p.ldc = D;
     p.bias = F + f.bf; p.epi = EPI_BIAS | EPI_ROUND; p.batch = 3;
     p.batch = 3; p.a_bs0 = RD; p.b_bs0 = (long long)D * D; p.c_bs0 = RD; p.bias_bs = D;
@@ -704,7 +705,8 @@ static cudaError_t forward_impl(Model* m, const float* img, const float* proc, i
       CVT_CUDA(launch_philox_mask(a.mask2, RD, c.drop_rate, m->dropout_seed, m->dropout_step, i * 4 + 2, s, m->dyn));
     }
   }
-  if (c.precision != CVT_PREC_FP32) {
+  const bool prep = training || !m->skip_prep;           // predict loop: weight-only work was done by the first chunk of the call
+  if (c.precision != CVT_PREC_FP32 && prep) {
     CVT_CUDA(launch_transpose_weights(m->P, m->Pt, m->Pr, m->tr_descs_dev, (int)m->tr_descs.size(), m->tr_tiles, s));
     m->pt_valid = true;
     if (m->folded) CVT_CUDA(launch_multigemm(m->mg_fwd_dev, m->mg_fwd_n, m->mg_fwd_tiles, s));
@@ -938,7 +940,7 @@ static int check_batch(Model* m, int batch, const char* who) {
   return CVT_OK;
 }
 
-static int infer_forward(Model* m, const float* img, const float* proc, int B);
+static int infer_forward(Model* m, const float* img, const float* proc, int B, bool cached = false);
 
 int cvt_forward(cvt_model* h, const float* img_dev, const float* proc_dev, int batch, int training, float* out_dev) {
   if (!h || !img_dev) { set_error("cvt_forward: null argument"); return CVT_ERR_INVALID; }
@@ -1071,7 +1073,7 @@ int cvt_optimizer_reset(cvt_model* h) {
 int64_t cvt_optimizer_step_count(const cvt_model* h) { return h ? h->m.adam_t : -1; }
 
 // ---- CUDA graphs: one captured graph per (kind, input buffers, batch) ----------------------------------------------
-enum { GRAPH_TRAIN = 0, GRAPH_INFER = 1 };
+enum { GRAPH_TRAIN = 0, GRAPH_INFER = 1, GRAPH_INFER_CACHED = 2 };
 static Model::GraphEntry* graph_slot(Model* m, int kind, const float* img, const float* proc, const float* y, int B) {
   for (auto& g : m->graphs) if (g.kind == kind && g.img == img && g.proc == proc && g.y == y && g.batch == B) return &g;
   if (m->graphs.size() >= 16) { if (m->graphs.front().exec) cudaGraphExecDestroy(m->graphs.front().exec); m->graphs.erase(m->graphs.begin()); }
@@ -1143,9 +1145,13 @@ static int train_step_dev(Model* m, const float* img, const float* proc, const f
   return train_step_body(m, img, proc, y, B, 3);
 }
 
-// inference forward (training = 0) through the graph cache; falls back to eager issue on first sighting
-static int infer_forward(Model* m, const float* img, const float* proc, int B) {
-  Model::GraphEntry* g = (m->use_graphs && !g_prof) ? graph_slot(m, GRAPH_INFER, img, proc, nullptr, B) : nullptr;
+// inference forward (training = 0) through the graph cache; falls back to eager issue on first sighting.
+// cached: the weights, BatchNorm moving statistics and everything derived from them alone (K-major / TF32 copies, folded q/k/v
+// kernels, BatchNorm scale / shift) are as the previous forward of this call left them: the predict loop's chunks after the first.
+static int infer_forward(Model* m, const float* img, const float* proc, int B, bool cached) {
+  struct Scope { Model* m; ~Scope() { m->skip_prep = false; } } scope{m};
+  m->skip_prep = cached;
+  Model::GraphEntry* g = (m->use_graphs && !g_prof) ? graph_slot(m, cached ? GRAPH_INFER_CACHED : GRAPH_INFER, img, proc, nullptr, B) : nullptr;
   if (g && !g->exec) {
     const long long l0 = g_launch_count;
     cudaGraph_t graph = nullptr;
@@ -1274,7 +1280,7 @@ int cvt_predict_host(cvt_model* h, const float* img, const float* proc, int64_t 
     const int B = (int)std::min<int64_t>(c.max_batch, n - o);
     { const int rs = stage_chunk(m, i, img + o * per, proc ? proc + o * c.proc_dim : nullptr, nullptr, B); if (rs) return rs; }
     last = staging_of(m, (int)(i & 1));
-    { const int rf = infer_forward(m, last.img, c.proc_dim > 0 ? last.proc : nullptr, B); if (rf) return rf; }
+    { const int rf = infer_forward(m, last.img, c.proc_dim > 0 ? last.proc : nullptr, B, i > 0); if (rf) return rf; }
     API_CUDA(cudaMemcpyAsync(m->pin_series + o * c.num_classes, m->pred, (size_t)B * c.num_classes * sizeof(float), cudaMemcpyDeviceToHost, m->stream));
     API_CUDA(cudaEventRecord(m->ev_done[i & 1], m->stream));
   }

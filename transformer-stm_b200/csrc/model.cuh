@@ -104,6 +104,7 @@ struct Model {
   // Per-step scalars (Adam step size, gradient scale, dropout counter) live in lr_dev so that replays see fresh values.
   struct GraphEntry { int kind; const float* img; const float* proc; const float* y; int batch; cudaGraphExec_t exec; long long launches; };
   int use_graphs = 1;
+  bool skip_prep = false;                 // set while a predict-loop chunk after the first is issued: weight-only kernels are skipped
   std::vector<GraphEntry> graphs;
   float* lr_dev = nullptr;
   const float* dyn = nullptr;             // == lr_dev while a train step is being issued (eagerly or under capture)
