@@ -1299,14 +1299,17 @@ int cvt_evaluate_host(cvt_model* h, const float* img, const float* proc, const f
   const size_t per = (size_t)c.image_h * c.image_w * c.in_chans;
   const long long l0 = g_launch_count;
   API_CUDA(cudaMemsetAsync(m->metrics + 2, 0, 2 * sizeof(float), m->stream));
-  for (int64_t o = 0; o < n; o += c.max_batch) {
+  Staging last = staging_of(m, 0);
+  int64_t i = 0;
+  for (int64_t o = 0; o < n; o += c.max_batch, ++i) {        // as cvt_predict_host: chunk i+1 is copied while chunk i runs
     const int B = (int)std::min<int64_t>(c.max_batch, n - o);
-    API_CUDA(cudaMemcpyAsync(m->in_img, img + o * per, B * per * sizeof(float), cudaMemcpyHostToDevice, m->stream));
-    if (c.proc_dim > 0) API_CUDA(cudaMemcpyAsync(m->in_proc, proc + o * c.proc_dim, (size_t)B * c.proc_dim * sizeof(float), cudaMemcpyHostToDevice, m->stream));
-    API_CUDA(cudaMemcpyAsync(m->in_y, y + o * c.num_classes, (size_t)B * c.num_classes * sizeof(float), cudaMemcpyHostToDevice, m->stream));
-    API_CUDA(forward_impl(m, m->in_img, c.proc_dim > 0 ? m->in_proc : nullptr, B, 0));
-    API_CUDA(launch_mse_loss(m->pred, m->in_y, B * c.num_classes, m->metrics + 2, nullptr, 1.f, 1, m->stream));
+    { const int rs = stage_chunk(m, i, img + o * per, proc ? proc + o * c.proc_dim : nullptr, y + o * c.num_classes, B); if (rs) return rs; }
+    last = staging_of(m, (int)(i & 1));
+    { const int rf = infer_forward(m, last.img, c.proc_dim > 0 ? last.proc : nullptr, B, i > 0); if (rf) return rf; }
+    API_CUDA(launch_mse_loss(m->pred, last.y, B * c.num_classes, m->metrics + 2, nullptr, 1.f, 1, m->stream));
+    API_CUDA(cudaEventRecord(m->ev_done[i & 1], m->stream));
   }
+  g_last_inputs = {last.img, c.proc_dim > 0 ? last.proc : nullptr};
   API_CUDA(cudaMemcpyAsync(m->pin_metrics + 2, m->metrics + 2, 2 * sizeof(float), cudaMemcpyDeviceToHost, m->stream));
   API_CUDA(cudaStreamSynchronize(m->stream));
   const double cnt = (double)n * c.num_classes;
