@@ -773,14 +773,15 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
   CVT_CUDA(wgrad_bias(m, a.y, D, D, m->gH, H4, H4, R, G + w.f1w, G + w.f1b, 1, 0, 0, s));
   CVT_CUDA(run_gemm(m, dense_dgrad(m->gH, H4, R, H4, P + w.f1w, D, m->gC, D), s));          // dY
   // second use of norm1 (:278): dX1 = dX2 + LN'(dY)
+  // ... and, in the same pass, the gradient through the dropout of the attention output projection (:189): gM = gD * mask_proj / keep
   CVT_CUDA(launch_ln_bwd(m->gC, D, a.x1, rowmap_none(), D, a.lnb_mean, a.lnb_rstd, P + w.ln_g, dX2, m->gD, rowmap_none(), D,
-                         G + w.ln_g, G + w.ln_b, R, D, s));
+                         G + w.ln_g, G + w.ln_b, R, D, s, drop ? a.mask_proj : nullptr, keep_scale, m->gM, m->folded ? 1 : 0));
   prof_mark(s, kStageNames[si][7]);
   if (m->folded) {
     // ---- folded path (fold.cu): one wgrad + one dgrad per stacked pair; individual gradients are unfolded at the end of backward ----
     const StageFold& f = m->fold[si]; float* F = m->Fd;
     const float* dA2 = m->gD;
-    if (drop) { CVT_CUDA(launch_mask_scale(m->gM, m->gD, a.mask_proj, keep_scale, RD, s, 1)); dA2 = m->gM; }
+    if (drop) dA2 = m->gM;
     CVT_CUDA(wgrad_bias(m, a.attn_o, D, D, dA2, D, D, R, G + f.Zo, G + w.prb, 1, 0, 0, s));        // Zo = o^T dA2, so = colsum dA2 = dbproj
     { GemmP q = dense_dgrad(dA2, D, R, D, F + f.Wo, D, m->gE, D); q.epi |= EPI_ROUND; CVT_CUDA(run_gemm(m, q, s)); }   // dO = dA2 Wo^T (TMA operand of attention backward)
     prof_mark(s, kStageNames[si][8]);
@@ -814,7 +815,7 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
   } else {
   // ---- attention output projections ----
   const float* dA2 = m->gD;
-  if (drop) { CVT_CUDA(launch_mask_scale(m->gM, m->gD, a.mask_proj, keep_scale, RD, s)); dA2 = m->gM; }
+  if (drop) dA2 = m->gM;
   CVT_CUDA(wgrad_bias(m, a.a1, D, D, dA2, D, D, R, G + w.prw, G + w.prb, 1, 0, 0, s));
   CVT_CUDA(run_gemm(m, dense_dgrad(dA2, D, R, D, P + w.prw, D, m->gC, D), s));              // dA1
   CVT_CUDA(wgrad_bias(m, a.attn_o, D, D, m->gC, D, D, R, G + w.ow, G + w.ob, 1, 0, 0, s));

@@ -140,7 +140,7 @@ __device__ __forceinline__ void epilogue_apply(const GemmP& p, float4 acc, float
   float v[4], pre[4]; uint32_t mk;
   epilogue_math<E>(p, acc, b4, alpha, m, idx0, use_cf, cf, o, v, pre, mk);
   if ((E & EPI_GELU) && aux) *reinterpret_cast<float4*>(aux + idx0) = make_float4(pre[0], pre[1], pre[2], pre[3]);
-  if ((E & EPI_PHILOX) && (p.epi & EPI_MASK)) *reinterpret_cast<uint32_t*>(p.mask_gen + idx0) = mk;
+  if ((E & EPI_PHILOX) && !(E & EPI_GELU_DSAVE) && (p.epi & EPI_MASK)) *reinterpret_cast<uint32_t*>(p.mask_gen + idx0) = mk;   // (DSAVE: the mask lives on inside aux)
   *reinterpret_cast<float4*>(Cp + idx0) = make_float4(v[0], v[1], v[2], v[3]);
 }
 // 8 consecutive columns of one row with 32-byte stores (st.global.v8.f32, sm_100): the per-warp store issue rate, not bytes, is what
@@ -158,7 +158,7 @@ __device__ __forceinline__ void epilogue_apply8(const GemmP& p, float4 acc0, flo
   epilogue_math<E>(p, acc0, b0, alpha, m, idx0, use_cf, cf0, o0, v0, pre0, mk0);
   epilogue_math<E>(p, acc1, b1, alpha, m, idx0 + 4, use_cf, cf1, o1, v1, pre1, mk1);
   if ((E & EPI_GELU) && aux) st_global_v8(aux + idx0, pre0, pre1);
-  if ((E & EPI_PHILOX) && (p.epi & EPI_MASK)) *reinterpret_cast<uint2*>(p.mask_gen + idx0) = make_uint2(mk0, mk1);
+  if ((E & EPI_PHILOX) && !(E & EPI_GELU_DSAVE) && (p.epi & EPI_MASK)) *reinterpret_cast<uint2*>(p.mask_gen + idx0) = make_uint2(mk0, mk1);
   st_global_v8(Cp + idx0, v0, v1);
 }
 

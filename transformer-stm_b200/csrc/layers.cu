@@ -528,11 +528,14 @@ cudaError_t launch_ln_fwd(const float* x, RowMap in_map, long long ldx, const fl
 
 cudaError_t launch_ln_bwd(const float* dy, long long lddy, const float* x, RowMap in_map, long long ldx, const float* mean,
                           const float* rstd, const float* gamma, const float* dres, float* dx, RowMap out_map, long long ldo,
-                          float* dgamma, float* dbeta, int rows, int D, cudaStream_t s) {
+                          float* dgamma, float* dbeta, int rows, int D, cudaStream_t s,
+                          const uint8_t* mask, float mscale, float* dxm, int round_m) {
   if (rows <= 0) return cudaSuccess;
   if (D % 32 != 0 || D > 32 * LN_MAXV) { set_error("layer norm: D must be a multiple of 32 and <= 512"); return cudaErrorInvalidValue; }
+  if (mask && (out_map.period || ldo != D)) { set_error("layer norm backward: the masked output needs a dense [rows, D] dx"); return cudaErrorInvalidValue; }
   {
-    const cudaError_t e = launch_ln_bwd_v4(dy, lddy, x, in_map, ldx, mean, rstd, gamma, dres, dx, out_map, ldo, dgamma, dbeta, rows, D, s);
+    const cudaError_t e = launch_ln_bwd_v4(dy, lddy, x, in_map, ldx, mean, rstd, gamma, dres, dx, out_map, ldo, dgamma, dbeta, rows, D, s,
+                                           mask, mscale, dxm, round_m);
     if (e != cudaErrorNotSupported) return e;
   }
   int blocks = cdiv(rows, 8);
@@ -540,6 +543,7 @@ cudaError_t launch_ln_bwd(const float* dy, long long lddy, const float* x, RowMa
   ln_bwd_kernel<<<blocks, 256, 2 * D * sizeof(float), s>>>(dy, lddy, x, in_map, ldx, mean, rstd, gamma, dres, dx, out_map, ldo,
                                                            dgamma, dbeta, rows, D);
   CVT_LAUNCH_CHECK();
+  if (mask) CVT_CUDA(launch_mask_scale(dxm, dx, mask, mscale, (long long)rows * D, s, round_m));
   return cudaSuccess;
 }
 

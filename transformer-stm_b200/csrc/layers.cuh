@@ -12,14 +12,18 @@ cudaError_t launch_ln_fwd(const float* x, RowMap in_map, long long ldx, const fl
 cudaError_t launch_ln_bwd(const float* dy, long long lddy, const float* x, RowMap in_map, long long ldx,
                           const float* mean, const float* rstd, const float* gamma,
                           const float* dres, float* dx, RowMap out_map, long long ldo,
-                          float* dgamma, float* dbeta, int rows, int D, cudaStream_t s);
+                          float* dgamma, float* dbeta, int rows, int D, cudaStream_t s,
+                          const uint8_t* mask = nullptr, float mscale = 0.f, float* dxm = nullptr, int round_m = 0);
+// mask != nullptr (identity out_map, ldo == D): also dxm = dx * (mask ? mscale : 0), the gradient through the dropout that follows in
+// backward order, in the same pass
 
 // vectorised instantiations (ln.cu); cudaErrorNotSupported -> caller uses the generic kernel
 cudaError_t launch_ln_fwd_v4(const float* x, RowMap in_map, long long ldx, const float* gamma, const float* beta, float eps,
                              float* y, long long ldy, float* mean, float* rstd, int rows, int D, cudaStream_t s, int round_out = 0);
 cudaError_t launch_ln_bwd_v4(const float* dy, long long lddy, const float* x, RowMap in_map, long long ldx, const float* mean,
                              const float* rstd, const float* gamma, const float* dres, float* dx, RowMap out_map, long long ldo,
-                             float* dgamma, float* dbeta, int rows, int D, cudaStream_t s);
+                             float* dgamma, float* dbeta, int rows, int D, cudaStream_t s,
+                             const uint8_t* mask = nullptr, float mscale = 0.f, float* dxm = nullptr, int round_m = 0);
 
 // Projection.call for q, k, v in one pass over the normalised map — models/CvT(Par).py:102-112,157-170.
 //   method[z]: 0 depthwise 3x3 (SAME, no bias), 1 3x3 average pool (SAME, valid-count divisor), 2 identity

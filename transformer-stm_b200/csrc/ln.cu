@@ -77,7 +77,10 @@ __global__ void __launch_bounds__(256) ln_bwd_v4_kernel(const float* __restrict_
                                                         RowMap in_map, long long ldx, const float* __restrict__ mean,
                                                         const float* __restrict__ rstd, const float* __restrict__ gamma,
                                                         const float* dres, float* dx, RowMap out_map, long long ldo,   // may alias
-                                                        float* __restrict__ dgamma, float* __restrict__ dbeta, int rows) {
+                                                        float* __restrict__ dgamma, float* __restrict__ dbeta, int rows,
+                                                        const uint8_t* __restrict__ mask, float mscale, float* __restrict__ dxm, int round_m) {
+  // mask != nullptr: a second output dxm = dx * (mask ? mscale : 0) (the gradient through the dropout that follows in backward order;
+  // mask and dxm are indexed like dx), optionally rounded to TF32 for the tensor-core GEMMs that consume it
   constexpr int RPW = 32 / LPR, D = LPR * VPL * 4;
   __shared__ float red[2 * D];
   for (int i = threadIdx.x; i < 2 * D; i += blockDim.x) red[i] = 0.f;
@@ -93,6 +96,7 @@ __global__ void __launch_bounds__(256) ln_bwd_v4_kernel(const float* __restrict_
   const float invD = 1.f / (float)D;
   for (int base = warp * RPW * U; base < rows; base += nwarps * RPW * U) {
     float4 xv[U][VPL], dv[U][VPL], rv[U][VPL];
+    uint32_t mk[U][VPL];
     float mu[U], rs[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
@@ -108,6 +112,7 @@ __global__ void __launch_bounds__(256) ln_bwd_v4_kernel(const float* __restrict_
         xv[u][v] = ok ? *reinterpret_cast<const float4*>(xr + c) : make_float4(0.f, 0.f, 0.f, 0.f);
         dv[u][v] = ok ? *reinterpret_cast<const float4*>(dr + c) : make_float4(0.f, 0.f, 0.f, 0.f);
         rv[u][v] = (ok && rr) ? *reinterpret_cast<const float4*>(rr + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+        mk[u][v] = (ok && mask) ? *reinterpret_cast<const uint32_t*>(mask + out_map(row) * ldo + c) : 0u;
       }
     }
 #pragma unroll
@@ -133,6 +138,13 @@ __global__ void __launch_bounds__(256) ln_bwd_v4_kernel(const float* __restrict_
           o.x = rv[u][v].x + rs[u] * (gg[v].x - m1 - xh[v].x * m2); o.y = rv[u][v].y + rs[u] * (gg[v].y - m1 - xh[v].y * m2);
           o.z = rv[u][v].z + rs[u] * (gg[v].z - m1 - xh[v].z * m2); o.w = rv[u][v].w + rs[u] * (gg[v].w - m1 - xh[v].w * m2);
           *reinterpret_cast<float4*>(dxr + (li + v * LPR) * 4) = o;
+          if (mask) {
+            float4 q;
+            q.x = (mk[u][v] & 0xFFu) ? o.x * mscale : 0.f; q.y = (mk[u][v] & 0xFF00u) ? o.y * mscale : 0.f;
+            q.z = (mk[u][v] & 0xFF0000u) ? o.z * mscale : 0.f; q.w = (mk[u][v] & 0xFF000000u) ? o.w * mscale : 0.f;
+            if (round_m) { q.x = round_tf32(q.x); q.y = round_tf32(q.y); q.z = round_tf32(q.z); q.w = round_tf32(q.w); }
+            *reinterpret_cast<float4*>(dxm + out_map(row) * ldo + (li + v * LPR) * 4) = q;
+          }
         }
       }
     }
@@ -179,10 +191,11 @@ cudaError_t launch_ln_fwd_v4(const float* x, RowMap in_map, long long ldx, const
 
 cudaError_t launch_ln_bwd_v4(const float* dy, long long lddy, const float* x, RowMap in_map, long long ldx, const float* mean,
                              const float* rstd, const float* gamma, const float* dres, float* dx, RowMap out_map, long long ldo,
-                             float* dgamma, float* dbeta, int rows, int D, cudaStream_t s) {
+                             float* dgamma, float* dbeta, int rows, int D, cudaStream_t s, const uint8_t* mask, float mscale, float* dxm, int round_m) {
   if ((ldx & 3) || (lddy & 3) || (ldo & 3) || !al16(x) || !al16(dy) || !al16(dx) || !al16(gamma) || (dres && !al16(dres))) return cudaErrorNotSupported;
+  if (mask && ((reinterpret_cast<uintptr_t>(mask) & 3) || !al16(dxm))) return cudaErrorNotSupported;
   auto grid = [&](int rpw_u) { long long w = cdivl(rows, rpw_u); long long b = cdivl(w, 8); return (int)(b < 1 ? 1 : (b > kNumSMs * 4 ? kNumSMs * 4 : b)); };
-#define LN_BWD(VPL, LPR, U) ln_bwd_v4_kernel<VPL, LPR, U><<<grid((32 / LPR) * U), 256, 0, s>>>(dy, lddy, x, in_map, ldx, mean, rstd, gamma, dres, dx, out_map, ldo, dgamma, dbeta, rows)
+#define LN_BWD(VPL, LPR, U) ln_bwd_v4_kernel<VPL, LPR, U><<<grid((32 / LPR) * U), 256, 0, s>>>(dy, lddy, x, in_map, ldx, mean, rstd, gamma, dres, dx, out_map, ldo, dgamma, dbeta, rows, mask, mscale, dxm, round_m)
   if (D == 64) LN_BWD(1, 16, 4);
   else if (D == 128) LN_BWD(1, 32, 4);
   else if (D == 192) LN_BWD(3, 16, 2);
