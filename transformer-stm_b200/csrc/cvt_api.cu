@@ -760,7 +760,8 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
   prof_mark(s, kStageNames[si][6]);
   // ---- Mlp ----
   const float* dM = dX2;
-  if (drop) { CVT_CUDA(launch_mask_scale(m->gM, dX2, a.mask2, keep_scale, RD, s, m->folded)); dM = m->gM; }
+  if (drop) { if (!m->premasked) CVT_CUDA(launch_mask_scale(m->gM, dX2, a.mask2, keep_scale, RD, s, m->folded)); dM = m->gM; }
+  m->premasked = false;
   CVT_CUDA(wgrad_bias(m, a.hact, H4, H4, dM, D, D, R, G + w.f2w, G + w.f2b, 1, 0, 0, s));
   {
     GemmP p = dense_dgrad(dM, D, R, D, P + w.f2w, H4, m->gH, H4);      // d hpre = (dM W2^T) * gelu'(hpre) * mask1/keep
@@ -888,7 +889,10 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
       GemmP q; q.M = B * g.T; q.N = f.Kc; q.K = D; q.A = dY; q.lda = D; q.B = m->Pr + w.conv_w; q.ldb = D; q.b_mode = B_NK;
       q.C = a.col; q.ldc = f.Kp;                   // dcol = dY W^T overwrites the patch matrix (its last reader was the wgrad above)
       CVT_CUDA(run_gemm(m, q, s));
-      CVT_CUDA(launch_col2im(a.col, cv, B, f.Kp, dXprev, s));
+      // the previous block ends in the Mlp dropout (:257): its masked gradient is written in the same pass (no cls rows there: dense offsets)
+      const bool pm = drop && !gp.has_cls && xin_boff == 0 && xin_bstride == (long long)gp.Tc * gp.D;
+      CVT_CUDA(launch_col2im(a.col, cv, B, f.Kp, dXprev, s, pm ? m->buf[si - 1].mask2 : nullptr, keep_scale, m->gM, 1));
+      m->premasked = pm;
     }
     return cudaSuccess;
   }
@@ -919,6 +923,7 @@ static thread_local FwdInputs g_last_inputs{nullptr, nullptr};
 static cudaError_t backward_impl(Model* m, const float* img, const float* proc, int B, int training, int stop_after_stage, float** tap_grad) {
   cudaStream_t s = m->stream;
   g_tc = m->cfg.precision != CVT_PREC_FP32;
+  m->premasked = false;
   CVT_CUDA(cudaMemsetAsync(m->G, 0, (size_t)(m->n_train + m->n_z) * sizeof(float), s));
   int cur = (m->n_stages - 1) & 1;
   CVT_CUDA(head_backward(m, proc, B, m->gX[cur]));

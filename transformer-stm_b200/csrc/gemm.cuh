@@ -89,7 +89,8 @@ cudaError_t launch_transpose_weights(const float* src, float* dst, float* dst2, 
 
 // explicit im2col / col2im for ConvEmbed in TF32 mode (im2col.cu)
 cudaError_t launch_im2col(const float* x, const ConvGeom& g, int M, int K, int ldc, float* col, cudaStream_t s);
-cudaError_t launch_col2im(const float* dcol, const ConvGeom& g, int B, int ldc, float* dx, cudaStream_t s);
+cudaError_t launch_col2im(const float* dcol, const ConvGeom& g, int B, int ldc, float* dx, cudaStream_t s, const uint8_t* mask = nullptr,
+                          float mscale = 0.f, float* dxm = nullptr, int round_m = 0);
 
 // column sums (bias gradients): out[z][n] += sum_r X[z][map(r)*ld + n]
 cudaError_t launch_colsum(const float* X, long long ld, RowMap map, int rows, int N, int batch, long long x_bs,

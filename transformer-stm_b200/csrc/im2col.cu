@@ -49,7 +49,10 @@ __global__ void __launch_bounds__(256) im2col_scalar_kernel(const float* __restr
 
 // transposed gather: dx[b, y, x, c] = sum over taps (kh, kw) with s | (y + pt - kh), s | (x + pl - kw) of dcol[(b,i,j)][(kh,kw,c)]
 // one thread per (b, y, x, float4 channel group); cin % 4 == 0
-__global__ void __launch_bounds__(256) col2im_v4_kernel(const float* __restrict__ dcol, ConvGeom g, int B, int ldc, float* __restrict__ dx) {
+// mask != nullptr: also dxm = dx * (mask ? mscale : 0) at the same offsets (the dropout at the end of the previous block's Mlp, next in
+// backward order), optionally rounded to TF32
+__global__ void __launch_bounds__(256) col2im_v4_kernel(const float* __restrict__ dcol, ConvGeom g, int B, int ldc, float* __restrict__ dx,
+                                                        const uint8_t* __restrict__ mask, float mscale, float* __restrict__ dxm, int round_m) {
   const int c4n = g.cin >> 2;
   const long long total = (long long)B * g.hin * g.win * c4n;
   for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
@@ -72,7 +75,16 @@ __global__ void __launch_bounds__(256) col2im_v4_kernel(const float* __restrict_
         a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
       }
     }
-    *reinterpret_cast<float4*>(dx + (long long)b * g.bstride + g.boff + ((long long)yy * g.win + xx) * g.cin + c) = a;
+    const long long off = (long long)b * g.bstride + g.boff + ((long long)yy * g.win + xx) * g.cin + c;
+    *reinterpret_cast<float4*>(dx + off) = a;
+    if (mask) {
+      const uint32_t mk = *reinterpret_cast<const uint32_t*>(mask + off);
+      float4 q;
+      q.x = (mk & 0xFFu) ? a.x * mscale : 0.f; q.y = (mk & 0xFF00u) ? a.y * mscale : 0.f;
+      q.z = (mk & 0xFF0000u) ? a.z * mscale : 0.f; q.w = (mk & 0xFF000000u) ? a.w * mscale : 0.f;
+      if (round_m) { q.x = round_tf32(q.x); q.y = round_tf32(q.y); q.z = round_tf32(q.z); q.w = round_tf32(q.w); }
+      *reinterpret_cast<float4*>(dxm + off) = q;
+    }
   }
 }
 
@@ -89,9 +101,10 @@ cudaError_t launch_im2col(const float* x, const ConvGeom& g, int M, int K, int l
   return cudaSuccess;
 }
 
-cudaError_t launch_col2im(const float* dcol, const ConvGeom& g, int B, int ldc, float* dx, cudaStream_t s) {
+cudaError_t launch_col2im(const float* dcol, const ConvGeom& g, int B, int ldc, float* dx, cudaStream_t s, const uint8_t* mask, float mscale,
+                          float* dxm, int round_m) {
   if ((g.cin & 3) || (g.boff & 3) || (g.bstride & 3)) { set_error("col2im: cin must be a multiple of 4"); return cudaErrorInvalidValue; }
-  col2im_v4_kernel<<<ew_grid((long long)B * g.hin * g.win * (g.cin >> 2)), 256, 0, s>>>(dcol, g, B, ldc, dx);
+  col2im_v4_kernel<<<ew_grid((long long)B * g.hin * g.win * (g.cin >> 2)), 256, 0, s>>>(dcol, g, B, ldc, dx, mask, mscale, dxm, round_m);
   CVT_LAUNCH_CHECK();
   return cudaSuccess;
 }

@@ -104,6 +104,7 @@ struct Model {
   // Per-step scalars (Adam step size, gradient scale, dropout counter) live in lr_dev so that replays see fresh values.
   struct GraphEntry { int kind; const float* img; const float* proc; const float* y; int batch; cudaGraphExec_t exec; long long launches; };
   int use_graphs = 1;
+  bool premasked = false;                 // backward: gM already holds dX2 * mask2 / keep of the stage about to run (written by col2im)
   bool skip_prep = false;                 // set while a predict-loop chunk after the first is issued: weight-only kernels are skipped
   std::vector<GraphEntry> graphs;
   float* lr_dev = nullptr;
