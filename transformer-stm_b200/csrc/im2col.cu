@@ -47,6 +47,29 @@ __global__ void __launch_bounds__(256) im2col_scalar_kernel(const float* __restr
   }
 }
 
+// any cin, ldc % 4 == 0: one thread per (row m, group of 4 padded columns): the index decode (runtime divisions) is paid once per 16-byte
+// store instead of once per element, and consecutive threads write consecutive 16-byte pieces of the contiguous patch matrix
+__global__ void __launch_bounds__(256) im2col_vec_kernel(const float* __restrict__ x, ConvGeom g, int M, int K, int ldc, float* __restrict__ col) {
+  const int q4n = ldc >> 2;
+  const long long total = (long long)M * q4n;
+  const int hw = g.ho * g.wo;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+    const int m = (int)(idx / q4n), kk = (int)(idx - (long long)m * q4n) << 2;
+    const int b = m / hw, pix = m - b * hw, oi = pix / g.wo, oj = pix - oi * g.wo;
+    int tap = kk / g.cin, c = kk - tap * g.cin, kh = tap / g.k, kw = tap - kh * g.k;
+    const float* xb = x + (long long)b * g.bstride + g.boff;
+    float v[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      v[e] = 0.f;
+      const int yy = g.s * oi + kh - g.pt, xx = g.s * oj + kw - g.pl;
+      if (kk + e < K && yy >= 0 && yy < g.hin && xx >= 0 && xx < g.win) v[e] = round_tf32(__ldg(xb + ((long long)yy * g.win + xx) * g.cin + c));
+      if (++c == g.cin) { c = 0; if (++kw == g.k) { kw = 0; ++kh; } }
+    }
+    *reinterpret_cast<float4*>(col + idx * 4) = make_float4(v[0], v[1], v[2], v[3]);
+  }
+}
+
 // transposed gather: dx[b, y, x, c] = sum over taps (kh, kw) with s | (y + pt - kh), s | (x + pl - kw) of dcol[(b,i,j)][(kh,kw,c)]
 // one thread per (b, y, x, float4 channel group); cin % 4 == 0
 // mask != nullptr: also dxm = dx * (mask ? mscale : 0) at the same offsets (the dropout at the end of the previous block's Mlp, next in
@@ -95,6 +118,8 @@ inline int ew_grid(long long n) { long long b = (n + 255) / 256; const long long
 cudaError_t launch_im2col(const float* x, const ConvGeom& g, int M, int K, int ldc, float* col, cudaStream_t s) {
   if ((g.cin & 3) == 0 && (g.boff & 3) == 0 && (g.bstride & 3) == 0 && ldc == K)
     im2col_v4_kernel<<<ew_grid((long long)M * (K >> 2)), 256, 0, s>>>(x, g, M, ldc, col);
+  else if ((ldc & 3) == 0 && (reinterpret_cast<uintptr_t>(col) & 15) == 0)
+    im2col_vec_kernel<<<ew_grid((long long)M * (ldc >> 2)), 256, 0, s>>>(x, g, M, K, ldc, col);
   else
     im2col_scalar_kernel<<<ew_grid((long long)M * ldc), 256, 0, s>>>(x, g, M, K, ldc, col);
   CVT_LAUNCH_CHECK();
