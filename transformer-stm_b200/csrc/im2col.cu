@@ -9,7 +9,9 @@ namespace cvt {
 namespace {
 
 // cin % 4 == 0: one thread per (row m, tap, float4 channel group)
+template <int KK, int SS>
 __global__ void __launch_bounds__(256) im2col_v4_kernel(const float* __restrict__ x, ConvGeom g, int M, int ldc, float* __restrict__ col) {
+  if (KK) { g.k = KK; g.s = SS; }
   const int c4n = g.cin >> 2, per_row = g.k * g.k * c4n;
   const long long total = (long long)M * per_row;
   const int hw = g.ho * g.wo;
@@ -74,8 +76,11 @@ __global__ void __launch_bounds__(256) im2col_vec_kernel(const float* __restrict
 // one thread per (b, y, x, float4 channel group); cin % 4 == 0
 // mask != nullptr: also dxm = dx * (mask ? mscale : 0) at the same offsets (the dropout at the end of the previous block's Mlp, next in
 // backward order), optionally rounded to TF32
+// KK / SS: compile-time kernel size and stride (0 = read them from g): the tap loops are full of `% s` and `/ s`
+template <int KK, int SS>
 __global__ void __launch_bounds__(256) col2im_v4_kernel(const float* __restrict__ dcol, ConvGeom g, int B, int ldc, float* __restrict__ dx,
                                                         const uint8_t* __restrict__ mask, float mscale, float* __restrict__ dxm, int round_m) {
+  if (KK) { g.k = KK; g.s = SS; }
   const int c4n = g.cin >> 2;
   const long long total = (long long)B * g.hin * g.win * c4n;
   for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
@@ -84,15 +89,17 @@ __global__ void __launch_bounds__(256) col2im_v4_kernel(const float* __restrict_
     const int xx = (int)(r % g.win); r /= g.win;
     const int yy = (int)(r % g.hin); const int b = (int)(r / g.hin);
     float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int kh = 0; kh < g.k; ++kh) {
+#pragma unroll
+    for (int kh = 0; kh < (KK ? KK : g.k); ++kh) {
       const int ty = yy + g.pt - kh;
-      if (ty < 0 || ty % g.s) continue;
-      const int oi = ty / g.s;
+      if (ty < 0 || ty % (SS ? SS : g.s)) continue;
+      const int oi = ty / (SS ? SS : g.s);
       if (oi >= g.ho) continue;
-      for (int kw = 0; kw < g.k; ++kw) {
+#pragma unroll
+      for (int kw = 0; kw < (KK ? KK : g.k); ++kw) {
         const int tx = xx + g.pl - kw;
-        if (tx < 0 || tx % g.s) continue;
-        const int oj = tx / g.s;
+        if (tx < 0 || tx % (SS ? SS : g.s)) continue;
+        const int oj = tx / (SS ? SS : g.s);
         if (oj >= g.wo) continue;
         const float4 v = *reinterpret_cast<const float4*>(dcol + ((long long)(b * g.ho + oi) * g.wo + oj) * ldc + (kh * g.k + kw) * g.cin + c);
         a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
@@ -117,7 +124,10 @@ inline int ew_grid(long long n) { long long b = (n + 255) / 256; const long long
 
 cudaError_t launch_im2col(const float* x, const ConvGeom& g, int M, int K, int ldc, float* col, cudaStream_t s) {
   if ((g.cin & 3) == 0 && (g.boff & 3) == 0 && (g.bstride & 3) == 0 && ldc == K)
-    im2col_v4_kernel<<<ew_grid((long long)M * (K >> 2)), 256, 0, s>>>(x, g, M, ldc, col);
+  {
+    if (g.k == 3 && g.s == 2) im2col_v4_kernel<3, 2><<<ew_grid((long long)M * (K >> 2)), 256, 0, s>>>(x, g, M, ldc, col);
+    else im2col_v4_kernel<0, 0><<<ew_grid((long long)M * (K >> 2)), 256, 0, s>>>(x, g, M, ldc, col);
+  }
   else if ((ldc & 3) == 0 && (reinterpret_cast<uintptr_t>(col) & 15) == 0)
     im2col_vec_kernel<<<ew_grid((long long)M * (ldc >> 2)), 256, 0, s>>>(x, g, M, K, ldc, col);
   else
@@ -129,7 +139,9 @@ cudaError_t launch_im2col(const float* x, const ConvGeom& g, int M, int K, int l
 cudaError_t launch_col2im(const float* dcol, const ConvGeom& g, int B, int ldc, float* dx, cudaStream_t s, const uint8_t* mask, float mscale,
                           float* dxm, int round_m) {
   if ((g.cin & 3) || (g.boff & 3) || (g.bstride & 3)) { set_error("col2im: cin must be a multiple of 4"); return cudaErrorInvalidValue; }
-  col2im_v4_kernel<<<ew_grid((long long)B * g.hin * g.win * (g.cin >> 2)), 256, 0, s>>>(dcol, g, B, ldc, dx, mask, mscale, dxm, round_m);
+  const int grid = ew_grid((long long)B * g.hin * g.win * (g.cin >> 2));
+  if (g.k == 3 && g.s == 2) col2im_v4_kernel<3, 2><<<grid, 256, 0, s>>>(dcol, g, B, ldc, dx, mask, mscale, dxm, round_m);     // ConvEmbed of stages 2, 3
+  else col2im_v4_kernel<0, 0><<<grid, 256, 0, s>>>(dcol, g, B, ldc, dx, mask, mscale, dxm, round_m);
   CVT_LAUNCH_CHECK();
   return cudaSuccess;
 }
