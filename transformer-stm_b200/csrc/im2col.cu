@@ -30,6 +30,30 @@ __global__ void __launch_bounds__(256) im2col_v4_kernel(const float* __restrict_
   }
 }
 
+// cin % 4 == 0 and k * k * cin / 4 <= 1024: a block walks a run of consecutive rows m; a thread keeps ONE (tap, float4 channel group) slot,
+// decoded once, and the (image, output row, output column) of the walk advances by increments: no division in the loop
+template <int KK, int SS>
+__global__ void __launch_bounds__(1024) im2col_rows_kernel(const float* __restrict__ x, ConvGeom g, int M, int ldc, float* __restrict__ col, int rpb) {
+  if (KK) { g.k = KK; g.s = SS; }
+  const int c4n = g.cin >> 2, per_row = g.k * g.k * c4n, r = threadIdx.x;
+  if (r >= per_row) return;
+  const int tap = r / c4n, c = (r - tap * c4n) << 2, kh = tap / g.k, kw = tap - kh * g.k;
+  const int dy = kh - g.pt, dx = kw - g.pl, koff = tap * g.cin + c;
+  const int m0 = blockIdx.x * rpb, m1 = min(M, m0 + rpb), hw = g.ho * g.wo;
+  int b = m0 / hw, pix = m0 - b * hw, oi = pix / g.wo, oj = pix - oi * g.wo;
+#pragma unroll 4
+  for (int m = m0; m < m1; ++m) {
+    const int yy = g.s * oi + dy, xx = g.s * oj + dx;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (yy >= 0 && yy < g.hin && xx >= 0 && xx < g.win) {
+      v = __ldg(reinterpret_cast<const float4*>(x + (long long)b * g.bstride + g.boff + ((long long)yy * g.win + xx) * g.cin + c));
+      v = make_float4(round_tf32(v.x), round_tf32(v.y), round_tf32(v.z), round_tf32(v.w));
+    }
+    *reinterpret_cast<float4*>(col + (long long)m * ldc + koff) = v;
+    if (++oj == g.wo) { oj = 0; if (++oi == g.ho) { oi = 0; ++b; } }
+  }
+}
+
 // any cin (stage 1: cin = 1): one thread per (row m, padded column kk)
 __global__ void __launch_bounds__(256) im2col_scalar_kernel(const float* __restrict__ x, ConvGeom g, int M, int K, int ldc, float* __restrict__ col) {
   const long long total = (long long)M * ldc;
@@ -125,6 +149,14 @@ inline int ew_grid(long long n) { long long b = (n + 255) / 256; const long long
 cudaError_t launch_im2col(const float* x, const ConvGeom& g, int M, int K, int ldc, float* col, cudaStream_t s) {
   if ((g.cin & 3) == 0 && (g.boff & 3) == 0 && (g.bstride & 3) == 0 && ldc == K)
   {
+    const int per_row = g.k * g.k * (g.cin >> 2), threads = (per_row + 31) / 32 * 32;
+    if (threads <= 1024) {
+      int rpb = 1;                                         // rows per block: about 16 blocks per SM
+      while (rpb < 16 && (M + 2 * rpb - 1) / (2 * rpb) >= kNumSMs * 16) rpb *= 2;
+      const int grid = (M + rpb - 1) / rpb;
+      if (g.k == 3 && g.s == 2) im2col_rows_kernel<3, 2><<<grid, threads, 0, s>>>(x, g, M, ldc, col, rpb);
+      else im2col_rows_kernel<0, 0><<<grid, threads, 0, s>>>(x, g, M, ldc, col, rpb);
+    } else
     if (g.k == 3 && g.s == 2) im2col_v4_kernel<3, 2><<<ew_grid((long long)M * (K >> 2)), 256, 0, s>>>(x, g, M, ldc, col);
     else im2col_v4_kernel<0, 0><<<ew_grid((long long)M * (K >> 2)), 256, 0, s>>>(x, g, M, ldc, col);
   }
