@@ -151,8 +151,7 @@ cudaError_t launch_im2col(const float* x, const ConvGeom& g, int M, int K, int l
   {
     const int per_row = g.k * g.k * (g.cin >> 2), threads = (per_row + 31) / 32 * 32;
     if (threads <= 1024) {
-      int rpb = 1;                                         // rows per block: about 16 blocks per SM
-      while (rpb < 16 && (M + 2 * rpb - 1) / (2 * rpb) >= kNumSMs * 16) rpb *= 2;
+      const int rpb = M >= kNumSMs * 16 ? 4 : 1;           // rows per block (measured: 4 beats 1 and 16 on both 3x3 ConvEmbeds)
       const int grid = (M + rpb - 1) / rpb;
       if (g.k == 3 && g.s == 2) im2col_rows_kernel<3, 2><<<grid, threads, 0, s>>>(x, g, M, ldc, col, rpb);
       else im2col_rows_kernel<0, 0><<<grid, threads, 0, s>>>(x, g, M, ldc, col, rpb);
