@@ -29,7 +29,18 @@ __global__ void __launch_bounds__(256) bn_fold_kernel(const float* __restrict__ 
   for (int r = ty; r < 32; r += 8) Wft[(long long)z * D * D + (long long)(j0 + r) * D + i0 + tx] = t[tx][r];
   if (blockIdx.y == 0) {
     float a = 0.f;
-    if (sh) for (int i = ty; i < D; i += 8) a += sh[z * D + i] * W[(long long)i * D + j0 + tx];
+    if (sh) {
+      for (int ib = ty; ib < D; ib += 8 * 16) {            // 16 independent weight loads in flight (the loop is pure latency otherwise)
+        float wv[16], sv[16];
+#pragma unroll
+        for (int u = 0; u < 16; ++u) {
+          const int i = ib + 8 * u; const bool ok = i < D;
+          wv[u] = ok ? W[(long long)i * D + j0 + tx] : 0.f; sv[u] = ok ? sh[z * D + i] : 0.f;
+        }
+#pragma unroll
+        for (int u = 0; u < 16; ++u) a = fmaf(sv[u], wv[u], a);
+      }
+    }
     red[ty][tx] = a;
     __syncthreads();
     if (ty == 0) {
