@@ -6,7 +6,7 @@
 // neighbours of a pixel are read from the ring slots of the neighbouring warps.  HBM-bound by design: forward reads xn once and
 // writes the three maps; backward reads the three map gradients and xn once and writes dxn.  CTAs are persistent and keep their
 // channel group, so BatchNorm statistics / depthwise-weight gradients stay in registers across work items and leave the CTA once,
-// as per-CTA partial slices (summed by bn_finalize_kernel / reduce_partials_kernel).
+// (statistics as per-CTA partial slices summed by bn_finalize_kernel, tap gradients by one atomic add per CTA and element).
 #include "layers.cuh"
 
 namespace cvt {
@@ -242,7 +242,7 @@ __global__ void __launch_bounds__(CT, 2) dwcol_bwd_kernel(const __grid_constant_
       *reinterpret_cast<float4*>(p.dxn + row) = s;
     }
   }
-  if (p.ddw) {       // partial slice (blockIdx / CG): [27][D]; this CTA fills its 32 channels
+  if (p.ddw) {       // this CTA's tap gradients of its 32 channels, summed over its 8 warps, go straight into ddw [27][D]
     float (*sred)[27][32] = reinterpret_cast<float (*)[27][32]>(smem);
     __syncthreads();                                     // the ring is dead
 #pragma unroll
@@ -255,7 +255,7 @@ __global__ void __launch_bounds__(CT, 2) dwcol_bwd_kernel(const __grid_constant_
       float a = 0.f;
 #pragma unroll
       for (int y = 0; y < NW; ++y) a += sred[y][k][l];
-      p.ddw_part[(long long)(blockIdx.x / g.CG) * 27 * D + k * D + cg * 32 + l] = a;
+      atomicAdd(p.ddw + k * D + cg * 32 + l, a);          // <= 296 / CG adds per address, spread over the kernel's lifetime
     }
   }
 }
@@ -275,8 +275,6 @@ bool make_colgeo(int B, int H, int W, int D, int cap_blocks, ColGeo* g, int* gri
 }
 }  // namespace
 
-cudaError_t launch_reduce_partials(const float* part, int nparts, int n, float* dst, cudaStream_t s);
-
 // the three branches must all be depthwise convolutions (projection_method 'dw_bn'); otherwise cudaErrorNotSupported
 cudaError_t launch_dwcol_fwd(const DwProjP& p, cudaStream_t s, int* stat_slices) {
   ColGeo g; int grid;
@@ -290,10 +288,8 @@ cudaError_t launch_dwcol_fwd(const DwProjP& p, cudaStream_t s, int* stat_slices)
 cudaError_t launch_dwcol_bwd(const DwProjBwdP& p, cudaStream_t s) {
   ColGeo g; int grid;
   if (p.method[0] != 0 || p.method[1] != 0 || p.method[2] != 0 || p.coef || !make_colgeo(p.B, p.H, p.W, p.D, 2 * kNumSMs, &g, &grid)) return cudaErrorNotSupported;
-  if (p.ddw && !p.ddw_part) return cudaErrorInvalidValue;
   dwcol_bwd_kernel<<<grid, CT, 0, s>>>(p, g);
   CVT_LAUNCH_CHECK();
-  if (p.ddw) CVT_CUDA(launch_reduce_partials(p.ddw_part, grid / g.CG, 27 * p.D, p.ddw, s));
   return cudaSuccess;
 }
 
