@@ -440,6 +440,15 @@ __global__ void __launch_bounds__(256) copy_rows_kernel(float* __restrict__ dst,
     dst[dmap(r) * ldd + c] = src[smap(r) * lds + c];
   }
 }
+// 16-byte version (D, ldd, lds multiples of 4, aligned bases): the row-map divisions are paid once per float4
+__global__ void __launch_bounds__(256) copy_rows_v4_kernel(float* __restrict__ dst, RowMap dmap, long long ldd, const float* __restrict__ src,
+                                                           RowMap smap, long long lds, int rows, int D4) {
+  const long long total = (long long)rows * D4;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int r = (int)(i / D4), c = (int)(i - (long long)r * D4) << 2;
+    *reinterpret_cast<float4*>(dst + dmap(r) * ldd + c) = *reinterpret_cast<const float4*>(src + smap(r) * lds + c);
+  }
+}
 __global__ void __launch_bounds__(256) token_mean_kernel(const float* __restrict__ x, int B, int T, int D, float* __restrict__ out, long long ldo) {
   // block = one image, threads over channels; coalesced over c
   const int b = blockIdx.x;
@@ -626,7 +635,10 @@ cudaError_t launch_fill_rows(float* dst, RowMap map, long long ld, const float* 
 }
 cudaError_t launch_copy_rows(float* dst, RowMap dmap, long long ldd, const float* src, RowMap smap, long long lds, int rows, int D, cudaStream_t s) {
   if (rows <= 0) return cudaSuccess;
-  copy_rows_kernel<<<ew_blocks((long long)rows * D), 256, 0, s>>>(dst, dmap, ldd, src, smap, lds, rows, D);
+  if (!(D & 3) && !(ldd & 3) && !(lds & 3) && !(reinterpret_cast<uintptr_t>(dst) & 15) && !(reinterpret_cast<uintptr_t>(src) & 15))
+    copy_rows_v4_kernel<<<ew_blocks((long long)rows * (D >> 2)), 256, 0, s>>>(dst, dmap, ldd, src, smap, lds, rows, D >> 2);
+  else
+    copy_rows_kernel<<<ew_blocks((long long)rows * D), 256, 0, s>>>(dst, dmap, ldd, src, smap, lds, rows, D);
   CVT_LAUNCH_CHECK();
   return cudaSuccess;
 }
