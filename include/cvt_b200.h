@@ -31,7 +31,8 @@ extern "C" {
 #endif
 
 #define CVT_MAX_STAGES 4
-#define CVT_ABI_VERSION 1
+#define CVT_DATASET_SLOTS 4
+#define CVT_ABI_VERSION 2
 
 typedef enum {
   CVT_OK = 0,
@@ -133,6 +134,42 @@ CVT_API int  cvt_read_metrics(cvt_model* m, float* loss, float* mae);         /*
 CVT_API int  cvt_optimizer_reset(cvt_model* m);                                /* zero m, v, t (a fresh compile) */
 CVT_API int64_t cvt_optimizer_step_count(const cvt_model* m);
 
+/* ---- input pipeline and resident datasets ------------------------------------------------------------------
+ * preprocess_data (models/CvT(Par).py:363-428) decodes 200 JPEGs per part on the host, resizes them with cv2 to 128x128, converts to
+ * grey, divides by 255 and hands model.fit float64 arrays [N,H,W], [N,5], [N]; Keras then shuffles and copies one batch per step.
+ * Here the decoded 8-bit images can be resized / converted on the device (bit-exact with cv2's 8-bit fixed-point path), the whole set
+ * stays in HBM (40 000 x 128 x 128 fp32 = 2.6 GB) and an epoch is a permutation: batches are gathered by index on the device. */
+typedef struct {
+  const void* img;   /* [n, H, W, C]  float32, or float64 when img_f64  (the reference passes float64 [N,H,W])   */
+  const void* proc;  /* [n, proc_dim] float32 / float64; NULL for the Img variant                                 */
+  const void* y;     /* [n, num_classes] float32 / float64; NULL where no targets are needed                      */
+  int32_t img_f64, proc_f64, y_f64;
+  int64_t n;
+} cvt_host_arrays;
+CVT_API int  cvt_dataset_alloc(cvt_model* m, int slot, int64_t n);          /* slot in [0, CVT_DATASET_SLOTS) */
+CVT_API int  cvt_dataset_free(cvt_model* m, int slot);
+CVT_API int64_t cvt_dataset_count(const cvt_model* m, int slot);
+/* rows [offset, offset + a->n) <- host arrays (pageable or pinned; any member may be NULL = left as is) */
+CVT_API int  cvt_dataset_write(cvt_model* m, int slot, int64_t offset, const cvt_host_arrays* a);
+/* images [offset, offset + count) <- decoded 8-bit pictures [count, src_h, src_w, src_c] (cv2.imread layout, src_c = 3 BGR or 1):
+ * cv2.resize(INTER_LINEAR) to (image_w, image_h), cv2.cvtColor(BGR2GRAY), / 255 — models/CvT(Par).py:420-423.  in_chans must be 1. */
+CVT_API int  cvt_dataset_write_u8(cvt_model* m, int slot, int64_t offset, int64_t count, const uint8_t* pixels, int src_h, int src_w, int src_c);
+CVT_API int  cvt_dataset_read(cvt_model* m, int slot, int64_t offset, int64_t count, float* img, float* proc, float* y);   /* any may be NULL */
+/* one epoch of model.fit (models/CvT(Par).py:475) over host arrays, batch i = rows order[i*batch .. ) (order == NULL: 0..n-1).  The rows of a
+ * batch are gathered into a pinned ring (shuffle and pageable->pinned staging are one pass over 4 MB, not a copy of the data set), copied
+ * to the device while the previous step runs, and - when fill_slot >= 0 - also stored at their own index of that resident dataset, so
+ * that the first epoch of a fit uploads the set as a side effect and later epochs call cvt_train_epoch_resident. */
+CVT_API int  cvt_train_epoch_stream(cvt_model* m, const cvt_host_arrays* a, const int32_t* order, int64_t n_order, int batch, float lr,
+                                    int fill_slot, float* loss_out, float* mae_out);
+CVT_API int  cvt_train_epoch_resident(cvt_model* m, int slot, const int32_t* order, int64_t n_order, int batch, float lr,
+                                      float* loss_out, float* mae_out);
+/* model.predict / model.evaluate on the caller's arrays as they are (float32 or float64, pageable or pinned), chunks of max_batch */
+CVT_API int  cvt_predict_arrays(cvt_model* m, const cvt_host_arrays* a, float* out);
+CVT_API int  cvt_evaluate_arrays(cvt_model* m, const cvt_host_arrays* a, float* loss, float* mae);
+/* validation pass / predict over a resident dataset: forward(training=0) in chunks of max_batch */
+CVT_API int  cvt_evaluate_resident(cvt_model* m, int slot, float* loss, float* mae);
+CVT_API int  cvt_predict_resident(cvt_model* m, int slot, float* out);
+
 /* ---- dropout (layers.Dropout at models/CvT(Par).py:189,255,257) ------------------------------- */
 /* PHILOX: keep-masks come from Philox4x32-10(seed, step, site) — reproducible by the oracle.
  * MASKS : the caller supplies uint8 keep-masks per site with cvt_set_dropout_mask (parity tests). */
@@ -166,6 +203,9 @@ CVT_API int64_t cvt_workspace_bytes(const cvt_model* m);
 /* name of the kernel group timed last + its device time; used by bench.py's roofline leg */
 CVT_API int  cvt_profile_step(cvt_model* m, const float* img_dev, const float* proc_dev, const float* y_dev, int batch,
                       int training, int max_entries, const char** names, float* ms, int* n_entries);
+
+/* (group name, kernels launched) of the last cvt_profile_step in issue order: lets a profiler's launch list be cut into the groups */
+CVT_API int  cvt_profile_group_launches(cvt_model* m, int max_entries, const char** names, int* launches, int* n_entries);
 
 /* diagnostics: C[M,N] = A x B through the fp32 FFMA kernel (use_tc = 0) or the tcgen05 kernel (use_tc = 1) on device 0.
  * a_mode 0: A is [M,K] row-major, 1: A is [K,M] (read transposed);  b_mode 0: B is [K,N], 1: B is [N,K]. */

@@ -24,12 +24,12 @@ def header_symbols():
 
 def test_header_symbols_are_exported_and_bound(lib):
     names = header_symbols()
-    assert len(names) >= 35
+    assert len(names) >= 47
     handle = C.CDLL(lib.LIB_PATH)
     for n in names:
         assert hasattr(handle, n), "library does not export %s" % n
     assert set(names) == set(lib.exported_names()), set(names) ^ set(lib.exported_names())
-    assert lib.load().cvt_abi_version() == 1
+    assert lib.load().cvt_abi_version() == lib.ABI_VERSION == 2
 
 
 def test_default_config_is_the_reference_spec(lib):

@@ -246,3 +246,90 @@ def test_widened_config_inference_and_train_step(precision):
         assert (num / den) ** 0.5 <= 2e-2, (num / den) ** 0.5
     assert not bad, "widened-config gradient mismatches:\n" + fmt(report)
     eng.close()
+
+
+def test_benched_configuration_batch64_tf32_graph_replay_philox():
+    """The exact configuration bench.py times (configs[1]): REF 128x128, batch 64, TF32, CUDA graphs on, dropout masks drawn in the GEMM
+    epilogues (Philox).  Three consecutive cvt_train_step calls on the same device buffers = eager issue, capture + replay, replay; before
+    each one the weights are read back so that the oracle differentiates exactly the function the step saw.  Every tap and every gradient
+    of every step is compared; the maxima are printed (pytest -s) and recorded in DESIGN.md."""
+    B = 64
+    spec, eng, params, img, proc, y = make_pair(hw=(128, 128), batch=B, precision="tf32", drop_rate=0.1)
+    eng.set_dropout("philox", seed=77)
+    eng.set_graphs(True)
+    d_img, d_proc, d_y = _dev(img), _dev(proc), _dev(y)
+    torch.cuda.synchronize()
+    from tests.parity_utils import TAPS
+    worst_act, worst_grad = 0.0, 0.0
+    for step in range(3):
+        cur = {k: v.astype(np.float64) for k, v in eng.get_params().items()}
+        l0 = eng.kernel_launches()
+        eng.train_step_dev(d_img, d_proc, d_y, B, 1e-3)
+        loss, mae = eng.read_metrics()
+        assert eng.kernel_launches() > l0
+        masks = O.make_dropout_masks(spec, B, seed=77, step=step)
+        r = O.loss_and_grads(spec, cur, img, proc, y, masks)
+        bad, report = compare_taps(eng, r["taps"], tol=5e-3, names=[t for t in TAPS if t not in ("qkv1", "a1", "hpre")])
+        assert not bad, "step %d forward mismatches:\n%s" % (step, fmt(report))
+        worst_act = max(worst_act, max(e for _, e in report))
+        assert abs(loss - r["loss"]) <= 2e-3 * abs(r["loss"]), (step, loss, r["loss"])
+        bad, report = compare_grads(eng, r["grads"], tol=2e-2, floor_frac=1e-3)
+        assert not bad, "step %d gradient mismatches:\n%s" % (step, fmt(report))
+        worst_grad = max(worst_grad, max(e for _, e in report))
+    print("\n[parity] batch-64 TF32 graph+Philox: max activation err %.3e, max gradient err %.3e (normwise per tensor)" % (worst_act, worst_grad))
+    eng.close()
+
+
+def test_predict_host_cached_graph_chunks_batch64_tf32():
+    """cvt_predict_host at the benched inference configuration: 4 chunks (64, 64, 64, 8) through GRAPH_INFER / GRAPH_INFER_CACHED."""
+    B, n = 64, 200
+    spec, eng, params, img, proc, y = make_pair(hw=(128, 128), batch=n, precision="tf32", max_batch=B)
+    ref, _ = O.forward(spec, params, img, proc, dtype=torch.float32)
+    for rep in range(3):                                   # eager, captured, replayed
+        pred = eng.predict(img, proc)
+        assert rel_err(pred, ref) <= 5e-3, rep
+    assert rel_err(eng.predict(img.astype(np.float64), proc.astype(np.float64)), pred) == 0.0      # float64 host arrays, as the scripts pass
+    eng.close()
+
+
+def test_two_models_on_one_thread_keep_their_own_inputs():
+    """the inputs of the last forward were a thread-local global; forward(A), forward(B), backward(A) read B's images."""
+    spec, a, params, img, proc, y = make_pair(hw=(32, 32), batch=2)
+    b = T.CvtEngine(a.cfg)
+    b.set_params(params)
+    a.set_dropout("off"); b.set_dropout("off")
+    img_b = (1.0 - img).astype(np.float32)
+    da, db = (_dev(img), _dev(proc), _dev(y)), (_dev(img_b), _dev(proc), _dev(y))
+    a.forward_dev(da[0], da[1], 2, True)
+    b.forward_dev(db[0], db[1], 2, True)
+    a.loss_backward_dev(da[2])
+    r = O.loss_and_grads(spec, params, img, proc, y, None)
+    bad, report = compare_grads(a, r["grads"], tol=1e-3)
+    assert not bad, fmt(report)
+    a.close(); b.close()
+
+
+def test_bf16_is_refused_not_aliased():
+    with pytest.raises(T.CvtError) as e:
+        T.CvtEngine(T.CvtConfig.reference(precision="bf16"))
+    assert "BF16" in str(e.value)
+
+
+def test_profile_step_leaves_the_model_untouched():
+    """cvt_profile_step used to overwrite the Adam moments, the BatchNorm moving statistics and the dropout counter."""
+    spec, eng, params, img, proc, y = make_pair(hw=(32, 32), batch=4, precision="tf32")
+    eng.set_dropout("philox", 5)
+    d = (_dev(img), _dev(proc), _dev(y))
+    torch.cuda.synchronize()
+    eng.train_step_dev(*d, 4, 1e-3); eng.synchronize()
+    before = eng.get_params()
+    twin = T.CvtEngine(eng.cfg); twin.set_params(params); twin.set_dropout("philox", 5)
+    twin.train_step_dev(*d, 4, 1e-3); twin.synchronize()
+    groups = eng.profile_step(*d, 4, True)
+    assert any(n == "s1.attention" for n, _ in groups)
+    after = eng.get_params()
+    assert all(np.array_equal(before[k], after[k]) for k in before)
+    eng.train_step_dev(*d, 4, 1e-3); twin.train_step_dev(*d, 4, 1e-3)
+    l1, l2 = eng.read_metrics(), twin.read_metrics()
+    assert abs(l1[0] - l2[0]) <= 1e-4 * abs(l2[0])          # same moments, same dropout step -> same second step
+    eng.close(); twin.close()

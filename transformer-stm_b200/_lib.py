@@ -5,6 +5,8 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "csrc", "libcvt_b200.so")
 MAX_STAGES = 4
+DATASET_SLOTS = 4
+ABI_VERSION = 2
 
 PROJ = {"dw_bn": 0, "avg": 1, "linear": 2}
 PREC = {"fp32": 0, "tf32": 1, "bf16": 2}
@@ -22,6 +24,12 @@ class Config(C.Structure):
                 ("proc_dim", C.c_int32), ("proc_hidden", C.c_int32), ("num_classes", C.c_int32), ("mlp_ratio", C.c_int32),
                 ("drop_rate", C.c_float), ("ln_eps", C.c_float), ("bn_eps", C.c_float), ("bn_momentum", C.c_float),
                 ("precision", C.c_int32), ("max_batch", C.c_int32), ("device", C.c_int32)]
+
+
+class HostArrays(C.Structure):
+    """cvt_host_arrays: the numpy arrays model.fit receives (float32 or float64), by pointer."""
+    _fields_ = [("img", C.c_void_p), ("proc", C.c_void_p), ("y", C.c_void_p),
+                ("img_f64", C.c_int32), ("proc_f64", C.c_int32), ("y_f64", C.c_int32), ("n", C.c_int64)]
 
 
 class CvtError(RuntimeError):
@@ -52,6 +60,19 @@ _PROTOS = {
                                       C.POINTER(C.c_float), C.POINTER(C.c_float)]),
     "cvt_evaluate_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
                                     C.POINTER(C.c_float), C.POINTER(C.c_float)]),
+    "cvt_dataset_alloc": (C.c_int, [C.c_void_p, C.c_int, C.c_int64]),
+    "cvt_dataset_free": (C.c_int, [C.c_void_p, C.c_int]),
+    "cvt_dataset_count": (C.c_int64, [C.c_void_p, C.c_int]),
+    "cvt_dataset_write": (C.c_int, [C.c_void_p, C.c_int, C.c_int64, C.POINTER(HostArrays)]),
+    "cvt_dataset_write_u8": (C.c_int, [C.c_void_p, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_int, C.c_int, C.c_int]),
+    "cvt_dataset_read": (C.c_int, [C.c_void_p, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "cvt_train_epoch_stream": (C.c_int, [C.c_void_p, C.POINTER(HostArrays), C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_int,
+                                         C.c_void_p, C.c_void_p]),
+    "cvt_train_epoch_resident": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_void_p, C.c_void_p]),
+    "cvt_predict_arrays": (C.c_int, [C.c_void_p, C.POINTER(HostArrays), C.c_void_p]),
+    "cvt_evaluate_arrays": (C.c_int, [C.c_void_p, C.POINTER(HostArrays), C.POINTER(C.c_float), C.POINTER(C.c_float)]),
+    "cvt_evaluate_resident": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
+    "cvt_predict_resident": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
     "cvt_read_metrics": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
     "cvt_optimizer_reset": (C.c_int, [C.c_void_p]),
     "cvt_optimizer_step_count": (C.c_int64, [C.c_void_p]),
@@ -73,6 +94,7 @@ _PROTOS = {
     "cvt_debug_attention": (C.c_int, [C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 9),
     "cvt_profile_step": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                    C.POINTER(C.c_char_p), C.POINTER(C.c_float), C.POINTER(C.c_int)]),
+    "cvt_profile_group_launches": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
 }
 
 _lib = None

@@ -8,6 +8,9 @@
 
 #include <algorithm>
 #include <random>
+#include <thread>
+
+#include <nvtx3/nvToolsExt.h>
 
 #include "model.cuh"
 
@@ -28,12 +31,20 @@ void set_error(const std::string& msg) { g_err = msg; }
   } while (0)
 
 // ---- profiling marks (cvt_profile_step) -----------------------------------------------------------------
-struct ProfMark { const char* name; cudaEvent_t ev; };
+struct ProfMark { const char* name; cudaEvent_t ev; long long launches; };
 static thread_local std::vector<ProfMark>* g_prof = nullptr;
+static thread_local bool g_nvtx_open = false;
+// group boundary: a CUDA event when cvt_profile_step is timing, and (CVT_NVTX=1) an NVTX range named after the kernel group, so that
+// nsys / ncu --nvtx attribute kernels to "s1.attention", "s2.bwd_mlp", ... (tracing)
 static inline void prof_mark(cudaStream_t s, const char* name) {
+  static const bool nvtx = getenv("CVT_NVTX") != nullptr;
+  if (nvtx) {
+    if (g_nvtx_open) { nvtxRangePop(); g_nvtx_open = false; }
+    if (strncmp(name, "end", 3) != 0) { nvtxRangePushA(name); g_nvtx_open = true; }
+  }
   if (!g_prof) return;
   cudaEvent_t e; cudaEventCreate(&e); cudaEventRecord(e, s);
-  g_prof->push_back({name, e});
+  g_prof->push_back({name, e, g_launch_count});
 }
 static const char* kStageNames[CVT_MAX_STAGES][12] = {
   {"s1.conv_embed", "s1.ln_proj_bn", "s1.qkv_gemm", "s1.attention", "s1.out_gemm", "s1.mlp", "s1.bwd_mlp", "s1.bwd_out", "s1.bwd_attention", "s1.bwd_qkv", "s1.bwd_proj_ln", "s1.bwd_conv"},
@@ -73,9 +84,9 @@ static bool gelu_dsave(const Model* m, int D) {
   return !off && m->folded && m->cfg.precision != CVT_PREC_FP32 && D % 16 == 0;
 }
 
-static thread_local bool g_tc = false;     // the model being run uses the tcgen05 contraction kernel (128-row tiles, 2 CTAs per SM)
-static int auto_splitk(int M, int N, int K, int batch) {
-  if (g_tc) {
+// tc: the model uses the tcgen05 contraction kernel (128-row tiles, 2 CTAs per SM)
+static int auto_splitk(bool tc, int M, int N, int K, int batch) {
+  if (tc) {
     const int tiles = cdiv(M, 128) * cdiv(N, 64) * batch;
     const int sk = cdiv(kNumSMs * 2, tiles);
     const int maxsk = std::max(1, K / 256);              // at least 8 k-tiles of 32 per CTA
@@ -98,9 +109,9 @@ static GemmP dense_dgrad(const float* dY, long long lddy, int M, int Nout, const
   return p;
 }
 // dW[Kin,Nout] += X[tokens,Kin]^T * dY[tokens,Nout]
-static GemmP dense_wgrad(const float* X, long long ldx, int Kin, const float* dY, long long lddy, int Nout, int tokens, float* dW) {
+static GemmP dense_wgrad(bool tc, const float* X, long long ldx, int Kin, const float* dY, long long lddy, int Nout, int tokens, float* dW) {
   GemmP p; p.M = Kin; p.N = Nout; p.K = tokens; p.A = X; p.lda = ldx; p.a_mode = A_TRANS; p.B = dY; p.ldb = lddy; p.b_mode = B_KN;
-  p.C = dW; p.ldc = Nout; p.epi = EPI_ATOMIC; p.splitk = auto_splitk(Kin, Nout, tokens, 1);
+  p.C = dW; p.ldc = Nout; p.epi = EPI_ATOMIC; p.splitk = auto_splitk(tc, Kin, Nout, tokens, 1);
   return p;
 }
 
@@ -114,8 +125,9 @@ static cudaError_t wgrad_bias(const Model* m, const float* X, long long ldx, int
     if (wgrad_tma_supports(w)) return launch_wgrad_tma(w, s);
   }
   if (db) CVT_CUDA(launch_colsum(dY, lddy, rowmap_none(), tokens, Nout, batch, dy_bs, db, Nout, s));
-  GemmP p = dense_wgrad(X, ldx, Kin, dY, lddy, Nout, tokens, dW);
-  if (batch > 1) { p.batch = batch; p.a_bs0 = x_bs; p.b_bs0 = dy_bs; p.c_bs0 = (long long)Kin * Nout; p.splitk = auto_splitk(Kin, Nout, tokens, batch); }
+  const bool tc = m->cfg.precision != CVT_PREC_FP32;
+  GemmP p = dense_wgrad(tc, X, ldx, Kin, dY, lddy, Nout, tokens, dW);
+  if (batch > 1) { p.batch = batch; p.a_bs0 = x_bs; p.b_bs0 = dy_bs; p.c_bs0 = (long long)Kin * Nout; p.splitk = auto_splitk(tc, Kin, Nout, tokens, batch); }
   return run_gemm(m, p, s);
 }
 
@@ -300,6 +312,11 @@ int cvt_create(const cvt_config* cfg, cvt_model** out) {
       c.max_batch < 1 || c.mlp_ratio < 1 || c.proc_dim < 0 || (c.proc_dim > 0 && c.proc_hidden < 1)) {
     set_error("cvt_create: invalid configuration"); return CVT_ERR_INVALID;
   }
+  if (c.precision == CVT_PREC_BF16) {
+    set_error("cvt_create: CVT_PREC_BF16 is not implemented (fp32 and tf32 are); refusing rather than running another precision under that name");
+    return CVT_ERR_INVALID;
+  }
+  if (c.precision != CVT_PREC_FP32 && c.precision != CVT_PREC_TF32) { set_error("cvt_create: unknown precision"); return CVT_ERR_INVALID; }
   if (c.drop_rate < 0.f || c.drop_rate >= 1.f) { set_error("cvt_create: drop_rate must be in [0,1)"); return CVT_ERR_INVALID; }
   for (int i = 0; i < c.n_stages; ++i) {
     const cvt_stage_config& s = c.stage[i];
@@ -323,6 +340,7 @@ int cvt_create(const cvt_config* cfg, cvt_model** out) {
   }
   API_CUDA(cudaSetDevice(c.device));
 
+#define CREATE_CUDA(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) { set_error(std::string(#expr) + ": " + cudaGetErrorString(_e)); cvt_destroy(h); return CVT_ERR_CUDA; } } while (0)
   cvt_model* h = new cvt_model();
   Model* m = &h->m;
   m->cfg = c; m->n_stages = c.n_stages;
@@ -360,13 +378,13 @@ int cvt_create(const cvt_config* cfg, cvt_model** out) {
   const int64_t arena_bytes = (4 * m->n_train + m->n_z + std::max<int64_t>(m->n_state, 4)) * (int64_t)sizeof(float);
   m->workspace_bytes = measure.off + 256 + arena_bytes + 8192;
   cudaError_t e = cudaMalloc(&m->workspace, (size_t)m->workspace_bytes);
-  if (e != cudaSuccess) { set_error(std::string("cvt_create: cudaMalloc of ") + std::to_string(m->workspace_bytes) + " bytes: " + cudaGetErrorString(e)); delete h; return CVT_ERR_CUDA; }
+  if (e != cudaSuccess) { set_error(std::string("cvt_create: cudaMalloc of ") + std::to_string(m->workspace_bytes) + " bytes: " + cudaGetErrorString(e)); m->workspace = nullptr; cvt_destroy(h); return CVT_ERR_CUDA; }
   Bump b; b.base = reinterpret_cast<char*>(m->workspace);
   m->P = b.take<float>(m->n_train); m->G = b.take<float>(m->n_train + m->n_z); m->Mo = b.take<float>(m->n_train); m->Vo = b.take<float>(m->n_train);
   m->St = b.take<float>(std::max<int64_t>(m->n_state, 4));
   carve(m, b);
-  API_CUDA(cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking));
-  API_CUDA(cudaMemsetAsync(m->workspace, 0, (size_t)m->workspace_bytes, m->stream));
+  CREATE_CUDA(cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking));
+  CREATE_CUDA(cudaMemsetAsync(m->workspace, 0, (size_t)m->workspace_bytes, m->stream));
   {  // dense kernels the forward GEMMs read K-major (transposed copies in Pt)
     m->tr_descs.clear(); int tiles = 0;
     auto add = [&](int64_t off, int K, int N, int copy = 0, int64_t toff = -1, int ldt = 0) {
@@ -381,7 +399,7 @@ int cvt_create(const cvt_config* cfg, cvt_model** out) {
       if (m->folded) add(w.conv_w, m->fold[i].Kc, D, i > 0 ? 1 : 0, m->fold[i].convt, m->fold[i].Kp);      // ConvEmbed kernel [K][D] -> [D][Kp]
     }
     m->tr_tiles = tiles;
-    API_CUDA(cudaMemcpyAsync(m->tr_descs_dev, m->tr_descs.data(), m->tr_descs.size() * sizeof(TrDesc), cudaMemcpyHostToDevice, m->stream));
+    CREATE_CUDA(cudaMemcpyAsync(m->tr_descs_dev, m->tr_descs.data(), m->tr_descs.size() * sizeof(TrDesc), cudaMemcpyHostToDevice, m->stream));
   }
   if (m->folded) {  // multi-GEMM lists that fold the stacked linear maps (forward) and unfold their gradients (backward), see fold.cu
     std::vector<MgDesc> fw, bw; int tf = 0, tb = 0;
@@ -413,30 +431,41 @@ int cvt_create(const cvt_config* cfg, cvt_model** out) {
     }
     if (fw.size() > 64 || bw.size() > 96) { set_error("cvt_create: too many stages for the fold descriptor tables"); cvt_destroy(h); return CVT_ERR_INVALID; }
     m->mg_fwd_n = (int)fw.size(); m->mg_fwd_tiles = tf; m->mg_bwd_n = (int)bw.size(); m->mg_bwd_tiles = tb;
-    API_CUDA(cudaMemcpyAsync(m->mg_fwd_dev, fw.data(), fw.size() * sizeof(MgDesc), cudaMemcpyHostToDevice, m->stream));
-    API_CUDA(cudaMemcpyAsync(m->mg_bwd_dev, bw.data(), bw.size() * sizeof(MgDesc), cudaMemcpyHostToDevice, m->stream));
-    API_CUDA(cudaStreamSynchronize(m->stream));      // fw / bw are locals
+    CREATE_CUDA(cudaMemcpyAsync(m->mg_fwd_dev, fw.data(), fw.size() * sizeof(MgDesc), cudaMemcpyHostToDevice, m->stream));
+    CREATE_CUDA(cudaMemcpyAsync(m->mg_bwd_dev, bw.data(), bw.size() * sizeof(MgDesc), cudaMemcpyHostToDevice, m->stream));
+    CREATE_CUDA(cudaStreamSynchronize(m->stream));      // fw / bw are locals
   }
-  API_CUDA(cudaMemsetAsync(m->head_ticket, 0, 16, m->stream));
-  API_CUDA(cudaMallocHost(&m->pin_metrics, 4 * sizeof(float)));
-  API_CUDA(cudaStreamCreateWithFlags(&m->copy_stream, cudaStreamNonBlocking));
-  for (int i = 0; i < 2; ++i) { API_CUDA(cudaEventCreateWithFlags(&m->ev_copy[i], cudaEventDisableTiming)); API_CUDA(cudaEventCreateWithFlags(&m->ev_done[i], cudaEventDisableTiming)); }
-  API_CUDA(cudaStreamSynchronize(m->stream));
+  CREATE_CUDA(cudaMemsetAsync(m->head_ticket, 0, 16, m->stream));
+  CREATE_CUDA(cudaMallocHost(&m->pin_metrics, 4 * sizeof(float)));
+  CREATE_CUDA(cudaStreamCreateWithFlags(&m->copy_stream, cudaStreamNonBlocking));
+  for (int i = 0; i < 2; ++i) { CREATE_CUDA(cudaEventCreateWithFlags(&m->ev_copy[i], cudaEventDisableTiming)); CREATE_CUDA(cudaEventCreateWithFlags(&m->ev_done[i], cudaEventDisableTiming)); }
+  CREATE_CUDA(cudaStreamSynchronize(m->stream));
   *out = h;
   return CVT_OK;
 }
+#undef CREATE_CUDA
 
 void cvt_destroy(cvt_model* h) {
   if (!h) return;
   Model* m = &h->m;
   cvt_comm_destroy(h);
   clear_graphs(m);
-  if (m->stream) { cudaStreamSynchronize(m->stream); cudaStreamDestroy(m->stream); }
+  if (m->stream) cudaStreamSynchronize(m->stream);
+  if (m->copy_stream) cudaStreamSynchronize(m->copy_stream);
+  for (int i = 0; i < CVT_DATASET_SLOTS; ++i) cvt_dataset_free(h, i);
+  for (int i = 0; i < Model::kRing; ++i) { if (m->ring[i]) cudaFreeHost(m->ring[i]); if (m->ring_ev[i]) cudaEventDestroy(m->ring_ev[i]); }
+  for (int i = 0; i < 2; ++i) if (m->raw64[i]) cudaFree(m->raw64[i]);
+  if (m->order_dev) cudaFree(m->order_dev);
+  if (m->pp_pix) cudaFree(m->pp_pix);
+  if (m->pp_tab) cudaFree(m->pp_tab);
+  if (m->pp_lut) cudaFree(m->pp_lut);
+  if (m->stream) cudaStreamDestroy(m->stream);
+  if (m->copy_stream) cudaStreamDestroy(m->copy_stream);
   if (m->workspace) cudaFree(m->workspace);
   if (m->pin_metrics) cudaFreeHost(m->pin_metrics);
   if (m->pin_series) cudaFreeHost(m->pin_series);
-  if (m->copy_stream) { cudaStreamSynchronize(m->copy_stream); cudaStreamDestroy(m->copy_stream); }
   for (int i = 0; i < 2; ++i) { if (m->ev_copy[i]) cudaEventDestroy(m->ev_copy[i]); if (m->ev_done[i]) cudaEventDestroy(m->ev_done[i]); }
+  (void)cudaGetLastError();
   delete h;
 }
 
@@ -834,8 +863,8 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
   // ---- proj_q/k/v Dense (input = BN(conv) recomputed on load) ----
   CVT_CUDA(launch_colsum(m->gQ2, D, rowmap_none(), R, D, 3, RD, G + w.pb, D, s));
   {
-    GemmP p = dense_wgrad(a.conv, D, D, m->gQ2, D, D, R, G + w.pw);
-    p.batch = 3; p.a_bs0 = RD; p.b_bs0 = RD; p.c_bs0 = (long long)D * D; p.splitk = auto_splitk(D, D, R, 3);
+    GemmP p = dense_wgrad(c.precision != CVT_PREC_FP32, a.conv, D, D, m->gQ2, D, D, R, G + w.pw);
+    p.batch = 3; p.a_bs0 = RD; p.b_bs0 = RD; p.c_bs0 = (long long)D * D; p.splitk = auto_splitk(c.precision != CVT_PREC_FP32, D, D, R, 3);
     if (g.method == CVT_PROJ_DW_BN) { p.a_scale = a.bn_scale; p.a_shift = a.bn_shift; p.a_aff_bs = D; p.a_skip_period = g.has_cls ? g.Tc : 0; }
     CVT_CUDA(run_gemm(m, p, s));
     GemmP q = dense_dgrad(m->gQ2, D, R, D, P + w.pw, D, m->gQ, D);
@@ -902,7 +931,7 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
   {
     GemmP p; p.M = g.k * g.k * g.cin; p.N = D; p.K = B * g.T; p.A = xin; p.a_mode = A_CONVT; p.cv = cv;
     p.B = m->gD; p.ldb = D; p.b_mode = B_KN; p.b_map = emap; p.C = G + w.conv_w; p.ldc = D; p.epi = EPI_ATOMIC;
-    p.splitk = auto_splitk(p.M, p.N, p.K, 1);
+    p.splitk = auto_splitk(c.precision != CVT_PREC_FP32, p.M, p.N, p.K, 1);
     CVT_CUDA(run_gemm(m, p, s));
   }
   if (dXprev) {
@@ -915,14 +944,11 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
   return cudaSuccess;
 }
 
-struct FwdInputs { const float* img; const float* proc; };
-static thread_local FwdInputs g_last_inputs{nullptr, nullptr};
 
 // runs the backward pass from m->dpred down to stage `stop_stage` (0 = all the way); returns the buffer holding the
 // gradient w.r.t. the output of block `stop_stage` when stop_stage > 0 ... (grad-cam tap)
 static cudaError_t backward_impl(Model* m, const float* img, const float* proc, int B, int training, int stop_after_stage, float** tap_grad) {
   cudaStream_t s = m->stream;
-  g_tc = m->cfg.precision != CVT_PREC_FP32;
   m->premasked = false;
   CVT_CUDA(cudaMemsetAsync(m->G, 0, (size_t)(m->n_train + m->n_z) * sizeof(float), s));
   int cur = (m->n_stages - 1) & 1;
@@ -957,7 +983,7 @@ int cvt_forward(cvt_model* h, const float* img_dev, const float* proc_dev, int b
   const long long l0 = g_launch_count;
   if (training) API_CUDA(forward_impl(m, img_dev, proc_dev, batch, training));
   else { const int rf = infer_forward(m, img_dev, proc_dev, batch); if (rf) return rf; }
-  g_last_inputs = {img_dev, proc_dev};
+  m->last_img = img_dev; m->last_proc = proc_dev;
   if (out_dev) API_CUDA(cudaMemcpyAsync(out_dev, m->pred, (size_t)batch * m->cfg.num_classes * sizeof(float), cudaMemcpyDeviceToDevice, m->stream));
   m->launches += g_launch_count - l0;
   return CVT_OK;
@@ -966,12 +992,12 @@ int cvt_forward(cvt_model* h, const float* img_dev, const float* proc_dev, int b
 int cvt_loss_backward(cvt_model* h, const float* y_dev, float* loss_host, float* mae_host) {
   if (!h || !y_dev) { set_error("cvt_loss_backward: null argument"); return CVT_ERR_INVALID; }
   Model* m = &h->m;
-  if (!m->have_forward || !g_last_inputs.img) { set_error("cvt_loss_backward: call cvt_forward first"); return CVT_ERR_STATE; }
+  if (!m->have_forward || !m->last_img) { set_error("cvt_loss_backward: call cvt_forward first"); return CVT_ERR_STATE; }
   const int B = m->last_batch;
   const long long l0 = g_launch_count;
   const float gs = 1.f;
   API_CUDA(launch_mse_loss(m->pred, y_dev, B * m->cfg.num_classes, m->metrics, m->dpred, gs, 0, m->stream));
-  API_CUDA(backward_impl(m, g_last_inputs.img, g_last_inputs.proc, B, m->last_training, -1, nullptr));
+  API_CUDA(backward_impl(m, m->last_img, m->last_proc, B, m->last_training, -1, nullptr));
   m->launches += g_launch_count - l0;
   if (loss_host || mae_host) {
     float l, a; int r = cvt_read_metrics(h, &l, &a); if (r) return r;
@@ -1194,7 +1220,7 @@ int cvt_train_step(cvt_model* h, const float* img_dev, const float* proc_dev, co
   API_CUDA(cudaSetDevice(m->cfg.device));
   const long long l0 = g_launch_count;
   r = train_step_dev(m, img_dev, proc_dev, y_dev, batch, lr);
-  g_last_inputs = {img_dev, proc_dev};
+  m->last_img = img_dev; m->last_proc = proc_dev;
   m->launches += g_launch_count - l0;
   return r;
 }
@@ -1215,20 +1241,126 @@ int cvt_train_step_host(cvt_model* h, const float* img, const float* proc, const
   return CVT_OK;
 }
 
+// =====================================================================================================================
+// input pipeline: pinned ring, resident datasets, epochs by permutation (models/CvT(Par).py:418-423,475)
+// =====================================================================================================================
+static bool host_is_pinned(const void* p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { (void)cudaGetLastError(); return false; }
+  return a.type == cudaMemoryTypeHost || a.type == cudaMemoryTypeManaged;
+}
+// dst[i] <- src[idx ? idx[first + i] : first + i], rows of row_bytes.  One core copies pageable memory at ~10 GB/s, which is less than a
+// B200 consumes at inference (64 images = 4 or 8 MB every 0.5 ms): copies of a megabyte or more are split over a few threads.
+static void host_gather(uint8_t* dst, const uint8_t* src, const int32_t* idx, int64_t first, int64_t cnt, size_t row_bytes) {
+  auto work = [=](int64_t lo, int64_t hi) {
+    if (!idx) { memcpy(dst + lo * row_bytes, src + (first + lo) * row_bytes, (size_t)(hi - lo) * row_bytes); return; }
+    for (int64_t i = lo; i < hi; ++i) memcpy(dst + i * row_bytes, src + (int64_t)idx[first + i] * row_bytes, row_bytes);
+  };
+  static const int max_threads = []() {
+    const char* e = getenv("CVT_COPY_THREADS");
+    int t = e ? atoi(e) : (int)std::min<unsigned>(4, std::max<unsigned>(1, std::thread::hardware_concurrency() / 2));
+    return std::max(1, std::min(t, 16));
+  }();
+  const size_t bytes = (size_t)cnt * row_bytes;
+  int nt = (int)std::min<int64_t>(std::min<int64_t>(max_threads, cnt), (int64_t)(bytes >> 19));      // >= 512 KB per thread
+  if (nt <= 1) { work(0, cnt); return; }
+  std::vector<std::thread> th;
+  for (int t = 1; t < nt; ++t) th.emplace_back(work, cnt * t / nt, cnt * (t + 1) / nt);
+  work(0, cnt / nt);
+  for (auto& x : th) x.join();
+}
+static int ring_init(Model* m) {
+  if (m->ring_cap) return CVT_OK;
+  const size_t cap = (size_t)8 << 20;
+  for (int i = 0; i < Model::kRing; ++i) {
+    API_CUDA(cudaMallocHost(reinterpret_cast<void**>(&m->ring[i]), cap));
+    API_CUDA(cudaEventCreateWithFlags(&m->ring_ev[i], cudaEventDisableTiming));
+    m->ring_busy[i] = false;
+  }
+  m->ring_cap = cap; m->ring_next = 0;
+  return CVT_OK;
+}
+static int ring_acquire(Model* m, int* slot) {
+  int r = ring_init(m); if (r) return r;
+  *slot = m->ring_next; m->ring_next = (m->ring_next + 1) % Model::kRing;
+  if (m->ring_busy[*slot]) { API_CUDA(cudaEventSynchronize(m->ring_ev[*slot])); m->ring_busy[*slot] = false; }
+  return CVT_OK;
+}
+// dst_dev[r] (dense rows of row_bytes) <- src[(idx ? idx[first + r] : first + r)] for r < nrows, asynchronously on stream s.  Pinned
+// contiguous sources are copied directly; everything else is gathered row by row into the pinned ring (the only host pass over the data).
+static int h2d_rows(Model* m, void* dst_dev, const void* src_host, const int32_t* idx, int64_t first, int64_t nrows, size_t row_bytes, cudaStream_t s) {
+  if (nrows <= 0 || row_bytes == 0) return CVT_OK;
+  const uint8_t* src = static_cast<const uint8_t*>(src_host);
+  if (!idx && host_is_pinned(src + first * row_bytes)) {
+    API_CUDA(cudaMemcpyAsync(dst_dev, src + first * row_bytes, (size_t)nrows * row_bytes, cudaMemcpyHostToDevice, s));
+    return CVT_OK;
+  }
+  int r = ring_init(m); if (r) return r;
+  if (row_bytes > m->ring_cap) { set_error("h2d_rows: one row exceeds the pinned ring slot (8 MB)"); return CVT_ERR_INVALID; }
+  const int64_t per_slot = (int64_t)(m->ring_cap / row_bytes);
+  for (int64_t done = 0; done < nrows; done += per_slot) {
+    const int64_t cnt = std::min(per_slot, nrows - done);
+    int slot; r = ring_acquire(m, &slot); if (r) return r;
+    host_gather(m->ring[slot], src, idx, first + done, cnt, row_bytes);
+    API_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(dst_dev) + done * row_bytes, m->ring[slot], (size_t)cnt * row_bytes, cudaMemcpyHostToDevice, s));
+    API_CUDA(cudaEventRecord(m->ring_ev[slot], s)); m->ring_busy[slot] = true;
+  }
+  return CVT_OK;
+}
+// small float rows (process parameters, targets): gathered and, when the host holds float64, converted on the host into a ring slot
+static int h2d_small(Model* m, float* dst_dev, const void* src_host, int f64, const int32_t* idx, int64_t first, int64_t nrows, int width, cudaStream_t s) {
+  if (nrows <= 0 || width <= 0) return CVT_OK;
+  if (!f64) return h2d_rows(m, dst_dev, src_host, idx, first, nrows, (size_t)width * sizeof(float), s);
+  int r = ring_init(m); if (r) return r;
+  const int64_t per_slot = (int64_t)(m->ring_cap / ((size_t)width * sizeof(float)));
+  const double* src = static_cast<const double*>(src_host);
+  for (int64_t done = 0; done < nrows; done += per_slot) {
+    const int64_t cnt = std::min(per_slot, nrows - done);
+    int slot; r = ring_acquire(m, &slot); if (r) return r;
+    float* d = reinterpret_cast<float*>(m->ring[slot]);
+    for (int64_t i = 0; i < cnt; ++i) {
+      const double* row = src + (idx ? (int64_t)idx[first + done + i] : first + done + i) * width;
+      for (int c = 0; c < width; ++c) d[i * width + c] = (float)row[c];
+    }
+    API_CUDA(cudaMemcpyAsync(dst_dev + done * width, d, (size_t)cnt * width * sizeof(float), cudaMemcpyHostToDevice, s));
+    API_CUDA(cudaEventRecord(m->ring_ev[slot], s)); m->ring_busy[slot] = true;
+  }
+  return CVT_OK;
+}
+static int ensure_raw64(Model* m) {
+  const size_t need = (size_t)m->cfg.max_batch * m->cfg.image_h * m->cfg.image_w * m->cfg.in_chans * sizeof(double);
+  if (m->raw64_cap >= need) return CVT_OK;
+  for (int i = 0; i < 2; ++i) { if (m->raw64[i]) cudaFree(m->raw64[i]); m->raw64[i] = nullptr; }
+  m->raw64_cap = 0;
+  for (int i = 0; i < 2; ++i) API_CUDA(cudaMalloc(reinterpret_cast<void**>(&m->raw64[i]), need));
+  m->raw64_cap = need;
+  return CVT_OK;
+}
+// image rows -> fp32 device rows; float64 host rows land in raw64[lane] and are converted by a kernel on the same stream (nrows <= max_batch)
+static int h2d_images(Model* m, float* dst_dev, const void* src_host, int f64, const int32_t* idx, int64_t first, int nrows, int lane, cudaStream_t s) {
+  const cvt_config& c = m->cfg;
+  const size_t per = (size_t)c.image_h * c.image_w * c.in_chans;
+  if (!f64) return h2d_rows(m, dst_dev, src_host, idx, first, nrows, per * sizeof(float), s);
+  int r = ensure_raw64(m); if (r) return r;
+  r = h2d_rows(m, m->raw64[lane], src_host, idx, first, nrows, per * sizeof(double), s); if (r) return r;
+  API_CUDA(launch_f64_to_f32(dst_dev, m->raw64[lane], (long long)nrows * (long long)per, s));
+  return CVT_OK;
+}
 // ---- double-buffered host -> device staging ----------------------------------------------------------------------------
 struct Staging { float* img; float* proc; float* y; };
 static Staging staging_of(Model* m, int slot) {
   return slot ? Staging{m->in_img2, m->in_proc2, m->in_y2} : Staging{m->in_img, m->in_proc, m->in_y};
 }
-// enqueue the copies of chunk `i` on the copy stream (after the step that last read this slot) and make the model stream wait for them
-static int stage_chunk(Model* m, int64_t i, const float* img, const float* proc, const float* y, int B) {
+// enqueue the copies of rows [o, o + B) of `a` on the copy stream (after the step that last read this staging slot) and make the model
+// stream wait for them.  Pinned float32 sources are copied in place; pageable and float64 ones (what numpy hands over) pass through the
+// library's pinned ring, so that the copy of chunk i+1 is asynchronous and really overlaps the step on chunk i.
+static int stage_chunk(Model* m, int64_t i, const cvt_host_arrays& a, int64_t o, int B, bool with_y) {
   const cvt_config& c = m->cfg;
   const int slot = (int)(i & 1); const Staging st = staging_of(m, slot);
-  const size_t per = (size_t)c.image_h * c.image_w * c.in_chans;
   if (i >= 2) API_CUDA(cudaStreamWaitEvent(m->copy_stream, m->ev_done[slot], 0));
-  API_CUDA(cudaMemcpyAsync(st.img, img, B * per * sizeof(float), cudaMemcpyHostToDevice, m->copy_stream));
-  if (c.proc_dim > 0) API_CUDA(cudaMemcpyAsync(st.proc, proc, (size_t)B * c.proc_dim * sizeof(float), cudaMemcpyHostToDevice, m->copy_stream));
-  if (y) API_CUDA(cudaMemcpyAsync(st.y, y, (size_t)B * c.num_classes * sizeof(float), cudaMemcpyHostToDevice, m->copy_stream));
+  { const int r = h2d_images(m, st.img, a.img, a.img_f64, nullptr, o, B, slot, m->copy_stream); if (r) return r; }
+  if (c.proc_dim > 0) { const int r = h2d_small(m, st.proc, a.proc, a.proc_f64, nullptr, o, B, c.proc_dim, m->copy_stream); if (r) return r; }
+  if (with_y) { const int r = h2d_small(m, st.y, a.y, a.y_f64, nullptr, o, B, c.num_classes, m->copy_stream); if (r) return r; }
   API_CUDA(cudaEventRecord(m->ev_copy[slot], m->copy_stream));
   API_CUDA(cudaStreamWaitEvent(m->stream, m->ev_copy[slot], 0));
   return CVT_OK;
@@ -1249,42 +1381,23 @@ static int ensure_pin_series(Model* m, int64_t floats) {
 int cvt_train_epoch_host(cvt_model* h, const float* img, const float* proc, const float* y, int64_t n, int batch, float lr,
                          float* loss_out, float* mae_out) {
   if (!h || !img || !y || n < 1) { set_error("cvt_train_epoch_host: bad argument"); return CVT_ERR_INVALID; }
-  Model* m = &h->m; const cvt_config& c = m->cfg;
-  if (c.proc_dim > 0 && !proc) { set_error("cvt_train_epoch_host: this model needs process parameters"); return CVT_ERR_INVALID; }
-  int r = check_batch(m, batch, "cvt_train_epoch_host"); if (r) return r;
-  API_CUDA(cudaSetDevice(c.device));
-  const int64_t nb = (n + batch - 1) / batch;
-  r = ensure_pin_series(m, 2 * nb); if (r) return r;
-  const size_t per = (size_t)c.image_h * c.image_w * c.in_chans;
-  const long long l0 = g_launch_count;
-  for (int64_t i = 0; i < nb; ++i) {
-    const int64_t o = i * batch; const int B = (int)std::min<int64_t>(batch, n - o);
-    r = stage_chunk(m, i, img + o * per, proc ? proc + o * c.proc_dim : nullptr, y + o * c.num_classes, B); if (r) return r;
-    const Staging st = staging_of(m, (int)(i & 1));
-    r = train_step_dev(m, st.img, c.proc_dim > 0 ? st.proc : nullptr, st.y, B, lr); if (r) return r;
-    API_CUDA(cudaMemcpyAsync(m->pin_series + 2 * i, m->metrics, 2 * sizeof(float), cudaMemcpyDeviceToHost, m->stream));
-    API_CUDA(cudaEventRecord(m->ev_done[i & 1], m->stream));
-    g_last_inputs = {st.img, c.proc_dim > 0 ? st.proc : nullptr};
-  }
-  API_CUDA(cudaStreamSynchronize(m->stream));
-  for (int64_t i = 0; i < nb; ++i) { if (loss_out) loss_out[i] = m->pin_series[2 * i]; if (mae_out) mae_out[i] = m->pin_series[2 * i + 1]; }
-  m->launches += g_launch_count - l0;
-  return CVT_OK;
+  const cvt_host_arrays a{img, proc, y, 0, 0, 0, n};
+  return cvt_train_epoch_stream(h, &a, nullptr, 0, batch, lr, -1, loss_out, mae_out);
 }
 
-int cvt_predict_host(cvt_model* h, const float* img, const float* proc, int64_t n, float* out) {
-  if (!h || !img || !out || n < 0) { set_error("cvt_predict_host: bad argument"); return CVT_ERR_INVALID; }
+int cvt_predict_arrays(cvt_model* h, const cvt_host_arrays* a, float* out) {
+  if (!h || !a || !a->img || !out || a->n < 0) { set_error("cvt_predict: bad argument"); return CVT_ERR_INVALID; }
   Model* m = &h->m; const cvt_config& c = m->cfg;
-  if (c.proc_dim > 0 && !proc) { set_error("cvt_predict_host: this model needs process parameters"); return CVT_ERR_INVALID; }
+  if (c.proc_dim > 0 && !a->proc) { set_error("cvt_predict: this model needs process parameters"); return CVT_ERR_INVALID; }
   API_CUDA(cudaSetDevice(c.device));
-  const size_t per = (size_t)c.image_h * c.image_w * c.in_chans;
+  const int64_t n = a->n;
   const long long l0 = g_launch_count;
   { const int rp = ensure_pin_series(m, n * c.num_classes); if (rp) return rp; }       // device -> pinned -> out: the loop never blocks
   Staging last = staging_of(m, 0);
   int64_t i = 0;
   for (int64_t o = 0; o < n; o += c.max_batch, ++i) {        // chunk i+1 is copied while chunk i runs
     const int B = (int)std::min<int64_t>(c.max_batch, n - o);
-    { const int rs = stage_chunk(m, i, img + o * per, proc ? proc + o * c.proc_dim : nullptr, nullptr, B); if (rs) return rs; }
+    { const int rs = stage_chunk(m, i, *a, o, B, false); if (rs) return rs; }
     last = staging_of(m, (int)(i & 1));
     { const int rf = infer_forward(m, last.img, c.proc_dim > 0 ? last.proc : nullptr, B, i > 0); if (rf) return rf; }
     API_CUDA(cudaMemcpyAsync(m->pin_series + o * c.num_classes, m->pred, (size_t)B * c.num_classes * sizeof(float), cudaMemcpyDeviceToHost, m->stream));
@@ -1292,30 +1405,35 @@ int cvt_predict_host(cvt_model* h, const float* img, const float* proc, int64_t 
   }
   API_CUDA(cudaStreamSynchronize(m->stream));
   memcpy(out, m->pin_series, (size_t)n * c.num_classes * sizeof(float));
-  g_last_inputs = {last.img, c.proc_dim > 0 ? last.proc : nullptr};
+  m->last_img = last.img; m->last_proc = c.proc_dim > 0 ? last.proc : nullptr;
   m->launches += g_launch_count - l0;
   return CVT_OK;
 }
+int cvt_predict_host(cvt_model* h, const float* img, const float* proc, int64_t n, float* out) {
+  if (!h || !img || !out || n < 0) { set_error("cvt_predict_host: bad argument"); return CVT_ERR_INVALID; }
+  const cvt_host_arrays a{img, proc, nullptr, 0, 0, 0, n};
+  return cvt_predict_arrays(h, &a, out);
+}
 
-int cvt_evaluate_host(cvt_model* h, const float* img, const float* proc, const float* y, int64_t n, float* loss, float* mae) {
-  if (!h || !img || !y || n < 1) { set_error("cvt_evaluate_host: bad argument"); return CVT_ERR_INVALID; }
+int cvt_evaluate_arrays(cvt_model* h, const cvt_host_arrays* a, float* loss, float* mae) {
+  if (!h || !a || !a->img || !a->y || a->n < 1) { set_error("cvt_evaluate: bad argument"); return CVT_ERR_INVALID; }
   Model* m = &h->m; const cvt_config& c = m->cfg;
-  if (c.proc_dim > 0 && !proc) { set_error("cvt_evaluate_host: this model needs process parameters"); return CVT_ERR_INVALID; }
+  if (c.proc_dim > 0 && !a->proc) { set_error("cvt_evaluate: this model needs process parameters"); return CVT_ERR_INVALID; }
   API_CUDA(cudaSetDevice(c.device));
-  const size_t per = (size_t)c.image_h * c.image_w * c.in_chans;
+  const int64_t n = a->n;
   const long long l0 = g_launch_count;
   API_CUDA(cudaMemsetAsync(m->metrics + 2, 0, 2 * sizeof(float), m->stream));
   Staging last = staging_of(m, 0);
   int64_t i = 0;
-  for (int64_t o = 0; o < n; o += c.max_batch, ++i) {        // as cvt_predict_host: chunk i+1 is copied while chunk i runs
+  for (int64_t o = 0; o < n; o += c.max_batch, ++i) {        // as cvt_predict_arrays: chunk i+1 is copied while chunk i runs
     const int B = (int)std::min<int64_t>(c.max_batch, n - o);
-    { const int rs = stage_chunk(m, i, img + o * per, proc ? proc + o * c.proc_dim : nullptr, y + o * c.num_classes, B); if (rs) return rs; }
+    { const int rs = stage_chunk(m, i, *a, o, B, true); if (rs) return rs; }
     last = staging_of(m, (int)(i & 1));
     { const int rf = infer_forward(m, last.img, c.proc_dim > 0 ? last.proc : nullptr, B, i > 0); if (rf) return rf; }
     API_CUDA(launch_mse_loss(m->pred, last.y, B * c.num_classes, m->metrics + 2, nullptr, 1.f, 1, m->stream));
     API_CUDA(cudaEventRecord(m->ev_done[i & 1], m->stream));
   }
-  g_last_inputs = {last.img, c.proc_dim > 0 ? last.proc : nullptr};
+  m->last_img = last.img; m->last_proc = c.proc_dim > 0 ? last.proc : nullptr;
   API_CUDA(cudaMemcpyAsync(m->pin_metrics + 2, m->metrics + 2, 2 * sizeof(float), cudaMemcpyDeviceToHost, m->stream));
   API_CUDA(cudaStreamSynchronize(m->stream));
   const double cnt = (double)n * c.num_classes;
@@ -1324,9 +1442,278 @@ int cvt_evaluate_host(cvt_model* h, const float* img, const float* proc, const f
   m->launches += g_launch_count - l0;
   return CVT_OK;
 }
+int cvt_evaluate_host(cvt_model* h, const float* img, const float* proc, const float* y, int64_t n, float* loss, float* mae) {
+  if (!h || !img || !y || n < 1) { set_error("cvt_evaluate_host: bad argument"); return CVT_ERR_INVALID; }
+  const cvt_host_arrays a{img, proc, y, 0, 0, 0, n};
+  return cvt_evaluate_arrays(h, &a, loss, mae);
+}
+
+// ---- resident datasets ----------------------------------------------------------------------------------------------------------
+static int check_slot(Model* m, int slot, const char* who, bool need_data) {
+  if (slot < 0 || slot >= CVT_DATASET_SLOTS) { set_error(std::string(who) + ": slot outside [0, CVT_DATASET_SLOTS)"); return CVT_ERR_INVALID; }
+  if (need_data && m->ds[slot].n < 1) { set_error(std::string(who) + ": dataset slot " + std::to_string(slot) + " is empty (cvt_dataset_alloc first)"); return CVT_ERR_STATE; }
+  return CVT_OK;
+}
+static int upload_order(Model* m, const int32_t* order, int64_t n, int64_t limit, const char* who) {
+  if (!order) return CVT_OK;
+  for (int64_t i = 0; i < n; ++i) if (order[i] < 0 || order[i] >= limit) { set_error(std::string(who) + ": order[" + std::to_string(i) + "] outside the data set"); return CVT_ERR_INVALID; }
+  if (m->order_cap < n) {
+    API_CUDA(cudaStreamSynchronize(m->stream)); API_CUDA(cudaStreamSynchronize(m->copy_stream));
+    if (m->order_dev) cudaFree(m->order_dev);
+    m->order_dev = nullptr; m->order_cap = 0;
+    API_CUDA(cudaMalloc(reinterpret_cast<void**>(&m->order_dev), (size_t)n * sizeof(int32_t)));
+    m->order_cap = n;
+  }
+  // (the previous epoch's gathers have been issued on m->stream / copy_stream: order the overwrite after both)
+  API_CUDA(cudaStreamSynchronize(m->copy_stream));
+  API_CUDA(cudaMemcpyAsync(m->order_dev, order, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, m->stream));
+  API_CUDA(cudaStreamSynchronize(m->stream));
+  return CVT_OK;
+}
+
+int cvt_dataset_free(cvt_model* h, int slot) {
+  if (!h) return CVT_ERR_INVALID;
+  Model* m = &h->m;
+  int r = check_slot(m, slot, "cvt_dataset_free", false); if (r) return r;
+  if (m->stream) cudaStreamSynchronize(m->stream);
+  if (m->copy_stream) cudaStreamSynchronize(m->copy_stream);
+  Model::Dataset& d = m->ds[slot];
+  if (d.img) cudaFree(d.img); if (d.proc) cudaFree(d.proc); if (d.y) cudaFree(d.y);
+  d = Model::Dataset{};
+  return CVT_OK;
+}
+int cvt_dataset_alloc(cvt_model* h, int slot, int64_t n) {
+  if (!h || n < 1) { set_error("cvt_dataset_alloc: bad argument"); return CVT_ERR_INVALID; }
+  Model* m = &h->m; const cvt_config& c = m->cfg;
+  int r = check_slot(m, slot, "cvt_dataset_alloc", false); if (r) return r;
+  API_CUDA(cudaSetDevice(c.device));
+  cvt_dataset_free(h, slot);
+  Model::Dataset& d = m->ds[slot];
+  const size_t per = (size_t)c.image_h * c.image_w * c.in_chans;
+  cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&d.img), (size_t)n * per * sizeof(float));
+  if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void**>(&d.proc), (size_t)n * std::max(1, c.proc_dim) * sizeof(float));
+  if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void**>(&d.y), (size_t)n * c.num_classes * sizeof(float));
+  if (e != cudaSuccess) {
+    set_error(std::string("cvt_dataset_alloc: ") + std::to_string(n) + " samples do not fit in device memory: " + cudaGetErrorString(e));
+    (void)cudaGetLastError(); cvt_dataset_free(h, slot); return CVT_ERR_CUDA;
+  }
+  d.n = n;
+  API_CUDA(cudaMemsetAsync(d.proc, 0, (size_t)n * std::max(1, c.proc_dim) * sizeof(float), m->stream));
+  API_CUDA(cudaMemsetAsync(d.y, 0, (size_t)n * c.num_classes * sizeof(float), m->stream));
+  return CVT_OK;
+}
+int64_t cvt_dataset_count(const cvt_model* h, int slot) {
+  if (!h || slot < 0 || slot >= CVT_DATASET_SLOTS) return CVT_ERR_INVALID;
+  return h->m.ds[slot].n;
+}
+int cvt_dataset_write(cvt_model* h, int slot, int64_t offset, const cvt_host_arrays* a) {
+  if (!h || !a || a->n < 0 || offset < 0) { set_error("cvt_dataset_write: bad argument"); return CVT_ERR_INVALID; }
+  Model* m = &h->m; const cvt_config& c = m->cfg;
+  int r = check_slot(m, slot, "cvt_dataset_write", true); if (r) return r;
+  Model::Dataset& d = m->ds[slot];
+  if (offset + a->n > d.n) { set_error("cvt_dataset_write: rows past the end of the dataset"); return CVT_ERR_INVALID; }
+  API_CUDA(cudaSetDevice(c.device));
+  const size_t per = (size_t)c.image_h * c.image_w * c.in_chans;
+  const long long l0 = g_launch_count;
+  if (a->img) {
+    for (int64_t o = 0; o < a->n; o += c.max_batch) {
+      const int cnt = (int)std::min<int64_t>(c.max_batch, a->n - o);
+      r = h2d_images(m, d.img + (offset + o) * per, a->img, a->img_f64, nullptr, o, cnt, 0, m->stream); if (r) return r;
+    }
+  }
+  if (a->proc && c.proc_dim > 0) { r = h2d_small(m, d.proc + offset * c.proc_dim, a->proc, a->proc_f64, nullptr, 0, a->n, c.proc_dim, m->stream); if (r) return r; }
+  if (a->y) { r = h2d_small(m, d.y + offset * c.num_classes, a->y, a->y_f64, nullptr, 0, a->n, c.num_classes, m->stream); if (r) return r; }
+  API_CUDA(cudaStreamSynchronize(m->stream));
+  m->launches += g_launch_count - l0;
+  return CVT_OK;
+}
+int cvt_dataset_write_u8(cvt_model* h, int slot, int64_t offset, int64_t count, const uint8_t* pixels, int src_h, int src_w, int src_c) {
+  if (!h || !pixels || count < 0 || offset < 0 || src_h < 1 || src_w < 1 || (src_c != 1 && src_c != 3)) { set_error("cvt_dataset_write_u8: bad argument (src_c must be 1 or 3)"); return CVT_ERR_INVALID; }
+  Model* m = &h->m; const cvt_config& c = m->cfg;
+  int r = check_slot(m, slot, "cvt_dataset_write_u8", true); if (r) return r;
+  if (c.in_chans != 1) { set_error("cvt_dataset_write_u8: the grey conversion needs a model with in_chans = 1"); return CVT_ERR_INVALID; }
+  Model::Dataset& d = m->ds[slot];
+  if (offset + count > d.n) { set_error("cvt_dataset_write_u8: rows past the end of the dataset"); return CVT_ERR_INVALID; }
+  API_CUDA(cudaSetDevice(c.device));
+  const int dh = c.image_h, dw = c.image_w;
+  if (!m->pp_tab) {
+    API_CUDA(cudaMalloc(reinterpret_cast<void**>(&m->pp_tab), (size_t)3 * (8192 + 8192) * sizeof(int32_t)));
+    API_CUDA(cudaMalloc(reinterpret_cast<void**>(&m->pp_lut), 256 * sizeof(float)));
+    float lut[256];
+    for (int g = 0; g < 256; ++g) lut[g] = (float)((double)g / 255.0);      // image / 255.0 in float64, then Keras' cast to float32
+    API_CUDA(cudaMemcpy(m->pp_lut, lut, sizeof(lut), cudaMemcpyHostToDevice));
+  }
+  if (dh > 8192 || dw > 8192) { set_error("cvt_dataset_write_u8: image larger than 8192"); return CVT_ERR_INVALID; }
+  if (m->pp_key[0] != src_h || m->pp_key[1] != src_w || m->pp_key[2] != dh || m->pp_key[3] != dw) {
+    std::vector<int32_t> tab((size_t)3 * (dw + dh));
+    resize_axis_table(src_w, dw, 1, tab.data(), tab.data() + dw, tab.data() + 2 * dw);
+    resize_axis_table(src_h, dh, 0, tab.data() + 3 * dw, tab.data() + 3 * dw + dh, tab.data() + 3 * dw + 2 * dh);
+    API_CUDA(cudaStreamSynchronize(m->stream));
+    API_CUDA(cudaMemcpy(m->pp_tab, tab.data(), tab.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+    m->pp_key[0] = src_h; m->pp_key[1] = src_w; m->pp_key[2] = dh; m->pp_key[3] = dw;
+  }
+  const size_t src_bytes = (size_t)src_h * src_w * src_c;
+  const int64_t chunk = std::max<int64_t>(1, ((int64_t)64 << 20) / (int64_t)src_bytes);
+  if (m->pp_pix_cap < (size_t)std::min<int64_t>(chunk, count) * src_bytes) {
+    API_CUDA(cudaStreamSynchronize(m->stream));
+    if (m->pp_pix) cudaFree(m->pp_pix);
+    m->pp_pix = nullptr; m->pp_pix_cap = 0;
+    API_CUDA(cudaMalloc(reinterpret_cast<void**>(&m->pp_pix), (size_t)chunk * src_bytes));
+    m->pp_pix_cap = (size_t)chunk * src_bytes;
+  }
+  const long long l0 = g_launch_count;
+  const size_t per = (size_t)dh * dw;
+  for (int64_t o = 0; o < count; o += chunk) {
+    const int64_t cnt = std::min(chunk, count - o);
+    r = h2d_rows(m, m->pp_pix, pixels, nullptr, o, cnt, src_bytes, m->stream); if (r) return r;
+    API_CUDA(launch_preprocess_u8(m->pp_pix, src_h, src_w, src_c, m->pp_tab, m->pp_lut, dh, dw, cnt, d.img + (offset + o) * per, m->stream));
+  }
+  API_CUDA(cudaStreamSynchronize(m->stream));
+  m->launches += g_launch_count - l0;
+  return CVT_OK;
+}
+int cvt_dataset_read(cvt_model* h, int slot, int64_t offset, int64_t count, float* img, float* proc, float* y) {
+  if (!h || offset < 0 || count < 0) { set_error("cvt_dataset_read: bad argument"); return CVT_ERR_INVALID; }
+  Model* m = &h->m; const cvt_config& c = m->cfg;
+  int r = check_slot(m, slot, "cvt_dataset_read", true); if (r) return r;
+  Model::Dataset& d = m->ds[slot];
+  if (offset + count > d.n) { set_error("cvt_dataset_read: rows past the end of the dataset"); return CVT_ERR_INVALID; }
+  const size_t per = (size_t)c.image_h * c.image_w * c.in_chans;
+  if (img) API_CUDA(cudaMemcpyAsync(img, d.img + offset * per, (size_t)count * per * sizeof(float), cudaMemcpyDeviceToHost, m->stream));
+  if (proc && c.proc_dim > 0) API_CUDA(cudaMemcpyAsync(proc, d.proc + offset * c.proc_dim, (size_t)count * c.proc_dim * sizeof(float), cudaMemcpyDeviceToHost, m->stream));
+  if (y) API_CUDA(cudaMemcpyAsync(y, d.y + offset * c.num_classes, (size_t)count * c.num_classes * sizeof(float), cudaMemcpyDeviceToHost, m->stream));
+  API_CUDA(cudaStreamSynchronize(m->stream));
+  return CVT_OK;
+}
+
+int cvt_train_epoch_stream(cvt_model* h, const cvt_host_arrays* a, const int32_t* order, int64_t n_order, int batch, float lr, int fill_slot,
+                           float* loss_out, float* mae_out) {
+  if (!h || !a || !a->img || !a->y || a->n < 1) { set_error("cvt_train_epoch_stream: bad argument"); return CVT_ERR_INVALID; }
+  Model* m = &h->m; const cvt_config& c = m->cfg;
+  if (c.proc_dim > 0 && !a->proc) { set_error("cvt_train_epoch_stream: this model needs process parameters"); return CVT_ERR_INVALID; }
+  int r = check_batch(m, batch, "cvt_train_epoch_stream"); if (r) return r;
+  const int64_t n = order ? n_order : a->n;
+  if (n < 1) { set_error("cvt_train_epoch_stream: empty epoch"); return CVT_ERR_INVALID; }
+  if (fill_slot >= 0) {
+    r = check_slot(m, fill_slot, "cvt_train_epoch_stream", true); if (r) return r;
+    if (m->ds[fill_slot].n != a->n) { set_error("cvt_train_epoch_stream: the dataset to fill must have as many rows as the host arrays"); return CVT_ERR_INVALID; }
+  }
+  API_CUDA(cudaSetDevice(c.device));
+  r = upload_order(m, order, n, a->n, "cvt_train_epoch_stream"); if (r) return r;
+  const int64_t nb = (n + batch - 1) / batch;
+  r = ensure_pin_series(m, 2 * nb); if (r) return r;
+  const size_t per = (size_t)c.image_h * c.image_w * c.in_chans;
+  const long long l0 = g_launch_count;
+  for (int64_t i = 0; i < nb; ++i) {
+    const int64_t o = i * batch; const int B = (int)std::min<int64_t>(batch, n - o);
+    const int slot = (int)(i & 1); const Staging st = staging_of(m, slot);
+    if (i >= 2) API_CUDA(cudaStreamWaitEvent(m->copy_stream, m->ev_done[slot], 0));
+    r = h2d_images(m, st.img, a->img, a->img_f64, order, o, B, slot, m->copy_stream); if (r) return r;
+    if (c.proc_dim > 0) { r = h2d_small(m, st.proc, a->proc, a->proc_f64, order, o, B, c.proc_dim, m->copy_stream); if (r) return r; }
+    r = h2d_small(m, st.y, a->y, a->y_f64, order, o, B, c.num_classes, m->copy_stream); if (r) return r;
+    if (fill_slot >= 0) {      // the batch also lands at its own rows of the resident dataset
+      Model::Dataset& d = m->ds[fill_slot];
+      const int32_t* di = order ? m->order_dev + o : nullptr;
+      const int64_t base = order ? 0 : o;
+      API_CUDA(launch_move_rows(d.img + base * per, di, st.img, nullptr, B, (long long)per, d.proc + base * c.proc_dim, c.proc_dim > 0 ? st.proc : nullptr,
+                                c.proc_dim, d.y + base * c.num_classes, st.y, c.num_classes, m->copy_stream));
+    }
+    API_CUDA(cudaEventRecord(m->ev_copy[slot], m->copy_stream));
+    API_CUDA(cudaStreamWaitEvent(m->stream, m->ev_copy[slot], 0));
+    r = train_step_dev(m, st.img, c.proc_dim > 0 ? st.proc : nullptr, st.y, B, lr); if (r) return r;
+    API_CUDA(cudaMemcpyAsync(m->pin_series + 2 * i, m->metrics, 2 * sizeof(float), cudaMemcpyDeviceToHost, m->stream));
+    API_CUDA(cudaEventRecord(m->ev_done[slot], m->stream));
+    m->last_img = st.img; m->last_proc = c.proc_dim > 0 ? st.proc : nullptr;
+  }
+  API_CUDA(cudaStreamSynchronize(m->copy_stream));
+  API_CUDA(cudaStreamSynchronize(m->stream));
+  for (int64_t i = 0; i < nb; ++i) { if (loss_out) loss_out[i] = m->pin_series[2 * i]; if (mae_out) mae_out[i] = m->pin_series[2 * i + 1]; }
+  m->launches += g_launch_count - l0;
+  return CVT_OK;
+}
+
+int cvt_train_epoch_resident(cvt_model* h, int slot, const int32_t* order, int64_t n_order, int batch, float lr, float* loss_out, float* mae_out) {
+  if (!h) { set_error("cvt_train_epoch_resident: null model"); return CVT_ERR_INVALID; }
+  Model* m = &h->m; const cvt_config& c = m->cfg;
+  int r = check_slot(m, slot, "cvt_train_epoch_resident", true); if (r) return r;
+  r = check_batch(m, batch, "cvt_train_epoch_resident"); if (r) return r;
+  Model::Dataset& d = m->ds[slot];
+  const int64_t n = order ? n_order : d.n;
+  if (n < 1) { set_error("cvt_train_epoch_resident: empty epoch"); return CVT_ERR_INVALID; }
+  API_CUDA(cudaSetDevice(c.device));
+  r = upload_order(m, order, n, d.n, "cvt_train_epoch_resident"); if (r) return r;
+  const int64_t nb = (n + batch - 1) / batch;
+  r = ensure_pin_series(m, 2 * nb); if (r) return r;
+  const size_t per = (size_t)c.image_h * c.image_w * c.in_chans;
+  const Staging st = staging_of(m, 0);
+  const long long l0 = g_launch_count;
+  for (int64_t i = 0; i < nb; ++i) {
+    const int64_t o = i * batch; const int B = (int)std::min<int64_t>(batch, n - o);
+    const int32_t* si = order ? m->order_dev + o : nullptr;
+    const int64_t base = order ? 0 : o;
+    API_CUDA(launch_move_rows(st.img, nullptr, d.img + base * per, si, B, (long long)per, st.proc, c.proc_dim > 0 ? d.proc + base * c.proc_dim : nullptr,
+                              c.proc_dim, st.y, d.y + base * c.num_classes, c.num_classes, m->stream));
+    r = train_step_dev(m, st.img, c.proc_dim > 0 ? st.proc : nullptr, st.y, B, lr); if (r) return r;
+    API_CUDA(cudaMemcpyAsync(m->pin_series + 2 * i, m->metrics, 2 * sizeof(float), cudaMemcpyDeviceToHost, m->stream));
+  }
+  m->last_img = st.img; m->last_proc = c.proc_dim > 0 ? st.proc : nullptr;
+  API_CUDA(cudaStreamSynchronize(m->stream));
+  for (int64_t i = 0; i < nb; ++i) { if (loss_out) loss_out[i] = m->pin_series[2 * i]; if (mae_out) mae_out[i] = m->pin_series[2 * i + 1]; }
+  m->launches += g_launch_count - l0;
+  return CVT_OK;
+}
+
+// forward(training = 0) over a resident dataset in chunks of max_batch; with_loss: MSE / MAE sums, else predictions into pin_series
+static int resident_forward(Model* m, int slot, bool with_loss) {
+  const cvt_config& c = m->cfg; Model::Dataset& d = m->ds[slot];
+  const size_t per = (size_t)c.image_h * c.image_w * c.in_chans;
+  const Staging st = staging_of(m, 0);
+  int64_t i = 0;
+  for (int64_t o = 0; o < d.n; o += c.max_batch, ++i) {
+    const int B = (int)std::min<int64_t>(c.max_batch, d.n - o);
+    // the chunk is copied into the staging buffers so that every chunk replays the same captured graph
+    API_CUDA(launch_move_rows(st.img, nullptr, d.img + o * per, nullptr, B, (long long)per, st.proc, c.proc_dim > 0 ? d.proc + o * c.proc_dim : nullptr,
+                              c.proc_dim, st.y, d.y + o * c.num_classes, c.num_classes, m->stream));
+    { const int rf = infer_forward(m, st.img, c.proc_dim > 0 ? st.proc : nullptr, B, i > 0); if (rf) return rf; }
+    if (with_loss) API_CUDA(launch_mse_loss(m->pred, st.y, B * c.num_classes, m->metrics + 2, nullptr, 1.f, 1, m->stream));
+    else API_CUDA(cudaMemcpyAsync(m->pin_series + o * c.num_classes, m->pred, (size_t)B * c.num_classes * sizeof(float), cudaMemcpyDeviceToHost, m->stream));
+  }
+  m->last_img = st.img; m->last_proc = c.proc_dim > 0 ? st.proc : nullptr;
+  return CVT_OK;
+}
+int cvt_evaluate_resident(cvt_model* h, int slot, float* loss, float* mae) {
+  if (!h) { set_error("cvt_evaluate_resident: null model"); return CVT_ERR_INVALID; }
+  Model* m = &h->m; const cvt_config& c = m->cfg;
+  int r = check_slot(m, slot, "cvt_evaluate_resident", true); if (r) return r;
+  API_CUDA(cudaSetDevice(c.device));
+  const long long l0 = g_launch_count;
+  API_CUDA(cudaMemsetAsync(m->metrics + 2, 0, 2 * sizeof(float), m->stream));
+  r = resident_forward(m, slot, true); if (r) return r;
+  API_CUDA(cudaMemcpyAsync(m->pin_metrics + 2, m->metrics + 2, 2 * sizeof(float), cudaMemcpyDeviceToHost, m->stream));
+  API_CUDA(cudaStreamSynchronize(m->stream));
+  const double cnt = (double)m->ds[slot].n * c.num_classes;
+  if (loss) *loss = (float)(m->pin_metrics[2] / cnt);
+  if (mae) *mae = (float)(m->pin_metrics[3] / cnt);
+  m->launches += g_launch_count - l0;
+  return CVT_OK;
+}
+int cvt_predict_resident(cvt_model* h, int slot, float* out) {
+  if (!h || !out) { set_error("cvt_predict_resident: null argument"); return CVT_ERR_INVALID; }
+  Model* m = &h->m; const cvt_config& c = m->cfg;
+  int r = check_slot(m, slot, "cvt_predict_resident", true); if (r) return r;
+  API_CUDA(cudaSetDevice(c.device));
+  const long long l0 = g_launch_count;
+  r = ensure_pin_series(m, m->ds[slot].n * c.num_classes); if (r) return r;
+  r = resident_forward(m, slot, false); if (r) return r;
+  API_CUDA(cudaStreamSynchronize(m->stream));
+  memcpy(out, m->pin_series, (size_t)m->ds[slot].n * c.num_classes * sizeof(float));
+  m->launches += g_launch_count - l0;
+  return CVT_OK;
+}
 
 int cvt_set_dropout(cvt_model* h, int mode, uint64_t seed) {
   if (!h || mode < 0 || mode > 2) { set_error("cvt_set_dropout: bad mode"); return CVT_ERR_INVALID; }
+  if (h->m.dropout_mode == mode && h->m.dropout_seed == seed) return CVT_OK;      // same stream: the step counter keeps running
   h->m.dropout_mode = mode; h->m.dropout_seed = seed; h->m.dropout_step = 0;
   clear_graphs(&h->m);                                   // mode and seed are baked into captured launches
   return CVT_OK;
@@ -1399,7 +1786,7 @@ int64_t cvt_get_tap(cvt_model* h, const char* name, float* dst, int64_t capacity
 int cvt_backward_to_tap(cvt_model* h, const float* dout_host, const char* name, float* dst, int64_t capacity) {
   if (!h || !dout_host || !name || !dst) { set_error("cvt_backward_to_tap: null argument"); return CVT_ERR_INVALID; }
   Model* m = &h->m;
-  if (!m->have_forward || !g_last_inputs.img) { set_error("cvt_backward_to_tap: call cvt_forward first"); return CVT_ERR_STATE; }
+  if (!m->have_forward || !m->last_img) { set_error("cvt_backward_to_tap: call cvt_forward first"); return CVT_ERR_STATE; }
   int si; const char* f;
   if (parse_stage(name, &si, &f) != 0 || si >= m->n_stages || strcmp(f, "x2") != 0) { set_error("cvt_backward_to_tap: tap must be s{i}.x2"); return CVT_ERR_INVALID; }
   const int B = m->last_batch; const StageGeo& g = m->geo[si];
@@ -1407,7 +1794,7 @@ int cvt_backward_to_tap(cvt_model* h, const float* dout_host, const char* name, 
   if (capacity < n) { set_error("cvt_backward_to_tap: destination too small"); return CVT_ERR_INVALID; }
   API_CUDA(cudaMemcpyAsync(m->dpred, dout_host, (size_t)B * m->cfg.num_classes * sizeof(float), cudaMemcpyHostToDevice, m->stream));
   float* gptr = nullptr;
-  API_CUDA(backward_impl(m, g_last_inputs.img, g_last_inputs.proc, B, m->last_training, si, &gptr));
+  API_CUDA(backward_impl(m, m->last_img, m->last_proc, B, m->last_training, si, &gptr));
   API_CUDA(cudaMemcpyAsync(dst, gptr, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, m->stream));
   API_CUDA(cudaStreamSynchronize(m->stream));
   return CVT_OK;
@@ -1429,6 +1816,17 @@ int cvt_profile_step(cvt_model* h, const float* img_dev, const float* proc_dev, 
   Model* m = &h->m;
   int r = check_batch(m, batch, "cvt_profile_step"); if (r) return r;
   if (training && !y_dev) { set_error("cvt_profile_step: training needs targets"); return CVT_ERR_INVALID; }
+  // the profiled step must leave the model as it found it: Adam moments, BatchNorm moving statistics and the dropout counter are
+  // saved here and restored below (the weights themselves do not move: the Adam launch runs with a zero step size)
+  const size_t n_mom = (size_t)m->n_train * sizeof(float), n_st = (size_t)std::max<int64_t>(m->n_state, 4) * sizeof(float);
+  float* save = nullptr;
+  const uint32_t save_step = m->dropout_step;
+  if (training) {
+    API_CUDA(cudaMalloc(&save, 2 * n_mom + n_st));
+    API_CUDA(cudaMemcpyAsync(save, m->Mo, n_mom, cudaMemcpyDeviceToDevice, m->stream));
+    API_CUDA(cudaMemcpyAsync(save + m->n_train, m->Vo, n_mom, cudaMemcpyDeviceToDevice, m->stream));
+    API_CUDA(cudaMemcpyAsync(save + 2 * m->n_train, m->St, n_st, cudaMemcpyDeviceToDevice, m->stream));
+  }
   std::vector<ProfMark> marks;
   g_prof = &marks;
   int rc = CVT_OK;
@@ -1444,17 +1842,36 @@ int cvt_profile_step(cvt_model* h, const float* img_dev, const float* proc_dev, 
     }
   } while (0);
   g_prof = nullptr;
+  if (save) {
+    cudaMemcpyAsync(m->Mo, save, n_mom, cudaMemcpyDeviceToDevice, m->stream);
+    cudaMemcpyAsync(m->Vo, save + m->n_train, n_mom, cudaMemcpyDeviceToDevice, m->stream);
+    cudaMemcpyAsync(m->St, save + 2 * m->n_train, n_st, cudaMemcpyDeviceToDevice, m->stream);
+    m->dropout_step = save_step;
+  }
   cudaStreamSynchronize(m->stream);
+  if (save) cudaFree(save);
   int n = 0;
+  m->prof_groups.clear();
   for (size_t i = 0; i + 1 < marks.size() && n < max_entries; ++i) {
     float t = 0.f; cudaEventElapsedTime(&t, marks[i].ev, marks[i + 1].ev);
     if (!strncmp(marks[i].name, "end", 3)) continue;
     names[n] = marks[i].name; ms[n] = t; ++n;
+    m->prof_groups.push_back({marks[i].name, (int)(marks[i + 1].launches - marks[i].launches)});
   }
   for (auto& mk : marks) cudaEventDestroy(mk.ev);
   *n_entries = n;
-  g_last_inputs = {img_dev, proc_dev};
+  m->last_img = img_dev; m->last_proc = proc_dev;
   return rc;
+}
+
+// kernels each group of the last cvt_profile_step launched, in issue order (joins an ncu launch list to the groups: tools/ncu_traffic.py)
+int cvt_profile_group_launches(cvt_model* h, int max_entries, const char** names, int* launches, int* n_entries) {
+  if (!h || !names || !launches || !n_entries) { set_error("cvt_profile_group_launches: null argument"); return CVT_ERR_INVALID; }
+  Model* m = &h->m;
+  int n = 0;
+  for (const auto& g : m->prof_groups) { if (n >= max_entries) break; names[n] = g.first; launches[n] = g.second; ++n; }
+  *n_entries = n;
+  return CVT_OK;
 }
 
 }  // extern "C"

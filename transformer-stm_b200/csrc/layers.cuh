@@ -102,6 +102,15 @@ cudaError_t launch_token_mean_bwd(const float* dy, long long lddy, int B, int T,
 // copy rows: dst[dmap(r)*ldd + c] = src[smap(r)*lds + c]
 cudaError_t launch_copy_rows(float* dst, RowMap dmap, long long ldd, const float* src, RowMap smap, long long lds, int rows, int D, cudaStream_t s);
 
+// input pipeline (dataset.cu): rows moved by index between a resident dataset and the staging buffers of a step (idx nullable = identity);
+// float64 host rows converted after their copy; OpenCV's 8-bit bilinear resize + BGR2GRAY + /255 (models/CvT(Par).py:420-423)
+cudaError_t launch_move_rows(float* dst_img, const int32_t* dst_idx, const float* src_img, const int32_t* src_idx, int rows, long long row_floats,
+                             float* dst_p, const float* src_p, int P, float* dst_y, const float* src_y, int nc, cudaStream_t s);
+cudaError_t launch_f64_to_f32(float* dst, const double* src, long long n, cudaStream_t s);
+void resize_axis_table(int src, int dst, int clamp_weights, int32_t* s_out, int32_t* w0, int32_t* w1);      // host: cv::resize INTER_LINEAR tables of one axis
+cudaError_t launch_preprocess_u8(const uint8_t* pix_dev, int sh, int sw, int sc, const int32_t* tab_dev, const float* lut_dev, int dh, int dw,
+                                 long long count, float* out, cudaStream_t s);
+
 // MSE + MAE + dL/dpred  (model.compile(loss='mean_squared_error', metrics=['mae']), models/CvT(Par).py:464-466)
 // metrics[0] = mean((p-y)^2), metrics[1] = mean(|p-y|); dpred = 2 (p-y) / (B*nc) * grad_scale (nullable)
 cudaError_t launch_mse_loss(const float* pred, const float* y, int n, float* metrics, float* dpred, float grad_scale, int accumulate, cudaStream_t s);

@@ -84,16 +84,29 @@ struct Model {
   cudaStream_t copy_stream = nullptr; cudaEvent_t ev_copy[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
   float* pin_series = nullptr; int64_t pin_series_cap = 0;     // pinned host: per-batch {loss, mae} of an epoch
 
+  // resident datasets (cvt_dataset_*): the training / validation sets live in HBM, epochs gather their batches by index
+  struct Dataset { float* img = nullptr; float* proc = nullptr; float* y = nullptr; int64_t n = 0; };
+  Dataset ds[CVT_DATASET_SLOTS];
+  int32_t* order_dev = nullptr; int64_t order_cap = 0;      // the epoch permutation
+  // pinned ring that pageable host rows are gathered into before their asynchronous copy (shuffle and staging are one pass)
+  static constexpr int kRing = 6;
+  uint8_t* ring[kRing] = {}; size_t ring_cap = 0; cudaEvent_t ring_ev[kRing] = {};
+  bool ring_busy[kRing] = {}; int ring_next = 0;
+  double* raw64[2] = {nullptr, nullptr}; size_t raw64_cap = 0;      // landing buffers of float64 host rows (converted on the device)
+  uint8_t* pp_pix = nullptr; size_t pp_pix_cap = 0; int32_t* pp_tab = nullptr; float* pp_lut = nullptr; int pp_key[4] = {0, 0, 0, 0};
+
   void* workspace = nullptr;
   int64_t workspace_bytes = 0;
 
   cudaStream_t stream = nullptr;
   int last_batch = 0, last_training = 0, have_forward = 0;
+  const float *last_img = nullptr, *last_proc = nullptr;   // device inputs of the last forward (read again by the backward pass)
   int dropout_mode = CVT_DROPOUT_OFF;
   uint64_t dropout_seed = 0;
   uint32_t dropout_step = 0;
   int64_t adam_t = 0;
   long long launches = 0;
+  std::vector<std::pair<const char*, int>> prof_groups;   // (group, kernels launched) of the last cvt_profile_step
 
   // data parallel
   void* nccl_comm = nullptr;

@@ -166,12 +166,12 @@ class CvtEngine:
         return a.reshape((-1, c.image_h, c.image_w, c.in_chans))
 
     def predict(self, img, proc=None) -> np.ndarray:
-        a = self._img(img)
-        n = a.shape[0]
-        p = _f32(proc, (n, self.cfg.proc_dim)) if (self.cfg.proc_dim > 0 and proc is not None) else None
-        out = np.empty((n, self.cfg.num_classes), dtype=np.float32)
-        L.check(self.lib.cvt_predict_host(self.h, a.ctypes.data_as(C.c_void_p), p.ctypes.data_as(C.c_void_p) if p is not None else None,
-                                          n, out.ctypes.data_as(C.c_void_p)), "cvt_predict_host")
+        """model.predict on the caller's arrays as they are (float32 / float64, pageable): chunks of max_batch, copies double-buffered."""
+        if self.cfg.proc_dim > 0 and proc is None:
+            raise L.CvtError("cvt_predict failed: this model needs process parameters")
+        ha, keep = self._host_arrays(img, proc, None)
+        out = np.empty((ha.n, self.cfg.num_classes), dtype=np.float32)
+        L.check(self.lib.cvt_predict_arrays(self.h, C.byref(ha), out.ctypes.data_as(C.c_void_p)), "cvt_predict_arrays")
         return out
 
     def train_step(self, img, proc, y, lr: float):
@@ -187,25 +187,12 @@ class CvtEngine:
     def train_epoch(self, img, proc, y, batch: int, lr: float):
         """One pass over (img, proc, y) in the given order, batches of `batch` (last partial batch kept, models/CvT(Par).py:475);
         returns per-batch (loss, mae) arrays.  Copies of batch i+1 overlap the step on batch i."""
-        a = self._img(img)
-        n = a.shape[0]
-        p = _f32(proc, (n, self.cfg.proc_dim)) if (self.cfg.proc_dim > 0 and proc is not None) else None
-        t = _f32(y, (n, self.cfg.num_classes))
-        nb = (n + batch - 1) // batch
-        loss = np.empty(nb, np.float32); mae = np.empty(nb, np.float32)
-        L.check(self.lib.cvt_train_epoch_host(self.h, a.ctypes.data_as(C.c_void_p), p.ctypes.data_as(C.c_void_p) if p is not None else None,
-                                              t.ctypes.data_as(C.c_void_p), n, int(batch), lr, loss.ctypes.data_as(C.c_void_p),
-                                              mae.ctypes.data_as(C.c_void_p)), "cvt_train_epoch_host")
-        return loss, mae
+        return self.train_epoch_stream(img, proc, y, None, batch, lr, -1)
 
     def evaluate(self, img, proc, y):
-        a = self._img(img)
-        n = a.shape[0]
-        p = _f32(proc, (n, self.cfg.proc_dim)) if (self.cfg.proc_dim > 0 and proc is not None) else None
-        t = _f32(y, (n, self.cfg.num_classes))
+        ha, keep = self._host_arrays(img, proc, y)
         loss, mae = C.c_float(), C.c_float()
-        L.check(self.lib.cvt_evaluate_host(self.h, a.ctypes.data_as(C.c_void_p), p.ctypes.data_as(C.c_void_p) if p is not None else None,
-                                           t.ctypes.data_as(C.c_void_p), n, C.byref(loss), C.byref(mae)), "cvt_evaluate_host")
+        L.check(self.lib.cvt_evaluate_arrays(self.h, C.byref(ha), C.byref(loss), C.byref(mae)), "cvt_evaluate_arrays")
         return loss.value, mae.value
 
     # ---- device-pointer entry points (torch tensors or raw ints) ----
@@ -230,6 +217,106 @@ class CvtEngine:
 
     def optimizer_reset(self):
         L.check(self.lib.cvt_optimizer_reset(self.h))
+
+    def optimizer_steps(self) -> int:
+        return int(self.lib.cvt_optimizer_step_count(self.h))
+
+    # ---- resident datasets / streamed epochs (include/cvt_b200.h, "input pipeline") ----
+    def _host_arrays(self, img, proc, y):
+        """cvt_host_arrays over the caller's numpy arrays without copying them when they are C-contiguous float32 / float64
+        (the reference hands model.fit float64 [N,H,W], [N,5], [N]); returns (struct, keep-alive list)."""
+        c = self.cfg
+        keep = []
+
+        def conform(a, tail):
+            if a is None:
+                return None, 0
+            a = np.asarray(a)
+            if a.dtype not in (np.float32, np.float64) or not a.flags["C_CONTIGUOUS"]:
+                a = np.ascontiguousarray(a, dtype=np.float32)
+            if int(np.prod(a.shape[1:], dtype=np.int64)) != tail:
+                raise ValueError("expected rows of %d values, got array of shape %s" % (tail, a.shape))
+            keep.append(a)
+            return a.ctypes.data, int(a.dtype == np.float64)
+
+        n = len(img) if img is not None else (len(y) if y is not None else len(proc))
+        ha = L.HostArrays()
+        ha.img, ha.img_f64 = conform(img, c.image_h * c.image_w * c.in_chans)
+        ha.proc, ha.proc_f64 = conform(proc if c.proc_dim > 0 else None, c.proc_dim)
+        ha.y, ha.y_f64 = conform(y, c.num_classes)
+        for a in keep:
+            if a.shape[0] != n:
+                raise ValueError("Data cardinality is ambiguous: arrays of %d and %d samples" % (n, a.shape[0]))
+        ha.n = n
+        return ha, keep
+
+    def dataset_alloc(self, slot: int, n: int):
+        L.check(self.lib.cvt_dataset_alloc(self.h, slot, n), "cvt_dataset_alloc")
+
+    def dataset_free(self, slot: int):
+        L.check(self.lib.cvt_dataset_free(self.h, slot), "cvt_dataset_free")
+
+    def dataset_count(self, slot: int) -> int:
+        return int(self.lib.cvt_dataset_count(self.h, slot))
+
+    def dataset_write(self, slot: int, offset: int, img=None, proc=None, y=None):
+        ha, keep = self._host_arrays(img, proc, y)
+        L.check(self.lib.cvt_dataset_write(self.h, slot, offset, C.byref(ha)), "cvt_dataset_write")
+
+    def dataset_write_u8(self, slot: int, offset: int, pixels: np.ndarray):
+        """pixels: uint8 [count, src_h, src_w, 3] (cv2.imread layout, BGR) or [count, src_h, src_w] / [.., 1] (already grey)."""
+        a = np.ascontiguousarray(pixels, dtype=np.uint8)
+        if a.ndim == 3:
+            a = a[..., None]
+        cnt, sh, sw, sc = a.shape
+        L.check(self.lib.cvt_dataset_write_u8(self.h, slot, offset, cnt, a.ctypes.data_as(C.c_void_p), sh, sw, sc), "cvt_dataset_write_u8")
+
+    def dataset_read(self, slot: int, offset: int, count: int):
+        c = self.cfg
+        img = np.empty((count, c.image_h, c.image_w, c.in_chans), np.float32)
+        proc = np.empty((count, c.proc_dim), np.float32) if c.proc_dim > 0 else None
+        y = np.empty((count, c.num_classes), np.float32)
+        L.check(self.lib.cvt_dataset_read(self.h, slot, offset, count, img.ctypes.data_as(C.c_void_p),
+                                          proc.ctypes.data_as(C.c_void_p) if proc is not None else None, y.ctypes.data_as(C.c_void_p)), "cvt_dataset_read")
+        return img, proc, y
+
+    @staticmethod
+    def _order(order):
+        if order is None:
+            return None, 0, None
+        o = np.ascontiguousarray(order, dtype=np.int32)
+        return o.ctypes.data_as(C.c_void_p), o.size, o
+
+    def train_epoch_stream(self, img, proc, y, order, batch: int, lr: float, fill_slot: int = -1):
+        """One fit epoch over host arrays in `order` (None = as stored): rows are gathered into the library's pinned ring, copied while
+        the previous step runs and, with fill_slot >= 0, also stored into that resident dataset."""
+        ha, keep = self._host_arrays(img, proc, y)
+        op, on, okeep = self._order(order)
+        n = on if order is not None else ha.n
+        nb = (n + batch - 1) // batch
+        loss = np.empty(nb, np.float32); mae = np.empty(nb, np.float32)
+        L.check(self.lib.cvt_train_epoch_stream(self.h, C.byref(ha), op, on, int(batch), lr, int(fill_slot), loss.ctypes.data_as(C.c_void_p),
+                                                mae.ctypes.data_as(C.c_void_p)), "cvt_train_epoch_stream")
+        return loss, mae
+
+    def train_epoch_resident(self, slot: int, order, batch: int, lr: float):
+        op, on, okeep = self._order(order)
+        n = on if order is not None else self.dataset_count(slot)
+        nb = (n + batch - 1) // batch
+        loss = np.empty(nb, np.float32); mae = np.empty(nb, np.float32)
+        L.check(self.lib.cvt_train_epoch_resident(self.h, slot, op, on, int(batch), lr, loss.ctypes.data_as(C.c_void_p),
+                                                  mae.ctypes.data_as(C.c_void_p)), "cvt_train_epoch_resident")
+        return loss, mae
+
+    def evaluate_resident(self, slot: int):
+        loss, mae = C.c_float(), C.c_float()
+        L.check(self.lib.cvt_evaluate_resident(self.h, slot, C.byref(loss), C.byref(mae)), "cvt_evaluate_resident")
+        return loss.value, mae.value
+
+    def predict_resident(self, slot: int) -> np.ndarray:
+        out = np.empty((self.dataset_count(slot), self.cfg.num_classes), np.float32)
+        L.check(self.lib.cvt_predict_resident(self.h, slot, out.ctypes.data_as(C.c_void_p)), "cvt_predict_resident")
+        return out
 
     # ---- dropout ----
     def set_dropout(self, mode: str, seed: int = 0):
@@ -256,6 +343,34 @@ class CvtEngine:
         a = np.empty(count, dtype=np.float32)
         L.check(self.lib.cvt_backward_to_tap(self.h, d.ctypes.data_as(C.c_void_p), name.encode(), a.ctypes.data_as(C.c_void_p), count), "cvt_backward_to_tap")
         return a
+
+    def gradcam(self, img, proc, stage: int):
+        """tools/grad_cam_CvT.py:430-457: forward (inference mode), then d sum_b pred[b, 0] / d output of block `stage` (0-based).
+        Returns (feature map [B,h,w,D], predictions [B,nc], gradient [B,h,w,D]); the cls row (not part of the block's output map) is dropped."""
+        pred = self.predict(img, proc)
+        n = pred.shape[0]
+        if n > self.cfg.max_batch:
+            raise ValueError("gradcam: %d images exceed max_batch %d (the tool calls it with batch_size 1)" % (n, self.cfg.max_batch))
+        st = self.cfg.stages[stage]
+        D = st.embed_dim
+        feat = self.tap("s%d.out" % (stage + 1))
+        T = feat.size // (n * D)
+        Tc = T + int(st.with_cls_token)
+        dout = np.zeros((n, self.cfg.num_classes), np.float32)
+        dout[:, 0] = 1.0
+        g = self.backward_to_tap(dout, "s%d.x2" % (stage + 1), n * Tc * D).reshape(n, Tc, D)
+        if st.with_cls_token:
+            g = g[:, 1:]
+        # spatial shape of the block's map
+        h, w = self.stage_hw(stage)
+        return feat.reshape(n, h, w, D), pred, np.ascontiguousarray(g).reshape(n, h, w, D)
+
+    def stage_hw(self, stage: int):
+        """Output map size of stage `stage` (0-based): Conv2D 'same' gives ceil(in / stride) per stage."""
+        h, w = self.cfg.image_h, self.cfg.image_w
+        for s in self.cfg.stages[:stage + 1]:
+            h, w = -(-h // s.stride), -(-w // s.stride)
+        return h, w
 
     # ---- data parallel ----
     def comm_unique_id(self) -> bytes:
@@ -290,3 +405,10 @@ class CvtEngine:
         L.check(self.lib.cvt_profile_step(self.h, _ptr(img_dev), _ptr(proc_dev), _ptr(y_dev), batch, int(training), max_entries, names, ms, C.byref(n)),
                 "cvt_profile_step")
         return [(names[i].decode(), ms[i]) for i in range(n.value)]
+
+    def profile_group_launches(self, max_entries=256):
+        names = (C.c_char_p * max_entries)()
+        cnt = (C.c_int * max_entries)()
+        n = C.c_int()
+        L.check(self.lib.cvt_profile_group_launches(self.h, max_entries, names, cnt, C.byref(n)), "cvt_profile_group_launches")
+        return [(names[i].decode(), cnt[i]) for i in range(n.value)]

@@ -24,6 +24,7 @@ from typing import Callable, Dict, List, Optional, Sequence
 
 import numpy as np
 
+from . import h5lite
 from .engine import CvtConfig, CvtEngine
 
 # ---- the switches the reference keeps as module-level constants (models/CvT(Par).py:25-28,66-72) ----------------
@@ -168,8 +169,9 @@ class _Layer:
         return [v for k, v in w.items() if k.startswith(self.name + "/")]
 
 
-def _as_inputs(x, has_proc):
-    """Keras input conformance: [x, proc] list (or bare x for the Img model); images [N,H,W] get a channel axis; fp32."""
+def _as_inputs(x, has_proc, cast=True):
+    """Keras input conformance: [x, proc] list (or bare x for the Img model); images [N,H,W] get a channel axis; fp32.
+    cast=False keeps float64 arrays as they are (the library converts them while it stages them: no host-side copy of the data set)."""
     if isinstance(x, (list, tuple)):
         if has_proc:
             if len(x) != 2:
@@ -181,15 +183,31 @@ def _as_inputs(x, has_proc):
         if has_proc:
             raise ValueError("Layer expects 2 input(s), but it received 1 input tensors")
         img, proc = x, None
-    img = np.asarray(img)
+
+    def conform(a):
+        a = np.asarray(a)
+        if cast or a.dtype not in (np.float32, np.float64) or not a.flags["C_CONTIGUOUS"]:
+            a = np.ascontiguousarray(a, dtype=np.float32)
+        return a
+
+    img = conform(img)
     if img.ndim == 3:
         img = img[..., None]
-    img = np.ascontiguousarray(img, dtype=np.float32)
     if proc is not None:
-        proc = np.ascontiguousarray(np.asarray(proc), dtype=np.float32)
+        proc = conform(proc)
         if proc.shape[0] != img.shape[0]:
             raise ValueError("Data cardinality is ambiguous: image and process-parameter sample counts differ")
     return img, proc
+
+
+def _as_targets(y, n, nc, cast=True):
+    a = np.asarray(y)
+    if cast or a.dtype not in (np.float32, np.float64) or not a.flags["C_CONTIGUOUS"]:
+        a = np.ascontiguousarray(a, dtype=np.float32)
+    a = a.reshape(n, -1)
+    if a.shape[1] != nc:
+        raise ValueError("targets have %d columns, the model has num_classes=%d" % (a.shape[1], nc))
+    return a
 
 
 class Model:
@@ -208,7 +226,10 @@ class Model:
         self.stop_training = False
         self.inputs = ["Image_inputs"] + (["Proc_inputs"] if cfg.proc_dim > 0 else [])
         self.output = "pred"
-        self.dropout_seed = 0 if seed is None else int(seed)
+        # seed=None behaves like Keras: fresh dropout masks and a fresh shuffle order for every model (so the 8 "(many)" repeats differ)
+        self.dropout_seed = int.from_bytes(os.urandom(6), "little") if seed is None else int(seed)
+        self._rng = np.random.default_rng(self.dropout_seed + 977)       # ONE shuffle stream per model, carried across fit() calls
+        self.resident_limit_bytes = 64 << 30                              # data sets up to this size are kept in HBM during fit()
 
     # -- engine lifetime ---------------------------------------------------------------------------------------
     @property
@@ -227,10 +248,10 @@ class Model:
         if batch <= self.cfg.max_batch:
             return
         if self._eng is not None:
-            self._pending_weights = self._eng.get_params()
             if self._eng.optimizer_steps() > 0:
                 raise ValueError("batch_size %d exceeds the model's max_batch %d after training started; create the model with "
                                  "max_batch >= batch_size" % (batch, self.cfg.max_batch))
+            self._pending_weights = self._eng.get_params()
             self._eng.close()
             self._eng = None
         self.cfg.max_batch = int(batch)
@@ -282,74 +303,91 @@ class Model:
 
     def fit(self, x=None, y=None, batch_size=None, epochs=1, verbose=1, callbacks=None, validation_data=None, shuffle=True,
             initial_epoch=0, **kw):
+        """model.fit of models/CvT(Par).py:475-476.  The arrays stay where the caller has them (float64 or float32, pageable):
+        the first epoch streams its batches through the library's pinned ring in shuffled order and, as a side effect, leaves the
+        set resident in HBM; every later epoch is a permutation gathered on the device.  The validation set is uploaded once."""
         if self.optimizer is None:
             raise RuntimeError("You must compile your model before training/testing. Use `model.compile(optimizer, loss)`.")
         has_proc = self.cfg.proc_dim > 0
-        img, proc = _as_inputs(x, has_proc)
+        img, proc = _as_inputs(x, has_proc, cast=False)
         nc = self.cfg.num_classes
-        yy = np.ascontiguousarray(np.asarray(y), dtype=np.float32).reshape(img.shape[0], -1)
-        if yy.shape[1] != nc:
-            raise ValueError("targets have %d columns, the model has num_classes=%d" % (yy.shape[1], nc))
+        n = img.shape[0]
+        yy = _as_targets(y, n, nc, cast=False)
         bs = int(batch_size or 32)
-        self._ensure_batch(min(bs, img.shape[0]))
+        self._ensure_batch(min(bs, n))
         eng = self.engine
-        val = None
+        TRAIN, VAL = 0, 1
+        has_val = False
         if validation_data is not None:
-            vimg, vproc = _as_inputs(validation_data[0], has_proc)
-            vy = np.ascontiguousarray(np.asarray(validation_data[1]), dtype=np.float32).reshape(vimg.shape[0], -1)
-            val = (vimg, vproc, vy)
+            vimg, vproc = _as_inputs(validation_data[0], has_proc, cast=False)
+            vy = _as_targets(validation_data[1], vimg.shape[0], nc, cast=False)
+            eng.dataset_alloc(VAL, vimg.shape[0])
+            eng.dataset_write(VAL, 0, vimg, vproc, vy)
+            has_val = True
         cbs = list(callbacks or [])
         self.history = History()
         for cb in cbs + [self.history]:
             cb.set_model(self)
-        eng.set_dropout("philox" if self.cfg.drop_rate > 0 else "off", self.dropout_seed)
-        rng = np.random.default_rng(self.dropout_seed + 977)
-        n = img.shape[0]
+        eng.set_dropout("philox" if self.cfg.drop_rate > 0 else "off", self.dropout_seed)      # same seed: the step counter keeps running
+        per_sample = 4 * (self.cfg.image_h * self.cfg.image_w * self.cfg.in_chans + self.cfg.proc_dim + nc)
+        resident = n * per_sample <= self.resident_limit_bytes and epochs - initial_epoch > 1
+        filled = False
+        if resident:
+            try:
+                eng.dataset_alloc(TRAIN, n)
+            except Exception:
+                resident = False
         self.stop_training = False
-        for cb in cbs:
-            cb.on_train_begin()
-        for epoch in range(initial_epoch, epochs):
+        try:
             for cb in cbs:
-                cb.on_epoch_begin(epoch)
-            t0 = time.time()
-            order = rng.permutation(n) if shuffle else np.arange(n)
-            # one native call per epoch: the batch loop (last partial batch kept, as Keras does) runs inside the library with
-            # host->device copies double-buffered against the train steps
-            ei = np.ascontiguousarray(img[order]) if shuffle else img
-            ep = (np.ascontiguousarray(proc[order]) if shuffle else proc) if has_proc else None
-            ey = np.ascontiguousarray(yy[order]) if shuffle else yy
-            losses, maes = eng.train_epoch(ei, ep, ey, bs, float(self.optimizer.learning_rate))
-            counts = np.minimum(bs, n - bs * np.arange(len(losses)))
-            lsum = float(np.dot(losses.astype(np.float64), counts)); asum = float(np.dot(maes.astype(np.float64), counts))
-            logs = {"loss": lsum / n}
-            if "mae" in self.metrics_names:
-                logs["mae"] = asum / n
-            if val is not None:
-                vl, va = eng.evaluate(val[0], val[1], val[2])
-                logs["val_loss"] = vl
+                cb.on_train_begin()
+            for epoch in range(initial_epoch, epochs):
+                for cb in cbs:
+                    cb.on_epoch_begin(epoch)
+                t0 = time.time()
+                order = self._rng.permutation(n).astype(np.int32) if shuffle else None
+                lr = float(self.optimizer.learning_rate)
+                if resident and filled:
+                    losses, maes = eng.train_epoch_resident(TRAIN, order, bs, lr)
+                else:
+                    losses, maes = eng.train_epoch_stream(img, proc, yy, order, bs, lr, TRAIN if resident else -1)
+                    filled = resident
+                counts = np.minimum(bs, n - bs * np.arange(len(losses)))
+                lsum = float(np.dot(losses.astype(np.float64), counts)); asum = float(np.dot(maes.astype(np.float64), counts))
+                logs = {"loss": lsum / n}
                 if "mae" in self.metrics_names:
-                    logs["val_mae"] = va
+                    logs["mae"] = asum / n
+                if has_val:
+                    vl, va = eng.evaluate_resident(VAL)
+                    logs["val_loss"] = vl
+                    if "mae" in self.metrics_names:
+                        logs["val_mae"] = va
+                for cb in cbs:
+                    cb.on_epoch_end(epoch, logs)
+                self.history.on_epoch_end(epoch, logs)
+                if verbose:
+                    print("Epoch %d/%d - %.1fs - %s" % (epoch + 1, epochs, time.time() - t0,
+                                                        " - ".join("%s: %.4f" % kv for kv in logs.items())))
+                if self.stop_training:
+                    break
             for cb in cbs:
-                cb.on_epoch_end(epoch, logs)
-            self.history.on_epoch_end(epoch, logs)
-            if verbose:
-                print("Epoch %d/%d - %.1fs - %s" % (epoch + 1, epochs, time.time() - t0,
-                                                    " - ".join("%s: %.4f" % kv for kv in logs.items())))
-            if self.stop_training:
-                break
-        for cb in cbs:
-            cb.on_train_end()
+                cb.on_train_end()
+        finally:
+            if resident:
+                eng.dataset_free(TRAIN)
+            if has_val:
+                eng.dataset_free(VAL)
         return self.history
 
     def predict(self, x, batch_size=None, verbose=0, **kw):
-        img, proc = _as_inputs(x, self.cfg.proc_dim > 0)
+        img, proc = _as_inputs(x, self.cfg.proc_dim > 0, cast=False)
         # chunking by max_batch inside the library gives the same numbers as Keras' default batch 32 (inference has
         # no cross-sample coupling: BatchNorm uses its moving statistics)
         return self.engine.predict(img, proc)
 
     def evaluate(self, x=None, y=None, batch_size=None, verbose=0, return_dict=False, **kw):
-        img, proc = _as_inputs(x, self.cfg.proc_dim > 0)
-        yy = np.ascontiguousarray(np.asarray(y), dtype=np.float32).reshape(img.shape[0], -1)
+        img, proc = _as_inputs(x, self.cfg.proc_dim > 0, cast=False)
+        yy = _as_targets(y, img.shape[0], self.cfg.num_classes, cast=False)
         loss, mae = self.engine.evaluate(img, proc, yy)
         if return_dict:
             return {"loss": loss, "mae": mae}
@@ -376,23 +414,108 @@ class Model:
     def set_weights_dict(self, w: Dict[str, np.ndarray]):
         self.engine.set_params(w)
 
-    def save_weights(self, filepath, overwrite=True, **kw):
-        """Keras-2 `save_weights(path.h5)` stand-in.  The container is a flat name->array archive (numpy .npz layout) written to
-        exactly `filepath`; h5py is not available here, the Keras-H5 layout is listed under 'next' in DESIGN.md."""
+    def keras_layout(self):
+        """[(keras layer name, [(keras weight name, canonical name), ...])] in the order Keras-2 `save_weights` writes an .h5 file for
+        the model create_cvt_model builds: one entry per layer of model.layers (weight-less layers with an empty list), and inside a
+        layer `trainable_weights + non_trainable_weights`, i.e. sub-layers in the order their attributes are assigned in __init__
+        (models/CvT(Par).py:126-142,244-259) with the BatchNorm moving statistics LAST.  Keras' auto-numbered names
+        (dense_3, layer_normalization_6) depend on a process-global counter: readers match by position and shape, as Keras itself does."""
+        cfg = self.cfg
+        out = [("Image_inputs", [])]
+        dn = 0
+        for i, st in enumerate(cfg.stages, 1):
+            ce, t = "stage%d_ConvEmbed" % i, "stage%d_transformer" % i
+            out.append((ce, [(ce + "/conv2d/kernel:0", ce + "/kernel"), (ce + "/conv2d/bias:0", ce + "/bias")]))
+            tr, nt = [], []
+            if st.with_cls_token:
+                tr.append((t + "/cls_token:0", t + "/cls_token"))
+            tr += [(t + "/layer_normalization/gamma:0", t + "/norm1/gamma"), (t + "/layer_normalization/beta:0", t + "/norm1/beta")]
+            ca = t + "/conv_attention/"
+            if st.qkv_method == "dw_bn":
+                for b in "qkv":
+                    tr += [(ca + b + "_proj/depthwise_conv2d/depthwise_kernel:0", t + "/attn/%s_proj/depthwise_kernel" % b),
+                           (ca + b + "_proj/batch_normalization/gamma:0", t + "/attn/%s_proj/bn/gamma" % b),
+                           (ca + b + "_proj/batch_normalization/beta:0", t + "/attn/%s_proj/bn/beta" % b)]
+                    nt += [(ca + b + "_proj/batch_normalization/moving_mean:0", t + "/attn/%s_proj/bn/moving_mean" % b),
+                           (ca + b + "_proj/batch_normalization/moving_variance:0", t + "/attn/%s_proj/bn/moving_variance" % b)]
+            for b in "qkv":
+                d = "dense%s" % ("_%d" % dn if dn else ""); dn += 1
+                tr += [(ca + d + "/kernel:0", t + "/attn/proj_%s/kernel" % b), (ca + d + "/bias:0", t + "/attn/proj_%s/bias" % b)]
+            for b in ("query", "key", "value", "attention_output"):
+                tr += [(ca + "multi_head_attention/%s/kernel:0" % b, t + "/attn/mha/%s/kernel" % b),
+                       (ca + "multi_head_attention/%s/bias:0" % b, t + "/attn/mha/%s/bias" % b)]
+            d = "dense_%d" % dn; dn += 1
+            tr += [(ca + d + "/kernel:0", t + "/attn/proj/kernel"), (ca + d + "/bias:0", t + "/attn/proj/bias")]
+            for fc in ("fc1", "fc2"):
+                d = "dense_%d" % dn; dn += 1
+                tr += [(t + "/sequential/" + d + "/kernel:0", t + "/mlp/%s/kernel" % fc), (t + "/sequential/" + d + "/bias:0", t + "/mlp/%s/bias" % fc)]
+            out.append((t, tr + nt))
+        ln = "layer_normalization_%d" % len(cfg.stages)
+        if cfg.proc_dim > 0:
+            out.append(("Proc_inputs", []))
+        out.append((ln, [(ln + "/gamma:0", "head_norm/gamma"), (ln + "/beta:0", "head_norm/beta")]))
+        if cfg.proc_dim > 0:
+            for nm in ("Proc_Dense_1", "Proc_Dense_2"):
+                out.append((nm, [(nm + "/kernel:0", nm + "/kernel"), (nm + "/bias:0", nm + "/bias")]))
+            out.append(("concatenate", []))
+        out.append(("Final_Dense", [("Final_Dense/kernel:0", "Final_Dense/kernel"), ("Final_Dense/bias:0", "Final_Dense/bias")]))
+        return out
+
+    def save_weights(self, filepath, overwrite=True, save_format=None, **kw):
+        """Keras-2 `model.save_weights(path)` (models/CvT(Par).py:489).  `.h5` / `.hdf5` / `.keras` paths (or save_format='h5') get the
+        legacy Keras-2 HDF5 layout, written by h5lite (no h5py needed); any other path a flat name->array .npz archive."""
         if os.path.exists(filepath) and not overwrite:
             raise IOError("%s exists" % filepath)
         os.makedirs(os.path.dirname(os.path.abspath(filepath)), exist_ok=True)
         w = self.get_weights_dict()
+        if save_format in ("h5", "hdf5", "keras") or str(filepath).lower().endswith((".h5", ".hdf5", ".keras")):
+            h5lite.save_keras_weights(filepath, [(ln, [(kn, w[cn]) for kn, cn in ws]) for ln, ws in self.keras_layout()])
+            return
         with open(filepath, "wb") as f:
             np.savez(f, __format__=np.array("cvt_b200_weights_v1"), **{k.replace("/", "|"): v for k, v in w.items()})
 
+    def _weights_from_h5(self, filepath) -> Dict[str, np.ndarray]:
+        """Matches a Keras-2 weight file to this model the way Keras' load_weights_from_hdf5_group does: layer by layer (by layer name;
+        the anonymous head LayerNormalization by its position among the weighted layers), weights inside a layer by POSITION, every shape checked."""
+        infos = {p["name"]: p for p in self.engine.param_infos()}
+        saved = h5lite.load_keras_weights(filepath)
+        layout = [(ln, ws) for ln, ws in self.keras_layout() if ws]
+        filled = [(ln, ws) for ln, ws in saved.items() if ws]
+        if len(filled) != len(layout):
+            raise ValueError("Layer count mismatch when loading weights from file. Model expected %d layers, found %d saved layers."
+                             % (len(layout), len(filled)))
+        by_name = dict(filled)
+        out = {}
+        for k, (ln, ws) in enumerate(layout):
+            if ln in by_name:
+                fw = by_name[ln]
+            elif ln.startswith("layer_normalization"):
+                cands = [(n, v) for n, v in filled if n.startswith("layer_normalization")]
+                if len(cands) != 1:
+                    raise ValueError("cannot identify the head LayerNormalization among saved layers %s" % [n for n, _ in cands])
+                fw = cands[0][1]
+            else:
+                raise ValueError("saved weights have no layer named %s" % ln)
+            if len(fw) != len(ws):
+                raise ValueError("Weight count mismatch for layer #%d (named %s). Layer expects %d weight(s). Received %d saved weight(s)"
+                                 % (k, ln, len(ws), len(fw)))
+            for (kn, cn), (fn, arr) in zip(ws, fw):
+                want = tuple(infos[cn]["shape"])
+                if tuple(arr.shape) != want:
+                    raise ValueError("Shape mismatch in layer #%d (named %s) for weight %s. Weight expects shape %s. Received saved weight "
+                                     "%s with shape %s" % (k, ln, kn, want, fn, tuple(arr.shape)))
+                out[cn] = np.asarray(arr, dtype=np.float32)
+        return out
+
     def load_weights(self, filepath, **kw):
+        """Keras-2 `model.load_weights(path)` (models/CvT_test(Par).py:513): HDF5 files (ours or Keras' own) and the .npz archive."""
         if not os.path.exists(filepath):
             raise FileNotFoundError("Unable to open file (unable to open file: name = '%s')" % filepath)
         with open(filepath, "rb") as f:
             magic = f.read(8)
-        if magic.startswith(b"\x89HDF"):
-            raise NotImplementedError("Keras-2 HDF5 weight files need h5py, which is not available here (DESIGN.md, 'next')")
+        if magic == h5lite.SIGNATURE:
+            self.engine.set_params(self._weights_from_h5(filepath))
+            return
         z = np.load(filepath, allow_pickle=False)
         w = {k.replace("|", "/"): z[k] for k in z.files if k != "__format__"}
         infos = {p["name"]: p for p in self.engine.param_infos()}
@@ -444,18 +567,33 @@ def make_gradcam_heatmap(img_array, proc_array, model: Model, last_conv_layer_na
 
 
 def save_predictions_to_excel(predictions, actual, train_num, test_num, r2, mse, mae, path):
-    """The xlsx contract tools/Compare_r.py:21-24 and tools/Compare_plot.py:13-26 read (writer: models/CvT_test(Par).py:440-477).
-    Written as .xlsx when openpyxl is importable, else as .csv with the same columns."""
-    import pandas as pd
-    predictions = np.asarray(predictions).flatten(); actual = np.asarray(actual).flatten()
-    df = pd.DataFrame({"Predictions": predictions, "Actual": actual, "Errors(%)": np.abs(predictions - actual) / actual * 100})
-    met = pd.DataFrame({"Train mounts": [train_num], "Test mounts": [test_num], "R2 Score": [r2], "MSE": [mse], "MAE": [mae]})
-    out = pd.concat([df, met], axis=1)
-    try:
-        import openpyxl  # noqa: F401
-        out.to_excel(path, index=False)
-        return path
-    except ImportError:
-        path = os.path.splitext(path)[0] + ".csv"
-        out.to_csv(path, index=False)
-        return path
+    """The sheet tools/Compare_r.py:21-24 and tools/Compare_plot.py:13-26 read (writer: models/CvT_test(Par).py:440-477): columns
+    Predictions, Actual, Errors(%), then Train mounts, Test mounts, R2 Score, MSE, MAE filled in the first row only.  Written as a
+    real .xlsx by xlsxlite (pandas' own writer needs openpyxl)."""
+    from . import xlsxlite
+    predictions = np.asarray(predictions, dtype=np.float64).flatten(); actual = np.asarray(actual, dtype=np.float64).flatten()
+    cols = {"Predictions": predictions.tolist(), "Actual": actual.tolist(), "Errors(%)": (np.abs(predictions - actual) / actual * 100).tolist(),
+            "Train mounts": [train_num], "Test mounts": [test_num], "R2 Score": [float(r2)], "MSE": [float(mse)], "MAE": [float(mae)]}
+    os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
+    xlsxlite.write_xlsx(path, cols)
+    return path
+
+
+def save_history_to_excel(history, path):
+    """models/CvT(Par).py:492-494: `pd.DataFrame(model.history.history)` with an `epoch` column (1-based) in front, index=False."""
+    from . import xlsxlite
+    h = history.history if hasattr(history, "history") else dict(history)
+    n = max([len(v) for v in h.values()] + [0])
+    cols = {"epoch": list(range(1, n + 1))}
+    cols.update({k: [float(x) for x in v] for k, v in h.items()})
+    os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
+    xlsxlite.write_xlsx(path, cols)
+    return path
+
+
+def regression_metrics(y_true, y_pred):
+    """sklearn's r2_score / mean_squared_error / mean_absolute_error as models/CvT_test(Par).py:525-527 calls them (single output)."""
+    t = np.asarray(y_true, dtype=np.float64).flatten(); p = np.asarray(y_pred, dtype=np.float64).flatten()
+    ss_res = float(((t - p) ** 2).sum()); ss_tot = float(((t - t.mean()) ** 2).sum())
+    r2 = 1.0 - ss_res / ss_tot if ss_tot > 0 else (1.0 if ss_res == 0 else 0.0)
+    return r2, float(((t - p) ** 2).mean()), float(np.abs(t - p).mean())
