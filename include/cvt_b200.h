@@ -32,7 +32,7 @@ extern "C" {
 
 #define CVT_MAX_STAGES 4
 #define CVT_DATASET_SLOTS 4
-#define CVT_ABI_VERSION 2
+#define CVT_ABI_VERSION 3
 
 typedef enum {
   CVT_OK = 0,
@@ -43,10 +43,13 @@ typedef enum {
   CVT_ERR_NCCL = -5
 } cvt_status;
 
-/* qkv_method of a stage — Projection.__init__, models/CvT(Par).py:92-100 */
-enum { CVT_PROJ_DW_BN = 0, CVT_PROJ_AVG = 1, CVT_PROJ_LINEAR = 2 };
-/* head of create_cvt_model, models/CvT(Par).py:326-337 */
-enum { CVT_HEAD_CLS_LN = 0, CVT_HEAD_LN_MEAN = 1 };
+/* qkv_method of a stage — Projection.__init__, models/CvT(Par).py:92-100; LINEAR is the identity there (self.proj = None, :101),
+ * LINEAR_DENSE is the Dense(dim) of the Grad-CAM script's Projection (tools/grad_cam_CvT.py:103-104,117) */
+enum { CVT_PROJ_DW_BN = 0, CVT_PROJ_AVG = 1, CVT_PROJ_LINEAR = 2, CVT_PROJ_LINEAR_DENSE = 3 };
+/* head of create_cvt_model.  AUTO = models/CvT(Par).py:326-337 (LayerNorm of the cls token when the last stage has one, else
+ * LayerNorm + mean over the tokens); CLS / MEAN = the un-normalised heads of tools/model_plot.py:289-292; MEAN is also the
+ * GlobalAveragePooling2D head of tools/grad_cam_CvT.py:336 (the cls token, if any, is dropped first) */
+enum { CVT_HEAD_AUTO = 0, CVT_HEAD_CLS_LN = 1, CVT_HEAD_LN_MEAN = 2, CVT_HEAD_CLS = 3, CVT_HEAD_MEAN = 4 };
 /* arithmetic of the dense contractions */
 enum { CVT_PREC_FP32 = 0,   /* fp32 FFMA everywhere (exact-parity mode) */
        CVT_PREC_TF32 = 1,   /* tcgen05 kind::tf32, fp32 accumulate in TMEM (what TF does on sm_80+) */
@@ -61,7 +64,8 @@ typedef struct {
   int32_t stride;         /* ConvEmbed stride (4 / 2 / 2) */
   int32_t num_heads;      /* embed_dim / 64 */
   int32_t qkv_method;     /* CVT_PROJ_* */
-  int32_t with_cls_token; /* 0/1; only honoured on the last stage (as in the reference) */
+  int32_t with_cls_token; /* 0/1 per stage: models/CvT(Par).py sets it on the last stage only, tools/grad_cam_CvT.py:324-332 on every
+                             stage (the token is concatenated at block entry and split off again at block exit, :264-268,283-286) */
 } cvt_stage_config;
 
 /* Mirrors the module-level constants + `spec` that create_cvt_model reads, models/CvT(Par).py:25-72,292 */
@@ -80,6 +84,10 @@ typedef struct {
   int32_t precision;                      /* CVT_PREC_* */
   int32_t max_batch;                      /* largest per-call batch; bigger host batches are chunked */
   int32_t device;                         /* CUDA ordinal */
+  /* variants of the tools/ scripts; all-zero = models/CvT(Par).py */
+  int32_t head_kind;                      /* CVT_HEAD_* */
+  int32_t skip_proj_qkv;                  /* 1: proj_q/k/v are not applied and own no weights (tools/grad_cam_CvT.py:146-149 vs :168-201) */
+  float   attn_drop_rate;                 /* > 0: Dropout on the MultiHeadAttention output before self.proj (tools/grad_cam_CvT.py:200) */
 } cvt_config;
 
 typedef struct cvt_model cvt_model;

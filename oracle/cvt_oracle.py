@@ -50,7 +50,7 @@ class StageSpec:
     num_heads: int
     kernel_size: int = 3
     strides: int = 1
-    qkv_method: str = "dw_bn"          # dw_bn | avg | linear
+    qkv_method: str = "dw_bn"          # dw_bn | avg | linear (identity, models/CvT(Par).py:101) | linear_dense (Dense(dim), tools/grad_cam_CvT.py:103)
     with_cls_token: bool = False
 
 
@@ -68,9 +68,16 @@ class CvtSpec:
     bn_eps: float = 1e-3
     bn_momentum: float = 0.99
     proc_hidden: int = 256
+    # variants of the tools/ scripts; the defaults are models/CvT(Par).py
+    head: str = "auto"                  # auto | cls_ln | ln_mean (models/CvT(Par).py:325-337) | cls | mean (tools/model_plot.py:289-292;
+                                        #   "mean" is also GlobalAveragePooling2D, tools/grad_cam_CvT.py:336)
+    apply_proj_qkv: bool = True         # False: proj_q/k/v are built but never called (tools/grad_cam_CvT.py:146-149 vs :168-201)
+    attn_drop_rate: float = 0.0         # > 0: Dropout on the MultiHeadAttention output before self.proj (tools/grad_cam_CvT.py:200)
 
     @property
     def head_kind(self) -> str:
+        if self.head != "auto":
+            return self.head
         return "cls_ln" if self.stages[-1].with_cls_token else "ln_mean"
 
 
@@ -84,6 +91,18 @@ def ref_spec(projection_method: str = "dw_bn", cls_token_switch: bool = True, pr
         StageSpec(dims[2], 3, 2, heads[2], 3, 1, projection_method, cls_token_switch),
     ]
     return CvtSpec(image_h, image_w, 1, st, proc_dim, num_classes)
+
+
+def gradcam_spec(cls_token_switch: bool = False, projection_method: str = "dw_bn", **kw) -> CvtSpec:
+    """The model tools/grad_cam_CvT.py:315-349 builds: cls token (when switched on) on EVERY stage and dropped after each block,
+    proj_q/k/v never applied, attention-output dropout, `linear` = Dense(dim), GlobalAveragePooling2D head without LayerNorm."""
+    spec = ref_spec(projection_method, cls_token_switch, **kw)
+    for st in spec.stages:
+        st.with_cls_token = cls_token_switch
+        if projection_method == "linear":
+            st.qkv_method = "linear_dense"
+    spec.head, spec.apply_proj_qkv, spec.attn_drop_rate = "mean", False, 0.1
+    return spec
 
 
 def wide_spec(**kw) -> CvtSpec:
@@ -137,8 +156,12 @@ def param_specs(spec: CvtSpec) -> List[Tuple[str, Tuple[int, ...], bool]]:
                         (f"{t}/attn/{b}_proj/bn/beta", (d,), True),
                         (f"{t}/attn/{b}_proj/bn/moving_mean", (d,), False),
                         (f"{t}/attn/{b}_proj/bn/moving_variance", (d,), False)]
-        for b in "qkv":
-            out += [(f"{t}/attn/proj_{b}/kernel", (d, d), True), (f"{t}/attn/proj_{b}/bias", (d,), True)]
+        if st.qkv_method == "linear_dense":
+            for b in "qkv":
+                out += [(f"{t}/attn/{b}_proj/dense/kernel", (d, d), True), (f"{t}/attn/{b}_proj/dense/bias", (d,), True)]
+        if spec.apply_proj_qkv:
+            for b in "qkv":
+                out += [(f"{t}/attn/proj_{b}/kernel", (d, d), True), (f"{t}/attn/proj_{b}/bias", (d,), True)]
         for b in ("query", "key", "value"):
             out += [(f"{t}/attn/mha/{b}/kernel", (d, n, hd), True), (f"{t}/attn/mha/{b}/bias", (n, hd), True)]
         out += [(f"{t}/attn/mha/attention_output/kernel", (n, hd, d), True),
@@ -148,7 +171,8 @@ def param_specs(spec: CvtSpec) -> List[Tuple[str, Tuple[int, ...], bool]]:
                 (f"{t}/mlp/fc2/kernel", (spec.mlp_ratio * d, d), True), (f"{t}/mlp/fc2/bias", (d,), True)]
         cin = d
     d = spec.stages[-1].embed_dim
-    out += [("head_norm/gamma", (d,), True), ("head_norm/beta", (d,), True)]
+    if spec.head_kind in ("cls_ln", "ln_mean"):
+        out += [("head_norm/gamma", (d,), True), ("head_norm/beta", (d,), True)]
     feat = d
     if spec.proc_dim > 0:
         out += [("Proc_Dense_1/kernel", (spec.proc_dim, spec.proc_hidden), True), ("Proc_Dense_1/bias", (spec.proc_hidden,), True),
@@ -242,6 +266,8 @@ def make_dropout_masks(spec: CvtSpec, batch: int, seed: int, step: int) -> Dict[
         d, tc = g["d"], g["tc"]
         for j, (nm, width) in enumerate((("proj", d), ("mlp1", spec.mlp_ratio * d), ("mlp2", d))):
             masks[f"s{i + 1}.{nm}"] = dropout_mask(batch * tc * width, spec.drop_rate, seed, step, i * 4 + j).reshape(batch, tc, width)
+        if spec.attn_drop_rate > 0.0:                                # site 3: attention-output dropout of the grad-cam variant
+            masks[f"s{i + 1}.attn"] = dropout_mask(batch * tc * d, spec.attn_drop_rate, seed, step, i * 4 + 3).reshape(batch, tc, d)
     return masks
 
 
@@ -369,13 +395,18 @@ def forward_torch(spec: CvtSpec, P: Dict[str, torch.Tensor], img: torch.Tensor, 
                 convs.append(c.reshape(bsz, h * w, d))
             elif method == "avg":
                 y = avgpool3x3_same(sp)
+            elif method == "linear_dense":                           # tools/grad_cam_CvT.py:103,117
+                y = sp @ P[f"{t}/attn/{b}_proj/dense/kernel"] + P[f"{t}/attn/{b}_proj/dense/bias"]
             else:
                 y = sp
             y = y.reshape(bsz, h * w, d)
             if cls_n is not None:
                 y = torch.cat([cls_n, y], dim=1)                     # :168-170 (cls bypasses conv/BN)
             qkv0.append(y)
-        qkv1 = [qkv0[j] @ P[f"{t}/attn/proj_{b}/kernel"] + P[f"{t}/attn/proj_{b}/bias"] for j, b in enumerate("qkv")]  # :180-182
+        if spec.apply_proj_qkv:
+            qkv1 = [qkv0[j] @ P[f"{t}/attn/proj_{b}/kernel"] + P[f"{t}/attn/proj_{b}/bias"] for j, b in enumerate("qkv")]  # :180-182
+        else:
+            qkv1 = list(qkv0)                                        # tools/grad_cam_CvT.py:199 (q, k, v go straight into the attention)
         # keras MultiHeadAttention(num_heads, key_dim), called (query=q, value=v, key=k)  :185
         def heads(z, nm):
             return torch.einsum("btd,dnh->btnh", z, P[f"{t}/attn/mha/{nm}/kernel"]) + P[f"{t}/attn/mha/{nm}/bias"]
@@ -386,6 +417,8 @@ def forward_torch(spec: CvtSpec, P: Dict[str, torch.Tensor], img: torch.Tensor, 
         Pm = torch.softmax(S, dim=-1)
         O = torch.einsum("bnts,bsnh->btnh", Pm, V)
         a1 = torch.einsum("btnh,nhd->btd", O, P[f"{t}/attn/mha/attention_output/kernel"]) + P[f"{t}/attn/mha/attention_output/bias"]
+        if spec.attn_drop_rate > 0.0:                                                         # tools/grad_cam_CvT.py:200
+            a1 = _apply_dropout(a1, masks.get(f"s{i}.attn") if masks else None, spec.attn_drop_rate, training)
         a2 = a1 @ P[f"{t}/attn/proj/kernel"] + P[f"{t}/attn/proj/bias"]                      # :188
         a2 = _apply_dropout(a2, masks.get(f"s{i}.proj") if masks else None, rate, training)   # :189
         x1 = a2 + x0                                                                          # :274
@@ -410,11 +443,19 @@ def forward_torch(spec: CvtSpec, P: Dict[str, torch.Tensor], img: torch.Tensor, 
             if convs:
                 taps[s + "conv_qkv"] = torch.stack(convs)
     # head  models/CvT(Par).py:325-350
-    hg, hb = P["head_norm/gamma"], P["head_norm/beta"]
-    if spec.stages[-1].with_cls_token:
-        feat = layer_norm(cls_out, hg, hb, spec.ln_eps).squeeze(1)
+    hk = spec.head_kind
+    if hk in ("cls_ln", "cls") and cls_out is None:
+        raise ValueError("head '%s' needs a cls token on the last stage" % hk)
+    if hk == "cls_ln":
+        feat = layer_norm(cls_out, P["head_norm/gamma"], P["head_norm/beta"], spec.ln_eps).squeeze(1)
+    elif hk == "ln_mean":
+        feat = layer_norm(x.reshape(bsz, -1, x.shape[-1]), P["head_norm/gamma"], P["head_norm/beta"], spec.ln_eps).mean(dim=1)
+    elif hk == "cls":                                                # tools/model_plot.py:289-290
+        feat = cls_out.squeeze(1)
+    elif hk == "mean":                                               # tools/model_plot.py:291-292, tools/grad_cam_CvT.py:336 (GAP)
+        feat = x.reshape(bsz, -1, x.shape[-1]).mean(dim=1)
     else:
-        feat = layer_norm(x.reshape(bsz, -1, x.shape[-1]), hg, hb, spec.ln_eps).mean(dim=1)
+        raise ValueError("unknown head kind %r" % hk)
     if spec.proc_dim > 0:
         p1 = torch.relu(proc @ P["Proc_Dense_1/kernel"] + P["Proc_Dense_1/bias"])
         p2 = torch.relu(p1 @ P["Proc_Dense_2/kernel"] + P["Proc_Dense_2/bias"])

@@ -29,7 +29,7 @@ def test_header_symbols_are_exported_and_bound(lib):
     for n in names:
         assert hasattr(handle, n), "library does not export %s" % n
     assert set(names) == set(lib.exported_names()), set(names) ^ set(lib.exported_names())
-    assert lib.load().cvt_abi_version() == lib.ABI_VERSION == 2
+    assert lib.load().cvt_abi_version() == lib.ABI_VERSION == 3
 
 
 def test_default_config_is_the_reference_spec(lib):

@@ -49,3 +49,24 @@ def test_flash_attention_forward_backward(B, T, heads):
     rO, rL, rQ, rK, rV = ref_attention(Q, K, V, dO, heads)
     errs = dict(O=rel(O, rO), LSE=rel(LSE, rL), dQ=rel(dQ, rQ), dK=rel(dK, rK), dV=rel(dV, rV))
     assert all(e < 2e-3 for e in errs.values()), errs
+
+
+@pytest.mark.parametrize("B,T,heads", [(64, 1024, 1), (64, 256, 2), (64, 65, 4), (160, 1024, 1)])
+def test_flash_attention_many_ctas_per_sm(B, T, heads):
+    """Grids of several hundred CTAs (two forward CTAs share an SM and its tensor pipe, several waves): the shapes of the benched batch-64
+    step.  Every image carries the same Q/K/V/dO, so each must reproduce the fp64 result of image 0.  Round 2 found a race here that the
+    small-grid cases above cannot see: a forward row warp read O before the last two PV products had landed."""
+    lib = _lib.load()
+    D = heads * 64
+    rng = np.random.default_rng(T + heads)
+    one = [(s * rng.standard_normal((1, T, D))).astype(np.float32) for s in (0.25, 2.0, 1.0, 1.0)]
+    rO, rL, rQ, rK, rV = ref_attention(*one, heads)
+    Q, K, V, dO = (np.ascontiguousarray(np.repeat(a, B, 0)) for a in one)
+    O = np.zeros_like(Q); dQ = np.zeros_like(Q); dK = np.zeros_like(Q); dV = np.zeros_like(Q)
+    LSE = np.zeros((B * heads, T), np.float32)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    for rep in range(3):
+        _lib.check(lib.cvt_debug_attention(B, T, heads, p(Q), p(K), p(V), p(dO), p(O), p(LSE), p(dQ), p(dK), p(dV)), "cvt_debug_attention")
+        for name, got, ref in (("O", O, rO), ("dQ", dQ, rQ), ("dK", dK, rK), ("dV", dV, rV)):
+            worst = max(rel(got[b], ref[0]) for b in range(B))
+            assert worst < 2e-3, (name, rep, worst)

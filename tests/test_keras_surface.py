@@ -198,12 +198,15 @@ def test_script_sequence_tf32_52_epochs_gpu(tmp_path):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("cls", [True, False])
-def test_gradcam_heatmap_gpu(cls):
-    K.configure(projection="dw_bn", cls_token=cls)
+@pytest.mark.parametrize("variant,cls", [("reference", False), ("gradcam", False), ("gradcam", True), ("model_plot", False)])
+def test_gradcam_heatmap_gpu(variant, cls):
+    """make_gradcam_heatmap (tools/grad_cam_CvT.py:422-481) on the models the tools build (configure(variant=...)) against oracle.gradcam."""
+    K.configure(projection="dw_bn", cls_token=cls, variant=variant)
     try:
         m = K.create_cvt_model(H, W, 1, 5, 1, precision="fp32", max_batch=2, seed=4)
-        spec = O.ref_spec("dw_bn", cls, 5, 1, H, W)
+        spec = O.gradcam_spec(cls, "dw_bn", image_h=H, image_w=W) if variant == "gradcam" else O.ref_spec("dw_bn", cls, 5, 1, H, W)
+        if variant == "model_plot":
+            spec.head = "mean"
         params = O.init_params(spec, 9, "parity")
         m.set_weights_dict(params)
         x, p, _ = _data(3, 8)
@@ -213,4 +216,16 @@ def test_gradcam_heatmap_gpu(cls):
             np.testing.assert_allclose(heat[i], ref[0], rtol=2e-3, atol=2e-4)
         m.close()
     finally:
-        K.configure(projection="dw_bn", cls_token=True)
+        K.configure(projection="dw_bn", cls_token=True, variant="reference")
+
+
+@pytest.mark.gpu
+def test_gradcam_on_the_cls_head_fails_like_the_reference():
+    """With the cls-token head of models/CvT(Par).py:326-329 the prediction never reads the spatial map: tape.gradient returns None in the
+    reference (tools/grad_cam_CvT.py:454 then raises); here the zero gradient is reported instead of a NaN heat-map."""
+    K.configure(projection="dw_bn", cls_token=True, variant="reference")
+    m = K.create_cvt_model(H, W, 1, 5, 1, precision="fp32", max_batch=2, seed=4)
+    x, p, _ = _data(2, 8)
+    with pytest.raises(ValueError, match="No gradients"):
+        K.make_gradcam_heatmap(x, p, m, "stage3_transformer")
+    m.close()

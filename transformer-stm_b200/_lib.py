@@ -6,9 +6,10 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "csrc", "libcvt_b200.so")
 MAX_STAGES = 4
 DATASET_SLOTS = 4
-ABI_VERSION = 2
+ABI_VERSION = 3
 
-PROJ = {"dw_bn": 0, "avg": 1, "linear": 2}
+PROJ = {"dw_bn": 0, "avg": 1, "linear": 2, "linear_dense": 3}
+HEAD = {"auto": 0, "cls_ln": 1, "ln_mean": 2, "cls": 3, "mean": 4, "gap": 4}
 PREC = {"fp32": 0, "tf32": 1, "bf16": 2}
 DROPOUT_OFF, DROPOUT_PHILOX, DROPOUT_MASKS = 0, 1, 2
 
@@ -23,7 +24,8 @@ class Config(C.Structure):
                 ("stage", StageConfig * MAX_STAGES),
                 ("proc_dim", C.c_int32), ("proc_hidden", C.c_int32), ("num_classes", C.c_int32), ("mlp_ratio", C.c_int32),
                 ("drop_rate", C.c_float), ("ln_eps", C.c_float), ("bn_eps", C.c_float), ("bn_momentum", C.c_float),
-                ("precision", C.c_int32), ("max_batch", C.c_int32), ("device", C.c_int32)]
+                ("precision", C.c_int32), ("max_batch", C.c_int32), ("device", C.c_int32),
+                ("head_kind", C.c_int32), ("skip_proj_qkv", C.c_int32), ("attn_drop_rate", C.c_float)]
 
 
 class HostArrays(C.Structure):

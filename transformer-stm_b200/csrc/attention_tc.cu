@@ -97,7 +97,7 @@ __device__ __forceinline__ float4 out4(const uint32_t* v, float sc, int round) {
 // =====================================================================================================================
 constexpr int FWD_THREADS = 192;
 constexpr int FWD_SMEM = 1024 + TILE32K + 4 * TILE16K + 128;
-enum { FB_Q = 0, FB_KF = 1, FB_KE = 3, FB_VF = 5, FB_VE = 7, FB_SF = 9, FB_PF = 11, FB_PV = 13, FB_COUNT = 14 };
+enum { FB_Q = 0, FB_KF = 1, FB_KE = 3, FB_VF = 5, FB_VE = 7, FB_SF = 9, FB_PF = 11, FB_PV = 13, FB_DONE = 14, FB_COUNT = 15 };
 
 __global__ void __launch_bounds__(FWD_THREADS, 2) attn_fwd_kernel(const __grid_constant__ AttnP p, const __grid_constant__ CUtensorMap tmQ,
                                                                    const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV) {
@@ -169,6 +169,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 2) attn_fwd_kernel(const __grid_c
         mma_tmn(tmem + 128, tmem + st * 64, dV[st], idesc_o, j > 0);
         mma_commit(&bars[FB_VE + st]);
         mma_commit(&bars[FB_PV]);
+        if (j == ntiles - 1) mma_commit(&bars[FB_DONE]);
       }
       __syncwarp();
     }
@@ -228,7 +229,10 @@ __global__ void __launch_bounds__(FWD_THREADS, 2) attn_fwd_kernel(const __grid_c
       tc_fence_before();
       mbar_arrive(&bars[FB_PF + st]);
     }
-    mbar_wait(&bars[FB_PV], (ntiles - 1) & 1);
+    // A barrier of its own for "the last PV product has landed": a row warp that never rescaled has not followed FB_PV, whose one-bit
+    // phase parity cannot tell "PV_{n-1} done" from "PV_{n-3} done" - with two CTAs sharing the tensor pipe a fast warp got here while
+    // PV_{n-2} was still in flight and read O two tiles short (found by the batch-64 parity test; 1 CTA per SM never showed it).
+    mbar_wait(&bars[FB_DONE], 0);
     tc_fence_after();
     const int q = q0 + quad * 32 + lane;
     const float inv = 1.f / l_run;

@@ -172,8 +172,16 @@ static void build_params(Model* m) {
       for (int z = 0; z < 3; ++z) { int64_t o = add_param(m, t + "/attn/" + qkv[z] + "_proj/bn/moving_mean", {D}, false); if (z == 0) w.bn_mm = o; }
       for (int z = 0; z < 3; ++z) { int64_t o = add_param(m, t + "/attn/" + qkv[z] + "_proj/bn/moving_variance", {D}, false); if (z == 0) w.bn_mv = o; }
     }
-    for (int z = 0; z < 3; ++z) { int64_t o = add_param(m, t + "/attn/proj_" + qkv[z] + "/kernel", {D, D}, true); if (z == 0) w.pw = o; }
-    for (int z = 0; z < 3; ++z) { int64_t o = add_param(m, t + "/attn/proj_" + qkv[z] + "/bias", {D}, true); if (z == 0) w.pb = o; }
+    w.lw = w.lb = -1;
+    if (g.method == CVT_PROJ_LINEAR_DENSE) {      // Projection(method='linear') of tools/grad_cam_CvT.py:103-104: Dense(dim)
+      for (int z = 0; z < 3; ++z) { int64_t o = add_param(m, t + "/attn/" + qkv[z] + "_proj/dense/kernel", {D, D}, true); if (z == 0) w.lw = o; }
+      for (int z = 0; z < 3; ++z) { int64_t o = add_param(m, t + "/attn/" + qkv[z] + "_proj/dense/bias", {D}, true); if (z == 0) w.lb = o; }
+    }
+    w.pw = w.pb = -1;
+    if (!c.skip_proj_qkv) {                       // tools/grad_cam_CvT.py builds proj_q/k/v but never calls them: no weights
+      for (int z = 0; z < 3; ++z) { int64_t o = add_param(m, t + "/attn/proj_" + qkv[z] + "/kernel", {D, D}, true); if (z == 0) w.pw = o; }
+      for (int z = 0; z < 3; ++z) { int64_t o = add_param(m, t + "/attn/proj_" + qkv[z] + "/bias", {D}, true); if (z == 0) w.pb = o; }
+    }
     const char* mh[3] = {"query", "key", "value"};
     for (int z = 0; z < 3; ++z) { int64_t o = add_param(m, t + "/attn/mha/" + mh[z] + "/kernel", {D, N, hd}, true); if (z == 0) w.mw = o; }
     for (int z = 0; z < 3; ++z) { int64_t o = add_param(m, t + "/attn/mha/" + mh[z] + "/bias", {N, hd}, true); if (z == 0) w.mb = o; }
@@ -188,8 +196,11 @@ static void build_params(Model* m) {
     cin = (int)D;
   }
   const int64_t D = m->d_last;
-  m->hn_g = add_param(m, "head_norm/gamma", {D}, true);
-  m->hn_b = add_param(m, "head_norm/beta", {D}, true);
+  m->hn_g = m->hn_b = -1;
+  if (m->head_kind == CVT_HEAD_CLS_LN || m->head_kind == CVT_HEAD_LN_MEAN) {
+    m->hn_g = add_param(m, "head_norm/gamma", {D}, true);
+    m->hn_b = add_param(m, "head_norm/beta", {D}, true);
+  }
   if (c.proc_dim > 0) {
     m->pd1w = add_param(m, "Proc_Dense_1/kernel", {c.proc_dim, c.proc_hidden}, true);
     m->pd1b = add_param(m, "Proc_Dense_1/bias", {c.proc_hidden}, true);
@@ -237,6 +248,7 @@ static void carve(Model* m, Bump& b) {
     s.scores = need_scores ? b.take<float>(S) : nullptr;
     s.lse = b.take<float>(MB * g.heads * (int64_t)g.Tc);
     s.mask_proj = b.take<uint8_t>(RD); s.mask1 = b.take<uint8_t>(RH); s.mask2 = b.take<uint8_t>(RD);
+    s.mask_attn = c.attn_drop_rate > 0.f ? b.take<uint8_t>(RD) : nullptr;
   }
   const StageGeo& gl = m->geo[m->n_stages - 1];
   m->feat = b.take<float>(MB * m->feat_dim);
@@ -323,9 +335,13 @@ int cvt_create(const cvt_config* cfg, cvt_model** out) {
     if (s.embed_dim < 64 || s.embed_dim % 64 != 0 || s.embed_dim > 512 || s.num_heads * 64 != s.embed_dim) {
       set_error("cvt_create: embed_dim must be a multiple of 64 (<= 512) with num_heads = embed_dim / 64 (key_dim 64)"); return CVT_ERR_INVALID;
     }
-    if (s.patch_size < 1 || s.stride < 1 || s.qkv_method < 0 || s.qkv_method > 2) { set_error("cvt_create: bad stage spec"); return CVT_ERR_INVALID; }
-    if (s.with_cls_token && i != c.n_stages - 1) { set_error("cvt_create: cls token is supported on the last stage only"); return CVT_ERR_INVALID; }
+    if (s.patch_size < 1 || s.stride < 1 || s.qkv_method < 0 || s.qkv_method > CVT_PROJ_LINEAR_DENSE) { set_error("cvt_create: bad stage spec"); return CVT_ERR_INVALID; }
   }
+  if (c.head_kind < CVT_HEAD_AUTO || c.head_kind > CVT_HEAD_MEAN) { set_error("cvt_create: unknown head_kind"); return CVT_ERR_INVALID; }
+  if ((c.head_kind == CVT_HEAD_CLS_LN || c.head_kind == CVT_HEAD_CLS) && !c.stage[c.n_stages - 1].with_cls_token) {
+    set_error("cvt_create: a cls head needs with_cls_token on the last stage"); return CVT_ERR_INVALID;
+  }
+  if (c.attn_drop_rate < 0.f || c.attn_drop_rate >= 1.f) { set_error("cvt_create: attn_drop_rate must be in [0,1)"); return CVT_ERR_INVALID; }
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= c.device) {
     (void)cudaGetLastError();
@@ -355,12 +371,16 @@ int cvt_create(const cvt_config* cfg, cvt_model** out) {
     hh = g.H; ww = g.W; cin = g.D;
   }
   m->d_last = m->geo[c.n_stages - 1].D;
-  m->head_kind = m->geo[c.n_stages - 1].has_cls ? CVT_HEAD_CLS_LN : CVT_HEAD_LN_MEAN;
+  m->head_kind = c.head_kind != CVT_HEAD_AUTO ? c.head_kind : (m->geo[c.n_stages - 1].has_cls ? CVT_HEAD_CLS_LN : CVT_HEAD_LN_MEAN);
   m->feat_dim = m->d_last + (c.proc_dim > 0 ? c.proc_hidden : 0);
   build_params(m);
 
   {  // folded-weight scratch layout (TF32 / BF16 modes only)
-    m->folded = c.precision != CVT_PREC_FP32 && getenv("CVT_NO_FOLD") == nullptr;
+    // the Grad-CAM script's variants (no proj_q/k/v, dropout between attention_output and proj, Dense projections) break the
+    // "two stacked affine maps" algebra the folding relies on: those models run the layer-by-layer path
+    bool variant = c.skip_proj_qkv != 0 || c.attn_drop_rate > 0.f;
+    for (int i = 0; i < c.n_stages; ++i) variant = variant || c.stage[i].qkv_method == CVT_PROJ_LINEAR_DENSE;
+    m->folded = c.precision != CVT_PREC_FP32 && getenv("CVT_NO_FOLD") == nullptr && !variant;
     if (getenv("CVT_NO_GRAPH")) m->use_graphs = 0;
     int64_t f = 0, zc = 0, pt_extra = 0;
     auto al = [](int64_t v) { return (v + 63) / 64 * 64; };
@@ -392,7 +412,7 @@ int cvt_create(const cvt_config* cfg, cvt_model** out) {
     for (int i = 0; i < m->n_stages; ++i) {
       const StageW& w = m->w[i]; const int D = m->geo[i].D, H4 = c.mlp_ratio * D;
       if (!m->folded) {
-        for (int z = 0; z < 3; ++z) { add(w.pw + (int64_t)z * D * D, D, D); add(w.mw + (int64_t)z * D * D, D, D); }
+        for (int z = 0; z < 3; ++z) { if (w.pw >= 0) add(w.pw + (int64_t)z * D * D, D, D); add(w.mw + (int64_t)z * D * D, D, D); if (w.lw >= 0) add(w.lw + (int64_t)z * D * D, D, D); }
         add(w.ow, D, D); add(w.prw, D, D);
       }
       add(w.f1w, D, H4, 1); add(w.f2w, H4, D, 1);
@@ -550,10 +570,10 @@ static bool inline_philox(const Model* m) {
   for (int i = 0; i < m->n_stages; ++i) if (m->geo[i].D % 64 != 0) return false;
   return true;
 }
-static void epi_dropout(const Model* m, GemmP& q, uint8_t* mask, int site, float keep_scale) {
+static void epi_dropout(const Model* m, GemmP& q, uint8_t* mask, int site, float keep_scale, float rate = -1.f) {
   q.epi |= EPI_MASK; q.mask = mask; q.mask_scale = keep_scale;
   if (inline_philox(m)) {
-    const double t = (double)m->cfg.drop_rate * 4294967296.0;
+    const double t = (double)(rate >= 0.f ? rate : m->cfg.drop_rate) * 4294967296.0;
     q.epi |= EPI_PHILOX; q.mask_gen = mask; q.ph_thr = t >= 4294967295.0 ? 0xFFFFFFFFu : (uint32_t)t;
     q.ph_k0 = (uint32_t)(m->dropout_seed & 0xFFFFFFFFu); q.ph_k1 = (uint32_t)(m->dropout_seed >> 32);
     q.ph_site = (uint32_t)site; q.ph_step = m->dropout_step; q.ph_dyn = m->dyn;
@@ -606,7 +626,17 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
     dp.round_out = m->folded;
     const bool fast = g.D <= 256 && (g.D & 3) == 0;
     int stat_parts = fast ? kStatParts : 1;
-    if (fast) {
+    if (g.method == CVT_PROJ_LINEAR_DENSE) {
+      // Projection(method='linear') of tools/grad_cam_CvT.py:103-104,117: q/k/v = Dense_z(x) on the spatial tokens; the cls row is
+      // concatenated back unchanged (:168-170)
+      GemmP p = dense_fwd(a.xn, D, R, D, P + w.lw, D, P + w.lb, a.conv, D);
+      p.batch = 3; p.a_bs0 = 0; p.b_bs0 = (long long)D * D; p.c_bs0 = RD; p.bias_bs = D;
+      CVT_CUDA(run_gemm(m, p, s));
+      if (g.has_cls)
+        for (int z = 0; z < 3; ++z)
+          CVT_CUDA(launch_copy_rows(a.conv + z * RD, RowMap{1, g.Tc, 0}, D, a.xn, RowMap{1, g.Tc, 0}, D, B, D, s));
+    }
+    else if (fast) {
       dp.nparts = kStatParts;
       static const bool use_col = getenv("CVT_NO_DWCOL") == nullptr;
       cudaError_t e = (m->folded && bn && use_col) ? launch_dwcol_fwd(dp, s, &stat_parts) : cudaErrorNotSupported;
@@ -639,13 +669,17 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
     if (bn && g.has_cls) CVT_CUDA(launch_cls_fix(a.xn, RD, F + f.Wc, F + f.bc, 0.125f, B, g.Tc, D, a.qkv2, s));   // cls rows skip BatchNorm
   } else
   {  // proj_q/k/v = Dense(dim)  :180-182  (BatchNorm applied while the A operand is loaded)
-    GemmP p = dense_fwd(a.conv, D, R, D, P + w.pw, D, P + w.pb, a.qkv1, D);
-    p.batch = 3; p.a_bs0 = RD; p.b_bs0 = (long long)D * D; p.c_bs0 = RD; p.bias_bs = D;
-    if (g.method == CVT_PROJ_DW_BN) { p.a_scale = a.bn_scale; p.a_shift = a.bn_shift; p.a_aff_bs = D; p.a_skip_period = g.has_cls ? g.Tc : 0; }
-    CVT_CUDA(run_gemm(m, p, s));
+    const bool skip = c.skip_proj_qkv != 0;     // tools/grad_cam_CvT.py:199: q, k, v enter the attention without proj_q/k/v
+    if (!skip) {
+      GemmP p = dense_fwd(a.conv, D, R, D, P + w.pw, D, P + w.pb, a.qkv1, D);
+      p.batch = 3; p.a_bs0 = RD; p.b_bs0 = (long long)D * D; p.c_bs0 = RD; p.bias_bs = D;
+      if (g.method == CVT_PROJ_DW_BN) { p.a_scale = a.bn_scale; p.a_shift = a.bn_shift; p.a_aff_bs = D; p.a_skip_period = g.has_cls ? g.Tc : 0; }
+      CVT_CUDA(run_gemm(m, p, s));
+    }
     // keras MultiHeadAttention query/key/value EinsumDense; query scaled by 1/sqrt(key_dim) after its bias
-    GemmP q = dense_fwd(a.qkv1, D, R, D, P + w.mw, D, P + w.mb, a.qkv2, D);
+    GemmP q = dense_fwd(skip ? a.conv : a.qkv1, D, R, D, P + w.mw, D, P + w.mb, a.qkv2, D);
     q.batch = 3; q.a_bs0 = RD; q.b_bs0 = (long long)D * D; q.c_bs0 = RD; q.bias_bs = D;
+    if (skip && g.method == CVT_PROJ_DW_BN) { q.a_scale = a.bn_scale; q.a_shift = a.bn_shift; q.a_aff_bs = D; q.a_skip_period = g.has_cls ? g.Tc : 0; }
     q.epi |= EPI_ALPHA0; q.alpha0 = 0.125f;
     if (c.precision != CVT_PREC_FP32) q.epi |= EPI_ROUND;
     CVT_CUDA(run_gemm(m, q, s));
@@ -663,6 +697,8 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
   } else
   {
     GemmP p = dense_fwd(a.attn_o, D, R, D, P + w.ow, D, P + w.ob, a.a1, D);      // MHA attention_output
+    if (training && m->dropout_mode != CVT_DROPOUT_OFF && c.attn_drop_rate > 0.f)   // self.attn_dropout, tools/grad_cam_CvT.py:200
+      epi_dropout(m, p, a.mask_attn, si * 4 + 3, 1.f / (1.f - c.attn_drop_rate), c.attn_drop_rate);
     CVT_CUDA(run_gemm(m, p, s));
     GemmP q = dense_fwd(a.a1, D, R, D, P + w.prw, D, P + w.prb, a.x1, D);        // self.proj :188, dropout :189, residual :274
     q.epi |= EPI_RESID; q.resid = a.x0; q.ldr = D;
@@ -695,14 +731,14 @@ static HeadP head_params(Model* m, const float* proc, int B) {
   p.B = B; p.D = g.D; p.F = m->feat_dim; p.PH = c.proc_dim > 0 ? c.proc_hidden : 0; p.proc_dim = c.proc_dim; p.nc = c.num_classes;
   p.cls_ln = m->head_kind == CVT_HEAD_CLS_LN; p.eps = c.ln_eps;
   p.x2 = a.x2; p.x2_bs = (long long)g.Tc * g.D;
-  p.hn_g = P + m->hn_g; p.hn_b = P + m->hn_b; p.h_mean = m->h_mean; p.h_rstd = m->h_rstd;
+  p.hn_g = m->hn_g >= 0 ? P + m->hn_g : nullptr; p.hn_b = m->hn_b >= 0 ? P + m->hn_b : nullptr; p.h_mean = m->h_mean; p.h_rstd = m->h_rstd;
   p.feat = m->feat; p.proc = proc; p.p1 = m->p1;
   if (c.proc_dim > 0) { p.w1 = P + m->pd1w; p.b1 = P + m->pd1b; p.w2 = P + m->pd2w; p.b2 = P + m->pd2b; }
   p.fw = P + m->fw; p.fb = P + m->fb; p.pred = m->pred;
   p.dpred = m->dpred; p.metrics = m->metrics; p.partial = m->head_partial; p.ticket = m->head_ticket;
   p.dfeat = m->dfeat; p.dz2 = m->dz2; p.dz1 = m->dp1;
   if (c.proc_dim > 0) { p.g_w1 = G + m->pd1w; p.g_b1 = G + m->pd1b; p.g_w2 = G + m->pd2w; p.g_b2 = G + m->pd2b; }
-  p.g_fw = G + m->fw; p.g_fb = G + m->fb; p.g_hn_g = G + m->hn_g; p.g_hn_b = G + m->hn_b;
+  p.g_fw = G + m->fw; p.g_fb = G + m->fb; p.g_hn_g = m->hn_g >= 0 ? G + m->hn_g : nullptr; p.g_hn_b = m->hn_b >= 0 ? G + m->hn_b : nullptr;
   return p;
 }
 
@@ -712,9 +748,16 @@ static cudaError_t head_forward(Model* m, const float* proc, int B) {
   const StageGeo& g = m->geo[m->n_stages - 1]; StageBuf& a = m->buf[m->n_stages - 1];
   const int D = g.D, F = m->feat_dim; float* P = m->P;
   prof_mark(s, "head");
-  if (m->head_kind != CVT_HEAD_CLS_LN) {          // reshape -> LN -> reduce_mean over tokens  :334-337
-    CVT_CUDA(launch_ln_fwd(a.x2, rowmap_none(), D, P + m->hn_g, P + m->hn_b, c.ln_eps, m->hln, D, m->h_mean, m->h_rstd, B * g.Tc, D, s));
-    CVT_CUDA(launch_token_mean(m->hln, B, g.Tc, D, m->feat, F, s));
+  const RowMap spatial = g.has_cls ? RowMap{g.T, g.Tc, 1} : rowmap_none();      // the block output without its cls rows (:283-286)
+  if (m->head_kind == CVT_HEAD_LN_MEAN) {         // reshape -> LN -> reduce_mean over tokens  :334-337
+    CVT_CUDA(launch_ln_fwd(a.x2, spatial, D, P + m->hn_g, P + m->hn_b, c.ln_eps, m->hln, D, m->h_mean, m->h_rstd, B * g.T, D, s));
+    CVT_CUDA(launch_token_mean(m->hln, B, g.T, D, m->feat, F, s));
+  } else if (m->head_kind == CVT_HEAD_MEAN) {     // tf.reduce_mean(x, [1, 2]) (tools/model_plot.py:292) / GlobalAveragePooling2D (tools/grad_cam_CvT.py:336)
+    const float* src = a.x2;
+    if (g.has_cls) { CVT_CUDA(launch_copy_rows(m->hln, rowmap_none(), D, a.x2, spatial, D, B * g.T, D, s)); src = m->hln; }
+    CVT_CUDA(launch_token_mean(src, B, g.T, D, m->feat, F, s));
+  } else if (m->head_kind == CVT_HEAD_CLS) {      // tf.squeeze(cls_tokens, axis=1) without LayerNorm (tools/model_plot.py:290)
+    CVT_CUDA(launch_copy_rows(m->feat, rowmap_none(), F, a.x2, RowMap{1, g.Tc, 0}, D, B, D, s));
   }
   HeadP p = head_params(m, proc, B);
   p.y = m->cur_y;
@@ -734,6 +777,10 @@ static cudaError_t forward_impl(Model* m, const float* img, const float* proc, i
       CVT_CUDA(launch_philox_mask(a.mask2, RD, c.drop_rate, m->dropout_seed, m->dropout_step, i * 4 + 2, s, m->dyn));
     }
   }
+  if (training && m->dropout_mode == CVT_DROPOUT_PHILOX && c.attn_drop_rate > 0.f && !inline_philox(m))
+    for (int i = 0; i < m->n_stages; ++i)
+      CVT_CUDA(launch_philox_mask(m->buf[i].mask_attn, (long long)B * m->geo[i].Tc * m->geo[i].D, c.attn_drop_rate, m->dropout_seed, m->dropout_step,
+                                  i * 4 + 3, s, m->dyn));
   const bool prep = training || !m->skip_prep;           // predict loop: weight-only work was done by the first chunk of the call
   if (c.precision != CVT_PREC_FP32 && prep) {
     CVT_CUDA(launch_transpose_weights(m->P, m->Pt, m->Pr, m->tr_descs_dev, (int)m->tr_descs.size(), m->tr_tiles, s));
@@ -766,10 +813,18 @@ static cudaError_t head_backward(Model* m, const float* proc, int B, float* dX2)
   HeadP p = head_params(m, proc, B);
   p.dx2 = dX2;
   CVT_CUDA(launch_head_bwd(p, s));                 // Final_Dense, Proc_Dense_1/2, cls LayerNormalization: input and parameter gradients
-  if (m->head_kind != CVT_HEAD_CLS_LN) {
-    CVT_CUDA(launch_token_mean_bwd(m->dfeat, F, B, g.Tc, D, m->dhln, s));
-    CVT_CUDA(launch_ln_bwd(m->dhln, D, a.x2, rowmap_none(), D, m->h_mean, m->h_rstd, P + m->hn_g, nullptr, dX2, rowmap_none(), D,
-                           G + m->hn_g, G + m->hn_b, B * g.Tc, D, s));
+  const RowMap spatial = g.has_cls ? RowMap{g.T, g.Tc, 1} : rowmap_none();
+  if (m->head_kind == CVT_HEAD_LN_MEAN) {
+    CVT_CUDA(launch_token_mean_bwd(m->dfeat, F, B, g.T, D, m->dhln, s));
+    CVT_CUDA(launch_ln_bwd(m->dhln, D, a.x2, spatial, D, m->h_mean, m->h_rstd, P + m->hn_g, nullptr, dX2, spatial, D,
+                           G + m->hn_g, G + m->hn_b, B * g.T, D, s));
+  } else if (m->head_kind == CVT_HEAD_MEAN) {
+    if (g.has_cls) {
+      CVT_CUDA(launch_token_mean_bwd(m->dfeat, F, B, g.T, D, m->dhln, s));
+      CVT_CUDA(launch_copy_rows(dX2, spatial, D, m->dhln, rowmap_none(), D, B * g.T, D, s));
+    } else CVT_CUDA(launch_token_mean_bwd(m->dfeat, F, B, g.T, D, dX2, s));
+  } else if (m->head_kind == CVT_HEAD_CLS) {
+    CVT_CUDA(launch_copy_rows(dX2, RowMap{1, g.Tc, 0}, D, m->dfeat, rowmap_none(), F, B, D, s));
   }
   return cudaSuccess;
 }
@@ -848,18 +903,33 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
   if (drop) dA2 = m->gM;
   CVT_CUDA(wgrad_bias(m, a.a1, D, D, dA2, D, D, R, G + w.prw, G + w.prb, 1, 0, 0, s));
   CVT_CUDA(run_gemm(m, dense_dgrad(dA2, D, R, D, P + w.prw, D, m->gC, D), s));              // dA1
+  if (drop && c.attn_drop_rate > 0.f)                                                       // through self.attn_dropout (tools/grad_cam_CvT.py:200)
+    CVT_CUDA(launch_mask_scale(m->gC, m->gC, a.mask_attn, 1.f / (1.f - c.attn_drop_rate), RD, s, 0));
   CVT_CUDA(wgrad_bias(m, a.attn_o, D, D, m->gC, D, D, R, G + w.ow, G + w.ob, 1, 0, 0, s));
   { GemmP q = dense_dgrad(m->gC, D, R, D, P + w.ow, D, m->gE, D); if (c.precision != CVT_PREC_FP32) q.epi |= EPI_ROUND; CVT_CUDA(run_gemm(m, q, s)); }   // dO
   prof_mark(s, kStageNames[si][8]);
   CVT_CUDA(attention_backward(m, si, B, m->gE, m->gQ, s));                                  // gQ = [dQ(pre-scale), dK, dV]
   prof_mark(s, kStageNames[si][9]);
   // ---- MHA q/k/v EinsumDense ----
-  CVT_CUDA(wgrad_bias(m, a.qkv1, D, D, m->gQ, D, D, R, G + w.mw, G + w.mb, 3, RD, RD, s));
+  const bool skip = c.skip_proj_qkv != 0;
+  float* dq0 = m->gQ;                      // d(q0, k0, v0): gradient w.r.t. the three Projection outputs
+  if (!skip) {
+    CVT_CUDA(wgrad_bias(m, a.qkv1, D, D, m->gQ, D, D, R, G + w.mw, G + w.mb, 3, RD, RD, s));
+  } else {
+    // proj_q/k/v never ran (tools/grad_cam_CvT.py:199): the EinsumDense input is the Projection output itself (BatchNorm recomputed on load)
+    CVT_CUDA(launch_colsum(m->gQ, D, rowmap_none(), R, D, 3, RD, G + w.mb, D, s));
+    GemmP p = dense_wgrad(c.precision != CVT_PREC_FP32, a.conv, D, D, m->gQ, D, D, R, G + w.mw);
+    p.batch = 3; p.a_bs0 = RD; p.b_bs0 = RD; p.c_bs0 = (long long)D * D; p.splitk = auto_splitk(c.precision != CVT_PREC_FP32, D, D, R, 3);
+    if (g.method == CVT_PROJ_DW_BN) { p.a_scale = a.bn_scale; p.a_shift = a.bn_shift; p.a_aff_bs = D; p.a_skip_period = g.has_cls ? g.Tc : 0; }
+    CVT_CUDA(run_gemm(m, p, s));
+  }
   {
     GemmP q = dense_dgrad(m->gQ, D, R, D, P + w.mw, D, m->gQ2, D);
     q.batch = 3; q.a_bs0 = RD; q.b_bs0 = (long long)D * D; q.c_bs0 = RD;
     CVT_CUDA(run_gemm(m, q, s));
   }
+  if (skip) dq0 = m->gQ2;
+  else {
   // ---- proj_q/k/v Dense (input = BN(conv) recomputed on load) ----
   CVT_CUDA(launch_colsum(m->gQ2, D, rowmap_none(), R, D, 3, RD, G + w.pb, D, s));
   {
@@ -871,6 +941,8 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
     q.batch = 3; q.a_bs0 = RD; q.b_bs0 = (long long)D * D; q.c_bs0 = RD;
     CVT_CUDA(run_gemm(m, q, s));                                                            // gQ = d(q0,k0,v0)
   }
+  }
+  float* dq_other = dq0 == m->gQ ? m->gQ2 : m->gQ;      // the free one of the two [3][R][D] scratch buffers
   prof_mark(s, kStageNames[si][10]);
   // ---- Projection backward (BatchNorm + depthwise conv / avg pool / identity) ----
   {
@@ -878,14 +950,29 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
     const bool fast = g.D <= 256 && (g.D & 3) == 0;
     if (bn) {
       if (training)
-        CVT_CUDA(launch_bn_bwd_reduce(m->gQ, a.conv, RD, a.bn_mean, a.bn_rstd, G + w.bn_g, G + w.bn_b, B, g.T, g.Tc, g.has_cls, D, s));
+        CVT_CUDA(launch_bn_bwd_reduce(dq0, a.conv, RD, a.bn_mean, a.bn_rstd, G + w.bn_g, G + w.bn_b, B, g.T, g.Tc, g.has_cls, D, s));
       if (fast)
         CVT_CUDA(launch_bn_bwd_coef(P + w.bn_g, a.bn_mean, a.bn_rstd, a.bn_scale, G + w.bn_g, G + w.bn_b, (long long)B * g.T, training, D, a.bn_coef, s));
       else
-        CVT_CUDA(launch_bn_bwd_apply(m->gQ, a.conv, RD, a.bn_mean, a.bn_rstd, P + w.bn_g, a.bn_scale, G + w.bn_g, G + w.bn_b, training,
+        CVT_CUDA(launch_bn_bwd_apply(dq0, a.conv, RD, a.bn_mean, a.bn_rstd, P + w.bn_g, a.bn_scale, G + w.bn_g, G + w.bn_b, training,
                                      B, g.T, g.Tc, g.has_cls, D, s));
     }
-    DwProjBwdP dp; dp.dconv = m->gQ; dp.bs = RD; dp.xn = a.xn; dp.w = bn ? P + w.dw : nullptr;
+    if (g.method == CVT_PROJ_LINEAR_DENSE) {
+      // Projection Dense backward (tools/grad_cam_CvT.py:103,117): weights see the spatial tokens only; the cls rows pass through
+      const RowMap sp = g.has_cls ? RowMap{g.T, g.Tc, 1} : rowmap_none();
+      CVT_CUDA(launch_colsum(dq0, D, sp, B * g.T, D, 3, RD, G + w.lb, D, s));
+      GemmP p = dense_wgrad(false, a.xn, D, D, dq0, D, D, B * g.T, G + w.lw);
+      p.a_map = sp; p.b_map = sp; p.batch = 3; p.a_bs0 = 0; p.b_bs0 = RD; p.c_bs0 = (long long)D * D; p.splitk = auto_splitk(false, D, D, B * g.T, 3);
+      CVT_CUDA(launch_gemm_simt(p, s));       // row-mapped operands: the fp32 kernel is the one that takes them (a tool-side variant, not the benched path)
+      GemmP q = dense_dgrad(dq0, D, R, D, P + w.lw, D, dq_other, D);
+      q.batch = 3; q.a_bs0 = RD; q.b_bs0 = (long long)D * D; q.c_bs0 = RD;
+      CVT_CUDA(run_gemm(m, q, s));
+      if (g.has_cls)
+        for (int z = 0; z < 3; ++z)
+          CVT_CUDA(launch_copy_rows(dq_other + z * RD, RowMap{1, g.Tc, 0}, D, dq0 + z * RD, RowMap{1, g.Tc, 0}, D, B, D, s));
+      dq0 = dq_other;                          // ... and the three branches are summed by the identity Projection backward below
+    }
+    DwProjBwdP dp; dp.dconv = dq0; dp.bs = RD; dp.xn = a.xn; dp.w = bn ? P + w.dw : nullptr;
     const int mz = bn ? 0 : (g.method == CVT_PROJ_AVG ? 1 : 2);
     dp.method[0] = (g.method == CVT_PROJ_AVG) ? 2 : mz; dp.method[1] = mz; dp.method[2] = mz;
     dp.B = B; dp.H = g.H; dp.W = g.W; dp.D = D; dp.Tc = g.Tc; dp.has_cls = g.has_cls; dp.dxn = m->gE; dp.ddw = bn ? G + w.dw : nullptr;
@@ -1719,12 +1806,12 @@ int cvt_set_dropout(cvt_model* h, int mode, uint64_t seed) {
   return CVT_OK;
 }
 int cvt_set_dropout_mask(cvt_model* h, int site, const uint8_t* host_mask, int64_t count) {
-  if (!h || !host_mask || site < 0 || site / 4 >= h->m.n_stages || site % 4 > 2) { set_error("cvt_set_dropout_mask: bad site"); return CVT_ERR_INVALID; }
+  if (!h || !host_mask || site < 0 || site / 4 >= h->m.n_stages || (site % 4 == 3 && !(h->m.cfg.attn_drop_rate > 0.f))) { set_error("cvt_set_dropout_mask: bad site"); return CVT_ERR_INVALID; }
   Model* m = &h->m; const StageGeo& g = m->geo[site / 4]; StageBuf& a = m->buf[site / 4];
   const int64_t width = (site % 4 == 1) ? (int64_t)m->cfg.mlp_ratio * g.D : g.D;
   const int64_t cap = (int64_t)m->cfg.max_batch * g.Tc * width;
   if (count < 0 || count > cap) { set_error("cvt_set_dropout_mask: count exceeds max_batch*Tc*width"); return CVT_ERR_INVALID; }
-  uint8_t* dst = site % 4 == 0 ? a.mask_proj : (site % 4 == 1 ? a.mask1 : a.mask2);
+  uint8_t* dst = site % 4 == 0 ? a.mask_proj : (site % 4 == 1 ? a.mask1 : (site % 4 == 2 ? a.mask2 : a.mask_attn));
   API_CUDA(cudaMemcpyAsync(dst, host_mask, (size_t)count, cudaMemcpyHostToDevice, m->stream));
   API_CUDA(cudaStreamSynchronize(m->stream));
   return CVT_OK;
@@ -1755,6 +1842,7 @@ int64_t cvt_get_tap(cvt_model* h, const char* name, float* dst, int64_t capacity
     else if (!strcmp(f, "xn")) { src = a.xn; n = RD; }
     else if (!strcmp(f, "qkv1") || !strcmp(f, "a1")) {
       if (m->folded) { set_error(std::string("cvt_get_tap: '") + name + "' does not exist in TF32 mode (the stacked linear maps are folded into one GEMM)"); return CVT_ERR_STATE; }
+      if (!strcmp(f, "qkv1") && m->cfg.skip_proj_qkv) { set_error("cvt_get_tap: this model does not apply proj_q/k/v"); return CVT_ERR_STATE; }
       if (!strcmp(f, "qkv1")) { src = a.qkv1; n = 3 * RD; } else { src = a.a1; n = RD; }
     }
     else if (!strcmp(f, "qkv2")) { src = a.qkv2; n = 3 * RD; }

@@ -23,7 +23,8 @@ struct ParamInfo {
 struct StageW {
   int64_t conv_w, conv_b, cls, ln_g, ln_b;
   int64_t dw, bn_g, bn_b;                 // [3][9][D], [3][D], [3][D]       (dw_bn only)
-  int64_t pw, pb, mw, mb;                 // proj_{q,k,v} [3][D][D],[3][D]; mha {query,key,value} [3][D][D],[3][D]
+  int64_t lw, lb;                         // Projection Dense of the 'linear_dense' method [3][D][D], [3][D]  (tools/grad_cam_CvT.py:103)
+  int64_t pw, pb, mw, mb;                 // proj_{q,k,v} [3][D][D],[3][D] (-1 when skip_proj_qkv); mha {query,key,value} [3][D][D],[3][D]
   int64_t ow, ob, prw, prb, f1w, f1b, f2w, f2b;
   int64_t bn_mm, bn_mv;                   // state arena: moving mean / variance [3][D]
 };
@@ -43,7 +44,7 @@ struct StageBuf {
   float *bn_stats, *bn_scale, *bn_shift, *bn_mean, *bn_rstd, *bn_coef;
   float *scores;                         // fp32 attention path: P [B*heads, Tc, Tc]
   float *lse;                            // tensor-core attention path: log-sum-exp [B*heads, Tc]
-  uint8_t *mask_proj, *mask1, *mask2;
+  uint8_t *mask_proj, *mask1, *mask2, *mask_attn;      // mask_attn: attention-output dropout of the Grad-CAM variant (null otherwise)
 };
 
 struct Model {

@@ -38,6 +38,21 @@ class CvtConfig:
     precision: str = "fp32"
     max_batch: int = 64
     device: int = 0
+    head: str = "auto"                  # auto | cls_ln | ln_mean | cls | mean (alias gap): include/cvt_b200.h CVT_HEAD_*
+    apply_proj_qkv: bool = True         # False: tools/grad_cam_CvT.py never calls proj_q/k/v
+    attn_drop_rate: float = 0.0         # tools/grad_cam_CvT.py:200
+
+    @staticmethod
+    def gradcam(cls_token_switch=False, projection_method="dw_bn", **kw) -> "CvtConfig":
+        """The model of tools/grad_cam_CvT.py:315-349: cls token (if switched on) on every stage, proj_q/k/v not applied, dropout on the
+        attention output, `linear` = Dense(dim), GlobalAveragePooling2D head without LayerNorm."""
+        c = CvtConfig.reference(projection_method, cls_token_switch, **kw)
+        for st in c.stages:
+            st.with_cls_token = bool(cls_token_switch)
+            if projection_method == "linear":
+                st.qkv_method = "linear_dense"
+        c.head, c.apply_proj_qkv, c.attn_drop_rate = "mean", False, 0.1
+        return c
 
     @staticmethod
     def reference(projection_method="dw_bn", cls_token_switch=True, proc_dim=5, num_classes=1, image_h=128, image_w=128,
@@ -69,6 +84,9 @@ class CvtConfig:
         c.proc_dim, c.proc_hidden, c.num_classes, c.mlp_ratio = self.proc_dim, self.proc_hidden, self.num_classes, self.mlp_ratio
         c.drop_rate, c.ln_eps, c.bn_eps, c.bn_momentum = self.drop_rate, self.ln_eps, self.bn_eps, self.bn_momentum
         c.precision, c.max_batch, c.device = L.PREC[self.precision], self.max_batch, self.device
+        if self.head not in L.HEAD:
+            raise ValueError("Unknown head: %s" % self.head)
+        c.head_kind, c.skip_proj_qkv, c.attn_drop_rate = L.HEAD[self.head], 0 if self.apply_proj_qkv else 1, float(self.attn_drop_rate)
         return c
 
 
@@ -323,8 +341,8 @@ class CvtEngine:
         L.check(self.lib.cvt_set_dropout(self.h, {"off": 0, "philox": 1, "masks": 2}[mode], seed), "cvt_set_dropout")
 
     def set_dropout_masks(self, masks: Dict[str, np.ndarray]):
-        """masks: {"s{i}.proj"|"s{i}.mlp1"|"s{i}.mlp2": uint8 [B,Tc,width]} (oracle.make_dropout_masks layout)."""
-        sub = {"proj": 0, "mlp1": 1, "mlp2": 2}
+        """masks: {"s{i}.proj"|"s{i}.mlp1"|"s{i}.mlp2"|"s{i}.attn": uint8 [B,Tc,width]} (oracle.make_dropout_masks layout)."""
+        sub = {"proj": 0, "mlp1": 1, "mlp2": 2, "attn": 3}
         for k, v in masks.items():
             st, nm = k.split(".")
             site = (int(st[1:]) - 1) * 4 + sub[nm]

@@ -30,6 +30,10 @@ from .engine import CvtConfig, CvtEngine
 # ---- the switches the reference keeps as module-level constants (models/CvT(Par).py:25-28,66-72) ----------------
 projection_method = "dw_bn"
 cls_token_switch = True
+# which script's create_cvt_model is mirrored: "reference" = models/CvT(Par).py:292-354 / CvT(Img).py; "gradcam" = tools/grad_cam_CvT.py:315-349
+# (cls token on every stage, proj_q/k/v never applied, attention-output dropout, 'linear' = Dense, GlobalAveragePooling2D head);
+# "model_plot" = tools/model_plot.py:254-300 (the reference network with the un-normalised head of :289-292)
+model_variant = "reference"
 
 
 def _make_spec():
@@ -46,9 +50,14 @@ def _make_spec():
 spec = _make_spec()
 
 
-def configure(projection: Optional[str] = None, cls_token: Optional[bool] = None, new_spec: Optional[dict] = None):
+def configure(projection: Optional[str] = None, cls_token: Optional[bool] = None, new_spec: Optional[dict] = None,
+              variant: Optional[str] = None):
     """Sets the module-level switches the reference scripts edit by hand, then rebuilds `spec` from them."""
-    global projection_method, cls_token_switch, spec
+    global projection_method, cls_token_switch, spec, model_variant
+    if variant is not None:
+        if variant not in ("reference", "gradcam", "model_plot"):
+            raise ValueError("unknown model variant %r" % (variant,))
+        model_variant = variant
     if projection is not None:
         projection_method = projection
     if cls_token is not None:
@@ -547,6 +556,14 @@ def create_cvt_model(image_height, image_width, num_channels, proc_dim=None, num
         raise TypeError("create_cvt_model() missing 1 required positional argument: 'num_classes'")
     cfg = CvtConfig.from_spec_dict(spec, int(image_height), int(image_width), int(num_channels), int(proc_dim or 0), int(num_classes),
                                    precision=precision, max_batch=int(max_batch), device=int(device))
+    if model_variant == "gradcam":       # tools/grad_cam_CvT.py:315-349
+        for st in cfg.stages:
+            st.with_cls_token = bool(cls_token_switch)
+            if st.qkv_method == "linear":
+                st.qkv_method = "linear_dense"
+        cfg.head, cfg.apply_proj_qkv, cfg.attn_drop_rate = "mean", False, 0.1
+    elif model_variant == "model_plot":  # tools/model_plot.py:289-292
+        cfg.head = "cls" if cfg.stages[-1].with_cls_token else "mean"
     return Model(cfg, engine_factory=engine_factory, seed=seed)
 
 
@@ -559,6 +576,11 @@ def make_gradcam_heatmap(img_array, proc_array, model: Model, last_conv_layer_na
         xs = img_array[o:o + batch_size]
         ps = None if proc_array is None else np.asarray(proc_array)[o:o + batch_size]
         feat, pred, grads = model.feature_and_gradient([xs, ps] if ps is not None else xs, last_conv_layer_name)
+        if not np.any(grads):
+            # the reference fails here too: tape.gradient returns None when the output does not depend on the layer (the cls-token head of
+            # models/CvT(Par).py:326-329 reads the cls row only, never the spatial map `get_layer(...).output` names)
+            raise ValueError("No gradients: the prediction does not depend on the output map of %r (cls-token head); Grad-CAM needs the "
+                             "pooled head of tools/grad_cam_CvT.py (configure(variant='gradcam')) or cls_token=False" % (last_conv_layer_name,))
         pooled = grads.mean(axis=(0, 1, 2))
         heat = (pooled * feat[0]).sum(axis=-1)
         heat = np.maximum(heat, 0) / heat.max()
