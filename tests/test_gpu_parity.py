@@ -333,3 +333,20 @@ def test_profile_step_leaves_the_model_untouched():
     l1, l2 = eng.read_metrics(), twin.read_metrics()
     assert abs(l1[0] - l2[0]) <= 1e-4 * abs(l2[0])          # same moments, same dropout step -> same second step
     eng.close(); twin.close()
+
+
+@pytest.mark.parametrize("hw,batch,cls", [((128, 128), 5, True), ((36, 44), 3, False), ((64, 64), 64, True)])
+def test_fused_inference_mlp_kernel_tf32(hw, batch, cls):
+    """TF32 inference runs norm1 + fc1 + GELU + fc2 + residual of stages with D = 64 / 128 as ONE kernel (mlp_fused.cu; the hidden
+    activation stays in TMEM).  Its output x2 (and everything downstream) against the oracle; token counts that are not multiples of the
+    128-row tile (297, 90) and grids of several CTAs per SM (batch 64)."""
+    spec, eng, params, img, proc, y = make_pair("dw_bn", cls, 5, 1, hw, batch=batch, precision="tf32")
+    pred = eng.predict(img, proc)
+    ref, taps = O.forward(spec, params, img, proc, training=False)
+    bad, report = compare_taps(eng, taps, tol=5e-3, names=["x0", "xn", "qkv2", "attn_o", "x1", "x2", "out"])
+    assert not bad, "fused-Mlp inference mismatches:\n" + fmt(report)
+    assert rel_err(pred, ref) <= 5e-3
+    with pytest.raises(T.CvtError):          # stages 1 and 2 never wrote the hidden activation
+        eng.tap("s1.hact")
+    eng.tap("s3.hact")                       # stage 3 (D = 256) still runs the three-kernel path
+    eng.close()

@@ -34,7 +34,8 @@ def _check(spec, eng, params, img, proc, y, tf32, masks_seed=5):
     # inference
     pred = eng.predict(img, proc if spec.proc_dim > 0 else None)
     ref, taps = O.forward(spec, params, img, proc, training=False)
-    bad, report = compare_taps(eng, taps, tol=at, names=TAPS)
+    # TF32 inference: stages with D = 64 / 128 run the fused Mlp kernel, which keeps y / hact on the SM
+    bad, report = compare_taps(eng, taps, tol=at, names=[t for t in TAPS if not (tf32 and t in ("y", "hact"))])
     assert not bad, "inference mismatches:\n" + fmt(report)
     assert rel_err(pred, ref) <= at
     # training forward + backward with the oracle's dropout masks

@@ -706,6 +706,11 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
     CVT_CUDA(run_gemm(m, q, s));
   }
   prof_mark(s, kStageNames[si][5]);
+  if (!training && mlp_fused_supports(m, si)) {
+    // inference: norm1 (:278) + Mlp (:253-258) + residual (:281) as one kernel, the 4D-wide hidden activation never leaves the SM
+    m->mlp_fused_last = true;
+    return launch_mlp_fused(m, si, R, s);
+  }
   // y = norm1(x)  :278  (same gamma/beta)
   CVT_CUDA(launch_ln_fwd(a.x1, rowmap_none(), D, P + w.ln_g, P + w.ln_b, c.ln_eps, a.y, D, a.lnb_mean, a.lnb_rstd, R, D, s, m->folded));
   {  // Mlp :253-258
@@ -781,6 +786,7 @@ static cudaError_t forward_impl(Model* m, const float* img, const float* proc, i
     for (int i = 0; i < m->n_stages; ++i)
       CVT_CUDA(launch_philox_mask(m->buf[i].mask_attn, (long long)B * m->geo[i].Tc * m->geo[i].D, c.attn_drop_rate, m->dropout_seed, m->dropout_step,
                                   i * 4 + 3, s, m->dyn));
+  m->mlp_fused_last = false;
   const bool prep = training || !m->skip_prep;           // predict loop: weight-only work was done by the first chunk of the call
   if (c.precision != CVT_PREC_FP32 && prep) {
     CVT_CUDA(launch_transpose_weights(m->P, m->Pt, m->Pr, m->tr_descs_dev, (int)m->tr_descs.size(), m->tr_tiles, s));
@@ -1848,6 +1854,10 @@ int64_t cvt_get_tap(cvt_model* h, const char* name, float* dst, int64_t capacity
     else if (!strcmp(f, "qkv2")) { src = a.qkv2; n = 3 * RD; }
     else if (!strcmp(f, "attn_o")) { src = a.attn_o; n = RD; }
     else if (!strcmp(f, "x1")) { src = a.x1; n = RD; }
+    else if (m->mlp_fused_last && mlp_fused_supports(m, si) && (!strcmp(f, "y") || !strcmp(f, "hpre") || !strcmp(f, "hact"))) {
+      set_error(std::string("cvt_get_tap: '") + name + "' is not materialised by the fused inference Mlp kernel (set CVT_NO_FUSED_MLP=1 to get it)");
+      return CVT_ERR_STATE;
+    }
     else if (!strcmp(f, "y")) { src = a.y; n = RD; }
     else if (!strcmp(f, "hpre")) { src = a.hpre; n = RD * m->cfg.mlp_ratio; }
     else if (!strcmp(f, "hact")) { src = a.hact; n = RD * m->cfg.mlp_ratio; }

@@ -119,6 +119,7 @@ struct Model {
   struct GraphEntry { int kind; const float* img; const float* proc; const float* y; int batch; cudaGraphExec_t exec; long long launches; };
   int use_graphs = 1;
   bool premasked = false;                 // backward: gM already holds dX2 * mask2 / keep of the stage about to run (written by col2im)
+  bool mlp_fused_last = false;            // the last forward ran the fused inference Mlp: y / hpre / hact were not materialised
   bool skip_prep = false;                 // set while a predict-loop chunk after the first is issued: weight-only kernels are skipped
   std::vector<GraphEntry> graphs;
   float* lr_dev = nullptr;
@@ -128,6 +129,10 @@ struct Model {
 // attention dispatch (attention.cu)
 cudaError_t attention_forward(Model* m, int si, int B, cudaStream_t s);
 cudaError_t attention_backward(Model* m, int si, int B, const float* dO, float* dQKV, cudaStream_t s);
+
+// fused inference Mlp (mlp_fused.cu): x2 = x1 + fc2(gelu(fc1(norm1(x1)))) in one kernel, the hidden activation stays in TMEM
+bool mlp_fused_supports(const Model* m, int si);
+cudaError_t launch_mlp_fused(const Model* m, int si, int R, cudaStream_t s);
 
 // contraction dispatch by precision (fp32 FFMA vs tcgen05)
 cudaError_t run_gemm(const Model* m, const GemmP& p, cudaStream_t s);
