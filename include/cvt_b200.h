@@ -32,6 +32,7 @@ extern "C" {
 
 #define CVT_MAX_STAGES 4
 #define CVT_DATASET_SLOTS 4
+#define CVT_MAX_PEERS 8          /* ranks of one NVSwitch box whose workspaces a model can map (cvt_comm_peer_open) */
 #define CVT_ABI_VERSION 3
 
 typedef enum {
@@ -198,6 +199,13 @@ CVT_API int  cvt_backward_to_tap(cvt_model* m, const float* dout_host, const cha
 CVT_API int  cvt_comm_unique_id(uint8_t id_out[128]);
 CVT_API int  cvt_comm_init(cvt_model* m, const uint8_t unique_id[128], int rank, int world);
 CVT_API int  cvt_comm_destroy(cvt_model* m);
+/* Peer-memory data parallelism inside one NVSwitch box (after cvt_comm_init, world <= CVT_MAX_PEERS): every rank exports a 64-byte
+ * cudaIpc handle of its workspace, the host gathers the `world` handles (torch.distributed all_gather) and hands all of them to every
+ * rank.  From then on cvt_train_step ends in ONE kernel that reduce-scatters the gradients over NVLink, applies Adam to the rank's slice
+ * and all-gathers the new weights straight into the peers' arenas (csrc/dp_peer.cu) instead of ncclAllReduce + a full Adam pass.
+ * sync_grads != 0 also leaves the reduced gradient in every rank's arena (cvt_get_grad in tests). */
+CVT_API int  cvt_comm_peer_export(cvt_model* m, uint8_t handle_out[64]);
+CVT_API int  cvt_comm_peer_open(cvt_model* m, const uint8_t* handles /* [world][64] */, int sync_grads);
 /* flat trainable arenas so the host may run its own collective instead (torch.distributed plumbing) */
 CVT_API int  cvt_grad_arena(cvt_model* m, float** grads_dev, int64_t* count);
 CVT_API int  cvt_param_arena(cvt_model* m, float** params_dev, int64_t* count);

@@ -39,7 +39,7 @@ def main():
     cfg = T.CvtConfig.reference(image_h=a.hw, image_w=a.hw, precision=a.precision, max_batch=B, device=local, drop_rate=0.0)
     eng = T.CvtEngine(cfg)
     eng.set_params(O.init_params(spec, 500 + rank, "parity"))          # ranks start different; init_data_parallel broadcasts rank 0's
-    dp.init_data_parallel(eng, dist, rank, world, dev)
+    dp.init_data_parallel(eng, dist, rank, world, dev, sync_grads=True)      # sync_grads: every rank's arena ends up holding the reduced gradient
     params = {k: v.astype(np.float64) for k, v in eng.get_params().items()}
     img, proc, y = O.synthetic_batch(spec, B * world, seed=11)
     lo, hi = dp.shard_bounds(B * world, rank, world)
@@ -48,8 +48,9 @@ def main():
     eng.set_dropout("off")
     eng.train_step_dev(d[0], d[1], d[2], B, 0.0)
     eng.synchronize()
-    got = eng.get_grads()
-    out = {"world": world, "precision": a.precision, "per_rank_batch": B, "image": a.hw}
+    # the library keeps the SUM over ranks in its gradient arena (the 1 / world factor is folded into the Adam update)
+    got = {k: v / world for k, v in eng.get_grads().items()}
+    out = {"world": world, "path": "nccl" if os.environ.get("CVT_DP_NCCL") else "peer-memory kernel", "precision": a.precision, "per_rank_batch": B, "image": a.hw}
     if rank == 0:
         shards = [O.loss_and_grads(spec, params, img[r * B:(r + 1) * B], proc[r * B:(r + 1) * B], y[r * B:(r + 1) * B], None)["grads"] for r in range(world)]
         mean = {k: sum(s[k] for s in shards) / world for k in shards[0]}
@@ -63,8 +64,10 @@ def main():
         eng.train_step_dev(d[0], d[1], d[2], B, 1e-3)
     eng.synchronize()
     div = dp.replica_divergence(eng, dist, world, dev)
+    div_bn = dp.replica_divergence(eng, dist, world, dev, trainable=False)
     if rank == 0:
         out["replica_divergence_after_5_steps"] = div
+        out["bn_moving_stat_divergence"] = div_bn       # per-replica BatchNorm: expected to be non-zero when the shards differ
         tol = 1e-3 if a.precision == "fp32" else 2e-2
         out["ok"] = bool(out["max_err_vs_mean_of_shard_gradients"] <= tol and div == 0.0)
         print(json.dumps(out))

@@ -85,6 +85,8 @@ _PROTOS = {
     "cvt_comm_unique_id": (C.c_int, [C.c_void_p]),
     "cvt_comm_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
     "cvt_comm_destroy": (C.c_int, [C.c_void_p]),
+    "cvt_comm_peer_export": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "cvt_comm_peer_open": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
     "cvt_grad_arena": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]),
     "cvt_param_arena": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]),
     "cvt_synchronize": (C.c_int, [C.c_void_p]),
@@ -118,6 +120,8 @@ def load():
         fn = getattr(lib, name)
         fn.restype = res
         fn.argtypes = args
+    if lib.cvt_abi_version() != ABI_VERSION:
+        raise CvtError("libcvt_b200.so has ABI %d, this binding expects %d: rebuild with `python __graft_entry__.py`" % (lib.cvt_abi_version(), ABI_VERSION))
     _lib = lib
     return lib
 

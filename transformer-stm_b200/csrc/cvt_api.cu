@@ -133,7 +133,7 @@ static cudaError_t wgrad_bias(const Model* m, const float* X, long long ldx, int
 
 // ---- parameters ------------------------------------------------------------------------------------------------
 static void clear_graphs(Model* m) {
-  for (auto& g : m->graphs) if (g.exec) cudaGraphExecDestroy(g.exec);
+  for (auto& g : m->graphs) { if (g.exec) cudaGraphExecDestroy(g.exec); for (auto e : g.seg) if (e) cudaGraphExecDestroy(e); }
   m->graphs.clear();
 }
 
@@ -278,6 +278,7 @@ static void carve(Model* m, Bump& b) {
   m->in_proc2 = b.take<float>(MB * std::max(1, c.proc_dim));
   m->in_y2 = b.take<float>(MB * c.num_classes);
   m->lr_dev = b.take<float>(4);
+  m->dp_flags = b.take<uint32_t>(64);
   m->Pt = b.take<float>(m->n_train + m->n_pt_extra);
   m->Pr = b.take<float>(m->n_train);
   m->Fd = b.take<float>(m->n_fold);
@@ -431,6 +432,7 @@ int cvt_create(const cvt_config* cfg, cvt_model** out) {
     float* P = m->P; float* G = m->G; float* F = m->Fd;
     for (int i = 0; i < m->n_stages; ++i) {
       const StageW& w = m->w[i]; const StageFold& q = m->fold[i]; const int D = m->geo[i].D; const int64_t DD = (int64_t)D * D;
+      m->mg_bwd_first[i] = (int)bw.size(); m->mg_bwd_tile0[i] = tb;
       for (int z = 0; z < 3; ++z) {
         const float* pw = P + w.pw + z * DD; const float* mw = P + w.mw + z * DD;
         push(fw, tf, pw, 0, mw, 0, F + q.Wc + z * DD, D, D, D, D, D, D, 0, nullptr, nullptr, 0);                                // Wc = Wp Wm
@@ -448,6 +450,7 @@ int cvt_create(const cvt_config* cfg, cvt_model** out) {
       push(bw, tb, ow, 1, Zo, 0, G + w.prw, D, D, D, D, D, D, 1, P + w.ob, so, 0);                                                // dWproj = Wout^T Zo + bout (x) so
       push(bw, tb, Zo, 0, prw, 1, G + w.ow, D, D, D, D, D, D, 1, nullptr, nullptr, 0);                                            // dWout = Zo Wproj^T
       push(bw, tb, so, 0, prw, 1, G + w.ob, 1, D, D, D, D, D, 1, nullptr, nullptr, 0);                                            // dbout = so Wproj^T
+      m->mg_bwd_cnt[i] = (int)bw.size() - m->mg_bwd_first[i]; m->mg_bwd_ntiles[i] = tb - m->mg_bwd_tile0[i];
     }
     if (fw.size() > 64 || bw.size() > 96) { set_error("cvt_create: too many stages for the fold descriptor tables"); cvt_destroy(h); return CVT_ERR_INVALID; }
     m->mg_fwd_n = (int)fw.size(); m->mg_fwd_tiles = tf; m->mg_bwd_n = (int)bw.size(); m->mg_bwd_tiles = tb;
@@ -1038,26 +1041,36 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
 }
 
 
-// runs the backward pass from m->dpred down to stage `stop_stage` (0 = all the way); returns the buffer holding the
-// gradient w.r.t. the output of block `stop_stage` when stop_stage > 0 ... (grad-cam tap)
-static cudaError_t backward_impl(Model* m, const float* img, const float* proc, int B, int training, int stop_after_stage, float** tap_grad) {
+// backward of stages hi, hi-1, ..., lo (hi == n_stages-1: preceded by the gradient-arena reset and the head).  The gradient w.r.t. the
+// output of block i lives in gX[i & 1].  stage_unfold: the folded attention weights get their individual gradients right after their
+// stage (data parallel: the stage's bucket can then be reduced while the earlier stages still run) instead of once at the end.
+// tap_grad != nullptr: stop before stage `stop_after_stage` and return the buffer holding the gradient w.r.t. its output (grad-cam tap).
+static cudaError_t backward_range(Model* m, const float* img, const float* proc, int B, int training, int hi, int lo, bool stage_unfold,
+                                  int stop_after_stage, float** tap_grad) {
   cudaStream_t s = m->stream;
-  m->premasked = false;
-  CVT_CUDA(cudaMemsetAsync(m->G, 0, (size_t)(m->n_train + m->n_z) * sizeof(float), s));
-  int cur = (m->n_stages - 1) & 1;
-  CVT_CUDA(head_backward(m, proc, B, m->gX[cur]));
-  for (int i = m->n_stages - 1; i >= 0; --i) {
-    if (tap_grad && i == stop_after_stage) { *tap_grad = m->gX[cur]; return cudaSuccess; }
+  if (hi == m->n_stages - 1) {
+    m->premasked = false;
+    CVT_CUDA(cudaMemsetAsync(m->G, 0, (size_t)(m->n_train + m->n_z) * sizeof(float), s));
+    CVT_CUDA(head_backward(m, proc, B, m->gX[hi & 1]));
+  }
+  for (int i = hi; i >= lo; --i) {
+    if (tap_grad && i == stop_after_stage) { *tap_grad = m->gX[i & 1]; return cudaSuccess; }
     const float* xin; long long bstride; int boff;
     if (i == 0) { xin = img; bstride = (long long)m->cfg.image_h * m->cfg.image_w * m->cfg.in_chans; boff = 0; }
     else { const StageGeo& gp = m->geo[i - 1]; xin = m->buf[i - 1].x2; bstride = (long long)gp.Tc * gp.D; boff = gp.has_cls * gp.D; }
-    float* dprev = i > 0 ? m->gX[cur ^ 1] : nullptr;
-    CVT_CUDA(stage_backward(m, i, xin, bstride, boff, B, training, m->gX[cur], dprev, false));
-    cur ^= 1;
+    float* dprev = i > 0 ? m->gX[(i & 1) ^ 1] : nullptr;
+    CVT_CUDA(stage_backward(m, i, xin, bstride, boff, B, training, m->gX[i & 1], dprev, false));
+    if (m->folded && stage_unfold && !tap_grad)
+      CVT_CUDA(launch_multigemm(m->mg_bwd_dev + m->mg_bwd_first[i], m->mg_bwd_cnt[i], m->mg_bwd_ntiles[i], s, m->mg_bwd_tile0[i]));
   }
-  if (m->folded && !tap_grad) CVT_CUDA(launch_multigemm(m->mg_bwd_dev, m->mg_bwd_n, m->mg_bwd_tiles, s));   // unfold dWp, dbp, dWm, dWout, dbout, dWproj
-  prof_mark(s, "end_backward");
+  if (lo == 0) {
+    if (m->folded && !stage_unfold && !tap_grad) CVT_CUDA(launch_multigemm(m->mg_bwd_dev, m->mg_bwd_n, m->mg_bwd_tiles, s));   // unfold dWp, dbp, dWm, dWout, dbout, dWproj
+    prof_mark(s, "end_backward");
+  }
   return cudaSuccess;
+}
+static cudaError_t backward_impl(Model* m, const float* img, const float* proc, int B, int training, int stop_after_stage, float** tap_grad) {
+  return backward_range(m, img, proc, B, training, m->n_stages - 1, 0, false, stop_after_stage, tap_grad);
 }
 
 static int check_batch(Model* m, int batch, const char* who) {
@@ -1147,14 +1160,66 @@ int cvt_comm_init(cvt_model* h, const uint8_t unique_id[128], int rank, int worl
   NcclUid uid; memcpy(uid.internal, unique_id, 128);
   API_NCCL(g_nccl.init_rank(&m->nccl_comm, world, uid, rank));
   m->rank = rank; m->world = world;
+  if (!m->comm_stream) {
+    int lo = 0, hi = 0;
+    API_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));      // the collective's CTAs should be placed as soon as an SM frees up
+    API_CUDA(cudaStreamCreateWithPriority(&m->comm_stream, cudaStreamNonBlocking, hi));
+    for (int i = 0; i < CVT_MAX_STAGES; ++i) API_CUDA(cudaEventCreateWithFlags(&m->ev_seg[i], cudaEventDisableTiming));
+    API_CUDA(cudaEventCreateWithFlags(&m->ev_red, cudaEventDisableTiming));
+  }
   clear_graphs(m);
   return CVT_OK;
 }
 int cvt_comm_destroy(cvt_model* h) {
   if (!h) return CVT_ERR_INVALID;
   Model* m = &h->m;
+  if (m->comm_stream) cudaStreamSynchronize(m->comm_stream);
+  if (m->peer_ready) {
+    if (m->stream) cudaStreamSynchronize(m->stream);
+    for (int p = 0; p < CVT_MAX_PEERS; ++p) if (m->peer_base[p] && p != m->rank) cudaIpcCloseMemHandle(m->peer_base[p]);
+    for (int p = 0; p < CVT_MAX_PEERS; ++p) m->peer_base[p] = nullptr;
+    m->peer_ready = false;
+  }
   if (m->nccl_comm && g_nccl.destroy) { g_nccl.destroy(m->nccl_comm); m->nccl_comm = nullptr; }
+  if (m->comm_stream) { cudaStreamDestroy(m->comm_stream); m->comm_stream = nullptr; }
+  for (int i = 0; i < CVT_MAX_STAGES; ++i) if (m->ev_seg[i]) { cudaEventDestroy(m->ev_seg[i]); m->ev_seg[i] = nullptr; }
+  if (m->ev_red) { cudaEventDestroy(m->ev_red); m->ev_red = nullptr; }
   m->world = 1; m->rank = 0;
+  clear_graphs(m);
+  return CVT_OK;
+}
+int cvt_comm_peer_export(cvt_model* h, uint8_t handle_out[64]) {
+  if (!h || !handle_out) { set_error("cvt_comm_peer_export: null argument"); return CVT_ERR_INVALID; }
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  Model* m = &h->m;
+  API_CUDA(cudaSetDevice(m->cfg.device));
+  cudaIpcMemHandle_t hd;
+  API_CUDA(cudaIpcGetMemHandle(&hd, m->workspace));
+  memcpy(handle_out, &hd, 64);
+  return CVT_OK;
+}
+int cvt_comm_peer_open(cvt_model* h, const uint8_t* handles, int sync_grads) {
+  if (!h || !handles) { set_error("cvt_comm_peer_open: null argument"); return CVT_ERR_INVALID; }
+  Model* m = &h->m;
+  if (m->world < 2 || m->world > CVT_MAX_PEERS) { set_error("cvt_comm_peer_open: needs cvt_comm_init with 2.." + std::to_string(CVT_MAX_PEERS) + " ranks first"); return CVT_ERR_STATE; }
+  if (m->peer_ready) return CVT_OK;
+  API_CUDA(cudaSetDevice(m->cfg.device));
+  for (int p = 0; p < m->world; ++p) {
+    if (p == m->rank) { m->peer_base[p] = m->workspace; continue; }
+    cudaIpcMemHandle_t hd; memcpy(&hd, handles + 64 * p, 64);
+    const cudaError_t e = cudaIpcOpenMemHandle(&m->peer_base[p], hd, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+      set_error(std::string("cvt_comm_peer_open: cudaIpcOpenMemHandle of rank ") + std::to_string(p) + ": " + cudaGetErrorString(e));
+      for (int q = 0; q < p; ++q) if (q != m->rank && m->peer_base[q]) cudaIpcCloseMemHandle(m->peer_base[q]);
+      for (int q = 0; q < CVT_MAX_PEERS; ++q) m->peer_base[q] = nullptr;
+      (void)cudaGetLastError();
+      return CVT_ERR_CUDA;
+    }
+  }
+  m->dp_sync_grads = sync_grads ? 1 : 0; m->dp_epoch = 0;
+  API_CUDA(cudaMemsetAsync(m->dp_flags, 0, 64 * sizeof(uint32_t), m->stream));
+  API_CUDA(cudaStreamSynchronize(m->stream));
+  m->peer_ready = true;
   clear_graphs(m);
   return CVT_OK;
 }
@@ -1201,51 +1266,128 @@ int64_t cvt_optimizer_step_count(const cvt_model* h) { return h ? h->m.adam_t : 
 enum { GRAPH_TRAIN = 0, GRAPH_INFER = 1, GRAPH_INFER_CACHED = 2 };
 static Model::GraphEntry* graph_slot(Model* m, int kind, const float* img, const float* proc, const float* y, int B) {
   for (auto& g : m->graphs) if (g.kind == kind && g.img == img && g.proc == proc && g.y == y && g.batch == B) return &g;
-  if (m->graphs.size() >= 16) { if (m->graphs.front().exec) cudaGraphExecDestroy(m->graphs.front().exec); m->graphs.erase(m->graphs.begin()); }
-  m->graphs.push_back(Model::GraphEntry{kind, img, proc, y, B, nullptr, 0});
+  if (m->graphs.size() >= 16) {
+    if (m->graphs.front().exec) cudaGraphExecDestroy(m->graphs.front().exec);
+    for (auto e : m->graphs.front().seg) if (e) cudaGraphExecDestroy(e);
+    m->graphs.erase(m->graphs.begin());
+  }
+  m->graphs.push_back(Model::GraphEntry{kind, img, proc, y, B, nullptr, 0, {}});
   return nullptr;                                        // first sighting: the caller runs eagerly (also warms every lazy initialiser)
 }
 
 // the stream work of one train step; per-step scalars come from m->lr_dev (set by the caller), so the sequence can be replayed.
-// parts: 1 = forward + loss + backward, 2 = gradient all-reduce + Adam.  With more than one rank only part 1 is captured into the
-// graph: the NCCL collective is issued on the stream directly after the replay.
-static int train_step_body(Model* m, const float* img, const float* proc, const float* y, int B, int parts) {
+static int train_step_body(Model* m, const float* img, const float* proc, const float* y, int B) {
   m->dyn = m->lr_dev;
   int rc = CVT_OK;
   do {
-    if (parts & 1) {
-      m->cur_y = y;                                      // the head kernel also emits loss, MAE and d pred (mse_loss_kernel otherwise)
-      const cudaError_t ef = forward_impl(m, img, proc, B, 1);
-      m->cur_y = nullptr;
-      if (ef != cudaSuccess) { rc = CVT_ERR_CUDA; break; }
-      if (backward_impl(m, img, proc, B, 1, -1, nullptr) != cudaSuccess) { rc = CVT_ERR_CUDA; break; }
-    }
-    if (parts & 2) {
-      if (m->nccl_comm && m->world > 1) {
-        // data parallel: sum of per-rank mean-loss gradients / world == gradient of the global-batch mean loss
-        const int r = g_nccl.allreduce(m->G, m->G, (size_t)m->n_train, /*ncclFloat32*/ 7, /*ncclSum*/ 0, m->nccl_comm, m->stream);
-        if (r != 0) { set_error(std::string("ncclAllReduce: ") + (g_nccl.errstr ? g_nccl.errstr(r) : "nccl error")); rc = CVT_ERR_NCCL; break; }
-      }
-      if (launch_adam(m->P, m->G, m->Mo, m->Vo, m->n_train, 0.f, 0.9f, 0.999f, 1e-7f, 1.f, m->stream, m->dyn) != cudaSuccess) { rc = CVT_ERR_CUDA; break; }
-    }
+    m->cur_y = y;                                      // the head kernel also emits loss, MAE and d pred (mse_loss_kernel otherwise)
+    const cudaError_t ef = forward_impl(m, img, proc, B, 1);
+    m->cur_y = nullptr;
+    if (ef != cudaSuccess) { rc = CVT_ERR_CUDA; break; }
+    if (backward_impl(m, img, proc, B, 1, -1, nullptr) != cudaSuccess) { rc = CVT_ERR_CUDA; break; }
+    if (launch_adam(m->P, m->G, m->Mo, m->Vo, m->n_train, 0.f, 0.9f, 0.999f, 1e-7f, 1.f, m->stream, m->dyn) != cudaSuccess) { rc = CVT_ERR_CUDA; break; }
   } while (0);
   m->dyn = nullptr;
   return rc;
+}
+
+// ---- data parallel: the step in n_stages segments, one gradient bucket each ------------------------------------------------------------
+// segment 0 = forward + loss + head backward + backward of the last stage, segment k = backward of stage n-1-k.  When segment k has been
+// issued its stage's gradients are final (the folded attention weights are unfolded per stage), so bucket k - the stage's slice of the
+// flat gradient arena, the head riding with the last stage: 77 % / 19 % / 4 % of the bytes at the reference sizes - is all-reduced on
+// comm_stream while the main stream runs the earlier stages.  Adam waits for the last bucket.
+// number of segments / buckets: one per stage unless CVT_DP_SEGMENTS asks for fewer (1 = a single reduction after the backward pass);
+// segment k covers stages hi..lo
+static int dp_segments(const Model* m) {
+  static const int env = getenv("CVT_DP_SEGMENTS") ? atoi(getenv("CVT_DP_SEGMENTS")) : 0;
+  if (m->peer_ready) return 1;                         // peer-memory tail: nothing to overlap, one forward + backward graph
+  return env >= 1 && env < m->n_stages ? env : m->n_stages;
+}
+static void dp_segment_range(const Model* m, int k, int* hi, int* lo) {
+  const int nseg = dp_segments(m);
+  *hi = m->n_stages - 1 - k;
+  *lo = k == nseg - 1 ? 0 : *hi;
+}
+static int train_segment(Model* m, const float* img, const float* proc, const float* y, int B, int k) {
+  m->dyn = m->lr_dev;
+  int rc = CVT_OK;
+  int hi_s, lo_s; dp_segment_range(m, k, &hi_s, &lo_s);
+  if (k == 0) {
+    m->cur_y = y;
+    const cudaError_t ef = forward_impl(m, img, proc, B, 1);
+    m->cur_y = nullptr;
+    if (ef != cudaSuccess) rc = CVT_ERR_CUDA;
+  }
+  if (rc == CVT_OK && backward_range(m, img, proc, B, 1, hi_s, lo_s, dp_segments(m) > 1, -1, nullptr) != cudaSuccess) rc = CVT_ERR_CUDA;
+  m->dyn = nullptr;
+  return rc;
+}
+static int reduce_bucket(Model* m, int k) {
+  int hi_s, lo_s; dp_segment_range(m, k, &hi_s, &lo_s);
+  const int64_t lo = m->w[lo_s].conv_w, hi = k == 0 ? m->n_train : m->w[hi_s + 1].conv_w;      // a stage's parameters are contiguous, ConvEmbed kernel first
+  API_CUDA(cudaEventRecord(m->ev_seg[k], m->stream));
+  API_CUDA(cudaStreamWaitEvent(m->comm_stream, m->ev_seg[k], 0));
+  // sum of per-rank mean-loss gradients; the 1 / world factor is folded into the Adam update (gradient scale in lr_dev)
+  const int r = g_nccl.allreduce(m->G + lo, m->G + lo, (size_t)(hi - lo), /*ncclFloat32*/ 7, /*ncclSum*/ 0, m->nccl_comm, m->comm_stream);
+  if (r != 0) { set_error(std::string("ncclAllReduce: ") + (g_nccl.errstr ? g_nccl.errstr(r) : "nccl error")); return CVT_ERR_NCCL; }
+  // ... and the bucket's Adam update follows on the same stream: the remaining backward reads neither these weights nor these gradients,
+  // so only the first stage's small bucket (4 % of the bytes) is reduced and stepped after the backward pass has ended
+  API_CUDA(launch_adam(m->P + lo, m->G + lo, m->Mo + lo, m->Vo + lo, hi - lo, 0.f, 0.9f, 0.999f, 1e-7f, 1.f, m->comm_stream, m->lr_dev));
+  return CVT_OK;
+}
+static int train_step_dp(Model* m, const float* img, const float* proc, const float* y, int B, Model::GraphEntry* g, bool philox, uint32_t step) {
+  const int nseg = dp_segments(m);
+  if (g && !g->exec) {                                  // second sighting: capture every segment into its own graph
+    const long long l0 = g_launch_count;
+    cudaGraphExec_t ex[CVT_MAX_STAGES] = {};
+    int rc = CVT_OK;
+    for (int k = 0; k < nseg && rc == CVT_OK; ++k) {
+      cudaGraph_t graph = nullptr;
+      API_CUDA(cudaStreamBeginCapture(m->stream, cudaStreamCaptureModeThreadLocal));
+      rc = train_segment(m, img, proc, y, B, k);
+      const cudaError_t e = cudaStreamEndCapture(m->stream, &graph);
+      if (rc == CVT_OK && (e != cudaSuccess || !graph)) { set_error(std::string("train segment capture: ") + cudaGetErrorString(e)); rc = CVT_ERR_CUDA; }
+      if (rc == CVT_OK && cudaGraphInstantiate(&ex[k], graph, 0) != cudaSuccess) { set_error("cudaGraphInstantiate (train segment) failed"); rc = CVT_ERR_CUDA; }
+      if (graph) cudaGraphDestroy(graph);
+    }
+    m->dropout_step = step;                             // forward_impl advanced it while capturing; the replay below counts
+    if (rc != CVT_OK) { for (int k = 0; k < nseg; ++k) if (ex[k]) cudaGraphExecDestroy(ex[k]); cudaGetLastError(); return rc; }
+    g->exec = ex[0];
+    for (int k = 1; k < nseg; ++k) g->seg[k] = ex[k];
+    g->launches = g_launch_count - l0;
+    g_launch_count = l0;
+  }
+  const bool replay = g && g->exec;
+  for (int k = 0; k < nseg; ++k) {
+    if (replay) API_CUDA(cudaGraphLaunch(k == 0 ? g->exec : g->seg[k], m->stream));
+    else { const int rc = train_segment(m, img, proc, y, B, k); if (rc != CVT_OK) return rc; }
+    if (!m->peer_ready) { const int rr = reduce_bucket(m, k); if (rr != CVT_OK) return rr; }
+  }
+  if (replay) {
+    g_launch_count += g->launches;
+    if (philox) m->dropout_step = step + 1;
+    m->last_batch = B; m->last_training = 1; m->have_forward = 1;
+  }
+  if (m->peer_ready) { API_CUDA(launch_dp_reduce_adam(m, m->stream)); return CVT_OK; }
+  API_CUDA(cudaEventRecord(m->ev_red, m->comm_stream));
+  API_CUDA(cudaStreamWaitEvent(m->stream, m->ev_red, 0));      // the next step (and any reader of the weights) follows the last bucket's update
+  return CVT_OK;
 }
 
 static int train_step_dev(Model* m, const float* img, const float* proc, const float* y, int B, float lr) {
   const bool philox = m->dropout_mode == CVT_DROPOUT_PHILOX && m->cfg.drop_rate > 0.f;
   const uint32_t step = m->dropout_step;
   m->adam_t += 1;
-  const float gs = (m->nccl_comm && m->world > 1) ? 1.f / (float)m->world : 1.f;
+  const bool dp = m->nccl_comm && m->world > 1;
+  const float gs = dp ? 1.f / (float)m->world : 1.f;
   API_CUDA(launch_set_step_params(m->lr_dev, adam_alpha(m, lr), gs, step, m->stream));
-  const int graph_parts = (m->nccl_comm && m->world > 1) ? 1 : 3;
   Model::GraphEntry* g = (m->use_graphs && !g_prof) ? graph_slot(m, GRAPH_TRAIN, img, proc, y, B) : nullptr;
+  if (dp) return train_step_dp(m, img, proc, y, B, g, philox, step);
   if (g && !g->exec) {
     const long long l0 = g_launch_count;
     cudaGraph_t graph = nullptr;
     API_CUDA(cudaStreamBeginCapture(m->stream, cudaStreamCaptureModeThreadLocal));
-    const int rc = train_step_body(m, img, proc, y, B, graph_parts);
+    const int rc = train_step_body(m, img, proc, y, B);
     const cudaError_t e = cudaStreamEndCapture(m->stream, &graph);
     m->dropout_step = step;                              // forward_impl advanced it while capturing; the replay below counts
     if (rc != CVT_OK || e != cudaSuccess || !graph) {
@@ -1265,9 +1407,9 @@ static int train_step_dev(Model* m, const float* img, const float* proc, const f
     g_launch_count += g->launches;
     if (philox) m->dropout_step = step + 1;
     m->last_batch = B; m->last_training = 1; m->have_forward = 1;
-    return graph_parts == 3 ? CVT_OK : train_step_body(m, img, proc, y, B, 2);
+    return CVT_OK;
   }
-  return train_step_body(m, img, proc, y, B, 3);
+  return train_step_body(m, img, proc, y, B);
 }
 
 // inference forward (training = 0) through the graph cache; falls back to eager issue on first sighting.

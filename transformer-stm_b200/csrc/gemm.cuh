@@ -82,7 +82,8 @@ struct MgDesc {
   int round;      // store round-to-nearest TF32 (the result is a tensor-core operand)
 };
 int mg_tiles(const MgDesc& d);
-cudaError_t launch_multigemm(const MgDesc* descs_dev, int ndesc, int total_tiles, cudaStream_t s);
+// tile_base: tile0 of descs_dev[0] when the launch covers a sub-range of a descriptor table (per-stage unfold)
+cudaError_t launch_multigemm(const MgDesc* descs_dev, int ndesc, int total_tiles, cudaStream_t s, int tile_base = 0);
 // dst[off + n*K + k] = src[off + k*N + n] for every registered dense kernel (forward GEMMs read their weights K-major)
 struct TrDesc { long long off; int K, N, tile0; int copy; long long toff; int ldt; };   // transposed copy at dst[toff + n*ldt + k]   // copy: dst2[off + k*N + n] = round(src) (a TF32-rounded straight copy, dgrad operand)
 cudaError_t launch_transpose_weights(const float* src, float* dst, float* dst2, const TrDesc* descs_dev, int ndesc, int total_tiles, cudaStream_t s);

@@ -28,7 +28,7 @@ struct MlpP {
 };
 
 template <int D> struct MfCfg {
-  static constexpr int RW = D == 64 ? 4 : 8;           // row warps
+  static constexpr int RW = 8;                         // row warps: warps w and w + 4 share a TMEM lane quadrant and split the 64 chunk columns
   static constexpr int NT = 64 + 32 * RW;
   static constexpr int KB = D / 32;                    // 32-float boxes along the LayerNorm / fc1 contraction axis
   static constexpr int Y_BYTES = 128 * D * 4;
@@ -54,15 +54,16 @@ __device__ __forceinline__ bool elect_one_mf() {
   return pred != 0;
 }
 
-// erf-GELU from one exponential (Abramowitz & Stegun 7.1.26, |error| <= 1.5e-7): the forward half of gelu_and_grad (common.cuh)
+// erf-GELU from one exponential (Abramowitz & Stegun 7.1.26, |error| <= 1.5e-7, as gelu_and_grad in common.cuh), without a select:
+// x Phi(x) = max(x, 0) - |x| * (erfc(|x| / sqrt 2) / 2); the 1/2 is folded into the polynomial coefficients
 __device__ __forceinline__ float gelu_fast(float x) {
-  const float z = fabsf(x) * 0.70710678118654752440f;
+  const float ax = fabsf(x);
+  const float z = ax * 0.70710678118654752440f;
   const float t = __fdividef(1.0f, fmaf(0.3275911f, z, 1.0f));
-  const float e = __expf(-z * z);
-  float q = fmaf(t, 1.061405429f, -1.453152027f);
-  q = fmaf(q, t, 1.421413741f); q = fmaf(q, t, -0.284496736f); q = fmaf(q, t, 0.254829592f);
-  const float half_erfc = 0.5f * q * t * e;
-  return x * (x >= 0.f ? 1.0f - half_erfc : half_erfc);
+  const float e = fast_ex2(-1.4426950408889634f * z * z);
+  float q = fmaf(t, 0.5f * 1.061405429f, 0.5f * -1.453152027f);
+  q = fmaf(q, t, 0.5f * 1.421413741f); q = fmaf(q, t, 0.5f * -0.284496736f); q = fmaf(q, t, 0.5f * 0.254829592f);
+  return fmaf(-ax, q * t * e, fmaxf(x, 0.f));
 }
 
 template <int D>
@@ -88,6 +89,10 @@ __global__ void __launch_bounds__(MfCfg<D>::NT, D == 64 ? 2 : 1) mlp_fused_kerne
     tma_prefetch_desc(&tmX); tma_prefetch_desc(&tmW1); tma_prefetch_desc(&tmW2);
     for (int i = 0; i < MB_COUNT; ++i) mbar_init(&bars[i], (i == MB_YF || i == MB_GF || i == MB_GF + 1) ? RW * 32 : 1);
     mbar_fence_init();
+    // the token tile is requested before the CTA has even finished setting up (parameter staging, TMEM allocation overlap its flight)
+    mbar_arrive_expect_tx(&bars[MB_XF], C::Y_BYTES);
+#pragma unroll
+    for (int kb = 0; kb < KB; ++kb) tma_load_3d(sY + kb * 16384, &tmX, &bars[MB_XF], kb * 32, row0, 0);
   }
   if (warp == 1) tmem_alloc(tmem_slot, C::TMEM_COLS);
   for (int i = tid; i < D; i += NT) { sG[i] = __ldg(p.gamma + i); sBe[i] = __ldg(p.beta + i); sB2[i] = __ldg(p.b2 + i); }
@@ -100,9 +105,6 @@ __global__ void __launch_bounds__(MfCfg<D>::NT, D == 64 ? 2 : 1) mlp_fused_kerne
   if (warp == 0) {
     // ===== TMA producer =====
     if (lane == 0) {
-      mbar_arrive_expect_tx(&bars[MB_XF], C::Y_BYTES);
-#pragma unroll
-      for (int kb = 0; kb < KB; ++kb) tma_load_3d(sY + kb * 16384, &tmX, &bars[MB_XF], kb * 32, row0, 0);
       for (int c = 0; c < nchunks; ++c) {
         const int st = c & 1; const uint32_t ph = (c >> 1) & 1;
         uint8_t* sg = ring + st * C::STAGE;
@@ -211,11 +213,23 @@ __global__ void __launch_bounds__(MfCfg<D>::NT, D == 64 ? 2 : 1) mlp_fused_kerne
       tc_fence_before();
       mbar_arrive(&bars[MB_GF + st]);
     }
-    // ===== epilogue: x2 = O + b2 + x1, 32 x 32 blocks through a padded transpose tile (the weight ring is idle by now) =====
+    // ===== epilogue: x2 = O + b2 + x1, 32 x 32 blocks through a padded transpose tile (the weight ring is idle by now).  The residual
+    // rows are fetched (from L2: the tile was just read) before the wait for the last fc2 product, lane = column =====
+    constexpr int NBLK = D / 32 / (RW / 4);            // 32-column blocks of O per warp
+    float res[NBLK][32];
+#pragma unroll
+    for (int blk = 0; blk < NBLK; ++blk) {
+      const int col = (half * NBLK + blk) * 32 + lane;
+#pragma unroll
+      for (int rr = 0; rr < 32; ++rr) {
+        const int row = min(row0 + quad * 32 + rr, p.R - 1);
+        res[blk][rr] = __ldg(p.x1 + (long long)row * D + col) + sB2[col];
+      }
+    }
     mbar_wait(&bars[MB_DONE], 0);
     tc_fence_after();
     float* stg = reinterpret_cast<float*>(ring) + (warp - 2) * (32 * 33);
-    constexpr int NBLK = D / 32 / (RW / 4);            // 32-column blocks of O per warp
+#pragma unroll
     for (int blk = 0; blk < NBLK; ++blk) {
       const int cb = half * NBLK + blk;
       float v[32];
@@ -224,11 +238,10 @@ __global__ void __launch_bounds__(MfCfg<D>::NT, D == 64 ? 2 : 1) mlp_fused_kerne
       for (int i = 0; i < 32; ++i) stg[lane * 33 + i] = v[i];
       __syncwarp();
       const int col = cb * 32 + lane;
-      const float b2 = sB2[col];
-#pragma unroll 8
+#pragma unroll
       for (int rr = 0; rr < 32; ++rr) {
         const int row = row0 + quad * 32 + rr;
-        if (row < p.R) p.x2[(long long)row * D + col] = stg[rr * 33 + lane] + b2 + __ldg(p.x1 + (long long)row * D + col);
+        if (row < p.R) p.x2[(long long)row * D + col] = stg[rr * 33 + lane] + res[blk][rr];
       }
       __syncwarp();
     }

@@ -112,11 +112,17 @@ struct Model {
   // data parallel
   void* nccl_comm = nullptr;
   int rank = 0, world = 1;
+  // peer-memory step tail (dp_peer.cu): every rank's workspace mapped through cudaIpc; flags live in the workspace too
+  void* peer_base[CVT_MAX_PEERS] = {}; bool peer_ready = false; uint32_t* dp_flags = nullptr; uint32_t dp_epoch = 0; int dp_sync_grads = 0;
+  // gradient buckets (one per stage, the last one with the head): reduced on comm_stream while the earlier stages' backward still runs
+  cudaStream_t comm_stream = nullptr; cudaEvent_t ev_seg[CVT_MAX_STAGES] = {}, ev_red = nullptr;
+  int mg_bwd_first[CVT_MAX_STAGES] = {}, mg_bwd_cnt[CVT_MAX_STAGES] = {}, mg_bwd_tile0[CVT_MAX_STAGES] = {}, mg_bwd_ntiles[CVT_MAX_STAGES] = {};
 
   // CUDA graphs
   // A step is first run eagerly for a given (kind, buffers, batch); the second time it is captured, afterwards replayed.
   // Per-step scalars (Adam step size, gradient scale, dropout counter) live in lr_dev so that replays see fresh values.
-  struct GraphEntry { int kind; const float* img; const float* proc; const float* y; int batch; cudaGraphExec_t exec; long long launches; };
+  struct GraphEntry { int kind; const float* img; const float* proc; const float* y; int batch; cudaGraphExec_t exec; long long launches;
+                      cudaGraphExec_t seg[CVT_MAX_STAGES]; };      // data parallel: exec = forward + head + last stage's backward, seg[k] = the k-th earlier stage
   int use_graphs = 1;
   bool premasked = false;                 // backward: gM already holds dX2 * mask2 / keep of the stage about to run (written by col2im)
   bool mlp_fused_last = false;            // the last forward ran the fused inference Mlp: y / hpre / hact were not materialised
@@ -133,6 +139,9 @@ cudaError_t attention_backward(Model* m, int si, int B, const float* dO, float* 
 // fused inference Mlp (mlp_fused.cu): x2 = x1 + fc2(gelu(fc1(norm1(x1)))) in one kernel, the hidden activation stays in TMEM
 bool mlp_fused_supports(const Model* m, int si);
 cudaError_t launch_mlp_fused(const Model* m, int si, int R, cudaStream_t s);
+
+// gradient reduce-scatter + Adam + weight all-gather over peer memory, one kernel (dp_peer.cu)
+cudaError_t launch_dp_reduce_adam(Model* m, cudaStream_t s);
 
 // contraction dispatch by precision (fp32 FFMA vs tcgen05)
 cudaError_t run_gemm(const Model* m, const GemmP& p, cudaStream_t s);

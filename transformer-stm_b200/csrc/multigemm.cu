@@ -12,12 +12,13 @@ namespace {
 // 64 x 64 tile, K chunks of 32, 256 threads (4 x 4 outputs each).  Operand chunks are fetched as float4s along whichever index is
 // contiguous in memory and prefetched into registers while the previous chunk is multiplied out of shared memory.
 // Shapes: K % 8 == 0; a dimension read along its contiguous axis must be a multiple of 4 (all sizes here are 1 or multiples of 64).
-__global__ void __launch_bounds__(256) multigemm_kernel(const MgDesc* __restrict__ descs, int ndesc) {
+__global__ void __launch_bounds__(256) multigemm_kernel(const MgDesc* __restrict__ descs, int ndesc, int tile_base) {
   __shared__ __align__(16) float sA[32][68], sB[32][68];
+  const int bid = (int)blockIdx.x + tile_base;          // tile0 of the descriptors is absolute; a launch may cover a sub-range of the table
   int d = 0;
-  while (d + 1 < ndesc && (int)blockIdx.x >= descs[d + 1].tile0) ++d;
+  while (d + 1 < ndesc && bid >= descs[d + 1].tile0) ++d;
   const MgDesc e = descs[d];
-  const int tile = blockIdx.x - e.tile0, tn = cdiv(e.N, 64);
+  const int tile = bid - e.tile0, tn = cdiv(e.N, 64);
   const int m0 = (tile / tn) * 64, n0 = (tile % tn) * 64;
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;      // thread computes rows ty*4.., cols tx*4..
   float acc[4][4];
@@ -111,9 +112,9 @@ __global__ void __launch_bounds__(256) multigemm_kernel(const MgDesc* __restrict
 
 int mg_tiles(const MgDesc& d) { return cdiv(d.M, 64) * cdiv(d.N, 64); }
 
-cudaError_t launch_multigemm(const MgDesc* descs_dev, int ndesc, int total_tiles, cudaStream_t s) {
+cudaError_t launch_multigemm(const MgDesc* descs_dev, int ndesc, int total_tiles, cudaStream_t s, int tile_base) {
   if (ndesc < 1 || total_tiles < 1) return cudaSuccess;
-  multigemm_kernel<<<total_tiles, 256, 0, s>>>(descs_dev, ndesc);
+  multigemm_kernel<<<total_tiles, 256, 0, s>>>(descs_dev, ndesc, tile_base);
   CVT_LAUNCH_CHECK();
   return cudaSuccess;
 }

@@ -38,8 +38,9 @@ def broadcast_weights(engine, dist, device=None, src: int = 0):
     engine.set_params(new)
 
 
-def init_data_parallel(engine, dist, rank: int, world: int, device=None):
-    """NCCL communicator inside the library (unique id made on rank 0, broadcast by torch.distributed) + identical initial weights."""
+def init_data_parallel(engine, dist, rank: int, world: int, device=None, peer_memory: bool = True, sync_grads: bool = False):
+    """NCCL communicator inside the library (unique id made on rank 0, broadcast by torch.distributed) + identical initial weights, then
+    (inside one box, world <= 8) the peer-memory mapping that replaces the per-step ncclAllReduce."""
     import torch
     uid = torch.zeros(128, dtype=torch.uint8, device=device)
     if rank == 0:
@@ -47,20 +48,53 @@ def init_data_parallel(engine, dist, rank: int, world: int, device=None):
     dist.broadcast(uid, 0)
     engine.comm_init(bytes(uid.cpu().tolist()), rank, world)
     broadcast_weights(engine, dist, device)
+    if peer_memory and 2 <= world <= 8:
+        open_peer_memory(engine, dist, rank, world, device, sync_grads)
 
 
-def param_checksum(engine) -> np.ndarray:
-    """[sum, sum of squares, sum of |x| weighted by position] over all weights in float64: equal on two ranks iff (practically) the weights are."""
+def open_peer_memory(engine, dist, rank: int, world: int, device=None, sync_grads: bool = False) -> bool:
+    """Exchanges the cudaIpc handles of the ranks' workspaces (all_gather through torch.distributed) and maps them: the train step then ends
+    in ONE kernel that reduce-scatters the gradients, applies Adam to the rank's slice and all-gathers the weights over NVLink peer memory
+    (csrc/dp_peer.cu) instead of ncclAllReduce + a full Adam pass.  All ranks must agree on the outcome, so the success flags are reduced:
+    if any rank cannot map its peers (no P2P between the devices) every rank stays on the NCCL path.  CVT_DP_NCCL=1 forces NCCL."""
+    import os
+    import torch
+    if os.environ.get("CVT_DP_NCCL"):
+        return False
+    mine = torch.tensor(list(engine.comm_peer_export()), dtype=torch.uint8, device=device)
+    parts = [torch.zeros_like(mine) for _ in range(world)]
+    dist.all_gather(parts, mine)
+    handles = b"".join(bytes(p.cpu().tolist()) for p in parts)
+    ok = torch.ones(1, dtype=torch.int32, device=device)
+    try:
+        engine.comm_peer_open(handles, sync_grads)
+    except Exception:                      # noqa: BLE001 - reported below, decided collectively
+        ok.zero_()
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    if int(ok.item()) == 0:
+        raise RuntimeError("peer-memory data parallelism: a rank could not map its peers' workspaces (set CVT_DP_NCCL=1 to use NCCL only)")
+    return True
+
+
+def param_checksum(engine, trainable: bool = True) -> np.ndarray:
+    """[sum, sum of squares, sum of |x| weighted by position] in float64 over the trainable weights (or, trainable=False, over the BatchNorm
+    moving statistics): equal on two ranks iff (practically) those weights are.  The two groups are checked apart because BatchNorm is per
+    replica (Keras MirroredStrategy batch statistics): every rank sees its own shard, so the moving statistics legitimately differ between
+    ranks (rank 0's are the ones saved), while the trainable weights must stay bit-identical."""
     p = engine.get_params()
-    flat = np.concatenate([np.asarray(v, dtype=np.float64).reshape(-1) for v in p.values()])
+    state = ("moving_mean", "moving_variance")
+    keep = [v for k, v in p.items() if (k.rsplit("/", 1)[-1] in state) != trainable]
+    if not keep:
+        return np.zeros(3)
+    flat = np.concatenate([np.asarray(v, dtype=np.float64).reshape(-1) for v in keep])
     w = 1.0 + (np.arange(flat.size, dtype=np.float64) % 977) / 977.0
     return np.array([flat.sum(), (flat * flat).sum(), (np.abs(flat) * w).sum()])
 
 
-def replica_divergence(engine, dist, world: int, device=None) -> float:
+def replica_divergence(engine, dist, world: int, device=None, trainable: bool = True) -> float:
     """max over ranks and checksum components of |checksum(rank) - checksum(rank 0)|; 0.0 means the replicas hold identical weights."""
     import torch
-    c = torch.as_tensor(param_checksum(engine))
+    c = torch.as_tensor(param_checksum(engine, trainable))
     if device is not None:
         c = c.to(device)
     out = [torch.zeros_like(c) for _ in range(world)]

@@ -400,6 +400,17 @@ class CvtEngine:
         buf = (C.c_uint8 * 128).from_buffer_copy(unique_id)
         L.check(self.lib.cvt_comm_init(self.h, buf, rank, world), "cvt_comm_init")
 
+    def comm_peer_export(self) -> bytes:
+        """64-byte cudaIpc handle of this rank's workspace (cvt_comm_peer_export)."""
+        buf = (C.c_uint8 * 64)()
+        L.check(self.lib.cvt_comm_peer_export(self.h, buf), "cvt_comm_peer_export")
+        return bytes(buf)
+
+    def comm_peer_open(self, handles: bytes, sync_grads: bool = False):
+        """handles: world x 64 bytes in rank order; afterwards the train step ends in the peer-memory reduce + Adam + all-gather kernel."""
+        buf = (C.c_uint8 * len(handles)).from_buffer_copy(handles)
+        L.check(self.lib.cvt_comm_peer_open(self.h, buf, int(sync_grads)), "cvt_comm_peer_open")
+
     # ---- misc ----
     def synchronize(self):
         L.check(self.lib.cvt_synchronize(self.h))
