@@ -97,19 +97,21 @@ def stage_geo(hw, dims, heads, cls_last=True):
 
 
 def group_work(geo, batch, mlp_ratio=4):
-    """{group: (flops, bytes)} per launch-group for a forward pass over `batch` images, as the kernels are split TODAY (the hidden layer
-    of the Mlp and the q/k/v intermediates count): the denominator of the per-group roofline fraction."""
+    """{group: (flops, bytes)} per kernel group for a forward pass over `batch` images: ALGORITHMIC work of the perfectly fused group as
+    SURVEY 8d's table counts it (activations read + written once at fp32: K1 input map + T*D, K2 4 T*D, K3 6, K4 4, K5 3, K6 2) - not the
+    traffic of the kernels as they happen to be split, so that an unfused group cannot flatter its roofline fraction."""
     out = {}
     for i, g in enumerate(geo, 1):
         T, Tc, D, H = g["t"], g["tc"], g["d"], g["heads"]
         kk = g["k"] * g["k"] * g["cin"]
         B = batch
+        e = 4.0 * B * Tc * D
         out["s%d.conv_embed" % i] = (2.0 * B * T * kk * D, 4.0 * B * (g["hin"] * g["win"] * g["cin"] + T * D))
-        out["s%d.ln_proj_bn" % i] = (B * Tc * D * (8 + 3 * 22.0), 4.0 * B * Tc * D * 5)            # read x0, write xn + 3 conv maps
-        out["s%d.qkv_gemm" % i] = (2.0 * B * Tc * D * D * 6, 4.0 * B * Tc * D * 9)                 # 3 in, 3 mid (kept for bwd), 3 out
-        out["s%d.attention" % i] = (4.0 * B * H * Tc * Tc * 64, 4.0 * B * Tc * D * 4)
-        out["s%d.out_gemm" % i] = (2.0 * B * Tc * D * D * 2, 4.0 * B * Tc * D * 4)
-        out["s%d.mlp" % i] = (2.0 * B * Tc * D * D * mlp_ratio * 2 + 8.0 * B * Tc * D, 4.0 * B * Tc * D * (3 + 2 * mlp_ratio))
+        out["s%d.ln_proj_bn" % i] = (B * Tc * D * (8 + 3 * 22.0), 4 * e)
+        out["s%d.qkv_gemm" % i] = (2.0 * B * Tc * D * D * 6, 6 * e)
+        out["s%d.attention" % i] = (4.0 * B * H * Tc * Tc * 64, 4 * e)
+        out["s%d.out_gemm" % i] = (2.0 * B * Tc * D * D * 2, 3 * e)
+        out["s%d.mlp" % i] = (2.0 * B * Tc * D * D * mlp_ratio * 2 + 8.0 * B * Tc * D, 2 * e)
     return out
 
 
