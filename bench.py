@@ -143,6 +143,7 @@ def parse():
     ap.add_argument("--sweep", action="store_true", help="configs[3]: inference at batch 1, 2, 4, ..., 4096 per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--no-batch128", action="store_true", help="skip the extra batch-128 measurement of the default cfg2 line")
     ap.add_argument("--no-flush", action="store_true", help="do not flush L2 between timed steps")
     return ap.parse_args()
 
@@ -470,6 +471,17 @@ def main_b200(a):
                 os.write(json_fd, (json.dumps(line) + "\n").encode())
     else:
         line = run_config(a, a.config, a.batch or dbatch, modes)
+        if a.config == "cfg2" and not a.batch and a.mode == "both" and not a.no_batch128 and int(os.environ.get("WORLD_SIZE", "1")) == 1:
+            # the reference's own training batch (models/CvT(Par).py:47: 128) beside the headline batch 64: device-timed only, same protocol
+            b = Bench(a, a.config, 128)
+            extra = {}
+            for mode in ("train", "infer"):
+                r = b.timed(mode == "train", a.steps, a.warmup)
+                roof, _ = b.roofline(mode == "train", r["ms_per_step"]) if rank == 0 else (None, None)
+                extra[mode] = {"value": r["value"], "unit": UNIT, "ms_per_step": r["ms_per_step"], "step_frac": roof["step_frac"] if roof else None}
+            b.close()
+            if line is not None:
+                line["batch128"] = dict(extra, note="per-GPU batch 128 (the reference scripts' batch_size), value / ms_per_step timed like the headline")
         if rank == 0 and line is not None:
             os.write(json_fd, (json.dumps(line) + "\n").encode())
     if int(os.environ.get("WORLD_SIZE", "1")) > 1:

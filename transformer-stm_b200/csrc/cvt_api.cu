@@ -583,6 +583,18 @@ static void epi_dropout(const Model* m, GemmP& q, uint8_t* mask, int site, float
   }
 }
 
+// ConvEmbed without a patch matrix (CVT_NO_IMPLICIT_CONV=1 restores im2col + GEMM); forward and weight gradient must agree on it
+static bool conv_implicit(const Model* m, int si, int B, long long xin_bstride, int xin_boff, const float* xin) {
+  static const bool off = getenv("CVT_NO_IMPLICIT_CONV") != nullptr || getenv("CVT_NO_TMA") != nullptr;
+  if (off || !m->folded) return false;
+  const StageGeo& g = m->geo[si]; const StageFold& f = m->fold[si];
+  if (f.Kc != f.Kp) return false;
+  const ConvGeom cv{g.hin, g.win, g.cin, g.H, g.W, g.k, g.s, g.pt, g.pl, xin_bstride, xin_boff};
+  GemmP p; p.M = B * g.T; p.N = g.D; p.K = f.Kc; p.A = xin; p.a_mode = A_CONV; p.cv = cv; p.B = m->Pt + f.convt; p.ldb = f.Kp; p.b_mode = B_NK;
+  WgradP w; w.X = xin; w.conv = 1; w.cv = cv; w.Kin = f.Kc; w.dY = m->gD; w.lddy = g.D; w.N = g.D; w.tokens = B * g.T; w.dW = m->G;
+  return gemm_tma_conv_supports(p) && wgrad_tma_supports(w);
+}
+
 static cudaError_t stage_forward(Model* m, int si, const float* xin, long long xin_bstride, int xin_boff, int B, int training) {
   const StageGeo& g = m->geo[si]; const StageW& w = m->w[si]; StageBuf& a = m->buf[si];
   const cvt_config& c = m->cfg;
@@ -598,11 +610,22 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
     // ConvEmbed as explicit im2col (kept for the weight gradient) + TMA-fed GEMM against the K-major kernel copy — im2col.cu
     const StageFold& f = m->fold[si];
     const ConvGeom cv{g.hin, g.win, g.cin, g.H, g.W, g.k, g.s, g.pt, g.pl, xin_bstride, xin_boff};
-    CVT_CUDA(launch_im2col(xin, cv, B * g.T, f.Kc, f.Kp, a.col, s));
     GemmP p; p.M = B * g.T; p.N = D; p.K = f.Kp; p.A = a.col; p.lda = f.Kp; p.B = m->Pt + f.convt; p.ldb = f.Kp; p.b_mode = B_NK;
     p.C = a.x0; p.ldc = D; if (g.has_cls) p.c_map = RowMap{g.T, g.Tc, 1};
     p.bias = P + w.conv_b; p.epi = EPI_BIAS;
-    CVT_CUDA(run_gemm(m, p, s));
+    GemmP ic = p; ic.A = xin; ic.a_mode = A_CONV; ic.cv = cv; ic.K = f.Kc; ic.lda = 0;
+    // measured at batch 64: the forward gains (s2 34 -> 25 us, s3 34 -> 28 us) but the weight gradient over 32-token strided boxes is slower than
+    // over the patch matrix (s2.bwd_conv 58 -> 71 us), so training keeps im2col (CVT_IMPLICIT_CONV_TRAIN=1 switches both)
+    static const bool train_too = getenv("CVT_IMPLICIT_CONV_TRAIN") != nullptr;
+    a.conv_implicit = (!training || train_too) && conv_implicit(m, si, B, xin_bstride, xin_boff, xin);
+    if (a.conv_implicit) {
+      // implicit GEMM: the A operand is gathered tap by tap straight from the NHWC activation by strided TMA boxes (zero fill = SAME
+      // padding); no patch matrix is written or read
+      CVT_CUDA(launch_gemm_tma(ic, s));
+    } else {
+      CVT_CUDA(launch_im2col(xin, cv, B * g.T, f.Kc, f.Kp, a.col, s));
+      CVT_CUDA(run_gemm(m, p, s));
+    }
     if (g.has_cls) CVT_CUDA(launch_fill_rows(a.x0, RowMap{1, g.Tc, 0}, D, P + w.cls, B, D, s));   // :264-268
   } else
   {  // ConvEmbed: Conv2D(D, patch, stride, 'same') + bias — models/CvT(Par).py:203-212 (its LayerNorm is dead code)
@@ -1006,6 +1029,10 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
     if (g.has_cls) { CVT_CUDA(launch_copy_rows(m->gC, rowmap_none(), D, m->gD, RowMap{g.T, g.Tc, 1}, D, B * g.T, D, s)); dY = m->gC; }
     WgradP wg; wg.X = a.col; wg.ldx = f.Kp; wg.Kin = f.Kc; wg.dY = dY; wg.lddy = D; wg.N = D; wg.tokens = B * g.T;
     wg.dW = G + w.conv_w; wg.dw_bs = 0; wg.db = G + w.conv_b; wg.db_bs = 0;
+    {
+      WgradP ic = wg; ic.X = xin; ic.conv = 1; ic.cv = ConvGeom{g.hin, g.win, g.cin, g.H, g.W, g.k, g.s, g.pt, g.pl, xin_bstride, xin_boff};
+      if (a.conv_implicit) wg = ic;      // the patches are read from the activation itself (the forward wrote no patch matrix)
+    }
     CVT_CUDA(launch_wgrad_tma(wg, s));             // dW = col^T dY, db = colsum dY
     if (dXprev) {
       const StageGeo& gp = m->geo[si - 1];

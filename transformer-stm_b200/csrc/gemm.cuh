@@ -63,6 +63,7 @@ bool gemm_tc_supports(const GemmP& p);
 // persistent TMA-fed tcgen05 kernel (gemm_tma.cu): A_PLAIN x B_NK (both K-major), no split-K
 cudaError_t launch_gemm_tma(const GemmP& p, cudaStream_t s);
 bool gemm_tma_supports(const GemmP& p);
+bool gemm_tma_conv_supports(const GemmP& p);      // a_mode == A_CONV: ConvEmbed as an implicit GEMM (4-D strided TMA boxes, no im2col)
 // TMA-fed split-K weight-gradient kernel (gemm_wgrad.cu):  dW[z][Kin,N] += X[z][tokens,Kin]^T . dY[z][tokens,N],
 // db[z][N] += column sums of dY (nullable).  Both operands are read MN-major straight from their row-major activations.
 struct WgradP {
@@ -72,6 +73,9 @@ struct WgradP {
   float* dW = nullptr; long long dw_bs = 0;
   float* db = nullptr; long long db_bs = 0;
   int dbg = 0;
+  // conv != 0: X is not a matrix but the im2col view of a Conv2D input (ConvEmbed weight gradient): X(token, feature) =
+  // x_pad[b, s*i + kh, s*j + kw, c] with token = (b, i, j), feature = (kh, kw, c); boxes are strided TMA boxes of the NHWC map itself
+  int conv = 0; ConvGeom cv{0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
 };
 cudaError_t launch_wgrad_tma(const WgradP& p, cudaStream_t s);
 bool wgrad_tma_supports(const WgradP& p);

@@ -80,6 +80,15 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tma_kernel(const __grid_cons
           mbar_wait(&empty[stage], phase ^ 1);
           if (kt == 0 && itp < 30) GEMM_TRACE(8 + itp * 8 + 0);
           mbar_arrive_expect_tx(&full[stage], A_STAGE + C::B_STAGE);
+          if (p.a_mode == A_CONV) {
+            // implicit GEMM: k-step kt = (filter tap, 32-channel chunk); the 128 rows are consecutive output pixels = one strided box of the
+            // input map, addressed by where the tap falls for the tile's first pixel
+            const ConvGeom& g = p.cv;
+            const int cpt = g.cin >> 5, tap = kt / cpt, c0 = (kt - tap * cpt) << 5;
+            const int kh = tap / g.k, kw = tap - kh * g.k;
+            const int m0 = mt * BM, hw = g.ho * g.wo, b0 = m0 / hw, i0 = (m0 - b0 * hw) / g.wo;
+            tma_load_4d(sA + stage * A_STAGE, &tmA, &full[stage], c0, kw - g.pl, g.s * i0 + kh - g.pt, b0);
+          } else
           tma_load_3d(sA + stage * A_STAGE, &tmA, &full[stage], kt * BK, mt * BM, z);
           tma_load_3d(sB + stage * C::B_STAGE, &tmB, &full[stage], kt * BK, nt * BN, z);
           if (++stage == NS) { stage = 0; phase ^= 1; }
@@ -262,6 +271,37 @@ bool make_tmap_3d(CUtensorMap* out, const float* base, long long d0, long long d
   return true;
 }
 
+bool conv_tma_box(int ho, int wo, int tokens, ConvBox* box) {
+  if (wo < 1 || ho < 1 || tokens % wo != 0) return false;
+  const int rows = tokens / wo;                        // output rows per box
+  if (rows <= ho) { if (ho % rows != 0) return false; *box = ConvBox{wo, rows, 1}; }
+  else { if (rows % ho != 0) return false; *box = ConvBox{wo, ho, rows / ho}; }
+  return true;
+}
+
+bool make_tmap_conv(CUtensorMap* out, const float* base, int hin, int win, int cin, long long bstride, int batch, int stride, ConvBox box,
+                    int swizzle_mode) {
+  typedef std::tuple<const float*, int, int, int, long long, int, int, int, int, int, int> Key;
+  static thread_local std::map<Key, CUtensorMap> cache;
+  const Key key{base, hin, win, cin, bstride, batch, stride, box.bw, box.bh, box.bb, swizzle_mode};
+  auto it = cache.find(key);
+  if (it != cache.end()) { *out = it->second; return true; }
+  encode_fn_t fn = encode_fn();
+  if (!fn) { set_error("cuTensorMapEncodeTiled entry point not found"); return false; }
+  const cuuint64_t dims[4] = {(cuuint64_t)cin, (cuuint64_t)win, (cuuint64_t)hin, (cuuint64_t)batch};
+  const cuuint64_t strides[3] = {(cuuint64_t)cin * 4, (cuuint64_t)win * cin * 4, (cuuint64_t)bstride * 4};
+  // a strided dimension loads ceil(boxDim / elementStride) elements: boxDim = pixels * stride
+  const cuuint32_t bx[4] = {32, (cuuint32_t)(box.bw * stride), (cuuint32_t)(box.bh * stride), (cuuint32_t)box.bb};
+  const cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
+  if (bx[1] > 256 || bx[2] > 256 || bx[3] > 256 || stride > 8) { set_error("make_tmap_conv: box exceeds the TMA limits"); return false; }
+  const CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(base), dims, strides, bx, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, (CUtensorMapSwizzle)swizzle_mode, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled (conv) failed with code " + std::to_string((int)r)); return false; }
+  cache[key] = *out;
+  return true;
+}
+
 namespace {
 template <int BN, uint32_t E>
 cudaError_t launch_tma_cfg(const GemmP& p, cudaStream_t s) {
@@ -271,6 +311,12 @@ cudaError_t launch_tma_cfg(const GemmP& p, cudaStream_t s) {
     configured = true;
   }
   CUtensorMap tmA, tmB;
+  if (p.a_mode == A_CONV) {
+    ConvBox box;
+    if (!conv_tma_box(p.cv.ho, p.cv.wo, BM, &box)) { set_error("gemm_tma: conv geometry does not tile"); return cudaErrorInvalidValue; }
+    const int nimg = p.M / (p.cv.ho * p.cv.wo);
+    if (!make_tmap_conv(&tmA, p.A + p.cv.boff, p.cv.hin, p.cv.win, p.cv.cin, p.cv.bstride, nimg, p.cv.s, box, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
+  } else
   if (!make_tmap_3d(&tmA, p.A, p.K, p.M, p.batch, p.lda, p.a_bs0, BM, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
   if (!make_tmap_3d(&tmB, p.B, p.K, p.N, p.batch, p.ldb, p.b_bs0, BN, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
   const int m_tiles = cdiv(p.M, BM), n_tiles = p.N / BN, num_tiles = m_tiles * n_tiles * p.batch;
@@ -295,7 +341,20 @@ cudaError_t launch_transpose_weights(const float* src, float* dst, float* dst2, 
   return cudaSuccess;
 }
 
+// ConvEmbed as an implicit GEMM: 32-channel chunks per tap, 128 consecutive output pixels = whole rows or whole images
+bool gemm_tma_conv_supports(const GemmP& p) {
+  const ConvGeom& g = p.cv; ConvBox box;
+  if (p.a_mode != A_CONV || p.b_mode != B_NK || p.batch != 1 || p.splitk != 1 || p.a_map.period || p.a_scale) return false;
+  if (g.cin < 32 || (g.cin & 31) || g.s < 1 || g.s > 8 || p.K != g.k * g.k * g.cin || p.M % (g.ho * g.wo) != 0) return false;
+  if (!conv_tma_box(g.ho, g.wo, BM, &box) || box.bw * g.s > 256 || box.bh * g.s > 256) return false;
+  if (p.N % 64 != 0 || (p.ldb & 3) || (g.bstride & 3) || (g.boff & 3)) return false;
+  if ((reinterpret_cast<uintptr_t>(p.A) & 15) || (reinterpret_cast<uintptr_t>(p.B) & 15)) return false;
+  if (p.epi & (EPI_RELU | EPI_RELU_BWD | EPI_ATOMIC | EPI_SCATTER)) return false;
+  return true;
+}
+
 bool gemm_tma_supports(const GemmP& p) {
+  if (p.a_mode == A_CONV) return gemm_tma_conv_supports(p);
   if (p.a_mode != A_PLAIN || p.b_mode != B_NK || p.a_map.period || p.a_scale || p.splitk != 1 || p.bdiv != 1) return false;
   if (p.N % 64 != 0 || p.K % 4 != 0 || p.M < 1 || (p.lda & 3) || (p.ldb & 3) || (p.a_bs0 & 3) || (p.b_bs0 & 3)) return false;
   if ((reinterpret_cast<uintptr_t>(p.A) & 15) || (reinterpret_cast<uintptr_t>(p.B) & 15)) return false;

@@ -74,7 +74,15 @@ __global__ void __launch_bounds__(NTHREADS, 1) wgrad_tma_kernel(const __grid_con
         mbar_wait(&empty[stage], phase ^ 1);
         mbar_arrive_expect_tx(&full[stage], C::A_STAGE + C::B_STAGE);
 #pragma unroll
-        for (int b = 0; b < BM / 32; ++b) tma_load_3d(sA + stage * C::A_STAGE + b * BOX, &tmX, &full[stage], mt * BM + b * 32, tok, z);
+        for (int b = 0; b < BM / 32; ++b) {
+          if (p.conv) {
+            const ConvGeom& g = p.cv;
+            const int f0 = mt * BM + b * 32, tap = f0 / g.cin, c0 = f0 - tap * g.cin, kh = tap / g.k, kw = tap - kh * g.k;
+            const int hw = g.ho * g.wo, b0 = tok / hw, i0 = (tok - b0 * hw) / g.wo;
+            tma_load_4d(sA + stage * C::A_STAGE + b * BOX, &tmX, &full[stage], c0, kw - g.pl, g.s * i0 + kh - g.pt, b0);
+          } else
+          tma_load_3d(sA + stage * C::A_STAGE + b * BOX, &tmX, &full[stage], mt * BM + b * 32, tok, z);
+        }
 #pragma unroll
         for (int b = 0; b < BN / 32; ++b) tma_load_3d(sB + stage * C::B_STAGE + b * BOX, &tmY, &full[stage], nt * BN + b * 32, tok, z);
         if (++stage == NS) { stage = 0; phase ^= 1; }
@@ -170,6 +178,12 @@ cudaError_t launch_w(const WgradP& p, cudaStream_t s) {
     configured = true;
   }
   CUtensorMap tmX, tmY;
+  if (p.conv) {
+    ConvBox box;
+    if (!conv_tma_box(p.cv.ho, p.cv.wo, KT, &box)) { set_error("wgrad_tma: conv geometry does not tile"); return cudaErrorInvalidValue; }
+    if (!make_tmap_conv(&tmX, p.X + p.cv.boff, p.cv.hin, p.cv.win, p.cv.cin, p.cv.bstride, p.tokens / (p.cv.ho * p.cv.wo), p.cv.s, box,
+                        CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)) return cudaErrorInvalidValue;
+  } else
   if (!make_tmap_3d(&tmX, p.X, p.Kin, p.tokens, p.batch, p.ldx, p.x_bs, KT, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)) return cudaErrorInvalidValue;
   if (!make_tmap_3d(&tmY, p.dY, p.N, p.tokens, p.batch, p.lddy, p.dy_bs, KT, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)) return cudaErrorInvalidValue;
   const int m_tiles = cdiv(p.Kin, BM), n_tiles = cdiv(p.N, BN);
@@ -188,6 +202,13 @@ cudaError_t launch_w(const WgradP& p, cudaStream_t s) {
 }  // namespace
 
 bool wgrad_tma_supports(const WgradP& p) {
+  if (p.conv) {
+    const ConvGeom& g = p.cv; ConvBox box;
+    if (p.batch != 1 || g.cin < 32 || (g.cin & 31) || g.s < 1 || g.s > 8 || p.Kin != g.k * g.k * g.cin || p.tokens % (g.ho * g.wo) != 0) return false;
+    if (!conv_tma_box(g.ho, g.wo, 32, &box) || box.bw * g.s > 256 || box.bh * g.s > 256) return false;
+    if ((g.bstride & 3) || (g.boff & 3) || (p.N & 3) || (p.lddy & 3)) return false;
+    return !((reinterpret_cast<uintptr_t>(p.X) & 15) || (reinterpret_cast<uintptr_t>(p.dY) & 15) || (reinterpret_cast<uintptr_t>(p.dW) & 15));
+  }
   if (p.Kin < 1 || p.N < 4 || (p.N & 3) || p.tokens < 1 || p.batch < 1) return false;      // Kin need not be a multiple of 4 (ldx must)
   if ((p.ldx & 3) || (p.lddy & 3) || (p.x_bs & 3) || (p.dy_bs & 3) || (p.dw_bs & 3)) return false;
   if ((reinterpret_cast<uintptr_t>(p.X) & 15) || (reinterpret_cast<uintptr_t>(p.dY) & 15) || (reinterpret_cast<uintptr_t>(p.dW) & 15)) return false;

@@ -38,6 +38,7 @@ struct StageGeo {
 
 // activations kept from the forward pass (training keeps everything the backward reads)
 struct StageBuf {
+  bool conv_implicit = false;            // the last forward ran this stage's ConvEmbed as an implicit GEMM: `col` holds no patches
   float* col;                            // TF32 mode: im2col patch matrix of this stage's ConvEmbed [B*T, Kp] (kept for the weight gradient)
   float *x0, *xn, *conv, *qkv1, *qkv2, *attn_o, *a1, *x1, *y, *hpre, *hact, *x2;
   float *lna_mean, *lna_rstd, *lnb_mean, *lnb_rstd;
