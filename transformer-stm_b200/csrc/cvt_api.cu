@@ -735,7 +735,15 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
   if (!training && mlp_fused_supports(m, si)) {
     // inference: norm1 (:278) + Mlp (:253-258) + residual (:281) as one kernel, the 4D-wide hidden activation never leaves the SM
     m->mlp_fused_last = true;
-    return launch_mlp_fused(m, si, R, s);
+    return launch_mlp_fused(m, si, R, 0, s);
+  }
+  {
+    // training (TF32 folded mode, saved-derivative backward): the same kernel also leaves y, the LayerNorm statistics, the dropped-out
+    // hidden activation, d hact / d hpre and the fc2 dropout mask for stage_backward
+    static const bool train_off = getenv("CVT_NO_FUSED_MLP_TRAIN") != nullptr;
+    const bool philox_or_masks = !drop || m->dropout_mode == CVT_DROPOUT_MASKS || inline_philox(m);
+    if (training && !train_off && gelu_dsave(m, D) && philox_or_masks && mlp_fused_supports(m, si))
+      return launch_mlp_fused(m, si, R, 1, s);
   }
   // y = norm1(x)  :278  (same gamma/beta)
   CVT_CUDA(launch_ln_fwd(a.x1, rowmap_none(), D, P + w.ln_g, P + w.ln_b, c.ln_eps, a.y, D, a.lnb_mean, a.lnb_rstd, R, D, s, m->folded));

@@ -25,6 +25,12 @@ struct MlpP {
   const float* gamma; const float* beta; float eps;    // norm1 (second use, :278)
   const float* b1; const float* b2;                    // fc1 bias [H4], fc2 bias [D]
   int R, H4;
+  // training only: what the backward pass reads (y through a TMA store of the normalised tile)
+  float* mean; float* rstd;                            // LayerNorm row statistics [R]
+  float* hact; float* dsave;                           // [R, H4]: dropout(gelu(pre)) rounded to TF32; d hact / d pre = gelu'(pre) * keep / (1 - rate)
+  uint8_t* mask1; uint8_t* mask2;                      // keep-masks [R, H4] (read in MASKS mode only), [R, D] (written in PHILOX mode, read in MASKS mode)
+  int drop_mode;                                       // CVT_DROPOUT_OFF / PHILOX / MASKS
+  float keep_scale; uint32_t ph_k0, ph_k1, ph_thr, ph_site1, ph_site2, ph_step; const float* ph_dyn;
 };
 
 template <int D> struct MfCfg {
@@ -66,10 +72,34 @@ __device__ __forceinline__ float gelu_fast(float x) {
   return fmaf(-ax, q * t * e, fmaxf(x, 0.f));
 }
 
-template <int D>
+__device__ __forceinline__ void st_v8(float* ptr, const float* a) {       // one 32-byte store per thread (st.global.v8.f32, sm_100)
+  asm volatile("st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(ptr), "f"(a[0]), "f"(a[1]), "f"(a[2]), "f"(a[3]), "f"(a[4]),
+               "f"(a[5]), "f"(a[6]), "f"(a[7])
+               : "memory");
+}
+__device__ __forceinline__ void tma_store_3d(const void* tmap, const void* smem_src, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+// keep bits (one byte per element, 0 / 1) of the 4 elements starting at flat index idx0 of a dropout site
+__device__ __forceinline__ uint32_t keep4(const MlpP& p, uint32_t site, const uint8_t* mask, long long idx0, uint32_t step) {
+  if (p.drop_mode == CVT_DROPOUT_PHILOX) {
+    uint32_t c[4] = {(uint32_t)(idx0 >> 2), site, step, 0u};
+    philox4x32_10(c, p.ph_k0, p.ph_k1);
+    return (c[0] >= p.ph_thr ? 1u : 0u) | (c[1] >= p.ph_thr ? 0x100u : 0u) | (c[2] >= p.ph_thr ? 0x10000u : 0u) | (c[3] >= p.ph_thr ? 0x1000000u : 0u);
+  }
+  if (p.drop_mode == CVT_DROPOUT_MASKS) return __ldg(reinterpret_cast<const uint32_t*>(mask + idx0));
+  return 0x01010101u;
+}
+
+// TRAIN: additionally leaves what the backward pass reads - y (TMA store of the normalised tile), the LayerNorm row statistics, the
+// dropped-out hidden activation and d hact / d pre (one exponential serves both, gelu_and_grad), the fc2 dropout mask - and applies
+// the two dropouts (Philox counters identical to the GEMM epilogues' and to oracle.dropout_mask, or caller-supplied masks)
+template <int D, bool TRAIN>
 __global__ void __launch_bounds__(MfCfg<D>::NT, D == 64 ? 2 : 1) mlp_fused_kernel(const __grid_constant__ MlpP p, const __grid_constant__ CUtensorMap tmX,
                                                                                   const __grid_constant__ CUtensorMap tmW1,
-                                                                                  const __grid_constant__ CUtensorMap tmW2) {
+                                                                                  const __grid_constant__ CUtensorMap tmW2,
+                                                                                  const __grid_constant__ CUtensorMap tmY) {
   using C = MfCfg<D>;
   constexpr int RW = C::RW, NT = C::NT, KB = C::KB, COLS = C::COLS;
   extern __shared__ uint8_t smem_raw[];
@@ -124,6 +154,12 @@ __global__ void __launch_bounds__(MfCfg<D>::NT, D == 64 ? 2 : 1) mlp_fused_kerne
     constexpr uint32_t idesc_o = make_idesc(kFmtTF32, 128, D, 0, 0);
     const uint32_t y0 = smem_u32(sY);
     mbar_wait(&bars[MB_YF], 0);
+    if (TRAIN && elect_one_mf()) {                      // y = norm1(x1), the operand of the fc1 weight gradient: the tile as it lies, rows past R clipped
+#pragma unroll
+      for (int kb = 0; kb < KB; ++kb) tma_store_3d(&tmY, sY + kb * 16384, kb * 32, row0, 0);
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    }
+    __syncwarp();
     auto issue_h = [&](int c) {
       const int st = c & 1;
       mbar_wait(&bars[MB_W1F + st], (c >> 1) & 1);
@@ -159,6 +195,7 @@ __global__ void __launch_bounds__(MfCfg<D>::NT, D == 64 ? 2 : 1) mlp_fused_kerne
       }
       __syncwarp();
     }
+    if (TRAIN) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");      // (the thread that committed the group is the one that waits)
   } else {
     // ===== row warps =====
     {  // LayerNorm in place: TPR threads per row (adjacent lanes), 16-byte chunks of the swizzled K-major tile
@@ -178,6 +215,7 @@ __global__ void __launch_bounds__(MfCfg<D>::NT, D == 64 ? 2 : 1) mlp_fused_kerne
       }
       if (TPR == 2) q += __shfl_xor_sync(0xffffffffu, q, 1);
       const float r = 1.0f / sqrtf(q * (1.f / (float)D) + p.eps);
+      if (TRAIN && sub == 0 && row0 + row < p.R) { p.mean[row0 + row] = mu; p.rstd[row0 + row] = r; }
       for (int c4 = sub; c4 < NCH; c4 += TPR) {
         float4* ptr = chunk(c4);
         const float4 v = *ptr;
@@ -192,6 +230,7 @@ __global__ void __launch_bounds__(MfCfg<D>::NT, D == 64 ? 2 : 1) mlp_fused_kerne
     }
     const int quad = warp & 3, half = (warp - 2) >> 2;
     const uint32_t t_row = tmem + ((uint32_t)(quad * 32) << 16);
+    const uint32_t step = (TRAIN && p.ph_dyn) ? __ldg(reinterpret_cast<const uint32_t*>(p.ph_dyn) + 2) : p.ph_step;
     for (int c = 0; c < nchunks; ++c) {
       const int st = c & 1;
       mbar_wait(&bars[MB_HF + st], (c >> 1) & 1);
@@ -201,11 +240,37 @@ __global__ void __launch_bounds__(MfCfg<D>::NT, D == 64 ? 2 : 1) mlp_fused_kerne
       for (int i = 0; i < COLS / 32; ++i) tmem_ld32_nowait(t_row + st * 64 + half * COLS + i * 32, h + i * 32);
       tmem_wait_ld();
       const float* bias = sB1 + c * 64 + half * COLS;
+      if (TRAIN) {
+        const int grow = row0 + quad * 32 + lane;       // this thread's token
+        const bool valid = grow < p.R;
+        const long long base = (long long)grow * p.H4 + c * 64 + half * COLS;
+#pragma unroll
+        for (int i = 0; i < COLS; i += 8) {
+          float hv[8], dv[8];
+#pragma unroll
+          for (int u = 0; u < 8; u += 4) {
+            const float4 b4 = *reinterpret_cast<const float4*>(bias + i + u);
+            const float bb[4] = {b4.x, b4.y, b4.z, b4.w};
+            const uint32_t mk = keep4(p, p.ph_site1, p.mask1, valid ? base + i + u : 0, step);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              float g, dg;
+              gelu_and_grad(__uint_as_float(h[i + u + j]) + bb[j], g, dg);
+              const bool keep = ((mk >> (8 * j)) & 0xFFu) != 0u;
+              hv[u + j] = to_tf32(keep ? g * p.keep_scale : 0.f);
+              dv[u + j] = keep ? dg * p.keep_scale : 0.f;
+              h[i + u + j] = __float_as_uint(hv[u + j]);
+            }
+          }
+          if (valid) { st_v8(p.hact + base + i, hv); st_v8(p.dsave + base + i, dv); }
+        }
+      } else {
 #pragma unroll
       for (int i = 0; i < COLS; i += 4) {
         const float4 b4 = *reinterpret_cast<const float4*>(bias + i);
         h[i] = tf32_rna_bits(gelu_fast(__uint_as_float(h[i]) + b4.x)); h[i + 1] = tf32_rna_bits(gelu_fast(__uint_as_float(h[i + 1]) + b4.y));
         h[i + 2] = tf32_rna_bits(gelu_fast(__uint_as_float(h[i + 2]) + b4.z)); h[i + 3] = tf32_rna_bits(gelu_fast(__uint_as_float(h[i + 3]) + b4.w));
+      }
       }
 #pragma unroll
       for (int i = 0; i < COLS / 32; ++i) tmem_st32(t_row + st * 64 + half * COLS + i * 32, h + i * 32);
@@ -223,7 +288,7 @@ __global__ void __launch_bounds__(MfCfg<D>::NT, D == 64 ? 2 : 1) mlp_fused_kerne
 #pragma unroll
       for (int rr = 0; rr < 32; ++rr) {
         const int row = min(row0 + quad * 32 + rr, p.R - 1);
-        res[blk][rr] = __ldg(p.x1 + (long long)row * D + col) + sB2[col];
+        res[blk][rr] = __ldg(p.x1 + (long long)row * D + col) + (TRAIN ? 0.f : sB2[col]);
       }
     }
     mbar_wait(&bars[MB_DONE], 0);
@@ -234,6 +299,18 @@ __global__ void __launch_bounds__(MfCfg<D>::NT, D == 64 ? 2 : 1) mlp_fused_kerne
       const int cb = half * NBLK + blk;
       float v[32];
       tmem_ld32(t_row + 128 + cb * 32, v);
+      if (TRAIN) {                                      // fc2 bias and dropout (:257) in the row layout (4 consecutive columns per Philox draw)
+        const int grow = row0 + quad * 32 + lane;
+        const bool valid = grow < p.R;
+        const long long base = (long long)grow * D + cb * 32;
+#pragma unroll
+        for (int i = 0; i < 32; i += 4) {
+          const uint32_t mk = keep4(p, p.ph_site2, p.mask2, valid ? base + i : 0, step);
+          if (valid && p.drop_mode == CVT_DROPOUT_PHILOX) *reinterpret_cast<uint32_t*>(p.mask2 + base + i) = mk;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) v[i + j] = ((mk >> (8 * j)) & 0xFFu) ? (v[i + j] + sB2[cb * 32 + i + j]) * p.keep_scale : 0.f;
+        }
+      }
 #pragma unroll
       for (int i = 0; i < 32; ++i) stg[lane * 33 + i] = v[i];
       __syncwarp();
@@ -251,19 +328,21 @@ __global__ void __launch_bounds__(MfCfg<D>::NT, D == 64 ? 2 : 1) mlp_fused_kerne
   if (warp == 1) tmem_dealloc(tmem, C::TMEM_COLS);
 }
 
-template <int D>
-cudaError_t launch_cfg(const MlpP& p, const float* w1t, const float* w2t, cudaStream_t s) {
+template <int D, bool TRAIN>
+cudaError_t launch_cfg(const MlpP& p, const float* w1t, const float* w2t, float* y_out, cudaStream_t s) {
   using C = MfCfg<D>;
   static bool configured = false;
   if (!configured) {
-    CVT_CUDA(cudaFuncSetAttribute(mlp_fused_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
+    CVT_CUDA(cudaFuncSetAttribute(mlp_fused_kernel<D, TRAIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
     configured = true;
   }
-  CUtensorMap tmX, tmW1, tmW2;
+  CUtensorMap tmX, tmW1, tmW2, tmY;
   if (!make_tmap_3d(&tmX, p.x1, D, p.R, 1, D, 0, 128, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
   if (!make_tmap_3d(&tmW1, w1t, D, p.H4, 1, D, 0, 64, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;      // fc1 kernel, K-major copy [H4][D]
   if (!make_tmap_3d(&tmW2, w2t, p.H4, D, 1, p.H4, 0, D, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;    // fc2 kernel, K-major copy [D][H4]
-  mlp_fused_kernel<D><<<cdiv(p.R, 128), C::NT, C::SMEM, s>>>(p, tmX, tmW1, tmW2);
+  tmY = tmX;
+  if (TRAIN && !make_tmap_3d(&tmY, y_out, D, p.R, 1, D, 0, 128, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
+  mlp_fused_kernel<D, TRAIN><<<cdiv(p.R, 128), C::NT, C::SMEM, s>>>(p, tmX, tmW1, tmW2, tmY);
   CVT_LAUNCH_CHECK();
   return cudaSuccess;
 }
@@ -276,14 +355,28 @@ bool mlp_fused_supports(const Model* m, int si) {
   return !off && m->cfg.precision != CVT_PREC_FP32 && m->pt_valid && (D == 64 || D == 128) && H4 % 64 == 0 && H4 <= 1024;
 }
 
-// x2 = x1 + Mlp(norm1(x1)) of stage si for R tokens (inference: no dropout, nothing kept for a backward pass)
-cudaError_t launch_mlp_fused(const Model* m, int si, int R, cudaStream_t s) {
+// x2 = x1 + Mlp(norm1(x1)) of stage si for R tokens.  training == 0: nothing is kept.  training != 0 (folded TF32 mode): y, the LayerNorm
+// statistics, hact, d hact / d pre (in the hpre buffer) and mask2 are left for stage_backward exactly as the three-kernel path leaves them.
+cudaError_t launch_mlp_fused(const Model* m, int si, int R, int training, cudaStream_t s) {
   const StageGeo& g = m->geo[si]; const StageW& w = m->w[si]; const StageBuf& a = m->buf[si];
   MlpP p{};
   p.x1 = a.x1; p.x2 = a.x2; p.gamma = m->P + w.ln_g; p.beta = m->P + w.ln_b; p.eps = m->cfg.ln_eps;
   p.b1 = m->P + w.f1b; p.b2 = m->P + w.f2b; p.R = R; p.H4 = m->cfg.mlp_ratio * g.D;
-  if (g.D == 64) return launch_cfg<64>(p, m->Pt + w.f1w, m->Pt + w.f2w, s);
-  if (g.D == 128) return launch_cfg<128>(p, m->Pt + w.f1w, m->Pt + w.f2w, s);
+  if (training) {
+    const bool drop = m->dropout_mode != CVT_DROPOUT_OFF && m->cfg.drop_rate > 0.f;
+    p.mean = a.lnb_mean; p.rstd = a.lnb_rstd; p.hact = a.hact; p.dsave = a.hpre; p.mask1 = a.mask1; p.mask2 = a.mask2;
+    p.drop_mode = drop ? m->dropout_mode : CVT_DROPOUT_OFF;
+    p.keep_scale = drop ? 1.f / (1.f - m->cfg.drop_rate) : 1.f;
+    const double t = (double)m->cfg.drop_rate * 4294967296.0;
+    p.ph_thr = t >= 4294967295.0 ? 0xFFFFFFFFu : (uint32_t)t;
+    p.ph_k0 = (uint32_t)(m->dropout_seed & 0xFFFFFFFFu); p.ph_k1 = (uint32_t)(m->dropout_seed >> 32);
+    p.ph_site1 = (uint32_t)(si * 4 + 1); p.ph_site2 = (uint32_t)(si * 4 + 2); p.ph_step = m->dropout_step; p.ph_dyn = m->dyn;
+    if (g.D == 64) return launch_cfg<64, true>(p, m->Pt + w.f1w, m->Pt + w.f2w, a.y, s);
+    if (g.D == 128) return launch_cfg<128, true>(p, m->Pt + w.f1w, m->Pt + w.f2w, a.y, s);
+  } else {
+    if (g.D == 64) return launch_cfg<64, false>(p, m->Pt + w.f1w, m->Pt + w.f2w, nullptr, s);
+    if (g.D == 128) return launch_cfg<128, false>(p, m->Pt + w.f1w, m->Pt + w.f2w, nullptr, s);
+  }
   set_error("mlp_fused: unsupported embed_dim");
   return cudaErrorNotSupported;
 }

@@ -139,7 +139,7 @@ cudaError_t attention_backward(Model* m, int si, int B, const float* dO, float* 
 
 // fused inference Mlp (mlp_fused.cu): x2 = x1 + fc2(gelu(fc1(norm1(x1)))) in one kernel, the hidden activation stays in TMEM
 bool mlp_fused_supports(const Model* m, int si);
-cudaError_t launch_mlp_fused(const Model* m, int si, int R, cudaStream_t s);
+cudaError_t launch_mlp_fused(const Model* m, int si, int R, int training, cudaStream_t s);
 
 // gradient reduce-scatter + Adam + weight all-gather over peer memory, one kernel (dp_peer.cu)
 cudaError_t launch_dp_reduce_adam(Model* m, cudaStream_t s);
