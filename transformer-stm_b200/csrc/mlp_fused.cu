@@ -81,27 +81,32 @@ __device__ __forceinline__ void tma_store_3d(const void* tmap, const void* smem_
   asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
                ::"l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2) : "memory");
 }
-// keep bits (one byte per element, 0 / 1) of the 4 elements starting at flat index idx0 of a dropout site
-__device__ __forceinline__ uint32_t keep4(const MlpP& p, uint32_t site, const uint8_t* mask, long long idx0, uint32_t step) {
-  if (p.drop_mode == CVT_DROPOUT_PHILOX) {
-    uint32_t c[4] = {(uint32_t)(idx0 >> 2), site, step, 0u};
+// keep bits (one byte per element, 0 / 1) of the 4 elements of quad `q` (= flat element index / 4) of a dropout site.  MODE is the kernel's
+// compile-time variant: 2 = Philox4x32-10 (counter {q, site, step, 0}, key = seed: the stream of philox_mask_kernel, the GEMM epilogues and
+// oracle.dropout_mask), 3 = caller-supplied masks, else no dropout
+template <int MODE>
+__device__ __forceinline__ uint32_t keep4(const MlpP& p, uint32_t site, const uint8_t* mask, uint32_t q, uint32_t step) {
+  if (MODE == 2) {
+    uint32_t c[4] = {q, site, step, 0u};
     philox4x32_10(c, p.ph_k0, p.ph_k1);
     return (c[0] >= p.ph_thr ? 1u : 0u) | (c[1] >= p.ph_thr ? 0x100u : 0u) | (c[2] >= p.ph_thr ? 0x10000u : 0u) | (c[3] >= p.ph_thr ? 0x1000000u : 0u);
   }
-  if (p.drop_mode == CVT_DROPOUT_MASKS) return __ldg(reinterpret_cast<const uint32_t*>(mask + idx0));
+  if (MODE == 3) return __ldg(reinterpret_cast<const uint32_t*>(mask) + q);
   return 0x01010101u;
 }
 
 // TRAIN: additionally leaves what the backward pass reads - y (TMA store of the normalised tile), the LayerNorm row statistics, the
 // dropped-out hidden activation and d hact / d pre (one exponential serves both, gelu_and_grad), the fc2 dropout mask - and applies
 // the two dropouts (Philox counters identical to the GEMM epilogues' and to oracle.dropout_mask, or caller-supplied masks)
-template <int D, bool TRAIN>
+// MODE: 0 inference, 1 training without dropout, 2 training with Philox dropout, 3 training with caller-supplied masks
+template <int D, int MODE>
 __global__ void __launch_bounds__(MfCfg<D>::NT, D == 64 ? 2 : 1) mlp_fused_kernel(const __grid_constant__ MlpP p, const __grid_constant__ CUtensorMap tmX,
                                                                                   const __grid_constant__ CUtensorMap tmW1,
                                                                                   const __grid_constant__ CUtensorMap tmW2,
                                                                                   const __grid_constant__ CUtensorMap tmY) {
   using C = MfCfg<D>;
   constexpr int RW = C::RW, NT = C::NT, KB = C::KB, COLS = C::COLS;
+  constexpr bool TRAIN = MODE > 0;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   uint8_t* sm = smem_raw + (((raw + 1023u) & ~1023u) - raw);
@@ -230,7 +235,7 @@ __global__ void __launch_bounds__(MfCfg<D>::NT, D == 64 ? 2 : 1) mlp_fused_kerne
     }
     const int quad = warp & 3, half = (warp - 2) >> 2;
     const uint32_t t_row = tmem + ((uint32_t)(quad * 32) << 16);
-    const uint32_t step = (TRAIN && p.ph_dyn) ? __ldg(reinterpret_cast<const uint32_t*>(p.ph_dyn) + 2) : p.ph_step;
+    const uint32_t step = (MODE == 2 && p.ph_dyn) ? __ldg(reinterpret_cast<const uint32_t*>(p.ph_dyn) + 2) : p.ph_step;
     for (int c = 0; c < nchunks; ++c) {
       const int st = c & 1;
       mbar_wait(&bars[MB_HF + st], (c >> 1) & 1);
@@ -244,6 +249,7 @@ __global__ void __launch_bounds__(MfCfg<D>::NT, D == 64 ? 2 : 1) mlp_fused_kerne
         const int grow = row0 + quad * 32 + lane;       // this thread's token
         const bool valid = grow < p.R;
         const long long base = (long long)grow * p.H4 + c * 64 + half * COLS;
+        const uint32_t q0 = valid ? (uint32_t)grow * (uint32_t)(p.H4 >> 2) + (uint32_t)((c * 64 + half * COLS) >> 2) : 0u;
 #pragma unroll
         for (int i = 0; i < COLS; i += 8) {
           float hv[8], dv[8];
@@ -251,7 +257,7 @@ __global__ void __launch_bounds__(MfCfg<D>::NT, D == 64 ? 2 : 1) mlp_fused_kerne
           for (int u = 0; u < 8; u += 4) {
             const float4 b4 = *reinterpret_cast<const float4*>(bias + i + u);
             const float bb[4] = {b4.x, b4.y, b4.z, b4.w};
-            const uint32_t mk = keep4(p, p.ph_site1, p.mask1, valid ? base + i + u : 0, step);
+            const uint32_t mk = keep4<MODE>(p, p.ph_site1, p.mask1, q0 + ((i + u) >> 2), step);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
               float g, dg;
@@ -303,10 +309,11 @@ __global__ void __launch_bounds__(MfCfg<D>::NT, D == 64 ? 2 : 1) mlp_fused_kerne
         const int grow = row0 + quad * 32 + lane;
         const bool valid = grow < p.R;
         const long long base = (long long)grow * D + cb * 32;
+        const uint32_t q0 = valid ? (uint32_t)grow * (uint32_t)(D >> 2) + (uint32_t)(cb * 8) : 0u;
 #pragma unroll
         for (int i = 0; i < 32; i += 4) {
-          const uint32_t mk = keep4(p, p.ph_site2, p.mask2, valid ? base + i : 0, step);
-          if (valid && p.drop_mode == CVT_DROPOUT_PHILOX) *reinterpret_cast<uint32_t*>(p.mask2 + base + i) = mk;
+          const uint32_t mk = keep4<MODE>(p, p.ph_site2, p.mask2, q0 + (i >> 2), step);
+          if (valid && MODE == 2) *reinterpret_cast<uint32_t*>(p.mask2 + base + i) = mk;
 #pragma unroll
           for (int j = 0; j < 4; ++j) v[i + j] = ((mk >> (8 * j)) & 0xFFu) ? (v[i + j] + sB2[cb * 32 + i + j]) * p.keep_scale : 0.f;
         }
@@ -328,12 +335,13 @@ __global__ void __launch_bounds__(MfCfg<D>::NT, D == 64 ? 2 : 1) mlp_fused_kerne
   if (warp == 1) tmem_dealloc(tmem, C::TMEM_COLS);
 }
 
-template <int D, bool TRAIN>
+template <int D, int MODE>
 cudaError_t launch_cfg(const MlpP& p, const float* w1t, const float* w2t, float* y_out, cudaStream_t s) {
   using C = MfCfg<D>;
+  constexpr bool TRAIN = MODE > 0;
   static bool configured = false;
   if (!configured) {
-    CVT_CUDA(cudaFuncSetAttribute(mlp_fused_kernel<D, TRAIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
+    CVT_CUDA(cudaFuncSetAttribute(mlp_fused_kernel<D, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
     configured = true;
   }
   CUtensorMap tmX, tmW1, tmW2, tmY;
@@ -342,7 +350,7 @@ cudaError_t launch_cfg(const MlpP& p, const float* w1t, const float* w2t, float*
   if (!make_tmap_3d(&tmW2, w2t, p.H4, D, 1, p.H4, 0, D, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;    // fc2 kernel, K-major copy [D][H4]
   tmY = tmX;
   if (TRAIN && !make_tmap_3d(&tmY, y_out, D, p.R, 1, D, 0, 128, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
-  mlp_fused_kernel<D, TRAIN><<<cdiv(p.R, 128), C::NT, C::SMEM, s>>>(p, tmX, tmW1, tmW2, tmY);
+  mlp_fused_kernel<D, MODE><<<cdiv(p.R, 128), C::NT, C::SMEM, s>>>(p, tmX, tmW1, tmW2, tmY);
   CVT_LAUNCH_CHECK();
   return cudaSuccess;
 }
@@ -371,11 +379,15 @@ cudaError_t launch_mlp_fused(const Model* m, int si, int R, int training, cudaSt
     p.ph_thr = t >= 4294967295.0 ? 0xFFFFFFFFu : (uint32_t)t;
     p.ph_k0 = (uint32_t)(m->dropout_seed & 0xFFFFFFFFu); p.ph_k1 = (uint32_t)(m->dropout_seed >> 32);
     p.ph_site1 = (uint32_t)(si * 4 + 1); p.ph_site2 = (uint32_t)(si * 4 + 2); p.ph_step = m->dropout_step; p.ph_dyn = m->dyn;
-    if (g.D == 64) return launch_cfg<64, true>(p, m->Pt + w.f1w, m->Pt + w.f2w, a.y, s);
-    if (g.D == 128) return launch_cfg<128, true>(p, m->Pt + w.f1w, m->Pt + w.f2w, a.y, s);
+    const int mode = p.drop_mode == CVT_DROPOUT_PHILOX ? 2 : (p.drop_mode == CVT_DROPOUT_MASKS ? 3 : 1);
+#define MF_LAUNCH(DD) (mode == 2 ? launch_cfg<DD, 2>(p, m->Pt + w.f1w, m->Pt + w.f2w, a.y, s) : mode == 3 ? launch_cfg<DD, 3>(p, m->Pt + w.f1w, m->Pt + w.f2w, a.y, s) \
+                                 : launch_cfg<DD, 1>(p, m->Pt + w.f1w, m->Pt + w.f2w, a.y, s))
+    if (g.D == 64) return MF_LAUNCH(64);
+    if (g.D == 128) return MF_LAUNCH(128);
+#undef MF_LAUNCH
   } else {
-    if (g.D == 64) return launch_cfg<64, false>(p, m->Pt + w.f1w, m->Pt + w.f2w, nullptr, s);
-    if (g.D == 128) return launch_cfg<128, false>(p, m->Pt + w.f1w, m->Pt + w.f2w, nullptr, s);
+    if (g.D == 64) return launch_cfg<64, 0>(p, m->Pt + w.f1w, m->Pt + w.f2w, nullptr, s);
+    if (g.D == 128) return launch_cfg<128, 0>(p, m->Pt + w.f1w, m->Pt + w.f2w, nullptr, s);
   }
   set_error("mlp_fused: unsupported embed_dim");
   return cudaErrorNotSupported;
