@@ -206,6 +206,8 @@ CVT_API int  cvt_comm_destroy(cvt_model* m);
  * sync_grads != 0 also leaves the reduced gradient in every rank's arena (cvt_get_grad in tests). */
 CVT_API int  cvt_comm_peer_export(cvt_model* m, uint8_t handle_out[64]);
 CVT_API int  cvt_comm_peer_open(cvt_model* m, const uint8_t* handles /* [world][64] */, int sync_grads);
+/* back to the NCCL path (used when some rank of the job could not map its peers: all ranks must take the same path) */
+CVT_API int  cvt_comm_peer_close(cvt_model* m);
 /* flat trainable arenas so the host may run its own collective instead (torch.distributed plumbing) */
 CVT_API int  cvt_grad_arena(cvt_model* m, float** grads_dev, int64_t* count);
 CVT_API int  cvt_param_arena(cvt_model* m, float** params_dev, int64_t* count);

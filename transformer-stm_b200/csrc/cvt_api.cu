@@ -1258,6 +1258,19 @@ int cvt_comm_peer_open(cvt_model* h, const uint8_t* handles, int sync_grads) {
   clear_graphs(m);
   return CVT_OK;
 }
+int cvt_comm_peer_close(cvt_model* h) {
+  if (!h) return CVT_ERR_INVALID;
+  Model* m = &h->m;
+  if (!m->peer_ready) return CVT_OK;
+  API_CUDA(cudaSetDevice(m->cfg.device));
+  if (m->stream) API_CUDA(cudaStreamSynchronize(m->stream));
+  for (int p = 0; p < CVT_MAX_PEERS; ++p) if (m->peer_base[p] && p != m->rank) cudaIpcCloseMemHandle(m->peer_base[p]);
+  for (int p = 0; p < CVT_MAX_PEERS; ++p) m->peer_base[p] = nullptr;
+  m->peer_ready = false;
+  clear_graphs(m);
+  (void)cudaGetLastError();
+  return CVT_OK;
+}
 int cvt_grad_arena(cvt_model* h, float** g, int64_t* count) {
   if (!h) return CVT_ERR_INVALID;
   if (g) *g = h->m.G; if (count) *count = h->m.n_train;

@@ -56,7 +56,7 @@ def open_peer_memory(engine, dist, rank: int, world: int, device=None, sync_grad
     """Exchanges the cudaIpc handles of the ranks' workspaces (all_gather through torch.distributed) and maps them: the train step then ends
     in ONE kernel that reduce-scatters the gradients, applies Adam to the rank's slice and all-gathers the weights over NVLink peer memory
     (csrc/dp_peer.cu) instead of ncclAllReduce + a full Adam pass.  All ranks must agree on the outcome, so the success flags are reduced:
-    if any rank cannot map its peers (no P2P between the devices) every rank stays on the NCCL path.  CVT_DP_NCCL=1 forces NCCL."""
+    if any rank cannot map its peers (no P2P between the devices) every rank stays on the NCCL path (returns False).  CVT_DP_NCCL=1 forces NCCL."""
     import os
     import torch
     if os.environ.get("CVT_DP_NCCL"):
@@ -66,13 +66,17 @@ def open_peer_memory(engine, dist, rank: int, world: int, device=None, sync_grad
     dist.all_gather(parts, mine)
     handles = b"".join(bytes(p.cpu().tolist()) for p in parts)
     ok = torch.ones(1, dtype=torch.int32, device=device)
+    why = ""
     try:
         engine.comm_peer_open(handles, sync_grads)
-    except Exception:                      # noqa: BLE001 - reported below, decided collectively
-        ok.zero_()
+    except Exception as e:                 # noqa: BLE001 - decided collectively below
+        ok.zero_(); why = str(e)
     dist.all_reduce(ok, op=dist.ReduceOp.MIN)
-    if int(ok.item()) == 0:
-        raise RuntimeError("peer-memory data parallelism: a rank could not map its peers' workspaces (set CVT_DP_NCCL=1 to use NCCL only)")
+    if int(ok.item()) == 0:                # every rank takes the same path: the ranks that did map their peers let go again
+        engine.comm_peer_close()
+        import sys
+        print("[cvt_b200] rank %d: peer memory unavailable (%s); the gradient all-reduce stays on NCCL" % (rank, why or "another rank failed"), file=sys.stderr)
+        return False
     return True
 
 

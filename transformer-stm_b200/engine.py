@@ -411,6 +411,9 @@ class CvtEngine:
         buf = (C.c_uint8 * len(handles)).from_buffer_copy(handles)
         L.check(self.lib.cvt_comm_peer_open(self.h, buf, int(sync_grads)), "cvt_comm_peer_open")
 
+    def comm_peer_close(self):
+        L.check(self.lib.cvt_comm_peer_close(self.h), "cvt_comm_peer_close")
+
     # ---- misc ----
     def synchronize(self):
         L.check(self.lib.cvt_synchronize(self.h))
