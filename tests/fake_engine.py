@@ -13,9 +13,10 @@ class OracleEngine:
               for s in cfg.stages]
         self.spec = O.CvtSpec(cfg.image_h, cfg.image_w, cfg.in_chans, st, cfg.proc_dim, cfg.num_classes, cfg.mlp_ratio, cfg.drop_rate,
                               cfg.ln_eps, cfg.bn_eps, cfg.bn_momentum, cfg.proc_hidden)
-        for k in ("head_kind", "apply_proj_qkv", "attn_drop_rate"):
-            if hasattr(cfg, k) and hasattr(self.spec, k):
-                setattr(self.spec, k, getattr(cfg, k))
+        # the tools' model variants (CvtConfig.head / apply_proj_qkv / attn_drop_rate, include/cvt_b200.h ABI 3)
+        self.spec.head = {"gap": "mean"}.get(getattr(cfg, "head", "auto"), getattr(cfg, "head", "auto"))
+        self.spec.apply_proj_qkv = bool(getattr(cfg, "apply_proj_qkv", True))
+        self.spec.attn_drop_rate = float(getattr(cfg, "attn_drop_rate", 0.0))
         self.params = {n: np.zeros(s, np.float64) for n, s, _ in O.param_specs(self.spec)}
         self.opt = O.new_opt_state(self.params)
         self.mode, self.seed, self.step = "off", 0, 0

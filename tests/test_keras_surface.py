@@ -229,3 +229,30 @@ def test_gradcam_on_the_cls_head_fails_like_the_reference():
     with pytest.raises(ValueError, match="No gradients"):
         K.make_gradcam_heatmap(x, p, m, "stage3_transformer")
     m.close()
+
+
+@pytest.mark.parametrize("variant,cls,proj", [("gradcam", False, "dw_bn"), ("gradcam", True, "linear"), ("model_plot", True, "dw_bn"),
+                                               ("model_plot", False, "avg")])
+def test_configure_variant_builds_the_tools_models(variant, cls, proj):
+    """keras_api.configure(variant=...) (CPU, oracle-backed engine): create_cvt_model then builds the model of tools/grad_cam_CvT.py:315-349
+    / tools/model_plot.py:254-300 - parameter table, one fit epoch and predict go through."""
+    K.configure(projection=proj, cls_token=cls, variant=variant)
+    try:
+        m = K.create_cvt_model(H, W, 1, 5, 1, precision="fp32", max_batch=4, seed=1, engine_factory=OracleEngine)
+        names = [p["name"] for p in m.engine.param_infos()]
+        if variant == "gradcam":
+            assert m.cfg.head == "mean" and not m.cfg.apply_proj_qkv and m.cfg.attn_drop_rate == pytest.approx(0.1)
+            assert all(st.with_cls_token == cls for st in m.cfg.stages)
+            assert not any("/proj_q/" in n or n.startswith("head_norm") for n in names)
+            assert any("q_proj/dense/kernel" in n for n in names) == (proj == "linear")
+        else:
+            assert m.cfg.head == ("cls" if cls else "mean") and m.cfg.apply_proj_qkv
+            assert not any(n.startswith("head_norm") for n in names) and any("/proj_q/" in n for n in names)
+        x, p, y = _data(6, 3)
+        m.compile(optimizer=K.Adam(learning_rate=1e-3), loss="mean_squared_error", metrics=["mae"])
+        h = m.fit([x, p], y, epochs=1, batch_size=4, verbose=0)
+        assert np.isfinite(h.history["loss"][0])
+        assert m.predict([x, p]).shape == (6, 1)
+        m.close()
+    finally:
+        K.configure(projection="dw_bn", cls_token=True, variant="reference")
