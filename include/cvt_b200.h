@@ -208,6 +208,9 @@ CVT_API int  cvt_comm_peer_export(cvt_model* m, uint8_t handle_out[64]);
 CVT_API int  cvt_comm_peer_open(cvt_model* m, const uint8_t* handles /* [world][64] */, int sync_grads);
 /* back to the NCCL path (used when some rank of the job could not map its peers: all ranks must take the same path) */
 CVT_API int  cvt_comm_peer_close(cvt_model* m);
+/* diagnostics: how many dense contractions issued by the calling thread went to {the TMA-fed tcgen05 kernel, the older tcgen05 kernel, the
+ * fp32 FFMA kernel} since the last reset.  In TF32 mode the last one should stay 0 for the shapes of the reference specs. */
+CVT_API int  cvt_gemm_dispatch_counts(int64_t out[3], int reset);
 /* flat trainable arenas so the host may run its own collective instead (torch.distributed plumbing) */
 CVT_API int  cvt_grad_arena(cvt_model* m, float** grads_dev, int64_t* count);
 CVT_API int  cvt_param_arena(cvt_model* m, float** params_dev, int64_t* count);

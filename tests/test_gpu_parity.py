@@ -350,3 +350,23 @@ def test_fused_inference_mlp_kernel_tf32(hw, batch, cls):
         eng.tap("s1.hact")
     eng.tap("s3.hact")                       # stage 3 (D = 256) still runs the three-kernel path
     eng.close()
+
+
+@pytest.mark.parametrize("wide", [False, True])
+def test_tf32_mode_never_lands_on_the_fp32_kernel(wide):
+    """run_gemm falls back gemm_tma -> gemm_tc -> gemm_simt without a word.  In TF32 mode every dense product of a train
+    step and of an inference forward of the reference AND of the widened (340x345, 64/192/384) configuration must take a tcgen05 kernel:
+    the FFMA count stays 0; the TMA-fed kernel takes all but the shapes it cannot (stage-1 ConvEmbed of the widened input has K = 49)."""
+    if wide:
+        spec, eng, params, img, proc, y = make_pair("dw_bn", True, 5, 1, (340, 345), dims=(64, 192, 384), heads=(1, 3, 6), batch=2, precision="tf32")
+    else:
+        spec, eng, params, img, proc, y = make_pair(hw=(128, 128), batch=4, precision="tf32")
+    eng.set_dropout("philox", 3)
+    eng.set_graphs(False)
+    eng.gemm_dispatch_counts(reset=True)
+    eng.train_step(img, proc, y, 1e-3)
+    eng.predict(img, proc)
+    tma, tc, simt = eng.gemm_dispatch_counts(reset=True)
+    assert simt == 0, (tma, tc, simt)
+    assert tma > 20 and tc <= 4, (tma, tc, simt)
+    eng.close()

@@ -88,6 +88,7 @@ _PROTOS = {
     "cvt_comm_peer_export": (C.c_int, [C.c_void_p, C.c_void_p]),
     "cvt_comm_peer_open": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
     "cvt_comm_peer_close": (C.c_int, [C.c_void_p]),
+    "cvt_gemm_dispatch_counts": (C.c_int, [C.POINTER(C.c_int64), C.c_int]),
     "cvt_grad_arena": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]),
     "cvt_param_arena": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]),
     "cvt_synchronize": (C.c_int, [C.c_void_p]),

@@ -53,25 +53,29 @@ static const char* kStageNames[CVT_MAX_STAGES][12] = {
   {"s4.conv_embed", "s4.ln_proj_bn", "s4.qkv_gemm", "s4.attention", "s4.out_gemm", "s4.mlp", "s4.bwd_mlp", "s4.bwd_out", "s4.bwd_attention", "s4.bwd_qkv", "s4.bwd_proj_ln", "s4.bwd_conv"}};
 
 // ---- contraction dispatch ----------------------------------------------------------------------------------
+// which contraction kernel every run_gemm call went to (cvt_gemm_dispatch_counts): a TF32-mode product that quietly lands on the FFMA
+// kernel is a 5x slowdown nobody asked for, so tests pin the counts for the reference and the widened configuration
+thread_local long long g_gemm_dispatch[3] = {0, 0, 0};      // gemm_tma, gemm_tc, gemm_simt
 cudaError_t run_gemm(const Model* m, const GemmP& p, cudaStream_t s) {
+  struct Count { int k; ~Count() { g_gemm_dispatch[k]++; } } count{2};
   if (m->cfg.precision != CVT_PREC_FP32) {
     static const bool no_tma = getenv("CVT_NO_TMA") != nullptr;
     if (!no_tma) {
       if (p.b_mode == B_KN && p.a_mode == A_PLAIN && m->pt_valid && p.B >= m->P && p.B < m->P + m->n_train && p.ldb == p.N) {
         // a dense kernel [K,N] of the parameter arena: read its K-major copy (same offset in Pt)
         GemmP q = p; q.B = m->Pt + (p.B - m->P); q.b_mode = B_NK; q.ldb = p.K;
-        if (gemm_tma_supports(q)) return launch_gemm_tma(q, s);
+        if (gemm_tma_supports(q)) { count.k = 0; return launch_gemm_tma(q, s); }
       }
       if (p.b_mode == B_NK && p.a_mode == A_PLAIN && m->pt_valid && p.B >= m->P && p.B < m->P + m->n_train) {
         // dgrad through a dense kernel of the parameter arena: read its TF32-rounded copy when one is kept
         const long long off = p.B - m->P;
         for (const TrDesc& d : m->tr_descs)
-          if (d.copy && d.off == off) { GemmP q = p; q.B = m->Pr + off; if (gemm_tma_supports(q)) return launch_gemm_tma(q, s); }
+          if (d.copy && d.off == off) { GemmP q = p; q.B = m->Pr + off; if (gemm_tma_supports(q)) { count.k = 0; return launch_gemm_tma(q, s); } }
       }
-      if (gemm_tma_supports(p)) return launch_gemm_tma(p, s);
+      if (gemm_tma_supports(p)) { count.k = 0; return launch_gemm_tma(p, s); }
     }
     if (p.epi & EPI_GELU_DSAVE) { set_error("run_gemm: the saved-GELU-derivative epilogue exists only in the TMA kernel"); return cudaErrorNotSupported; }
-    if (gemm_tc_supports(p)) return launch_gemm_tc(p, s);
+    if (gemm_tc_supports(p)) { count.k = 1; return launch_gemm_tc(p, s); }
   }
   if (p.epi & EPI_GELU_DSAVE) { set_error("run_gemm: the saved-GELU-derivative epilogue exists only in the TMA kernel"); return cudaErrorNotSupported; }
   if (p.epi & EPI_PHILOX) { set_error("run_gemm: in-epilogue dropout needs a tensor-core shape"); return cudaErrorNotSupported; }
@@ -1271,6 +1275,11 @@ int cvt_comm_peer_close(cvt_model* h) {
   (void)cudaGetLastError();
   return CVT_OK;
 }
+int cvt_gemm_dispatch_counts(int64_t out[3], int reset) {
+  if (out) for (int i = 0; i < 3; ++i) out[i] = g_gemm_dispatch[i];
+  if (reset) for (int i = 0; i < 3; ++i) g_gemm_dispatch[i] = 0;
+  return CVT_OK;
+}
 int cvt_grad_arena(cvt_model* h, float** g, int64_t* count) {
   if (!h) return CVT_ERR_INVALID;
   if (g) *g = h->m.G; if (count) *count = h->m.n_train;
@@ -2119,6 +2128,7 @@ int cvt_profile_step(cvt_model* h, const float* img_dev, const float* proc_dev, 
   g_prof = &marks;
   int rc = CVT_OK;
   do {
+    prof_mark(m->stream, "prep");          // weight-only kernels ahead of stage 1: K-major / TF32 weight copies, the folded q/k/v products
     if (forward_impl(m, img_dev, proc_dev, batch, training) != cudaSuccess) { rc = CVT_ERR_CUDA; break; }
     if (training) {
       if (launch_mse_loss(m->pred, y_dev, batch * m->cfg.num_classes, m->metrics, m->dpred, 1.f, 0, m->stream) != cudaSuccess) { rc = CVT_ERR_CUDA; break; }
@@ -2142,9 +2152,11 @@ int cvt_profile_step(cvt_model* h, const float* img_dev, const float* proc_dev, 
   m->prof_groups.clear();
   for (size_t i = 0; i + 1 < marks.size() && n < max_entries; ++i) {
     float t = 0.f; cudaEventElapsedTime(&t, marks[i].ev, marks[i + 1].ev);
-    if (!strncmp(marks[i].name, "end", 3)) continue;
-    names[n] = marks[i].name; ms[n] = t; ++n;
-    m->prof_groups.push_back({marks[i].name, (int)(marks[i + 1].launches - marks[i].launches)});
+    const char* nm = marks[i].name;
+    if (!strcmp(nm, "end_forward") && training) nm = "loss";      // the separate loss kernel of the profiled step (the fused head emits it in cvt_train_step)
+    else if (!strncmp(nm, "end", 3)) continue;
+    names[n] = nm; ms[n] = t; ++n;
+    m->prof_groups.push_back({nm, (int)(marks[i + 1].launches - marks[i].launches)});
   }
   for (auto& mk : marks) cudaEventDestroy(mk.ev);
   *n_entries = n;

@@ -411,6 +411,12 @@ class CvtEngine:
         buf = (C.c_uint8 * len(handles)).from_buffer_copy(handles)
         L.check(self.lib.cvt_comm_peer_open(self.h, buf, int(sync_grads)), "cvt_comm_peer_open")
 
+    def gemm_dispatch_counts(self, reset: bool = False):
+        """(gemm_tma, gemm_tc, gemm_simt) launches issued by this thread since the last reset (cvt_gemm_dispatch_counts)."""
+        out = (C.c_int64 * 3)()
+        L.check(self.lib.cvt_gemm_dispatch_counts(out, int(reset)))
+        return tuple(int(v) for v in out)
+
     def comm_peer_close(self):
         L.check(self.lib.cvt_comm_peer_close(self.h), "cvt_comm_peer_close")
 
