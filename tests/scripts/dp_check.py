@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Data-parallel correctness on real GPUs: run under torchrun with N >= 2 ranks.
 
-  torchrun --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tools/dp_check.py [--precision tf32]
+  torchrun --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tests/scripts/dp_check.py [--precision tf32]
 
 1. one cvt_train_step with lr = 0 on a global batch split contiguously over the ranks: the gradient arena every rank holds after the
    NCCL all-reduce must equal the MEAN of the per-shard oracle gradients (per-replica BatchNorm statistics, MirroredStrategy semantics);
@@ -14,7 +14,7 @@ import sys
 
 import numpy as np
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 
 
