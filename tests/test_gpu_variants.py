@@ -99,3 +99,22 @@ def test_variant_errors_are_loud():
         T.CvtEngine(T.CvtConfig.reference("dw_bn", False, head="cls"))            # cls head without a cls token
     with pytest.raises(ValueError):
         T.CvtConfig.reference(head="nope").to_c()
+
+
+def test_which_contraction_kernels_the_layer_by_layer_tf32_path_uses():
+    """The Grad-CAM script's model in TF32 mode runs the unfolded (layer-by-layer) path.  Pins where its dense products go: everything the
+    TMA-fed kernel takes goes there; the ConvEmbeds (implicit GEMM with a gathered A operand: stage 1 has Cin = 1, the unfolded path keeps
+    no patch matrix) and the split-K weight gradients go to the older tcgen05 kernel (gemm_tc.cu); nothing lands on the FFMA kernel."""
+    hw = (64, 64)
+    spec = O.gradcam_spec(False, "dw_bn", image_h=hw[0], image_w=hw[1])
+    cfg = T.CvtConfig.gradcam(False, "dw_bn", image_h=hw[0], image_w=hw[1], max_batch=4, precision="tf32")
+    eng, params, img, proc, y = _pair(spec, cfg, 4)
+    eng.set_dropout("off")
+    eng.set_graphs(False)
+    eng.gemm_dispatch_counts(reset=True)
+    eng.train_step(img, proc, y, 1e-3)
+    tma, tc, simt = eng.gemm_dispatch_counts(reset=True)
+    print("\n[dispatch] gradcam variant, TF32 unfolded: gemm_tma %d, gemm_tc %d, gemm_simt %d" % (tma, tc, simt))
+    assert tma > 0 and tc > 0, (tma, tc, simt)
+    assert simt == 0, (tma, tc, simt)
+    eng.close()

@@ -668,9 +668,8 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
     }
     else if (fast) {
       dp.nparts = kStatParts;
-      static const bool use_col = getenv("CVT_NO_DWCOL") == nullptr;
-      cudaError_t e = (m->folded && bn && use_col) ? launch_dwcol_fwd(dp, s, &stat_parts) : cudaErrorNotSupported;
-      if (e == cudaErrorNotSupported) e = (m->folded && bn) ? launch_dwplane_fwd(dp, s) : cudaErrorNotSupported;
+      // dw_bn in the folded path: the column walkers (dwcol.cu); avg / linear projections and the layer-by-layer path: the register-window kernels
+      cudaError_t e = (m->folded && bn) ? launch_dwcol_fwd(dp, s, &stat_parts) : cudaErrorNotSupported;
       if (e == cudaErrorNotSupported) e = launch_dwproj_fwd2(dp, s);
       CVT_CUDA(e);
     }
@@ -934,9 +933,7 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
     dp.B = B; dp.H = g.H; dp.W = g.W; dp.D = D; dp.Tc = g.Tc; dp.has_cls = g.has_cls; dp.dxn = m->gE; dp.ddw = bn ? G + w.dw : nullptr;
     if (g.D <= 256 && (g.D & 3) == 0) {
       dp.ddw_part = m->dw_part;
-      static const bool use_col = getenv("CVT_NO_DWCOL") == nullptr;
-      cudaError_t e = (bn && use_col) ? launch_dwcol_bwd(dp, s) : cudaErrorNotSupported;
-      if (e == cudaErrorNotSupported) e = bn ? launch_dwplane_bwd(dp, s) : cudaErrorNotSupported;
+      cudaError_t e = bn ? launch_dwcol_bwd(dp, s) : cudaErrorNotSupported;
       if (e == cudaErrorNotSupported) e = launch_dwproj_bwd2(dp, s);
       CVT_CUDA(e);
     }

@@ -65,9 +65,6 @@ cudaError_t launch_dwproj_bwd(const DwProjBwdP& p, cudaStream_t s);
 // register sliding-window versions (dwproj.cu); cudaErrorNotSupported -> caller uses the generic kernels above
 cudaError_t launch_dwproj_fwd2(const DwProjP& p, cudaStream_t s);
 cudaError_t launch_dwproj_bwd2(const DwProjBwdP& p, cudaStream_t s);
-// shared-memory band kernels for the dw_bn method (dwplane.cu); cudaErrorNotSupported -> caller uses the kernels above
-cudaError_t launch_dwplane_fwd(const DwProjP& p, cudaStream_t s);
-cudaError_t launch_dwplane_bwd(const DwProjBwdP& p, cudaStream_t s);
 // register column walkers, one channel per lane (dwcol.cu): D % 32 == 0; cudaErrorNotSupported -> caller uses the kernels above
 cudaError_t launch_dwcol_fwd(const DwProjP& p, cudaStream_t s, int* stat_slices);
 cudaError_t launch_dwcol_bwd(const DwProjBwdP& p, cudaStream_t s);
