@@ -83,3 +83,31 @@ def test_tma_wgrad_matches_truncated_tf32(Kin, N, tokens):
     got = run(1, 0, Kin, N, tokens, 1, 8, X, dY)
     err = np.abs(got - ref).max()
     assert err < 2e-4 * np.sqrt(tokens), (Kin, N, tokens, err, np.abs(got).max())
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 64, 32), (256, 128, 96), (300, 256, 64), (1000, 192, 256), (65536, 64, 64), (16384, 128, 512),
+                                   (4160, 256, 1024), (4160, 1024, 256)])
+def test_tma_gemm_x3_is_fp32_grade(M, N, K):
+    """The error-compensated variant (CVT_PREC_TF32X3): operand tiles split into high and low parts in shared memory, three tcgen05 MMAs per
+    k-step.  Against the fp64 product of the UNROUNDED operands: at least 50x closer than one TF32 pass."""
+    rng = np.random.default_rng(M + N * 3 + K + 1)
+    A = rng.standard_normal((M, K)).astype(np.float32)
+    B = rng.standard_normal((K, N)).astype(np.float32)
+    ref = A.astype(np.float64) @ B.astype(np.float64)
+    one = run(0, 1, M, N, K, 1, 4, A, np.ascontiguousarray(B.T))
+    got = run(0, 1, M, N, K, 1, 4 | 16, A, np.ascontiguousarray(B.T))
+    e1, e3 = np.abs(one - ref).max(), np.abs(got - ref).max()
+    # what is left is the tensor core's own accumulation (one-sided rounding of the running sum in TMEM, ~1e-6 per accumulated k): linear in K
+    assert e3 < 2e-6 * K + 2e-5 and e3 < e1 / 50, (M, N, K, e1, e3)
+
+
+@pytest.mark.parametrize("Kin,N,tokens", [(64, 64, 65536), (64, 256, 8192), (256, 64, 8192), (128, 512, 4096), (256, 1024, 4160), (192, 192, 1000)])
+def test_tma_wgrad_x3_is_fp32_grade(Kin, N, tokens):
+    rng = np.random.default_rng(Kin + N * 3 + tokens + 1)
+    X = rng.standard_normal((tokens, Kin)).astype(np.float32)
+    dY = rng.standard_normal((tokens, N)).astype(np.float32)
+    ref = X.astype(np.float64).T @ dY.astype(np.float64)
+    one = run(1, 0, Kin, N, tokens, 1, 8, X, dY)
+    got = run(1, 0, Kin, N, tokens, 1, 8 | 16, X, dY)
+    e1, e3 = np.abs(one - ref).max(), np.abs(got - ref).max()
+    assert e3 < 1e-6 * tokens + 2e-5 and e3 < e1 / 50, (Kin, N, tokens, e1, e3)      # split-K partials are added with fp32 atomics

@@ -51,6 +51,7 @@ struct GemmP {
   const float* epi_coef = nullptr; long long epi_coef_bs = 0; int epi_skip_period = 0;   // EPI_BN_BWD (rows m % period == 0 are cls rows: identity)
   long long* trace = nullptr;                  // diagnostics only (CVT_GEMM_TRACE): clock64 timeline of CTA 0 of gemm_tma_kernel
   int dbg = 0;                                 // diagnostics only (cvt_debug_gemm): bit 0 swaps LBO/SBO of MN-major descriptors
+  int x3 = 0;                                  // TMA kernel only: error-compensated product (hi.hi + lo.hi + hi.lo, operands split in shared memory)
   float* aux = nullptr;                        // same indexing as C: GELU pre-activation (write) / saved activation (read)
 };
 
@@ -73,6 +74,7 @@ struct WgradP {
   float* dW = nullptr; long long dw_bs = 0;
   float* db = nullptr; long long db_bs = 0;
   int dbg = 0;
+  int x3 = 0;                                  // error-compensated product: both operand tiles are split into high and low parts in shared memory
   // conv != 0: X is not a matrix but the im2col view of a Conv2D input (ConvEmbed weight gradient): X(token, feature) =
   // x_pad[b, s*i + kh, s*j + kw, c] with token = (b, i, j), feature = (kh, kw, c); boxes are strided TMA boxes of the NHWC map itself
   int conv = 0; ConvGeom cv{0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};

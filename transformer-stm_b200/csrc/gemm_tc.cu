@@ -393,8 +393,9 @@ extern "C" CVT_API int cvt_debug_gemm(int a_mode, int b_mode, int M, int N, int 
   p.B = dB; p.b_mode = b_mode; p.ldb = b_mode == B_KN ? N : K;
   p.C = dC; p.ldc = N; if (splitk > 1) p.epi = EPI_ATOMIC;
   p.dbg = (use_tc >> 1) & 1;
+  const int x3 = (use_tc >> 4) & 1; use_tc &= 15; p.x3 = x3;      // bit 4: the error-compensated (3 x TF32) variant of the TMA-fed kernels
   if (use_tc & 8) {      // TMA-fed weight-gradient kernel: A is X[tokens=K, Kin=M], B is dY[tokens=K, N]
-    WgradP w; w.X = dA; w.ldx = M; w.Kin = M; w.dY = dB; w.lddy = N; w.N = N; w.tokens = K; w.dW = dC; w.dbg = use_tc & 1;
+    WgradP w; w.X = dA; w.ldx = M; w.Kin = M; w.dY = dB; w.lddy = N; w.N = N; w.tokens = K; w.dW = dC; w.dbg = use_tc & 1; w.x3 = x3;
     if (a_mode != A_TRANS || b_mode != B_KN || !wgrad_tma_supports(w)) { cudaFree(dA); cudaFree(dB); cudaFree(dC); set_error("cvt_debug_gemm: shape not supported by the wgrad kernel"); return CVT_ERR_INVALID; }
     e = launch_wgrad_tma(w, 0);
     if (e != cudaSuccess) return fail(e);

@@ -26,27 +26,37 @@ constexpr int BM = 128, BK = 32, NEPI = 16, NTHREADS = 64 + 32 * NEPI;   // 16 e
 constexpr int A_STAGE = BM * BK * 4;                 // 16 KB
 constexpr int STG_BYTES = NEPI * 32 * 20 * 4;        // epilogue transpose tiles (32 rows x 16 columns, padded), one per epilogue warp
 
-template <int BN> struct TCfg {
+// X3: error-compensated products (CVT_PREC_TF32X3).  The tensor core truncates an fp32 word to TF32, so the word a TMA box delivers IS
+// the high part; four extra warps write the low parts (x - trunc(x), exact in fp32) of both operand tiles of a stage into twin tiles and
+// the issuer runs three MMAs per k-step: hi.hi + lo.hi + hi.lo (the dropped lo.lo term is 2^-22 relative).  fp32-grade results on tcgen05.
+constexpr int NSPLIT = 4;                              // splitter warps of the X3 variant
+template <int BN, bool X3> struct TCfg {
   static constexpr int B_STAGE = BN * BK * 4;
-  static constexpr int NS = BN == 64 ? 6 : (BN == 128 ? 5 : 3);
-  static constexpr int SMEM = 1024 + NS * (A_STAGE + B_STAGE) + STG_BYTES + (2 * NS + 4) * 8 + 16;
+  static constexpr int NS = X3 ? (BN == 64 ? 3 : 2) : (BN == 64 ? 6 : (BN == 128 ? 5 : 3));      // X3: twice the bytes per stage, N tiles of at most 128
+  static constexpr int STAGE_ALL = (A_STAGE + B_STAGE) * (X3 ? 2 : 1);
+  static constexpr int SMEM = 1024 + NS * STAGE_ALL + STG_BYTES + (3 * NS + 4) * 8 + 16;
+  static_assert(SMEM <= 232448, "gemm_tma: shared memory budget");
+  static constexpr int THREADS = NTHREADS + (X3 ? 32 * NSPLIT : 0);
 };
 
-template <int BN, uint32_t E>
-__global__ void __launch_bounds__(NTHREADS, 1) gemm_tma_kernel(const __grid_constant__ GemmP p, const __grid_constant__ CUtensorMap tmA,
-                                                                const __grid_constant__ CUtensorMap tmB, int m_tiles, int n_tiles,
-                                                                int num_tiles) {
-  using C = TCfg<BN>;
+template <int BN, uint32_t E, bool X3>
+__global__ void __launch_bounds__(TCfg<BN, X3>::THREADS, 1) gemm_tma_kernel(const __grid_constant__ GemmP p, const __grid_constant__ CUtensorMap tmA,
+                                                                             const __grid_constant__ CUtensorMap tmB, int m_tiles, int n_tiles,
+                                                                             int num_tiles) {
+  using C = TCfg<BN, X3>;
   constexpr int NS = C::NS;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
   uint8_t* sA = smem;
   uint8_t* sB = sA + NS * A_STAGE;
-  float* stg_all = reinterpret_cast<float*>(sB + NS * C::B_STAGE);
+  uint8_t* sAlo = sB + NS * C::B_STAGE;                // X3 only: low parts of the A / B tiles of every stage
+  uint8_t* sBlo = sAlo + (X3 ? NS * A_STAGE : 0);
+  float* stg_all = reinterpret_cast<float*>(sBlo + (X3 ? NS * C::B_STAGE : 0));
   uint64_t* full = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(stg_all) + STG_BYTES);
   uint64_t* empty = full + NS;
-  uint64_t* acc_full = empty + NS;       // [2]
+  uint64_t* ready = empty + NS;          // X3: the splitter warps are done with the stage
+  uint64_t* acc_full = ready + NS;       // [2]
   uint64_t* acc_empty = acc_full + 2;    // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
 
@@ -58,7 +68,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tma_kernel(const __grid_cons
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB);
-    for (int i = 0; i < NS; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    for (int i = 0; i < NS; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); mbar_init(&ready[i], 32 * NSPLIT); }
     for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], NEPI); }
     mbar_fence_init();
   }
@@ -108,18 +118,49 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_tma_kernel(const __grid_cons
         tc_fence_after();
         const uint32_t d = tmem_base + buf * BN;
         for (int kt = 0; kt < nk; ++kt) {
-          mbar_wait(&full[stage], phase);
+          mbar_wait(X3 ? &ready[stage] : &full[stage], phase);
           if (kt == 0 && it < 30) GEMM_TRACE(8 + it * 8 + 3);
           tc_fence_after();
           const uint32_t a0 = smem_u32(sA + stage * A_STAGE), b0 = smem_u32(sB + stage * C::B_STAGE);
 #pragma unroll
-          for (int j = 0; j < BK / 8; ++j)
-            mma_tf32_ss(d, make_smem_desc(a0 + j * 32, 16, 1024), make_smem_desc(b0 + j * 32, 16, 1024), idesc, (kt > 0 || j > 0) ? 1u : 0u);
+          for (int j = 0; j < BK / 8; ++j) {
+            const uint64_t da = make_smem_desc(a0 + j * 32, 16, 1024), db = make_smem_desc(b0 + j * 32, 16, 1024);
+            mma_tf32_ss(d, da, db, idesc, (kt > 0 || j > 0) ? 1u : 0u);
+            if (X3) {
+              mma_tf32_ss(d, make_smem_desc(smem_u32(sAlo + stage * A_STAGE) + j * 32, 16, 1024), db, idesc, 1u);
+              mma_tf32_ss(d, da, make_smem_desc(smem_u32(sBlo + stage * C::B_STAGE) + j * 32, 16, 1024), idesc, 1u);
+            }
+          }
           mma_commit(&empty[stage]);
           if (++stage == NS) { stage = 0; phase ^= 1; }
         }
         mma_commit(&acc_full[buf]);
         if (it < 30) GEMM_TRACE(8 + it * 8 + 4);
+      }
+    }
+  } else if (X3 && warp >= 2 + NEPI) {
+    // ===== X3 splitter warps: low parts of both operand tiles of every stage, element for element (the swizzle is position-preserving) =====
+    const int t = threadIdx.x - 32 * (2 + NEPI);
+    int stage = 0; uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int kt = 0; kt < nk; ++kt) {
+        mbar_wait(&full[stage], phase);
+        auto split = [&](const uint8_t* src, uint8_t* dst, int n4) {
+          for (int i = t; i < n4; i += 32 * NSPLIT) {
+            const float4 v = reinterpret_cast<const float4*>(src)[i];
+            float4 lo;
+            // the low part is itself rounded to nearest TF32 here: left to the tensor core's truncation its error would be one-sided and
+            // grow linearly with K
+            lo.x = to_tf32(v.x - __uint_as_float(__float_as_uint(v.x) & 0xFFFFE000u)); lo.y = to_tf32(v.y - __uint_as_float(__float_as_uint(v.y) & 0xFFFFE000u));
+            lo.z = to_tf32(v.z - __uint_as_float(__float_as_uint(v.z) & 0xFFFFE000u)); lo.w = to_tf32(v.w - __uint_as_float(__float_as_uint(v.w) & 0xFFFFE000u));
+            reinterpret_cast<float4*>(dst)[i] = lo;
+          }
+        };
+        split(sA + stage * A_STAGE, sAlo + stage * A_STAGE, A_STAGE / 16);
+        split(sB + stage * C::B_STAGE, sBlo + stage * C::B_STAGE, C::B_STAGE / 16);
+        fence_proxy_async_smem();
+        mbar_arrive(&ready[stage]);
+        if (++stage == NS) { stage = 0; phase ^= 1; }
       }
     }
   } else {
@@ -303,11 +344,11 @@ bool make_tmap_conv(CUtensorMap* out, const float* base, int hin, int win, int c
 }
 
 namespace {
-template <int BN, uint32_t E>
+template <int BN, uint32_t E, bool X3>
 cudaError_t launch_tma_cfg(const GemmP& p, cudaStream_t s) {
   static bool configured = false;
   if (!configured) {
-    CVT_CUDA(cudaFuncSetAttribute(gemm_tma_kernel<BN, E>, cudaFuncAttributeMaxDynamicSharedMemorySize, TCfg<BN>::SMEM));
+    CVT_CUDA(cudaFuncSetAttribute(gemm_tma_kernel<BN, E, X3>, cudaFuncAttributeMaxDynamicSharedMemorySize, TCfg<BN, X3>::SMEM));
     configured = true;
   }
   CUtensorMap tmA, tmB;
@@ -321,15 +362,19 @@ cudaError_t launch_tma_cfg(const GemmP& p, cudaStream_t s) {
   if (!make_tmap_3d(&tmB, p.B, p.K, p.N, p.batch, p.ldb, p.b_bs0, BN, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
   const int m_tiles = cdiv(p.M, BM), n_tiles = p.N / BN, num_tiles = m_tiles * n_tiles * p.batch;
   const int grid = num_tiles < kNumSMs ? num_tiles : kNumSMs;
-  gemm_tma_kernel<BN, E><<<grid, NTHREADS, TCfg<BN>::SMEM, s>>>(p, tmA, tmB, m_tiles, n_tiles, num_tiles);
+  gemm_tma_kernel<BN, E, X3><<<grid, TCfg<BN, X3>::THREADS, TCfg<BN, X3>::SMEM, s>>>(p, tmA, tmB, m_tiles, n_tiles, num_tiles);
   CVT_LAUNCH_CHECK();
   return cudaSuccess;
 }
 template <uint32_t E>
 cudaError_t launch_tma_bn(const GemmP& p, int bn, cudaStream_t s) {
-  if (bn == 256) return launch_tma_cfg<256, E>(p, s);
-  if (bn == 128) return launch_tma_cfg<128, E>(p, s);
-  return launch_tma_cfg<64, E>(p, s);
+  if (p.x3) {
+    if (bn >= 128) return launch_tma_cfg<128, E, true>(p, s);
+    return launch_tma_cfg<64, E, true>(p, s);
+  }
+  if (bn == 256) return launch_tma_cfg<256, E, false>(p, s);
+  if (bn == 128) return launch_tma_cfg<128, E, false>(p, s);
+  return launch_tma_cfg<64, E, false>(p, s);
 }
 constexpr uint32_t kTmaEpiKinds = EPI_GELU | EPI_RESID | EPI_GELU_BWD | EPI_PHILOX | EPI_BN_BWD | EPI_GELU_DSAVE;
 }  // namespace

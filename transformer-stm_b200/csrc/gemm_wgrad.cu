@@ -20,28 +20,36 @@ using namespace tc;
 namespace {
 constexpr int BM = 128, KT = 32, BOX = 32 * KT * 4, NTHREADS = 192;      // BOX: one 32-feature x 32-token box = 4 KB
 
-template <int BN> struct WCfg {
+// X3: error-compensated variant (CVT_PREC_TF32X3), as in gemm_tma.cu: four more warps write the low parts of both operand tiles of a
+// stage (x - trunc(x)) into twin tiles, three MMAs per step (hi.hi + lo.hi + hi.lo)
+constexpr int NSPLITW = 4;
+template <int BN, bool X3> struct WCfg {
   static constexpr int A_STAGE = (BM / 32) * BOX, B_STAGE = (BN / 32) * BOX;
-  static constexpr int NS = BN == 64 ? 8 : (BN == 128 ? 6 : 4);
+  static constexpr int NS = X3 ? (BN == 64 ? 4 : (BN == 128 ? 3 : 2)) : (BN == 64 ? 8 : (BN == 128 ? 6 : 4));
   static constexpr int STG = 4 * 32 * 36 * 4;
-  static constexpr int SMEM = 1024 + NS * (A_STAGE + B_STAGE) + STG + (2 * NS + 1) * 8 + 16;
+  static constexpr int SMEM = 1024 + NS * (A_STAGE + B_STAGE) * (X3 ? 2 : 1) + STG + (3 * NS + 1) * 8 + 16;
+  static constexpr int THREADS = NTHREADS + (X3 ? 32 * NSPLITW : 0);
+  static_assert(SMEM <= 232448, "wgrad_tma: shared memory budget");
 };
 
-template <int BN>
-__global__ void __launch_bounds__(NTHREADS, 1) wgrad_tma_kernel(const __grid_constant__ WgradP p, const __grid_constant__ CUtensorMap tmX,
-                                                                 const __grid_constant__ CUtensorMap tmY, int m_tiles, int n_tiles,
-                                                                 int splits, int steps_per_split) {
-  using C = WCfg<BN>;
+template <int BN, bool X3>
+__global__ void __launch_bounds__(WCfg<BN, X3>::THREADS, 1) wgrad_tma_kernel(const __grid_constant__ WgradP p, const __grid_constant__ CUtensorMap tmX,
+                                                                              const __grid_constant__ CUtensorMap tmY, int m_tiles, int n_tiles,
+                                                                              int splits, int steps_per_split) {
+  using C = WCfg<BN, X3>;
   constexpr int NS = C::NS;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
   uint8_t* sA = smem;
   uint8_t* sB = sA + NS * C::A_STAGE;
-  float* stg_all = reinterpret_cast<float*>(sB + NS * C::B_STAGE);
+  uint8_t* sAlo = sB + NS * C::B_STAGE;
+  uint8_t* sBlo = sAlo + (X3 ? NS * C::A_STAGE : 0);
+  float* stg_all = reinterpret_cast<float*>(sBlo + (X3 ? NS * C::B_STAGE : 0));
   uint64_t* full = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(stg_all) + C::STG);
   uint64_t* empty = full + NS;
-  uint64_t* acc_full = empty + NS;
+  uint64_t* ready = empty + NS;
+  uint64_t* acc_full = ready + NS;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -56,7 +64,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) wgrad_tma_kernel(const __grid_con
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmX); tma_prefetch_desc(&tmY);
-    for (int i = 0; i < NS; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], do_colsum ? 5 : 1); }
+    for (int i = 0; i < NS; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], do_colsum ? 5 : 1); mbar_init(&ready[i], 32 * NSPLITW); }
     mbar_init(acc_full, 1);
     mbar_fence_init();
   }
@@ -94,17 +102,45 @@ __global__ void __launch_bounds__(NTHREADS, 1) wgrad_tma_kernel(const __grid_con
       const uint32_t lbo = (p.dbg & 1) ? 512u : (uint32_t)BOX, sbo = (p.dbg & 1) ? (uint32_t)BOX : 512u;
       int stage = 0; uint32_t phase = 0;
       for (int it = 0; it < nsteps; ++it) {
-        mbar_wait(&full[stage], phase);
+        mbar_wait(X3 ? &ready[stage] : &full[stage], phase);
         tc_fence_after();
         const uint32_t a0 = smem_u32(sA + stage * C::A_STAGE), b0 = smem_u32(sB + stage * C::B_STAGE);
 #pragma unroll
-        for (int j = 0; j < KT / 8; ++j)      // 8 tokens = two 4-token groups of 512 bytes inside every box
-          mma_tf32_ss(tmem_base, make_smem_desc(a0 + j * 1024, lbo, sbo, kLayoutSw128Base32),
-                      make_smem_desc(b0 + j * 1024, lbo, sbo, kLayoutSw128Base32), idesc, (it > 0 || j > 0) ? 1u : 0u);
+        for (int j = 0; j < KT / 8; ++j) {    // 8 tokens = two 4-token groups of 512 bytes inside every box
+          const uint64_t da = make_smem_desc(a0 + j * 1024, lbo, sbo, kLayoutSw128Base32), db = make_smem_desc(b0 + j * 1024, lbo, sbo, kLayoutSw128Base32);
+          mma_tf32_ss(tmem_base, da, db, idesc, (it > 0 || j > 0) ? 1u : 0u);
+          if (X3) {
+            mma_tf32_ss(tmem_base, make_smem_desc(smem_u32(sAlo + stage * C::A_STAGE) + j * 1024, lbo, sbo, kLayoutSw128Base32), db, idesc, 1u);
+            mma_tf32_ss(tmem_base, da, make_smem_desc(smem_u32(sBlo + stage * C::B_STAGE) + j * 1024, lbo, sbo, kLayoutSw128Base32), idesc, 1u);
+          }
+        }
         mma_commit(&empty[stage]);
         if (++stage == NS) { stage = 0; phase ^= 1; }
       }
       mma_commit(acc_full);
+    }
+  } else if (X3 && warp >= 6) {
+    // ===== X3 splitter warps =====
+    const int t = threadIdx.x - 32 * 6;
+    int stage = 0; uint32_t phase = 0;
+    for (int it = 0; it < nsteps; ++it) {
+      mbar_wait(&full[stage], phase);
+      auto split = [&](const uint8_t* src, uint8_t* dst, int n4) {
+        for (int i = t; i < n4; i += 32 * NSPLITW) {
+          const float4 v = reinterpret_cast<const float4*>(src)[i];
+          float4 lo;
+          // the low part is itself rounded to nearest TF32 here: left to the tensor core's truncation its error would be one-sided and
+          // grow linearly with K
+          lo.x = to_tf32(v.x - __uint_as_float(__float_as_uint(v.x) & 0xFFFFE000u)); lo.y = to_tf32(v.y - __uint_as_float(__float_as_uint(v.y) & 0xFFFFE000u));
+          lo.z = to_tf32(v.z - __uint_as_float(__float_as_uint(v.z) & 0xFFFFE000u)); lo.w = to_tf32(v.w - __uint_as_float(__float_as_uint(v.w) & 0xFFFFE000u));
+          reinterpret_cast<float4*>(dst)[i] = lo;
+        }
+      };
+      split(sA + stage * C::A_STAGE, sAlo + stage * C::A_STAGE, C::A_STAGE / 16);
+      split(sB + stage * C::B_STAGE, sBlo + stage * C::B_STAGE, C::B_STAGE / 16);
+      fence_proxy_async_smem();
+      mbar_arrive(&ready[stage]);
+      if (++stage == NS) { stage = 0; phase ^= 1; }
     }
   } else {
     const int ew = warp - 2, et = ew * 32 + lane;          // 0..127
@@ -170,11 +206,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) wgrad_tma_kernel(const __grid_con
   if (warp == 1) tmem_dealloc(tmem_base, BN);
 }
 
-template <int BN>
+template <int BN, bool X3>
 cudaError_t launch_w(const WgradP& p, cudaStream_t s) {
   static bool configured = false;
   if (!configured) {
-    CVT_CUDA(cudaFuncSetAttribute(wgrad_tma_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, WCfg<BN>::SMEM));
+    CVT_CUDA(cudaFuncSetAttribute(wgrad_tma_kernel<BN, X3>, cudaFuncAttributeMaxDynamicSharedMemorySize, WCfg<BN, X3>::SMEM));
     configured = true;
   }
   CUtensorMap tmX, tmY;
@@ -195,7 +231,7 @@ cudaError_t launch_w(const WgradP& p, cudaStream_t s) {
   if (splits < 1) splits = 1;
   const int steps_per_split = cdiv(total_steps, splits);
   splits = cdiv(total_steps, steps_per_split);
-  wgrad_tma_kernel<BN><<<tiles * splits, NTHREADS, WCfg<BN>::SMEM, s>>>(p, tmX, tmY, m_tiles, n_tiles, splits, steps_per_split);
+  wgrad_tma_kernel<BN, X3><<<tiles * splits, WCfg<BN, X3>::THREADS, WCfg<BN, X3>::SMEM, s>>>(p, tmX, tmY, m_tiles, n_tiles, splits, steps_per_split);
   CVT_LAUNCH_CHECK();
   return cudaSuccess;
 }
@@ -217,9 +253,14 @@ bool wgrad_tma_supports(const WgradP& p) {
 
 cudaError_t launch_wgrad_tma(const WgradP& p, cudaStream_t s) {
   if (!wgrad_tma_supports(p)) { set_error("wgrad_tma: unsupported shape"); return cudaErrorNotSupported; }
-  if (p.N > 128) return launch_w<256>(p, s);
-  if (p.N > 64) return launch_w<128>(p, s);
-  return launch_w<64>(p, s);
+  if (p.x3) {
+    if (p.N > 128) return launch_w<256, true>(p, s);
+    if (p.N > 64) return launch_w<128, true>(p, s);
+    return launch_w<64, true>(p, s);
+  }
+  if (p.N > 128) return launch_w<256, false>(p, s);
+  if (p.N > 64) return launch_w<128, false>(p, s);
+  return launch_w<64, false>(p, s);
 }
 
 }  // namespace cvt
