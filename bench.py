@@ -136,7 +136,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--precision", default=os.environ.get("CVT_PRECISION", "tf32"), choices=["fp32", "tf32"])
+    ap.add_argument("--precision", default=os.environ.get("CVT_PRECISION", "tf32"), choices=["fp32", "tf32", "tf32x3"])
     ap.add_argument("--config", default="cfg2", choices=sorted(CONFIGS))
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (default: the configuration's own)")
     ap.add_argument("--mode", default="both", choices=["both", "train", "infer"])
@@ -430,7 +430,7 @@ def run_config(a, cfgname, batch, modes, first=True):
     train_line = modes[0] == "train"
     line = {"metric": METRIC if train_line else "cvt_par_infer_images_per_sec", "value": head["value"], "unit": UNIT, "n_gpus": world, "steps": a.steps,
             "warmup": max(a.warmup, 3), "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": {"fp32": "f32", "tf32": "tf32"}[a.precision], "data": "synthetic",
+            "dtype": {"fp32": "f32", "tf32": "tf32", "tf32x3": "tf32x3"}[a.precision], "data": "synthetic",
             "config": {"workload": b.wl, "name": cfgname, "per_gpu_batch": batch, "global_batch": batch * world, "parallelism": "dp%d" % world,
                        "l2": "flushed between timed steps" if b.flush is not None else "not flushed",
                        "weights": "random-init (Keras initialisers)", "dropout": "philox 0.1 (train), off (inference)"},

@@ -54,7 +54,9 @@ enum { CVT_HEAD_AUTO = 0, CVT_HEAD_CLS_LN = 1, CVT_HEAD_LN_MEAN = 2, CVT_HEAD_CL
 /* arithmetic of the dense contractions */
 enum { CVT_PREC_FP32 = 0,   /* fp32 FFMA everywhere (exact-parity mode) */
        CVT_PREC_TF32 = 1,   /* tcgen05 kind::tf32, fp32 accumulate in TMEM (what TF does on sm_80+) */
-       CVT_PREC_BF16 = 2 }; /* tcgen05 kind::f16 (bf16 operands), fp32 accumulate */
+       CVT_PREC_BF16 = 2,   /* tcgen05 kind::f16 (bf16 operands), fp32 accumulate: NOT implemented, cvt_create refuses it */
+       CVT_PREC_TF32X3 = 3 }; /* error-compensated tcgen05: every dense product as hi.hi + lo.hi + hi.lo (operand tiles split in shared memory),
+                                 activations kept unrounded; attention stays single-pass TF32.  Between TF32 speed and fp32 accuracy. */
 /* dropout source */
 enum { CVT_DROPOUT_OFF = 0, CVT_DROPOUT_PHILOX = 1, CVT_DROPOUT_MASKS = 2 };
 

@@ -10,7 +10,7 @@ ABI_VERSION = 3
 
 PROJ = {"dw_bn": 0, "avg": 1, "linear": 2, "linear_dense": 3}
 HEAD = {"auto": 0, "cls_ln": 1, "ln_mean": 2, "cls": 3, "mean": 4, "gap": 4}
-PREC = {"fp32": 0, "tf32": 1, "bf16": 2}
+PREC = {"fp32": 0, "tf32": 1, "bf16": 2, "tf32x3": 3}
 DROPOUT_OFF, DROPOUT_PHILOX, DROPOUT_MASKS = 0, 1, 2
 
 

@@ -631,7 +631,7 @@ cudaError_t attention_forward_tc(Model* m, int si, int B, cudaStream_t s) {
   const long long RD = (long long)B * g.Tc * g.D;
   AttnP p{};
   p.Q = a.qkv2; p.K = a.qkv2 + RD; p.V = a.qkv2 + 2 * RD; p.O = a.attn_o; p.LSE = a.lse;
-  p.Tc = g.Tc; p.D = g.D; p.heads = g.heads; p.dq_scale = 0.125f; p.round_out = m->folded;
+  p.Tc = g.Tc; p.D = g.D; p.heads = g.heads; p.dq_scale = 0.125f; p.round_out = m->folded && !m->x3;      // (TF32X3: O / dQ / dK / dV feed error-compensated GEMMs, keep them in full fp32)
   return run_fwd(p, B, s);
 }
 
@@ -641,7 +641,7 @@ cudaError_t attention_backward_tc(Model* m, int si, int B, const float* dO, floa
   AttnP p{};
   p.Q = a.qkv2; p.K = a.qkv2 + RD; p.V = a.qkv2 + 2 * RD; p.O = a.attn_o; p.LSE = a.lse;
   p.dO = dO; p.Dd = m->attn_dd; p.dQ = dQKV; p.dK = dQKV + RD; p.dV = dQKV + 2 * RD;
-  p.Tc = g.Tc; p.D = g.D; p.heads = g.heads; p.dq_scale = 0.125f; p.round_out = m->folded;
+  p.Tc = g.Tc; p.D = g.D; p.heads = g.heads; p.dq_scale = 0.125f; p.round_out = m->folded && !m->x3;      // (TF32X3: O / dQ / dK / dV feed error-compensated GEMMs, keep them in full fp32)
   return run_bwd(p, m->attn_dd, B, s);
 }
 

@@ -56,8 +56,14 @@ static const char* kStageNames[CVT_MAX_STAGES][12] = {
 // which contraction kernel every run_gemm call went to (cvt_gemm_dispatch_counts): a TF32-mode product that quietly lands on the FFMA
 // kernel is a 5x slowdown nobody asked for, so tests pin the counts for the reference and the widened configuration
 thread_local long long g_gemm_dispatch[3] = {0, 0, 0};      // gemm_tma, gemm_tc, gemm_simt
-cudaError_t run_gemm(const Model* m, const GemmP& p, cudaStream_t s) {
+cudaError_t run_gemm(const Model* m, const GemmP& p_in, cudaStream_t s) {
   struct Count { int k; ~Count() { g_gemm_dispatch[k]++; } } count{2};
+  GemmP p = p_in;
+  if (m->x3) {
+    p.x3 = 1;                                  // the TMA-fed kernel runs three MMAs per k-step on split operand tiles
+    if (!(p.epi & EPI_KEEP_ROUND)) p.epi &= ~EPI_ROUND;      // nothing is pre-rounded in this mode except what only the attention kernels read
+  }
+  p.epi &= ~EPI_KEEP_ROUND;
   if (m->cfg.precision != CVT_PREC_FP32) {
     static const bool no_tma = getenv("CVT_NO_TMA") != nullptr;
     if (!no_tma) {
@@ -75,12 +81,15 @@ cudaError_t run_gemm(const Model* m, const GemmP& p, cudaStream_t s) {
       if (gemm_tma_supports(p)) { count.k = 0; return launch_gemm_tma(p, s); }
     }
     if (p.epi & EPI_GELU_DSAVE) { set_error("run_gemm: the saved-GELU-derivative epilogue exists only in the TMA kernel"); return cudaErrorNotSupported; }
-    if (gemm_tc_supports(p)) { count.k = 1; return launch_gemm_tc(p, s); }
+    if (!m->x3 && gemm_tc_supports(p)) { count.k = 1; return launch_gemm_tc(p, s); }      // (a single-pass TF32 kernel would break the TF32X3 contract)
   }
   if (p.epi & EPI_GELU_DSAVE) { set_error("run_gemm: the saved-GELU-derivative epilogue exists only in the TMA kernel"); return cudaErrorNotSupported; }
   if (p.epi & EPI_PHILOX) { set_error("run_gemm: in-epilogue dropout needs a tensor-core shape"); return cudaErrorNotSupported; }
   return launch_gemm_simt(p, s);
 }
+
+// producers round what only feeds single-pass TF32 products; CVT_PREC_TF32X3 keeps everything in full fp32 (its GEMM kernels split operands)
+static inline bool round_ops(const Model* m) { return m->folded && !m->x3; }
 
 // TF32 folded mode on the TMA kernel: the Mlp forward epilogue stores the GELU derivative instead of the pre-activation (gemm.cuh)
 static bool gelu_dsave(const Model* m, int D) {
@@ -125,7 +134,7 @@ static cudaError_t wgrad_bias(const Model* m, const float* X, long long ldx, int
   static const bool no_tma = getenv("CVT_NO_TMA") != nullptr;
   if (m->cfg.precision != CVT_PREC_FP32 && !no_tma) {
     WgradP w; w.X = X; w.ldx = ldx; w.x_bs = x_bs; w.Kin = Kin; w.dY = dY; w.lddy = lddy; w.dy_bs = dy_bs; w.N = Nout; w.tokens = tokens;
-    w.batch = batch; w.dW = dW; w.dw_bs = (long long)Kin * Nout; w.db = db; w.db_bs = Nout;
+    w.batch = batch; w.dW = dW; w.dw_bs = (long long)Kin * Nout; w.db = db; w.db_bs = Nout; w.x3 = m->x3 ? 1 : 0;
     if (wgrad_tma_supports(w)) return launch_wgrad_tma(w, s);
   }
   if (db) CVT_CUDA(launch_colsum(dY, lddy, rowmap_none(), tokens, Nout, batch, dy_bs, db, Nout, s));
@@ -333,7 +342,7 @@ int cvt_create(const cvt_config* cfg, cvt_model** out) {
     set_error("cvt_create: CVT_PREC_BF16 is not implemented (fp32 and tf32 are); refusing rather than running another precision under that name");
     return CVT_ERR_INVALID;
   }
-  if (c.precision != CVT_PREC_FP32 && c.precision != CVT_PREC_TF32) { set_error("cvt_create: unknown precision"); return CVT_ERR_INVALID; }
+  if (c.precision != CVT_PREC_FP32 && c.precision != CVT_PREC_TF32 && c.precision != CVT_PREC_TF32X3) { set_error("cvt_create: unknown precision"); return CVT_ERR_INVALID; }
   if (c.drop_rate < 0.f || c.drop_rate >= 1.f) { set_error("cvt_create: drop_rate must be in [0,1)"); return CVT_ERR_INVALID; }
   for (int i = 0; i < c.n_stages; ++i) {
     const cvt_stage_config& s = c.stage[i];
@@ -386,6 +395,8 @@ int cvt_create(const cvt_config* cfg, cvt_model** out) {
     bool variant = c.skip_proj_qkv != 0 || c.attn_drop_rate > 0.f;
     for (int i = 0; i < c.n_stages; ++i) variant = variant || c.stage[i].qkv_method == CVT_PROJ_LINEAR_DENSE;
     m->folded = c.precision != CVT_PREC_FP32 && getenv("CVT_NO_FOLD") == nullptr && !variant;
+    m->x3 = c.precision == CVT_PREC_TF32X3;
+    if (m->x3 && !m->folded) { set_error("cvt_create: CVT_PREC_TF32X3 is implemented for the folded path only (reference network, any head / cls layout)"); delete h; return CVT_ERR_INVALID; }
     if (getenv("CVT_NO_GRAPH")) m->use_graphs = 0;
     int64_t f = 0, zc = 0, pt_extra = 0;
     auto al = [](int64_t v) { return (v + 63) / 64 * 64; };
@@ -428,9 +439,10 @@ int cvt_create(const cvt_config* cfg, cvt_model** out) {
   }
   if (m->folded) {  // multi-GEMM lists that fold the stacked linear maps (forward) and unfold their gradients (backward), see fold.cu
     std::vector<MgDesc> fw, bw; int tf = 0, tb = 0;
-    auto push = [](std::vector<MgDesc>& v, int& tiles, const float* A, int ta, const float* B, int tbb, float* C, int M, int N, int K,
+    const bool round_fold = !m->x3;          // TF32X3 keeps the folded kernels in full fp32: the GEMM kernels split them into high / low parts
+    auto push = [round_fold](std::vector<MgDesc>& v, int& tiles, const float* A, int ta, const float* B, int tbb, float* C, int M, int N, int K,
                    int lda, int ldb, int ldc, int acc, const float* u, const float* vv, int u1) {
-      MgDesc d{A, B, C, M, N, K, lda, ldb, ldc, ta, tbb, 1.f, acc, u, vv, u1, tiles, (M > 1 && !acc) ? 1 : 0};   // folded kernels are MMA operands
+      MgDesc d{A, B, C, M, N, K, lda, ldb, ldc, ta, tbb, 1.f, acc, u, vv, u1, tiles, (M > 1 && !acc && round_fold) ? 1 : 0};   // folded kernels are MMA operands
       tiles += mg_tiles(d); v.push_back(d);
     };
     float* P = m->P; float* G = m->G; float* F = m->Fd;
@@ -613,11 +625,11 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
   if (m->folded) {
     // ConvEmbed as explicit im2col (kept for the weight gradient) + TMA-fed GEMM against the K-major kernel copy — im2col.cu
     const StageFold& f = m->fold[si];
-    const ConvGeom cv{g.hin, g.win, g.cin, g.H, g.W, g.k, g.s, g.pt, g.pl, xin_bstride, xin_boff};
+    const ConvGeom cv{g.hin, g.win, g.cin, g.H, g.W, g.k, g.s, g.pt, g.pl, xin_bstride, xin_boff, m->x3 ? 1 : 0};
     GemmP p; p.M = B * g.T; p.N = D; p.K = f.Kp; p.A = a.col; p.lda = f.Kp; p.B = m->Pt + f.convt; p.ldb = f.Kp; p.b_mode = B_NK;
     p.C = a.x0; p.ldc = D; if (g.has_cls) p.c_map = RowMap{g.T, g.Tc, 1};
     p.bias = P + w.conv_b; p.epi = EPI_BIAS;
-    GemmP ic = p; ic.A = xin; ic.a_mode = A_CONV; ic.cv = cv; ic.K = f.Kc; ic.lda = 0;
+    GemmP ic = p; ic.A = xin; ic.a_mode = A_CONV; ic.cv = cv; ic.K = f.Kc; ic.lda = 0; ic.x3 = m->x3 ? 1 : 0;
     // measured at batch 64: the forward gains (s2 34 -> 25 us, s3 34 -> 28 us) but the weight gradient over 32-token strided boxes is slower than
     // over the patch matrix (s2.bwd_conv 58 -> 71 us), so training keeps im2col (CVT_IMPLICIT_CONV_TRAIN=1 switches both)
     static const bool train_too = getenv("CVT_IMPLICIT_CONV_TRAIN") != nullptr;
@@ -653,7 +665,7 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
     dp.B = B; dp.H = g.H; dp.W = g.W; dp.D = D; dp.Tc = g.Tc; dp.has_cls = g.has_cls;
     dp.stats = (bn && training) ? a.bn_stats : nullptr;
     dp.cls_zero = m->folded && bn;
-    dp.round_out = m->folded;
+    dp.round_out = round_ops(m);
     const bool fast = g.D <= 256 && (g.D & 3) == 0;
     int stat_parts = fast ? kStatParts : 1;
     if (g.method == CVT_PROJ_LINEAR_DENSE) {
@@ -690,9 +702,9 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
     const StageFold& f = m->fold[si]; float* F = m->Fd;
     const bool bn = g.method == CVT_PROJ_DW_BN;
     if (training || !m->skip_prep)
-      CVT_CUDA(launch_bn_fold(F + f.Wc, F + f.bc, bn ? a.bn_scale : nullptr, bn ? a.bn_shift : nullptr, 0.125f, D, F + f.Wft, F + f.bf, s));
+      CVT_CUDA(launch_bn_fold(F + f.Wc, F + f.bc, bn ? a.bn_scale : nullptr, bn ? a.bn_shift : nullptr, 0.125f, D, F + f.Wft, F + f.bf, s, m->x3 ? 0 : 1));
     GemmP p; p.M = R; p.N = D; p.K = D; p.A = a.conv; p.lda = D; p.B = F + f.Wft; p.ldb = D; p.b_mode = B_NK; p.C = a.qkv2; p.ldc = D;
-    p.bias = F + f.bf; p.epi = EPI_BIAS | EPI_ROUND; p.batch = 3;
+    p.bias = F + f.bf; p.epi = EPI_BIAS | EPI_ROUND | EPI_KEEP_ROUND; p.batch = 3;      // Q, K, V: operands of the (single-pass TF32) attention kernels
     p.batch = 3; p.a_bs0 = RD; p.b_bs0 = (long long)D * D; p.c_bs0 = RD; p.bias_bs = D;
     CVT_CUDA(run_gemm(m, p, s));
     if (bn && g.has_cls) CVT_CUDA(launch_cls_fix(a.xn, RD, F + f.Wc, F + f.bc, 0.125f, B, g.Tc, D, a.qkv2, s));   // cls rows skip BatchNorm
@@ -749,7 +761,7 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
       return launch_mlp_fused(m, si, R, 1, s);
   }
   // y = norm1(x)  :278  (same gamma/beta)
-  CVT_CUDA(launch_ln_fwd(a.x1, rowmap_none(), D, P + w.ln_g, P + w.ln_b, c.ln_eps, a.y, D, a.lnb_mean, a.lnb_rstd, R, D, s, m->folded));
+  CVT_CUDA(launch_ln_fwd(a.x1, rowmap_none(), D, P + w.ln_g, P + w.ln_b, c.ln_eps, a.y, D, a.lnb_mean, a.lnb_rstd, R, D, s, round_ops(m)));
   {  // Mlp :253-258
     GemmP p = dense_fwd(a.y, D, R, D, P + w.f1w, H4, P + w.f1b, a.hact, H4);
     p.epi |= EPI_GELU; p.aux = a.hpre;
@@ -826,7 +838,7 @@ static cudaError_t forward_impl(Model* m, const float* img, const float* proc, i
   m->mlp_fused_last = false;
   const bool prep = training || !m->skip_prep;           // predict loop: weight-only work was done by the first chunk of the call
   if (c.precision != CVT_PREC_FP32 && prep) {
-    CVT_CUDA(launch_transpose_weights(m->P, m->Pt, m->Pr, m->tr_descs_dev, (int)m->tr_descs.size(), m->tr_tiles, s));
+    CVT_CUDA(launch_transpose_weights(m->P, m->Pt, m->Pr, m->tr_descs_dev, (int)m->tr_descs.size(), m->tr_tiles, s, m->x3 ? 0 : 1));
     m->pt_valid = true;
     if (m->folded) CVT_CUDA(launch_multigemm(m->mg_fwd_dev, m->mg_fwd_n, m->mg_fwd_tiles, s));
   }
@@ -887,7 +899,7 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
   prof_mark(s, kStageNames[si][6]);
   // ---- Mlp ----
   const float* dM = dX2;
-  if (drop) { if (!m->premasked) CVT_CUDA(launch_mask_scale(m->gM, dX2, a.mask2, keep_scale, RD, s, m->folded)); dM = m->gM; }
+  if (drop) { if (!m->premasked) CVT_CUDA(launch_mask_scale(m->gM, dX2, a.mask2, keep_scale, RD, s, round_ops(m))); dM = m->gM; }
   m->premasked = false;
   CVT_CUDA(wgrad_bias(m, a.hact, H4, H4, dM, D, D, R, G + w.f2w, G + w.f2b, 1, 0, 0, s));
   {
@@ -903,7 +915,7 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
   // second use of norm1 (:278): dX1 = dX2 + LN'(dY)
   // ... and, in the same pass, the gradient through the dropout of the attention output projection (:189): gM = gD * mask_proj / keep
   CVT_CUDA(launch_ln_bwd(m->gC, D, a.x1, rowmap_none(), D, a.lnb_mean, a.lnb_rstd, P + w.ln_g, dX2, m->gD, rowmap_none(), D,
-                         G + w.ln_g, G + w.ln_b, R, D, s, drop ? a.mask_proj : nullptr, keep_scale, m->gM, m->folded ? 1 : 0));
+                         G + w.ln_g, G + w.ln_b, R, D, s, drop ? a.mask_proj : nullptr, keep_scale, m->gM, round_ops(m) ? 1 : 0));
   prof_mark(s, kStageNames[si][7]);
   if (m->folded) {
     // ---- folded path (fold.cu): one wgrad + one dgrad per stacked pair; individual gradients are unfolded at the end of backward ----
@@ -911,7 +923,7 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
     const float* dA2 = m->gD;
     if (drop) dA2 = m->gM;
     CVT_CUDA(wgrad_bias(m, a.attn_o, D, D, dA2, D, D, R, G + f.Zo, G + w.prb, 1, 0, 0, s));        // Zo = o^T dA2, so = colsum dA2 = dbproj
-    { GemmP q = dense_dgrad(dA2, D, R, D, F + f.Wo, D, m->gE, D); q.epi |= EPI_ROUND; CVT_CUDA(run_gemm(m, q, s)); }   // dO = dA2 Wo^T (TMA operand of attention backward)
+    { GemmP q = dense_dgrad(dA2, D, R, D, F + f.Wo, D, m->gE, D); q.epi |= EPI_ROUND | EPI_KEEP_ROUND; CVT_CUDA(run_gemm(m, q, s)); }   // dO = dA2 Wo^T (TMA operand of attention backward)
     prof_mark(s, kStageNames[si][8]);
     CVT_CUDA(attention_backward(m, si, B, m->gE, m->gQ, s));                                        // gQ = [dQ(pre-scale), dK, dV]
     prof_mark(s, kStageNames[si][9]);
@@ -1037,7 +1049,7 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
     const float* dY = m->gD;                       // gradient w.r.t. the embed output, spatial rows only
     if (g.has_cls) { CVT_CUDA(launch_copy_rows(m->gC, rowmap_none(), D, m->gD, RowMap{g.T, g.Tc, 1}, D, B * g.T, D, s)); dY = m->gC; }
     WgradP wg; wg.X = a.col; wg.ldx = f.Kp; wg.Kin = f.Kc; wg.dY = dY; wg.lddy = D; wg.N = D; wg.tokens = B * g.T;
-    wg.dW = G + w.conv_w; wg.dw_bs = 0; wg.db = G + w.conv_b; wg.db_bs = 0;
+    wg.dW = G + w.conv_w; wg.dw_bs = 0; wg.db = G + w.conv_b; wg.db_bs = 0; wg.x3 = m->x3 ? 1 : 0;
     {
       WgradP ic = wg; ic.X = xin; ic.conv = 1; ic.cv = ConvGeom{g.hin, g.win, g.cin, g.H, g.W, g.k, g.s, g.pt, g.pl, xin_bstride, xin_boff};
       if (a.conv_implicit) wg = ic;      // the patches are read from the activation itself (the forward wrote no patch matrix)
@@ -1052,7 +1064,7 @@ static cudaError_t stage_backward(Model* m, int si, const float* xin, long long 
       CVT_CUDA(run_gemm(m, q, s));
       // the previous block ends in the Mlp dropout (:257): its masked gradient is written in the same pass (no cls rows there: dense offsets)
       const bool pm = drop && !gp.has_cls && xin_boff == 0 && xin_bstride == (long long)gp.Tc * gp.D;
-      CVT_CUDA(launch_col2im(a.col, cv, B, f.Kp, dXprev, s, pm ? m->buf[si - 1].mask2 : nullptr, keep_scale, m->gM, 1));
+      CVT_CUDA(launch_col2im(a.col, cv, B, f.Kp, dXprev, s, pm ? m->buf[si - 1].mask2 : nullptr, keep_scale, m->gM, round_ops(m) ? 1 : 0));
       m->premasked = pm;
     }
     return cudaSuccess;

@@ -14,7 +14,7 @@ namespace {
 // grid (D/32 j-tiles, D/32 i-tiles, 3), block (32, 8)
 __global__ void __launch_bounds__(256) bn_fold_kernel(const float* __restrict__ Wc, const float* __restrict__ bc, const float* __restrict__ sc,
                                                       const float* __restrict__ sh, float alpha0, int D, float* __restrict__ Wft,
-                                                      float* __restrict__ bf) {
+                                                      float* __restrict__ bf, int round) {
   __shared__ float t[32][33];
   __shared__ float red[8][33];
   const int z = blockIdx.z, j0 = blockIdx.x * 32, i0 = blockIdx.y * 32, tx = threadIdx.x, ty = threadIdx.y;
@@ -23,7 +23,8 @@ __global__ void __launch_bounds__(256) bn_fold_kernel(const float* __restrict__ 
   for (int r = ty; r < 32; r += 8) {
     const int i = i0 + r;
     const float s = sc ? sc[z * D + i] : 1.f;
-    t[r][tx] = round_tf32(W[(long long)i * D + j0 + tx] * s * alpha);      // B operand of the folded q/k/v GEMM
+    const float wv = W[(long long)i * D + j0 + tx] * s * alpha;      // B operand of the folded q/k/v GEMM
+    t[r][tx] = round ? round_tf32(wv) : wv;
   }
   __syncthreads();
   for (int r = ty; r < 32; r += 8) Wft[(long long)z * D * D + (long long)(j0 + r) * D + i0 + tx] = t[tx][r];
@@ -175,9 +176,9 @@ __global__ void __launch_bounds__(256) qkv_unfold_kernel(float* __restrict__ Z, 
 }  // namespace
 
 cudaError_t launch_bn_fold(const float* Wc, const float* bc, const float* sc, const float* sh, float alpha0, int D, float* Wft, float* bf,
-                           cudaStream_t s) {
+                           cudaStream_t s, int round) {
   if (D % 32 != 0) { set_error("bn_fold: D must be a multiple of 32"); return cudaErrorInvalidValue; }
-  bn_fold_kernel<<<dim3(D / 32, D / 32, 3), dim3(32, 8), 0, s>>>(Wc, bc, sc, sh, alpha0, D, Wft, bf);
+  bn_fold_kernel<<<dim3(D / 32, D / 32, 3), dim3(32, 8), 0, s>>>(Wc, bc, sc, sh, alpha0, D, Wft, bf, round);
   CVT_LAUNCH_CHECK();
   return cudaSuccess;
 }

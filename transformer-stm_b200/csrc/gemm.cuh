@@ -20,12 +20,13 @@ enum Epi : uint32_t {
   EPI_PHILOX = 4096u,     // with EPI_MASK: the keep-mask is drawn here (Philox4x32-10, same counters as philox_mask_kernel) and stored to mask_gen
   EPI_GELU_DSAVE = 8192u, // tcgen05/TMA kernel only.  With EPI_GELU: aux receives d out / d pre = gelu'(pre) (times the dropout keep factor when
                           // EPI_MASK) instead of pre; with EPI_GELU_BWD: aux holds that derivative, v *= aux (no erf, no mask load)
+  EPI_KEEP_ROUND = 16384u, // orchestration only (never reaches a kernel): EPI_ROUND stays on in CVT_PREC_TF32X3 too, the result feeds the attention kernels
   EPI_BN_BWD = 1024u      // v = A[n] v + E[n] aux[idx] + F[n]  (BatchNorm backward as an affine map of (dn, conv); coef = [A|E|F][N])
 };
 
 // Conv2D(padding='same') geometry.  The input map of image b starts at x + b*bstride + boff (floats), which lets a
 // [B,Tc,D] block output with a leading cls row be read as the next stage's [B,H,W,C] input without a copy.
-struct ConvGeom { int hin, win, cin, ho, wo, k, s, pt, pl; long long bstride; int boff; };
+struct ConvGeom { int hin, win, cin, ho, wo, k, s, pt, pl; long long bstride; int boff; int noround; };      // noround: im2col keeps full fp32 (CVT_PREC_TF32X3)
 
 struct GemmP {
   int M = 0, N = 0, K = 0;
@@ -35,7 +36,7 @@ struct GemmP {
   int a_mode = A_PLAIN; RowMap a_map{0, 0, 0};
   const float* a_scale = nullptr; const float* a_shift = nullptr; long long a_aff_bs = 0;   // per-feature affine (BN on load)
   int a_skip_period = 0;                       // tokens with tok % period == 0 (cls rows) skip the affine
-  ConvGeom cv{0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+  ConvGeom cv{0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
   // B
   const float* B = nullptr; long long ldb = 0, b_bs0 = 0, b_bs1 = 0;
   int b_mode = B_KN; RowMap b_map{0, 0, 0};
@@ -77,7 +78,7 @@ struct WgradP {
   int x3 = 0;                                  // error-compensated product: both operand tiles are split into high and low parts in shared memory
   // conv != 0: X is not a matrix but the im2col view of a Conv2D input (ConvEmbed weight gradient): X(token, feature) =
   // x_pad[b, s*i + kh, s*j + kw, c] with token = (b, i, j), feature = (kh, kw, c); boxes are strided TMA boxes of the NHWC map itself
-  int conv = 0; ConvGeom cv{0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+  int conv = 0; ConvGeom cv{0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
 };
 cudaError_t launch_wgrad_tma(const WgradP& p, cudaStream_t s);
 bool wgrad_tma_supports(const WgradP& p);
@@ -92,7 +93,7 @@ int mg_tiles(const MgDesc& d);
 cudaError_t launch_multigemm(const MgDesc* descs_dev, int ndesc, int total_tiles, cudaStream_t s, int tile_base = 0);
 // dst[off + n*K + k] = src[off + k*N + n] for every registered dense kernel (forward GEMMs read their weights K-major)
 struct TrDesc { long long off; int K, N, tile0; int copy; long long toff; int ldt; };   // transposed copy at dst[toff + n*ldt + k]   // copy: dst2[off + k*N + n] = round(src) (a TF32-rounded straight copy, dgrad operand)
-cudaError_t launch_transpose_weights(const float* src, float* dst, float* dst2, const TrDesc* descs_dev, int ndesc, int total_tiles, cudaStream_t s);
+cudaError_t launch_transpose_weights(const float* src, float* dst, float* dst2, const TrDesc* descs_dev, int ndesc, int total_tiles, cudaStream_t s, int round = 1);
 
 // explicit im2col / col2im for ConvEmbed in TF32 mode (im2col.cu)
 cudaError_t launch_im2col(const float* x, const ConvGeom& g, int M, int K, int ldc, float* col, cudaStream_t s);

@@ -255,7 +255,7 @@ __global__ void __launch_bounds__(TCfg<BN, X3>::THREADS, 1) gemm_tma_kernel(cons
 }
 
 __global__ void __launch_bounds__(256) transpose_weights_kernel(const float* __restrict__ src, float* __restrict__ dst, float* __restrict__ dst2,
-                                                                const TrDesc* __restrict__ descs, int ndesc) {
+                                                                const TrDesc* __restrict__ descs, int ndesc, int round) {
   __shared__ float t[32][33];
   int d = 0;
   while (d + 1 < ndesc && (int)blockIdx.x >= descs[d + 1].tile0) ++d;
@@ -265,7 +265,8 @@ __global__ void __launch_bounds__(256) transpose_weights_kernel(const float* __r
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   for (int i = ty; i < 32; i += 8) {
     const int k = k0 + i, n = n0 + tx;
-    const float v = (k < e.K && n < e.N) ? round_tf32(src[e.off + (long long)k * e.N + n]) : 0.f;       // both copies are tensor-core operands
+    float v = (k < e.K && n < e.N) ? src[e.off + (long long)k * e.N + n] : 0.f;       // both copies are tensor-core operands
+    if (round) v = round_tf32(v);
     t[i][tx] = v;
     if (e.copy && k < e.K && n < e.N) dst2[e.off + (long long)k * e.N + n] = v;
   }
@@ -379,9 +380,9 @@ cudaError_t launch_tma_bn(const GemmP& p, int bn, cudaStream_t s) {
 constexpr uint32_t kTmaEpiKinds = EPI_GELU | EPI_RESID | EPI_GELU_BWD | EPI_PHILOX | EPI_BN_BWD | EPI_GELU_DSAVE;
 }  // namespace
 
-cudaError_t launch_transpose_weights(const float* src, float* dst, float* dst2, const TrDesc* descs_dev, int ndesc, int total_tiles, cudaStream_t s) {
+cudaError_t launch_transpose_weights(const float* src, float* dst, float* dst2, const TrDesc* descs_dev, int ndesc, int total_tiles, cudaStream_t s, int round) {
   if (ndesc < 1 || total_tiles < 1) return cudaSuccess;
-  transpose_weights_kernel<<<total_tiles, 256, 0, s>>>(src, dst, dst2, descs_dev, ndesc);
+  transpose_weights_kernel<<<total_tiles, 256, 0, s>>>(src, dst, dst2, descs_dev, ndesc, round);
   CVT_LAUNCH_CHECK();
   return cudaSuccess;
 }

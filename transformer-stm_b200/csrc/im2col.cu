@@ -24,7 +24,7 @@ __global__ void __launch_bounds__(256) im2col_v4_kernel(const float* __restrict_
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
     if (yy >= 0 && yy < g.hin && xx >= 0 && xx < g.win) {
       v = *reinterpret_cast<const float4*>(x + (long long)b * g.bstride + g.boff + ((long long)yy * g.win + xx) * g.cin + c);
-      v = make_float4(round_tf32(v.x), round_tf32(v.y), round_tf32(v.z), round_tf32(v.w));
+      if (!g.noround) v = make_float4(round_tf32(v.x), round_tf32(v.y), round_tf32(v.z), round_tf32(v.w));
     }
     *reinterpret_cast<float4*>(col + (long long)m * ldc + tap * g.cin + c) = v;
   }
@@ -47,7 +47,7 @@ __global__ void __launch_bounds__(1024) im2col_rows_kernel(const float* __restri
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
     if (yy >= 0 && yy < g.hin && xx >= 0 && xx < g.win) {
       v = __ldg(reinterpret_cast<const float4*>(x + (long long)b * g.bstride + g.boff + ((long long)yy * g.win + xx) * g.cin + c));
-      v = make_float4(round_tf32(v.x), round_tf32(v.y), round_tf32(v.z), round_tf32(v.w));
+      if (!g.noround) v = make_float4(round_tf32(v.x), round_tf32(v.y), round_tf32(v.z), round_tf32(v.w));
     }
     *reinterpret_cast<float4*>(col + (long long)m * ldc + koff) = v;
     if (++oj == g.wo) { oj = 0; if (++oi == g.ho) { oi = 0; ++b; } }
@@ -67,7 +67,7 @@ __global__ void __launch_bounds__(256) im2col_scalar_kernel(const float* __restr
       const int b = m / hw, pix = m - b * hw, oi = pix / g.wo, oj = pix - oi * g.wo;
       const int yy = g.s * oi + kh - g.pt, xx = g.s * oj + kw - g.pl;
       if (yy >= 0 && yy < g.hin && xx >= 0 && xx < g.win)
-        v = round_tf32(x[(long long)b * g.bstride + g.boff + ((long long)yy * g.win + xx) * g.cin + c]);
+        { v = x[(long long)b * g.bstride + g.boff + ((long long)yy * g.win + xx) * g.cin + c]; if (!g.noround) v = round_tf32(v); }
     }
     col[idx] = v;
   }
@@ -89,7 +89,7 @@ __global__ void __launch_bounds__(256) im2col_vec_kernel(const float* __restrict
     for (int e = 0; e < 4; ++e) {
       v[e] = 0.f;
       const int yy = g.s * oi + kh - g.pt, xx = g.s * oj + kw - g.pl;
-      if (kk + e < K && yy >= 0 && yy < g.hin && xx >= 0 && xx < g.win) v[e] = round_tf32(__ldg(xb + ((long long)yy * g.win + xx) * g.cin + c));
+      if (kk + e < K && yy >= 0 && yy < g.hin && xx >= 0 && xx < g.win) { v[e] = __ldg(xb + ((long long)yy * g.win + xx) * g.cin + c); if (!g.noround) v[e] = round_tf32(v[e]); }
       if (++c == g.cin) { c = 0; if (++kw == g.k) { kw = 0; ++kh; } }
     }
     *reinterpret_cast<float4*>(col + idx * 4) = make_float4(v[0], v[1], v[2], v[3]);

@@ -74,7 +74,7 @@ cudaError_t launch_bn_bwd_coef(const float* gamma, const float* mean, const floa
 
 // folded q/k/v path (fold.cu)
 cudaError_t launch_bn_fold(const float* Wc, const float* bc, const float* sc, const float* sh, float alpha0, int D, float* Wft, float* bf,
-                           cudaStream_t s);
+                           cudaStream_t s, int round = 1);
 cudaError_t launch_cls_fix(const float* xn, long long bs, const float* Wc, const float* bc, float alpha0, int B, int Tc, int D, float* q,
                            cudaStream_t s);
 cudaError_t launch_qkv_unfold(float* Z, const float* s_all, const float* xn, const float* dq, long long bs, int B, int T, int Tc, int has_cls,

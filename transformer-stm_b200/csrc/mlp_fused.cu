@@ -360,7 +360,7 @@ cudaError_t launch_cfg(const MlpP& p, const float* w1t, const float* w2t, float*
 bool mlp_fused_supports(const Model* m, int si) {
   static const bool off = getenv("CVT_NO_FUSED_MLP") != nullptr || getenv("CVT_NO_TMA") != nullptr;
   const int D = m->geo[si].D, H4 = m->cfg.mlp_ratio * D;
-  return !off && m->cfg.precision != CVT_PREC_FP32 && m->pt_valid && (D == 64 || D == 128) && H4 % 64 == 0 && H4 <= 1024;
+  return !off && m->cfg.precision != CVT_PREC_FP32 && !m->x3 && m->pt_valid && (D == 64 || D == 128) && H4 % 64 == 0 && H4 <= 1024;
 }
 
 // x2 = x1 + Mlp(norm1(x1)) of stage si for R tokens.  training == 0: nothing is kept.  training != 0 (folded TF32 mode): y, the LayerNorm

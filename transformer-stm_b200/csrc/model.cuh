@@ -62,6 +62,7 @@ struct Model {
   float *P = nullptr, *G = nullptr, *Mo = nullptr, *Vo = nullptr, *St = nullptr;
   // K-major (transposed) copies of the dense kernels the forward GEMMs read, same offsets as P; refreshed at the start of a forward pass
   float* Fd = nullptr; int64_t n_fold = 0, n_z = 0, n_pt_extra = 0; StageFold fold[CVT_MAX_STAGES]; bool folded = false;
+  bool x3 = false;                        // CVT_PREC_TF32X3: dense products error-compensated, nothing is pre-rounded to TF32 except the attention operands
   MgDesc* mg_fwd_dev = nullptr; int mg_fwd_n = 0, mg_fwd_tiles = 0; MgDesc* mg_bwd_dev = nullptr; int mg_bwd_n = 0, mg_bwd_tiles = 0;
   float* Pr = nullptr;                    // TF32-rounded straight copies of the dense kernels the dgrad GEMMs read (same offsets as P)
   float* Pt = nullptr; std::vector<TrDesc> tr_descs; TrDesc* tr_descs_dev = nullptr; int tr_tiles = 0; bool pt_valid = false;
