@@ -143,6 +143,7 @@ def parse():
     ap.add_argument("--sweep", action="store_true", help="configs[3]: inference at batch 1, 2, 4, ..., 4096 per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--no-x3", action="store_true", help="skip the extra tf32x3 (error-compensated mode) measurement of the default cfg2 line")
     ap.add_argument("--no-batch128", action="store_true", help="skip the extra batch-128 measurement of the default cfg2 line")
     ap.add_argument("--no-flush", action="store_true", help="do not flush L2 between timed steps")
     return ap.parse_args()
@@ -482,6 +483,21 @@ def main_b200(a):
             b.close()
             if line is not None:
                 line["batch128"] = dict(extra, note="per-GPU batch 128 (the reference scripts' batch_size), value / ms_per_step timed like the headline")
+        if (a.config == "cfg2" and not a.batch and a.mode == "both" and a.precision == "tf32" and not a.no_x3
+                and int(os.environ.get("WORLD_SIZE", "1")) == 1):
+            # the error-compensated tensor-core mode (CVT_PREC_TF32X3) beside the headline: the mode that MEETS north_star's rtol 1e-3, with its
+            # own first-step parity check and device-timed throughput (same protocol, same batch)
+            import copy
+            a3 = copy.copy(a); a3.precision = "tf32x3"
+            b = Bench(a3, a.config, dbatch)
+            extra = {"parity": b.parity() if not a.no_parity else None}
+            for mode in ("train", "infer"):
+                r = b.timed(mode == "train", a.steps, a.warmup)
+                extra[mode] = {"value": r["value"], "unit": UNIT, "ms_per_step": r["ms_per_step"], "gpu_launches": r["launches"]}
+            b.close()
+            if line is not None:
+                line["tf32x3"] = dict(extra, note="precision tf32x3: every dense product as hi.hi + lo.hi + hi.lo on tcgen05 (operand tiles split in "
+                                                  "shared memory), attention single-pass TF32; `bench.py --precision tf32x3` gives its full line")
         if rank == 0 and line is not None:
             os.write(json_fd, (json.dumps(line) + "\n").encode())
     if int(os.environ.get("WORLD_SIZE", "1")) > 1:
