@@ -7,6 +7,9 @@
 #include <stdlib.h>
 
 #include <algorithm>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
 #include <random>
 #include <thread>
 
@@ -1550,25 +1553,72 @@ static bool host_is_pinned(const void* p) {
   if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { (void)cudaGetLastError(); return false; }
   return a.type == cudaMemoryTypeHost || a.type == cudaMemoryTypeManaged;
 }
-// dst[i] <- src[idx ? idx[first + i] : first + i], rows of row_bytes.  One core copies pageable memory at ~10 GB/s, which is less than a
-// B200 consumes at inference (64 images = 4 or 8 MB every 0.5 ms): copies of a megabyte or more are split over a few threads.
+// A small persistent pool for the host-side gathers (pageable numpy rows -> pinned ring).  One core copies pageable memory at 5-10 GB/s,
+// less than a B200 consumes (64 float64 images = 8.4 MB every 0.5 ms at inference), and spawning threads per batch costs as much as the
+// copy itself: the workers are created once and woken per job.  CVT_COPY_THREADS overrides the count (default: half the cores, at most 8).
+class CopyPool {
+ public:
+  static CopyPool& get() { static CopyPool p; return p; }
+  int threads() const { return nthreads_; }
+  // runs fn(part, nparts) for part = 0 .. nparts-1 (part 0 on the caller's thread); returns when all parts are done
+  void run(int nparts, const std::function<void(int, int)>& fn) {
+    if (nparts <= 1) { fn(0, 1); return; }
+    std::lock_guard<std::mutex> job(job_mu_);            // one job at a time (models on different host threads share the pool)
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      fn_ = &fn; nparts_ = nparts; next_ = 1; pending_ = nparts - 1; ++epoch_;
+    }
+    cv_.notify_all();
+    fn(0, nparts);
+    std::unique_lock<std::mutex> lk(mu_);
+    done_.wait(lk, [&] { return pending_ == 0; });
+    fn_ = nullptr;
+  }
+ private:
+  CopyPool() {
+    const char* e = getenv("CVT_COPY_THREADS");
+    int t = e ? atoi(e) : (int)std::min<unsigned>(8, std::max<unsigned>(1, std::thread::hardware_concurrency() / 2));
+    nthreads_ = std::max(1, std::min(t, 16));
+    for (int i = 1; i < nthreads_; ++i) workers_.emplace_back([this] { loop(); });
+  }
+  ~CopyPool() {
+    { std::lock_guard<std::mutex> lk(mu_); stop_ = true; }
+    cv_.notify_all();
+    for (auto& w : workers_) w.join();
+  }
+  void loop() {
+    uint64_t seen = 0;
+    for (;;) {
+      std::unique_lock<std::mutex> lk(mu_);
+      cv_.wait(lk, [&] { return stop_ || (epoch_ != seen && fn_ && next_ < nparts_); });
+      if (stop_) return;
+      while (fn_ && next_ < nparts_) {
+        const int part = next_++; const int np = nparts_; const auto* fn = fn_;
+        lk.unlock();
+        (*fn)(part, np);
+        lk.lock();
+        if (--pending_ == 0) done_.notify_all();
+      }
+      seen = epoch_;
+    }
+  }
+  std::mutex mu_, job_mu_; std::condition_variable cv_, done_;
+  std::vector<std::thread> workers_;
+  const std::function<void(int, int)>* fn_ = nullptr;
+  int nthreads_ = 1, nparts_ = 0, next_ = 0, pending_ = 0; uint64_t epoch_ = 0; bool stop_ = false;
+};
+
+// dst[i] <- src[idx ? idx[first + i] : first + i], rows of row_bytes; copies of a megabyte or more are split over the pool
 static void host_gather(uint8_t* dst, const uint8_t* src, const int32_t* idx, int64_t first, int64_t cnt, size_t row_bytes) {
   auto work = [=](int64_t lo, int64_t hi) {
     if (!idx) { memcpy(dst + lo * row_bytes, src + (first + lo) * row_bytes, (size_t)(hi - lo) * row_bytes); return; }
     for (int64_t i = lo; i < hi; ++i) memcpy(dst + i * row_bytes, src + (int64_t)idx[first + i] * row_bytes, row_bytes);
   };
-  static const int max_threads = []() {
-    const char* e = getenv("CVT_COPY_THREADS");
-    int t = e ? atoi(e) : (int)std::min<unsigned>(4, std::max<unsigned>(1, std::thread::hardware_concurrency() / 2));
-    return std::max(1, std::min(t, 16));
-  }();
   const size_t bytes = (size_t)cnt * row_bytes;
-  int nt = (int)std::min<int64_t>(std::min<int64_t>(max_threads, cnt), (int64_t)(bytes >> 19));      // >= 512 KB per thread
+  CopyPool& pool = CopyPool::get();
+  const int nt = (int)std::min<int64_t>(std::min<int64_t>(pool.threads(), cnt), (int64_t)(bytes >> 19));      // >= 512 KB per thread
   if (nt <= 1) { work(0, cnt); return; }
-  std::vector<std::thread> th;
-  for (int t = 1; t < nt; ++t) th.emplace_back(work, cnt * t / nt, cnt * (t + 1) / nt);
-  work(0, cnt / nt);
-  for (auto& x : th) x.join();
+  pool.run(nt, [&](int part, int np) { work(cnt * part / np, cnt * (part + 1) / np); });
 }
 static int ring_init(Model* m) {
   if (m->ring_cap) return CVT_OK;
