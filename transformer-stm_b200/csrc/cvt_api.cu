@@ -535,6 +535,7 @@ static float* param_ptr(Model* m, const ParamInfo& p, float* train_arena) { retu
 int cvt_set_param(cvt_model* h, int index, const float* src) {
   if (!h || !src || index < 0 || index >= (int)h->m.params.size()) { set_error("cvt_set_param: bad argument"); return CVT_ERR_INVALID; }
   Model* m = &h->m; const ParamInfo& p = m->params[index];
+  m->infer_prep_valid = false;
   API_CUDA(cudaMemcpyAsync(param_ptr(m, p, m->P), src, p.numel * sizeof(float), cudaMemcpyHostToDevice, m->stream));
   API_CUDA(cudaStreamSynchronize(m->stream));
   return CVT_OK;
@@ -839,6 +840,7 @@ static cudaError_t forward_impl(Model* m, const float* img, const float* proc, i
       CVT_CUDA(launch_philox_mask(m->buf[i].mask_attn, (long long)B * m->geo[i].Tc * m->geo[i].D, c.attn_drop_rate, m->dropout_seed, m->dropout_step,
                                   i * 4 + 3, s, m->dyn));
   m->mlp_fused_last = false;
+  if (training) m->infer_prep_valid = false;            // the BatchNorm moving statistics move, and a weight update usually follows
   const bool prep = training || !m->skip_prep;           // predict loop: weight-only work was done by the first chunk of the call
   if (c.precision != CVT_PREC_FP32 && prep) {
     CVT_CUDA(launch_transpose_weights(m->P, m->Pt, m->Pr, m->tr_descs_dev, (int)m->tr_descs.size(), m->tr_tiles, s, m->x3 ? 0 : 1));
@@ -1299,6 +1301,7 @@ int cvt_grad_arena(cvt_model* h, float** g, int64_t* count) {
 }
 int cvt_param_arena(cvt_model* h, float** p, int64_t* count) {
   if (!h) return CVT_ERR_INVALID;
+  h->m.arena_exposed = true;      // the caller may now write weights directly: inference never trusts cached weight-only products again
   if (p) *p = h->m.P; if (count) *count = h->m.n_train;
   return CVT_OK;
 }
@@ -1309,7 +1312,7 @@ static float adam_alpha(Model* m, float lr) {
   return (float)((double)lr * sqrt(1.0 - pow(b2, t)) / (1.0 - pow(b1, t)));
 }
 static cudaError_t adam_impl(Model* m, float lr, float grad_scale) {
-  m->adam_t += 1;
+  m->adam_t += 1; m->infer_prep_valid = false;
   return launch_adam(m->P, m->G, m->Mo, m->Vo, m->n_train, adam_alpha(m, lr), 0.9f, 0.999f, 1e-7f, grad_scale, m->stream);
 }
 
@@ -1446,7 +1449,7 @@ static int train_step_dp(Model* m, const float* img, const float* proc, const fl
 static int train_step_dev(Model* m, const float* img, const float* proc, const float* y, int B, float lr) {
   const bool philox = m->dropout_mode == CVT_DROPOUT_PHILOX && m->cfg.drop_rate > 0.f;
   const uint32_t step = m->dropout_step;
-  m->adam_t += 1;
+  m->adam_t += 1; m->infer_prep_valid = false;
   const bool dp = m->nccl_comm && m->world > 1;
   const float gs = dp ? 1.f / (float)m->world : 1.f;
   API_CUDA(launch_set_step_params(m->lr_dev, adam_alpha(m, lr), gs, step, m->stream));
@@ -1486,6 +1489,8 @@ static int train_step_dev(Model* m, const float* img, const float* proc, const f
 // kernels, BatchNorm scale / shift) are as the previous forward of this call left them: the predict loop's chunks after the first.
 static int infer_forward(Model* m, const float* img, const float* proc, int B, bool cached) {
   struct Scope { Model* m; ~Scope() { m->skip_prep = false; } } scope{m};
+  // also across calls: repeated inference on unchanged weights (model.predict after model.predict) finds the weight-only work done
+  if (m->infer_prep_valid && !m->arena_exposed && m->pt_valid) cached = true;
   m->skip_prep = cached;
   Model::GraphEntry* g = (m->use_graphs && !g_prof) ? graph_slot(m, cached ? GRAPH_INFER_CACHED : GRAPH_INFER, img, proc, nullptr, B) : nullptr;
   if (g && !g->exec) {
@@ -1510,9 +1515,11 @@ static int infer_forward(Model* m, const float* img, const float* proc, int B, b
     API_CUDA(cudaGraphLaunch(g->exec, m->stream));
     g_launch_count += g->launches;
     m->last_batch = B; m->last_training = 0; m->have_forward = 1;
+    m->infer_prep_valid = true;
     return CVT_OK;
   }
   API_CUDA(forward_impl(m, img, proc, B, 0));
+  m->infer_prep_valid = true;
   return CVT_OK;
 }
 

@@ -128,6 +128,9 @@ struct Model {
   int use_graphs = 1;
   bool premasked = false;                 // backward: gM already holds dX2 * mask2 / keep of the stage about to run (written by col2im)
   bool mlp_fused_last = false;            // the last forward ran the fused inference Mlp: y / hpre / hact were not materialised
+  bool infer_prep_valid = false;          // the weight-only products of an inference forward (K-major / TF32 copies, folded kernels, BN scale / shift,
+                                          // bn_fold) are current: no weight, moving statistic or optimizer step has touched them since they were made
+  bool arena_exposed = false;             // cvt_param_arena handed the weight arena to the caller: weights may change behind the library's back
   bool skip_prep = false;                 // set while a predict-loop chunk after the first is issued: weight-only kernels are skipped
   std::vector<GraphEntry> graphs;
   float* lr_dev = nullptr;
