@@ -626,14 +626,6 @@ static cudaError_t stage_forward(Model* m, int si, const float* xin, long long x
   float* P = m->P;
 
   prof_mark(s, kStageNames[si][0]);
-  static const bool no_direct = getenv("CVT_NO_DIRECT_CONV") != nullptr;
-  const ConvGeom cv0{g.hin, g.win, g.cin, g.H, g.W, g.k, g.s, g.pt, g.pl, xin_bstride, xin_boff};
-  if (!training && !no_direct && conv1_direct_supports(cv0, D)) {
-    // inference, 1-channel 7x7 stride-4 ConvEmbed of the reference spec: direct fp32 convolution, no patch matrix, no GEMM (conv1_direct.cu)
-    a.conv_implicit = true;
-    CVT_CUDA(launch_conv1_direct(xin, cv0, P + w.conv_w, P + w.conv_b, a.x0, (long long)g.Tc * D, g.has_cls, B, s));
-    if (g.has_cls) CVT_CUDA(launch_fill_rows(a.x0, RowMap{1, g.Tc, 0}, D, P + w.cls, B, D, s));
-  } else
   if (m->folded) {
     // ConvEmbed as explicit im2col (kept for the weight gradient) + TMA-fed GEMM against the K-major kernel copy — im2col.cu
     const StageFold& f = m->fold[si];

@@ -81,12 +81,6 @@ cudaError_t launch_qkv_unfold(float* Z, const float* s_all, const float* xn, con
                               int D, const float* Wc, const float* sc, const float* sh, const float* gamma, const float* mu, const float* rstd,
                               int training, float* dgamma, float* dbeta, float* coef, float* scratch /* [3][D][D] + [3][D] */, cudaStream_t s);
 
-// stage-1 ConvEmbed (C_in = 1, 7x7 stride 4, 64 channels) as a direct fp32 convolution, inference (conv1_direct.cu)
-struct ConvGeom;
-bool conv1_direct_supports(const ConvGeom& g, int D);
-cudaError_t launch_conv1_direct(const float* x, const ConvGeom& g, const float* w, const float* bias, float* out, long long out_img_stride,
-                                int out_row_off, int B, cudaStream_t s);
-
 // softmax over the last axis, in place (fp32 attention path) and its backward dS = P*(dP - sum(dP*P)), in place on dP
 cudaError_t launch_softmax_rows(float* S, long long rows, int cols, cudaStream_t s);
 cudaError_t launch_softmax_bwd_rows(float* dP, const float* P, long long rows, int cols, cudaStream_t s);
