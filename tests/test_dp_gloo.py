@@ -82,3 +82,50 @@ def test_world2_gloo_broadcast_and_gradient_mean(tmp_path):
             gg = O.loss_and_grads(eng.spec, eng.params, img, proc, y, None)["grads"]
             for k in gg:
                 np.testing.assert_allclose(a["red"][k], gg[k], rtol=1e-9, atol=1e-11, err_msg=k)
+
+
+class _PeerStub:
+    """Records the peer-memory calls dp.open_peer_memory makes; rank `fail_rank` cannot map its peers."""
+
+    def __init__(self, rank, fail_rank):
+        self.rank, self.fail_rank, self.opened, self.closed, self.handles = rank, fail_rank, False, False, None
+
+    def comm_peer_export(self):
+        return bytes([self.rank + 1]) * 64
+
+    def comm_peer_open(self, handles, sync_grads=False):
+        self.handles = handles
+        if self.rank == self.fail_rank:
+            raise RuntimeError("cudaIpcOpenMemHandle: peer access is not supported between these two devices")
+        self.opened = True
+
+    def comm_peer_close(self):
+        self.opened, self.closed = False, True
+
+
+def _peer_worker(rank, world, port, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from transformer_stm_b200 import dp
+        res = {}
+        for name, fail in (("all_ok", -1), ("rank1_fails", 1)):
+            eng = _PeerStub(rank, fail)
+            ok = dp.open_peer_memory(eng, dist, rank, world)
+            res[name] = dict(ok=ok, opened=eng.opened, closed=eng.closed, handles=eng.handles)
+        np.save(os.path.join(out_dir, "peer%d.npy" % rank), res, allow_pickle=True)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_world2_gloo_peer_memory_handshake_is_collective(tmp_path):
+    """dp.open_peer_memory: the cudaIpc handles are all-gathered in rank order, and when ONE rank cannot map its peers EVERY rank lets go
+    again and stays on the NCCL path (a mixed job would deadlock: the peer-memory kernel waits for flags the NCCL ranks never write)."""
+    world, port = 2, _free_port()
+    mp.spawn(_peer_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+    r = [np.load(tmp_path / ("peer%d.npy" % i), allow_pickle=True).item() for i in range(world)]
+    want = bytes([1]) * 64 + bytes([2]) * 64
+    for i in range(world):
+        assert r[i]["all_ok"]["ok"] is True and r[i]["all_ok"]["opened"] and not r[i]["all_ok"]["closed"]
+        assert r[i]["all_ok"]["handles"] == want
+        assert r[i]["rank1_fails"]["ok"] is False and not r[i]["rank1_fails"]["opened"] and r[i]["rank1_fails"]["closed"]
