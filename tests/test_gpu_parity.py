@@ -407,3 +407,29 @@ def test_tf32x3_error_compensated_mode(hw, batch, cls):
              max(e for _, e in report), (num / den) ** 0.5))
     assert (num / den) ** 0.5 <= 5e-4
     eng.close()
+
+
+def test_training_trajectories_of_the_three_precision_modes_agree():
+    """120 Adam steps (Philox dropout, same stream in every mode) on a small synthetic regression problem in fp32, TF32 and TF32X3: the TF32
+    mode's looser per-step parity does not change what is learned - the loss curves stay together and all of them fall."""
+    hw, B, steps = (32, 32), 32, 120
+    curves = {}
+    for prec in ("fp32", "tf32", "tf32x3"):
+        spec, eng, params, img, proc, y = make_pair(hw=hw, batch=B, precision=prec, drop_rate=0.1)
+        y = (0.5 * proc[:, :1] + img.reshape(B, -1).mean(axis=1, keepdims=True)).astype(np.float32)      # a learnable target of order 1
+        eng.set_dropout("philox", seed=11)
+        d = (_dev(img), _dev(proc), _dev(y))
+        torch.cuda.synchronize()
+        losses = []
+        for _ in range(steps):
+            eng.train_step_dev(d[0], d[1], d[2], B, 1e-3)
+            losses.append(eng.read_metrics()[0])
+        curves[prec] = np.asarray(losses, dtype=np.float64)
+        eng.close()
+    ref = curves["fp32"]
+    assert ref[-10:].mean() < 0.5 * ref[:5].mean(), (ref[:5], ref[-10:])                 # it learns
+    for prec in ("tf32", "tf32x3"):
+        c = curves[prec]
+        assert abs(c[:20] - ref[:20]).max() <= 2e-2 * ref[:20].max(), (prec, c[:20], ref[:20])      # same early trajectory
+        assert abs(c[-10:].mean() - ref[-10:].mean()) <= 0.25 * ref[-10:].mean() + 1e-3, (prec, c[-10:].mean(), ref[-10:].mean())
+    print("\n[trajectories] first / last-10-mean loss: " + ", ".join("%s %.4f / %.4f" % (k, v[0], v[-10:].mean()) for k, v in curves.items()))
