@@ -218,6 +218,31 @@ def test_epoch_loop_equals_step_by_step(precision):
     e1.close(); e2.close()
 
 
+def test_widened_config_tf32x3():
+    """The widened geometry (340x345 input, dims 64/192/384, heads 1/3/6: 7395 / 1892 / 485 tokens, N tiles of 64, ragged against every tile size) in
+    the error-compensated mode: predictions 5e-4, every gradient tensor 1e-2 (TF32: 5e-2 with one tensor at 0.25), all gradients 1e-3 in L2."""
+    dims, heads, hw = (64, 192, 384), (1, 3, 6), (340, 345)
+    spec, eng, params, img, proc, y = make_pair("dw_bn", True, 5, 1, hw, dims=dims, heads=heads, batch=2, precision="tf32x3", drop_rate=0.0)
+    pred = eng.predict(img, proc)
+    ref, _ = O.forward(spec, params, img, proc, dtype=torch.float32)
+    assert rel_err(pred, ref) <= 5e-4, (pred, ref)
+    eng.set_dropout("off")
+    eng.gemm_dispatch_counts(reset=True)
+    loss, mae = eng.train_step(img, proc, y, 1e-3)
+    tma, tc, simt = eng.gemm_dispatch_counts(reset=True)
+    assert tc == 0, (tma, tc, simt)
+    r = O.loss_and_grads(spec, params, img, proc, y, None, dtype=torch.float32)
+    assert abs(loss - r["loss"]) <= 2e-4 * abs(r["loss"]), (loss, r["loss"])
+    bad, report = compare_grads(eng, r["grads"], tol=1e-2)
+    got = eng.get_grads()
+    num = sum(float(((got[k].astype(np.float64) - g) ** 2).sum()) for k, g in r["grads"].items())
+    den = sum(float((g.astype(np.float64) ** 2).sum()) for g in r["grads"].values())
+    print("\n[wide tf32x3] pred %.2e, worst gradient tensor %.2e, L2 %.2e, ffma products %d" % (rel_err(pred, ref), max(e for _, e in report), (num / den) ** 0.5, simt))
+    assert not bad, "widened-config tf32x3 gradient mismatches:\n" + fmt(report)
+    assert (num / den) ** 0.5 <= 1e-3
+    eng.close()
+
+
 @pytest.mark.parametrize("precision", ["fp32", "tf32"])
 def test_widened_config_inference_and_train_step(precision):
     """BASELINE.json configs[4]: 3 stages with embed dims 64/192/384 (heads 1/3/6) on a 340x345 input, i.e. 7395 / 1892 / 485(+cls)
