@@ -604,7 +604,10 @@ cudaError_t run_fwd(const AttnP& p, int B, cudaStream_t s) {
   CVT_LAUNCH_CHECK();
   return cudaSuccess;
 }
-cudaError_t run_bwd(const AttnP& p, float* Dd, int B, cudaStream_t s) {
+// side / ev_fork / ev_join (nullable): the dQ kernel runs on `side` next to the dK/dV kernel.  Both are grids of one ~170 KB CTA per SM, 512 of them on
+// 148 SMs at the benched size: 3.46 waves each, i.e. two partial last waves when serialised; side by side the second kernel's CTAs take the SMs the
+// first one's last wave leaves idle (6.9 waves in 7 slots instead of 8).  The kernels share only read-only inputs.
+cudaError_t run_bwd(const AttnP& p, float* Dd, int B, cudaStream_t s, cudaStream_t side = nullptr, cudaEvent_t ev_fork = nullptr, cudaEvent_t ev_join = nullptr) {
   CVT_CUDA(configure_once());
   const long long groups = (long long)B * p.Tc * p.heads;
   attn_dd_kernel<<<(unsigned)cdivl(groups * 16, 256), 256, 0, s>>>(p.dO, p.O, Dd, B, p.Tc, p.D, p.heads);
@@ -616,10 +619,14 @@ cudaError_t run_bwd(const AttnP& p, float* Dd, int B, cudaStream_t s) {
       !tmap_mnmajor(&domn, p.dO, p, B) || !tmap_mnmajor(&kmn, p.K, p, B))
     return cudaErrorInvalidValue;
   const dim3 grid(cdiv(p.Tc, 128), B * p.heads);
+  static const bool serial = getenv("CVT_ATTN_BWD_SERIAL") != nullptr;
+  const bool fork = side && ev_fork && ev_join && !serial;
+  if (fork) { CVT_CUDA(cudaEventRecord(ev_fork, s)); CVT_CUDA(cudaStreamWaitEvent(side, ev_fork, 0)); }
   attn_bwd_dkv_kernel<<<grid, BWD_THREADS, BK_SMEM, s>>>(p, k128, v128, q64, do64, qmn, domn);
   CVT_LAUNCH_CHECK();
-  attn_bwd_dq_kernel<<<grid, BWD_THREADS, BQ_SMEM, s>>>(p, q128, do128, k64, v64, kmn);
+  attn_bwd_dq_kernel<<<grid, BWD_THREADS, BQ_SMEM, fork ? side : s>>>(p, q128, do128, k64, v64, kmn);
   CVT_LAUNCH_CHECK();
+  if (fork) { CVT_CUDA(cudaEventRecord(ev_join, side)); CVT_CUDA(cudaStreamWaitEvent(s, ev_join, 0)); }
   return cudaSuccess;
 }
 }  // namespace
@@ -642,7 +649,7 @@ cudaError_t attention_backward_tc(Model* m, int si, int B, const float* dO, floa
   p.Q = a.qkv2; p.K = a.qkv2 + RD; p.V = a.qkv2 + 2 * RD; p.O = a.attn_o; p.LSE = a.lse;
   p.dO = dO; p.Dd = m->attn_dd; p.dQ = dQKV; p.dK = dQKV + RD; p.dV = dQKV + 2 * RD;
   p.Tc = g.Tc; p.D = g.D; p.heads = g.heads; p.dq_scale = 0.125f; p.round_out = m->folded && !m->x3;      // (TF32X3: O / dQ / dK / dV feed error-compensated GEMMs, keep them in full fp32)
-  return run_bwd(p, m->attn_dd, B, s);
+  return run_bwd(p, m->attn_dd, B, s, m->side_stream, m->ev_fork, m->ev_join);
 }
 
 }  // namespace cvt

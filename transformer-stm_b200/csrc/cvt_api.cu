@@ -480,6 +480,8 @@ int cvt_create(const cvt_config* cfg, cvt_model** out) {
   CREATE_CUDA(cudaMemsetAsync(m->head_ticket, 0, 16, m->stream));
   CREATE_CUDA(cudaMallocHost(&m->pin_metrics, 4 * sizeof(float)));
   CREATE_CUDA(cudaStreamCreateWithFlags(&m->copy_stream, cudaStreamNonBlocking));
+  CREATE_CUDA(cudaStreamCreateWithFlags(&m->side_stream, cudaStreamNonBlocking));
+  CREATE_CUDA(cudaEventCreateWithFlags(&m->ev_fork, cudaEventDisableTiming)); CREATE_CUDA(cudaEventCreateWithFlags(&m->ev_join, cudaEventDisableTiming));
   for (int i = 0; i < 2; ++i) { CREATE_CUDA(cudaEventCreateWithFlags(&m->ev_copy[i], cudaEventDisableTiming)); CREATE_CUDA(cudaEventCreateWithFlags(&m->ev_done[i], cudaEventDisableTiming)); }
   CREATE_CUDA(cudaStreamSynchronize(m->stream));
   *out = h;
@@ -503,6 +505,9 @@ void cvt_destroy(cvt_model* h) {
   if (m->pp_lut) cudaFree(m->pp_lut);
   if (m->stream) cudaStreamDestroy(m->stream);
   if (m->copy_stream) cudaStreamDestroy(m->copy_stream);
+  if (m->side_stream) { cudaStreamSynchronize(m->side_stream); cudaStreamDestroy(m->side_stream); }
+  if (m->ev_fork) cudaEventDestroy(m->ev_fork);
+  if (m->ev_join) cudaEventDestroy(m->ev_join);
   if (m->workspace) cudaFree(m->workspace);
   if (m->pin_metrics) cudaFreeHost(m->pin_metrics);
   if (m->pin_series) cudaFreeHost(m->pin_series);

@@ -102,6 +102,9 @@ struct Model {
   int64_t workspace_bytes = 0;
 
   cudaStream_t stream = nullptr;
+  // independent kernels of one step may run side by side (attention backward: the dQ kernel fills the SMs the dK/dV kernel's last, partial wave
+  // leaves idle); forked and joined with events, also under graph capture
+  cudaStream_t side_stream = nullptr; cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   int last_batch = 0, last_training = 0, have_forward = 0;
   const float *last_img = nullptr, *last_proc = nullptr;   // device inputs of the last forward (read again by the backward pass)
   int dropout_mode = CVT_DROPOUT_OFF;
