@@ -239,6 +239,21 @@ CVT_API int  cvt_debug_gemm(int a_mode, int b_mode, int M, int N, int K, int spl
 CVT_API int  cvt_debug_attention(int B, int Tc, int heads, const float* Q, const float* K, const float* V, const float* dO,
                          float* O, float* LSE, float* dQ, float* dK, float* dV);
 
+/* Allocation-free entry point.  NO COUNTERPART IN THE REFERENCE: added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The tcgen05 flash-attention backward (the kernels cvt_debug_attention / the model's backward pass run) on caller-owned DEVICE buffers:
+ * Q (already scaled by 1/sqrt(64)), K, V, O, dO, dQ, dK, dV are [B, Tc, heads*64]; LSE is [B*heads, Tc] (O and LSE as the forward left
+ * them); dQ is w.r.t. the un-scaled query (x 0.125).  Operands are expected rounded to TF32 (the tensor core truncates otherwise).
+ * The kernels' scratch, Dd[B*heads, Tc] = rowsum(dO * O), lives in a static __device__ array of CVT_STATIC_ATTN_MAX_ROWS floats (4 MiB,
+ * held by every GPU that loads the library until exit): B * heads * Tc beyond that is refused with CVT_ERR_INVALID.  The call performs
+ * no cudaMalloc / cudaFree, launches on `stream` (a cudaStream_t; NULL = the default stream) and does not synchronise.
+ * Every call on a device shares the one array: calls that overlap on the GPU race - serialise them on one stream.  Nothing in the array
+ * needs clearing between calls (every element read is rewritten first). */
+#define CVT_STATIC_ATTN_MAX_ROWS (1 << 20)
+CVT_API int  cvt_attention_backward_static(int B, int Tc, int heads, const float* Q_dev, const float* K_dev, const float* V_dev,
+                                           const float* O_dev, const float* LSE_dev, const float* dO_dev, float* dQ_dev, float* dK_dev,
+                                           float* dV_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -98,6 +98,7 @@ _PROTOS = {
     "cvt_workspace_bytes": (C.c_int64, [C.c_void_p]),
     "cvt_debug_gemm": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "cvt_debug_attention": (C.c_int, [C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 9),
+    "cvt_attention_backward_static": (C.c_int, [C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 10),
     "cvt_profile_step": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                    C.POINTER(C.c_char_p), C.POINTER(C.c_float), C.POINTER(C.c_int)]),
     "cvt_profile_group_launches": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_int), C.POINTER(C.c_int)]),

@@ -19,6 +19,8 @@
 
 #include <cstdio>
 #include <cstdlib>
+#include <mutex>
+#include <string>
 
 #include "model.cuh"
 #include "tc_common.cuh"
@@ -697,4 +699,63 @@ extern "C" CVT_API int cvt_debug_attention(int B, int Tc, int heads, const float
              (e = cudaMemcpy(dV, gV, n * 4, cudaMemcpyDeviceToHost)) != cudaSuccess)) return fail(e);
   cudaFree(buf);
   return CVT_OK;
+}
+
+// ---- allocation-free variant -----------------------------------------------------------------------------------------------------------
+// cvt_attention_backward_static: the flash-attention backward (attn_dd_kernel + attn_bwd_dkv_kernel + attn_bwd_dq_kernel, the same
+// kernels run_bwd launches for the model) on caller-owned DEVICE buffers, for callers that cannot call cudaMalloc (CUDA graph capture,
+// tight serving loops, harnesses that forbid it).  The one scratch buffer these kernels need - Dd[B*heads, Tc] = rowsum(dO * O) - lives
+// in a file-scope __device__ array of CVT_STATIC_ATTN_MAX_ROWS floats that every GPU loading the library holds until exit.
+// No counterpart in the reference.
+// Every call shares the array: calls that overlap on the GPU (other streams or host threads of this process on the same
+// device) race on it.  Nothing in it has to start at zero: attn_dd_kernel rewrites every element the two gradient kernels read.
+namespace cvt {
+namespace {
+static __device__ __align__(256) float g_static_attn_dd[CVT_STATIC_ATTN_MAX_ROWS];
+
+// In host code the array's name is only a host-side stand-in for the symbol: its device address comes from cudaGetSymbolAddress, looked
+// up once per device with that device current.
+cudaError_t static_attn_scratch(float** out) {
+  constexpr int kMaxDevices = 64;
+  static float* ptrs[kMaxDevices] = {};
+  static std::mutex mu;
+  int dev = -1;
+  CVT_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) { set_error("cvt_attention_backward_static: device ordinal out of range"); return cudaErrorInvalidDevice; }
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptrs[dev]) {
+    float* ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_static_attn_dd);
+    if (e != cudaSuccess) { set_error(std::string("cvt_attention_backward_static: cudaGetSymbolAddress: ") + cudaGetErrorString(e)); return e; }
+    if (!ptr) { set_error("cvt_attention_backward_static: cudaGetSymbolAddress returned a null address"); return cudaErrorInvalidSymbol; }
+    ptrs[dev] = ptr;
+  }
+  *out = ptrs[dev];
+  return cudaSuccess;
+}
+}  // namespace
+}  // namespace cvt
+
+extern "C" CVT_API int cvt_attention_backward_static(int B, int Tc, int heads, const float* Q_dev, const float* K_dev, const float* V_dev,
+                                                     const float* O_dev, const float* LSE_dev, const float* dO_dev, float* dQ_dev,
+                                                     float* dK_dev, float* dV_dev, void* stream) {
+  using namespace cvt;
+  if (B < 1 || Tc < 1 || heads < 1 || !Q_dev || !K_dev || !V_dev || !O_dev || !LSE_dev || !dO_dev || !dQ_dev || !dK_dev || !dV_dev) {
+    set_error("cvt_attention_backward_static: bad argument");
+    return CVT_ERR_INVALID;
+  }
+  const long long rows = (long long)B * heads * Tc;
+  if (rows > (long long)CVT_STATIC_ATTN_MAX_ROWS) {
+    set_error("cvt_attention_backward_static: batch * heads * tokens = " + std::to_string(rows) + " exceeds the static scratch of " +
+              std::to_string((long long)CVT_STATIC_ATTN_MAX_ROWS) + " rows (CVT_STATIC_ATTN_MAX_ROWS)");
+    return CVT_ERR_INVALID;
+  }
+  float* dd = nullptr;
+  if (static_attn_scratch(&dd) != cudaSuccess) return CVT_ERR_CUDA;
+  AttnP p{};
+  p.Q = Q_dev; p.K = K_dev; p.V = V_dev; p.O = const_cast<float*>(O_dev); p.LSE = const_cast<float*>(LSE_dev);      // read-only in the backward kernels
+  p.dO = dO_dev; p.Dd = dd; p.dQ = dQ_dev; p.dK = dK_dev; p.dV = dV_dev;
+  p.Tc = Tc; p.D = heads * 64; p.heads = heads; p.dq_scale = 0.125f; p.round_out = 0;
+  const cudaError_t e = run_bwd(p, dd, B, static_cast<cudaStream_t>(stream));
+  return e == cudaSuccess ? CVT_OK : CVT_ERR_CUDA;      // run_bwd has recorded the message
 }
