@@ -123,6 +123,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 2) attn_fwd_kernel(const __grid_c
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait(); pdl_trigger();      // everything above touches no global memory
   const uint32_t tmem = *tmem_slot;                      // columns: S0 [0,64), S1 [64,128), O [128,192)
 
   if (warp == 0) {
@@ -262,6 +263,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 2) attn_fwd_kernel(const __grid_c
 // Dd[bh, t] = sum_d dO[b,t,h,d] * O[b,t,h,d]   (half a warp per (token, head))
 __global__ void __launch_bounds__(256) attn_dd_kernel(const float* __restrict__ dO, const float* __restrict__ O, float* __restrict__ Dd,
                                                       int B, int Tc, int D, int heads) {
+  pdl_wait(); pdl_trigger();
   const long long gid = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 4;     // (b, t, h)
   const int l16 = threadIdx.x & 15;
   const long long total = (long long)B * Tc * heads;
@@ -311,6 +313,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dq_kernel(const __gri
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait(); pdl_trigger();      // everything above touches no global memory
   const uint32_t tmem = *tmem_slot;                      // columns: S0 0, S1 64, dP0 128, dP1 192, dQ 256
 
   if (warp == 0) {
@@ -448,6 +451,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dkv_kernel(const __gr
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait(); pdl_trigger();      // everything above touches no global memory
   const uint32_t tmem = *tmem_slot;                      // columns: S^T0 0, S^T1 64, dP^T0 128, dP^T1 192, dV 256, dK 320
 
   if (warp == 0) {
@@ -576,6 +580,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dkv_kernel(const __gr
 }
 
 __global__ void __launch_bounds__(256) round_tf32_inplace_kernel(float* x, long long n) {
+  pdl_wait(); pdl_trigger();
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) x[i] = to_tf32(x[i]);
 }
 
@@ -602,8 +607,7 @@ cudaError_t run_fwd(const AttnP& p, int B, cudaStream_t s) {
   if (p.D % 4 != 0 || p.D != p.heads * HD) { set_error("attention_tc: D must equal heads * 64"); return cudaErrorInvalidValue; }
   CUtensorMap tmQ, tmK, tmV;
   if (!tmap_kmajor(&tmQ, p.Q, p, B, 128) || !tmap_kmajor(&tmK, p.K, p, B, 64) || !tmap_mnmajor(&tmV, p.V, p, B)) return cudaErrorInvalidValue;
-  attn_fwd_kernel<<<dim3(cdiv(p.Tc, 128), B * p.heads), FWD_THREADS, FWD_SMEM, s>>>(p, tmQ, tmK, tmV);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((attn_fwd_kernel), dim3(cdiv(p.Tc, 128), B * p.heads), FWD_THREADS, FWD_SMEM, s, p, tmQ, tmK, tmV);
   return cudaSuccess;
 }
 // side / ev_fork / ev_join (nullable): the dQ kernel runs on `side` next to the dK/dV kernel.  Both are grids of one ~170 KB CTA per SM, 512 of them on
@@ -612,8 +616,7 @@ cudaError_t run_fwd(const AttnP& p, int B, cudaStream_t s) {
 cudaError_t run_bwd(const AttnP& p, float* Dd, int B, cudaStream_t s, cudaStream_t side = nullptr, cudaEvent_t ev_fork = nullptr, cudaEvent_t ev_join = nullptr) {
   CVT_CUDA(configure_once());
   const long long groups = (long long)B * p.Tc * p.heads;
-  attn_dd_kernel<<<(unsigned)cdivl(groups * 16, 256), 256, 0, s>>>(p.dO, p.O, Dd, B, p.Tc, p.D, p.heads);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((attn_dd_kernel), (unsigned)cdivl(groups * 16, 256), 256, 0, s, p.dO, p.O, Dd, B, p.Tc, p.D, p.heads);
   CUtensorMap q128, do128, k128, v128, q64, do64, k64, v64, qmn, domn, kmn;
   if (!tmap_kmajor(&q128, p.Q, p, B, 128) || !tmap_kmajor(&do128, p.dO, p, B, 128) || !tmap_kmajor(&k128, p.K, p, B, 128) ||
       !tmap_kmajor(&v128, p.V, p, B, 128) || !tmap_kmajor(&q64, p.Q, p, B, 64) || !tmap_kmajor(&do64, p.dO, p, B, 64) ||
@@ -624,10 +627,8 @@ cudaError_t run_bwd(const AttnP& p, float* Dd, int B, cudaStream_t s, cudaStream
   static const bool serial = getenv("CVT_ATTN_BWD_SERIAL") != nullptr;
   const bool fork = side && ev_fork && ev_join && !serial;
   if (fork) { CVT_CUDA(cudaEventRecord(ev_fork, s)); CVT_CUDA(cudaStreamWaitEvent(side, ev_fork, 0)); }
-  attn_bwd_dkv_kernel<<<grid, BWD_THREADS, BK_SMEM, s>>>(p, k128, v128, q64, do64, qmn, domn);
-  CVT_LAUNCH_CHECK();
-  attn_bwd_dq_kernel<<<grid, BWD_THREADS, BQ_SMEM, fork ? side : s>>>(p, q128, do128, k64, v64, kmn);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((attn_bwd_dkv_kernel), grid, BWD_THREADS, BK_SMEM, s, p, k128, v128, q64, do64, qmn, domn);
+  CVT_LAUNCH((attn_bwd_dq_kernel), grid, BWD_THREADS, BQ_SMEM, fork ? side : s, p, q128, do128, k64, v64, kmn);
   if (fork) { CVT_CUDA(cudaEventRecord(ev_join, side)); CVT_CUDA(cudaStreamWaitEvent(s, ev_join, 0)); }
   return cudaSuccess;
 }

@@ -30,6 +30,41 @@ extern thread_local long long g_launch_count;      // kernels launched by this t
     }                                                                                       \
   } while (0)
 
+// ---- programmatic dependent launch (PDL) ----
+// The step is ~100 kernels of 5-100 us in one stream / one CUDA graph: without PDL every kernel boundary is a full drain (last CTA exits,
+// memory flush) followed by the next grid's launch and prologue (shared-memory carve-up, mbarrier init, TMEM allocation, tensor-map
+// fetch).  Every step kernel therefore
+//   * is launched through CVT_LAUNCH with cudaLaunchAttributeProgrammaticStreamSerialization (in a captured graph: a programmatic edge),
+//   * does everything that touches no global memory first, then pdl_wait() - returns once EVERY grid it depends on has completed and its
+//     memory is visible, so nothing after it can race with a predecessor - and pdl_trigger(), which lets the NEXT grid's CTAs become
+//     resident (as SMs free up) and run their own prologue while this grid is still computing.
+// A kernel launched without the attribute sees both instructions as no-ops.  CVT_NO_PDL=1 launches everything without the attribute.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+bool pdl_enabled();
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_kernel(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<Args&&>(args)...);
+}
+// launch + count + error check; every kernel launched this way starts with pdl_wait() before its first global-memory access
+#define CVT_LAUNCH(kernel, grid, block, smem, stream, ...)                                                                      \
+  do {                                                                                                                          \
+    ::cvt::g_launch_count++;                                                                                                    \
+    cudaError_t _e = ::cvt::launch_kernel(kernel, dim3(grid), dim3(block), (size_t)(smem), stream, __VA_ARGS__);                \
+    if (_e == cudaSuccess) _e = cudaGetLastError();                                                                             \
+    if (_e != cudaSuccess) {                                                                                                    \
+      ::cvt::set_error(std::string("kernel launch: ") + cudaGetErrorString(_e) + " @" + __FILE__ + ":" + std::to_string(__LINE__)); \
+      return _e;                                                                                                                \
+    }                                                                                                                           \
+  } while (0)
+
 constexpr int kNumSMs = 148;
 
 __host__ __device__ inline int cdiv(int a, int b) { return (a + b - 1) / b; }

@@ -22,6 +22,7 @@ namespace cvt {
 static thread_local std::string g_err;
 thread_local long long g_launch_count = 0;
 void set_error(const std::string& msg) { g_err = msg; }
+bool pdl_enabled() { static const bool on = getenv("CVT_NO_PDL") == nullptr; return on; }
 
 #define API_CUDA(expr)                                   \
   do {                                                   \

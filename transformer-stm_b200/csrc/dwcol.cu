@@ -28,6 +28,7 @@ template <int N> __device__ __forceinline__ void cp_wait() { asm volatile("cp.as
 
 // ---- forward -------------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(CT, 2) dwcol_fwd_kernel(const __grid_constant__ DwProjP p, const ColGeo g) {
+  pdl_wait(); pdl_trigger();
   __shared__ float ring[FR][COLS + 2][32];               // column slot s <-> image column colg * COLS - 1 + s
   __shared__ float sred[NW][6][32];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
@@ -136,6 +137,7 @@ __global__ void __launch_bounds__(CT, 2) dwcol_fwd_kernel(const __grid_constant_
 // ---- backward ------------------------------------------------------------------------------------------------------------------
 // dx[i,j] = sum_z sum_{kh,kw} d_z[i-kh+1, j-kw+1] w_z[kh,kw];   dw_z[kh,kw] += x[i+kh-1, j+kw-1] d_z[i,j]
 __global__ void __launch_bounds__(CT, 2) dwcol_bwd_kernel(const __grid_constant__ DwProjBwdP p, const ColGeo g) {
+  pdl_wait(); pdl_trigger();
   constexpr int RING = BR * (COLS + 2) * 4 * 32, RED = NW * 27 * 32;
   __shared__ float smem[RING > RED ? RING : RED];
   float (*ring)[COLS + 2][4][32] = reinterpret_cast<float (*)[COLS + 2][4][32]>(smem);      // [row slot][column slot][x, d_q, d_k, d_v][channel]
@@ -280,16 +282,14 @@ cudaError_t launch_dwcol_fwd(const DwProjP& p, cudaStream_t s, int* stat_slices)
   ColGeo g; int grid;
   if (p.method[0] != 0 || p.method[1] != 0 || p.method[2] != 0 || !make_colgeo(p.B, p.H, p.W, p.D, p.nparts, &g, &grid)) return cudaErrorNotSupported;
   *stat_slices = grid / g.CG;                            // slices of p.stats written by this launch (<= p.nparts): bn_finalize sums exactly these
-  dwcol_fwd_kernel<<<grid, CT, 0, s>>>(p, g);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((dwcol_fwd_kernel), grid, CT, 0, s, p, g);
   return cudaSuccess;
 }
 
 cudaError_t launch_dwcol_bwd(const DwProjBwdP& p, cudaStream_t s) {
   ColGeo g; int grid;
   if (p.method[0] != 0 || p.method[1] != 0 || p.method[2] != 0 || p.coef || !make_colgeo(p.B, p.H, p.W, p.D, 2 * kNumSMs, &g, &grid)) return cudaErrorNotSupported;
-  dwcol_bwd_kernel<<<grid, CT, 0, s>>>(p, g);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((dwcol_bwd_kernel), grid, CT, 0, s, p, g);
   return cudaSuccess;
 }
 

@@ -20,6 +20,7 @@ __device__ __forceinline__ float inv_count(int i, int j, int H, int W) {
 
 // block = (D/2 channel pairs, CW columns, 3 branches): thread (c2, jl, z) produces branch z of column j for a strip of TH rows
 __global__ void __launch_bounds__(384) dwproj_fwd2_kernel(const __grid_constant__ DwProjP p) {
+  pdl_wait(); pdl_trigger();
   extern __shared__ __align__(16) float sstat[];          // [6][D] block partials of the BN statistics
   const int D = p.D, H = p.H, W = p.W;
   const int c = threadIdx.x * 2, jl = threadIdx.y, z = threadIdx.z;
@@ -88,6 +89,7 @@ __global__ void __launch_bounds__(384) dwproj_fwd2_kernel(const __grid_constant_
 // block = (D/2 channel pairs, CW columns, 6): threadIdx.z = role * 3 + z; role 0 threads compute branch z's contribution to the
 // input gradient, role 1 threads accumulate branch z's depthwise-weight gradient.
 __global__ void __launch_bounds__(768, 1) dwproj_bwd2_kernel(const __grid_constant__ DwProjBwdP p) {
+  pdl_wait(); pdl_trigger();
   extern __shared__ __align__(16) float sdw[];            // [3][9][D] block partials of ddw, then [3][TH][nxy] float2 partial dx per branch
   const int D = p.D, H = p.H, W = p.W;
   const int c = threadIdx.x * 2, jl = threadIdx.y, z = threadIdx.z % 3, role = threadIdx.z / 3;
@@ -214,6 +216,7 @@ __global__ void __launch_bounds__(768, 1) dwproj_bwd2_kernel(const __grid_consta
 
 // dst[i] += sum_k part[k][i];  block = (32 elements, 8 partial lanes)
 __global__ void __launch_bounds__(256) reduce_partials_kernel(const float* __restrict__ part, int nparts, int n, float* __restrict__ dst) {
+  pdl_wait(); pdl_trigger();
   __shared__ float red[8][33];
   const int i = blockIdx.x * 32 + threadIdx.x;
   float a = 0.f;
@@ -234,6 +237,7 @@ __global__ void __launch_bounds__(256) reduce_partials_kernel(const float* __res
 __global__ void bn_bwd_coef_kernel(const float* __restrict__ gamma, const float* __restrict__ mean, const float* __restrict__ rstd,
                                    const float* __restrict__ scale, const float* __restrict__ dgamma, const float* __restrict__ dbeta,
                                    float invN, int training, int D, float* __restrict__ coef) {
+  pdl_wait(); pdl_trigger();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;       // (z, c)
   if (i >= 3 * D) return;
   const int z = i / D, c = i - z * D;
@@ -260,8 +264,7 @@ cudaError_t launch_dwproj_fwd2(const DwProjP& p, cudaStream_t s) {
   const int grid = ntiles < p.nparts ? ntiles : p.nparts;
   if (p.stats && grid < p.nparts) CVT_CUDA(cudaMemsetAsync(p.stats + (size_t)grid * 6 * p.D, 0, (size_t)(p.nparts - grid) * 6 * p.D * sizeof(float), s));
   const size_t smem = p.stats ? (size_t)6 * p.D * sizeof(float) : 0;
-  dwproj_fwd2_kernel<<<grid, blk, smem, s>>>(p);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((dwproj_fwd2_kernel), grid, blk, smem, s, p);
   return cudaSuccess;
 }
 
@@ -274,25 +277,21 @@ cudaError_t launch_dwproj_bwd2(const DwProjBwdP& p, cudaStream_t s) {
   const size_t smem = (size_t)27 * p.D * sizeof(float) + (size_t)3 * TH * blk.x * blk.y * sizeof(float2);
   static bool configured = false;
   if (!configured) { CVT_CUDA(cudaFuncSetAttribute(dwproj_bwd2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024)); configured = true; }
-  dwproj_bwd2_kernel<<<grid, blk, smem, s>>>(p);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((dwproj_bwd2_kernel), grid, blk, smem, s, p);
   if (p.ddw) {
-    reduce_partials_kernel<<<cdiv(27 * p.D, 32), dim3(32, 8), 0, s>>>(p.ddw_part, grid, 27 * p.D, p.ddw);
-    CVT_LAUNCH_CHECK();
+    CVT_LAUNCH((reduce_partials_kernel), cdiv(27 * p.D, 32), dim3(32, 8), 0, s, p.ddw_part, grid, 27 * p.D, p.ddw);
   }
   return cudaSuccess;
 }
 
 cudaError_t launch_reduce_partials(const float* part, int nparts, int n, float* dst, cudaStream_t s) {
-  reduce_partials_kernel<<<cdiv(n, 32), dim3(32, 8), 0, s>>>(part, nparts, n, dst);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((reduce_partials_kernel), cdiv(n, 32), dim3(32, 8), 0, s, part, nparts, n, dst);
   return cudaSuccess;
 }
 
 cudaError_t launch_bn_bwd_coef(const float* gamma, const float* mean, const float* rstd, const float* scale, const float* dgamma,
                                const float* dbeta, long long count, int training, int D, float* coef, cudaStream_t s) {
-  bn_bwd_coef_kernel<<<cdiv(3 * D, 128), 128, 0, s>>>(gamma, mean, rstd, scale, dgamma, dbeta, 1.f / (float)count, training, D, coef);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((bn_bwd_coef_kernel), cdiv(3 * D, 128), 128, 0, s, gamma, mean, rstd, scale, dgamma, dbeta, 1.f / (float)count, training, D, coef);
   return cudaSuccess;
 }
 

@@ -15,6 +15,7 @@ namespace {
 __global__ void __launch_bounds__(256) bn_fold_kernel(const float* __restrict__ Wc, const float* __restrict__ bc, const float* __restrict__ sc,
                                                       const float* __restrict__ sh, float alpha0, int D, float* __restrict__ Wft,
                                                       float* __restrict__ bf, int round) {
+  pdl_wait(); pdl_trigger();
   __shared__ float t[32][33];
   __shared__ float red[8][33];
   const int z = blockIdx.z, j0 = blockIdx.x * 32, i0 = blockIdx.y * 32, tx = threadIdx.x, ty = threadIdx.y;
@@ -60,6 +61,7 @@ __global__ void __launch_bounds__(256) bn_fold_kernel(const float* __restrict__ 
 constexpr int CF_B = 16, CF_U = 16;
 __global__ void __launch_bounds__(256) cls_fix_kernel(const float* __restrict__ xn, long long bs, const float* __restrict__ Wc,
                                                       const float* __restrict__ bc, float alpha0, int B, int Tc, int D, float* __restrict__ q) {
+  pdl_wait(); pdl_trigger();
   extern __shared__ float4 cf_smem[];
   float* sx = reinterpret_cast<float*>(cf_smem);          // [CF_B][D] cls rows; reused as [8][CF_B][32] partial sums
   const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * 32 + tx;
@@ -108,6 +110,7 @@ __global__ void __launch_bounds__(256) cls_fix_kernel(const float* __restrict__ 
 // of the block that reaches the q/k/v GEMM without going through conv + BatchNorm).  grid (D/32 j, D/32 c, 3), block (32, 8)
 __global__ void __launch_bounds__(256) cls_outer_kernel(const float* __restrict__ xn, const float* __restrict__ dq, long long bs, int B, int Tc,
                                                         int D, float* __restrict__ Zcls, float* __restrict__ scls) {
+  pdl_wait(); pdl_trigger();
   __shared__ float sx[32][33], sg[32][33];
   const int z = blockIdx.z, j0 = blockIdx.x * 32, c0 = blockIdx.y * 32, tx = threadIdx.x, ty = threadIdx.y;
   float acc[4] = {0.f, 0.f, 0.f, 0.f}, ssum = 0.f;
@@ -147,6 +150,7 @@ __global__ void __launch_bounds__(256) qkv_unfold_kernel(float* __restrict__ Z, 
                                                          const float* __restrict__ gamma, const float* __restrict__ mu, const float* __restrict__ rstd,
                                                          float invN, int training, float* __restrict__ dgamma, float* __restrict__ dbeta,
                                                          float* __restrict__ coef) {
+  pdl_wait(); pdl_trigger();
   const int z = blockIdx.y, c = blockIdx.x * 8 + (threadIdx.x >> 5), l = threadIdx.x & 31;
   float* Zr = Z + (long long)z * D * D + (long long)c * D;
   const float* Wr = Wc + (long long)z * D * D + (long long)c * D;
@@ -178,8 +182,7 @@ __global__ void __launch_bounds__(256) qkv_unfold_kernel(float* __restrict__ Z, 
 cudaError_t launch_bn_fold(const float* Wc, const float* bc, const float* sc, const float* sh, float alpha0, int D, float* Wft, float* bf,
                            cudaStream_t s, int round) {
   if (D % 32 != 0) { set_error("bn_fold: D must be a multiple of 32"); return cudaErrorInvalidValue; }
-  bn_fold_kernel<<<dim3(D / 32, D / 32, 3), dim3(32, 8), 0, s>>>(Wc, bc, sc, sh, alpha0, D, Wft, bf, round);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((bn_fold_kernel), dim3(D / 32, D / 32, 3), dim3(32, 8), 0, s, Wc, bc, sc, sh, alpha0, D, Wft, bf, round);
   return cudaSuccess;
 }
 
@@ -189,8 +192,7 @@ cudaError_t launch_cls_fix(const float* xn, long long bs, const float* Wc, const
   static bool configured = false;
   if (!configured) { CVT_CUDA(cudaFuncSetAttribute(cls_fix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CF_B * 1024 * 4)); configured = true; }
   const size_t smem = (size_t)CF_B * (D > 256 ? D : 256) * sizeof(float);      // cls rows, later the [8][CF_B][32] partial sums
-  cls_fix_kernel<<<dim3(D / 32, (B + CF_B - 1) / CF_B, 3), dim3(32, 8), smem, s>>>(xn, bs, Wc, bc, alpha0, B, Tc, D, q);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((cls_fix_kernel), dim3(D / 32, (B + CF_B - 1) / CF_B, 3), dim3(32, 8), smem, s, xn, bs, Wc, bc, alpha0, B, Tc, D, q);
   return cudaSuccess;
 }
 
@@ -201,12 +203,10 @@ cudaError_t launch_qkv_unfold(float* Z, const float* s_all, const float* xn, con
   float* Zcls = nullptr; float* scls = nullptr;
   if (has_cls) {
     Zcls = scratch; scls = scratch + (long long)3 * D * D;
-    cls_outer_kernel<<<dim3(D / 32, D / 32, 3), dim3(32, 8), 0, s>>>(xn, dq, bs, B, Tc, D, Zcls, scls);
-    CVT_LAUNCH_CHECK();
+    CVT_LAUNCH((cls_outer_kernel), dim3(D / 32, D / 32, 3), dim3(32, 8), 0, s, xn, dq, bs, B, Tc, D, Zcls, scls);
   }
-  qkv_unfold_kernel<<<dim3(D / 8, 3), 256, 0, s>>>(Z, s_all, Zcls, scls, D, Wc, sc, sh, gamma, mu, rstd,
+  CVT_LAUNCH((qkv_unfold_kernel), dim3(D / 8, 3), 256, 0, s, Z, s_all, Zcls, scls, D, Wc, sc, sh, gamma, mu, rstd,
                                                    1.f / (float)((long long)B * T), training, dgamma, dbeta, coef);
-  CVT_LAUNCH_CHECK();
   return cudaSuccess;
 }
 

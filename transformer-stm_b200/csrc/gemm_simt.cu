@@ -13,6 +13,7 @@ using namespace fetch;
 
 template <int AM, int BMODE>
 __global__ void __launch_bounds__(256) gemm_simt_kernel(const __grid_constant__ GemmP p) {
+  pdl_wait(); pdl_trigger();
   __shared__ __align__(16) float As[2][BK][LDS];
   __shared__ __align__(16) float Bs[2][BK][LDS];
   constexpr bool A_ROWFIXED = (AM == A_PLAIN || AM == A_CONV);
@@ -168,14 +169,14 @@ __global__ void __launch_bounds__(256) gemm_simt_kernel(const __grid_constant__ 
 template <int AM, int BMODE>
 cudaError_t launch_one(const GemmP& p, cudaStream_t s) {
   dim3 grid(cdiv(p.N, BN), cdiv(p.M, BM), p.batch * p.splitk);
-  gemm_simt_kernel<AM, BMODE><<<grid, 256, 0, s>>>(p);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((gemm_simt_kernel<AM, BMODE>), grid, 256, 0, s, p);
   return cudaSuccess;
 }
 
 // ---- column sums -------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) colsum_kernel(const float* __restrict__ X, long long ld, RowMap map, int rows, int N,
                                                      long long x_bs, float* __restrict__ out, long long out_bs, int rows_per_chunk) {
+  pdl_wait(); pdl_trigger();
   __shared__ float red[8][33];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int n = blockIdx.x * 32 + tx;
@@ -224,8 +225,7 @@ cudaError_t launch_colsum(const float* X, long long ld, RowMap map, int rows, in
   const int rows_per_chunk = cdiv(rows, chunks);
   chunks = cdiv(rows, rows_per_chunk);
   dim3 grid(colblocks, chunks, batch);
-  colsum_kernel<<<grid, 256, 0, s>>>(X, ld, map, rows, N, x_bs, out, out_bs, rows_per_chunk);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((colsum_kernel), grid, 256, 0, s, X, ld, map, rows, N, x_bs, out, out_bs, rows_per_chunk);
   return cudaSuccess;
 }
 

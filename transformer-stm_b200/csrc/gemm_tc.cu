@@ -86,6 +86,7 @@ __device__ __forceinline__ void copy_chunk(uint8_t* dst, const Src& s) {
 
 template <int AM, int BMODE, int BN, uint32_t E>
 __global__ void __launch_bounds__(NT, 2) gemm_tc_kernel(const __grid_constant__ GemmP p) {
+  pdl_wait(); pdl_trigger();
   using C = Cfg<BN>;
   constexpr int NS = C::NS;
   constexpr bool A_ROWFIXED = (AM == A_PLAIN || AM == A_CONV);     // K-contiguous A  -> K-major
@@ -315,8 +316,7 @@ cudaError_t launch_cfg(const GemmP& p, cudaStream_t s) {
     configured = true;
   }
   dim3 grid(cdiv(p.N, BN), cdiv(p.M, TBM), p.batch * p.splitk);
-  gemm_tc_kernel<AM, BMODE, BN, E><<<grid, NT, Cfg<BN>::SMEM, s>>>(p);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((gemm_tc_kernel<AM, BMODE, BN, E>), grid, NT, Cfg<BN>::SMEM, s, p);
   return cudaSuccess;
 }
 

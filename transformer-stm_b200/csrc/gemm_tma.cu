@@ -76,6 +76,7 @@ __global__ void __launch_bounds__(TCfg<BN, X3>::THREADS, 1) gemm_tma_kernel(cons
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait(); pdl_trigger();      // everything above touches no global memory
   const uint32_t tmem_base = *tmem_slot;
   if (threadIdx.x == 0) GEMM_TRACE(1);
 
@@ -256,6 +257,7 @@ __global__ void __launch_bounds__(TCfg<BN, X3>::THREADS, 1) gemm_tma_kernel(cons
 
 __global__ void __launch_bounds__(256) transpose_weights_kernel(const float* __restrict__ src, float* __restrict__ dst, float* __restrict__ dst2,
                                                                 const TrDesc* __restrict__ descs, int ndesc, int round) {
+  pdl_wait(); pdl_trigger();
   __shared__ float t[32][33];
   int d = 0;
   while (d + 1 < ndesc && (int)blockIdx.x >= descs[d + 1].tile0) ++d;
@@ -363,8 +365,7 @@ cudaError_t launch_tma_cfg(const GemmP& p, cudaStream_t s) {
   if (!make_tmap_3d(&tmB, p.B, p.K, p.N, p.batch, p.ldb, p.b_bs0, BN, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
   const int m_tiles = cdiv(p.M, BM), n_tiles = p.N / BN, num_tiles = m_tiles * n_tiles * p.batch;
   const int grid = num_tiles < kNumSMs ? num_tiles : kNumSMs;
-  gemm_tma_kernel<BN, E, X3><<<grid, TCfg<BN, X3>::THREADS, TCfg<BN, X3>::SMEM, s>>>(p, tmA, tmB, m_tiles, n_tiles, num_tiles);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((gemm_tma_kernel<BN, E, X3>), grid, (TCfg<BN, X3>::THREADS), (TCfg<BN, X3>::SMEM), s, p, tmA, tmB, m_tiles, n_tiles, num_tiles);
   return cudaSuccess;
 }
 template <uint32_t E>
@@ -382,8 +383,7 @@ constexpr uint32_t kTmaEpiKinds = EPI_GELU | EPI_RESID | EPI_GELU_BWD | EPI_PHIL
 
 cudaError_t launch_transpose_weights(const float* src, float* dst, float* dst2, const TrDesc* descs_dev, int ndesc, int total_tiles, cudaStream_t s, int round) {
   if (ndesc < 1 || total_tiles < 1) return cudaSuccess;
-  transpose_weights_kernel<<<total_tiles, 256, 0, s>>>(src, dst, dst2, descs_dev, ndesc, round);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((transpose_weights_kernel), total_tiles, 256, 0, s, src, dst, dst2, descs_dev, ndesc, round);
   return cudaSuccess;
 }
 

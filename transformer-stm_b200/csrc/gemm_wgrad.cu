@@ -72,6 +72,7 @@ __global__ void __launch_bounds__(WCfg<BN, X3>::THREADS, 1) wgrad_tma_kernel(con
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait(); pdl_trigger();      // everything above touches no global memory
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
@@ -231,8 +232,7 @@ cudaError_t launch_w(const WgradP& p, cudaStream_t s) {
   if (splits < 1) splits = 1;
   const int steps_per_split = cdiv(total_steps, splits);
   splits = cdiv(total_steps, steps_per_split);
-  wgrad_tma_kernel<BN, X3><<<tiles * splits, WCfg<BN, X3>::THREADS, WCfg<BN, X3>::SMEM, s>>>(p, tmX, tmY, m_tiles, n_tiles, splits, steps_per_split);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((wgrad_tma_kernel<BN, X3>), tiles * splits, (WCfg<BN, X3>::THREADS), (WCfg<BN, X3>::SMEM), s, p, tmX, tmY, m_tiles, n_tiles, splits, steps_per_split);
   return cudaSuccess;
 }
 }  // namespace

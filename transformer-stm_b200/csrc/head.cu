@@ -22,6 +22,7 @@ __device__ __forceinline__ float block_sum(float v, float* red) {   // red: 8 fl
 
 // ---- forward: grid = B, block = 256.  Shared: feat[F] + p1[PH] ------------------------------------------------------------
 __global__ void __launch_bounds__(HT) head_fwd_kernel(const HeadP p) {
+  pdl_wait(); pdl_trigger();
   extern __shared__ float sh[];
   float* s_feat = sh; float* s_p1 = sh + p.F; float* s_part = s_p1 + p.PH;     // s_part: [8][PH] partial sums of Proc_Dense_2
   __shared__ float red[8];
@@ -130,6 +131,7 @@ __global__ void __launch_bounds__(HT) head_fwd_kernel(const HeadP p) {
 
 // ---- backward A: per-image input gradients.  grid = B, block = 256.  Shared: dfeat[F] + dz2[PH] -------------------------------
 __global__ void __launch_bounds__(HT) head_bwd_image_kernel(const HeadP p) {
+  pdl_wait(); pdl_trigger();
   extern __shared__ float sh[];
   float* s_dfeat = sh; float* s_dz2 = sh + p.F;
   __shared__ float red[8];
@@ -212,6 +214,7 @@ __global__ void __launch_bounds__(HT) head_bwd_image_kernel(const HeadP p) {
 //   n0 blocks {db2, db1, dW1} (32 hidden units each) | n1 blocks dW_final (+ db_final in the first) | n2 blocks LayerNorm d gamma, d beta
 // Every loop issues its loads for a batch of images before the arithmetic: the work is tiny, the cost is exposed memory latency.
 __global__ void __launch_bounds__(HT) head_bwd_param_kernel(const HeadP p, int tiles2, int tn, int n0, int n1) {
+  pdl_wait(); pdl_trigger();
   __shared__ float red[8][10][33];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5, tid = threadIdx.x;
   const int B = p.B, PH = p.PH, D = p.D, nc = p.nc;
@@ -345,20 +348,17 @@ __global__ void __launch_bounds__(HT) head_bwd_param_kernel(const HeadP p, int t
 cudaError_t launch_head_fwd(const HeadP& p, cudaStream_t s) {
   const size_t smem = (size_t)(p.F + 9 * p.PH) * sizeof(float);
   if (smem > 48 * 1024) { set_error("head: feature + hidden width too large for the fused head kernel"); return cudaErrorInvalidValue; }
-  head_fwd_kernel<<<p.B, HT, smem, s>>>(p);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((head_fwd_kernel), p.B, HT, smem, s, p);
   return cudaSuccess;
 }
 
 cudaError_t launch_head_bwd(const HeadP& p, cudaStream_t s) {
   const size_t smem = (size_t)(p.F + p.PH) * sizeof(float);
   if (smem > 48 * 1024) { set_error("head: feature + hidden width too large for the fused head kernel"); return cudaErrorInvalidValue; }
-  head_bwd_image_kernel<<<p.B, HT, smem, s>>>(p);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((head_bwd_image_kernel), p.B, HT, smem, s, p);
   const int tn = p.proc_dim > 0 ? (p.PH + 31) / 32 : 0, tiles2 = tn * tn;
   const int n0 = tn, n1 = (p.F * p.nc + 31) / 32, n2 = p.cls_ln ? (p.D + 31) / 32 : 0;
-  head_bwd_param_kernel<<<tiles2 + n0 + n1 + n2, HT, 0, s>>>(p, tiles2, tn, n0, n1);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((head_bwd_param_kernel), tiles2 + n0 + n1 + n2, HT, 0, s, p, tiles2, tn, n0, n1);
   return cudaSuccess;
 }
 

@@ -11,6 +11,7 @@ namespace {
 // cin % 4 == 0: one thread per (row m, tap, float4 channel group)
 template <int KK, int SS>
 __global__ void __launch_bounds__(256) im2col_v4_kernel(const float* __restrict__ x, ConvGeom g, int M, int ldc, float* __restrict__ col) {
+  pdl_wait(); pdl_trigger();
   if (KK) { g.k = KK; g.s = SS; }
   const int c4n = g.cin >> 2, per_row = g.k * g.k * c4n;
   const long long total = (long long)M * per_row;
@@ -34,6 +35,7 @@ __global__ void __launch_bounds__(256) im2col_v4_kernel(const float* __restrict_
 // decoded once, and the (image, output row, output column) of the walk advances by increments: no division in the loop
 template <int KK, int SS>
 __global__ void __launch_bounds__(1024) im2col_rows_kernel(const float* __restrict__ x, ConvGeom g, int M, int ldc, float* __restrict__ col, int rpb) {
+  pdl_wait(); pdl_trigger();
   if (KK) { g.k = KK; g.s = SS; }
   const int c4n = g.cin >> 2, per_row = g.k * g.k * c4n, r = threadIdx.x;
   if (r >= per_row) return;
@@ -56,6 +58,7 @@ __global__ void __launch_bounds__(1024) im2col_rows_kernel(const float* __restri
 
 // any cin (stage 1: cin = 1): one thread per (row m, padded column kk)
 __global__ void __launch_bounds__(256) im2col_scalar_kernel(const float* __restrict__ x, ConvGeom g, int M, int K, int ldc, float* __restrict__ col) {
+  pdl_wait(); pdl_trigger();
   const long long total = (long long)M * ldc;
   const int hw = g.ho * g.wo;
   for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
@@ -76,6 +79,7 @@ __global__ void __launch_bounds__(256) im2col_scalar_kernel(const float* __restr
 // any cin, ldc % 4 == 0: one thread per (row m, group of 4 padded columns): the index decode (runtime divisions) is paid once per 16-byte
 // store instead of once per element, and consecutive threads write consecutive 16-byte pieces of the contiguous patch matrix
 __global__ void __launch_bounds__(256) im2col_vec_kernel(const float* __restrict__ x, ConvGeom g, int M, int K, int ldc, float* __restrict__ col) {
+  pdl_wait(); pdl_trigger();
   const int q4n = ldc >> 2;
   const long long total = (long long)M * q4n;
   const int hw = g.ho * g.wo;
@@ -104,6 +108,7 @@ __global__ void __launch_bounds__(256) im2col_vec_kernel(const float* __restrict
 template <int KK, int SS>
 __global__ void __launch_bounds__(256) col2im_v4_kernel(const float* __restrict__ dcol, ConvGeom g, int B, int ldc, float* __restrict__ dx,
                                                         const uint8_t* __restrict__ mask, float mscale, float* __restrict__ dxm, int round_m) {
+  pdl_wait(); pdl_trigger();
   if (KK) { g.k = KK; g.s = SS; }
   const int c4n = g.cin >> 2;
   const long long total = (long long)B * g.hin * g.win * c4n;
@@ -153,17 +158,16 @@ cudaError_t launch_im2col(const float* x, const ConvGeom& g, int M, int K, int l
     if (threads <= 1024) {
       const int rpb = M >= kNumSMs * 16 ? 4 : 1;           // rows per block (measured: 4 beats 1 and 16 on both 3x3 ConvEmbeds)
       const int grid = (M + rpb - 1) / rpb;
-      if (g.k == 3 && g.s == 2) im2col_rows_kernel<3, 2><<<grid, threads, 0, s>>>(x, g, M, ldc, col, rpb);
-      else im2col_rows_kernel<0, 0><<<grid, threads, 0, s>>>(x, g, M, ldc, col, rpb);
+      if (g.k == 3 && g.s == 2) CVT_LAUNCH((im2col_rows_kernel<3, 2>), grid, threads, 0, s, x, g, M, ldc, col, rpb);
+      else CVT_LAUNCH((im2col_rows_kernel<0, 0>), grid, threads, 0, s, x, g, M, ldc, col, rpb);
     } else
-    if (g.k == 3 && g.s == 2) im2col_v4_kernel<3, 2><<<ew_grid((long long)M * (K >> 2)), 256, 0, s>>>(x, g, M, ldc, col);
-    else im2col_v4_kernel<0, 0><<<ew_grid((long long)M * (K >> 2)), 256, 0, s>>>(x, g, M, ldc, col);
+    if (g.k == 3 && g.s == 2) CVT_LAUNCH((im2col_v4_kernel<3, 2>), ew_grid((long long)M * (K >> 2)), 256, 0, s, x, g, M, ldc, col);
+    else CVT_LAUNCH((im2col_v4_kernel<0, 0>), ew_grid((long long)M * (K >> 2)), 256, 0, s, x, g, M, ldc, col);
   }
   else if ((ldc & 3) == 0 && (reinterpret_cast<uintptr_t>(col) & 15) == 0)
-    im2col_vec_kernel<<<ew_grid((long long)M * (ldc >> 2)), 256, 0, s>>>(x, g, M, K, ldc, col);
+    CVT_LAUNCH((im2col_vec_kernel), ew_grid((long long)M * (ldc >> 2)), 256, 0, s, x, g, M, K, ldc, col);
   else
-    im2col_scalar_kernel<<<ew_grid((long long)M * ldc), 256, 0, s>>>(x, g, M, K, ldc, col);
-  CVT_LAUNCH_CHECK();
+    CVT_LAUNCH((im2col_scalar_kernel), ew_grid((long long)M * ldc), 256, 0, s, x, g, M, K, ldc, col);
   return cudaSuccess;
 }
 
@@ -171,9 +175,8 @@ cudaError_t launch_col2im(const float* dcol, const ConvGeom& g, int B, int ldc, 
                           float* dxm, int round_m) {
   if ((g.cin & 3) || (g.boff & 3) || (g.bstride & 3)) { set_error("col2im: cin must be a multiple of 4"); return cudaErrorInvalidValue; }
   const int grid = ew_grid((long long)B * g.hin * g.win * (g.cin >> 2));
-  if (g.k == 3 && g.s == 2) col2im_v4_kernel<3, 2><<<grid, 256, 0, s>>>(dcol, g, B, ldc, dx, mask, mscale, dxm, round_m);     // ConvEmbed of stages 2, 3
-  else col2im_v4_kernel<0, 0><<<grid, 256, 0, s>>>(dcol, g, B, ldc, dx, mask, mscale, dxm, round_m);
-  CVT_LAUNCH_CHECK();
+  if (g.k == 3 && g.s == 2) CVT_LAUNCH((col2im_v4_kernel<3, 2>), grid, 256, 0, s, dcol, g, B, ldc, dx, mask, mscale, dxm, round_m);     // ConvEmbed of stages 2, 3
+  else CVT_LAUNCH((col2im_v4_kernel<0, 0>), grid, 256, 0, s, dcol, g, B, ldc, dx, mask, mscale, dxm, round_m);
   return cudaSuccess;
 }
 

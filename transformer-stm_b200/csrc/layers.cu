@@ -14,6 +14,7 @@ __global__ void __launch_bounds__(256) ln_fwd_kernel(const float* __restrict__ x
                                                      const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
                                                      float* __restrict__ y, long long ldy, float* __restrict__ mean,
                                                      float* __restrict__ rstd, int rows, int D) {
+  pdl_wait(); pdl_trigger();
   const int lane = threadIdx.x & 31;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int nwarps = (gridDim.x * blockDim.x) >> 5;
@@ -50,6 +51,7 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const float* __restrict__ d
                                                      const float* dres, float* dx, RowMap out_map,   // may alias (in-place add)
                                                      long long ldo, float* __restrict__ dgamma, float* __restrict__ dbeta,
                                                      int rows, int D) {
+  pdl_wait(); pdl_trigger();
   extern __shared__ float sm[];   // [2][D]
   float* sg = sm; float* sb = sm + D;
   for (int i = threadIdx.x; i < 2 * D; i += blockDim.x) sm[i] = 0.f;
@@ -109,6 +111,7 @@ __device__ __forceinline__ float4 f4_scale(float4 a, float s) { return make_floa
 __device__ __forceinline__ float4 f4_zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }
 
 __global__ void dwproj_fwd_kernel(const __grid_constant__ DwProjP p) {
+  pdl_wait(); pdl_trigger();
   extern __shared__ __align__(16) float smw[];            // [3][9][D] weights, then (stats) [6][D] block partials
   const int D = p.D, C4 = D >> 2;
   const int c4 = threadIdx.x, py = threadIdx.y, PY = blockDim.y;
@@ -178,6 +181,7 @@ __global__ void dwproj_fwd_kernel(const __grid_constant__ DwProjP p) {
 
 // block = (32 channels, 32 partial lanes): the per-CTA partial slices of the statistics are summed 32-way in parallel
 __global__ void __launch_bounds__(1024) bn_finalize_kernel(const __grid_constant__ BnFinalizeP p) {
+  pdl_wait(); pdl_trigger();
   __shared__ double red[2][32][33];
   const int i = blockIdx.x * 32 + threadIdx.x;      // (z, c)
   const bool ok = i < 3 * p.D;
@@ -217,6 +221,7 @@ __global__ void __launch_bounds__(1024) bn_finalize_kernel(const __grid_constant
 __global__ void bn_bwd_reduce_kernel(const float* __restrict__ dy, const float* __restrict__ conv, long long bs,
                                      const float* __restrict__ save_mean, const float* __restrict__ save_rstd,
                                      float* __restrict__ dgamma, float* __restrict__ dbeta, int B, int T, int Tc, int has_cls, int D) {
+  pdl_wait(); pdl_trigger();
   extern __shared__ __align__(16) float sred[];             // [6][D]
   const int C4 = D >> 2, c4 = threadIdx.x, py = threadIdx.y, PY = blockDim.y;
   const int tid = py * C4 + c4, nthreads = C4 * PY;
@@ -257,6 +262,7 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(float* __restrict__ d
                                                            const float* __restrict__ gamma, const float* __restrict__ scale,
                                                            const float* __restrict__ dgamma, const float* __restrict__ dbeta,
                                                            int training, int B, int T, int Tc, int has_cls, int D) {
+  pdl_wait(); pdl_trigger();
   const int C4 = D >> 2;
   const long long per = (long long)B * T * C4;
   const long long total = 3 * per;
@@ -288,6 +294,7 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(float* __restrict__ d
 }
 
 __global__ void dwproj_bwd_kernel(const __grid_constant__ DwProjBwdP p) {
+  pdl_wait(); pdl_trigger();
   extern __shared__ __align__(16) float smw[];            // [3][9][D] weights, then [9][D] block partial of ddw (per z)
   const int D = p.D, C4 = D >> 2;
   const int c4 = threadIdx.x, py = threadIdx.y, PY = blockDim.y;
@@ -367,6 +374,7 @@ __global__ void dwproj_bwd_kernel(const __grid_constant__ DwProjBwdP p) {
 // softmax rows (fp32 attention path)
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) softmax_rows_kernel(float* __restrict__ S, long long rows, int cols) {
+  pdl_wait(); pdl_trigger();
   const int lane = threadIdx.x & 31;
   const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
@@ -383,6 +391,7 @@ __global__ void __launch_bounds__(256) softmax_rows_kernel(float* __restrict__ S
   }
 }
 __global__ void __launch_bounds__(256) softmax_bwd_rows_kernel(float* __restrict__ dP, const float* __restrict__ P, long long rows, int cols) {
+  pdl_wait(); pdl_trigger();
   const int lane = threadIdx.x & 31;
   const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
@@ -400,10 +409,12 @@ __global__ void __launch_bounds__(256) softmax_bwd_rows_kernel(float* __restrict
 // ------------------------------------------------------------------------------------------------
 // dyn (optional): per-step values kept in device memory so that a captured CUDA graph can be replayed: {alpha, grad_scale, dropout step}
 __global__ void set_step_params_kernel(float* dyn, float alpha, float gs, uint32_t step) {
+  pdl_wait(); pdl_trigger();
   dyn[0] = alpha; dyn[1] = gs; reinterpret_cast<uint32_t*>(dyn)[2] = step;
 }
 __global__ void __launch_bounds__(256) philox_mask_kernel(uint8_t* __restrict__ mask, long long n, uint32_t thr, uint32_t k0, uint32_t k1,
                                                           uint32_t step, uint32_t site, const float* __restrict__ dyn) {
+  pdl_wait(); pdl_trigger();
   if (dyn) step = reinterpret_cast<const uint32_t*>(dyn)[2];
   const long long nq = (n + 3) >> 2;
   for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < nq; q += (long long)gridDim.x * blockDim.x) {
@@ -420,12 +431,14 @@ __global__ void __launch_bounds__(256) philox_mask_kernel(uint8_t* __restrict__ 
 }
 __global__ void __launch_bounds__(256) mask_scale_kernel(float* __restrict__ dst, const float* __restrict__ src,
                                                          const uint8_t* __restrict__ mask, float scale, long long n, int round) {
+  pdl_wait(); pdl_trigger();
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
     const float v = mask[i] ? src[i] * scale : 0.f;
     dst[i] = round ? round_tf32(v) : v;
   }
 }
 __global__ void __launch_bounds__(256) fill_rows_kernel(float* __restrict__ dst, RowMap map, long long ld, const float* __restrict__ src, int rows, int D) {
+  pdl_wait(); pdl_trigger();
   const long long total = (long long)rows * D;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
     const long long r = i / D; const int c = (int)(i - r * D);
@@ -434,6 +447,7 @@ __global__ void __launch_bounds__(256) fill_rows_kernel(float* __restrict__ dst,
 }
 __global__ void __launch_bounds__(256) copy_rows_kernel(float* __restrict__ dst, RowMap dmap, long long ldd, const float* __restrict__ src,
                                                         RowMap smap, long long lds, int rows, int D) {
+  pdl_wait(); pdl_trigger();
   const long long total = (long long)rows * D;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
     const long long r = i / D; const int c = (int)(i - r * D);
@@ -443,6 +457,7 @@ __global__ void __launch_bounds__(256) copy_rows_kernel(float* __restrict__ dst,
 // 16-byte version (D, ldd, lds multiples of 4, aligned bases): the row-map divisions are paid once per float4
 __global__ void __launch_bounds__(256) copy_rows_v4_kernel(float* __restrict__ dst, RowMap dmap, long long ldd, const float* __restrict__ src,
                                                            RowMap smap, long long lds, int rows, int D4) {
+  pdl_wait(); pdl_trigger();
   const long long total = (long long)rows * D4;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
     const int r = (int)(i / D4), c = (int)(i - (long long)r * D4) << 2;
@@ -450,6 +465,7 @@ __global__ void __launch_bounds__(256) copy_rows_v4_kernel(float* __restrict__ d
   }
 }
 __global__ void __launch_bounds__(256) token_mean_kernel(const float* __restrict__ x, int B, int T, int D, float* __restrict__ out, long long ldo) {
+  pdl_wait(); pdl_trigger();
   // block = one image, threads over channels; coalesced over c
   const int b = blockIdx.x;
   for (int c = threadIdx.x; c < D; c += blockDim.x) {
@@ -459,6 +475,7 @@ __global__ void __launch_bounds__(256) token_mean_kernel(const float* __restrict
   }
 }
 __global__ void __launch_bounds__(256) token_mean_bwd_kernel(const float* __restrict__ dy, long long lddy, int B, int T, int D, float* __restrict__ dx) {
+  pdl_wait(); pdl_trigger();
   const long long total = (long long)B * T * D;
   const float inv = 1.f / (float)T;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -469,6 +486,7 @@ __global__ void __launch_bounds__(256) token_mean_bwd_kernel(const float* __rest
 
 __global__ void __launch_bounds__(256) mse_loss_kernel(const float* __restrict__ pred, const float* __restrict__ y, int n,
                                                        float* __restrict__ metrics, float* __restrict__ dpred, float grad_scale, int accumulate) {
+  pdl_wait(); pdl_trigger();
   __shared__ float s1[8], s2[8];
   float a = 0.f, b = 0.f;
   for (int i = threadIdx.x; i < n; i += blockDim.x) {
@@ -490,6 +508,7 @@ __global__ void __launch_bounds__(256) mse_loss_kernel(const float* __restrict__
 __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                                                    float* __restrict__ v, long long n4, float alpha, float b1, float b2, float eps, float gs,
                                                    const float* __restrict__ dyn) {
+  pdl_wait(); pdl_trigger();
   if (dyn) { alpha = dyn[0]; gs = dyn[1]; }
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
     float4 pp = reinterpret_cast<float4*>(p)[i];
@@ -530,8 +549,7 @@ cudaError_t launch_ln_fwd(const float* x, RowMap in_map, long long ldx, const fl
     const cudaError_t e = launch_ln_fwd_v4(x, in_map, ldx, gamma, beta, eps, y, ldy, mean, rstd, rows, D, s, round_out);
     if (e != cudaErrorNotSupported) return e;
   }
-  ln_fwd_kernel<<<ew_blocks(rows, 8), 256, 0, s>>>(x, in_map, ldx, gamma, beta, eps, y, ldy, mean, rstd, rows, D);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((ln_fwd_kernel), ew_blocks(rows, 8), 256, 0, s, x, in_map, ldx, gamma, beta, eps, y, ldy, mean, rstd, rows, D);
   return cudaSuccess;
 }
 
@@ -549,9 +567,8 @@ cudaError_t launch_ln_bwd(const float* dy, long long lddy, const float* x, RowMa
   }
   int blocks = cdiv(rows, 8);
   if (blocks > kNumSMs * 2) blocks = kNumSMs * 2;
-  ln_bwd_kernel<<<blocks, 256, 2 * D * sizeof(float), s>>>(dy, lddy, x, in_map, ldx, mean, rstd, gamma, dres, dx, out_map, ldo,
+  CVT_LAUNCH((ln_bwd_kernel), blocks, 256, 2 * D * sizeof(float), s, dy, lddy, x, in_map, ldx, mean, rstd, gamma, dres, dx, out_map, ldo,
                                                            dgamma, dbeta, rows, D);
-  CVT_LAUNCH_CHECK();
   if (mask) CVT_CUDA(launch_mask_scale(dxm, dx, mask, mscale, (long long)rows * D, s, round_m));
   return cudaSuccess;
 }
@@ -561,23 +578,20 @@ cudaError_t launch_dwproj_fwd(const DwProjP& p, cudaStream_t s) {
   const dim3 blk = proj_block(p.D);
   const size_t smem = (size_t)(27 + 6) * p.D * sizeof(float);
   if (smem > 48 * 1024) CVT_CUDA(cudaFuncSetAttribute(dwproj_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  dwproj_fwd_kernel<<<proj_grid((long long)p.B * p.H * p.W, blk.y), blk, smem, s>>>(p);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((dwproj_fwd_kernel), proj_grid((long long)p.B * p.H * p.W, blk.y), blk, smem, s, p);
   return cudaSuccess;
 }
 
 cudaError_t launch_bn_finalize(const BnFinalizeP& p, cudaStream_t s) {
-  bn_finalize_kernel<<<cdiv(3 * p.D, 32), dim3(32, 32), 0, s>>>(p);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((bn_finalize_kernel), cdiv(3 * p.D, 32), dim3(32, 32), 0, s, p);
   return cudaSuccess;
 }
 
 cudaError_t launch_bn_bwd_reduce(const float* dy, const float* conv, long long bs, const float* save_mean, const float* save_rstd,
                                  float* dgamma, float* dbeta, int B, int T, int Tc, int has_cls, int D, cudaStream_t s) {
   const dim3 blk = proj_block(D);
-  bn_bwd_reduce_kernel<<<proj_grid((long long)B * T, blk.y), blk, 6 * D * sizeof(float), s>>>(dy, conv, bs, save_mean, save_rstd,
+  CVT_LAUNCH((bn_bwd_reduce_kernel), proj_grid((long long)B * T, blk.y), blk, 6 * D * sizeof(float), s, dy, conv, bs, save_mean, save_rstd,
                                                                                              dgamma, dbeta, B, T, Tc, has_cls, D);
-  CVT_LAUNCH_CHECK();
   return cudaSuccess;
 }
 
@@ -585,9 +599,8 @@ cudaError_t launch_bn_bwd_apply(float* dy, const float* conv, long long bs, cons
                                 const float* gamma, const float* scale, const float* dgamma, const float* dbeta, int training,
                                 int B, int T, int Tc, int has_cls, int D, cudaStream_t s) {
   const long long total = 3ll * B * T * (D / 4);
-  bn_bwd_apply_kernel<<<ew_blocks(total), 256, 0, s>>>(dy, conv, bs, save_mean, save_rstd, gamma, scale, dgamma, dbeta, training,
+  CVT_LAUNCH((bn_bwd_apply_kernel), ew_blocks(total), 256, 0, s, dy, conv, bs, save_mean, save_rstd, gamma, scale, dgamma, dbeta, training,
                                                        B, T, Tc, has_cls, D);
-  CVT_LAUNCH_CHECK();
   return cudaSuccess;
 }
 
@@ -595,21 +608,18 @@ cudaError_t launch_dwproj_bwd(const DwProjBwdP& p, cudaStream_t s) {
   const dim3 blk = proj_block(p.D);
   const size_t smem = (size_t)(27 + 9) * p.D * sizeof(float);
   if (smem > 48 * 1024) CVT_CUDA(cudaFuncSetAttribute(dwproj_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  dwproj_bwd_kernel<<<proj_grid((long long)p.B * p.H * p.W, blk.y), blk, smem, s>>>(p);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((dwproj_bwd_kernel), proj_grid((long long)p.B * p.H * p.W, blk.y), blk, smem, s, p);
   return cudaSuccess;
 }
 
 cudaError_t launch_softmax_rows(float* S, long long rows, int cols, cudaStream_t s) {
   if (rows <= 0) return cudaSuccess;
-  softmax_rows_kernel<<<ew_blocks(rows, 8), 256, 0, s>>>(S, rows, cols);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((softmax_rows_kernel), ew_blocks(rows, 8), 256, 0, s, S, rows, cols);
   return cudaSuccess;
 }
 cudaError_t launch_softmax_bwd_rows(float* dP, const float* P, long long rows, int cols, cudaStream_t s) {
   if (rows <= 0) return cudaSuccess;
-  softmax_bwd_rows_kernel<<<ew_blocks(rows, 8), 256, 0, s>>>(dP, P, rows, cols);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((softmax_bwd_rows_kernel), ew_blocks(rows, 8), 256, 0, s, dP, P, rows, cols);
   return cudaSuccess;
 }
 
@@ -617,57 +627,48 @@ cudaError_t launch_philox_mask(uint8_t* mask, long long n, float rate, uint64_t 
   if (n <= 0) return cudaSuccess;
   double t = (double)rate * 4294967296.0;
   const uint32_t thr = t >= 4294967295.0 ? 0xFFFFFFFFu : (uint32_t)t;
-  philox_mask_kernel<<<ew_blocks((n + 3) / 4), 256, 0, s>>>(mask, n, thr, (uint32_t)(seed & 0xFFFFFFFFu), (uint32_t)(seed >> 32), step, site, dyn);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((philox_mask_kernel), ew_blocks((n + 3) / 4), 256, 0, s, mask, n, thr, (uint32_t)(seed & 0xFFFFFFFFu), (uint32_t)(seed >> 32), step, site, dyn);
   return cudaSuccess;
 }
 cudaError_t launch_mask_scale(float* dst, const float* src, const uint8_t* mask, float scale, long long n, cudaStream_t s, int round) {
   if (n <= 0) return cudaSuccess;
-  mask_scale_kernel<<<ew_blocks(n), 256, 0, s>>>(dst, src, mask, scale, n, round);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((mask_scale_kernel), ew_blocks(n), 256, 0, s, dst, src, mask, scale, n, round);
   return cudaSuccess;
 }
 cudaError_t launch_fill_rows(float* dst, RowMap map, long long ld, const float* src, int rows, int D, cudaStream_t s) {
   if (rows <= 0) return cudaSuccess;
-  fill_rows_kernel<<<ew_blocks((long long)rows * D), 256, 0, s>>>(dst, map, ld, src, rows, D);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((fill_rows_kernel), ew_blocks((long long)rows * D), 256, 0, s, dst, map, ld, src, rows, D);
   return cudaSuccess;
 }
 cudaError_t launch_copy_rows(float* dst, RowMap dmap, long long ldd, const float* src, RowMap smap, long long lds, int rows, int D, cudaStream_t s) {
   if (rows <= 0) return cudaSuccess;
   if (!(D & 3) && !(ldd & 3) && !(lds & 3) && !(reinterpret_cast<uintptr_t>(dst) & 15) && !(reinterpret_cast<uintptr_t>(src) & 15))
-    copy_rows_v4_kernel<<<ew_blocks((long long)rows * (D >> 2)), 256, 0, s>>>(dst, dmap, ldd, src, smap, lds, rows, D >> 2);
+    CVT_LAUNCH((copy_rows_v4_kernel), ew_blocks((long long)rows * (D >> 2)), 256, 0, s, dst, dmap, ldd, src, smap, lds, rows, D >> 2);
   else
-    copy_rows_kernel<<<ew_blocks((long long)rows * D), 256, 0, s>>>(dst, dmap, ldd, src, smap, lds, rows, D);
-  CVT_LAUNCH_CHECK();
+    CVT_LAUNCH((copy_rows_kernel), ew_blocks((long long)rows * D), 256, 0, s, dst, dmap, ldd, src, smap, lds, rows, D);
   return cudaSuccess;
 }
 cudaError_t launch_token_mean(const float* x, int B, int T, int D, float* out, long long ldo, cudaStream_t s) {
-  token_mean_kernel<<<B, 256, 0, s>>>(x, B, T, D, out, ldo);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((token_mean_kernel), B, 256, 0, s, x, B, T, D, out, ldo);
   return cudaSuccess;
 }
 cudaError_t launch_token_mean_bwd(const float* dy, long long lddy, int B, int T, int D, float* dx, cudaStream_t s) {
-  token_mean_bwd_kernel<<<ew_blocks((long long)B * T * D), 256, 0, s>>>(dy, lddy, B, T, D, dx);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((token_mean_bwd_kernel), ew_blocks((long long)B * T * D), 256, 0, s, dy, lddy, B, T, D, dx);
   return cudaSuccess;
 }
 cudaError_t launch_mse_loss(const float* pred, const float* y, int n, float* metrics, float* dpred, float grad_scale, int accumulate, cudaStream_t s) {
-  mse_loss_kernel<<<1, 256, 0, s>>>(pred, y, n, metrics, dpred, grad_scale, accumulate);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((mse_loss_kernel), 1, 256, 0, s, pred, y, n, metrics, dpred, grad_scale, accumulate);
   return cudaSuccess;
 }
 cudaError_t launch_set_step_params(float* dyn, float alpha, float gs, uint32_t step, cudaStream_t s) {
-  set_step_params_kernel<<<1, 1, 0, s>>>(dyn, alpha, gs, step);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((set_step_params_kernel), 1, 1, 0, s, dyn, alpha, gs, step);
   return cudaSuccess;
 }
 cudaError_t launch_adam(float* params, const float* grads, float* m, float* v, long long n, float alpha, float b1, float b2,
                         float eps, float grad_scale, cudaStream_t s, const float* dyn) {
   if (n <= 0) return cudaSuccess;
   if (n % 4 != 0) { set_error("adam: arena length must be a multiple of 4"); return cudaErrorInvalidValue; }
-  adam_kernel<<<ew_blocks(n / 4), 256, 0, s>>>(params, grads, m, v, n / 4, alpha, b1, b2, eps, grad_scale, dyn);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((adam_kernel), ew_blocks(n / 4), 256, 0, s, params, grads, m, v, n / 4, alpha, b1, b2, eps, grad_scale, dyn);
   return cudaSuccess;
 }
 

@@ -18,6 +18,7 @@ __global__ void __launch_bounds__(256) ln_fwd_v4_kernel(const float* __restrict_
                                                         const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
                                                         float* __restrict__ y, long long ldy, float* __restrict__ mean,
                                                         float* __restrict__ rstd, int rows, int round_out) {
+  pdl_wait(); pdl_trigger();
   constexpr int RPW = 32 / LPR, D = LPR * VPL * 4;
   const int lane = threadIdx.x & 31, sub = lane / LPR, li = lane % LPR;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
@@ -79,6 +80,7 @@ __global__ void __launch_bounds__(256) ln_bwd_v4_kernel(const float* __restrict_
                                                         const float* dres, float* dx, RowMap out_map, long long ldo,   // may alias
                                                         float* __restrict__ dgamma, float* __restrict__ dbeta, int rows,
                                                         const uint8_t* __restrict__ mask, float mscale, float* __restrict__ dxm, int round_m) {
+  pdl_wait(); pdl_trigger();
   // mask != nullptr: a second output dxm = dx * (mask ? mscale : 0) (the gradient through the dropout that follows in backward order;
   // mask and dxm are indexed like dx), optionally rounded to TF32 for the tensor-core GEMMs that consume it
   constexpr int RPW = 32 / LPR, D = LPR * VPL * 4;
@@ -176,7 +178,7 @@ cudaError_t launch_ln_fwd_v4(const float* x, RowMap in_map, long long ldx, const
                              float* y, long long ldy, float* mean, float* rstd, int rows, int D, cudaStream_t s, int round_out) {
   if ((ldx & 3) || (ldy & 3) || !al16(x) || !al16(y) || !al16(gamma) || !al16(beta)) return cudaErrorNotSupported;
   auto grid = [&](int rpw_u) { long long w = cdivl(rows, rpw_u); long long b = cdivl(w, 8); return (int)(b < 1 ? 1 : (b > kNumSMs * 8 ? kNumSMs * 8 : b)); };
-#define LN_FWD(VPL, LPR, U) ln_fwd_v4_kernel<VPL, LPR, U><<<grid((32 / LPR) * U), 256, 0, s>>>(x, in_map, ldx, gamma, beta, eps, y, ldy, mean, rstd, rows, round_out)
+#define LN_FWD(VPL, LPR, U) CVT_LAUNCH((ln_fwd_v4_kernel<VPL, LPR, U>), grid((32 / LPR) * U), 256, 0, s, x, in_map, ldx, gamma, beta, eps, y, ldy, mean, rstd, rows, round_out)
   if (D == 64) LN_FWD(1, 16, 4);
   else if (D == 128) LN_FWD(1, 32, 4);
   else if (D == 192) LN_FWD(3, 16, 2);
@@ -185,7 +187,6 @@ cudaError_t launch_ln_fwd_v4(const float* x, RowMap in_map, long long ldx, const
   else if (D == 512) LN_FWD(4, 32, 2);
   else return cudaErrorNotSupported;
 #undef LN_FWD
-  CVT_LAUNCH_CHECK();
   return cudaSuccess;
 }
 
@@ -195,7 +196,7 @@ cudaError_t launch_ln_bwd_v4(const float* dy, long long lddy, const float* x, Ro
   if ((ldx & 3) || (lddy & 3) || (ldo & 3) || !al16(x) || !al16(dy) || !al16(dx) || !al16(gamma) || (dres && !al16(dres))) return cudaErrorNotSupported;
   if (mask && ((reinterpret_cast<uintptr_t>(mask) & 3) || !al16(dxm))) return cudaErrorNotSupported;
   auto grid = [&](int rpw_u) { long long w = cdivl(rows, rpw_u); long long b = cdivl(w, 8); return (int)(b < 1 ? 1 : (b > kNumSMs * 4 ? kNumSMs * 4 : b)); };
-#define LN_BWD(VPL, LPR, U) ln_bwd_v4_kernel<VPL, LPR, U><<<grid((32 / LPR) * U), 256, 0, s>>>(dy, lddy, x, in_map, ldx, mean, rstd, gamma, dres, dx, out_map, ldo, dgamma, dbeta, rows, mask, mscale, dxm, round_m)
+#define LN_BWD(VPL, LPR, U) CVT_LAUNCH((ln_bwd_v4_kernel<VPL, LPR, U>), grid((32 / LPR) * U), 256, 0, s, dy, lddy, x, in_map, ldx, mean, rstd, gamma, dres, dx, out_map, ldo, dgamma, dbeta, rows, mask, mscale, dxm, round_m)
   if (D == 64) LN_BWD(1, 16, 4);
   else if (D == 128) LN_BWD(1, 32, 4);
   else if (D == 192) LN_BWD(3, 16, 2);
@@ -204,7 +205,6 @@ cudaError_t launch_ln_bwd_v4(const float* dy, long long lddy, const float* x, Ro
   else if (D == 512) LN_BWD(4, 32, 1);
   else return cudaErrorNotSupported;
 #undef LN_BWD
-  CVT_LAUNCH_CHECK();
   return cudaSuccess;
 }
 

@@ -124,12 +124,15 @@ __global__ void __launch_bounds__(MfCfg<D>::NT, D == 64 ? 2 : 1) mlp_fused_kerne
     tma_prefetch_desc(&tmX); tma_prefetch_desc(&tmW1); tma_prefetch_desc(&tmW2);
     for (int i = 0; i < MB_COUNT; ++i) mbar_init(&bars[i], (i == MB_YF || i == MB_GF || i == MB_GF + 1) ? RW * 32 : 1);
     mbar_fence_init();
-    // the token tile is requested before the CTA has even finished setting up (parameter staging, TMEM allocation overlap its flight)
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, C::TMEM_COLS);
+  pdl_wait(); pdl_trigger();      // everything above touches no global memory
+  if (tid == 0) {
+    // the token tile is requested before the CTA has finished setting up (parameter staging overlaps its flight)
     mbar_arrive_expect_tx(&bars[MB_XF], C::Y_BYTES);
 #pragma unroll
     for (int kb = 0; kb < KB; ++kb) tma_load_3d(sY + kb * 16384, &tmX, &bars[MB_XF], kb * 32, row0, 0);
   }
-  if (warp == 1) tmem_alloc(tmem_slot, C::TMEM_COLS);
   for (int i = tid; i < D; i += NT) { sG[i] = __ldg(p.gamma + i); sBe[i] = __ldg(p.beta + i); sB2[i] = __ldg(p.b2 + i); }
   for (int i = tid; i < p.H4; i += NT) sB1[i] = __ldg(p.b1 + i);
   tc_fence_before();
@@ -350,8 +353,7 @@ cudaError_t launch_cfg(const MlpP& p, const float* w1t, const float* w2t, float*
   if (!make_tmap_3d(&tmW2, w2t, p.H4, D, 1, p.H4, 0, D, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;    // fc2 kernel, K-major copy [D][H4]
   tmY = tmX;
   if (TRAIN && !make_tmap_3d(&tmY, y_out, D, p.R, 1, D, 0, 128, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
-  mlp_fused_kernel<D, MODE><<<cdiv(p.R, 128), C::NT, C::SMEM, s>>>(p, tmX, tmW1, tmW2, tmY);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((mlp_fused_kernel<D, MODE>), cdiv(p.R, 128), C::NT, C::SMEM, s, p, tmX, tmW1, tmW2, tmY);
   return cudaSuccess;
 }
 

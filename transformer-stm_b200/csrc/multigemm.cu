@@ -13,6 +13,7 @@ namespace {
 // contiguous in memory and prefetched into registers while the previous chunk is multiplied out of shared memory.
 // Shapes: K % 8 == 0; a dimension read along its contiguous axis must be a multiple of 4 (all sizes here are 1 or multiples of 64).
 __global__ void __launch_bounds__(256) multigemm_kernel(const MgDesc* __restrict__ descs, int ndesc, int tile_base) {
+  pdl_wait(); pdl_trigger();
   __shared__ __align__(16) float sA[32][68], sB[32][68];
   const int bid = (int)blockIdx.x + tile_base;          // tile0 of the descriptors is absolute; a launch may cover a sub-range of the table
   int d = 0;
@@ -114,8 +115,7 @@ int mg_tiles(const MgDesc& d) { return cdiv(d.M, 64) * cdiv(d.N, 64); }
 
 cudaError_t launch_multigemm(const MgDesc* descs_dev, int ndesc, int total_tiles, cudaStream_t s, int tile_base) {
   if (ndesc < 1 || total_tiles < 1) return cudaSuccess;
-  multigemm_kernel<<<total_tiles, 256, 0, s>>>(descs_dev, ndesc, tile_base);
-  CVT_LAUNCH_CHECK();
+  CVT_LAUNCH((multigemm_kernel), total_tiles, 256, 0, s, descs_dev, ndesc, tile_base);
   return cudaSuccess;
 }
 
