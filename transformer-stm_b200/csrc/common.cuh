@@ -83,6 +83,22 @@ struct RowMap {
 };
 inline RowMap rowmap_none() { return RowMap{0, 0, 0}; }
 
+// descriptor-table lookup of "multi-problem" launches: the last descriptor whose first tile (tile0, ascending) is <= bid.  One warp scans the
+// table with independent loads (a serial scan is a chain of dependent global loads: ~0.3 us each, 10 us for the last entries of a 40-entry table)
+template <typename Desc>
+__device__ __forceinline__ int find_desc(const Desc* __restrict__ descs, int ndesc, int bid) {
+  __shared__ int s_desc;
+  if (threadIdx.x < 32) {
+    int best = 0;
+    for (int i = threadIdx.x; i < ndesc; i += 32)
+      if (bid >= descs[i].tile0) best = i;
+    best = __reduce_max_sync(0xffffffffu, best);
+    if (threadIdx.x == 0) s_desc = best;
+  }
+  __syncthreads();
+  return s_desc;
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -259,9 +259,7 @@ __global__ void __launch_bounds__(256) transpose_weights_kernel(const float* __r
                                                                 const TrDesc* __restrict__ descs, int ndesc, int round) {
   pdl_wait(); pdl_trigger();
   __shared__ float t[32][33];
-  int d = 0;
-  while (d + 1 < ndesc && (int)blockIdx.x >= descs[d + 1].tile0) ++d;
-  const TrDesc e = descs[d];
+  const TrDesc e = descs[find_desc(descs, ndesc, (int)blockIdx.x)];
   const int tile = blockIdx.x - e.tile0, tn = cdiv(e.N, 32);
   const int k0 = (tile / tn) * 32, n0 = (tile % tn) * 32;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;

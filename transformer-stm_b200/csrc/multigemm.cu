@@ -16,9 +16,7 @@ __global__ void __launch_bounds__(256) multigemm_kernel(const MgDesc* __restrict
   pdl_wait(); pdl_trigger();
   __shared__ __align__(16) float sA[32][68], sB[32][68];
   const int bid = (int)blockIdx.x + tile_base;          // tile0 of the descriptors is absolute; a launch may cover a sub-range of the table
-  int d = 0;
-  while (d + 1 < ndesc && bid >= descs[d + 1].tile0) ++d;
-  const MgDesc e = descs[d];
+  const MgDesc e = descs[find_desc(descs, ndesc, bid)];
   const int tile = bid - e.tile0, tn = cdiv(e.N, 64);
   const int m0 = (tile / tn) * 64, n0 = (tile % tn) * 64;
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;      // thread computes rows ty*4.., cols tx*4..
