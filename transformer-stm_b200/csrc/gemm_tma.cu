@@ -36,7 +36,7 @@ template <int BN, bool X3> struct TCfg {
   static constexpr int STAGE_ALL = (A_STAGE + B_STAGE) * (X3 ? 2 : 1);
   static constexpr int SMEM = 1024 + NS * STAGE_ALL + STG_BYTES + (3 * NS + 4) * 8 + 16;
   static_assert(SMEM <= 232448, "gemm_tma: shared memory budget");
-  static constexpr int THREADS = NTHREADS + (X3 ? 32 * NSPLIT : 0);
+  static constexpr int THREADS = NTHREADS + (X3 ? 32 * NSPLIT : 32);      // single-pass kernel: one more warp issues the B operand's TMA loads
 };
 
 template <int BN, uint32_t E, bool X3>
@@ -101,7 +101,7 @@ __global__ void __launch_bounds__(TCfg<BN, X3>::THREADS, 1) gemm_tma_kernel(cons
             tma_load_4d(sA + stage * A_STAGE, &tmA, &full[stage], c0, kw - g.pl, g.s * i0 + kh - g.pt, b0);
           } else
           tma_load_3d(sA + stage * A_STAGE, &tmA, &full[stage], kt * BK, mt * BM, z);
-          tma_load_3d(sB + stage * C::B_STAGE, &tmB, &full[stage], kt * BK, nt * BN, z);
+          if (X3) tma_load_3d(sB + stage * C::B_STAGE, &tmB, &full[stage], kt * BK, nt * BN, z);
           if (++stage == NS) { stage = 0; phase ^= 1; }
         }
         if (itp < 30) GEMM_TRACE(8 + itp * 8 + 1);
@@ -137,6 +137,24 @@ __global__ void __launch_bounds__(TCfg<BN, X3>::THREADS, 1) gemm_tma_kernel(cons
         }
         mma_commit(&acc_full[buf]);
         if (it < 30) GEMM_TRACE(8 + it * 8 + 4);
+      }
+    }
+  } else if (!X3 && warp == 2 + NEPI) {
+    // ===== second TMA producer: the B operand =====
+    // One thread issuing both operands' loads is what bounds the small-K products (K = 64: two k-steps per tile; measured ~450 cycles per
+    // k-step in the single producer against a 128 x 64 tile's ~900 MMA / ~1300 epilogue cycles).  This warp waits on the same empty barrier
+    // and only adds bytes to the full barrier the A producer arms: a complete_tx that lands before that expect_tx leaves the count
+    // transiently negative, which the mbarrier allows; the phase cannot complete before the A producer's arrival.
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int z = tile / (m_tiles * n_tiles), r = tile - z * (m_tiles * n_tiles);
+        const int nt = r % n_tiles;
+        for (int kt = 0; kt < nk; ++kt) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          tma_load_3d(sB + stage * C::B_STAGE, &tmB, &full[stage], kt * BK, nt * BN, z);
+          if (++stage == NS) { stage = 0; phase ^= 1; }
+        }
       }
     }
   } else if (X3 && warp >= 2 + NEPI) {
