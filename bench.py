@@ -57,7 +57,7 @@ class ClockSampler(threading.Thread):
 
     def run(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "200"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             for line in self.proc.stdout:
                 if self.stop_flag:
@@ -302,7 +302,7 @@ class Bench:
         per = [s.elapsed_time(e) for s, e in ev]
         total_ms = self.maxr(sum(per))
         return dict(value=self.world * B * steps / (total_ms / 1e3), ms_per_step=total_ms / steps, launches=int(launches), wall_s=t_wall,
-                    per_step_ms={"min": min(per), "median": float(np.median(per)), "max": max(per)})
+                    per_step_ms={"min": min(per), "median": float(np.median(per)), "max": max(per), "argmax": int(np.argmax(per))})
 
     def e2e(self, train, steps):
         """End to end through the Keras-facing API with ordinary numpy arrays, as the reference scripts hold them (float64 [N,H,W], pageable):
