@@ -587,13 +587,19 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dkv_kernel(const __gr
 // row threads still overlap - S_{j+1} is issued BEFORE the products that consume tile j, the row threads exponentiate S_{j+1} while
 // the tensor core works on those, and only the short dS = P * (dP - D) step sits between dP_j and its consumers.
 // =====================================================================================================================
-// ---- dQ: CTA = 128 query rows, loop over 128-key tiles ---------------------------------------------------------------
-constexpr int Q2_SMEM = 1024 + 2 * TILE32K + 2 * (2 * TILE32K) + TILE32K + 256;      // Q, dO | 2 stages of (K, V) K-major | K MN-major (single)
-enum { Q2_QDO = 0, Q2_KVF = 1, Q2_KVE = 3, Q2_KMF = 5, Q2_KME = 7, Q2_SF = 9, Q2_DPF = 11, Q2_DSF = 12, Q2_DONE = 13, Q2_COUNT = 14 };
+// Both kernels are PERSISTENT: one CTA per SM walks the work items (128-row block, image, head) w = blockIdx.x, + gridDim.x, ...  A CTA of
+// this size spends ~7k cycles outside its steady state (launch, TMEM allocation, barrier set-up, the first 128 KB of operands, the
+// accumulator read-out) against ~18-24k inside; the roles therefore run straight on into the next item - every barrier keeps its phase
+// across items (indexed by the global tile count g = item * ntiles + tile), the producer refills each buffer the moment the item's last
+// product has read it, and the tensor core starts the next item's S / dP while the row threads still store the previous gradients.
+// ---- dQ: work item = 128 query rows, loop over 128-key tiles -----------------------------------------------------------
+constexpr int Q2_SMEM = 1024 + 2 * TILE32K + 2 * (2 * TILE32K) + TILE32K + 256;      // Q, dO | 2 stages of (K, V) K-major | K MN-major (two 64-key sub-tiles)
+enum { Q2_QDO = 0, Q2_QDOE = 1, Q2_KVF = 2, Q2_KVE = 4, Q2_KMF = 6, Q2_KME = 8, Q2_SF = 10, Q2_DPF = 12, Q2_DSF = 13, Q2_DONE = 14, Q2_ACCE = 15, Q2_COUNT = 16 };
 
 __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dq128_kernel(const __grid_constant__ AttnP p, const __grid_constant__ CUtensorMap tmQ,
                                                                          const __grid_constant__ CUtensorMap tmdO, const __grid_constant__ CUtensorMap tmK,
-                                                                         const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmKmn) {
+                                                                         const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmKmn,
+                                                                         int nblk, int nitems) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = align1024(smem_raw);
   uint8_t* sQ = sm; uint8_t* sdO = sQ + TILE32K; uint8_t* sKV = sdO + TILE32K; uint8_t* sKmn = sKV + 4 * TILE32K;
@@ -601,13 +607,11 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dq128_kernel(const __
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + Q2_COUNT);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int bh = blockIdx.y, b = bh / p.heads, h = bh - b * p.heads;
-  const int q0 = blockIdx.x * 128;
   const int ntiles = cdiv(p.Tc, 128);
 
   if (tid == 0) {
     tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmdO); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); tma_prefetch_desc(&tmKmn);
-    for (int i = 0; i < Q2_COUNT; ++i) mbar_init(&bars[i], i == Q2_DSF ? 256 : 1);
+    for (int i = 0; i < Q2_COUNT; ++i) mbar_init(&bars[i], (i == Q2_DSF || i == Q2_ACCE) ? 256 : 1);
     mbar_fence_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, 512);
@@ -619,23 +623,29 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dq128_kernel(const __
 
   if (warp == 0) {
     if (lane == 0) {
-      mbar_arrive_expect_tx(&bars[Q2_QDO], 2 * TILE32K);
-      tma_tile(sQ, &tmQ, &bars[Q2_QDO], h * HD, q0, b, 128);
-      tma_tile(sdO, &tmdO, &bars[Q2_QDO], h * HD, q0, b, 128);
-      auto load_kv = [&](int j) {
-        const int st = j & 1; const uint32_t ph = (j >> 1) & 1;
-        mbar_wait(&bars[Q2_KVE + st], ph ^ 1);
-        mbar_arrive_expect_tx(&bars[Q2_KVF + st], 2 * TILE32K);
-        tma_tile(sKV + st * 2 * TILE32K, &tmK, &bars[Q2_KVF + st], h * HD, j * 128, b, 128);
-        tma_tile(sKV + st * 2 * TILE32K + TILE32K, &tmV, &bars[Q2_KVF + st], h * HD, j * 128, b, 128);
-      };
-      load_kv(0);
-      for (int j = 0; j < ntiles; ++j) {
-        if (j + 1 < ntiles) load_kv(j + 1);              // gated by dP_{j-1}: long done when dQ_{j-1} (the next wait) completes
-        for (int sub = 0; sub < 2; ++sub) {              // the MN-major K tile is two independent 64-key sub-tiles: each is refilled as soon as its 8 products are done
-          mbar_wait(&bars[Q2_KME + sub], (j & 1) ^ 1);
-          mbar_arrive_expect_tx(&bars[Q2_KMF + sub], TILE16K);
-          tma_tile(sKmn + sub * TILE16K, &tmKmn, &bars[Q2_KMF + sub], h * HD, j * 128 + sub * 64, b, 64);
+      int it = 0;
+      for (int w = blockIdx.x; w < nitems; w += gridDim.x, ++it) {
+        const int bh = w / nblk, q0 = (w - bh * nblk) * 128, b = bh / p.heads, h = bh - b * p.heads;
+        const int g0 = it * ntiles;
+        mbar_wait(&bars[Q2_QDOE], (it & 1) ^ 1);         // the previous item's last S / dP product has read Q and dO
+        mbar_arrive_expect_tx(&bars[Q2_QDO], 2 * TILE32K);
+        tma_tile(sQ, &tmQ, &bars[Q2_QDO], h * HD, q0, b, 128);
+        tma_tile(sdO, &tmdO, &bars[Q2_QDO], h * HD, q0, b, 128);
+        auto load_kv = [&](int j) {
+          const int g = g0 + j, st = g & 1; const uint32_t ph = (g >> 1) & 1;
+          mbar_wait(&bars[Q2_KVE + st], ph ^ 1);
+          mbar_arrive_expect_tx(&bars[Q2_KVF + st], 2 * TILE32K);
+          tma_tile(sKV + st * 2 * TILE32K, &tmK, &bars[Q2_KVF + st], h * HD, j * 128, b, 128);
+          tma_tile(sKV + st * 2 * TILE32K + TILE32K, &tmV, &bars[Q2_KVF + st], h * HD, j * 128, b, 128);
+        };
+        load_kv(0);
+        for (int j = 0; j < ntiles; ++j) {
+          if (j + 1 < ntiles) load_kv(j + 1);            // gated by dP_{j-1}: long done when dQ_{j-1} (the next wait) completes
+          for (int sub = 0; sub < 2; ++sub) {            // the MN-major K tile is two independent 64-key sub-tiles: each is refilled as soon as its 8 products are done
+            mbar_wait(&bars[Q2_KME + sub], ((g0 + j) & 1) ^ 1);
+            mbar_arrive_expect_tx(&bars[Q2_KMF + sub], TILE16K);
+            tma_tile(sKmn + sub * TILE16K, &tmKmn, &bars[Q2_KMF + sub], h * HD, j * 128 + sub * 64, b, 64);
+          }
         }
       }
     }
@@ -646,89 +656,102 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dq128_kernel(const __
     const uint64_t dK[2] = {desc_kmajor(smem_u32(sKV)), desc_kmajor(smem_u32(sKV + 2 * TILE32K))};
     const uint64_t dV[2] = {desc_kmajor(smem_u32(sKV + TILE32K)), desc_kmajor(smem_u32(sKV + 3 * TILE32K))};
     const uint64_t dKmn[2] = {desc_mnmajor(smem_u32(sKmn)), desc_mnmajor(smem_u32(sKmn + TILE16K))};
-    mbar_wait(&bars[Q2_QDO], 0);
-    mbar_wait(&bars[Q2_KVF], 0);
-    tc_fence_after();
-    if (elect_one()) {
-      mma_kk<128, 128>(tmem, dQ, dK[0], idesc_s);                               // S_0 = Q K_0^T
-      mma_commit(&bars[Q2_SF]);
-    }
-    __syncwarp();
-    for (int j = 0; j < ntiles; ++j) {
-      const int st = j & 1;
+    int it = 0;
+    for (int w = blockIdx.x; w < nitems; w += gridDim.x, ++it) {
+      const int g0 = it * ntiles;
+      mbar_wait(&bars[Q2_QDO], it & 1);
+      mbar_wait(&bars[Q2_KVF + (g0 & 1)], (g0 >> 1) & 1);
+      tc_fence_after();
       if (elect_one()) {
-        mma_kk<128, 128>(tmem + 256, ddO, dV[st], idesc_s);                     // dP_j = dO V_j^T (after dQ_{j-1}, which read dS_{j-1} from these columns)
-        mma_commit(&bars[Q2_KVE + st]);
-        mma_commit(&bars[Q2_DPF]);
+        mma_kk<128, 128>(tmem + (g0 & 1) * 128, dQ, dK[g0 & 1], idesc_s);       // S_0 = Q K_0^T
+        mma_commit(&bars[Q2_SF + (g0 & 1)]);
       }
       __syncwarp();
-      if (j + 1 < ntiles) {
-        mbar_wait(&bars[Q2_KVF + (st ^ 1)], ((j + 1) >> 1) & 1);
+      for (int j = 0; j < ntiles; ++j) {
+        const int g = g0 + j, st = g & 1;
+        if (elect_one()) {
+          mma_kk<128, 128>(tmem + 256, ddO, dV[st], idesc_s);                   // dP_j = dO V_j^T (after dQ_{j-1}, which read dS_{j-1} from these columns)
+          mma_commit(&bars[Q2_KVE + st]);
+          mma_commit(&bars[Q2_DPF]);
+          if (j + 1 == ntiles) mma_commit(&bars[Q2_QDOE]);                      // the item's last product that reads Q / dO
+        }
+        __syncwarp();
+        if (j + 1 < ntiles) {
+          mbar_wait(&bars[Q2_KVF + (st ^ 1)], ((g + 1) >> 1) & 1);
+          tc_fence_after();
+          if (elect_one()) {
+            mma_kk<128, 128>(tmem + (st ^ 1) * 128, dQ, dK[st ^ 1], idesc_s);   // S_{j+1}
+            mma_commit(&bars[Q2_SF + (st ^ 1)]);
+          }
+          __syncwarp();
+        }
+        mbar_wait(&bars[Q2_DSF], g & 1);
+        if (j == 0 && it > 0) mbar_wait(&bars[Q2_ACCE], (it - 1) & 1);           // the row threads have read the previous item's dQ
+        mbar_wait(&bars[Q2_KMF], g & 1);
         tc_fence_after();
         if (elect_one()) {
-          mma_kk<128, 128>(tmem + (st ^ 1) * 128, dQ, dK[st ^ 1], idesc_s);     // S_{j+1}
-          mma_commit(&bars[Q2_SF + (st ^ 1)]);
+          mma_tmn(tmem + 384, tmem + 256, dKmn[0], idesc_q, j > 0);             // dQ += dS_j K_j (keys 0..63, then 64..127 of the tile)
+          mma_commit(&bars[Q2_KME]);
+        }
+        __syncwarp();
+        mbar_wait(&bars[Q2_KMF + 1], g & 1);
+        tc_fence_after();
+        if (elect_one()) {
+          mma_tmn(tmem + 384, tmem + 256 + 64, dKmn[1], idesc_q, true);
+          mma_commit(&bars[Q2_KME + 1]);
+          if (j == ntiles - 1) mma_commit(&bars[Q2_DONE]);
         }
         __syncwarp();
       }
-      mbar_wait(&bars[Q2_DSF], j & 1);
-      mbar_wait(&bars[Q2_KMF], j & 1);
-      tc_fence_after();
-      if (elect_one()) {
-        mma_tmn(tmem + 384, tmem + 256, dKmn[0], idesc_q, j > 0);               // dQ += dS_j K_j (keys 0..63, then 64..127 of the tile)
-        mma_commit(&bars[Q2_KME]);
-      }
-      __syncwarp();
-      mbar_wait(&bars[Q2_KMF + 1], j & 1);
-      tc_fence_after();
-      if (elect_one()) {
-        mma_tmn(tmem + 384, tmem + 256 + 64, dKmn[1], idesc_q, true);
-        mma_commit(&bars[Q2_KME + 1]);
-        if (j == ntiles - 1) mma_commit(&bars[Q2_DONE]);
-      }
-      __syncwarp();
     }
   } else {
     const int quad = warp & 3, half = (warp - 2) >> 2;
-    const int q = q0 + quad * 32 + lane;
     const uint32_t t_lane = tmem + ((uint32_t)(quad * 32) << 16);
     const uint32_t t_row = t_lane + half * 64;
-    const float lse2 = q < p.Tc ? p.LSE[(long long)bh * p.Tc + q] * kLog2e : 0.f;
-    const float dd = q < p.Tc ? p.Dd[(long long)bh * p.Tc + q] : 0.f;
-    for (int j = 0; j < ntiles; ++j) {
-      const int sb = j & 1;
-      mbar_wait(&bars[Q2_SF + sb], (j >> 1) & 1);
-      tc_fence_after();
-      uint32_t s[64];
-      tmem_ld32_nowait(t_row + sb * 128, s);
-      tmem_ld32_nowait(t_row + sb * 128 + 32, s + 32);
-      tmem_wait_ld();
-#pragma unroll
-      for (int c = 0; c < 64; ++c) s[c] = __float_as_uint(fast_ex2(fmaf(__uint_as_float(s[c]), kLog2e, -lse2)));      // P
-      mbar_wait(&bars[Q2_DPF], j & 1);
-      tc_fence_after();
-#pragma unroll
-      for (int hh = 0; hh < 2; ++hh) {
-        uint32_t dp[32];
-        tmem_ld32_nowait(t_row + 256 + hh * 32, dp);
+    int it = 0;
+    for (int w = blockIdx.x; w < nitems; w += gridDim.x, ++it) {
+      const int bh = w / nblk, q0 = (w - bh * nblk) * 128, b = bh / p.heads, h = bh - b * p.heads;
+      const int g0 = it * ntiles;
+      const int q = q0 + quad * 32 + lane;
+      const float lse2 = q < p.Tc ? p.LSE[(long long)bh * p.Tc + q] * kLog2e : 0.f;
+      const float dd = q < p.Tc ? p.Dd[(long long)bh * p.Tc + q] : 0.f;
+      for (int j = 0; j < ntiles; ++j) {
+        const int g = g0 + j, sb = g & 1;
+        mbar_wait(&bars[Q2_SF + sb], (g >> 1) & 1);
+        tc_fence_after();
+        uint32_t s[64];
+        tmem_ld32_nowait(t_row + sb * 128, s);
+        tmem_ld32_nowait(t_row + sb * 128 + 32, s + 32);
         tmem_wait_ld();
 #pragma unroll
-        for (int c = 0; c < 32; ++c) dp[c] = tf32_rna_bits(__uint_as_float(s[hh * 32 + c]) * (__uint_as_float(dp[c]) - dd));      // dS = P * (dP - D)
-        tmem_st32(t_row + 256 + hh * 32, dp);
-      }
-      tmem_wait_st();
-      tc_fence_before();
-      mbar_arrive(&bars[Q2_DSF]);
-    }
-    mbar_wait(&bars[Q2_DONE], 0);
-    tc_fence_after();
-    uint32_t acc[32];
-    tmem_ld32_nowait(t_lane + 384 + half * 32, acc);
-    tmem_wait_ld();
-    if (q < p.Tc) {
-      float* dst = p.dQ + ((long long)b * p.Tc + q) * p.D + h * HD + half * 32;
+        for (int c = 0; c < 64; ++c) s[c] = __float_as_uint(fast_ex2(fmaf(__uint_as_float(s[c]), kLog2e, -lse2)));      // P
+        mbar_wait(&bars[Q2_DPF], g & 1);
+        tc_fence_after();
 #pragma unroll
-      for (int c = 0; c < 8; ++c) *reinterpret_cast<float4*>(dst + 4 * c) = out4(acc + 4 * c, p.dq_scale, p.round_out);
+        for (int hh = 0; hh < 2; ++hh) {
+          uint32_t dp[32];
+          tmem_ld32_nowait(t_row + 256 + hh * 32, dp);
+          tmem_wait_ld();
+#pragma unroll
+          for (int c = 0; c < 32; ++c) dp[c] = tf32_rna_bits(__uint_as_float(s[hh * 32 + c]) * (__uint_as_float(dp[c]) - dd));      // dS = P * (dP - D)
+          tmem_st32(t_row + 256 + hh * 32, dp);
+        }
+        tmem_wait_st();
+        tc_fence_before();
+        mbar_arrive(&bars[Q2_DSF]);
+      }
+      mbar_wait(&bars[Q2_DONE], it & 1);
+      tc_fence_after();
+      uint32_t acc[32];
+      tmem_ld32_nowait(t_lane + 384 + half * 32, acc);
+      tmem_wait_ld();
+      tc_fence_before();
+      mbar_arrive(&bars[Q2_ACCE]);                       // the accumulator may be overwritten by the next item
+      if (q < p.Tc) {
+        float* dst = p.dQ + ((long long)b * p.Tc + q) * p.D + h * HD + half * 32;
+#pragma unroll
+        for (int c = 0; c < 8; ++c) *reinterpret_cast<float4*>(dst + 4 * c) = out4(acc + 4 * c, p.dq_scale, p.round_out);
+      }
     }
   }
   tc_fence_before();
@@ -736,14 +759,15 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dq128_kernel(const __
   if (warp == 1) tmem_dealloc(tmem, 512);
 }
 
-// ---- dK, dV: CTA = 128 key rows, loop over 128-query tiles; works on S^T ---------------------------------------------
+// ---- dK, dV: work item = 128 key rows, loop over 128-query tiles; works on S^T ---------------------------------------
 constexpr int K2_SMEM = 1024 + 2 * TILE32K + 4 * TILE32K + 256 + 2 * BK_ROWSTAT * 4;      // K, V | Q, dO K-major | Q, dO MN-major (all single-buffered)
-enum { K2_KV = 0, K2_QF = 1, K2_QE = 2, K2_OF = 3, K2_OE = 4, K2_OMF = 5, K2_OME = 7, K2_QMF = 9, K2_QME = 11, K2_SF = 13, K2_DPF = 15, K2_DSF = 16, K2_DONE = 17, K2_COUNT = 18 };
+enum { K2_KV = 0, K2_KVE = 1, K2_QF = 2, K2_QE = 3, K2_OF = 4, K2_OE = 5, K2_OMF = 6, K2_OME = 8, K2_QMF = 10, K2_QME = 12, K2_SF = 14, K2_DPF = 16, K2_DSF = 17,
+       K2_DONE = 18, K2_ACCE = 19, K2_COUNT = 20 };
 
 __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dkv128_kernel(const __grid_constant__ AttnP p, const __grid_constant__ CUtensorMap tmK,
                                                                           const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmQ,
                                                                           const __grid_constant__ CUtensorMap tmdO, const __grid_constant__ CUtensorMap tmQmn,
-                                                                          const __grid_constant__ CUtensorMap tmdOmn) {
+                                                                          const __grid_constant__ CUtensorMap tmdOmn, int nblk, int nitems) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = align1024(smem_raw);
   uint8_t* sK = sm; uint8_t* sV = sK + TILE32K; uint8_t* sQk = sV + TILE32K; uint8_t* sOk = sQk + TILE32K; uint8_t* sQm = sOk + TILE32K; uint8_t* sOm = sQm + TILE32K;
@@ -752,13 +776,11 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dkv128_kernel(const _
   float* s_lse = reinterpret_cast<float*>(sOm + TILE32K + 256); float* s_dd = s_lse + BK_ROWSTAT;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int bh = blockIdx.y, b = bh / p.heads, h = bh - b * p.heads;
-  const int kv0 = blockIdx.x * 128;
   const int ntiles = cdiv(p.Tc, 128);
 
   if (tid == 0) {
     tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmdO); tma_prefetch_desc(&tmQmn); tma_prefetch_desc(&tmdOmn);
-    for (int i = 0; i < K2_COUNT; ++i) mbar_init(&bars[i], i == K2_DSF ? 256 : 1);
+    for (int i = 0; i < K2_COUNT; ++i) mbar_init(&bars[i], (i == K2_DSF || i == K2_ACCE) ? 256 : 1);
     mbar_fence_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, 512);
@@ -770,39 +792,45 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dkv128_kernel(const _
 
   if (warp == 0) {
     if (lane == 0) {
-      mbar_arrive_expect_tx(&bars[K2_KV], 2 * TILE32K);
-      tma_tile(sK, &tmK, &bars[K2_KV], h * HD, kv0, b, 128);
-      tma_tile(sV, &tmV, &bars[K2_KV], h * HD, kv0, b, 128);
-      // every operand tile is single-buffered: the loads are issued in the order their buffers come free on the tensor pipe
-      // (S_0, dP_0, S_1, dV_0 dK_0, dP_1, S_2, dV_1 dK_1, ...)
-      auto load_q = [&](int i) {
-        mbar_wait(&bars[K2_QE], (i & 1) ^ 1);
-        mbar_arrive_expect_tx(&bars[K2_QF], TILE32K);
-        tma_tile(sQk, &tmQ, &bars[K2_QF], h * HD, i * 128, b, 128);
-      };
-      auto load_o = [&](int i) {
-        mbar_wait(&bars[K2_OE], (i & 1) ^ 1);
-        mbar_arrive_expect_tx(&bars[K2_OF], TILE32K);
-        tma_tile(sOk, &tmdO, &bars[K2_OF], h * HD, i * 128, b, 128);
-      };
-      auto load_m = [&](int i) {                         // MN-major tiles: four independent 64-query sub-tiles, each refilled as soon as its 8 products are done
-        for (int sub = 0; sub < 2; ++sub) {
-          mbar_wait(&bars[K2_OME + sub], (i & 1) ^ 1);
-          mbar_arrive_expect_tx(&bars[K2_OMF + sub], TILE16K);
-          tma_tile(sOm + sub * TILE16K, &tmdOmn, &bars[K2_OMF + sub], h * HD, i * 128 + sub * 64, b, 64);
+      int it = 0;
+      for (int w = blockIdx.x; w < nitems; w += gridDim.x, ++it) {
+        const int bh = w / nblk, kv0 = (w - bh * nblk) * 128, b = bh / p.heads, h = bh - b * p.heads;
+        const int g0 = it * ntiles;
+        mbar_wait(&bars[K2_KVE], (it & 1) ^ 1);          // the previous item's last S / dP product has read K and V
+        mbar_arrive_expect_tx(&bars[K2_KV], 2 * TILE32K);
+        tma_tile(sK, &tmK, &bars[K2_KV], h * HD, kv0, b, 128);
+        tma_tile(sV, &tmV, &bars[K2_KV], h * HD, kv0, b, 128);
+        // every operand tile is single-buffered: the loads are issued in the order their buffers come free on the tensor pipe
+        // (S_0, dP_0, S_1, dV_0 dK_0, dP_1, S_2, dV_1 dK_1, ...)
+        auto load_q = [&](int i) {
+          mbar_wait(&bars[K2_QE], ((g0 + i) & 1) ^ 1);
+          mbar_arrive_expect_tx(&bars[K2_QF], TILE32K);
+          tma_tile(sQk, &tmQ, &bars[K2_QF], h * HD, i * 128, b, 128);
+        };
+        auto load_o = [&](int i) {
+          mbar_wait(&bars[K2_OE], ((g0 + i) & 1) ^ 1);
+          mbar_arrive_expect_tx(&bars[K2_OF], TILE32K);
+          tma_tile(sOk, &tmdO, &bars[K2_OF], h * HD, i * 128, b, 128);
+        };
+        auto load_m = [&](int i) {                       // MN-major tiles: four independent 64-query sub-tiles, each refilled as soon as its 8 products are done
+          for (int sub = 0; sub < 2; ++sub) {
+            mbar_wait(&bars[K2_OME + sub], ((g0 + i) & 1) ^ 1);
+            mbar_arrive_expect_tx(&bars[K2_OMF + sub], TILE16K);
+            tma_tile(sOm + sub * TILE16K, &tmdOmn, &bars[K2_OMF + sub], h * HD, i * 128 + sub * 64, b, 64);
+          }
+          for (int sub = 0; sub < 2; ++sub) {
+            mbar_wait(&bars[K2_QME + sub], ((g0 + i) & 1) ^ 1);
+            mbar_arrive_expect_tx(&bars[K2_QMF + sub], TILE16K);
+            tma_tile(sQm + sub * TILE16K, &tmQmn, &bars[K2_QMF + sub], h * HD, i * 128 + sub * 64, b, 64);
+          }
+        };
+        load_q(0); load_o(0); load_m(0);
+        if (ntiles > 1) load_q(1);
+        for (int i = 1; i < ntiles; ++i) {
+          load_o(i);                                     // after dP_{i-1}
+          if (i + 1 < ntiles) load_q(i + 1);             // after S_i
+          load_m(i);                                     // after dV_{i-1}, then dK_{i-1}
         }
-        for (int sub = 0; sub < 2; ++sub) {
-          mbar_wait(&bars[K2_QME + sub], (i & 1) ^ 1);
-          mbar_arrive_expect_tx(&bars[K2_QMF + sub], TILE16K);
-          tma_tile(sQm + sub * TILE16K, &tmQmn, &bars[K2_QMF + sub], h * HD, i * 128 + sub * 64, b, 64);
-        }
-      };
-      load_q(0); load_o(0); load_m(0);
-      if (ntiles > 1) load_q(1);
-      for (int i = 1; i < ntiles; ++i) {
-        load_o(i);                                       // after dP_{i-1}
-        if (i + 1 < ntiles) load_q(i + 1);               // after S_i
-        load_m(i);                                       // after dV_{i-1}, then dK_{i-1}
       }
     }
   } else if (warp == 1) {
@@ -812,141 +840,153 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dkv128_kernel(const _
     const uint64_t dQk = desc_kmajor(smem_u32(sQk)), dOk = desc_kmajor(smem_u32(sOk));
     const uint64_t dQm[2] = {desc_mnmajor(smem_u32(sQm)), desc_mnmajor(smem_u32(sQm + TILE16K))};
     const uint64_t dOm[2] = {desc_mnmajor(smem_u32(sOm)), desc_mnmajor(smem_u32(sOm + TILE16K))};
-    mbar_wait(&bars[K2_KV], 0);
-    mbar_wait(&bars[K2_QF], 0);
-    tc_fence_after();
-    if (elect_one()) {
-      mma_kk<128, 128>(tmem, dK, dQk, idesc_s);                                 // S^T_0 = K Q_0^T
-      mma_commit(&bars[K2_QE]);
-      mma_commit(&bars[K2_SF]);
-    }
-    __syncwarp();
-    for (int i = 0; i < ntiles; ++i) {
-      const int sb = i & 1;
-      mbar_wait(&bars[K2_OF], i & 1);
+    int it = 0;
+    for (int w = blockIdx.x; w < nitems; w += gridDim.x, ++it) {
+      const int g0 = it * ntiles;
+      mbar_wait(&bars[K2_KV], it & 1);
+      mbar_wait(&bars[K2_QF], g0 & 1);
       tc_fence_after();
       if (elect_one()) {
-        mma_kk<128, 128>(tmem + 256, dV, dOk, idesc_s);                         // dP^T_i = V dO_i^T (after dK_{i-1}, which read dS^T_{i-1} from these columns)
-        mma_commit(&bars[K2_OE]);
-        mma_commit(&bars[K2_DPF]);
+        mma_kk<128, 128>(tmem + (g0 & 1) * 128, dK, dQk, idesc_s);              // S^T_0 = K Q_0^T
+        mma_commit(&bars[K2_QE]);
+        mma_commit(&bars[K2_SF + (g0 & 1)]);
       }
       __syncwarp();
-      if (i + 1 < ntiles) {
-        mbar_wait(&bars[K2_QF], (i + 1) & 1);
+      for (int i = 0; i < ntiles; ++i) {
+        const int g = g0 + i, sb = g & 1;
+        mbar_wait(&bars[K2_OF], g & 1);
         tc_fence_after();
         if (elect_one()) {
-          mma_kk<128, 128>(tmem + (sb ^ 1) * 128, dK, dQk, idesc_s);            // S^T_{i+1}
-          mma_commit(&bars[K2_QE]);
-          mma_commit(&bars[K2_SF + (sb ^ 1)]);
+          mma_kk<128, 128>(tmem + 256, dV, dOk, idesc_s);                       // dP^T_i = V dO_i^T (after dK_{i-1}, which read dS^T_{i-1} from these columns)
+          mma_commit(&bars[K2_OE]);
+          mma_commit(&bars[K2_DPF]);
+          if (i + 1 == ntiles) mma_commit(&bars[K2_KVE]);                       // the item's last product that reads K / V
         }
         __syncwarp();
-      }
-      mbar_wait(&bars[K2_DSF], i & 1);
+        if (i + 1 < ntiles) {
+          mbar_wait(&bars[K2_QF], (g + 1) & 1);
+          tc_fence_after();
+          if (elect_one()) {
+            mma_kk<128, 128>(tmem + (sb ^ 1) * 128, dK, dQk, idesc_s);          // S^T_{i+1}
+            mma_commit(&bars[K2_QE]);
+            mma_commit(&bars[K2_SF + (sb ^ 1)]);
+          }
+          __syncwarp();
+        }
+        mbar_wait(&bars[K2_DSF], g & 1);
+        if (i == 0 && it > 0) mbar_wait(&bars[K2_ACCE], (it - 1) & 1);           // the row threads have read the previous item's dV, dK
 #pragma unroll
-      for (int sub = 0; sub < 2; ++sub) {                                        // dV += P^T dO
-        mbar_wait(&bars[K2_OMF + sub], i & 1);
-        tc_fence_after();
-        if (elect_one()) {
-          mma_tmn(tmem + 384, tmem + sb * 128 + sub * 64, dOm[sub], idesc_t, i > 0 || sub > 0);
-          mma_commit(&bars[K2_OME + sub]);
+        for (int sub = 0; sub < 2; ++sub) {                                      // dV += P^T dO
+          mbar_wait(&bars[K2_OMF + sub], g & 1);
+          tc_fence_after();
+          if (elect_one()) {
+            mma_tmn(tmem + 384, tmem + sb * 128 + sub * 64, dOm[sub], idesc_t, i > 0 || sub > 0);
+            mma_commit(&bars[K2_OME + sub]);
+          }
+          __syncwarp();
         }
-        __syncwarp();
-      }
 #pragma unroll
-      for (int sub = 0; sub < 2; ++sub) {                                        // dK += dS^T Q
-        mbar_wait(&bars[K2_QMF + sub], i & 1);
-        tc_fence_after();
-        if (elect_one()) {
-          mma_tmn(tmem + 448, tmem + 256 + sub * 64, dQm[sub], idesc_t, i > 0 || sub > 0);
-          mma_commit(&bars[K2_QME + sub]);
-          if (i == ntiles - 1 && sub == 1) mma_commit(&bars[K2_DONE]);
+        for (int sub = 0; sub < 2; ++sub) {                                      // dK += dS^T Q
+          mbar_wait(&bars[K2_QMF + sub], g & 1);
+          tc_fence_after();
+          if (elect_one()) {
+            mma_tmn(tmem + 448, tmem + 256 + sub * 64, dQm[sub], idesc_t, i > 0 || sub > 0);
+            mma_commit(&bars[K2_QME + sub]);
+            if (i == ntiles - 1 && sub == 1) mma_commit(&bars[K2_DONE]);
+          }
+          __syncwarp();
         }
-        __syncwarp();
       }
     }
   } else {
     const int quad = warp & 3, half = (warp - 2) >> 2;
-    const int kv = kv0 + quad * 32 + lane;
     const uint32_t t_lane = tmem + ((uint32_t)(quad * 32) << 16);
     const uint32_t t_row = t_lane + half * 64;
-    const float* LSE = p.LSE + (long long)bh * p.Tc; const float* Dd = p.Dd + (long long)bh * p.Tc;
     const bool staged = ntiles * 128 <= BK_ROWSTAT;
-    if (staged) {                                        // LSE * log2(e) and D of every query of this (image, head), zero past Tc
-      for (int t = tid - 64; t < ntiles * 128; t += BWD_THREADS - 64) {
-        const bool ok = t < p.Tc;
-        s_lse[t] = ok ? __ldg(LSE + t) * kLog2e : 0.f; s_dd[t] = ok ? __ldg(Dd + t) : 0.f;
-      }
-      asm volatile("bar.sync 1, 256;" ::: "memory");     // the 8 row warps only
-    }
-    for (int i = 0; i < ntiles; ++i) {
-      const int sb = i & 1;
-      int qc = i * 128 + half * 64;                      // this thread's 64 tile columns are queries qc .. qc + 63 (warp-uniform shared-memory addresses)
-      if (!staged) {                                     // long sequences: the tile's 128 statistics are staged tile by tile (two alternating slots; one code path below -
-        const int t = tid - 64, slot = sb * 128;         // the kernel has to stay inside the instruction cache)
-        const int qq = i * 128 + (t & 127); const bool ok = qq < p.Tc;
-        if (t < 128) s_lse[slot + t] = ok ? __ldg(LSE + qq) * kLog2e : 0.f;
-        else s_dd[slot + t - 128] = ok ? __ldg(Dd + qq) : 0.f;
-        asm volatile("bar.sync 1, 256;" ::: "memory");
-        qc = slot + half * 64;
-      }
-      mbar_wait(&bars[K2_SF + sb], (i >> 1) & 1);
-      tc_fence_after();
-      uint32_t s[64];
-      tmem_ld32_nowait(t_row + sb * 128, s);
-      tmem_ld32_nowait(t_row + sb * 128 + 32, s + 32);
-      tmem_wait_ld();
-#pragma unroll
-      for (int hh = 0; hh < 2; ++hh) {
-        uint32_t pr[32];
-#pragma unroll
-        for (int c4 = 0; c4 < 8; ++c4) {
-          const int c = hh * 32 + 4 * c4;
-          const float4 l4 = *reinterpret_cast<const float4*>(s_lse + qc + c);
-          const float p0 = fast_ex2(fmaf(__uint_as_float(s[c]), kLog2e, -l4.x)), p1 = fast_ex2(fmaf(__uint_as_float(s[c + 1]), kLog2e, -l4.y));
-          const float p2 = fast_ex2(fmaf(__uint_as_float(s[c + 2]), kLog2e, -l4.z)), p3 = fast_ex2(fmaf(__uint_as_float(s[c + 3]), kLog2e, -l4.w));
-          s[c] = __float_as_uint(p0); s[c + 1] = __float_as_uint(p1); s[c + 2] = __float_as_uint(p2); s[c + 3] = __float_as_uint(p3);
-          pr[4 * c4] = tf32_rna_bits(p0); pr[4 * c4 + 1] = tf32_rna_bits(p1); pr[4 * c4 + 2] = tf32_rna_bits(p2); pr[4 * c4 + 3] = tf32_rna_bits(p3);
+    int it = 0, staged_bh = -1;
+    for (int w = blockIdx.x; w < nitems; w += gridDim.x, ++it) {
+      const int bh = w / nblk, kv0 = (w - bh * nblk) * 128, b = bh / p.heads, h = bh - b * p.heads;
+      const int g0 = it * ntiles;
+      const int kv = kv0 + quad * 32 + lane;
+      const float* LSE = p.LSE + (long long)bh * p.Tc; const float* Dd = p.Dd + (long long)bh * p.Tc;
+      if (staged && bh != staged_bh) {                   // LSE * log2(e) and D of every query of this (image, head), zero past Tc
+        asm volatile("bar.sync 1, 256;" ::: "memory");   // (every row warp is done with the previous head's statistics)
+        for (int t = tid - 64; t < ntiles * 128; t += BWD_THREADS - 64) {
+          const bool ok = t < p.Tc;
+          s_lse[t] = ok ? __ldg(LSE + t) * kLog2e : 0.f; s_dd[t] = ok ? __ldg(Dd + t) : 0.f;
         }
-        tmem_st32(t_row + sb * 128 + hh * 32, pr);       // P^T (the A operand of the dV product)
+        asm volatile("bar.sync 1, 256;" ::: "memory");   // the 8 row warps only
+        staged_bh = bh;
       }
-      mbar_wait(&bars[K2_DPF], i & 1);
-      tc_fence_after();
-#pragma unroll
-      for (int hh = 0; hh < 2; ++hh) {
-        uint32_t dp[32];
-        tmem_ld32_nowait(t_row + 256 + hh * 32, dp);
+      for (int i = 0; i < ntiles; ++i) {
+        const int g = g0 + i, sb = g & 1;
+        int qc = i * 128 + half * 64;                    // this thread's 64 tile columns are queries qc .. qc + 63 (warp-uniform shared-memory addresses)
+        if (!staged) {                                   // long sequences: the tile's 128 statistics are staged tile by tile (two alternating slots; one code path below -
+          const int t = tid - 64, slot = sb * 128;       // the kernel has to stay inside the instruction cache)
+          const int qq = i * 128 + (t & 127); const bool ok = qq < p.Tc;
+          if (t < 128) s_lse[slot + t] = ok ? __ldg(LSE + qq) * kLog2e : 0.f;
+          else s_dd[slot + t - 128] = ok ? __ldg(Dd + qq) : 0.f;
+          asm volatile("bar.sync 1, 256;" ::: "memory");
+          qc = slot + half * 64;
+        }
+        mbar_wait(&bars[K2_SF + sb], (g >> 1) & 1);
+        tc_fence_after();
+        uint32_t s[64];
+        tmem_ld32_nowait(t_row + sb * 128, s);
+        tmem_ld32_nowait(t_row + sb * 128 + 32, s + 32);
         tmem_wait_ld();
 #pragma unroll
-        for (int c4 = 0; c4 < 8; ++c4) {
-          const int c = hh * 32 + 4 * c4;
-          const float4 d4 = *reinterpret_cast<const float4*>(s_dd + qc + c);
-          dp[4 * c4] = tf32_rna_bits(__uint_as_float(s[c]) * (__uint_as_float(dp[4 * c4]) - d4.x));
-          dp[4 * c4 + 1] = tf32_rna_bits(__uint_as_float(s[c + 1]) * (__uint_as_float(dp[4 * c4 + 1]) - d4.y));
-          dp[4 * c4 + 2] = tf32_rna_bits(__uint_as_float(s[c + 2]) * (__uint_as_float(dp[4 * c4 + 2]) - d4.z));
-          dp[4 * c4 + 3] = tf32_rna_bits(__uint_as_float(s[c + 3]) * (__uint_as_float(dp[4 * c4 + 3]) - d4.w));
+        for (int hh = 0; hh < 2; ++hh) {
+          uint32_t pr[32];
+#pragma unroll
+          for (int c4 = 0; c4 < 8; ++c4) {
+            const int c = hh * 32 + 4 * c4;
+            const float4 l4 = *reinterpret_cast<const float4*>(s_lse + qc + c);
+            const float p0 = fast_ex2(fmaf(__uint_as_float(s[c]), kLog2e, -l4.x)), p1 = fast_ex2(fmaf(__uint_as_float(s[c + 1]), kLog2e, -l4.y));
+            const float p2 = fast_ex2(fmaf(__uint_as_float(s[c + 2]), kLog2e, -l4.z)), p3 = fast_ex2(fmaf(__uint_as_float(s[c + 3]), kLog2e, -l4.w));
+            s[c] = __float_as_uint(p0); s[c + 1] = __float_as_uint(p1); s[c + 2] = __float_as_uint(p2); s[c + 3] = __float_as_uint(p3);
+            pr[4 * c4] = tf32_rna_bits(p0); pr[4 * c4 + 1] = tf32_rna_bits(p1); pr[4 * c4 + 2] = tf32_rna_bits(p2); pr[4 * c4 + 3] = tf32_rna_bits(p3);
+          }
+          tmem_st32(t_row + sb * 128 + hh * 32, pr);     // P^T (the A operand of the dV product)
         }
-        tmem_st32(t_row + 256 + hh * 32, dp);            // dS^T (the A operand of the dK product)
+        mbar_wait(&bars[K2_DPF], g & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          uint32_t dp[32];
+          tmem_ld32_nowait(t_row + 256 + hh * 32, dp);
+          tmem_wait_ld();
+#pragma unroll
+          for (int c4 = 0; c4 < 8; ++c4) {
+            const int c = hh * 32 + 4 * c4;
+            const float4 d4 = *reinterpret_cast<const float4*>(s_dd + qc + c);
+            dp[4 * c4] = tf32_rna_bits(__uint_as_float(s[c]) * (__uint_as_float(dp[4 * c4]) - d4.x));
+            dp[4 * c4 + 1] = tf32_rna_bits(__uint_as_float(s[c + 1]) * (__uint_as_float(dp[4 * c4 + 1]) - d4.y));
+            dp[4 * c4 + 2] = tf32_rna_bits(__uint_as_float(s[c + 2]) * (__uint_as_float(dp[4 * c4 + 2]) - d4.z));
+            dp[4 * c4 + 3] = tf32_rna_bits(__uint_as_float(s[c + 3]) * (__uint_as_float(dp[4 * c4 + 3]) - d4.w));
+          }
+          tmem_st32(t_row + 256 + hh * 32, dp);          // dS^T (the A operand of the dK product)
+        }
+        tmem_wait_st();
+        tc_fence_before();
+        mbar_arrive(&bars[K2_DSF]);
       }
-      tmem_wait_st();
+      mbar_wait(&bars[K2_DONE], it & 1);
+      tc_fence_after();
+      uint32_t accv[32], acck[32];
+      tmem_ld32_nowait(t_lane + 384 + half * 32, accv);
+      tmem_ld32_nowait(t_lane + 448 + half * 32, acck);
+      tmem_wait_ld();
       tc_fence_before();
-      mbar_arrive(&bars[K2_DSF]);
-    }
-    mbar_wait(&bars[K2_DONE], 0);
-    tc_fence_after();
-    uint32_t acc[32];
-    tmem_ld32_nowait(t_lane + 384 + half * 32, acc);
-    tmem_wait_ld();
-    if (kv < p.Tc) {
-      float* dst = p.dV + ((long long)b * p.Tc + kv) * p.D + h * HD + half * 32;
+      mbar_arrive(&bars[K2_ACCE]);                       // the accumulators may be overwritten by the next item
+      if (kv < p.Tc) {
+        float* dv = p.dV + ((long long)b * p.Tc + kv) * p.D + h * HD + half * 32;
+        float* dk = p.dK + ((long long)b * p.Tc + kv) * p.D + h * HD + half * 32;
 #pragma unroll
-      for (int c = 0; c < 8; ++c) *reinterpret_cast<float4*>(dst + 4 * c) = out4(acc + 4 * c, 1.f, p.round_out);
-    }
-    tmem_ld32_nowait(t_lane + 448 + half * 32, acc);
-    tmem_wait_ld();
-    if (kv < p.Tc) {
-      float* dst = p.dK + ((long long)b * p.Tc + kv) * p.D + h * HD + half * 32;
+        for (int c = 0; c < 8; ++c) *reinterpret_cast<float4*>(dv + 4 * c) = out4(accv + 4 * c, 1.f, p.round_out);
 #pragma unroll
-      for (int c = 0; c < 8; ++c) *reinterpret_cast<float4*>(dst + 4 * c) = out4(acc + 4 * c, 1.f, p.round_out);
+        for (int c = 0; c < 8; ++c) *reinterpret_cast<float4*>(dk + 4 * c) = out4(acck + 4 * c, 1.f, p.round_out);
+      }
     }
   }
   tc_fence_before();
@@ -1008,9 +1048,12 @@ cudaError_t run_bwd(const AttnP& p, float* Dd, int B, cudaStream_t s, cudaStream
   static const int force = getenv("CVT_ATTN_BWD_TILE") ? atoi(getenv("CVT_ATTN_BWD_TILE")) : 0;
   const bool wide = force == 128 || (force != 64 && p.Tc > 128 && !p.trace);
   const bool wide_dkv = wide;
-  if (wide_dkv) { CVT_LAUNCH((attn_bwd_dkv128_kernel), grid, BWD_THREADS, K2_SMEM, s, p, k128, v128, q128, do128, qmn, domn); }
+  // the wide kernels are persistent (one CTA per SM walking 128-row work items, w = blockIdx.x, + gridDim.x, ...).  Side by side still pays: the
+  // CTAs of the first grid that drew one item less exit early, and the second grid's lowest-numbered CTAs (one item more) start there
+  const int nblk = cdiv(p.Tc, 128), nitems = nblk * B * p.heads, pgrid = nitems < kNumSMs ? nitems : kNumSMs;
+  if (wide_dkv) { CVT_LAUNCH((attn_bwd_dkv128_kernel), pgrid, BWD_THREADS, K2_SMEM, s, p, k128, v128, q128, do128, qmn, domn, nblk, nitems); }
   else { CVT_LAUNCH((attn_bwd_dkv_kernel), grid, BWD_THREADS, BK_SMEM, s, p, k128, v128, q64, do64, qmn, domn); }
-  if (wide) { CVT_LAUNCH((attn_bwd_dq128_kernel), grid, BWD_THREADS, Q2_SMEM, fork ? side : s, p, q128, do128, k128, v128, kmn); }
+  if (wide) { CVT_LAUNCH((attn_bwd_dq128_kernel), pgrid, BWD_THREADS, Q2_SMEM, fork ? side : s, p, q128, do128, k128, v128, kmn, nblk, nitems); }
   else { CVT_LAUNCH((attn_bwd_dq_kernel), grid, BWD_THREADS, BQ_SMEM, fork ? side : s, p, q128, do128, k64, v64, kmn); }
   if (fork) { CVT_CUDA(cudaEventRecord(ev_join, side)); CVT_CUDA(cudaStreamWaitEvent(s, ev_join, 0)); }
   return cudaSuccess;
