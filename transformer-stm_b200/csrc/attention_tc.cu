@@ -708,13 +708,24 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dq128_kernel(const __
     const int quad = warp & 3, half = (warp - 2) >> 2;
     const uint32_t t_lane = tmem + ((uint32_t)(quad * 32) << 16);
     const uint32_t t_row = t_lane + half * 64;
+    // The finished rows of an item leave one float4 per tile of the NEXT item: written in one burst after the accumulator read-out they held the
+    // row threads for ~3.8k cycles (32 half-filled sectors per instruction) exactly while the tensor core waited for the next item's first dS.
+    float4 pend[8];
+    float* pend_dst = nullptr;
+    const int cpt = cdiv(8, ntiles);                     // pending float4 chunks stored per tile
+    auto row_stats = [&](int w, float& lse2, float& dd) {
+      const int bh = w / nblk, q = (w - bh * nblk) * 128 + quad * 32 + lane;
+      const bool ok = w < nitems && q < p.Tc;
+      lse2 = ok ? __ldg(p.LSE + (long long)bh * p.Tc + q) * kLog2e : 0.f;
+      dd = ok ? __ldg(p.Dd + (long long)bh * p.Tc + q) : 0.f;
+    };
+    float lse2, dd;
+    row_stats(blockIdx.x, lse2, dd);
     int it = 0;
     for (int w = blockIdx.x; w < nitems; w += gridDim.x, ++it) {
       const int bh = w / nblk, q0 = (w - bh * nblk) * 128, b = bh / p.heads, h = bh - b * p.heads;
       const int g0 = it * ntiles;
       const int q = q0 + quad * 32 + lane;
-      const float lse2 = q < p.Tc ? p.LSE[(long long)bh * p.Tc + q] * kLog2e : 0.f;
-      const float dd = q < p.Tc ? p.Dd[(long long)bh * p.Tc + q] : 0.f;
       for (int j = 0; j < ntiles; ++j) {
         const int g = g0 + j, sb = g & 1;
         mbar_wait(&bars[Q2_SF + sb], (g >> 1) & 1);
@@ -739,7 +750,14 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dq128_kernel(const __
         tmem_wait_st();
         tc_fence_before();
         mbar_arrive(&bars[Q2_DSF]);
+        if (pend_dst) {
+#pragma unroll
+          for (int c = 0; c < 8; ++c)
+            if (c / cpt == j) *reinterpret_cast<float4*>(pend_dst + 4 * c) = pend[c];
+        }
       }
+      float lse2n, ddn;
+      row_stats(w + gridDim.x, lse2n, ddn);              // the next item's row statistics, fetched under the last dQ product
       mbar_wait(&bars[Q2_DONE], it & 1);
       tc_fence_after();
       uint32_t acc[32];
@@ -747,11 +765,14 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dq128_kernel(const __
       tmem_wait_ld();
       tc_fence_before();
       mbar_arrive(&bars[Q2_ACCE]);                       // the accumulator may be overwritten by the next item
-      if (q < p.Tc) {
-        float* dst = p.dQ + ((long long)b * p.Tc + q) * p.D + h * HD + half * 32;
 #pragma unroll
-        for (int c = 0; c < 8; ++c) *reinterpret_cast<float4*>(dst + 4 * c) = out4(acc + 4 * c, p.dq_scale, p.round_out);
-      }
+      for (int c = 0; c < 8; ++c) pend[c] = out4(acc + 4 * c, p.dq_scale, p.round_out);
+      pend_dst = q < p.Tc ? p.dQ + ((long long)b * p.Tc + q) * p.D + h * HD + half * 32 : nullptr;
+      lse2 = lse2n; dd = ddn;
+    }
+    if (pend_dst) {
+#pragma unroll
+      for (int c = 0; c < 8; ++c) *reinterpret_cast<float4*>(pend_dst + 4 * c) = pend[c];
     }
   }
   tc_fence_before();
