@@ -34,9 +34,14 @@ CONFIGS = {
     "cfg1": ("CvT(Img) forward inference, batch 32, 128x128x1 (configs[0])", (128, 128), (64, 128, 256), (1, 2, 4), 0, 32, ("infer",)),
     "cfg2": ("CvT(Par) train step + batch inference, batch 64 per GPU, 128x128x1 + 5 process parameters (configs[1]), dw_bn, cls on stage 3",
              (128, 128), (64, 128, 256), (1, 2, 4), 5, 64, ("train", "infer")),
+    "cfg3": ("CvT(Par)(many): the same network with a multi-target regression head (num_classes = 20; num_classes = 1 is cfg2), data-parallel training, "
+             "batch 64 per GPU (configs[2]; run with --gpus 8 for the 8 x B200 line)", (128, 128), (64, 128, 256), (1, 2, 4), 5, 64, ("train", "infer")),
     "cfg5": ("widened CvT(Par) (configs[4] geometry: 340x345 input, dims 64/192/384, heads 1/3/6), TF32 (bf16 mode is not implemented)",
              (340, 345), (64, 192, 384), (1, 3, 6), 5, 8, ("train", "infer")),
 }
+
+
+NUM_CLASSES = {"cfg3": 20}                                # every other configuration: 1 (models/CvT(Par).py:388)
 
 
 def load_peaks():
@@ -172,7 +177,7 @@ def cpu_reference_run(steps, warmup, batch, mode, cfgname="cfg2", budget_s=120.0
     import torch
     from oracle import cvt_oracle as O
     torch.set_num_threads(cores)
-    spec = O.ref_spec(proc_dim=proc_dim, image_h=hw[0], image_w=hw[1], dims=dims, heads=heads)
+    spec = O.ref_spec(proc_dim=proc_dim, image_h=hw[0], image_w=hw[1], dims=dims, heads=heads, num_classes=NUM_CLASSES.get(cfgname, 1))
     params = O.init_params(spec, 1234, "keras")
     img, proc, y = O.synthetic_batch(spec, batch, 0)
     st = O.new_opt_state(params)
@@ -234,7 +239,8 @@ class Bench:
             if not dist.is_initialized():
                 dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
             self.dist = dist
-        self.cfg = T.CvtConfig.reference(precision=a.precision, max_batch=batch, device=self.local, proc_dim=self.proc_dim,
+        self.nc = NUM_CLASSES.get(cfgname, 1)
+        self.cfg = T.CvtConfig.reference(precision=a.precision, max_batch=batch, device=self.local, proc_dim=self.proc_dim, num_classes=self.nc,
                                          image_h=self.hw[0], image_w=self.hw[1], dims=self.dims, heads=self.heads)
         self.eng = T.CvtEngine(self.cfg)
         self.eng.init_params(1234)                                   # Keras initialisers, random-init weights
@@ -247,7 +253,7 @@ class Bench:
         H, W = self.hw
         self.imgs = [torch.rand((batch, H, W, 1), device="cuda", generator=g) for _ in range(NB)]
         self.procs = [torch.randn((batch, max(self.proc_dim, 1)), device="cuda", generator=g) for _ in range(NB)] if self.proc_dim else [None] * NB
-        self.ys = [1000.0 + 100.0 * torch.randn((batch, 1), device="cuda", generator=g) for _ in range(NB)]
+        self.ys = [1000.0 + 100.0 * torch.randn((batch, self.nc), device="cuda", generator=g) for _ in range(NB)]
         self.NB = NB
         self.flush = None if a.no_flush else torch.empty(256 << 20, dtype=torch.uint8, device="cuda")      # > 126 MB L2
         self.stream = torch.cuda.ExternalStream(self.eng.stream())
@@ -317,7 +323,7 @@ class Bench:
         steps = max(2, min(max(steps, 64), (1 << 30) // (B * H * W * 8)))      # at most 1 GiB of float64 images on the host (batch sweep)
         n = steps * B
         rng = np.random.default_rng(100 + self.rank)
-        x64 = rng.random((n, H, W)); p64 = rng.standard_normal((n, max(self.proc_dim, 1))); y64 = 1000.0 + 100.0 * rng.standard_normal(n)
+        x64 = rng.random((n, H, W)); p64 = rng.standard_normal((n, max(self.proc_dim, 1))); y64 = 1000.0 + 100.0 * rng.standard_normal(n if self.nc == 1 else (n, self.nc))
         model = K.Model(self.cfg, engine_factory=lambda cfg: self.eng, seed=5)
         model.compile(optimizer=K.Adam(1e-3), loss="mean_squared_error", metrics=["mae"])
         out = {}
@@ -341,7 +347,7 @@ class Bench:
             out[tag] = float(np.median(reps))
             out[tag + "_reps"] = [round(v, 1) for v in reps]
         elem = 8
-        h2d = B * (H * W * elem + self.proc_dim * 4 + (4 if train else 0)); d2h = 8 if train else B * 4
+        h2d = B * (H * W * elem + self.proc_dim * 4 + (4 * self.nc if train else 0)); d2h = 8 if train else B * 4 * self.nc
         return {"value": out["f64"], "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "api": "keras_api.Model.fit(epochs=1, shuffle=True)" if train else "keras_api.Model.predict", "inputs": "float64 numpy, pageable",
                 "samples_per_epoch": n, "protocol": "3 timed calls of %d batches each, median; all three in `repeats`" % steps, "repeats": out["f64_reps"],
@@ -393,7 +399,7 @@ class Bench:
         from oracle import cvt_oracle as O          # checker only
         import torch
         eng, B = self.eng, self.B
-        spec = O.ref_spec(proc_dim=self.proc_dim, image_h=self.hw[0], image_w=self.hw[1], dims=self.dims, heads=self.heads)
+        spec = O.ref_spec(proc_dim=self.proc_dim, image_h=self.hw[0], image_w=self.hw[1], dims=self.dims, heads=self.heads, num_classes=self.nc)
         params = {k: v.astype(np.float64) for k, v in eng.get_params().items()}
         img = self.imgs[0].cpu().numpy(); proc = self.procs[0].cpu().numpy() if self.proc_dim else None; y = self.ys[0].cpu().numpy()
         eng.set_dropout("off")

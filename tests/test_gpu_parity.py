@@ -45,6 +45,7 @@ def test_param_table_matches_oracle():
     ("avg", True, 5, 3, (32, 32)),
     ("linear", False, 5, 1, (32, 32)),
     ("dw_bn", True, 5, 1, (36, 44)),          # ragged maps: 9x11 / 5x6 / 3x3, odd SAME pads
+    ("dw_bn", True, 5, 20, (32, 32)),         # the multi-target head of bench.py's cfg3 (CvT(Par)(many) read as 20 regression targets)
 ])
 def test_inference_forward_taps(method, cls, proc_dim, nc, hw):
     spec, eng, params, img, proc, y = make_pair(method, cls, proc_dim, nc, hw, batch=3)
@@ -62,6 +63,7 @@ def test_inference_forward_taps(method, cls, proc_dim, nc, hw):
     ("avg", False, 5, 1, (32, 32), 3),
     ("linear", True, 5, 1, (32, 32), 3),
     ("dw_bn", True, 5, 1, (36, 44), 2),
+    ("dw_bn", True, 5, 20, (32, 32), 3),
 ])
 def test_training_forward_and_gradients(method, cls, proc_dim, nc, hw, batch):
     spec, eng, params, img, proc, y = make_pair(method, cls, proc_dim, nc, hw, batch=batch)

@@ -13,7 +13,8 @@
 //             so O is rescaled in TMEM a handful of times per row block instead of once per tile.
 //   backward  dQ kernel (CTA = 128 query rows, loops over key tiles) and dK/dV kernel (CTA = 128 key rows, loops over query
 //             tiles, works on S^T so that P^T / dS^T are produced row-per-thread).  8 row warps: warps w and w+4 share a TMEM
-//             lane quadrant and split the 64 tile columns.  No atomics.
+//             lane quadrant and split the tile columns.  No atomics.  Two families: 64-wide score tiles, one CTA per 128-row
+//             block (Tc <= 64, and the trace hooks), and persistent kernels with 128-wide score tiles (everything longer).
 //   operands  Q/K/V/dO must already be rounded to TF32 by their producers (EPI_ROUND); TMA moves raw fp32 words.
 #include <cuda.h>
 
@@ -580,7 +581,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_dkv_kernel(const __gr
 }
 
 // =====================================================================================================================
-// backward, 128-wide score tiles (Tc > 128).  The S / dP products above run with N = 64, where a 128 x N x 8 tcgen05.mma costs 48
+// backward, 128-wide score tiles (Tc > 64).  The S / dP products above run with N = 64, where a 128 x N x 8 tcgen05.mma costs 48
 // cycles whatever N is (shared-memory operand bandwidth: 4 KB of A per instruction; tools/micro/mma_rate.cu: N = 64 -> 48, N = 128 -> 64,
 // N = 256 -> 128 cycles); with N = 128 the same instruction count does twice the work at the tensor core's own rate.  TMEM holds
 // 512 columns, so only the S tile is double-buffered (2 x 128) and dP is single (128): the issuer orders the products so that the
@@ -1065,9 +1066,9 @@ cudaError_t run_bwd(const AttnP& p, float* Dd, int B, cudaStream_t s, cudaStream
   static const bool serial = getenv("CVT_ATTN_BWD_SERIAL") != nullptr;
   const bool fork = side && ev_fork && ev_join && !serial;
   if (fork) { CVT_CUDA(cudaEventRecord(ev_fork, s)); CVT_CUDA(cudaStreamWaitEvent(side, ev_fork, 0)); }
-  // 128-wide score tiles pay from two tiles up (CVT_ATTN_BWD_TILE=64 / 128 force one family; the trace build uses the 64-wide dQ kernel)
+  // 128-wide score tiles as soon as the 64-wide kernels would need two tiles (CVT_ATTN_BWD_TILE=64 / 128 force one family; the trace hooks live in the 64-wide dQ kernel)
   static const int force = getenv("CVT_ATTN_BWD_TILE") ? atoi(getenv("CVT_ATTN_BWD_TILE")) : 0;
-  const bool wide = force == 128 || (force != 64 && p.Tc > 128 && !p.trace);
+  const bool wide = force == 128 || (force != 64 && p.Tc > 64 && !p.trace);
   const bool wide_dkv = wide;
   // the wide kernels are persistent (one CTA per SM walking 128-row work items, w = blockIdx.x, + gridDim.x, ...).  Side by side still pays: the
   // CTAs of the first grid that drew one item less exit early, and the second grid's lowest-numbered CTAs (one item more) start there
