@@ -62,7 +62,7 @@ class ClockSampler(threading.Thread):
 
     def run(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "200"],
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             for line in self.proc.stdout:
                 if self.stop_flag:
@@ -291,6 +291,12 @@ class Bench:
         if sampler:
             sampler.start()
             sampler.wait_first(5.0)                                  # nvidia-smi's own start-up (driver locks) stays out of the timed region
+        if sampler:                                                  # extra warm-up steps until three clock samples were taken UNDER LOAD (at most 1.5 s)
+            n0, t0, i = len(sampler.samples), time.time(), 0
+            while len(sampler.samples) < n0 + 3 and time.time() - t0 < 1.5:
+                step(i); i += 1
+                if i % 8 == 0:
+                    eng.synchronize()
         for i in range(max(warmup, 3)):                              # the W warm-up steps run last, so the timed region starts on a busy, clocked-up GPU
             step(i)
         self.barrier()
