@@ -51,7 +51,9 @@ def test_flash_attention_forward_backward(B, T, heads):
     assert all(e < 2e-3 for e in errs.values()), errs
 
 
-@pytest.mark.parametrize("B,T,heads", [(64, 1024, 1), (64, 256, 2), (64, 65, 4), (160, 1024, 1)])
+# (40, 320, 2), (10, 1100, 2), (3, 1892, 3): odd tile counts (3, 9, 15) in the persistent 128-wide backward kernels - a CTA that walks several
+# work items then starts every other item on the opposite buffer / barrier parity; 2100 tokens: the dK/dV kernel's tile-by-tile statistics path
+@pytest.mark.parametrize("B,T,heads", [(64, 1024, 1), (64, 256, 2), (64, 65, 4), (160, 1024, 1), (40, 320, 2), (10, 1100, 2), (3, 1892, 3), (12, 2100, 1)])
 def test_flash_attention_many_ctas_per_sm(B, T, heads):
     """Grids of several hundred CTAs (two forward CTAs share an SM and its tensor pipe, several waves): the shapes of the benched batch-64
     step.  Every image carries the same Q/K/V/dO, so each must reproduce the fp64 result of image 0.  Round 2 found a race here that the
