@@ -160,3 +160,41 @@ def test_cvt_img_training_script(tmp_path):
     assert w.result("Weight", "Images", "cvt_model_weights_%s_dw_bn_clsTrue.h5" % FREQ).exists()
     check_history_sheet(w, model, w.result("Records", "Images", "cvt_records_%s_dw_bn_clsTrue.xlsx" % FREQ))
     assert model.predict([images[:3]]).shape == (3, 1)
+
+
+def test_gradcam_tool_script(tmp_path):
+    """tools/grad_cam_CvT.py:484-610 as written (validation split, load_weights, cv2 colour maps and overlays, predict, sklearn metrics), with the
+    one function that is TensorFlow through and through - make_gradcam_heatmap (:422-481: tf.data, tf.GradientTape) - supplied by keras_api."""
+    w = World(tmp_path)
+    K = w.K
+    from tqdm import tqdm
+    K.configure(projection="dw_bn", cls_token=False, variant="gradcam")            # the constants of tools/grad_cam_CvT.py:25-31 and its model variant
+    try:
+        calls = []
+
+        def heatmaps(img_array, proc_array, model, last_conv_layer_name, **kw):
+            h = K.make_gradcam_heatmap(img_array, proc_array, model, last_conv_layer_name, **kw)
+            calls.append((last_conv_layer_name, h))
+            return h
+
+        noop = lambda *a, **kw: None
+        w.ns.update(cls_token_switch=False, last_conv_layer_name="stage3_transformer", make_gradcam_heatmap=heatmaps, tqdm=tqdm,
+                    plt=types.SimpleNamespace(figure=noop, subplot=noop, imshow=noop, axis=noop, title=noop, savefig=noop, clf=noop, close=noop))
+        preprocess, run = w.run(os.path.join("..", "tools", "grad_cam_CvT.py"), "preprocess_data", "test_and_save_results")
+        labels_dict, proc_scaled, images, valid_dict, count = preprocess(w.excel_data, w.excel_process, 1, GROUPS, 1, PIECES, LAYERS, H, W)
+        # the weights the tool loads: a model of the same variant, saved under the name the tool expects (:513)
+        trained = w.ns["create_cvt_model"](H, W, 1, 5, 1)
+        wdir = w.result("Weight", "Images & Parameters")
+        wdir.mkdir(parents=True)
+        trained.save_weights(str(wdir / ("cvt_model_weights_%s.h5" % FREQ)))
+
+        run(FREQ, labels_dict, proc_scaled, images, valid_dict, count)
+
+        assert len(calls) == 1 and calls[0][0] == "stage3_transformer"
+        h = calls[0][1]
+        n_val = 2 * LAYERS
+        assert h.shape[0] == n_val and h.ndim == 3 and np.nanmax(h) <= 1.0 + 1e-6      # one normalised map per validation image, [n, h3, w3]
+        assert w.result("Plots", "Heatmap").is_dir()
+        assert len(w.made) == 2 and w.made[1].cfg.stages[0].with_cls_token == w.made[0].cfg.stages[0].with_cls_token
+    finally:
+        K.configure(projection="dw_bn", cls_token=True, variant="reference")

@@ -101,6 +101,33 @@ def test_h5_weights_roundtrip_between_models(tmp_path, cls, method, proc):
         other.load_weights(p)
 
 
+@pytest.mark.parametrize("variant,method,cls", [("gradcam", "dw_bn", False), ("gradcam", "linear", True), ("model_plot", "dw_bn", True), ("model_plot", "avg", False)])
+def test_h5_weights_roundtrip_of_the_tools_model_variants(tmp_path, variant, method, cls):
+    """tools/grad_cam_CvT.py:315-349 / tools/model_plot.py:254-300: proj_q/k/v built but never applied (Keras never creates their weights), a Dense
+    inside the 'linear' Projection, heads without a LayerNormalization.  The layout used to list the reference model's weights only and
+    save_weights raised KeyError on these models (found by running the tool script itself, tests/test_reference_script_dropin.py)."""
+    def make(seed):
+        K.configure(projection=method, cls_token=cls, variant=variant)
+        try:
+            return K.create_cvt_model(32, 32, 1, 5, 1, engine_factory=OracleEngine, seed=seed, max_batch=2)
+        finally:
+            K.configure(projection="dw_bn", cls_token=True, variant="reference")
+    m = make(1)
+    rng = np.random.default_rng(6)
+    m.set_weights_dict({p["name"]: rng.standard_normal(p["shape"]).astype(np.float32) for p in m.engine.param_infos()})
+    flat = [c for _, ws in m.keras_layout() for _, c in ws]
+    assert sorted(flat) == sorted(p["name"] for p in m.engine.param_infos())      # everything the engine holds, once
+    p = str(tmp_path / "w.h5")
+    m.save_weights(p)
+    m2 = make(2)
+    m2.load_weights(p)
+    a, b = m.get_weights_dict(), m2.get_weights_dict()
+    assert a.keys() == b.keys() and all(np.array_equal(a[k], b[k]) for k in a)
+    ref = _model()                                                                 # the reference model is another architecture: refused
+    with pytest.raises(ValueError):
+        ref.load_weights(p)
+
+
 def test_loading_matches_by_position_not_by_auto_numbered_names(tmp_path):
     """A file written by a Keras process whose global name counters stood elsewhere: dense_17.., layer_normalization_41."""
     m = _model()

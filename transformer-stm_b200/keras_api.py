@@ -447,8 +447,13 @@ class Model:
                            (ca + b + "_proj/batch_normalization/beta:0", t + "/attn/%s_proj/bn/beta" % b)]
                     nt += [(ca + b + "_proj/batch_normalization/moving_mean:0", t + "/attn/%s_proj/bn/moving_mean" % b),
                            (ca + b + "_proj/batch_normalization/moving_variance:0", t + "/attn/%s_proj/bn/moving_variance" % b)]
-            for b in "qkv":
-                d = "dense%s" % ("_%d" % dn if dn else ""); dn += 1
+            if st.qkv_method == "linear_dense":              # tools/grad_cam_CvT.py:103-104: the 'linear' Projection there is a Dense(dim)
+                for b in "qkv":
+                    d = "dense%s" % ("_%d" % dn if dn else ""); dn += 1
+                    tr += [(ca + b + "_proj/" + d + "/kernel:0", t + "/attn/%s_proj/dense/kernel" % b),
+                           (ca + b + "_proj/" + d + "/bias:0", t + "/attn/%s_proj/dense/bias" % b)]
+            for b in "qkv":                                  # (built but never called in the tools' variants: Keras then never creates their weights -
+                d = "dense%s" % ("_%d" % dn if dn else ""); dn += 1      #  filtered out below - but the name counter has moved on)
                 tr += [(ca + d + "/kernel:0", t + "/attn/proj_%s/kernel" % b), (ca + d + "/bias:0", t + "/attn/proj_%s/bias" % b)]
             for b in ("query", "key", "value", "attention_output"):
                 tr += [(ca + "multi_head_attention/%s/kernel:0" % b, t + "/attn/mha/%s/kernel" % b),
@@ -468,6 +473,14 @@ class Model:
                 out.append((nm, [(nm + "/kernel:0", nm + "/kernel"), (nm + "/bias:0", nm + "/bias")]))
             out.append(("concatenate", []))
         out.append(("Final_Dense", [("Final_Dense/kernel:0", "Final_Dense/kernel"), ("Final_Dense/bias:0", "Final_Dense/bias")]))
+        # the model variants of the tools (configure(variant=...)) lack some of these weights: proj_q/k/v never applied, heads without a
+        # LayerNormalization.  What the engine does not hold is not in the file; everything it holds has to be.
+        have = [p["name"] for p in self.engine.param_infos()]
+        out = [(ln, [(kn, cn) for kn, cn in ws if cn in set(have)]) for ln, ws in out]
+        listed = [cn for _, ws in out for _, cn in ws]
+        if sorted(listed) != sorted(have):
+            missing = sorted(set(have) - set(listed))
+            raise RuntimeError("keras_layout: no Keras-2 position known for %s" % (missing or "duplicated entries"))
         return out
 
     def save_weights(self, filepath, overwrite=True, save_format=None, **kw):
