@@ -1,5 +1,5 @@
 """The drop-in claim of INTEGRATION.md, executed: the reference's OWN functions - `preprocess_data`, `lr_scheduler`, `train_and_save_model`
-of models/CvT(Par).py, CvT(Par)(many).py and CvT(Img).py, `test_and_save_results` and `save_predictions_to_excel` of models/CvT_test(Par).py -
+of models/CvT(Par).py, CvT(Par)(many).py and CvT(Img).py, `test_and_save_results` and `save_predictions_to_excel` of the three CvT_test scripts and of tools/grad_cam_CvT.py -
 are taken from /root/reference as they lie there (parsed, compiled and run from those files: nothing of them is copied into this repository)
 and run against transformer_stm_b200.keras_api in place of TensorFlow / Keras: real cv2 on JPEG files written to a temporary tree, real pandas
 frames for the two Excel sheets, real sklearn scalers and metrics; `create_cvt_model`, `keras.optimizers.Adam`,
@@ -148,6 +148,13 @@ def test_cvt_par_many_script_repeats(tmp_path):
         assert w.result("Weight", "Images & Parameters", "cvt_model_weights_%s_%d_dw_bn_clsTrue.h5" % (FREQ, t)).exists()
         check_history_sheet(w, w.made[-1], w.result("Records", "Images & Parameters", "cvt_records_%s_%d_dw_bn_clsTrue.xlsx" % (FREQ, t)))
     assert len(w.made) == 2
+    # models/CvT_test(Par)(many).py:450-530 for the second repeat
+    test_results, _ = w.run("CvT_test(Par)(many).py", "test_and_save_results", "save_predictions_to_excel")
+    test_results(FREQ, *data)
+    sheet = w.xlsxlite.read_xlsx(str(w.result("Excel", "Images & Parameters", "Predictions_Metrics_%s_2.xlsx" % FREQ)))
+    labels_dict, proc_scaled, images, valid_dict, _ = data
+    val_idx = [i * LAYERS + k for i, v in enumerate(valid_dict) if v in (0, 5) for k in range(LAYERS)]
+    np.testing.assert_allclose(np.asarray(sheet["Predictions"], dtype=np.float64), w.made[1].predict([images[val_idx], proc_scaled[val_idx]]).ravel(), rtol=1e-6)
 
 
 def test_cvt_img_training_script(tmp_path):
@@ -160,6 +167,13 @@ def test_cvt_img_training_script(tmp_path):
     assert w.result("Weight", "Images", "cvt_model_weights_%s_dw_bn_clsTrue.h5" % FREQ).exists()
     check_history_sheet(w, model, w.result("Records", "Images", "cvt_records_%s_dw_bn_clsTrue.xlsx" % FREQ))
     assert model.predict([images[:3]]).shape == (3, 1)
+    # models/CvT_test(Img).py:417-480
+    test_results, _ = w.run("CvT_test(Img).py", "test_and_save_results", "save_predictions_to_excel")
+    test_results(FREQ, labels_dict, images, valid_dict, count)
+    sheet = w.xlsxlite.read_xlsx(str(w.result("Excel", "Images", "Predictions_Metrics_%s.xlsx" % FREQ)))
+    assert list(sheet) == ["Predictions", "Actual", "Errors(%)", "Train mounts", "Test mounts", "R2 Score", "MSE", "MAE"]
+    val_idx = [i * LAYERS + k for i, v in enumerate(valid_dict) if v in (0, 5) for k in range(LAYERS)]
+    np.testing.assert_allclose(np.asarray(sheet["Predictions"], dtype=np.float64), model.predict(images[val_idx]).ravel(), rtol=1e-6)
 
 
 def test_gradcam_tool_script(tmp_path):
