@@ -4,15 +4,30 @@ TEST INFRASTRUCTURE ONLY.  Nothing under ``transformer-stm_b200/`` (the product)
 may import this file; only ``tests/``, ``__graft_entry__.smoke()`` and the
 ``cpu_baseline`` / ``--impl reference`` legs of ``bench.py`` do.
 
-PARITY UNPINNED.  The reference's arithmetic lives in TensorFlow 2.x / Keras 2.x,
-an un-vendored and un-pinned dependency (`models/CvT(Par).py:1-3`; the README points
-at a requirements.txt that does not exist).  TensorFlow cannot be imported or
-installed in the build container or on the GPU box and the reference ships neither
-tests nor golden vectors nor weights for this path, so this restatement follows the
-*published* Keras-2 layer definitions at the reference's own call sites.  It is
-self-checked by (tests/test_oracle.py): fp64 finite-difference gradients, independent
-re-derivations of every layer with torch.nn.functional library ops, and the shape
-goldens of `model_plot_Cls.png` / `model_plot_NoCls.png`.
+PARITY: PINNED TO THE REFERENCE'S MODEL SOURCE, UNPINNED AGAINST TENSORFLOW'S KERNELS.
+The reference's arithmetic lives in TensorFlow 2.x / Keras 2.x, an un-vendored and
+un-pinned dependency (`models/CvT(Par).py:1-3`; the README points at a requirements.txt
+that does not exist).  TensorFlow cannot be imported or installed in the build container
+or on the GPU box and the reference ships neither tests nor golden vectors nor weights
+for this path.  Two anchors instead:
+  (1) the reference's own call sites, EXECUTED: the model classes and create_cvt_model of
+      models/CvT(Par).py, CvT(Img).py, CvT(Par)(many).py, CvT_test(Par)*.py, tools/grad_cam_CvT.py
+      and tools/model_plot.py are compiled from /root/reference unmodified and run over
+      oracle/mini_keras.py (a float64 define-by-run stand-in for the Keras layers they use);
+      predictions and the gradients of one Keras train step (batch-statistics BatchNorm,
+      dropout with given keep masks, MSE) agree with this file to 1e-10
+      (tests/test_oracle_vs_reference_source.py; vectors committed as tests/golden/refsrc_*.npz
+      by tests/golden/make_refsrc_golden.py and checked wherever the tests run,
+      tests/test_refsrc_golden.py).  That pins the WIRING - which layer feeds which, variable
+      creation order, the dead ConvEmbed LayerNorm, norm1 used twice, attention(q, v, k), the
+      cls-token bypass, every head - to what the reference source does when run.
+  (2) the arithmetic INSIDE each Keras layer follows the *published* Keras-2 layer
+      definitions (restated here and, independently, in oracle/mini_keras.py) and is
+      self-checked by (tests/test_oracle.py): fp64 finite-difference gradients, independent
+      re-derivations of every layer with torch.nn.functional library ops, and the shape
+      goldens of `model_plot_Cls.png` / `model_plot_NoCls.png`.  No number produced by
+      TensorFlow itself exists here: at that level parity stays unpinned
+      (baseline/run_tf_reference.py closes it on a box that has TensorFlow).
 
 What each function follows (paths relative to /root/reference):
   conv_same ............ ConvEmbed.call        models/CvT(Par).py:194-217  (LN branch dead: :209 vs :304)

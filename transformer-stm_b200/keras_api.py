@@ -570,6 +570,11 @@ def create_cvt_model(image_height, image_width, num_channels, proc_dim=None, num
     cfg = CvtConfig.from_spec_dict(spec, int(image_height), int(image_width), int(num_channels), int(proc_dim or 0), int(num_classes),
                                    precision=precision, max_batch=int(max_batch), device=int(device))
     if model_variant == "gradcam":       # tools/grad_cam_CvT.py:315-349
+        if any(st.qkv_method == "avg" for st in cfg.stages):
+            # found by executing the tool's own source (tests/test_oracle_vs_reference_source.py): its ConvAttention hands q the 'linear'
+            # Projection when the method is 'avg' (:141), and in this script 'linear' is a Dense(dim) (:103) - q through a Dense, k / v pooled
+            raise NotImplementedError("tools/grad_cam_CvT.py with projection_method='avg' mixes a Dense q-projection with average-pooled k / v: "
+                                      "that combination is not implemented (dw_bn and linear are)")
         for st in cfg.stages:
             st.with_cls_token = bool(cls_token_switch)
             if st.qkv_method == "linear":
