@@ -429,7 +429,7 @@ class Bench:
                 "tensors_over_1e-3": int(sum(e > 1e-3 for e in over)), "tensors": len(over),
                 "norm": "max|a-b| / max|b| per tensor (gradient floor 1e-3 of the largest gradient); grad_l2_all = ||a-b|| / ||b|| over all gradients",
                 "contract": "north_star asks rtol 1e-3; the fp32 mode meets it, this TF32 tensor-core mode is measured here (DESIGN.md 4)",
-                "oracle": "torch-CPU port, parity unpinned"}
+                "oracle": "torch-CPU port; pinned to the reference's model source executed over oracle/mini_keras.py (tests/golden/refsrc_*.npz), unpinned against TensorFlow's kernels"}
 
     def close(self):
         self.eng.close()
