@@ -9,7 +9,8 @@ tools/grad_cam_CvT.py, tools/model_plot.py), compiled from /root/reference as th
 (which layer feeds which, the dead ConvEmbed LayerNorm, norm1 used twice, attention(q, v, k), the cls-token bypass, the heads) is
 checked against what the reference source does when run, not against a reading of it (tests/test_oracle_vs_reference_source.py,
 tests/golden/make_refsrc_golden.py).  TensorFlow itself is not available here: what stays restated is the arithmetic INSIDE each Keras
-layer, written below from the Keras-2 layer definitions and checked layer by layer against torch.nn.functional in tests/test_oracle.py:
+layer, written below from the Keras-2 layer definitions - independently of oracle/cvt_oracle.py, which restates the same definitions, is
+checked layer by layer against torch.nn.functional in tests/test_oracle.py, and agrees with this file to 1e-10:
   Dense                 y = x W + b                                                  keras/layers/core/dense.py
   LayerNormalization    biased variance over the last axis, epsilon default 1e-3    keras/layers/normalization/layer_normalization.py
   BatchNormalization    epsilon 1e-3, momentum 0.99; batch statistics (biased variance) over N, H, W when training, moving ones otherwise
