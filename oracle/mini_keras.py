@@ -39,6 +39,7 @@ class session:
         self.weights, self.inputs, self.training = list(weights), inputs, training
         self.masks = list(dropout_masks) if dropout_masks is not None else None
         self.pos, self.mask_pos, self.taken, self.bn_batch_stats = 0, 0, [], []
+        self.captured = {}                                   # outputs of named layers (what `model.get_layer(name).output` stands for)
 
     def __enter__(self):
         global _S
@@ -76,7 +77,10 @@ class Layer:
         return _S.next_weight(shape, "%s.add_weight(%s)" % (type(self).__name__, name))
 
     def __call__(self, *args, **kw):
-        return self.call(*args, **kw)
+        out = self.call(*args, **kw)
+        if self.name is not None and _S is not None:
+            _S.captured[self.name] = out
+        return out
 
     def get_config(self):
         return {}
@@ -318,6 +322,79 @@ tf = types.SimpleNamespace(
     expand_dims=lambda x, axis: x.unsqueeze(axis),
     cast=lambda x, dtype: x,
     float32="float32", nn=nn, keras=keras)
+
+
+# ---- the slice of tf that tools/grad_cam_CvT.py:422-481 (make_gradcam_heatmap) uses on top of the above ---------------------------------
+class _Ref:
+    """A symbolic tensor of a ReferenceModel: its final output, or the output of one named layer."""
+
+    def __init__(self, model, layer):
+        self.model, self.layer = model, layer
+
+
+class ReferenceModel:
+    """What `create_cvt_model(...)` stands for when the model has to be called more than once (Grad-CAM): every call re-executes the
+    reference's create_cvt_model on the given inputs with the same weights."""
+
+    def __init__(self, path, script_globals, args, weights, input_names=("Image_inputs", "Proc_inputs")):
+        self.path, self.script_globals, self.args, self.weights = path, dict(script_globals), list(args), list(weights)
+        self.inputs = list(input_names)
+        self.output = _Ref(self, None)
+
+    def get_layer(self, name):
+        return types.SimpleNamespace(output=_Ref(self, name))
+
+    def run(self, tensors, layers_wanted):
+        inputs = dict(zip(self.inputs, tensors))
+        out, s = run_reference_model(self.path, self.script_globals, self.args, self.weights, inputs)
+        return [out if l is None else s.captured[l] for l in layers_wanted]
+
+
+class _SubModel:
+    def __init__(self, inputs=None, outputs=None):
+        assert all(isinstance(o, _Ref) for o in outputs) and len({id(o.model) for o in outputs}) == 1
+        self.model, self.wanted = outputs[0].model, [o.layer for o in outputs]
+
+    def __call__(self, tensors):
+        tensors = [t.detach().clone().requires_grad_(True) for t in tensors]      # so that an intermediate output is part of a differentiable graph
+        return self.model.run(tensors, self.wanted)
+
+
+class GradientTape:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        return False
+
+    def gradient(self, target, source):                      # tf: the gradient of sum(target)
+        return torch.autograd.grad(target.sum(), source, retain_graph=True, allow_unused=True)[0]
+
+
+class _Dataset:
+    def __init__(self, tensors):
+        self.tensors, self.bs = tensors, 1
+
+    def batch(self, n):
+        self.bs = int(n)
+        return self
+
+    def __iter__(self):
+        n = self.tensors[0].shape[0]
+        for i in range(0, n, self.bs):
+            yield tuple(t[i:i + self.bs] for t in self.tensors)
+
+    def __len__(self):
+        return -(-self.tensors[0].shape[0] // self.bs)
+
+
+tf.GradientTape = GradientTape
+tf.data = types.SimpleNamespace(Dataset=types.SimpleNamespace(from_tensor_slices=lambda ts: _Dataset([torch.as_tensor(t, dtype=torch.float64) for t in ts])))
+tf.config = types.SimpleNamespace(experimental=types.SimpleNamespace(get_memory_usage=lambda dev: 0))
+tf.reduce_sum = lambda x, axis=None: x.sum(axis) if axis is not None else x.sum()
+tf.maximum = lambda x, y: torch.clamp_min(x.detach(), float(y))      # (only used for the heat-map post-processing: no gradient wanted)
+tf.math = types.SimpleNamespace(reduce_max=lambda x: x.detach().max())
+keras.models = types.SimpleNamespace(Model=_SubModel)
 
 
 # ---- running a reference script's model section ------------------------------------------------------------------------------------

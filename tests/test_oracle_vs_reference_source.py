@@ -161,3 +161,35 @@ def test_model_plot_tool_variant_matches_its_source(cls):
     got, _ = run("tools/model_plot.py", spec, params, img, proc, method=method, cls=cls)
     np.testing.assert_allclose(got.numpy(), want, rtol=1e-10, atol=1e-10)
     assert not any(n.startswith("head_norm") for n, _, _ in O.param_specs(spec))
+
+
+@pytest.mark.parametrize("method", ["dw_bn", "linear"])
+def test_gradcam_heatmaps_match_the_tools_own_function(method):
+    """tools/grad_cam_CvT.py:422-481 make_gradcam_heatmap as written (tf.data batches, a sub-model to the named block's output, GradientTape,
+    pooled gradients, relu / max normalisation) over the tool's own model source - against oracle.gradcam and keras_api.make_gradcam_heatmap."""
+    import ast
+    from tqdm import tqdm
+    from transformer_stm_b200 import keras_api as K
+    from tests.fake_engine import OracleEngine
+    path = os.path.join(REF, "tools/grad_cam_CvT.py")
+    spec = O.gradcam_spec(False, method, proc_dim=5, num_classes=1, image_h=32, image_w=32)
+    params = O.init_params(spec, 21, "parity")
+    img, proc, _ = O.synthetic_batch(spec, 3, 8)
+    tree = ast.parse(open(path, encoding="utf-8").read(), path)
+    fn = [n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name == "make_gradcam_heatmap"]
+    ns = dict(tf=MK.tf, np=np, tqdm=tqdm, print=lambda *a, **k: None)
+    exec(compile(ast.Module(body=fn, type_ignores=[]), path, "exec"), ns)
+    model = MK.ReferenceModel(path, dict(projection_method=method, cls_token_switch=False), [32, 32, 1, 5, 1], weights_of(spec, params))
+    heat = ns["make_gradcam_heatmap"](img[..., 0].astype(np.float64), proc.astype(np.float64), model, "stage3_transformer")      # [n, h3, w3]
+    assert heat.shape == (3, 2, 2)
+    for i in range(3):
+        ref, _, _ = O.gradcam(spec, params, img[i:i + 1], proc[i:i + 1], "s3.out")
+        np.testing.assert_allclose(heat[i], ref[0], rtol=1e-8, atol=1e-10)
+    K.configure(projection=method, cls_token=False, variant="gradcam")
+    try:
+        m = K.create_cvt_model(32, 32, 1, 5, 1, engine_factory=OracleEngine, max_batch=2)
+        m.set_weights_dict(params)
+        mine = K.make_gradcam_heatmap(img[..., 0], proc, m, "stage3_transformer")
+        np.testing.assert_allclose(mine, heat, rtol=1e-4, atol=1e-6)
+    finally:
+        K.configure(projection="dw_bn", cls_token=True, variant="reference")
