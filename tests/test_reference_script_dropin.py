@@ -137,6 +137,24 @@ def test_cvt_par_training_script_then_the_test_script(tmp_path):
     np.testing.assert_allclose(np.asarray(sheet["Predictions"], dtype=np.float64), want, rtol=1e-6)
     np.testing.assert_allclose(np.asarray(sheet["Actual"], dtype=np.float64), labels_dict[val_idx], rtol=1e-12)
 
+    # the consumer of that sheet, tools/Compare_r.py:12-62 as written: reads 'R2 Score' of Sheet1 and plots it (pandas' reader needs openpyxl too:
+    # read_excel goes through xlsxlite; the plot calls are recorded instead of drawn)
+    import pandas
+    from sklearn.metrics import r2_score
+    plotted = []
+    w.ns["pd"].read_excel = lambda path, sheet_name=None: pandas.DataFrame({k: pandas.Series(v, dtype="float64") for k, v in w.xlsxlite.read_xlsx(str(path)).items()})
+    noop = lambda *a, **kw: None
+    w.ns["plt"] = types.SimpleNamespace(figure=noop, plot=lambda x, yv, **kw: plotted.append((list(x), list(yv), kw.get("label"))), title=noop, xlabel=noop,
+                                        ylabel=noop, legend=noop, grid=noop, savefig=noop, close=noop)
+    from collections import OrderedDict
+    w.ns["OrderedDict"] = OrderedDict
+    w.ns["script_dir"] = str(tmp_path / "tools")
+    (tmp_path / "tools").mkdir()
+    collect, = w.run(os.path.join("..", "tools", "Compare_r.py"), "collect_data_and_plot")
+    collect(["CvT"], [FREQ.split("_")[1]], [FREQ])
+    assert len(plotted) == 1 and plotted[0][0] == [FREQ.split("_")[0]] and plotted[0][2] == "CvT"
+    assert plotted[0][1][0] == pytest.approx(r2_score(labels_dict[val_idx], want), rel=1e-6)
+
 
 def test_cvt_par_many_script_repeats(tmp_path):
     w = World(tmp_path)
