@@ -291,15 +291,9 @@ class Bench:
         if sampler:
             sampler.start()
             sampler.wait_first(5.0)                                  # nvidia-smi's own start-up (driver locks) stays out of the timed region
-        # extra warm-up steps until three clock samples were taken UNDER LOAD (at most 1.5 s).  Only where the step count may differ between ranks:
-        # a data-parallel train step is collective (every rank has to issue the same number of steps - rank 0 alone running ahead here trapped
-        # the peer-memory tail kernel of its step at 8 GPUs and hung the other ranks), an inference forward is not
-        if sampler and (self.world == 1 or not train):
-            n0, t0, i = len(sampler.samples), time.time(), 0
-            while len(sampler.samples) < n0 + 3 and time.time() - t0 < 1.5:
-                step(i); i += 1
-                if i % 8 == 0:
-                    eng.synchronize()
+        # (No rank-dependent number of extra steps here: a data-parallel train step is collective.  A loop that kept rank 0 - the only rank with a
+        #  sampler - stepping until it had three clock samples let it run ahead at 8 GPUs: its peer-memory tail kernel trapped after the bounded
+        #  spin and the other ranks hung.  tests/test_bench_protocol.py pins the step counts.)
         for i in range(max(warmup, 3)):                              # the W warm-up steps run last, so the timed region starts on a busy, clocked-up GPU
             step(i)
         self.barrier()

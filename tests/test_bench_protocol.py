@@ -126,20 +126,20 @@ def test_every_rank_issues_the_same_number_of_train_steps(world):
     assert counts[0] == 2 * 4 + 5 + 20                            # graph priming of the four buffer sets, W warm-up steps, K timed steps
 
 
-def test_single_gpu_run_keeps_stepping_until_clock_samples_were_taken_under_load():
+def test_single_gpu_run_counts_only_the_timed_steps():
     mod = load_bench()
     b = make_bench(mod, 1, 0)
     s = FakeSampler()
     r = b.timed(True, steps=20, warmup=5, sampler=s)
-    assert b.eng.train_steps > 2 * 4 + 5 + 20                     # the extra, untimed warm-up steps
-    assert len(s._list) >= 4                                       # first sample + three under load
+    assert s.started and b.eng.train_steps == 2 * 4 + 5 + 20
     assert r["value"] == pytest.approx(64 * 20 / (20 * 1.5e-3))
     assert r["launches"] == 96 * 20                                # only the timed steps are counted
+    assert r["per_step_ms"]["median"] == pytest.approx(1.5) and len(r["per_step_ms"]["all"]) == 20
 
 
 def test_inference_ranks_are_independent():
     mod = load_bench()
     b = make_bench(mod, 8, 0)
     r = b.timed(False, steps=10, warmup=3, sampler=FakeSampler())
-    assert b.eng.train_steps == 0 and b.eng.forwards >= 2 * 4 + 3 + 10
+    assert b.eng.train_steps == 0 and b.eng.forwards == 2 * 4 + 3 + 10
     assert r["launches"] == 27 * 10
