@@ -1,5 +1,5 @@
-"""Self-checks that pin the oracle as far as it can be pinned without TensorFlow
-(parity unpinned, see oracle/cvt_oracle.py header)."""
+"""Self-checks of the arithmetic inside each layer of the oracle (the level that stays unpinned without TensorFlow; the wiring is pinned
+to the reference's own model source by tests/test_oracle_vs_reference_source.py - see oracle/cvt_oracle.py header)."""
 import math
 
 import numpy as np
